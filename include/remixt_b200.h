@@ -1,0 +1,189 @@
+/*
+ * remixt_b200 -- C-ABI of the B200-native ReMixT variational-inference core.
+ *
+ * This is the drop-in boundary for the reference's Cython extension `remixt/bpmodel.pyx`
+ * (class RemixtModel and the module functions sum_product / max_product).  Every entry
+ * point below names the reference interface it replaces (paths relative to the reference
+ * tree).  Plain pointers and sizes only; all pointers are HOST pointers unless stated;
+ * all arrays are C-contiguous, float64 / int64 exactly as the reference's typed buffers.
+ *
+ * Every function returns an rmx_status.  On failure rmx_last_error() returns the message;
+ * RMX_ERR_VALUE maps to Python ValueError, RMX_ERR_ASSERT to AssertionError (the two
+ * exception classes the reference raises on this path, bpmodel.pyx:208,270,336,345,
+ * 384,392,722,739,829 and :934-962).
+ *
+ * There is no CPU fallback behind this interface: every compute entry point launches
+ * sm_100a kernels on the handle's device and fails with RMX_ERR_CUDA if it cannot.
+ */
+#ifndef REMIXT_B200_H
+#define REMIXT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rmx_model_s* rmx_handle;
+
+typedef enum {
+    RMX_OK = 0,
+    RMX_ERR_CUDA = 1,        /* CUDA runtime failure (no device, launch error, OOM)      */
+    RMX_ERR_VALUE = 2,       /* reference raises ValueError                              */
+    RMX_ERR_ASSERT = 3,      /* reference `assert` fails (NaN checks, bpmodel.pyx:934-962) */
+    RMX_ERR_UNSUPPORTED = 4, /* input outside what the device layout supports            */
+    RMX_ERR_ARG = 5          /* bad id / size passed through this C-ABI                  */
+} rmx_status;
+
+/* Constructor arguments: RemixtModel.__cinit__ (bpmodel.pyx:461-476), same order/meaning. */
+typedef struct {
+    int32_t num_clones;            /* M  (bpmodel.pyx:462) */
+    int32_t num_segments;          /* N1 (bpmodel.pyx:463) */
+    int32_t num_breakpoints;       /* K  (bpmodel.pyx:464) */
+    int32_t normal_contamination;  /* bint (bpmodel.pyx:465) */
+    int32_t num_cn_states;         /* S = cn_states.shape[1] */
+    int32_t num_brk_states;        /* B = brk_states.shape[0] */
+    int32_t device;                /* CUDA device ordinal the model lives on */
+    int32_t reserved;
+    const int64_t* cn_states;      /* (N1,S,M,2) (bpmodel.pyx:466); may be NULL if the compact pair below is given */
+    const int64_t* cn_table;       /* optional compact form: (S,M,2), clone 0 row ignored */
+    const int64_t* normal_copies;  /* optional compact form: (N1,2) = cn_states[n,:,0,:]  */
+    const int64_t* brk_states;     /* (B,M)      (bpmodel.pyx:467) */
+    const double* h_init;          /* (M)        (bpmodel.pyx:468) */
+    const double* l;               /* (N1)       (bpmodel.pyx:469) */
+    const double* x;               /* (N1)       (bpmodel.pyx:470) */
+    const double* y;               /* (N1,2)     (bpmodel.pyx:471) */
+    const int64_t* is_telomere;        /* (N1)   (bpmodel.pyx:472) */
+    const int64_t* breakpoint_idx;     /* (N1)   (bpmodel.pyx:473) */
+    const int64_t* breakpoint_orient;  /* (N1)   (bpmodel.pyx:474) */
+    double transition_penalty;     /* (bpmodel.pyx:475), stored as fabs() (:534) */
+    double divergence_weight;      /* (bpmodel.pyx:476), stored as fabs() (:535) */
+} rmx_desc;
+
+/* Array attributes (`cdef public` memoryviews, bpmodel.pyx:405-442). */
+typedef enum {
+    RMX_A_H = 0,                    /* f64 (M)        :442 */
+    RMX_A_P_BREAKPOINT = 1,         /* f64 (K,B)      :420 */
+    RMX_A_P_ALLELE_SWAP = 2,        /* f64 (N1,2)     :429 */
+    RMX_A_P_OUTLIER_TOTAL = 3,      /* f64 (N1,2)     :430 */
+    RMX_A_P_OUTLIER_ALLELE = 4,     /* f64 (N1,2)     :431 */
+    RMX_A_POSTERIOR_MARGINALS = 5,  /* f64 (N1,S)     :426 */
+    RMX_A_FRAMELOGPROB = 6,         /* f64 (N1,S)     :423 */
+    RMX_A_TOTAL_LIKELIHOOD_MASK = 7,  /* i64 (N1)     :439 */
+    RMX_A_ALLELE_LIKELIHOOD_MASK = 8, /* i64 (N1)     :440 */
+    RMX_A_LOG_TRANSMAT = 9,           /* f64 (N1-1,S,S) :424, get only, materialised on demand */
+    RMX_A_CACHED_LOG_TRANSMAT = 10,   /* f64 (N1-1,S,S) :425, get only, materialised on demand */
+    RMX_A_JOINT_POSTERIOR_MARGINALS = 11, /* f64 (N1-1,S,S) :427, get only, materialised on demand */
+    RMX_A_L = 12, RMX_A_X = 13, RMX_A_Y = 14,   /* f64, get only (:436-438) */
+    RMX_A_STATE_PATH = 15             /* i64 (N1): Viterbi path of the last rmx_infer_cn, get only */
+} rmx_array_id;
+
+/* Scalar attributes (`cdef public` doubles / ints, bpmodel.pyx:417-456). */
+typedef enum {
+    RMX_S_NEGBIN_R_0 = 0, RMX_S_NEGBIN_R_1 = 1, RMX_S_NEGBIN_HDEL_MU = 2,
+    RMX_S_NEGBIN_HDEL_R_0 = 3, RMX_S_NEGBIN_HDEL_R_1 = 4,
+    RMX_S_BETABIN_M_0 = 5, RMX_S_BETABIN_M_1 = 6, RMX_S_BETABIN_LOH_P = 7,
+    RMX_S_BETABIN_LOH_M_0 = 8, RMX_S_BETABIN_LOH_M_1 = 9,
+    RMX_S_PRIOR_OUTLIER_TOTAL = 10, RMX_S_PRIOR_OUTLIER_ALLELE = 11,
+    RMX_S_TRANSITION_PENALTY = 12, RMX_S_DIVERGENCE_WEIGHT = 13,
+    RMX_S_TRANSITION_MODEL = 14, RMX_S_HMM_LOG_NORM_CONST = 15,
+    RMX_S_COUNT_ = 16
+} rmx_scalar_id;
+
+/* Coordinate updates (cpdef methods, bpmodel.pyx:898-1042). */
+typedef enum {
+    RMX_U_ALLELE_SWAP = 0,    /* update_p_allele_swap   :1025 */
+    RMX_U_CN = 1,             /* update_p_cn            :921  */
+    RMX_U_BREAKPOINT = 2,     /* update_p_breakpoint    :964  */
+    RMX_U_OUTLIER_TOTAL = 3,  /* update_p_outlier_total :987  */
+    RMX_U_OUTLIER_ALLELE = 4, /* update_p_outlier_allele:1005 */
+    RMX_U_FRAMELOGPROB = 5    /* update_framelogprob    :898  */
+} rmx_update_id;
+
+/* Per-(n,s) scalar accessors (cpdef, bpmodel.pyx:686-896). */
+typedef enum {
+    RMX_E_EXPECTED_TOTAL_READS = 0,           /* :686  -> out[0]      */
+    RMX_E_EXPECTED_TOTAL_READS_PARTIAL_H = 1, /* :700  -> out[0..M)   */
+    RMX_E_EXPECTED_ALLELE_RATIO = 2,          /* :709  -> out[0]      */
+    RMX_E_EXPECTED_ALLELE_RATIO_PARTIAL_H = 3,/* :726  -> out[0..M)   */
+    RMX_E_LOG_PRIOR_CN = 4,                   /* :746  -> out[0]      */
+    RMX_E_LOG_LIKELIHOOD_TOTAL = 5,           /* :751  (n,s,u)        */
+    RMX_E_LOG_LIKELIHOOD_TOTAL_PARTIAL_H = 6, /* :778  (n,s,u)        */
+    RMX_E_LOG_LIKELIHOOD_ALLELE = 7,          /* :809  (n,s,v,w)      */
+    RMX_E_LOG_LIKELIHOOD_ALLELE_PARTIAL_H = 8 /* :855  (n,s,v,w)      */
+} rmx_eval_id;
+
+/* ---- lifetime ---------------------------------------------------------------------- */
+/* RemixtModel.__cinit__ (bpmodel.pyx:461-604): validates, uploads, builds derived tables,
+ * initial q-factors and the first cached transition expectation. */
+int rmx_create(const rmx_desc* desc, rmx_handle* out);
+int rmx_destroy(rmx_handle h);
+/* Message of the last failure on this handle (or of rmx_create when h == NULL). */
+const char* rmx_last_error(rmx_handle h);
+int rmx_device_count(int* count);
+
+/* ---- attribute access (cdef public attributes, bpmodel.pyx:398-456) ------------------ */
+/* `count` is the number of ELEMENTS of the host buffer and must match the attribute. */
+int rmx_set_array(rmx_handle h, int array_id, const void* src, int64_t count);
+int rmx_get_array(rmx_handle h, int array_id, void* dst, int64_t count);
+int rmx_set_scalar(rmx_handle h, int scalar_id, double value);
+int rmx_get_scalar(rmx_handle h, int scalar_id, double* value);
+/* Derived int64 tables of the constructor (bpmodel.pyx:497-507): which = 0 cn_states_total
+ * (N1,S,M); 1 num_alleles_subclonal (N1,S); 2 is_hdel (N1,S); 3 is_loh (N1,S). */
+int rmx_get_derived(rmx_handle h, int which, int64_t* dst, int64_t count);
+
+/* ---- coordinate updates -------------------------------------------------------------- */
+int rmx_update(rmx_handle h, int update_id);
+/* n_iter rounds of swap -> cn -> breakpoint -> outlier_total -> outlier_allele, the order of
+ * cn_model.py:444-460, on the handle's stream with ONE host synchronisation at the end. */
+int rmx_variational_update(rmx_handle h, int n_iter);
+
+/* ---- objective / M-step reductions ---------------------------------------------------- */
+int rmx_variational_energy(rmx_handle h, double* energy);    /* bpmodel.pyx:1060 */
+int rmx_variational_entropy(rmx_handle h, double* entropy);  /* bpmodel.pyx:1044 */
+int rmx_elbo(rmx_handle h, double* elbo);                    /* bpmodel.pyx:1119 */
+/* calculate_expected_log_likelihood(sample) (bpmodel.pyx:1125); sample is the (N1) int64 mask. */
+int rmx_expected_log_likelihood(rmx_handle h, const int64_t* sample, double* out);
+/* calculate_expected_log_likelihood_partial_h(sample, partial_h) (bpmodel.pyx:1159); out (M). */
+int rmx_expected_log_likelihood_partial_h(rmx_handle h, const int64_t* sample, double* out);
+/* One launch for a whole 1-D parameter grid (cn_model.py:553-558 evaluates scipy.optimize.brute's
+ * grid one point at a time): out[g] = E[LL](sample) with scalar `scalar_id` set to values[g].
+ * The model's stored value of the scalar is left at values[n_values-1], which is what the
+ * reference's point-by-point evaluation leaves behind (stale-parameter quirk). */
+int rmx_expected_log_likelihood_grid(rmx_handle h, const int64_t* sample, int scalar_id,
+                                     const double* values, int n_values, double* out);
+
+/* ---- decode ----------------------------------------------------------------------------- */
+/* infer_cn(cn) (bpmodel.pyx:1197): cn is (N1,M,2) int64, filled in place. */
+int rmx_infer_cn(rmx_handle h, int64_t* cn);
+/* calculate_log_transmat(out) (bpmodel.pyx:640): out is (N1-1,S,S) f64 filled in place. */
+int rmx_calculate_log_transmat(rmx_handle h, double* out);
+int rmx_eval(rmx_handle h, int eval_id, int n, int s, int u, int v, int w, double* out);
+
+/* ---- stateless module functions --------------------------------------------------------- */
+/* sum_product(framelogprob, log_transmat, alphas, betas) (bpmodel.pyx:1213). */
+int rmx_sum_product(int device, int64_t n_obs, int64_t n_comp, const double* framelogprob,
+                    const double* log_transmat, double* alphas, double* betas);
+/* sum_product_2paramtrans(framelogprob, alphas, betas, e0, e1) (bpmodel.pyx:1249). */
+int rmx_sum_product_2paramtrans(int device, int64_t n_obs, int64_t n_comp, const double* framelogprob,
+                                double* alphas, double* betas, double e0, double e1);
+/* max_product(framelogprob, log_transmat, state_sequence) -> logprob (bpmodel.pyx:1296). */
+int rmx_max_product(int device, int64_t n_obs, int64_t n_comp, const double* framelogprob,
+                    const double* log_transmat, int64_t* state_sequence, double* logprob);
+
+/* ---- instrumentation ---------------------------------------------------------------------- */
+/* Number of kernels this handle has launched since creation. */
+int rmx_launch_count(rmx_handle h, int64_t* count);
+/* Number of kernels launched by the whole library in this process. */
+int rmx_global_launch_count(int64_t* count);
+/* Device-side duration (CUDA events on the handle's stream) of the chain-message kernel
+ * launches since the last reset: total milliseconds and number of launches. */
+int rmx_chain_timing(rmx_handle h, int enable, double* total_ms, int64_t* launches);
+int rmx_synchronize(rmx_handle h);
+/* The cudaStream_t the handle launches on (for CUDA-event timing by the caller). */
+int rmx_stream(rmx_handle h, void** stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REMIXT_B200_H */

@@ -1,0 +1,212 @@
+"""Generate golden vectors with the UNMODIFIED reference (this container only).
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``remixt_b200/`` may import this.
+
+For an experiment fixture ``tests/golden/exp_NAME.npz`` (made by ``oracle/make_inputs.py``):
+
+1. ``init``:  runs the reference ``remixt.analysis.pipeline.init`` (``pipeline.py:12-109``) on the
+   fixture and stores the initialisation grid INTO the fixture (keys ``init_*``), so that the
+   GPU box, where the reference Python cannot travel, fits the same grid.
+2. ``steps``: drives the compiled reference ``RemixtModel`` through the reference
+   ``cn_model.BreakpointModel`` for one round of the five coordinate updates and records every
+   public quantity after each call -> ``tests/golden/steps_NAME.npz``.
+3. ``fit``:   a complete reference ``pipeline.fit`` (seeded) -> ``tests/golden/fit_NAME.npz``.
+
+Usage: python oracle/make_golden.py NAME [init] [steps] [fit] [--em E --vi V] [--init-id I]
+"""
+import contextlib
+import io
+import os
+import pickle
+import sys
+import tempfile
+import time
+import warnings
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import refenv  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, 'tests', 'golden')
+
+
+class ArrayExperimentRef(object):
+    """Stand-in for the reference Experiment with exactly the attributes ``pipeline.init`` /
+    ``pipeline.fit`` read.  start/end only feed the unused ``high_quality`` column."""
+
+    def __init__(self, x, l, adjacencies, breakpoints, breakpoint_ids, chromosome):
+        self.x = x
+        self.l = l
+        self.adjacencies = set((int(a), int(b)) for a, b in adjacencies)
+        self.breakpoints = dict()
+        for bp_id, (n1, s1, n2, s2) in zip(breakpoint_ids, breakpoints):
+            self.breakpoints[str(bp_id)] = frozenset([(int(n1), int(s1)), (int(n2), int(s2))])
+        self.segment_chromosome_id = chromosome
+        self.segment_start = np.zeros(l.shape[0], dtype=int)
+        self.segment_end = np.maximum(l.astype(int) - 1, 0)
+        self.segment_major_is_allele_a = np.ones(l.shape[0], dtype=int)
+
+
+def load_experiment(name):
+    d = np.load(os.path.join(GOLDEN, 'exp_%s.npz' % name), allow_pickle=False)
+    return d, ArrayExperimentRef(d['x'], d['l'], d['adjacencies'], d['breakpoints'], d['breakpoint_ids'],
+                                 d['chromosome'])
+
+
+class _DictStore(dict):
+    """Context-manager dict standing in for pd.HDFStore in pipeline.init (PyTables is absent)."""
+    def __init__(self, *a, **k):
+        dict.__init__(self)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+def config_for(name):
+    cfg = {'max_copy_number': 6}
+    if name in ('config2', 'genome5k'):
+        cfg['max_ploidy'] = 4.0
+    return cfg
+
+
+def run_init(name):
+    refenv.install()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        import pandas as pd
+        import remixt.analysis.pipeline as rp
+    d, exp = load_experiment(name)
+    with tempfile.TemporaryDirectory() as tmp:
+        exp_fn = os.path.join(tmp, 'exp.pickle')
+        with open(exp_fn, 'wb') as f:
+            pickle.dump(exp, f)
+        real = pd.HDFStore
+        pd.HDFStore = _DictStore
+        try:
+            cfg = config_for(name)
+            try:
+                init = rp.init(os.path.join(tmp, 'init.h5'), exp_fn, cfg)
+            except ValueError as e:
+                print('init with', cfg, 'failed:', e, '-> retrying with max_ploidy 4.0')
+                cfg['max_ploidy'] = 4.0
+                init = rp.init(os.path.join(tmp, 'init.h5'), exp_fn, cfg)
+        finally:
+            pd.HDFStore = real
+    ids = sorted(init.keys())
+    out = dict(d)
+    for key, dtype in (('mode_idx', np.int64), ('h_normal', float), ('h_tumour', float), ('mix_frac', float),
+                       ('divergence_weight', float), ('max_depth', float)):
+        out['init_' + key] = np.array([init[i][key] for i in ids], dtype=dtype)
+    out['init_max_ploidy'] = np.array(cfg.get('max_ploidy', 6.0))
+    np.savez_compressed(os.path.join(GOLDEN, 'exp_%s.npz' % name), **out)
+    print(name, 'init grid:', len(ids), 'initialisations; max_depth', out['init_max_depth'][0])
+
+
+def init_params_of(d, i):
+    return dict(mode_idx=int(d['init_mode_idx'][i]), h_normal=float(d['init_h_normal'][i]),
+                h_tumour=float(d['init_h_tumour'][i]), mix_frac=float(d['init_mix_frac'][i]),
+                divergence_weight=float(d['init_divergence_weight'][i]), max_depth=float(d['init_max_depth'][i]))
+
+
+def _snapshot(model, out, tag, big=True):
+    out[tag + '/elbo'] = model.calculate_elbo()
+    out[tag + '/energy'] = model.calculate_variational_energy()
+    out[tag + '/entropy'] = model.calculate_variational_entropy()
+    out[tag + '/hmm_log_norm_const'] = model.hmm_log_norm_const
+    for a in ('p_allele_swap', 'p_outlier_total', 'p_outlier_allele', 'p_breakpoint'):
+        out[tag + '/' + a] = np.asarray(getattr(model, a)).copy()
+    if big:
+        out[tag + '/posterior_marginals'] = np.asarray(model.posterior_marginals).copy()
+        out[tag + '/framelogprob'] = np.asarray(model.framelogprob).copy()
+
+
+def run_steps(name, init_id=0):
+    refenv.install()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        import remixt.analysis.pipeline as rp  # noqa: F401
+        import remixt.cn_model as rcn
+    d, exp = load_experiment(name)
+    ip = init_params_of(d, init_id)
+    h_init = np.array([ip['h_normal'], ip['h_tumour'] * ip['mix_frac'], ip['h_tumour'] * (1. - ip['mix_frac'])])
+    bm = rcn.BreakpointModel(exp.x, exp.l, exp.adjacencies, exp.breakpoints, max_copy_number=6,
+                             normal_contamination=True, divergence_weight=ip['divergence_weight'],
+                             min_segment_length=10000, min_proportion_genotyped=0.01, max_depth=ip['max_depth'],
+                             normal_copies=np.array([[1, 1]] * exp.l.shape[0]))
+    bm.num_em_iter = 0
+    with contextlib.redirect_stdout(io.StringIO()):
+        bm.fit(h_init)
+    model = bm.model
+    out = {'init_id': init_id, 'h_init': h_init}
+    _snapshot(model, out, 's0')
+    for r in range(2):
+        for k, step in enumerate(('update_p_allele_swap', 'update_p_cn', 'update_p_breakpoint',
+                                  'update_p_outlier_total', 'update_p_outlier_allele')):
+            getattr(model, step)()
+            _snapshot(model, out, 'r%d_%d' % (r, k), big=(step == 'update_p_cn'))
+    np.random.seed(4321)
+    sample = bm._create_sample()
+    out['sample'] = sample
+    out['ell_sample'] = model.calculate_expected_log_likelihood(sample)
+    out['ell_all'] = model.calculate_expected_log_likelihood(np.ones(model.num_segments, dtype=int))
+    g = np.zeros(3)
+    model.calculate_expected_log_likelihood_partial_h(sample, g)
+    out['grad_sample'] = g.copy()
+    model.calculate_expected_log_likelihood_partial_h(np.ones(model.num_segments, dtype=int), g)
+    out['grad_all'] = g.copy()
+    cn = np.zeros((model.num_segments, 3, 2), dtype=int)
+    model.infer_cn(cn)
+    out['cn'] = cn
+    np.savez_compressed(os.path.join(GOLDEN, 'steps_%s.npz' % name), **out)
+    print(name, 'steps: elbo', out['s0/elbo'], '->', out['r1_4/elbo'])
+
+
+def run_fit(name, init_id=0, em=5, vi=5, tag=None):
+    refenv.install()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        import remixt.analysis.pipeline as rp
+    d, exp = load_experiment(name)
+    ip = init_params_of(d, init_id)
+    cfg = {'max_copy_number': 6, 'num_em_iter': em, 'num_update_iter': vi}
+    np.random.seed(1234)
+    t0 = time.time()
+    with contextlib.redirect_stdout(io.StringIO()):
+        res = rp.fit(exp, ip, cfg)
+    dt = time.time() - t0
+    out = {'init_id': init_id, 'num_em_iter': em, 'num_update_iter': vi, 'seconds': dt,
+           'h': res['h'], 'cn': res['cn'], 'p_outlier_total': res['p_outlier_total'],
+           'p_outlier_allele': res['p_outlier_allele'], 'elbo': res['stats']['elbo'],
+           'elbo_diff': res['stats']['elbo_diff'], 'ploidy': res['stats']['ploidy'],
+           'proportion_divergent': res['stats']['proportion_divergent']}
+    for k in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
+        out[k] = res['stats'][k]
+    ids = sorted(res['brk_cn'].keys())
+    out['brk_ids'] = np.array(ids)
+    out['brk_cn'] = np.array([res['brk_cn'][i] for i in ids])
+    np.savez_compressed(os.path.join(GOLDEN, 'fit_%s%s.npz' % (name, tag or '')), **out)
+    print(name, 'fit init', init_id, ': %.1f s, elbo %.10f, h %s' % (dt, out['elbo'], res['h']))
+
+
+def main():
+    args = sys.argv[1:]
+    name = args[0]
+    em = int(args[args.index('--em') + 1]) if '--em' in args else 5
+    vi = int(args[args.index('--vi') + 1]) if '--vi' in args else 5
+    init_id = int(args[args.index('--init-id') + 1]) if '--init-id' in args else 0
+    tag = args[args.index('--tag') + 1] if '--tag' in args else None
+    if 'init' in args:
+        run_init(name)
+    if 'steps' in args:
+        run_steps(name, init_id)
+    if 'fit' in args:
+        run_fit(name, init_id, em, vi, tag)
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,599 @@
+// Likelihood kernels: the per-(segment,state) negative-binomial / beta-binomial expected
+// log-likelihood table, the frame log-probability, the 2-way q-factor posteriors
+// (allele swap, outliers), and the M-step / ELBO reductions.
+//
+// Reference: remixt/bpmodel.pyx
+//   negbin_log_likelihood :238-272      betabin_log_likelihood :304-347
+//   calculate_log_likelihood_total :751  calculate_log_likelihood_allele :809
+//   update_framelogprob :898            update_p_outlier_total :987
+//   update_p_outlier_allele :1005       update_p_allele_swap :1025
+//   calculate_expected_log_likelihood :1125   ..._partial_h :1159
+#include "common.cuh"
+#include "kernels.h"
+
+// ---------------------------------------------------------------------------------------------
+// Per-segment hoisted constants.  The state-independent lgamma terms of the two pmfs:
+//   NB (u):    lgamma(x+r_u) - lgamma(x+1) - lgamma(r_u)
+//   BB (v,w):  lgamma(n+1) - lgamma(k_w+1) - lgamma(n-k_w+1) - lgamma(n+M_v) + lgamma(M_v)
+// plus the same with the hdel / LOH dispersions (only used when normal_contamination is off).
+// Layout: segc[c * R + r], c in [0,12), r = position in the row list.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_segconst(RmxTables T, RmxParams P, const int* __restrict__ rows, int R,
+                           double* __restrict__ segc) {
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    int n = rows ? rows[r] : r;
+    double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n];
+    double na = y0 + y1;
+    double lgx1 = lgamma(x + 1.);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        double rr = P.negbin_r[u];
+        segc[(0 + u) * R + r] = lgamma(x + rr) - lgx1 - lgamma(rr);
+        double rh = P.negbin_hdel_r[u];
+        segc[(2 + u) * R + r] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
+    }
+    double lgn1 = lgamma(na + 1.);
+    double comb[2];
+    comb[0] = lgn1 - lgamma(y0 + 1.) - lgamma(na - y0 + 1.);
+    comb[1] = lgn1 - lgamma(y1 + 1.) - lgamma(na - y1 + 1.);
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+        double Mv = P.betabin_M[v];
+        double t = -lgamma(na + Mv) + lgamma(Mv);
+        double Ml = P.betabin_loh_M[v];
+        double tl = P.normal_contamination ? 0. : (-lgamma(na + Ml) + lgamma(Ml));
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            segc[(4 + v * 2 + w) * R + r] = comb[w] + t;
+            segc[(8 + v * 2 + w) * R + r] = comb[w] + tl;
+        }
+    }
+}
+
+// Six log-likelihood terms of one (segment, state): ll[0..1] total (u), ll[2..5] allele (v*2+w).
+__device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P,
+                                         const double* __restrict__ segc, int R, int r, int n, int s,
+                                         double* ll, int* flags) {
+    StateCN c = load_state(T, d, n, s);
+    const bool special = !P.normal_contamination;
+    // ---- total reads: negative binomial (bpmodel.pyx:751-776, :238-272)
+    if (T.tmask[n]) {
+        double x = T.x[n];
+        bool hd = special && c.hdel;
+        double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, T.l[n]);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            double rr = hd ? P.negbin_hdel_r[u] : P.negbin_r[u];
+            double p = mu / (rr + mu);
+            if (p < 0. || p > 1.) p = 0.5;
+            double v = segc[((hd ? 2 : 0) + u) * R + r] + x * log(p) + rr * log(1. - p);
+            if (isnan(v)) *flags |= RMX_F_NB_NAN;
+            ll[u] = v;
+        }
+    } else {
+        ll[0] = 0.;
+        ll[1] = 0.;
+    }
+    // ---- allele reads: beta binomial (bpmodel.pyx:809-853, :304-347)
+    ll[2] = ll[3] = ll[4] = ll[5] = 0.;
+    if (T.amask[n]) {
+        double p;
+        if (c.hdel) {
+            p = 0.;
+        } else {
+            double md, td;
+            p = expected_allele_ratio(P, d, c, &md, &td);
+            if (td <= 0.) {
+                *flags |= RMX_F_TOTAL_DEPTH;
+                return;
+            }
+        }
+        bool loh = special && c.loh;
+        if (loh) {
+            if (p == 0.) p = P.betabin_loh_p;
+            else if (p == 1.) p = 1. - P.betabin_loh_p;
+            else {
+                *flags |= RMX_F_LOH_P;
+                return;
+            }
+        }
+        double y0 = T.y0[n], y1 = T.y1[n];
+        double na = y0 + y1;
+        if (na == 0.) return;
+        if (p <= 0. || (1. - p) <= 0.) {
+            *flags |= RMX_F_BB_P_RANGE;
+            return;
+        }
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            double Mv = loh ? P.betabin_loh_M[v] : P.betabin_M[v];
+            double a = Mv * p, b = Mv * (1. - p);
+            double base = -lgamma(a) - lgamma(b);
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                double k = w ? y1 : y0;
+                double val = segc[((loh ? 8 : 4) + v * 2 + w) * R + r] + lgamma(k + a) + lgamma(na - k + b) + base;
+                if (isnan(val)) *flags |= RMX_F_BB_NAN;
+                ll[2 + v * 2 + w] = val;
+            }
+        }
+    }
+}
+
+// K1: the likelihood table, LL[t][n*S+s], one thread per (n,s), fully coalesced planar writes.
+__global__ void __launch_bounds__(256) k_lltable(RmxTables T, RmxDims d, RmxParams P,
+                                                  const double* __restrict__ segc,
+                                                  double* __restrict__ LL, int* __restrict__ dflags) {
+    int64_t NS = (int64_t)d.N * d.S;
+    int flags = 0;
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < NS;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int n = (int)(idx / d.S), s = (int)(idx - (int64_t)n * d.S);
+        double ll[RMX_NTERM];
+        ll_terms(T, d, P, segc, d.N, n, n, s, ll, &flags);
+#pragma unroll
+        for (int t = 0; t < RMX_NTERM; ++t) LL[(int64_t)t * NS + idx] = ll[t];
+    }
+    if (flags) atomicOr(dflags, flags);
+}
+
+// Frame log-probability (bpmodel.pyx:898-919) from the LL table, one warp per segment.
+// Also writes the row max mF[n] and fexp[n,s] = exp(F[n,s] - mF[n]) for the scaled chain messages.
+__global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, RmxParams P,
+                                               const double* __restrict__ LL,
+                                               const double* __restrict__ q_ot, const double* __restrict__ q_oa,
+                                               const double* __restrict__ q_sw,
+                                               double* __restrict__ F, double* __restrict__ fexp,
+                                               double* __restrict__ mF, int* __restrict__ dflags) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    int n = warp;
+    int64_t NS = (int64_t)d.N * d.S;
+    double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
+    double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
+    double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
+    double ln = T.l[n];
+    double mx = -INFINITY;
+    bool bad = false;
+    for (int s = lane; s < d.S; s += 32) {
+        int64_t i = (int64_t)n * d.S + s;
+        double f = 0.;
+        f += ot0 * LL[i];
+        f += ot1 * LL[NS + i];
+        f += oa0 * sw0 * LL[2 * NS + i];
+        f += oa0 * sw1 * LL[3 * NS + i];
+        f += oa1 * sw0 * LL[4 * NS + i];
+        f += oa1 * sw1 * LL[5 * NS + i];
+        f += -1.0 * (double)T.nsub[s] * ln * P.divergence_weight;   // bpmodel.pyx:746-749
+        F[i] = f;
+        bad |= isnan(f);
+        mx = fmax(mx, f);
+    }
+    mx = warp_max(mx);
+    for (int s = lane; s < d.S; s += 32) {
+        int64_t i = (int64_t)n * d.S + s;
+        fexp[i] = exp(F[i] - mx);
+    }
+    if (lane == 0) mF[n] = mx;
+    if (bad) atomicOr(dflags, RMX_F_FRAME_NAN);
+}
+
+// exp-normalise of a 2-vector as bpmodel.pyx:120-128 does it.
+__device__ __forceinline__ void exp_normalize2(double a, double b, double* out) {
+    double m = fmax(a, b);
+    double lse = log(exp(a - m) + exp(b - m)) + m;
+    double ea = exp(a - lse), eb = exp(b - lse);
+    double z = ea + eb;
+    out[0] = ea / z;
+    out[1] = eb / z;
+}
+
+// The three 2-way factor updates, one warp per segment, reading the LL table and the posterior.
+//   which = 0: update_p_allele_swap   (bpmodel.pyx:1025-1042)
+//   which = 1: update_p_outlier_total (bpmodel.pyx:987-1003)
+//   which = 2: update_p_outlier_allele(bpmodel.pyx:1005-1023)
+__global__ void __launch_bounds__(256) k_qfactor(RmxDims d, int which, const double* __restrict__ LL,
+                                                 const double* __restrict__ post,
+                                                 const double* __restrict__ q_oa, const double* __restrict__ q_sw,
+                                                 double prior, double* __restrict__ out) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    int n = warp;
+    int64_t NS = (int64_t)d.N * d.S;
+    double a0 = 0., a1 = 0.;
+    if (which == 1) {
+        for (int s = lane; s < d.S; s += 32) {
+            int64_t i = (int64_t)n * d.S + s;
+            double p = post[i];
+            a0 += p * LL[i];
+            a1 += p * LL[NS + i];
+        }
+    } else if (which == 0) {
+        double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
+        for (int s = lane; s < d.S; s += 32) {
+            int64_t i = (int64_t)n * d.S + s;
+            double p = post[i];
+            a0 += oa0 * p * LL[2 * NS + i] + oa1 * p * LL[4 * NS + i];
+            a1 += oa0 * p * LL[3 * NS + i] + oa1 * p * LL[5 * NS + i];
+        }
+    } else {
+        double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
+        for (int s = lane; s < d.S; s += 32) {
+            int64_t i = (int64_t)n * d.S + s;
+            double p = post[i];
+            a0 += sw0 * p * LL[2 * NS + i] + sw1 * p * LL[3 * NS + i];
+            a1 += sw0 * p * LL[4 * NS + i] + sw1 * p * LL[5 * NS + i];
+        }
+    }
+    a0 = warp_sum(a0);
+    a1 = warp_sum(a1);
+    if (lane == 0) {
+        if (which != 0) {
+            a0 += log(1. - prior);
+            a1 += log(prior);
+        }
+        exp_normalize2(a0, a1, out + 2 * n);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Reductions.  Every scalar the host reads is produced by the same two-stage scheme: per-row
+// values (one warp per segment, fixed lane order) then one CTA summing the row values in a fixed
+// strided order, so results are reproducible run to run.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_reduce_cols(const double* __restrict__ in, int64_t n, int ncol,
+                                                      double* __restrict__ out) {
+    // out[c] = sum_i in[c*n + i], one CTA per column
+    __shared__ double sm[32];
+    int c = blockIdx.x;
+    if (c >= ncol) return;
+    const double* p = in + (int64_t)c * n;
+    double acc = 0.;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += p[i];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double v = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) out[c] = v;
+    }
+}
+
+__device__ __forceinline__ double plogp(double p) { return p > 0. ? p * log(p) : 0.; }
+
+// Per-segment ELBO terms from the LL table (bpmodel.pyx:1044-1117), one warp per segment.
+// rowv columns (each length N):
+//   0: sum_s post*prior_cn          1: sum_s post * sum_u q_ot*LLtot   2: sum_s post * sum_vw q_oa q_sw LLal
+//   3: q_ot . log prior            4: q_oa . log prior                 5: sum_s post*F
+//   6: entropy terms of q_ot,q_oa,q_sw  (sum p log p)
+__global__ void __launch_bounds__(256) k_elbo_rows(RmxTables T, RmxDims d, RmxParams P, const double* __restrict__ LL,
+                                                   const double* __restrict__ post, const double* __restrict__ F,
+                                                   const double* __restrict__ q_ot, const double* __restrict__ q_oa,
+                                                   const double* __restrict__ q_sw, double prior_ot, double prior_oa,
+                                                   double* __restrict__ rowv) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    int n = warp;
+    int64_t NS = (int64_t)d.N * d.S;
+    double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
+    double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
+    double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
+    double ln = T.l[n];
+    double e0 = 0., e1 = 0., e2 = 0., e5 = 0.;
+    for (int s = lane; s < d.S; s += 32) {
+        int64_t i = (int64_t)n * d.S + s;
+        double p = post[i];
+        e0 += p * (-1.0 * (double)T.nsub[s] * ln * P.divergence_weight);
+        e1 += p * ot0 * LL[i] + p * ot1 * LL[NS + i];
+        e2 += p * oa0 * sw0 * LL[2 * NS + i] + p * oa0 * sw1 * LL[3 * NS + i] +
+              p * oa1 * sw0 * LL[4 * NS + i] + p * oa1 * sw1 * LL[5 * NS + i];
+        e5 += p * F[i];
+    }
+    e0 = warp_sum(e0);
+    e1 = warp_sum(e1);
+    e2 = warp_sum(e2);
+    e5 = warp_sum(e5);
+    if (lane == 0) {
+        int64_t N = d.N;
+        rowv[0 * N + n] = e0;
+        rowv[1 * N + n] = e1;
+        rowv[2 * N + n] = e2;
+        rowv[3 * N + n] = ot0 * log(1. - prior_ot) + ot1 * log(prior_ot);
+        rowv[4 * N + n] = oa0 * log(1. - prior_oa) + oa1 * log(prior_oa);
+        rowv[5 * N + n] = e5;
+        rowv[6 * N + n] = plogp(ot0) + plogp(ot1) + plogp(oa0) + plogp(oa1) + plogp(sw0) + plogp(sw1);
+    }
+}
+
+// sum p log p over a flat array (p_breakpoint) -> rowv[i]
+__global__ void k_plogp(const double* __restrict__ p, int64_t n, double* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = plogp(p[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// M-step objective on a row list: E_q[log lik] (bpmodel.pyx:1125-1157) and its gradient in h
+// (bpmodel.pyx:1159-1195), with the LL terms evaluated for the CURRENT parameters (the LL table
+// belongs to the E-step generation and is not touched).  One thread per (row, state); the CTA
+// sum goes to part[blockIdx.x] (ELL) or part[m*gridDim.x + blockIdx.x] (gradient).
+// ---------------------------------------------------------------------------------------------
+template <int NV>
+__device__ __forceinline__ void block_sum_store(double* v, double* __restrict__ part, int stride) {
+    __shared__ double sm[NV][8];
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double x = warp_sum(v[k]);
+        if (lane == 0) sm[k][wid] = x;
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        double a = 0.;
+        int nw = blockDim.x >> 5;
+        for (int w = 0; w < nw; ++w) a += sm[threadIdx.x][w];
+        part[(int64_t)threadIdx.x * stride + blockIdx.x] = a;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, RmxParams P, const int* __restrict__ rows, int R,
+                                             const double* __restrict__ segc, const double* __restrict__ post,
+                                             const double* __restrict__ q_ot, const double* __restrict__ q_oa,
+                                             const double* __restrict__ q_sw, double* __restrict__ part,
+                                             int* __restrict__ dflags) {
+    int64_t RS = (int64_t)R * d.S;
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double acc[1] = {0.};
+    int flags = 0;
+    if (idx < RS) {
+        int r = (int)(idx / d.S), s = (int)(idx - (int64_t)r * d.S);
+        int n = rows ? rows[r] : r;
+        double ll[RMX_NTERM];
+        ll_terms(T, d, P, segc, R, r, n, s, ll, &flags);
+        double p = post[(int64_t)n * d.S + s];
+        double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
+        double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
+        double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
+        acc[0] = p * ot0 * ll[0] + p * ot1 * ll[1] + p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3] +
+                 p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
+    }
+    block_sum_store<1>(acc, part, gridDim.x);
+    if (flags) atomicOr(dflags, flags);
+}
+
+__global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, RmxParams P, const int* __restrict__ rows,
+                                                  int R, const double* __restrict__ post,
+                                                  const double* __restrict__ q_ot, const double* __restrict__ q_oa,
+                                                  const double* __restrict__ q_sw, double* __restrict__ part,
+                                                  int* __restrict__ dflags) {
+    int64_t RS = (int64_t)R * d.S;
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double g[RMX_MAXM];
+#pragma unroll
+    for (int m = 0; m < RMX_MAXM; ++m) g[m] = 0.;
+    int flags = 0;
+    if (idx < RS) {
+        int r = (int)(idx / d.S), s = (int)(idx - (int64_t)r * d.S);
+        int n = rows ? rows[r] : r;
+        StateCN c = load_state(T, d, n, s);
+        const bool special = !P.normal_contamination;
+        double p = post[(int64_t)n * d.S + s];
+        // total reads (bpmodel.pyx:778-807, :275-301)
+        if (T.tmask[n] && !(special && c.hdel)) {
+            double l = T.l[n], x = T.x[n];
+            double mu = expected_total_reads(P, d, c, l);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                double rr = P.negbin_r[u];
+                double dmu = x / mu - (rr + x) / (rr + mu);
+                if (isnan(dmu)) flags |= RMX_F_NB_PARTIAL_NAN;
+                double wgt = p * q_ot[2 * n + u];
+#pragma unroll
+                for (int m = 0; m < RMX_MAXM; ++m)
+                    if (m < d.M) g[m] += wgt * ((l * (double)c.tot[m]) * dmu);
+            }
+        }
+        // allele reads (bpmodel.pyx:855-896, :350-394, :726-744)
+        if (T.amask[n] && !(special && c.loh)) {
+            double md, td;
+            double pr = expected_allele_ratio(P, d, c, &md, &td);
+            if (td <= 0.) {
+                flags |= RMX_F_TOTAL_DEPTH;
+            } else {
+                double y0 = T.y0[n], y1 = T.y1[n];
+                double na = y0 + y1;
+                if (na != 0.) {
+                    if (pr <= 0. || (1. - pr) <= 0.) {
+                        flags |= RMX_F_BB_P_RANGE;
+                    } else {
+                        double rp[RMX_MAXM];
+#pragma unroll
+                        for (int m = 0; m < RMX_MAXM; ++m)
+                            rp[m] = (m < d.M) ? ((double)c.a0[m] * td - md * (double)c.tot[m]) / (td * td) : 0.;
+#pragma unroll
+                        for (int v = 0; v < 2; ++v) {
+                            double Mv = P.betabin_M[v];
+                            double a = Mv * pr, b = Mv * (1. - pr);
+                            double dga = digamma_as103(a, &flags), dgb = digamma_as103(b, &flags);
+#pragma unroll
+                            for (int w = 0; w < 2; ++w) {
+                                double k = w ? y1 : y0;
+                                double dp = Mv * digamma_as103(k + a, &flags) + (-Mv) * digamma_as103(na - k + b, &flags) -
+                                            Mv * dga - (-Mv) * dgb;
+                                if (isnan(dp)) flags |= RMX_F_BB_PARTIAL_NAN;
+                                double wgt = p * q_oa[2 * n + v] * q_sw[2 * n + w];
+#pragma unroll
+                                for (int m = 0; m < RMX_MAXM; ++m)
+                                    if (m < d.M) g[m] += wgt * (rp[m] * dp);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    block_sum_store<RMX_MAXM>(g, part, gridDim.x);
+    if (flags) atomicOr(dflags, flags);
+}
+
+// Single-(n,s) scalar accessors (bpmodel.pyx:686-896), evaluated on the device.
+__global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int s, int u, int v, int w,
+                       double* __restrict__ out, int* __restrict__ dflags) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int flags = 0;
+    for (int m = 0; m < RMX_MAXM; ++m) out[m] = 0.;
+    StateCN c = load_state(T, d, n, s);
+    const bool special = !P.normal_contamination;
+    double l = T.l[n];
+    switch (what) {
+    case 0: out[0] = expected_total_reads(P, d, c, l); break;
+    case 1: for (int m = 0; m < d.M; ++m) out[m] = l * (double)c.tot[m]; break;
+    case 2:
+    case 3: {
+        double md, td;
+        double pr = expected_allele_ratio(P, d, c, &md, &td);
+        if (td <= 0.) { flags |= RMX_F_TOTAL_DEPTH; break; }
+        if (what == 2) out[0] = pr;
+        else for (int m = 0; m < d.M; ++m) out[m] = ((double)c.a0[m] * td - md * (double)c.tot[m]) / (td * td);
+        break;
+    }
+    case 4: out[0] = -1.0 * (double)T.nsub[s] * l * P.divergence_weight; break;
+    case 5: {
+        if (!T.tmask[n]) break;
+        bool hd = special && c.hdel;
+        double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, l);
+        double rr = hd ? P.negbin_hdel_r[u] : P.negbin_r[u];
+        double x = T.x[n];
+        double p = mu / (rr + mu);
+        if (p < 0. || p > 1.) p = 0.5;
+        double val = lgamma(x + rr) - lgamma(x + 1.) - lgamma(rr) + x * log(p) + rr * log(1. - p);
+        if (isnan(val)) flags |= RMX_F_NB_NAN;
+        out[0] = val;
+        break;
+    }
+    case 6: {
+        if (!T.tmask[n] || (special && c.hdel)) break;
+        double mu = expected_total_reads(P, d, c, l);
+        double rr = P.negbin_r[u], x = T.x[n];
+        double dmu = x / mu - (rr + x) / (rr + mu);
+        if (isnan(dmu)) flags |= RMX_F_NB_PARTIAL_NAN;
+        for (int m = 0; m < d.M; ++m) out[m] = (l * (double)c.tot[m]) * dmu;
+        break;
+    }
+    case 7: {
+        if (!T.amask[n]) break;
+        double p = 0.;
+        if (!c.hdel) {
+            double md, td;
+            p = expected_allele_ratio(P, d, c, &md, &td);
+            if (td <= 0.) { flags |= RMX_F_TOTAL_DEPTH; break; }
+        }
+        bool loh = special && c.loh;
+        if (loh) {
+            if (p == 0.) p = P.betabin_loh_p;
+            else if (p == 1.) p = 1. - P.betabin_loh_p;
+            else { flags |= RMX_F_LOH_P; break; }
+        }
+        double Mv = loh ? P.betabin_loh_M[v] : P.betabin_M[v];
+        double y0 = T.y0[n], y1 = T.y1[n], na = y0 + y1;
+        if (na == 0.) break;
+        double k = w ? y1 : y0;
+        if (p <= 0. || (1. - p) <= 0.) { flags |= RMX_F_BB_P_RANGE; break; }
+        double val = lgamma(na + 1.) - lgamma(k + 1.) - lgamma(na - k + 1.) + lgamma(k + Mv * p) +
+                     lgamma(na - k + Mv * (1. - p)) - lgamma(na + Mv) - lgamma(Mv * p) - lgamma(Mv * (1. - p)) +
+                     lgamma(Mv);
+        if (isnan(val)) flags |= RMX_F_BB_NAN;
+        out[0] = val;
+        break;
+    }
+    case 8: {
+        if (!T.amask[n] || (special && c.loh)) break;
+        double md, td;
+        double pr = expected_allele_ratio(P, d, c, &md, &td);
+        if (td <= 0.) { flags |= RMX_F_TOTAL_DEPTH; break; }
+        double Mv = P.betabin_M[v];
+        double y0 = T.y0[n], y1 = T.y1[n], na = y0 + y1;
+        if (na == 0.) break;
+        double k = w ? y1 : y0;
+        if (pr <= 0. || (1. - pr) <= 0.) { flags |= RMX_F_BB_P_RANGE; break; }
+        double dp = Mv * digamma_as103(k + Mv * pr, &flags) + (-Mv) * digamma_as103(na - k + Mv * (1. - pr), &flags) -
+                    Mv * digamma_as103(Mv * pr, &flags) - (-Mv) * digamma_as103(Mv * (1. - pr), &flags);
+        if (isnan(dp)) flags |= RMX_F_BB_PARTIAL_NAN;
+        for (int m = 0; m < d.M; ++m) out[m] = (((double)c.a0[m] * td - md * (double)c.tot[m]) / (td * td)) * dp;
+        break;
+    }
+    default: break;
+    }
+    if (flags) atomicOr(dflags, flags);
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxParams& P, const int* rows, int R, double* segc) {
+    if (R <= 0) return;
+    k_segconst<<<cdiv(R, 128), 128, 0, st>>>(T, P, rows, R, segc);
+}
+
+void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams& P,
+                        const double* segc, double* LL, int* dflags) {
+    int64_t NS = (int64_t)d.N * d.S;
+    if (NS <= 0) return;
+    int64_t want = (NS + 255) / 256;
+    int64_t cap = (int64_t)sm_count * 8;           // grid sized in multiples of the SM count
+    int grid = (int)(want < cap ? want : cap);
+    k_lltable<<<grid, 256, 0, st>>>(T, d, P, segc, LL, dflags);
+}
+
+void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
+                      const double* q_ot, const double* q_oa, const double* q_sw, double* F, double* fexp, double* mF,
+                      int* dflags) {
+    if (d.N <= 0) return;
+    k_frame<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(T, d, P, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+}
+
+void rmx_launch_qfactor(cudaStream_t st, const RmxDims& d, int which, const double* LL, const double* post,
+                        const double* q_oa, const double* q_sw, double prior, double* out) {
+    if (d.N <= 0) return;
+    k_qfactor<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(d, which, LL, post, q_oa, q_sw, prior, out);
+}
+
+void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, double* out) {
+    if (ncol <= 0) return;
+    k_reduce_cols<<<ncol, 1024, 0, st>>>(in, n, ncol, out);
+}
+
+void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
+                          const double* post, const double* F, const double* q_ot, const double* q_oa,
+                          const double* q_sw, double prior_ot, double prior_oa, double* rowv) {
+    if (d.N <= 0) return;
+    k_elbo_rows<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(T, d, P, LL, post, F, q_ot, q_oa, q_sw, prior_ot,
+                                                              prior_oa, rowv);
+}
+
+void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, double* out) {
+    if (n <= 0) return;
+    k_plogp<<<cdiv(n, 256), 256, 0, st>>>(p, n, out);
+}
+
+int rmx_ell_blocks(const RmxDims& d, int R) { return cdiv((int64_t)R * d.S, 256); }
+
+void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows, int R,
+                    const double* segc, const double* post, const double* q_ot, const double* q_oa,
+                    const double* q_sw, double* part, int* dflags) {
+    k_ell<<<rmx_ell_blocks(d, R), 256, 0, st>>>(T, d, P, rows, R, segc, post, q_ot, q_oa, q_sw, part, dflags);
+}
+
+void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows,
+                         int R, const double* post, const double* q_ot, const double* q_oa, const double* q_sw,
+                         double* part, int* dflags) {
+    k_ell_grad<<<rmx_ell_blocks(d, R), 256, 0, st>>>(T, d, P, rows, R, post, q_ot, q_oa, q_sw, part, dflags);
+}
+
+void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, int what, int n, int s,
+                     int u, int v, int w, double* out, int* dflags) {
+    k_eval<<<1, 32, 0, st>>>(T, d, P, what, n, s, u, v, w, out, dflags);
+}

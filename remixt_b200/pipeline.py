@@ -1,0 +1,190 @@
+"""Fit orchestration: the mirror of ``remixt/analysis/pipeline.py`` ``fit`` (``:127-228``) and of
+the solution selection of ``store_optimal_solution`` (``:253-264``), plus an in-process grid
+driver that replaces the reference's pypeliner process fan-out over ``init_id``
+(``workflow.py:329-340``) with one host thread per GPU.
+
+An *experiment* is anything with attributes ``x (N,3)``, ``l (N,)``, ``adjacencies``,
+``breakpoints`` (dict id -> frozenset of two (segment, side)) and ``segment_chromosome_id``;
+the reference's ``remixt.analysis.experiment.Experiment`` qualifies, and so does
+:class:`ArrayExperiment`, which is built from the plain arrays of the ``tests/golden`` fixtures.
+"""
+import threading
+
+import numpy as np
+
+from . import cn_model
+
+# the fit-relevant subset of remixt/defaults.py:114-163
+DEFAULTS = {
+    'max_copy_number': 12,
+    'tumour_mix_fractions': [0.45, 0.3, 0.2, 0.1],
+    'min_ploidy': 1.5,
+    'max_ploidy': 6.0,
+    'max_prop_diverge': 0.5,
+    'normal_contamination': True,
+    'likelihood_min_segment_length': 10000,
+    'likelihood_min_proportion_genotyped': 0.01,
+    'divergence_weights': [1e-6, 1e-7, 1e-8],
+    'num_em_iter': 5,
+    'num_update_iter': 5,
+    'disable_breakpoints': False,
+    'do_h_update': True,
+    'is_female': True,
+}
+
+
+def get_param(config, name):
+    return config[name] if name in config else DEFAULTS[name]
+
+
+class ArrayExperiment(object):
+    """Experiment container over plain arrays (see ``oracle/make_inputs.py`` for the layout)."""
+
+    def __init__(self, x, l, adjacencies, breakpoints, breakpoint_ids=None, chromosome=None):
+        self.x = np.asarray(x, dtype=float)
+        self.l = np.asarray(l, dtype=float)
+        self.adjacencies = set((int(a), int(b)) for a, b in np.asarray(adjacencies).reshape(-1, 2))
+        bps = np.asarray(breakpoints).reshape(-1, 4)
+        if breakpoint_ids is None:
+            breakpoint_ids = [str(i) for i in range(bps.shape[0])]
+        self.breakpoints = dict()
+        for bp_id, (n1, s1, n2, s2) in zip(breakpoint_ids, bps):
+            self.breakpoints[str(bp_id)] = frozenset([(int(n1), int(s1)), (int(n2), int(s2))])
+        self.segment_chromosome_id = (np.asarray(chromosome) if chromosome is not None
+                                      else np.array(['1'] * self.x.shape[0]))
+
+    @classmethod
+    def from_npz(cls, path):
+        d = np.load(path, allow_pickle=False)
+        return cls(d['x'], d['l'], d['adjacencies'], d['breakpoints'],
+                   breakpoint_ids=d['breakpoint_ids'] if 'breakpoint_ids' in d else None,
+                   chromosome=d['chromosome'] if 'chromosome' in d else None)
+
+
+def build_model(experiment, init_params, config, **model_kwargs):
+    """The ``BreakpointModel`` construction of ``analysis/pipeline.py:164-189``."""
+    is_female = get_param(config, 'is_female')
+    normal_copies = np.array([[1, 1]] * experiment.l.shape[0])
+    if not is_female:
+        on_x = experiment.segment_chromosome_id == 'X'
+        normal_copies[on_x, :] = np.array([1, 0])
+        if np.any(experiment.x[on_x, 0:2] > 0):
+            raise Exception('inconsistent allele read counts for chromosome X')
+
+    model = cn_model.BreakpointModel(
+        experiment.x, experiment.l, experiment.adjacencies, experiment.breakpoints,
+        max_copy_number=get_param(config, 'max_copy_number'),
+        normal_contamination=get_param(config, 'normal_contamination'),
+        divergence_weight=init_params['divergence_weight'],
+        min_segment_length=get_param(config, 'likelihood_min_segment_length'),
+        min_proportion_genotyped=get_param(config, 'likelihood_min_proportion_genotyped'),
+        max_depth=init_params['max_depth'],
+        normal_copies=normal_copies,
+        disable_breakpoints=get_param(config, 'disable_breakpoints'),
+        breakpoint_init=None,
+        do_h_update=get_param(config, 'do_h_update'),
+        **model_kwargs)
+    model.num_em_iter = get_param(config, 'num_em_iter')
+    model.num_update_iter = get_param(config, 'num_update_iter')
+    return model
+
+
+def init_h(init_params):
+    # analysis/pipeline.py:128-132
+    return np.array([
+        init_params['h_normal'],
+        init_params['h_tumour'] * init_params['mix_frac'],
+        init_params['h_tumour'] * (1. - init_params['mix_frac']),
+    ])
+
+
+def fit(experiment, init_params, config, **model_kwargs):
+    """One fit from one initialisation; returns the reference's ``fit_results`` dict
+    (``analysis/pipeline.py:127-228``)."""
+    model = build_model(experiment, init_params, config, **model_kwargs)
+    model.fit(init_h(init_params))
+
+    cn, brk_cn = model.optimal_cn()
+    if get_param(config, 'disable_breakpoints'):
+        brk_cn = cn_model.decode_breakpoints_naive(cn, experiment.adjacencies, experiment.breakpoints)
+
+    results = dict()
+    results['h'] = model.h
+    results['cn'] = cn
+    results['brk_cn'] = brk_cn
+    results['p_outlier_total'] = model.p_outlier_total
+    results['p_outlier_allele'] = model.p_outlier_allele
+    results['total_likelihood_mask'] = model.total_likelihood_mask
+    results['allele_likelihood_mask'] = model.allele_likelihood_mask
+
+    stats = dict()
+    stats['elbo'] = model.prev_elbo
+    stats['elbo_diff'] = model.prev_elbo_diff
+    stats['error_message'] = ''
+    stats.update(model.get_likelihood_param_values())
+    l = experiment.l
+    stats['num_clones'] = len(model.h)
+    stats['num_segments'] = len(experiment.x)
+    stats['ploidy'] = (cn[:, 1:, :].mean(axis=1).T * l).sum() / l.sum()
+    divergent = (cn[:, 1:, :].max(axis=1) != cn[:, 1:, :].min(axis=1)) * 1.
+    stats['proportion_divergent'] = (divergent.T * l).sum() / (2. * l.sum())
+    stats['mode_idx'] = init_params.get('mode_idx', 0)
+    stats['divergence_weight'] = init_params['divergence_weight']
+    results['stats'] = stats
+    return results
+
+
+def select_solution(stats_by_init, config=None):
+    """``init_id`` the reference's collate step would pick (``analysis/pipeline.py:253-259``):
+    highest ELBO among solutions with ``proportion_divergent < max_prop_diverge`` (all solutions
+    if none qualifies); ties keep the earlier ``init_id`` (stable sort)."""
+    max_prop_diverge = get_param(config or {}, 'max_prop_diverge')
+    ids = list(stats_by_init.keys())
+    ok = [i for i in ids if stats_by_init[i]['proportion_divergent'] < max_prop_diverge]
+    pool = ok if ok else ids
+    best = pool[0]
+    for i in pool[1:]:
+        if stats_by_init[i]['elbo'] > stats_by_init[best]['elbo']:
+            best = i
+    return best
+
+
+def fit_grid(experiment, init_params_by_id, config, device=None, random_seed=1234, num_threads=4,
+             init_ids=None):
+    """Fit the initialisations ``init_ids`` (default: all) of the grid on ONE GPU, ``num_threads``
+    fits in flight at a time (one host thread and one CUDA stream each), and pick the solution.
+
+    The reference runs each ``init_id`` as its own process (``workflow.py:329-340``).  Here every
+    fit draws its M-step subsamples from its own ``RandomState(random_seed)``, which is the stream
+    a process that called ``numpy.random.seed(random_seed)`` before ``fit`` would see, so results
+    do not depend on how fits interleave.  Across GPUs the grid is sharded by rank
+    (``init_ids = ids[rank::world_size]``) with no collective; rank 0 gathers the stats.
+    """
+    ids = list(init_params_by_id.keys()) if init_ids is None else list(init_ids)
+    results = {}
+    errors = {}
+    model_kwargs = {} if device is None else {'device': device}
+
+    def worker(slot):
+        for pos in range(slot, len(ids), num_threads):
+            init_id = ids[pos]
+            try:
+                results[init_id] = fit(experiment, init_params_by_id[init_id], config, model_kwargs=model_kwargs,
+                                       random_state=np.random.RandomState(random_seed))
+            except Exception as e:  # a failed initialisation must not take the grid down
+                errors[init_id] = e
+
+    num_threads = max(1, min(num_threads, len(ids)))
+    if num_threads == 1:
+        worker(0)
+    else:
+        threads = [threading.Thread(target=worker, args=(s,)) for s in range(num_threads)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    if errors and not results:
+        raise next(iter(errors.values()))
+    stats = dict((i, results[i]['stats']) for i in ids if i in results)
+    best = select_solution(stats, config) if stats else None
+    return results, best, errors
