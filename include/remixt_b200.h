@@ -182,6 +182,13 @@ int rmx_chain_timing(rmx_handle h, int enable, double* total_ms, int64_t* launch
 int rmx_synchronize(rmx_handle h);
 /* The cudaStream_t the handle launches on (for CUDA-event timing by the caller). */
 int rmx_stream(rmx_handle h, void** stream);
+/* CUDA-event timing on the handle's stream: record event `slot` (0..15); elapsed ms between two
+ * recorded events (possibly of two handles on one device); both must have completed. */
+int rmx_event_record(rmx_handle h, int slot);
+int rmx_event_elapsed(rmx_handle h0, int slot0, rmx_handle h1, int slot1, double* ms);
+/* Measured FP64 FMA peak of the device (dependent-chain-free DFMA micro-benchmark, best of 5),
+ * in TFLOP/s: the denominator of the FP64 roofline. */
+int rmx_fp64_peak(int device, double* tflops);
 
 #ifdef __cplusplus
 }

@@ -39,6 +39,7 @@ EXPORTS = [
     'rmx_infer_cn', 'rmx_calculate_log_transmat', 'rmx_eval',
     'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product',
     'rmx_launch_count', 'rmx_global_launch_count', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
+    'rmx_event_record', 'rmx_event_elapsed', 'rmx_fp64_peak',
 ]
 
 
@@ -90,6 +91,9 @@ def _load():
         'rmx_chain_timing': [H, I, C.POINTER(D), C.POINTER(I64)],
         'rmx_synchronize': [H],
         'rmx_stream': [H, C.POINTER(P)],
+        'rmx_event_record': [H, I],
+        'rmx_event_elapsed': [H, I, H, I, C.POINTER(D)],
+        'rmx_fp64_peak': [I, C.POINTER(D)],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -132,3 +136,10 @@ def global_launch_count():
     n = C.c_int64(0)
     lib.rmx_global_launch_count(C.byref(n))
     return n.value
+
+
+def fp64_peak(device=0):
+    """Measured DFMA peak of the device in TFLOP/s."""
+    v = C.c_double(0.)
+    check(lib.rmx_fp64_peak(int(device), C.byref(v)), None)
+    return v.value

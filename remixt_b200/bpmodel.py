@@ -359,6 +359,15 @@ class RemixtModel(object):
     def synchronize(self):
         check(lib.rmx_synchronize(self._handle), self._handle)
 
+    def event_record(self, slot):
+        check(lib.rmx_event_record(self._handle, int(slot)), self._handle)
+
+    def event_elapsed(self, slot0, other, slot1):
+        """Milliseconds between event ``slot0`` of this model and event ``slot1`` of ``other``."""
+        ms = C.c_double()
+        check(lib.rmx_event_elapsed(self._handle, int(slot0), other._handle, int(slot1), C.byref(ms)), self._handle)
+        return ms.value
+
 
 def _scalar_property(name):
     return property(lambda self: self._get_scalar(name), lambda self, v: self._set_scalar(name, v))

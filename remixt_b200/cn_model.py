@@ -274,8 +274,9 @@ class BreakpointModel(object):
             self.is_telomere, self.breakpoint_idx, self.breakpoint_orient,
             self.transition_log_prob, self.divergence_weight, **self.model_kwargs)
 
-    def fit(self, h_init):
-        """Fit the model with a series of updates (``cn_model.py:354-428``)."""
+    def prepare(self, h_init):
+        """Everything ``fit`` does before its EM loop (``cn_model.py:354-407``): build the ``RemixtModel``,
+        set masks and transition model, evaluate the first ELBO."""
         self.model = self._make_model(h_init)
         self.model.total_likelihood_mask = self._total_likelihood_mask.astype(int)
         self.model.allele_likelihood_mask = self._allele_likelihood_mask.astype(int)
@@ -293,6 +294,10 @@ class BreakpointModel(object):
 
         if self.prev_elbo is None:
             self.prev_elbo = self.model.calculate_elbo()
+
+    def fit(self, h_init):
+        """Fit the model with a series of updates (``cn_model.py:354-428``)."""
+        self.prepare(h_init)
 
         for i in range(self.num_em_iter):
             for j in range(self.num_update_iter):

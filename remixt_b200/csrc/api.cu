@@ -86,6 +86,7 @@ struct rmx_model_s {
     bool hist_valid = false;
     bool path_valid = false;
 
+    cudaEvent_t ev[16] = {};
     // chain timing
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> tev;
@@ -343,6 +344,7 @@ int rmx_destroy(rmx_handle m) {
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
     for (auto& pr : m->tev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+    for (int i = 0; i < 16; ++i) if (m->ev[i]) cudaEventDestroy(m->ev[i]);
     for (void* p : m->allocs) cudaFree(p);
     if (m->hp) cudaFreeHost(m->hp);
     if (m->hflags) cudaFreeHost(m->hflags);
@@ -1273,6 +1275,33 @@ int rmx_synchronize(rmx_handle m) {
 int rmx_stream(rmx_handle m, void** stream) {
     if (!m) return RMX_ERR_ARG;
     *stream = (void*)m->stream;
+    return RMX_OK;
+}
+
+int rmx_event_record(rmx_handle m, int slot) {
+    if (!m || slot < 0 || slot >= 16) return RMX_ERR_ARG;
+    cudaSetDevice(m->device);
+    if (!m->ev[slot]) CK(cudaEventCreate(&m->ev[slot]));
+    CK(cudaEventRecord(m->ev[slot], m->stream));
+    return RMX_OK;
+}
+int rmx_event_elapsed(rmx_handle m, int slot0, rmx_handle m1, int slot1, double* ms) {
+    if (!m || !m1 || slot0 < 0 || slot0 >= 16 || slot1 < 0 || slot1 >= 16) return RMX_ERR_ARG;
+    if (!m->ev[slot0] || !m1->ev[slot1]) return m->fail(RMX_ERR_ARG, "event was never recorded");
+    cudaSetDevice(m->device);
+    CK(cudaEventSynchronize(m->ev[slot0]));
+    CK(cudaEventSynchronize(m1->ev[slot1]));
+    float f = 0.f;
+    CK(cudaEventElapsedTime(&f, m->ev[slot0], m1->ev[slot1]));
+    *ms = (double)f;
+    return RMX_OK;
+}
+int rmx_fp64_peak(int device, double* tflops) {
+    double v = 0.;
+    const char* e = rmx_measure_fp64_peak(device, &v);
+    if (e) { g_create_error = e; return RMX_ERR_CUDA; }
+    *tflops = v;
+    g_launches += 6;
     return RMX_OK;
 }
 

@@ -91,3 +91,6 @@ void rmx_launch_sum_product_2p(cudaStream_t st, int64_t N, int S, const double* 
                                double e0, double e1);
 void rmx_launch_max_product(cudaStream_t st, int64_t N, int S, const double* F, const double* Tm, double* lattice,
                             int64_t* path, double* logprob);
+
+// DFMA micro-benchmark; returns nullptr on success, else an error string
+const char* rmx_measure_fp64_peak(int device, double* tflops);

@@ -597,3 +597,48 @@ void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, cons
                      int u, int v, int w, double* out, int* dflags) {
     k_eval<<<1, 32, 0, st>>>(T, d, P, what, n, s, u, v, w, out, dflags);
 }
+
+// ---------------------------------------------------------------------------------------------
+// FP64 peak: 8 independent DFMA chains per thread, 1024 iterations, 148*8 CTAs of 256 threads.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_dfma_peak(double* __restrict__ out, double a, double b, int iters) {
+    double x0 = threadIdx.x, x1 = x0 + 1., x2 = x0 + 2., x3 = x0 + 3., x4 = x0 + 4., x5 = x0 + 5., x6 = x0 + 6., x7 = x0 + 7.;
+    for (int i = 0; i < iters; ++i) {
+        x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+        x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+    double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 123.456) out[blockIdx.x * blockDim.x + threadIdx.x] = s;   // never true; keeps the chains live
+}
+
+const char* rmx_measure_fp64_peak(int device, double* tflops) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    double* buf = nullptr;
+    const int grid = sms * 8, iters = 4096;
+    e = cudaMalloc((void**)&buf, (size_t)grid * 256 * sizeof(double));
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.;
+    for (int rep = 0; rep < 6; ++rep) {
+        cudaEventRecord(e0, 0);
+        k_dfma_peak<<<grid, 256>>>(buf, 0.999999, 1e-9, iters);
+        cudaEventRecord(e1, 0);
+        e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double tf = 2.0 * 8.0 * iters * (double)grid * 256.0 / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    *tflops = best;
+    return nullptr;
+}
