@@ -188,3 +188,52 @@ def fit_grid(experiment, init_params_by_id, config, device=None, random_seed=123
     stats = dict((i, results[i]['stats']) for i in ids if i in results)
     best = select_solution(stats, config) if stats else None
     return results, best, errors
+
+
+def shard_ids(ids, rank, world_size):
+    """Initialisations of the grid that rank ``rank`` fits: a strided slice, so every rank gets a
+    mix of (mode, mix_frac, divergence_weight) combinations of similar cost."""
+    return list(ids)[rank::world_size]
+
+
+def fit_grid_distributed(experiment, init_params_by_id, config, dist=None, device=None, random_seed=1234,
+                         num_threads=4, **fit_kwargs):
+    """The init grid over the ranks of a ``torch.distributed`` process group (one process per GPU).
+
+    The grid is the unit that shards: fits are independent, so there is no data-path
+    collective; every rank fits ``shard_ids(ids, rank, world)`` on its own device and the per-fit
+    ``stats`` dicts (about ten scalars each) are exchanged once at the end with ``all_gather_object``.
+    Every rank then applies the reference's selection rule (``analysis/pipeline.py:253-259``) to the
+    full table, so all ranks return the same ``best`` id.  Returns ``(local_results, all_stats, best)``.
+    """
+    ids = list(init_params_by_id.keys())
+    rank = dist.get_rank() if dist is not None else 0
+    world = dist.get_world_size() if dist is not None else 1
+    mine = shard_ids(ids, rank, world)
+    model_kwargs = {} if device is None else {'device': device}
+    results = {}
+
+    def worker(slot):
+        for pos in range(slot, len(mine), num_threads):
+            init_id = mine[pos]
+            results[init_id] = fit(experiment, init_params_by_id[init_id], config, model_kwargs=model_kwargs,
+                                   random_state=np.random.RandomState(random_seed), **fit_kwargs)
+
+    nt = max(1, min(num_threads, len(mine)))
+    threads = [threading.Thread(target=worker, args=(s,)) for s in range(nt)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    local_stats = dict((i, results[i]['stats']) for i in mine if i in results)
+    if dist is not None and world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, local_stats)
+        all_stats = {}
+        for part in gathered:
+            all_stats.update(part)
+    else:
+        all_stats = local_stats
+    ordered = dict((i, all_stats[i]) for i in ids if i in all_stats)
+    best = select_solution(ordered, config) if ordered else None
+    return results, ordered, best

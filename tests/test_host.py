@@ -1,0 +1,125 @@
+"""Host-side logic and the C-ABI surface, CPU only (no compute entry point is called without a GPU).
+
+  * libremixt_b200.so loads and exports every symbol include/remixt_b200.h declares;
+  * the state-space enumerators and the segment remap of the host driver (remixt_b200/cn_model.py)
+    against the reference's own cn_model.py, imported in place where /root/reference exists;
+  * the host driver's EM loop (scipy M-steps, global RNG consumption, accept/reject) driving the
+    compiled UNMODIFIED reference RemixtModel reproduces the reference's full fit bit for bit;
+  * solution selection.
+"""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from tests import util
+
+ROOT = util.ROOT
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    from remixt_b200 import _lib
+    header = open(os.path.join(ROOT, 'include', 'remixt_b200.h')).read()
+    declared = set(re.findall(r'^(?:int|const char\*)\s+(rmx_\w+)\s*\(', header, flags=re.M))
+    assert len(declared) >= 30
+    assert declared == set(_lib.EXPORTS), declared.symmetric_difference(_lib.EXPORTS)
+    for name in declared:
+        assert hasattr(_lib.lib, name), name
+
+
+def test_cabi_fails_loudly_without_gpu():
+    """No CPU fallback: on a machine without a CUDA device creating a model raises."""
+    from remixt_b200 import _lib
+    if _lib.device_count() > 0:
+        pytest.skip('a CUDA device is present')
+    exp = util.load_experiment('small')
+    with pytest.raises(RuntimeError):
+        util.make_driver(exp, util.init_params('small', 0))
+
+
+@pytest.mark.parametrize('M,cn_max,S,B', [(2, 6, 16, 7), (3, 6, 97, 19), (3, 8, 165, 25), (4, 6, 457, 43)])
+def test_state_space_sizes(M, cn_max, S, B):
+    """Sizes the reference's enumerators produce (probe)."""
+    from remixt_b200 import cn_model
+    assert cn_model.create_cn_states(M, 2, cn_max, 1).shape == (S, M, 2)
+    assert cn_model.create_brk_states(M, cn_max, 1).shape == (B, M)
+
+
+@pytest.fixture(scope='module')
+def ref_cn_model():
+    from oracle import refenv
+    if not refenv.available():
+        pytest.skip('/root/reference not present (GPU box)')
+    from oracle import build_ref
+    if build_ref.build(verbose=False) is None:
+        pytest.skip('reference extension could not be built')
+    refenv.install()
+    import remixt.cn_model as rcn
+    return rcn
+
+
+def test_state_tables_match_reference(ref_cn_model):
+    from remixt_b200 import cn_model
+    ref = ref_cn_model.BreakpointModel.__new__(ref_cn_model.BreakpointModel)
+    for M, cn_max in ((2, 6), (3, 6), (3, 8)):
+        assert np.array_equal(cn_model.create_cn_states(M, 2, cn_max, 1), ref.create_cn_states(M, 2, cn_max, 1))
+        assert np.array_equal(cn_model.create_brk_states(M, cn_max, 1), ref.create_brk_states(M, cn_max, 1))
+
+
+@pytest.mark.parametrize('name', ['small', 'config1', 'genome5k'])
+def test_segment_remap_matches_reference(ref_cn_model, name):
+    """Dummy-segment insertion (cn_model.py:82-167) and the likelihood masks (:169-184)."""
+    from remixt_b200 import cn_model
+    exp = util.load_experiment(name)
+    ip = util.init_params(name, 0)
+    kw = dict(max_copy_number=6, normal_contamination=True, divergence_weight=ip['divergence_weight'],
+              min_segment_length=10000, min_proportion_genotyped=0.01, max_depth=ip['max_depth'],
+              normal_copies=np.array([[1, 1]] * exp.l.shape[0]))
+    a = cn_model.BreakpointModel(exp.x, exp.l, exp.adjacencies, exp.breakpoints, **kw)
+    b = ref_cn_model.BreakpointModel(exp.x, exp.l, exp.adjacencies, exp.breakpoints, **kw)
+    assert a.N1 == b.N1
+    for attr in ('seg_fwd_remap', 'seg_rev_remap', 'is_telomere', 'breakpoint_idx', 'breakpoint_orient', 'x1', 'l1',
+                 '_total_likelihood_mask', '_allele_likelihood_mask'):
+        assert np.array_equal(np.asarray(getattr(a, attr)), np.asarray(getattr(b, attr))), attr
+    assert list(a.breakpoint_ids) == list(b.breakpoint_ids)
+
+
+@pytest.mark.slow
+def test_host_driver_full_fit_on_reference_model_is_bit_exact(ref_bpmodel):
+    """pipeline.fit of this repo (host driver) on the compiled reference RemixtModel == the reference's
+    own pipeline.fit (golden fit_small.npz): the host side adds no numerical difference of its own."""
+    from remixt_b200 import pipeline
+    g = util.golden('fit_small.npz')
+    exp = util.load_experiment('small')
+    ip = util.init_params('small', int(g['init_id']))
+    cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
+    np.random.seed(1234)
+    res = pipeline.fit(exp, ip, cfg, model_class=ref_bpmodel.RemixtModel)
+    assert res['stats']['elbo'] == float(g['elbo'])
+    assert np.array_equal(res['h'], g['h'])
+    assert np.array_equal(res['cn'], g['cn'])
+    ids = [str(i) for i in g['brk_ids']]
+    assert np.array_equal(np.array([res['brk_cn'][i] for i in ids]), g['brk_cn'])
+    for k in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
+        assert res['stats'][k] == float(g[k]), k
+    assert np.array_equal(res['p_outlier_total'], g['p_outlier_total'])
+
+
+def test_select_solution_rule():
+    """analysis/pipeline.py:253-259: best ELBO among proportion_divergent < 0.5, else among all."""
+    from remixt_b200 import pipeline
+    stats = {0: dict(elbo=-10., proportion_divergent=0.6), 1: dict(elbo=-20., proportion_divergent=0.1),
+             2: dict(elbo=-15., proportion_divergent=0.2), 3: dict(elbo=-15., proportion_divergent=0.3)}
+    assert pipeline.select_solution(stats) == 2
+    assert pipeline.select_solution({0: stats[0]}) == 0
+    assert pipeline.shard_ids(range(7), 1, 3) == [1, 4]
+
+
+def test_decode_breakpoints_naive():
+    from remixt_b200 import cn_model
+    cn = np.array([[[1, 1], [2, 1]], [[1, 1], [1, 1]], [[1, 1], [2, 1]]])
+    adj = [(0, 1), (1, 2)]
+    brk = {'a': frozenset([(0, 1), (2, 0)])}
+    out = cn_model.decode_breakpoints_naive(cn, adj, brk)
+    assert np.array_equal(out['a'], [0, 1])
