@@ -7,9 +7,12 @@ Three kinds of checks, in decreasing strength:
     (oracle/make_golden.py -> tests/golden/steps_*.npz, fit_*.npz);
   * properties at sizes the reference cannot run in test time.
 
-Tolerances: FP64 quantities 1e-6 relative as BASELINE.json's north_star states (observed
-agreement is ~1e-12; a tighter 1e-9 is asserted where nothing chaotic sits in between);
-MAP copy number, breakpoint copy number and Viterbi paths bit-exact.
+Tolerances: FP64 quantities 1e-6 relative as BASELINE.json's north_star states; a tighter 1e-7 is
+asserted where nothing chaotic sits in between.  The floor is libm: CUDA's and glibc's lgamma
+each carry a few ulp of error on lgamma(1e5) ~ 1e6, i.e. ~1e-9 absolute on a log-likelihood, which
+shows up as ~1e-9 relative on the posteriors (CPython's math.lgamma differs from glibc's by the
+same amount, see oracle/bpmodel_np.py).  MAP copy number, breakpoint copy number and Viterbi
+paths bit-exact.
 """
 import numpy as np
 import pytest
@@ -19,7 +22,7 @@ from tests import util
 pytestmark = pytest.mark.gpu
 
 RTOL = 1e-6       # the north_star tolerance
-RTOL_TIGHT = 1e-9
+RTOL_TIGHT = 1e-7
 
 
 @pytest.fixture(scope='module')
