@@ -14,6 +14,15 @@
  *
  * There is no CPU fallback behind this interface: every compute entry point launches
  * sm_100a kernels on the handle's device and fails with RMX_ERR_CUDA if it cannot.
+ *
+ * Batches.  The reference fits one RemixtModel per initialisation of its (h, ploidy) grid, each in its own
+ * process (workflow.py:329-340, analysis/pipeline.py:42-103).  Those fits share the data, the state tables
+ * and the breakpoint structure, so here they live in one BATCH whose kernels each serve all fits in one
+ * launch.  A handle addresses a contiguous range of `gn` fits of a batch: rmx_create makes a batch of one
+ * (gn = 1, the reference's semantics exactly), rmx_batch_create a batch of G, rmx_batch_view a sub-range.
+ * Every entry point acts on all fits of its handle: array attributes gain a leading dimension gn, scalar
+ * outputs become arrays of gn doubles, scalar setters assign the value to every fit of the handle.
+ * Calls on handles of one batch are serialised by a per-batch mutex (one CUDA stream per batch).
  */
 #ifndef REMIXT_B200_H
 #define REMIXT_B200_H
@@ -117,13 +126,23 @@ typedef enum {
 /* RemixtModel.__cinit__ (bpmodel.pyx:461-604): validates, uploads, builds derived tables,
  * initial q-factors and the first cached transition expectation. */
 int rmx_create(const rmx_desc* desc, rmx_handle* out);
+/* G fits sharing desc's data and tables; h_init is (G,M) and divergence_weight (G) (desc->h_init and
+ * desc->divergence_weight are ignored).  The returned handle covers all G fits. */
+int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, const double* divergence_weight,
+                     rmx_handle* out);
+/* A handle on fits [first_fit, first_fit + num_fits) of h's range.  The batch lives until its last handle
+ * is destroyed. */
+int rmx_batch_view(rmx_handle h, int first_fit, int num_fits, rmx_handle* out);
+int rmx_num_fits(rmx_handle h, int* num_fits);
 int rmx_destroy(rmx_handle h);
 /* Message of the last failure on this handle (or of rmx_create when h == NULL). */
 const char* rmx_last_error(rmx_handle h);
 int rmx_device_count(int* count);
 
 /* ---- attribute access (cdef public attributes, bpmodel.pyx:398-456) ------------------ */
-/* `count` is the number of ELEMENTS of the host buffer and must match the attribute. */
+/* `count` is the number of ELEMENTS of the host buffer: gn times the attribute's size, fit-major.
+ * rmx_get_scalar writes gn doubles.  The derived tables are the same for every fit (no leading gn).
+ * transition_penalty is fixed at creation; the outlier priors are per batch. */
 int rmx_set_array(rmx_handle h, int array_id, const void* src, int64_t count);
 int rmx_get_array(rmx_handle h, int array_id, void* dst, int64_t count);
 int rmx_set_scalar(rmx_handle h, int scalar_id, double value);
@@ -142,21 +161,24 @@ int rmx_variational_update(rmx_handle h, int n_iter);
 int rmx_variational_energy(rmx_handle h, double* energy);    /* bpmodel.pyx:1060 */
 int rmx_variational_entropy(rmx_handle h, double* entropy);  /* bpmodel.pyx:1044 */
 int rmx_elbo(rmx_handle h, double* elbo);                    /* bpmodel.pyx:1119 */
-/* calculate_expected_log_likelihood(sample) (bpmodel.pyx:1125); sample is the (N1) int64 mask. */
+/* All of the following write gn values (energy / entropy / elbo / E[LL]) or (gn,M) (gradient).
+ * calculate_expected_log_likelihood(sample) (bpmodel.pyx:1125); sample is the (gn,N1) int64 mask. */
 int rmx_expected_log_likelihood(rmx_handle h, const int64_t* sample, double* out);
 /* calculate_expected_log_likelihood_partial_h(sample, partial_h) (bpmodel.pyx:1159); out (M). */
 int rmx_expected_log_likelihood_partial_h(rmx_handle h, const int64_t* sample, double* out);
-/* One launch for a whole 1-D parameter grid (cn_model.py:553-558 evaluates scipy.optimize.brute's
- * grid one point at a time): out[g] = E[LL](sample) with scalar `scalar_id` set to values[g].
- * The model's stored value of the scalar is left at values[n_values-1], which is what the
+/* A whole 1-D parameter grid with one synchronisation (cn_model.py:553-558 evaluates
+ * scipy.optimize.brute's grid one point at a time): values and out are (gn, n_values);
+ * out[g][v] = E[LL](sample[g]) of fit g with scalar `scalar_id` set to values[g][v].
+ * The stored value of the scalar is left at values[g][n_values-1], which is what the
  * reference's point-by-point evaluation leaves behind (stale-parameter quirk). */
 int rmx_expected_log_likelihood_grid(rmx_handle h, const int64_t* sample, int scalar_id,
                                      const double* values, int n_values, double* out);
 
 /* ---- decode ----------------------------------------------------------------------------- */
-/* infer_cn(cn) (bpmodel.pyx:1197): cn is (N1,M,2) int64, filled in place. */
+/* infer_cn(cn) (bpmodel.pyx:1197): cn is (gn,N1,M,2) int64, filled in place. */
 int rmx_infer_cn(rmx_handle h, int64_t* cn);
-/* calculate_log_transmat(out) (bpmodel.pyx:640): out is (N1-1,S,S) f64 filled in place. */
+/* calculate_log_transmat(out) (bpmodel.pyx:640): out is (N1-1,S,S) f64 filled in place; gn must be 1,
+ * as for rmx_eval. */
 int rmx_calculate_log_transmat(rmx_handle h, double* out);
 int rmx_eval(rmx_handle h, int eval_id, int n, int s, int u, int v, int w, double* out);
 

@@ -12,7 +12,11 @@ For an experiment fixture ``tests/golden/exp_NAME.npz`` (made by ``oracle/make_i
    public quantity after each call -> ``tests/golden/steps_NAME.npz``.
 3. ``fit``:   a complete reference ``pipeline.fit`` (seeded) -> ``tests/golden/fit_NAME.npz``.
 
-Usage: python oracle/make_golden.py NAME [init] [steps] [fit] [--em E --vi V] [--init-id I]
+Usage: python oracle/make_golden.py NAME [init] [steps] [fit] [--em E --vi V] [--init-id I] [--tag T] [--h-scale F]
+
+``--h-scale 1.0000000000001 --tag _perturbed`` re-runs the reference fit from an initial h_normal moved by one
+part in 1e13: the spread between that fit and the unperturbed one is the reference's OWN sensitivity to
+rounding-level noise (its Nelder-Mead / L-BFGS-B M-steps amplify it), which calibrates full-fit parity.
 """
 import contextlib
 import io
@@ -166,7 +170,7 @@ def run_steps(name, init_id=0):
     print(name, 'steps: elbo', out['s0/elbo'], '->', out['r1_4/elbo'])
 
 
-def run_fit(name, init_id=0, em=5, vi=5, tag=None):
+def run_fit(name, init_id=0, em=5, vi=5, tag=None, h_scale=1.):
     refenv.install()
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
@@ -174,16 +178,40 @@ def run_fit(name, init_id=0, em=5, vi=5, tag=None):
     d, exp = load_experiment(name)
     ip = init_params_of(d, init_id)
     cfg = {'max_copy_number': 6, 'num_em_iter': em, 'num_update_iter': vi}
+    # record the M-step trajectory (h and dispersion parameters after every EM iteration, ELBO before
+    # every h update) so that the E-step path can be replayed on it (tests: teacher-forced fit)
+    import remixt.cn_model as rcn
+    trace = {'h': [], 'params': [], 'elbo_pre_h': []}
+    orig_h, orig_params = rcn.BreakpointModel.em_update_h, rcn.BreakpointModel.em_update_params
+
+    def em_update_h(self):
+        trace['elbo_pre_h'].append(self.model.calculate_elbo())
+        orig_h(self)
+        trace['h'].append(np.asarray(self.model.h).copy())
+
+    def em_update_params(self):
+        orig_params(self)
+        trace['params'].append([getattr(self.model, k) for k in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')])
+
+    rcn.BreakpointModel.em_update_h, rcn.BreakpointModel.em_update_params = em_update_h, em_update_params
+    if h_scale != 1.:
+        ip = dict(ip)
+        ip['h_normal'] *= h_scale
     np.random.seed(1234)
     t0 = time.time()
-    with contextlib.redirect_stdout(io.StringIO()):
-        res = rp.fit(exp, ip, cfg)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = rp.fit(exp, ip, cfg)
+    finally:
+        rcn.BreakpointModel.em_update_h, rcn.BreakpointModel.em_update_params = orig_h, orig_params
     dt = time.time() - t0
     out = {'init_id': init_id, 'num_em_iter': em, 'num_update_iter': vi, 'seconds': dt,
            'h': res['h'], 'cn': res['cn'], 'p_outlier_total': res['p_outlier_total'],
            'p_outlier_allele': res['p_outlier_allele'], 'elbo': res['stats']['elbo'],
            'elbo_diff': res['stats']['elbo_diff'], 'ploidy': res['stats']['ploidy'],
-           'proportion_divergent': res['stats']['proportion_divergent']}
+           'proportion_divergent': res['stats']['proportion_divergent'],
+           'trace_h': np.array(trace['h']), 'trace_params': np.array(trace['params']),
+           'trace_elbo_pre_h': np.array(trace['elbo_pre_h']), 'h_scale': h_scale}
     for k in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
         out[k] = res['stats'][k]
     ids = sorted(res['brk_cn'].keys())
@@ -204,8 +232,9 @@ def main():
         run_init(name)
     if 'steps' in args:
         run_steps(name, init_id)
+    h_scale = float(args[args.index('--h-scale') + 1]) if '--h-scale' in args else 1.
     if 'fit' in args:
-        run_fit(name, init_id, em, vi, tag)
+        run_fit(name, init_id, em, vi, tag, h_scale)
 
 
 if __name__ == '__main__':

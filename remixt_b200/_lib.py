@@ -30,7 +30,7 @@ U_ALLELE_SWAP, U_CN, U_BREAKPOINT, U_OUTLIER_TOTAL, U_OUTLIER_ALLELE, U_FRAMELOG
 
 # every symbol include/remixt_b200.h declares
 EXPORTS = [
-    'rmx_create', 'rmx_destroy', 'rmx_last_error', 'rmx_device_count',
+    'rmx_create', 'rmx_batch_create', 'rmx_batch_view', 'rmx_num_fits', 'rmx_destroy', 'rmx_last_error', 'rmx_device_count',
     'rmx_set_array', 'rmx_get_array', 'rmx_set_scalar', 'rmx_get_scalar', 'rmx_get_derived',
     'rmx_update', 'rmx_variational_update',
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
@@ -65,19 +65,22 @@ def _load():
     H, I, I64, D, P = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_void_p
     sigs = {
         'rmx_create': [C.POINTER(RmxDesc), C.POINTER(H)],
+        'rmx_batch_create': [C.POINTER(RmxDesc), I, P, P, C.POINTER(H)],
+        'rmx_batch_view': [H, I, I, C.POINTER(H)],
+        'rmx_num_fits': [H, C.POINTER(I)],
         'rmx_destroy': [H],
         'rmx_device_count': [C.POINTER(I)],
         'rmx_set_array': [H, I, P, I64],
         'rmx_get_array': [H, I, P, I64],
         'rmx_set_scalar': [H, I, D],
-        'rmx_get_scalar': [H, I, C.POINTER(D)],
+        'rmx_get_scalar': [H, I, P],
         'rmx_get_derived': [H, I, P, I64],
         'rmx_update': [H, I],
         'rmx_variational_update': [H, I],
-        'rmx_variational_energy': [H, C.POINTER(D)],
-        'rmx_variational_entropy': [H, C.POINTER(D)],
-        'rmx_elbo': [H, C.POINTER(D)],
-        'rmx_expected_log_likelihood': [H, P, C.POINTER(D)],
+        'rmx_variational_energy': [H, P],
+        'rmx_variational_entropy': [H, P],
+        'rmx_elbo': [H, P],
+        'rmx_expected_log_likelihood': [H, P, P],
         'rmx_expected_log_likelihood_partial_h': [H, P, P],
         'rmx_expected_log_likelihood_grid': [H, P, I, P, I, P],
         'rmx_infer_cn': [H, P],

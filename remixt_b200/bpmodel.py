@@ -51,17 +51,22 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-class RemixtModel(object):
-    """Structured variational inference core of ReMixT on one B200 (``bpmodel.pyx:397``)."""
+class _ModelBase(object):
+    """Shared plumbing of :class:`RemixtModel` (one fit) and :class:`RemixtBatch` (G fits in one set of
+    launches).  ``_gn`` is the number of fits the handle covers; with ``_single`` the leading fit
+    dimension is dropped so the object looks exactly like the reference's ``RemixtModel``."""
 
     _handle = None
+    _single = True
+    _gn = 1
+    _parent = None
 
-    def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination,
-                 cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
-                 breakpoint_orient, transition_penalty, divergence_weight, device=None):
+    def _setup(self, num_clones, num_segments, num_breakpoints, normal_contamination,
+               cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
+               breakpoint_orient, transition_penalty, divergence_weight, device, num_fits):
         cn_states = _typed(cn_states, np.int64, 4, 'cn_states')
         brk_states = _typed(brk_states, np.int64, 2, 'brk_states')
-        h_init = _typed(h_init, np.float64, 1, 'h_init')
+        h_init = _typed(h_init, np.float64, 1 if num_fits is None else 2, 'h_init')
         l = _typed(l, np.float64, 1, 'l')
         x = _typed(x, np.float64, 1, 'x')
         y = _typed(y, np.float64, 2, 'y')
@@ -86,7 +91,7 @@ class RemixtModel(object):
             raise ValueError('cn_states must have shape (num_segments, num_cn_states, num_clones, num_alleles)')
         if brk_states.shape[1] != num_clones:
             raise ValueError('cn_states must have shape (num_brk_states, num_clones)')
-        if h_init.shape[0] != num_clones:
+        if h_init.shape[-1] != num_clones:
             raise ValueError('h must have length equal to num_clones')
         if is_telomere.shape[0] != num_segments:
             raise ValueError('is_telomere must have length equal to num_segments')
@@ -124,9 +129,16 @@ class RemixtModel(object):
         desc.breakpoint_idx = _ptr(breakpoint_idx)
         desc.breakpoint_orient = _ptr(breakpoint_orient)
         desc.transition_penalty = float(transition_penalty)
-        desc.divergence_weight = float(divergence_weight)
         handle = C.c_void_p()
-        rc = lib.rmx_create(C.byref(desc), C.byref(handle))
+        if num_fits is None:
+            desc.divergence_weight = float(divergence_weight)
+            rc = lib.rmx_create(C.byref(desc), C.byref(handle))
+        else:
+            dw = np.ascontiguousarray(np.broadcast_to(np.asarray(divergence_weight, dtype=np.float64), (num_fits,)))
+            if h_init.shape[0] != num_fits:
+                raise ValueError('h_init must have one row per fit')
+            desc.divergence_weight = 0.
+            rc = lib.rmx_batch_create(C.byref(desc), int(num_fits), _ptr(h_init), _ptr(dw), C.byref(handle))
         check(rc, None)
         self._handle = handle
         self._derived = {}
@@ -140,21 +152,31 @@ class RemixtModel(object):
                 pass
 
     # ------------------------------------------------------------------ attribute plumbing
+    def _out(self, a):
+        return a[0] if self._single else a
+
     def _get(self, array_id, shape, dtype=np.float64):
-        out = np.empty(shape, dtype=dtype)
+        out = np.empty((self._gn,) + tuple(shape), dtype=dtype)
         check(lib.rmx_get_array(self._handle, array_id, _ptr(out), out.size), self._handle)
-        return out
+        return self._out(out)
 
     def _set(self, array_id, value, shape, dtype=np.float64):
-        a = np.ascontiguousarray(np.asarray(value), dtype=dtype)
-        if a.shape != tuple(shape):
+        a = np.asarray(value)
+        full = (self._gn,) + tuple(shape)
+        if a.shape != tuple(shape) and a.shape != full:
             raise ValueError('array of shape %s expected, got %s' % (tuple(shape), a.shape))
+        a = np.ascontiguousarray(np.broadcast_to(a, full), dtype=dtype)
         check(lib.rmx_set_array(self._handle, array_id, _ptr(a), a.size), self._handle)
 
     def _get_scalar(self, name):
-        v = C.c_double()
-        check(lib.rmx_get_scalar(self._handle, _lib.SCALAR_IDS[name], C.byref(v)), self._handle)
-        return v.value
+        v = np.empty((self._gn,), dtype=np.float64)
+        check(lib.rmx_get_scalar(self._handle, _lib.SCALAR_IDS[name], _ptr(v)), self._handle)
+        return float(v[0]) if self._single else v
+
+    def _scalars_out(self, fn, *args):
+        v = np.empty((self._gn,), dtype=np.float64)
+        check(fn(self._handle, *(args + (_ptr(v),))), self._handle)
+        return float(v[0]) if self._single else v
 
     def _set_scalar(self, name, value):
         check(lib.rmx_set_scalar(self._handle, _lib.SCALAR_IDS[name], float(value)), self._handle)
@@ -221,7 +243,8 @@ class RemixtModel(object):
 
     @property
     def transition_model(self):
-        return int(self._get_scalar('transition_model'))
+        v = self._get_scalar('transition_model')
+        return int(v) if self._single else v.astype(int)
 
     @transition_model.setter
     def transition_model(self, value):
@@ -253,53 +276,50 @@ class RemixtModel(object):
 
     # ------------------------------------------------------------------ objective
     def calculate_variational_entropy(self):
-        v = C.c_double()
-        check(lib.rmx_variational_entropy(self._handle, C.byref(v)), self._handle)
-        return v.value
+        return self._scalars_out(lib.rmx_variational_entropy)
 
     def calculate_variational_energy(self):
-        v = C.c_double()
-        check(lib.rmx_variational_energy(self._handle, C.byref(v)), self._handle)
-        return v.value
+        return self._scalars_out(lib.rmx_variational_energy)
 
     def calculate_elbo(self):
-        v = C.c_double()
-        check(lib.rmx_elbo(self._handle, C.byref(v)), self._handle)
-        return v.value
+        return self._scalars_out(lib.rmx_elbo)
 
     def _sample(self, sample):
-        s = np.ascontiguousarray(np.asarray(sample), dtype=np.int64)
-        if s.shape != (self.num_segments,):
+        s = np.asarray(sample)
+        if s.shape != (self.num_segments,) and s.shape != (self._gn, self.num_segments):
             raise ValueError('sample must have length equal to num_segments')
-        return s
+        return np.ascontiguousarray(np.broadcast_to(s, (self._gn, self.num_segments)), dtype=np.int64)
 
     def calculate_expected_log_likelihood(self, sample):
         s = self._sample(sample)
-        v = C.c_double()
-        check(lib.rmx_expected_log_likelihood(self._handle, _ptr(s), C.byref(v)), self._handle)
-        return v.value
+        return self._scalars_out(lib.rmx_expected_log_likelihood, _ptr(s))
 
     def calculate_expected_log_likelihood_partial_h(self, sample, partial_h):
         s = self._sample(sample)
-        out = np.zeros((self.num_clones,), dtype=np.float64)
+        out = np.zeros((self._gn, self.num_clones), dtype=np.float64)
         check(lib.rmx_expected_log_likelihood_partial_h(self._handle, _ptr(s), _ptr(out)), self._handle)
-        partial_h[:] = out
+        partial_h[...] = self._out(out)
 
     def calculate_expected_log_likelihood_grid(self, sample, name, values):
         """E[LL](sample) for each value of the named dispersion parameter, one synchronisation
-        (extension used by the batched M-step; see ``rmx_expected_log_likelihood_grid``)."""
+        (extension used by the batched M-step; see ``rmx_expected_log_likelihood_grid``).  ``values`` is
+        ``(n,)`` (every fit evaluates the same grid) or ``(gn, n)``."""
         s = self._sample(sample)
-        vals = np.ascontiguousarray(values, dtype=np.float64)
+        vals = np.asarray(values, dtype=np.float64)
+        n = vals.shape[-1]
+        vals = np.ascontiguousarray(np.broadcast_to(vals, (self._gn, n)))
         out = np.zeros(vals.shape, dtype=np.float64)
         check(lib.rmx_expected_log_likelihood_grid(self._handle, _ptr(s), _lib.SCALAR_IDS[name], _ptr(vals),
-                                                   vals.size, _ptr(out)), self._handle)
-        return out
+                                                   n, _ptr(out)), self._handle)
+        return self._out(out)
 
     # ------------------------------------------------------------------ decode / inspection
     def infer_cn(self, cn):
-        if not (isinstance(cn, np.ndarray) and cn.dtype == np.int64 and cn.flags.c_contiguous and
-                cn.shape == (self.num_segments, self.num_clones, self.num_alleles)):
-            raise ValueError('cn must be a C-contiguous int64 array of shape (num_segments, num_clones, 2)')
+        shape = (self.num_segments, self.num_clones, self.num_alleles)
+        if not self._single:
+            shape = (self._gn,) + shape
+        if not (isinstance(cn, np.ndarray) and cn.dtype == np.int64 and cn.flags.c_contiguous and cn.shape == shape):
+            raise ValueError('cn must be a C-contiguous int64 array of shape %s' % (shape,))
         check(lib.rmx_infer_cn(self._handle, _ptr(cn)), self._handle)
 
     @property
@@ -369,6 +389,69 @@ class RemixtModel(object):
         return ms.value
 
 
+class RemixtModel(_ModelBase):
+    """Structured variational inference core of ReMixT on one B200 (``bpmodel.pyx:397``): one fit."""
+
+    def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination,
+                 cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
+                 breakpoint_orient, transition_penalty, divergence_weight, device=None):
+        self._setup(num_clones, num_segments, num_breakpoints, normal_contamination, cn_states, brk_states,
+                    h_init, l, x, y, is_telomere, breakpoint_idx, breakpoint_orient, transition_penalty,
+                    divergence_weight, device, None)
+
+
+class RemixtBatch(_ModelBase):
+    """G fits that share data, state tables and breakpoint structure -- the fits of the reference's
+    initialisation grid (``analysis/pipeline.py:42-103``) -- advanced by the same kernel launches.
+
+    Same constructor as :class:`RemixtModel` except ``h_init`` is ``(G, M)`` and ``divergence_weight``
+    ``(G,)``.  Every method acts on all G fits: array attributes have a leading dimension G, scalar
+    results are ``(G,)`` arrays.  ``batch.fit(g)`` is a :class:`RemixtModel` view of fit ``g`` (the same
+    device state) on which the host driver of one fit runs unchanged.
+    """
+    _single = False
+
+    def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination,
+                 cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
+                 breakpoint_orient, transition_penalty, divergence_weight, device=None):
+        h_init = np.ascontiguousarray(h_init, dtype=np.float64)
+        if h_init.ndim != 2:
+            raise ValueError('h_init of a batch must be (num_fits, num_clones)')
+        self._gn = h_init.shape[0]
+        self._setup(num_clones, num_segments, num_breakpoints, normal_contamination, cn_states, brk_states,
+                    h_init, l, x, y, is_telomere, breakpoint_idx, breakpoint_orient, transition_penalty,
+                    divergence_weight, device, self._gn)
+        self._views = {}
+
+    @property
+    def num_fits(self):
+        return self._gn
+
+    def fit(self, g):
+        """:class:`RemixtModel` view of fit ``g``."""
+        if g not in self._views:
+            if not 0 <= g < self._gn:
+                raise IndexError(g)
+            handle = C.c_void_p()
+            check(lib.rmx_batch_view(self._handle, int(g), 1, C.byref(handle)), self._handle)
+            view = RemixtModel.__new__(RemixtModel)
+            for k in ('num_clones', 'num_segments', 'num_breakpoints', 'normal_contamination', 'num_alleles',
+                      'cn_states', 'brk_states', 'cn_max', 'num_cn_states', 'num_brk_states', 'is_telomere',
+                      'breakpoint_idx', 'breakpoint_orient', 'device'):
+                setattr(view, k, getattr(self, k))
+            view._handle = handle
+            view._derived = self._derived
+            view._parent = self          # keeps the batch object (not only the device batch) alive
+            self._views[g] = view
+        return self._views[g]
+
+    def __len__(self):
+        return self._gn
+
+    def __getitem__(self, g):
+        return self.fit(g)
+
+
 def _scalar_property(name):
     return property(lambda self: self._get_scalar(name), lambda self, v: self._set_scalar(name, v))
 
@@ -377,7 +460,7 @@ for _name in ('negbin_r_0', 'negbin_r_1', 'negbin_hdel_mu', 'negbin_hdel_r_0', '
               'betabin_M_0', 'betabin_M_1', 'betabin_loh_p', 'betabin_loh_M_0', 'betabin_loh_M_1',
               'prior_outlier_total', 'prior_outlier_allele', 'transition_penalty', 'divergence_weight',
               'hmm_log_norm_const'):
-    setattr(RemixtModel, _name, _scalar_property(_name))
+    setattr(_ModelBase, _name, _scalar_property(_name))
 
 
 # ---------------------------------------------------------------------- module functions

@@ -258,8 +258,10 @@ class BreakpointModel(object):
             print('nothing for ' + name)
         return None
 
-    def _make_model(self, h_init):
-        M = h_init.shape[0]
+    def model_args(self, h_init):
+        """Positional arguments of the ``RemixtModel`` constructor for this segmentation
+        (``cn_model.py:359-384``); ``h_init`` is ``(M,)``, or ``(G, M)`` for a ``RemixtBatch``."""
+        M = np.asarray(h_init).shape[-1]
         table = create_cn_states(M, 2, self.max_copy_number, self.max_copy_number_diff)
         brk_states = create_brk_states(M, self.max_copy_number, self.max_copy_number_diff)
         # (N1, S, M, 2): the shared state table with clone 0 replaced by the segment's germline
@@ -267,17 +269,19 @@ class BreakpointModel(object):
         cn_states = np.empty((self.N1,) + table.shape, dtype=table.dtype)
         cn_states[:] = table[np.newaxis]
         cn_states[:, :, 0, :] = np.asarray(self.normal_copies)[self.seg_rev_remap][:, np.newaxis, :]
-        return self.model_class(
-            M, self.N1, self.num_breakpoints, self.normal_contamination,
-            cn_states, brk_states, h_init,
-            self.l1, self.x1[:, 2], self.x1[:, 0:2],
-            self.is_telomere, self.breakpoint_idx, self.breakpoint_orient,
-            self.transition_log_prob, self.divergence_weight, **self.model_kwargs)
+        return (M, self.N1, self.num_breakpoints, self.normal_contamination,
+                cn_states, brk_states, h_init,
+                self.l1, self.x1[:, 2], self.x1[:, 0:2],
+                self.is_telomere, self.breakpoint_idx, self.breakpoint_orient,
+                self.transition_log_prob)
 
-    def prepare(self, h_init):
-        """Everything ``fit`` does before its EM loop (``cn_model.py:354-407``): build the ``RemixtModel``,
-        set masks and transition model, evaluate the first ELBO."""
-        self.model = self._make_model(h_init)
+    def _make_model(self, h_init):
+        return self.model_class(*(self.model_args(h_init) + (self.divergence_weight,)), **self.model_kwargs)
+
+    def attach(self, model):
+        """Adopt ``model`` (a fresh ``RemixtModel``, or a view of one fit of a ``RemixtBatch``) and apply the
+        per-fit settings ``fit`` applies after construction (``cn_model.py:386-404``)."""
+        self.model = model
         self.model.total_likelihood_mask = self._total_likelihood_mask.astype(int)
         self.model.allele_likelihood_mask = self._allele_likelihood_mask.astype(int)
 
@@ -292,33 +296,38 @@ class BreakpointModel(object):
 
         self.model.transition_model = self.transition_model
 
+    def prepare(self, h_init):
+        """Everything ``fit`` does before its EM loop (``cn_model.py:354-407``): build the ``RemixtModel``,
+        set masks and transition model, evaluate the first ELBO."""
+        self.attach(self._make_model(h_init))
         if self.prev_elbo is None:
             self.prev_elbo = self.model.calculate_elbo()
+
+    def record_iteration(self, i, elbo):
+        """Bookkeeping at the end of an EM iteration (``cn_model.py:418-428``)."""
+        self.prev_elbo_diff = elbo - self.prev_elbo
+        self.prev_elbo = elbo
+        if self.verbose:
+            print('[{}] completed iteration {}'.format(_now(), i))
+            print('[{}]     elbo: {:.10f}'.format(_now(), self.prev_elbo))
+            print('[{}]     elbo diff: {:.10f}'.format(_now(), self.prev_elbo_diff))
+            print('[{}]     h = {}'.format(_now(), np.asarray(self.model.h)))
+            for name, value in self.get_likelihood_param_values().items():
+                print('[{}]     {} = {}'.format(_now(), name, value))
 
     def fit(self, h_init):
         """Fit the model with a series of updates (``cn_model.py:354-428``)."""
         self.prepare(h_init)
 
         for i in range(self.num_em_iter):
-            for j in range(self.num_update_iter):
-                self.variational_update()
+            self.variational_update(self.num_update_iter)
 
             if self.do_h_update:
                 self.em_update_h()
 
             self.em_update_params()
 
-            elbo = self.model.calculate_elbo()
-            self.prev_elbo_diff = elbo - self.prev_elbo
-            self.prev_elbo = elbo
-
-            if self.verbose:
-                print('[{}] completed iteration {}'.format(_now(), i))
-                print('[{}]     elbo: {:.10f}'.format(_now(), self.prev_elbo))
-                print('[{}]     elbo diff: {:.10f}'.format(_now(), self.prev_elbo_diff))
-                print('[{}]     h = {}'.format(_now(), np.asarray(self.model.h)))
-                for name, value in self.get_likelihood_param_values().items():
-                    print('[{}]     {} = {}'.format(_now(), name, value))
+            self.record_iteration(i, self.model.calculate_elbo())
 
     @contextlib.contextmanager
     def elbo_check(self, name, threshold=-1e-6):
@@ -336,11 +345,15 @@ class BreakpointModel(object):
         if elbo_after - elbo_before < threshold:
             raise Exception('elbo error for step {}!'.format(name))
 
-    def variational_update(self):
-        """One round of the coordinate updates, in the reference's order (``cn_model.py:444-460``)."""
+    def variational_update(self, n_iter=1):
+        """``n_iter`` rounds of the coordinate updates, in the reference's order (``cn_model.py:444-460``)."""
         if not self.check_elbo and hasattr(self.model, 'variational_update'):
-            self.model.variational_update(1)     # same five updates, one device synchronisation
+            self.model.variational_update(n_iter)     # same updates, one device synchronisation
             return
+        for _ in range(n_iter):
+            self._variational_update_stepwise()
+
+    def _variational_update_stepwise(self):
         for name, step in (('update_p_allele_swap', 'update_p_allele_swap'), ('p_cn', 'update_p_cn'),
                            ('p_breakpoint', 'update_p_breakpoint'), ('p_outlier_total', 'update_p_outlier_total'),
                            ('p_outlier_allele', 'update_p_outlier_allele')):
@@ -442,12 +455,9 @@ class BreakpointModel(object):
         else:
             setattr(model, name, result_value)
 
-    def optimal_cn(self):
-        """MAP clone copy number per original segment and per breakpoint (``cn_model.py:571-598``)."""
+    def decode_breakpoints(self, cn):
+        """Breakpoint copy number given the MAP segment copy number of the model segments (``cn_model.py:578-596``)."""
         model = self.model
-        cn = np.zeros((model.num_segments, model.num_clones, model.num_alleles), dtype=int)
-        model.infer_cn(cn)
-
         brk_states = np.asarray(model.brk_states)
         bidx = np.asarray(model.breakpoint_idx)
         borient = np.asarray(model.breakpoint_orient)
@@ -462,8 +472,14 @@ class BreakpointModel(object):
         brk_cn = dict()
         for k in range(model.num_breakpoints):
             brk_cn[self.breakpoint_ids[k]] = brk_states[log_p[k, :].argmax()]
+        return brk_cn
 
-        return cn[self.seg_fwd_remap], brk_cn
+    def optimal_cn(self):
+        """MAP clone copy number per original segment and per breakpoint (``cn_model.py:571-598``)."""
+        model = self.model
+        cn = np.zeros((model.num_segments, model.num_clones, model.num_alleles), dtype=int)
+        model.infer_cn(cn)
+        return cn[self.seg_fwd_remap], self.decode_breakpoints(cn)
 
     def breakpoint_prob(self):
         return dict(zip(self.breakpoints, np.asarray(self.model.p_breakpoint)))

@@ -1,16 +1,25 @@
-// C-ABI of libremixt_b200 (see include/remixt_b200.h): the model handle, its device buffers,
+// C-ABI of libremixt_b200 (see include/remixt_b200.h): batches of fits, their device buffers,
 // generation tracking of cached quantities, and the host-side sequencing of kernel launches.
+//
+// A BATCH is G fits that share the data (x, l, y), the state tables and the breakpoint structure and
+// differ in h, the dispersion parameters, divergence_weight, the likelihood masks and the variational
+// state -- exactly the fits of the reference's initialisation grid (analysis/pipeline.py:42-103).
+// Every per-fit array has the fit as its leading dimension and every kernel launch covers a range of
+// fits.  A HANDLE addresses a contiguous range [g0, g0+gn) of a batch; rmx_create makes a batch of one.
 //
 // State semantics kept from the reference (remixt/bpmodel.pyx):
 //   framelogprob / log_transmat / joint_posterior_marginals are "as of the last update_p_cn" (:921-962);
 //   cached_log_transmat is "as of the constructor or the last update_p_breakpoint" (:604, :985);
 //   the likelihood terms always use the CURRENT h / dispersion parameters (:751-853).
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -20,82 +29,79 @@
 static thread_local std::string g_create_error;
 static std::atomic<int64_t> g_launches{0};
 
-#define CK(call)                                                                                     \
-    do {                                                                                             \
-        cudaError_t e__ = (call);                                                                    \
-        if (e__ != cudaSuccess) {                                                                    \
-            char buf__[512];                                                                         \
-            snprintf(buf__, sizeof buf__, "CUDA error %s at %s:%d: %s", cudaGetErrorName(e__),       \
-                     __FILE__, __LINE__, cudaGetErrorString(e__));                                   \
-            return m->fail(RMX_ERR_CUDA, buf__);                                                        \
-        }                                                                                            \
-    } while (0)
-
 struct ClassMats {
     double *Tmat = nullptr, *Emat = nullptr, *flipc = nullptr, *flipE = nullptr;
-    double pen = NAN;
     bool built = false;
 };
 
-struct rmx_model_s {
+struct Batch {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    std::recursive_mutex mu;
     RmxDims d{};
-    RmxParams P{};
+    int G = 1;
     double pen = 0., prior_ot = 0.01, prior_oa = 0.01;
-    int tm = 0;
-    double logZ = 0.;
-    std::string err;
-    int64_t launches = 0;
     std::vector<void*> allocs;
+
+    // per-fit host state
+    std::vector<RmxParams> P;
+    std::vector<int> tm, tm_used, tm_cached;
+    std::vector<double> logZ;
+    std::vector<char> ll_dirty, cn_updated, hist_valid, asum_valid, path_valid;
+    bool params_dirty = true;
 
     // host copies of the small integer tables
     std::vector<int8_t> h_tab, h_nrm, h_nsub, h_brk;
-    std::vector<int64_t> h_tmask, h_amask;
-    std::vector<int> h_path;
+    std::vector<int64_t> h_tmask, h_amask;   // (G,N)
+    std::vector<int> h_path;                 // (G,N)
 
-    // device: static tables
+    // device: shared tables
     int8_t *tab = nullptr, *nrm = nullptr, *nsub = nullptr, *brk = nullptr, *d0 = nullptr, *class_nrm = nullptr;
     double *l = nullptr, *x = nullptr, *y0 = nullptr, *y1 = nullptr;
-    uint8_t *tmask = nullptr, *amask = nullptr;
     int *bidx = nullptr, *borient = nullptr, *tclass = nullptr, *brow = nullptr, *brk_rows = nullptr;
-    int *krow_ptr = nullptr, *krow_idx = nullptr, *ch_start = nullptr, *ch_end = nullptr;
+    int *krow_ptr = nullptr, *krow_idx = nullptr, *ch_start = nullptr, *ch_end = nullptr, *ch_order = nullptr;
     int NC = 0, C = 0, R = 0;
+    int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
+    ClassMats mats[2];
 
-    // device: variational state and scratch
+    // device: per-fit (leading dimension G)
+    RmxParams* dP = nullptr;
+    uint8_t *tmask = nullptr, *amask = nullptr;
     double *LL = nullptr, *segc = nullptr, *F = nullptr, *fexp = nullptr, *mF = nullptr;
-    double *ahat = nullptr, *bhat = nullptr, *cnorm = nullptr, *zp = nullptr, *post = nullptr;
+    double *ahat = nullptr, *bhat = nullptr, *post = nullptr, *Asum = nullptr;
     double *q_sw = nullptr, *q_ot = nullptr, *q_oa = nullptr, *p_brk = nullptr;
     double *pd_used = nullptr, *wexp_used = nullptr, *pd_cached = nullptr, *wexp_cached = nullptr;
-    double *hist = nullptr, *logq = nullptr, *chain_logz = nullptr, *rowv = nullptr, *rowsum = nullptr;
+    double *hist = nullptr, *chain_logz = nullptr, *rowv = nullptr, *rowsum = nullptr;
     double *red_out = nullptr, *part = nullptr, *lattice = nullptr, *segc_s = nullptr, *evalbuf = nullptr;
-    int *path = nullptr, *d_rows = nullptr, *dflags = nullptr;
-    int64_t part_cap = 0;
-    ClassMats mats[2];
-    int tm_used = 0, tm_cached = 0;
-    double pen_used = 0., pen_cached = 0.;
+    int *path = nullptr, *d_rows = nullptr, *d_Rn = nullptr, *dflags = nullptr;
+    int64_t part_stride = 0;
+    int lattice_fits = 0;
+    static const int RED = 64;   // doubles of reduction output per fit
 
     // pinned host staging
-    double* hp = nullptr;   // 64 doubles
-    int* hflags = nullptr;  // 1 int
-    int* hrows = nullptr;   // N ints
+    double* hp = nullptr;       // G*RED doubles
+    int* hflags = nullptr;      // 1 int
+    int* hrows = nullptr;       // G*N ints
+    int* hRn = nullptr;         // G ints
 
-    bool ll_dirty = true;
-    bool cn_updated = false;   // false: constructor state (uniform posteriors, F == 1, log_transmat == 0)
-    bool hist_valid = false;
-    bool path_valid = false;
-
-    cudaEvent_t ev[16] = {};
-    // chain timing
+    // chain timing (CUDA events around the chain kernel)
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> tev;
     double chain_ms = 0.;
     int64_t chain_launches = 0;
+    int64_t launches = 0;
 
-    int fail(int code, const std::string& m) {
-        err = m;
-        return code;
+    ~Batch() {
+        cudaSetDevice(device);
+        if (stream) cudaStreamSynchronize(stream);
+        for (auto& pr : tev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        for (void* p : allocs) cudaFree(p);
+        if (hp) cudaFreeHost(hp);
+        if (hflags) cudaFreeHost(hflags);
+        if (hrows) cudaFreeHost(hrows);
+        if (hRn) cudaFreeHost(hRn);
+        if (stream) cudaStreamDestroy(stream);
     }
     void count(int k = 1) {
         launches += k;
@@ -103,91 +109,166 @@ struct rmx_model_s {
     }
 };
 
+struct rmx_model_s {
+    std::shared_ptr<Batch> b;
+    int g0 = 0, gn = 1;
+    std::string err;
+    cudaEvent_t ev[16] = {};
+    int fail(int code, const std::string& m) {
+        err = m;
+        return code;
+    }
+};
 typedef rmx_model_s Model;
+typedef std::lock_guard<std::recursive_mutex> Lock;
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess) {                                                                    \
+            char buf__[512];                                                                         \
+            snprintf(buf__, sizeof buf__, "CUDA error %s at %s:%d: %s", cudaGetErrorName(e__),       \
+                     __FILE__, __LINE__, cudaGetErrorString(e__));                                   \
+            return m->fail(RMX_ERR_CUDA, buf__);                                                     \
+        }                                                                                            \
+    } while (0)
 
 template <typename T>
-static cudaError_t dalloc(Model* m, T** p, size_t n) {
+static cudaError_t dalloc(Batch* b, T** p, size_t n) {
     if (n == 0) n = 1;
     cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
-    if (e == cudaSuccess) m->allocs.push_back((void*)*p);
+    if (e == cudaSuccess) b->allocs.push_back((void*)*p);
     return e;
 }
-
 template <typename T>
-static cudaError_t upload(Model* m, T** dptr, const std::vector<T>& v) {
-    cudaError_t e = dalloc(m, dptr, v.size());
+static cudaError_t upload(Batch* b, T** dptr, const std::vector<T>& v) {
+    cudaError_t e = dalloc(b, dptr, v.size());
     if (e != cudaSuccess) return e;
     if (!v.empty()) e = cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
     return e;
 }
 
-static RmxTables tables(const Model* m) {
+static RmxTables tables(const Batch* b) {
     RmxTables T;
-    T.tab = m->tab; T.nrm = m->nrm; T.nsub = m->nsub; T.l = m->l; T.x = m->x; T.y0 = m->y0; T.y1 = m->y1;
-    T.tmask = m->tmask; T.amask = m->amask;
+    T.tab = b->tab; T.nrm = b->nrm; T.nsub = b->nsub; T.l = b->l; T.x = b->x; T.y0 = b->y0; T.y1 = b->y1;
+    T.tmask = b->tmask; T.amask = b->amask;
     return T;
 }
-static RmxRows rowsof(const Model* m) {
+static RmxRows rowsof(const Batch* b) {
     RmxRows r;
-    r.tclass = m->tclass; r.brow = m->brow; r.d0 = m->d0; r.brk_rows = m->brk_rows;
+    r.tclass = b->tclass; r.brow = b->brow; r.d0 = b->d0; r.brk_rows = b->brk_rows;
     return r;
 }
-static RmxChains chainsof(const Model* m) {
+static RmxChains chainsof(const Batch* b) {
     RmxChains c;
-    c.start = m->ch_start; c.end = m->ch_end; c.NC = m->NC;
+    c.start = b->ch_start; c.end = b->ch_end; c.order = b->ch_order; c.NC = b->NC;
     return c;
 }
 
-// class matrices for (tm, pen), built on demand
-static int ensure_mats(Model* m, int tm, double pen) {
-    ClassMats& cm = m->mats[tm];
-    size_t n = (size_t)m->C * m->d.S * m->d.S;
+// [g0, g0+gn) split into maximal runs over which key[] is constant and flag[] (if given) is nonzero
+template <typename K, typename F>
+static void for_runs(int g0, int gn, const std::vector<K>& key, const std::vector<char>* flag, F fn) {
+    int g = g0;
+    const int ge = g0 + gn;
+    while (g < ge) {
+        if (flag && !(*flag)[g]) { ++g; continue; }
+        int e = g + 1;
+        while (e < ge && key[e] == key[g] && (!flag || (*flag)[e])) ++e;
+        fn(g, e - g);
+        g = e;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cached-quantity maintenance (all launch-only; callers synchronise)
+// ---------------------------------------------------------------------------------------------
+static int push_params(Model* m) {
+    Batch* b = m->b.get();
+    if (!b->params_dirty) return RMX_OK;
+    // pageable source: the runtime stages small copies before returning, so P may be modified right after
+    CK(cudaMemcpyAsync(b->dP, b->P.data(), sizeof(RmxParams) * b->G, cudaMemcpyHostToDevice, b->stream));
+    b->params_dirty = false;
+    return RMX_OK;
+}
+
+// class matrices for transition model tm (penalty is fixed per batch), built on demand
+static int ensure_mats(Model* m, int tm) {
+    Batch* b = m->b.get();
+    ClassMats& cm = b->mats[tm];
+    size_t n = (size_t)b->C * b->d.S * b->d.S;
     if (!cm.Tmat) {
-        if (dalloc(m, &cm.Tmat, n) != cudaSuccess || dalloc(m, &cm.Emat, n) != cudaSuccess ||
-            dalloc(m, &cm.flipc, n) != cudaSuccess || dalloc(m, &cm.flipE, n) != cudaSuccess)
+        if (dalloc(b, &cm.Tmat, n) != cudaSuccess || dalloc(b, &cm.Emat, n) != cudaSuccess ||
+            dalloc(b, &cm.flipc, n) != cudaSuccess || dalloc(b, &cm.flipE, n) != cudaSuccess)
             return m->fail(RMX_ERR_CUDA, "out of device memory for transition class matrices");
     }
-    if (!cm.built || cm.pen != pen) {
-        rmx_launch_build_class(m->stream, tables(m), m->d, m->C, m->class_nrm, pen, tm, cm.Tmat, cm.Emat, cm.flipc,
+    if (!cm.built) {
+        rmx_launch_build_class(b->stream, tables(b), b->d, b->C, b->class_nrm, b->pen, tm, cm.Tmat, cm.Emat, cm.flipc,
                                cm.flipE);
-        m->count();
+        b->count();
         cm.built = true;
-        cm.pen = pen;
     }
     return RMX_OK;
 }
 
-static RmxTransSpec spec_of(Model* m, bool cached) {
+static RmxTransSpec spec_of(Batch* b, bool cached, int tm) {
     RmxTransSpec s;
-    int tm = cached ? m->tm_cached : m->tm_used;
-    ClassMats& cm = m->mats[tm];
-    s.pd = cached ? m->pd_cached : m->pd_used;
-    s.wexp = cached ? m->wexp_cached : m->wexp_used;
+    ClassMats& cm = b->mats[tm];
+    s.pd = cached ? b->pd_cached : b->pd_used;
+    s.wexp = cached ? b->wexp_cached : b->wexp_used;
     s.Tmat = cm.Tmat; s.Emat = cm.Emat; s.flipc = cm.flipc; s.flipE = cm.flipE;
-    s.pen = cached ? m->pen_cached : m->pen_used;
+    s.pen = b->pen;
     s.tm = tm;
     return s;
 }
 
-// snapshot the current (p_breakpoint, transition_model, penalty) as the `used` or `cached` spec
-static int snapshot_spec(Model* m, bool cached) {
-    int rc = ensure_mats(m, m->tm, m->pen);
+// snapshot the current (p_breakpoint, transition_model) of the fits as their `used` or `cached` spec
+static int snapshot_spec(Model* m, int g0, int gn, bool cached) {
+    Batch* b = m->b.get();
+    int rc = RMX_OK;
+    for_runs(g0, gn, b->tm, nullptr, [&](int g, int n) {
+        if (rc) return;
+        rc = ensure_mats(m, b->tm[g]);
+        if (rc) return;
+        rmx_launch_prep_brk(b->stream, b->d, g, n, b->R, b->brk_rows, b->bidx, b->borient, b->brk, b->p_brk, b->pen,
+                            b->tm[g], b->rmd, cached ? b->pd_cached : b->pd_used, cached ? b->wexp_cached : b->wexp_used);
+        if (b->R > 0) b->count();
+        for (int k = g; k < g + n; ++k) (cached ? b->tm_cached : b->tm_used)[k] = b->tm[g];
+    });
+    return rc;
+}
+
+// likelihood table of the fits whose h / dispersions / masks changed since it was last built
+static int ensure_ll(Model* m, int g0, int gn) {
+    Batch* b = m->b.get();
+    bool any = false;
+    for (int g = g0; g < g0 + gn; ++g) any |= b->ll_dirty[g] != 0;
+    if (!any) return RMX_OK;
+    int rc = push_params(m);
     if (rc) return rc;
-    rmx_launch_prep_brk(m->stream, m->d, m->R, m->brk_rows, m->bidx, m->borient, m->brk, m->p_brk, m->pen, m->tm,
-                        cached ? m->pd_cached : m->pd_used, cached ? m->wexp_cached : m->wexp_used);
-    if (m->R > 0) m->count();
-    if (cached) { m->tm_cached = m->tm; m->pen_cached = m->pen; }
-    else { m->tm_used = m->tm; m->pen_used = m->pen; }
+    RmxTables T = tables(b);
+    std::vector<int> key(b->G, 0);
+    for_runs(g0, gn, key, &b->ll_dirty, [&](int g, int n) {
+        rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc);
+        rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags);
+        b->count(2);
+        for (int k = g; k < g + n; ++k) { b->ll_dirty[k] = 0; b->asum_valid[k] = 0; }
+    });
     return RMX_OK;
 }
 
-static int ensure_ll(Model* m) {
-    if (!m->ll_dirty) return RMX_OK;
-    RmxTables T = tables(m);
-    rmx_launch_segconst(m->stream, T, m->P, nullptr, m->d.N, m->segc);
-    rmx_launch_lltable(m->stream, m->sm_count, T, m->d, m->P, m->segc, m->LL, m->dflags);
-    m->count(2);
-    m->ll_dirty = false;
+// posterior-weighted likelihood sums of the fits whose posterior or likelihood table changed
+static int ensure_asum(Model* m, int g0, int gn) {
+    Batch* b = m->b.get();
+    int rc = ensure_ll(m, g0, gn);
+    if (rc) return rc;
+    std::vector<int> key(b->G, 0);
+    std::vector<char> need(b->G, 0);
+    for (int g = g0; g < g0 + gn; ++g) need[g] = !b->asum_valid[g];
+    for_runs(g0, gn, key, &need, [&](int g, int n) {
+        rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum);
+        b->count();
+        for (int k = g; k < g + n; ++k) b->asum_valid[k] = 1;
+    });
     return RMX_OK;
 }
 
@@ -211,26 +292,27 @@ static const char* flag_message(int f, int* code) {
 
 // synchronise the stream, collect timing events and device error flags
 static int sync_check(Model* m) {
-    cudaError_t e = cudaMemcpyAsync(m->hflags, m->dflags, sizeof(int), cudaMemcpyDeviceToHost, m->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+    Batch* b = m->b.get();
+    cudaError_t e = cudaMemcpyAsync(b->hflags, b->dflags, sizeof(int), cudaMemcpyDeviceToHost, b->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
     if (e != cudaSuccess) {
         char buf[512];
         snprintf(buf, sizeof buf, "CUDA error %s: %s", cudaGetErrorName(e), cudaGetErrorString(e));
         return m->fail(RMX_ERR_CUDA, buf);
     }
-    for (auto& pr : m->tev) {
+    for (auto& pr : b->tev) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
-            m->chain_ms += ms;
-            m->chain_launches += 1;
+            b->chain_ms += ms;
+            b->chain_launches += 1;
         }
         cudaEventDestroy(pr.first);
         cudaEventDestroy(pr.second);
     }
-    m->tev.clear();
-    int f = *m->hflags;
+    b->tev.clear();
+    int f = *b->hflags;
     if (f) {
-        cudaMemsetAsync(m->dflags, 0, sizeof(int), m->stream);
+        cudaMemsetAsync(b->dflags, 0, sizeof(int), b->stream);
         int code;
         const char* msg = flag_message(f, &code);
         return m->fail(code, msg);
@@ -239,75 +321,98 @@ static int sync_check(Model* m) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// coordinate updates (launch only; callers synchronise)
+// coordinate updates over the handle's fits (launch only; callers synchronise)
 // ---------------------------------------------------------------------------------------------
 static int do_update_framelogprob(Model* m) {
-    int rc = ensure_ll(m);
+    Batch* b = m->b.get();
+    int rc = ensure_ll(m, m->g0, m->gn);
     if (rc) return rc;
-    rmx_launch_frame(m->stream, tables(m), m->d, m->P, m->LL, m->q_ot, m->q_oa, m->q_sw, m->F, m->fexp, m->mF,
-                     m->dflags);
-    m->count();
+    rmx_launch_frame(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->q_ot, b->q_oa, b->q_sw, b->F, b->fexp,
+                     b->mF, b->dflags);
+    b->count();
     return RMX_OK;
 }
 
 static int do_update_p_cn(Model* m) {
+    Batch* b = m->b.get();
+    const int g0 = m->g0, gn = m->gn;
     int rc = do_update_framelogprob(m);
     if (rc) return rc;
-    rc = snapshot_spec(m, false);
+    rc = snapshot_spec(m, g0, gn, false);
     if (rc) return rc;
-    RmxTransSpec sp = spec_of(m, false);
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (m->timing) {
-        cudaEventCreate(&e0);
-        cudaEventCreate(&e1);
-        cudaEventRecord(e0, m->stream);
-    }
-    int lc = rmx_launch_chain(m->stream, tables(m), m->d, chainsof(m), rowsof(m), sp, m->fexp, m->mF, m->ahat, m->bhat,
-                              m->cnorm, m->chain_logz, m->dflags);
-    if (m->timing) {
-        cudaEventRecord(e1, m->stream);
-        m->tev.push_back({e0, e1});
-    }
-    if (lc == 2) return m->fail(RMX_ERR_UNSUPPORTED, "num_cn_states > 1024 is not supported by the chain kernel");
+    int lc = 0;
+    for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
+        if (lc) return;
+        RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (b->timing) {
+            cudaEventCreate(&e0);
+            cudaEventCreate(&e1);
+            cudaEventRecord(e0, b->stream);
+        }
+        lc = rmx_launch_chain(b->stream, tables(b), b->d, chainsof(b), rowsof(b), sp, b->rmd, g, n, b->fexp, b->mF,
+                              b->ahat, b->bhat, b->chain_logz, b->dflags);
+        if (b->timing) {
+            cudaEventRecord(e1, b->stream);
+            b->tev.push_back({e0, e1});
+        }
+        b->count();
+    });
+    if (lc == 2) return m->fail(RMX_ERR_UNSUPPORTED, "this number of copy number states is not supported by the chain kernel");
     if (lc) return m->fail(RMX_ERR_CUDA, "could not configure shared memory for the chain kernel");
-    m->count();
-    rmx_launch_reduce_cols(m->stream, m->chain_logz, m->NC, 1, m->red_out + 15);
-    rmx_launch_post(m->stream, m->d, m->ahat, m->bhat, m->post, m->zp, m->dflags);
-    m->count(2);
-    m->cn_updated = true;
-    rmx_launch_hist(m->stream, tables(m), m->d, m->R, rowsof(m), sp, 0, m->ahat, m->bhat, m->fexp, m->hist, m->dflags);
-    if (m->R > 0) m->count();
-    m->hist_valid = true;
-    m->path_valid = false;
-    CK(cudaMemcpyAsync(m->hp + 15, m->red_out + 15, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    rmx_launch_reduce_cols(b->stream, b->chain_logz, b->NC, 1, g0, gn, b->NC, b->red_out + 15, Batch::RED);
+    rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags);
+    b->count(2);
+    for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
+        RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
+        rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
+                        b->dflags);
+        if (b->R > 0) b->count();
+    });
+    for (int g = g0; g < g0 + gn; ++g) {
+        b->cn_updated[g] = 1;
+        b->hist_valid[g] = 1;
+        b->path_valid[g] = 0;
+        b->asum_valid[g] = 0;
+    }
+    CK(cudaMemcpyAsync(b->hp + (size_t)g0 * Batch::RED, b->red_out + (size_t)g0 * Batch::RED,
+                       sizeof(double) * Batch::RED * gn, cudaMemcpyDeviceToHost, b->stream));
     return RMX_OK;
 }
 
 static int do_update_p_breakpoint(Model* m) {
-    if (m->d.K > 0 && m->R > 0) {
-        if (!m->hist_valid) {
-            RmxTransSpec sp = spec_of(m, true);
-            rmx_launch_hist(m->stream, tables(m), m->d, m->R, rowsof(m), sp, 1, m->ahat, m->bhat, m->fexp, m->hist,
-                            m->dflags);
-            m->count();
-            m->hist_valid = true;
-        }
+    Batch* b = m->b.get();
+    const int g0 = m->g0, gn = m->gn;
+    if (b->d.K > 0 && b->R > 0) {
+        // fits still in the constructor state take the histogram of the uniform joint (bpmodel.pyx:566-567)
+        std::vector<char> need(b->G, 0);
+        for (int g = g0; g < g0 + gn; ++g) need[g] = !b->hist_valid[g];
+        for_runs(g0, gn, b->tm_cached, &need, [&](int g, int n) {
+            RmxTransSpec sp = spec_of(b, true, b->tm_cached[g]);
+            rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 1, b->ahat, b->bhat, b->fexp,
+                            b->hist, b->dflags);
+            b->count();
+            for (int k = g; k < g + n; ++k) b->hist_valid[k] = 1;
+        });
     }
-    if (m->d.K > 0) {
-        rmx_launch_brk_update(m->stream, m->d, m->krow_ptr, m->krow_idx, m->brk_rows, m->borient, m->brk, m->hist,
-                              m->pen, m->tm, m->p_brk, m->logq);
-        m->count();
+    if (b->d.K > 0) {
+        for_runs(g0, gn, b->tm, nullptr, [&](int g, int n) {
+            rmx_launch_brk_update(b->stream, b->d, g, n, b->krow_ptr, b->krow_idx, b->brk_rows, b->borient, b->brk, b->hist,
+                                  b->rmd, b->pen, b->tm[g], b->p_brk);
+            b->count();
+        });
     }
-    return snapshot_spec(m, true);
+    return snapshot_spec(m, g0, gn, true);
 }
 
 static int do_update_q(Model* m, int which) {
-    int rc = ensure_ll(m);
+    Batch* b = m->b.get();
+    int rc = ensure_asum(m, m->g0, m->gn);
     if (rc) return rc;
-    double* out = which == 0 ? m->q_sw : (which == 1 ? m->q_ot : m->q_oa);
-    double prior = which == 1 ? m->prior_ot : m->prior_oa;
-    rmx_launch_qfactor(m->stream, m->d, which, m->LL, m->post, m->q_oa, m->q_sw, prior, out);
-    m->count();
+    double* out = which == 0 ? b->q_sw : (which == 1 ? b->q_ot : b->q_oa);
+    double prior = which == 1 ? b->prior_ot : b->prior_oa;
+    rmx_launch_qupdate(b->stream, b->d, m->g0, m->gn, which, b->Asum, b->q_oa, b->q_sw, prior, out);
+    b->count();
     return RMX_OK;
 }
 
@@ -341,23 +446,17 @@ int rmx_device_count(int* count) {
 
 int rmx_destroy(rmx_handle m) {
     if (!m) return RMX_OK;
-    cudaSetDevice(m->device);
-    if (m->stream) cudaStreamSynchronize(m->stream);
-    for (auto& pr : m->tev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
-    for (int i = 0; i < 16; ++i) if (m->ev[i]) cudaEventDestroy(m->ev[i]);
-    for (void* p : m->allocs) cudaFree(p);
-    if (m->hp) cudaFreeHost(m->hp);
-    if (m->hflags) cudaFreeHost(m->hflags);
-    if (m->hrows) cudaFreeHost(m->hrows);
-    if (m->stream) cudaStreamDestroy(m->stream);
-    delete m;
+    if (m->b) cudaSetDevice(m->b->device);
+    for (int i = 0; i < 16; ++i)
+        if (m->ev[i]) cudaEventDestroy(m->ev[i]);
+    delete m;    // the batch goes with its last handle
     return RMX_OK;
 }
 
 #define CREATE_FAIL(code, msg)          \
     do {                                \
         g_create_error = (msg);         \
-        rmx_destroy(m);                 \
+        delete m;                       \
         return (code);                  \
     } while (0)
 #define CCK(call)                                                                               \
@@ -371,26 +470,35 @@ int rmx_destroy(rmx_handle m) {
         }                                                                                       \
     } while (0)
 
-int rmx_create(const rmx_desc* desc, rmx_handle* out) {
+int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, const double* divergence_weight,
+                     rmx_handle* out) {
     *out = nullptr;
     Model* m = new Model();
+    m->b = std::make_shared<Batch>();
+    Batch* b = m->b.get();
+    const int G = num_fits;
     const int N = desc->num_segments, S = desc->num_cn_states, M = desc->num_clones, B = desc->num_brk_states,
               K = desc->num_breakpoints;
+    if (G < 1) CREATE_FAIL(RMX_ERR_VALUE, "num_fits must be positive");
     if (N < 1 || S < 1 || B < 1) CREATE_FAIL(RMX_ERR_VALUE, "num_segments, num_cn_states and num_brk_states must be positive");
     if (M < 2 || M > RMX_MAXM) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_clones must be between 2 and 8");
     if (S > 1024) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_cn_states > 1024 is not supported");
+    if (B > 64) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_brk_states > 64 is not supported");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
         CREATE_FAIL(RMX_ERR_CUDA, "no CUDA device available: remixt_b200 has no CPU fallback");
     if (desc->device < 0 || desc->device >= ndev) CREATE_FAIL(RMX_ERR_ARG, "device ordinal out of range");
-    m->device = desc->device;
-    CCK(cudaSetDevice(m->device));
-    cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, m->device);
-    CCK(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+    b->device = desc->device;
+    b->G = G;
+    m->g0 = 0;
+    m->gn = G;
+    CCK(cudaSetDevice(b->device));
+    cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, b->device);
+    CCK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
 
     // ---- state table + per-segment normal copies (cn_model.py:359-364 builds cn_states this way)
-    m->h_tab.assign((size_t)S * M * 2, 0);
-    m->h_nrm.assign((size_t)N * 2, 0);
+    b->h_tab.assign((size_t)S * M * 2, 0);
+    b->h_nrm.assign((size_t)N * 2, 0);
     int64_t vmax = 0;
     auto fits = [](int64_t v) { return v >= 0 && v <= 100; };
     if (desc->cn_states) {
@@ -401,15 +509,15 @@ int rmx_create(const rmx_desc* desc, rmx_handle* out) {
                 for (int a = 0; a < 2; ++a) {
                     int64_t v = cs[((size_t)s * M + mm) * 2 + a];
                     if (!fits(v)) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "cn_states entries must be in [0, 100]");
-                    m->h_tab[((size_t)s * M + mm) * 2 + a] = (int8_t)v;
+                    b->h_tab[((size_t)s * M + mm) * 2 + a] = (int8_t)v;
                     if (v > vmax) vmax = v;
                 }
         for (int n = 0; n < N; ++n) {
             const int64_t* r = cs + (size_t)n * row;
             int64_t n0 = r[0], n1 = r[1];
             if (!fits(n0) || !fits(n1)) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "cn_states entries must be in [0, 100]");
-            m->h_nrm[2 * n] = (int8_t)n0;
-            m->h_nrm[2 * n + 1] = (int8_t)n1;
+            b->h_nrm[2 * n] = (int8_t)n0;
+            b->h_nrm[2 * n + 1] = (int8_t)n1;
             if (n0 > vmax) vmax = n0;
             if (n1 > vmax) vmax = n1;
             for (int s = 0; s < S; ++s) {
@@ -418,7 +526,7 @@ int rmx_create(const rmx_desc* desc, rmx_handle* out) {
                     CREATE_FAIL(RMX_ERR_UNSUPPORTED,
                                 "cn_states[n,s,0,:] (normal copies) must not depend on the state s");
                 for (int e = 2; e < M * 2; ++e)
-                    if (rs[e] != (int64_t)m->h_tab[(size_t)s * M * 2 + e])
+                    if (rs[e] != (int64_t)b->h_tab[(size_t)s * M * 2 + e])
                         CREATE_FAIL(RMX_ERR_UNSUPPORTED,
                                     "cn_states[n,s,1:,:] (tumour clone copies) must be the same state table for every segment");
             }
@@ -429,50 +537,50 @@ int rmx_create(const rmx_desc* desc, rmx_handle* out) {
                 for (int a = 0; a < 2; ++a) {
                     int64_t v = desc->cn_table[((size_t)s * M + mm) * 2 + a];
                     if (!fits(v)) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "cn_states entries must be in [0, 100]");
-                    m->h_tab[((size_t)s * M + mm) * 2 + a] = (int8_t)v;
+                    b->h_tab[((size_t)s * M + mm) * 2 + a] = (int8_t)v;
                     if (v > vmax) vmax = v;
                 }
         for (int n = 0; n < 2 * N; ++n) {
             int64_t v = desc->normal_copies[n];
             if (!fits(v)) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "cn_states entries must be in [0, 100]");
-            m->h_nrm[n] = (int8_t)v;
+            b->h_nrm[n] = (int8_t)v;
             if (v > vmax) vmax = v;
         }
     } else {
         CREATE_FAIL(RMX_ERR_ARG, "either cn_states or (cn_table, normal_copies) must be given");
     }
-    m->h_brk.assign((size_t)B * M, 0);
+    b->h_brk.assign((size_t)B * M, 0);
     for (int e = 0; e < B * M; ++e) {
         int64_t v = desc->brk_states[e];
         if (!fits(v)) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "brk_states entries must be in [0, 100]");
-        m->h_brk[e] = (int8_t)v;
+        b->h_brk[e] = (int8_t)v;
         if (v > vmax) vmax = v;
     }
     // num_alleles_subclonal (bpmodel.pyx:505): alleles whose copy number differs between tumour clones
-    m->h_nsub.assign(S, 0);
+    b->h_nsub.assign(S, 0);
     int maxtot = 0;
     for (int s = 0; s < S; ++s) {
         int cnt = 0;
         for (int a = 0; a < 2; ++a) {
             int lo = 127, hi = -1;
             for (int mm = 1; mm < M; ++mm) {
-                int v = m->h_tab[((size_t)s * M + mm) * 2 + a];
+                int v = b->h_tab[((size_t)s * M + mm) * 2 + a];
                 lo = v < lo ? v : lo;
                 hi = v > hi ? v : hi;
             }
             cnt += (hi != lo);
         }
-        m->h_nsub[s] = (int8_t)cnt;
+        b->h_nsub[s] = (int8_t)cnt;
         for (int mm = 1; mm < M; ++mm) {
-            int t = m->h_tab[((size_t)s * M + mm) * 2] + m->h_tab[((size_t)s * M + mm) * 2 + 1];
+            int t = b->h_tab[((size_t)s * M + mm) * 2] + b->h_tab[((size_t)s * M + mm) * 2 + 1];
             if (t > maxtot) maxtot = t;
         }
     }
     for (int n = 0; n < N; ++n) {
-        int t = m->h_nrm[2 * n] + m->h_nrm[2 * n + 1];
+        int t = b->h_nrm[2 * n] + b->h_nrm[2 * n + 1];
         if (t > maxtot) maxtot = t;
     }
-    RmxDims& d = m->d;
+    RmxDims& d = b->d;
     d.N = N; d.S = S; d.M = M; d.B = B; d.K = K;
     d.cn_max = (int)vmax;                      // bpmodel.pyx:489
     if (maxtot > d.cn_max + 1)
@@ -503,158 +611,202 @@ int rmx_create(const rmx_desc* desc, rmx_handle* out) {
             brow[n] = (int)brk_rows.size();
             brk_rows.push_back(n);
         }
-        d0[n] = (int8_t)((m->h_nrm[2 * n] + m->h_nrm[2 * n + 1]) - (m->h_nrm[2 * n + 2] + m->h_nrm[2 * n + 3]));
+        d0[n] = (int8_t)((b->h_nrm[2 * n] + b->h_nrm[2 * n + 1]) - (b->h_nrm[2 * n + 2] + b->h_nrm[2 * n + 3]));
         if (tel) {
             tclass[n] = -1;
             ch_end.push_back(n);
             ch_start.push_back(n + 1);
         } else {
-            uint32_t key = ((uint32_t)(uint8_t)m->h_nrm[2 * n] << 24) | ((uint32_t)(uint8_t)m->h_nrm[2 * n + 1] << 16) |
-                           ((uint32_t)(uint8_t)m->h_nrm[2 * n + 2] << 8) | (uint32_t)(uint8_t)m->h_nrm[2 * n + 3];
+            uint32_t key = ((uint32_t)(uint8_t)b->h_nrm[2 * n] << 24) | ((uint32_t)(uint8_t)b->h_nrm[2 * n + 1] << 16) |
+                           ((uint32_t)(uint8_t)b->h_nrm[2 * n + 2] << 8) | (uint32_t)(uint8_t)b->h_nrm[2 * n + 3];
             auto it = class_of.find(key);
             if (it == class_of.end()) {
                 it = class_of.emplace(key, (int)class_of.size()).first;
-                for (int e = 0; e < 4; ++e) class_nrm.push_back(m->h_nrm[2 * n + e]);
+                for (int e = 0; e < 4; ++e) class_nrm.push_back(b->h_nrm[2 * n + e]);
             }
             tclass[n] = it->second;
         }
     }
     ch_end.push_back(N - 1);
-    m->NC = (int)ch_start.size();
-    m->C = (int)class_of.size();
-    if (m->C == 0) { m->C = 1; class_nrm.assign(4, 1); }
-    m->R = (int)brk_rows.size();
+    b->NC = (int)ch_start.size();
+    b->C = (int)class_of.size();
+    if (b->C == 0) { b->C = 1; class_nrm.assign(4, 1); }
+    b->R = (int)brk_rows.size();
+    b->rmd = (int64_t)b->R * M * d.D;
+    if (b->rmd < 1) b->rmd = 1;
+    // chains longest first: the launch order of the chain kernel (longest sequential jobs start first)
+    std::vector<int> ch_order(b->NC);
+    for (int c = 0; c < b->NC; ++c) ch_order[c] = c;
+    std::stable_sort(ch_order.begin(), ch_order.end(), [&](int a2, int b2) {
+        return (ch_end[a2] - ch_start[a2]) > (ch_end[b2] - ch_start[b2]);
+    });
     // breakpoint -> its breakend rows, ascending n (the order bpmodel.pyx:971-980 visits them)
-    std::vector<int> krow_ptr(K + 1, 0), krow_idx(m->R);
-    for (int r = 0; r < m->R; ++r) krow_ptr[bidx[brk_rows[r]] + 1]++;
+    std::vector<int> krow_ptr(K + 1, 0), krow_idx(b->R);
+    for (int r = 0; r < b->R; ++r) krow_ptr[bidx[brk_rows[r]] + 1]++;
     for (int k = 0; k < K; ++k) krow_ptr[k + 1] += krow_ptr[k];
     {
         std::vector<int> fill(krow_ptr.begin(), krow_ptr.end() - 1);
-        for (int r = 0; r < m->R; ++r) krow_idx[fill[bidx[brk_rows[r]]]++] = r;
+        for (int r = 0; r < b->R; ++r) krow_idx[fill[bidx[brk_rows[r]]]++] = r;
     }
 
-    // ---- uploads
+    // ---- uploads (shared)
     std::vector<double> y0(N), y1(N);
     for (int n = 0; n < N; ++n) { y0[n] = desc->y[2 * n]; y1[n] = desc->y[2 * n + 1]; }
-    m->h_tmask.assign(N, 1);
-    m->h_amask.assign(N, 1);
-    std::vector<uint8_t> ones(N, 1);
-    CCK(upload(m, &m->tab, m->h_tab));
-    CCK(upload(m, &m->nrm, m->h_nrm));
-    CCK(upload(m, &m->nsub, m->h_nsub));
-    CCK(upload(m, &m->brk, m->h_brk));
-    CCK(upload(m, &m->d0, d0));
-    CCK(upload(m, &m->class_nrm, class_nrm));
-    CCK(upload(m, &m->l, std::vector<double>(desc->l, desc->l + N)));
-    CCK(upload(m, &m->x, std::vector<double>(desc->x, desc->x + N)));
-    CCK(upload(m, &m->y0, y0));
-    CCK(upload(m, &m->y1, y1));
-    CCK(upload(m, &m->tmask, ones));
-    CCK(upload(m, &m->amask, ones));
-    CCK(upload(m, &m->bidx, bidx));
-    CCK(upload(m, &m->borient, borient));
-    CCK(upload(m, &m->tclass, tclass));
-    CCK(upload(m, &m->brow, brow));
-    CCK(upload(m, &m->brk_rows, brk_rows));
-    CCK(upload(m, &m->krow_ptr, krow_ptr));
-    CCK(upload(m, &m->krow_idx, krow_idx));
-    CCK(upload(m, &m->ch_start, ch_start));
-    CCK(upload(m, &m->ch_end, ch_end));
+    CCK(upload(b, &b->tab, b->h_tab));
+    CCK(upload(b, &b->nrm, b->h_nrm));
+    CCK(upload(b, &b->nsub, b->h_nsub));
+    CCK(upload(b, &b->brk, b->h_brk));
+    CCK(upload(b, &b->d0, d0));
+    CCK(upload(b, &b->class_nrm, class_nrm));
+    CCK(upload(b, &b->l, std::vector<double>(desc->l, desc->l + N)));
+    CCK(upload(b, &b->x, std::vector<double>(desc->x, desc->x + N)));
+    CCK(upload(b, &b->y0, y0));
+    CCK(upload(b, &b->y1, y1));
+    CCK(upload(b, &b->bidx, bidx));
+    CCK(upload(b, &b->borient, borient));
+    CCK(upload(b, &b->tclass, tclass));
+    CCK(upload(b, &b->brow, brow));
+    CCK(upload(b, &b->brk_rows, brk_rows));
+    CCK(upload(b, &b->krow_ptr, krow_ptr));
+    CCK(upload(b, &b->krow_idx, krow_idx));
+    CCK(upload(b, &b->ch_start, ch_start));
+    CCK(upload(b, &b->ch_end, ch_end));
+    CCK(upload(b, &b->ch_order, ch_order));
 
-    // ---- parameters (bpmodel.pyx:573-597)
-    RmxParams& P = m->P;
-    memset(&P, 0, sizeof P);
-    for (int mm = 0; mm < M; ++mm) P.h[mm] = desc->h_init[mm];
-    P.negbin_r[0] = 500.; P.negbin_r[1] = 10.;
-    P.negbin_hdel_mu = 1e-5; P.negbin_hdel_r[0] = 10.; P.negbin_hdel_r[1] = 1.;
-    P.betabin_M[0] = 500.; P.betabin_M[1] = 10.;
-    P.betabin_loh_p = 1e-3; P.betabin_loh_M[0] = 10.; P.betabin_loh_M[1] = 1.;
-    P.divergence_weight = fabs(desc->divergence_weight);
-    P.normal_contamination = desc->normal_contamination ? 1 : 0;
-    m->pen = fabs(desc->transition_penalty);
-    m->tm = 0;
+    // ---- per-fit parameters (bpmodel.pyx:573-597)
+    b->P.resize(G);
+    for (int g = 0; g < G; ++g) {
+        RmxParams& P = b->P[g];
+        memset(&P, 0, sizeof P);
+        for (int mm = 0; mm < M; ++mm) P.h[mm] = h_init[(size_t)g * M + mm];
+        P.negbin_r[0] = 500.; P.negbin_r[1] = 10.;
+        P.negbin_hdel_mu = 1e-5; P.negbin_hdel_r[0] = 10.; P.negbin_hdel_r[1] = 1.;
+        P.betabin_M[0] = 500.; P.betabin_M[1] = 10.;
+        P.betabin_loh_p = 1e-3; P.betabin_loh_M[0] = 10.; P.betabin_loh_M[1] = 1.;
+        P.divergence_weight = fabs(divergence_weight[g]);
+        P.normal_contamination = desc->normal_contamination ? 1 : 0;
+    }
+    b->pen = fabs(desc->transition_penalty);
+    b->tm.assign(G, 0);
+    b->tm_used.assign(G, 0);
+    b->tm_cached.assign(G, 0);
+    b->logZ.assign(G, 0.);
+    b->ll_dirty.assign(G, 1);
+    b->cn_updated.assign(G, 0);
+    b->hist_valid.assign(G, 0);
+    b->asum_valid.assign(G, 0);
+    b->path_valid.assign(G, 0);
+    b->h_tmask.assign((size_t)G * N, 1);
+    b->h_amask.assign((size_t)G * N, 1);
+    b->h_path.assign((size_t)G * N, 0);
 
-    // ---- variational state
-    const size_t NS = (size_t)N * S;
-    CCK(dalloc(m, &m->LL, NS * RMX_NTERM));
-    CCK(dalloc(m, &m->segc, (size_t)N * 12));
-    CCK(dalloc(m, &m->F, NS));
-    CCK(dalloc(m, &m->fexp, NS));
-    CCK(dalloc(m, &m->mF, (size_t)N));
-    CCK(dalloc(m, &m->ahat, NS));
-    CCK(dalloc(m, &m->bhat, NS));
-    CCK(dalloc(m, &m->cnorm, (size_t)N));
-    CCK(dalloc(m, &m->zp, (size_t)N));
-    CCK(dalloc(m, &m->post, NS));
-    CCK(dalloc(m, &m->q_sw, (size_t)N * 2));
-    CCK(dalloc(m, &m->q_ot, (size_t)N * 2));
-    CCK(dalloc(m, &m->q_oa, (size_t)N * 2));
-    CCK(dalloc(m, &m->p_brk, (size_t)K * B));
-    size_t rmd = (size_t)m->R * M * d.D;
-    CCK(dalloc(m, &m->pd_used, rmd));
-    CCK(dalloc(m, &m->wexp_used, rmd));
-    CCK(dalloc(m, &m->pd_cached, rmd));
-    CCK(dalloc(m, &m->wexp_cached, rmd));
-    CCK(dalloc(m, &m->hist, rmd));
-    CCK(dalloc(m, &m->logq, (size_t)K * B));
-    CCK(dalloc(m, &m->chain_logz, (size_t)m->NC));
-    CCK(dalloc(m, &m->rowv, (size_t)N * 8 + (size_t)K * B));
-    CCK(dalloc(m, &m->rowsum, (size_t)N));
-    CCK(dalloc(m, &m->red_out, 64));
-    m->part_cap = (int64_t)rmx_ell_blocks(d, N) * RMX_MAXM + 64;
-    CCK(dalloc(m, &m->part, (size_t)m->part_cap));
-    CCK(dalloc(m, &m->segc_s, (size_t)N * 12));
-    CCK(dalloc(m, &m->evalbuf, 16));
-    CCK(dalloc(m, &m->path, (size_t)N));
-    CCK(dalloc(m, &m->d_rows, (size_t)N));
-    CCK(dalloc(m, &m->dflags, 1));
-    CCK(cudaMemset(m->dflags, 0, sizeof(int)));
-    CCK(cudaMallocHost((void**)&m->hp, 64 * sizeof(double)));
-    CCK(cudaMallocHost((void**)&m->hflags, sizeof(int)));
-    CCK(cudaMallocHost((void**)&m->hrows, (size_t)N * sizeof(int)));
-    *m->hflags = 0;
+    // ---- per-fit device state
+    const size_t NS = (size_t)N * S, GNS = (size_t)G * NS, GN = (size_t)G * N;
+    CCK(dalloc(b, &b->dP, (size_t)G));
+    CCK(upload(b, &b->tmask, std::vector<uint8_t>(GN, 1)));
+    CCK(upload(b, &b->amask, std::vector<uint8_t>(GN, 1)));
+    CCK(dalloc(b, &b->LL, GNS * RMX_NTERM));
+    CCK(dalloc(b, &b->segc, GN * 12));
+    CCK(dalloc(b, &b->F, GNS));
+    CCK(dalloc(b, &b->fexp, GNS));
+    CCK(dalloc(b, &b->mF, GN));
+    CCK(dalloc(b, &b->ahat, GNS));
+    CCK(dalloc(b, &b->bhat, GNS));
+    CCK(dalloc(b, &b->post, GNS));
+    CCK(dalloc(b, &b->Asum, GN * RMX_NTERM));
+    CCK(dalloc(b, &b->q_sw, GN * 2));
+    CCK(dalloc(b, &b->q_ot, GN * 2));
+    CCK(dalloc(b, &b->q_oa, GN * 2));
+    CCK(dalloc(b, &b->p_brk, (size_t)G * K * B));
+    const size_t grmd = (size_t)G * b->rmd;
+    CCK(dalloc(b, &b->pd_used, grmd));
+    CCK(dalloc(b, &b->wexp_used, grmd));
+    CCK(dalloc(b, &b->pd_cached, grmd));
+    CCK(dalloc(b, &b->wexp_cached, grmd));
+    CCK(dalloc(b, &b->hist, grmd));
+    CCK(dalloc(b, &b->chain_logz, (size_t)G * b->NC));
+    CCK(dalloc(b, &b->rowv, GN * 8 + (size_t)G * K * B));
+    CCK(dalloc(b, &b->rowsum, GN));
+    CCK(dalloc(b, &b->red_out, (size_t)G * Batch::RED));
+    b->part_stride = (int64_t)rmx_ell_blocks(d, N) * RMX_MAXM + 64;
+    CCK(dalloc(b, &b->part, (size_t)G * b->part_stride));
+    CCK(dalloc(b, &b->segc_s, GN * 12));
+    CCK(dalloc(b, &b->evalbuf, 16));
+    CCK(dalloc(b, &b->path, GN));
+    CCK(dalloc(b, &b->d_rows, GN));
+    CCK(dalloc(b, &b->d_Rn, (size_t)G));
+    CCK(dalloc(b, &b->dflags, 1));
+    CCK(cudaMemset(b->dflags, 0, sizeof(int)));
+    CCK(cudaMallocHost((void**)&b->hp, (size_t)G * Batch::RED * sizeof(double)));
+    CCK(cudaMallocHost((void**)&b->hflags, sizeof(int)));
+    CCK(cudaMallocHost((void**)&b->hrows, GN * sizeof(int)));
+    CCK(cudaMallocHost((void**)&b->hRn, (size_t)G * sizeof(int)));
+    *b->hflags = 0;
 
-    {   // initial factors (bpmodel.pyx:546-584)
-        std::vector<double> v(NS, 1.0);
-        CCK(cudaMemcpy(m->F, v.data(), NS * sizeof(double), cudaMemcpyHostToDevice));
-        std::fill(v.begin(), v.end(), 1.0 / (double)S);
+    {   // initial factors (bpmodel.pyx:546-584), the same for every fit
+        std::vector<double> v(GNS, 1.0);
+        CCK(cudaMemcpy(b->F, v.data(), GNS * sizeof(double), cudaMemcpyHostToDevice));
         {   // posterior_marginals[:] = 1; /= sum  (bpmodel.pyx:564-565)
             double sum = 0.;
             for (int s = 0; s < S; ++s) sum += 1.0;
             std::fill(v.begin(), v.end(), 1.0 / sum);
         }
-        CCK(cudaMemcpy(m->post, v.data(), NS * sizeof(double), cudaMemcpyHostToDevice));
-        std::vector<double> q(2 * (size_t)N);
-        for (int n = 0; n < N; ++n) { q[2 * n] = 0.5; q[2 * n + 1] = 0.5; }
-        CCK(cudaMemcpy(m->q_sw, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
-        for (int n = 0; n < N; ++n) { q[2 * n] = 1. - 0.01; q[2 * n + 1] = 0.01; }
-        CCK(cudaMemcpy(m->q_ot, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
-        CCK(cudaMemcpy(m->q_oa, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CCK(cudaMemcpy(b->post, v.data(), GNS * sizeof(double), cudaMemcpyHostToDevice));
+        std::vector<double> q(2 * GN);
+        for (size_t n = 0; n < GN; ++n) { q[2 * n] = 0.5; q[2 * n + 1] = 0.5; }
+        CCK(cudaMemcpy(b->q_sw, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
+        for (size_t n = 0; n < GN; ++n) { q[2 * n] = 1. - 0.01; q[2 * n + 1] = 0.01; }
+        CCK(cudaMemcpy(b->q_ot, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CCK(cudaMemcpy(b->q_oa, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
         // p_breakpoint favours states with at most one copy in every clone (bpmodel.pyx:546-554)
-        std::vector<double> pb((size_t)K * B, 0.);
+        std::vector<double> pb((size_t)G * K * B, 0.);
         double cnt = 0.;
         std::vector<double> rowp(B, 0.);
-        for (int b = 0; b < B; ++b) {
+        for (int bb = 0; bb < B; ++bb) {
             int mx = 0;
-            for (int mm = 0; mm < M; ++mm) mx = m->h_brk[(size_t)b * M + mm] > mx ? m->h_brk[(size_t)b * M + mm] : mx;
-            if (mx <= 1) { rowp[b] = 1.; cnt += 1.; }
+            for (int mm = 0; mm < M; ++mm) mx = b->h_brk[(size_t)bb * M + mm] > mx ? b->h_brk[(size_t)bb * M + mm] : mx;
+            if (mx <= 1) { rowp[bb] = 1.; cnt += 1.; }
         }
-        for (int k = 0; k < K; ++k)
-            for (int b = 0; b < B; ++b) pb[(size_t)k * B + b] = rowp[b] / cnt;
-        if (K > 0) CCK(cudaMemcpy(m->p_brk, pb.data(), pb.size() * sizeof(double), cudaMemcpyHostToDevice));
+        for (size_t k = 0; k < (size_t)G * K; ++k)
+            for (int bb = 0; bb < B; ++bb) pb[k * B + bb] = rowp[bb] / cnt;
+        if (K > 0) CCK(cudaMemcpy(b->p_brk, pb.data(), pb.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     CCK(cudaDeviceSynchronize());   // pageable uploads above went through the legacy stream
     // first cached transition expectation (bpmodel.pyx:604), transition_model still 0 here
-    if (snapshot_spec(m, true) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
-    if (snapshot_spec(m, false) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
-    CCK(cudaStreamSynchronize(m->stream));
+    if (snapshot_spec(m, 0, G, true) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
+    if (snapshot_spec(m, 0, G, false) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
+    CCK(cudaStreamSynchronize(b->stream));
     CCK(cudaGetLastError());
     *out = m;
     return RMX_OK;
 }
 
-static int64_t array_count(Model* m, int id, bool* is_i64) {
-    const RmxDims& d = m->d;
+int rmx_create(const rmx_desc* desc, rmx_handle* out) {
+    return rmx_batch_create(desc, 1, desc->h_init, &desc->divergence_weight, out);
+}
+
+int rmx_batch_view(rmx_handle m, int first_fit, int num_fits, rmx_handle* out) {
+    *out = nullptr;
+    if (!m) return RMX_ERR_ARG;
+    if (first_fit < 0 || num_fits < 1 || first_fit + num_fits > m->gn)
+        return m->fail(RMX_ERR_ARG, "fit range outside the handle's fits");
+    Model* v = new Model();
+    v->b = m->b;
+    v->g0 = m->g0 + first_fit;
+    v->gn = num_fits;
+    *out = v;
+    return RMX_OK;
+}
+
+int rmx_num_fits(rmx_handle m, int* num_fits) {
+    if (!m) return RMX_ERR_ARG;
+    *num_fits = m->gn;
+    return RMX_OK;
+}
+
+// per-fit element count of an array attribute
+static int64_t array_count(Batch* b, int id, bool* is_i64) {
+    const RmxDims& d = b->d;
     *is_i64 = false;
     switch (id) {
     case RMX_A_H: return d.M;
@@ -679,73 +831,91 @@ static int64_t array_count(Model* m, int id, bool* is_i64) {
 
 int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
     bool i64;
-    int64_t want = array_count(m, id, &i64);
-    if (want < 0) return m->fail(RMX_ERR_ARG, "unknown array id");
-    if (want != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
+    const int64_t per = array_count(b, id, &i64);
+    if (per < 0) return m->fail(RMX_ERR_ARG, "unknown array id");
+    if (per * m->gn != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
+    const int g0 = m->g0, gn = m->gn;
     double* dst = nullptr;
     switch (id) {
     case RMX_A_H: {
         const double* s = (const double*)src;
-        for (int k = 0; k < m->d.M; ++k) m->P.h[k] = s[k];
-        m->ll_dirty = true;
+        for (int g = 0; g < gn; ++g) {
+            for (int k = 0; k < b->d.M; ++k) b->P[g0 + g].h[k] = s[(size_t)g * b->d.M + k];
+            b->ll_dirty[g0 + g] = 1;
+        }
+        b->params_dirty = true;
         return RMX_OK;
     }
-    case RMX_A_P_BREAKPOINT: dst = m->p_brk; break;
-    case RMX_A_P_ALLELE_SWAP: dst = m->q_sw; break;
-    case RMX_A_P_OUTLIER_TOTAL: dst = m->q_ot; break;
-    case RMX_A_P_OUTLIER_ALLELE: dst = m->q_oa; break;
-    case RMX_A_POSTERIOR_MARGINALS: dst = m->post; break;
-    case RMX_A_FRAMELOGPROB: dst = m->F; break;
+    case RMX_A_P_BREAKPOINT: dst = b->p_brk; break;
+    case RMX_A_P_ALLELE_SWAP: dst = b->q_sw; break;
+    case RMX_A_P_OUTLIER_TOTAL: dst = b->q_ot; break;
+    case RMX_A_P_OUTLIER_ALLELE: dst = b->q_oa; break;
+    case RMX_A_POSTERIOR_MARGINALS:
+        dst = b->post;
+        for (int g = g0; g < g0 + gn; ++g) b->asum_valid[g] = 0;
+        break;
+    case RMX_A_FRAMELOGPROB: dst = b->F; break;
     case RMX_A_TOTAL_LIKELIHOOD_MASK:
     case RMX_A_ALLELE_LIKELIHOOD_MASK: {
         const int64_t* s = (const int64_t*)src;
-        std::vector<uint8_t> v(m->d.N);
-        std::vector<int64_t>& keep = id == RMX_A_TOTAL_LIKELIHOOD_MASK ? m->h_tmask : m->h_amask;
-        for (int n = 0; n < m->d.N; ++n) { keep[n] = s[n]; v[n] = s[n] != 0; }
-        CK(cudaMemcpyAsync(id == RMX_A_TOTAL_LIKELIHOOD_MASK ? m->tmask : m->amask, v.data(), v.size(),
-                           cudaMemcpyHostToDevice, m->stream));
-        CK(cudaStreamSynchronize(m->stream));
-        m->ll_dirty = true;
+        const size_t n = (size_t)gn * b->d.N, off = (size_t)g0 * b->d.N;
+        std::vector<uint8_t> v(n);
+        std::vector<int64_t>& keep = id == RMX_A_TOTAL_LIKELIHOOD_MASK ? b->h_tmask : b->h_amask;
+        for (size_t e = 0; e < n; ++e) { keep[off + e] = s[e]; v[e] = s[e] != 0; }
+        CK(cudaMemcpyAsync((id == RMX_A_TOTAL_LIKELIHOOD_MASK ? b->tmask : b->amask) + off, v.data(), n,
+                           cudaMemcpyHostToDevice, b->stream));
+        CK(cudaStreamSynchronize(b->stream));
+        for (int g = g0; g < g0 + gn; ++g) b->ll_dirty[g] = 1;
         return RMX_OK;
     }
     default: return m->fail(RMX_ERR_ARG, "this attribute cannot be assigned");
     }
     if (count > 0) {
-        CK(cudaMemcpyAsync(dst, src, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, m->stream));
-        CK(cudaStreamSynchronize(m->stream));
+        CK(cudaMemcpyAsync(dst + (size_t)g0 * per, src, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+        CK(cudaStreamSynchronize(b->stream));
     }
     return RMX_OK;
 }
 
-static int materialize(Model* m, int id, double* dst) {
-    const RmxDims& d = m->d;
+// the (N-1,S,S) attributes of ONE fit, materialised in chunks (inspection / tests only)
+static int materialize(Model* m, int g, int id, double* dst) {
+    Batch* b = m->b.get();
+    const RmxDims& d = b->d;
     const int64_t SS = (int64_t)d.S * d.S;
     const int64_t nrows = d.N - 1;
     if (nrows <= 0) return RMX_OK;
-    if (id == RMX_A_LOG_TRANSMAT && !m->cn_updated) {   // constructor state: zeros (bpmodel.pyx:558)
+    if (id == RMX_A_LOG_TRANSMAT && !b->cn_updated[g]) {   // constructor state: zeros (bpmodel.pyx:558)
         memset(dst, 0, (size_t)(nrows * SS) * sizeof(double));
         return RMX_OK;
     }
+    const bool cached = id == RMX_A_CACHED_LOG_TRANSMAT;
+    const int tm = cached ? b->tm_cached[g] : b->tm_used[g];
+    int rc = ensure_mats(m, tm);
+    if (rc) return rc;
+    RmxTransSpec sp = spec_of(b, cached, tm);
+    sp.pd += (int64_t)g * b->rmd;
+    sp.wexp += (int64_t)g * b->rmd;
+    const int64_t NSo = (int64_t)g * d.N * d.S;
     int64_t chunk = (int64_t)(64 << 20) / (SS * 8);
     if (chunk < 1) chunk = 1;
     if (chunk > nrows) chunk = nrows;
     double* buf = nullptr;
     CK(cudaMalloc((void**)&buf, (size_t)(chunk * SS) * sizeof(double)));
-    int rc = RMX_OK;
     for (int64_t r0 = 0; r0 < nrows && rc == RMX_OK; r0 += chunk) {
         int64_t nr = nrows - r0 < chunk ? nrows - r0 : chunk;
         if (id == RMX_A_JOINT_POSTERIOR_MARGINALS)
-            rmx_launch_materialize_joint(m->stream, tables(m), d, rowsof(m), spec_of(m, false), m->cn_updated ? 0 : 1,
-                                         m->ahat, m->bhat, m->fexp, r0, nr, buf);
+            rmx_launch_materialize_joint(b->stream, tables(b), d, rowsof(b), sp, b->cn_updated[g] ? 0 : 1, b->ahat + NSo,
+                                         b->bhat + NSo, b->fexp + NSo, r0, nr, buf);
         else
-            rmx_launch_materialize_T(m->stream, tables(m), d, rowsof(m), spec_of(m, id == RMX_A_CACHED_LOG_TRANSMAT),
-                                     r0, nr, buf);
-        m->count();
+            rmx_launch_materialize_T(b->stream, tables(b), d, rowsof(b), sp, r0, nr, buf);
+        b->count();
         cudaError_t e = cudaMemcpyAsync(dst + r0 * SS, buf, (size_t)(nr * SS) * sizeof(double), cudaMemcpyDeviceToHost,
-                                        m->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+                                        b->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
         if (e != cudaSuccess) rc = m->fail(RMX_ERR_CUDA, cudaGetErrorString(e));
     }
     cudaFree(buf);
@@ -754,124 +924,166 @@ static int materialize(Model* m, int id, double* dst) {
 
 int rmx_get_array(rmx_handle m, int id, void* dstv, int64_t count) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
     bool i64;
-    int64_t want = array_count(m, id, &i64);
-    if (want < 0) return m->fail(RMX_ERR_ARG, "unknown array id");
-    if (want != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
+    const int64_t per = array_count(b, id, &i64);
+    if (per < 0) return m->fail(RMX_ERR_ARG, "unknown array id");
+    if (per * m->gn != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
+    const int g0 = m->g0, gn = m->gn, N = b->d.N;
     const double* src = nullptr;
+    bool shared = false;
     switch (id) {
-    case RMX_A_H: memcpy(dstv, m->P.h, sizeof(double) * m->d.M); return RMX_OK;
-    case RMX_A_P_BREAKPOINT: src = m->p_brk; break;
-    case RMX_A_P_ALLELE_SWAP: src = m->q_sw; break;
-    case RMX_A_P_OUTLIER_TOTAL: src = m->q_ot; break;
-    case RMX_A_P_OUTLIER_ALLELE: src = m->q_oa; break;
-    case RMX_A_POSTERIOR_MARGINALS: src = m->post; break;
-    case RMX_A_FRAMELOGPROB: src = m->F; break;
-    case RMX_A_TOTAL_LIKELIHOOD_MASK: memcpy(dstv, m->h_tmask.data(), sizeof(int64_t) * m->d.N); return RMX_OK;
-    case RMX_A_ALLELE_LIKELIHOOD_MASK: memcpy(dstv, m->h_amask.data(), sizeof(int64_t) * m->d.N); return RMX_OK;
+    case RMX_A_H:
+        for (int g = 0; g < gn; ++g) memcpy((double*)dstv + (size_t)g * b->d.M, b->P[g0 + g].h, sizeof(double) * b->d.M);
+        return RMX_OK;
+    case RMX_A_P_BREAKPOINT: src = b->p_brk; break;
+    case RMX_A_P_ALLELE_SWAP: src = b->q_sw; break;
+    case RMX_A_P_OUTLIER_TOTAL: src = b->q_ot; break;
+    case RMX_A_P_OUTLIER_ALLELE: src = b->q_oa; break;
+    case RMX_A_POSTERIOR_MARGINALS: src = b->post; break;
+    case RMX_A_FRAMELOGPROB: src = b->F; break;
+    case RMX_A_TOTAL_LIKELIHOOD_MASK: memcpy(dstv, b->h_tmask.data() + (size_t)g0 * N, sizeof(int64_t) * N * gn); return RMX_OK;
+    case RMX_A_ALLELE_LIKELIHOOD_MASK: memcpy(dstv, b->h_amask.data() + (size_t)g0 * N, sizeof(int64_t) * N * gn); return RMX_OK;
     case RMX_A_LOG_TRANSMAT:
     case RMX_A_CACHED_LOG_TRANSMAT:
-    case RMX_A_JOINT_POSTERIOR_MARGINALS: return materialize(m, id, (double*)dstv);
-    case RMX_A_L: src = m->l; break;
-    case RMX_A_X: src = m->x; break;
+    case RMX_A_JOINT_POSTERIOR_MARGINALS:
+        for (int g = 0; g < gn; ++g) {
+            int rc = materialize(m, g0 + g, id, (double*)dstv + (size_t)g * per);
+            if (rc) return rc;
+        }
+        return RMX_OK;
+    case RMX_A_L: src = b->l; shared = true; break;
+    case RMX_A_X: src = b->x; shared = true; break;
     case RMX_A_Y: {
-        std::vector<double> a(m->d.N), b(m->d.N);
-        CK(cudaMemcpy(a.data(), m->y0, sizeof(double) * m->d.N, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(b.data(), m->y1, sizeof(double) * m->d.N, cudaMemcpyDeviceToHost));
+        std::vector<double> a(N), c(N);
+        CK(cudaMemcpy(a.data(), b->y0, sizeof(double) * N, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(c.data(), b->y1, sizeof(double) * N, cudaMemcpyDeviceToHost));
         double* o = (double*)dstv;
-        for (int n = 0; n < m->d.N; ++n) { o[2 * n] = a[n]; o[2 * n + 1] = b[n]; }
+        for (int g = 0; g < gn; ++g)
+            for (int n = 0; n < N; ++n) { o[((size_t)g * N + n) * 2] = a[n]; o[((size_t)g * N + n) * 2 + 1] = c[n]; }
         return RMX_OK;
     }
     case RMX_A_STATE_PATH: {
         int64_t* o = (int64_t*)dstv;
-        if (!m->path_valid) return m->fail(RMX_ERR_VALUE, "no state path: call rmx_infer_cn first");
-        for (int n = 0; n < m->d.N; ++n) o[n] = m->h_path[n];
+        for (int g = 0; g < gn; ++g) {
+            if (!b->path_valid[g0 + g]) return m->fail(RMX_ERR_VALUE, "no state path: call rmx_infer_cn first");
+            for (int n = 0; n < N; ++n) o[(size_t)g * N + n] = b->h_path[(size_t)(g0 + g) * N + n];
+        }
         return RMX_OK;
     }
     default: return m->fail(RMX_ERR_ARG, "unknown array id");
     }
     if (count > 0) {
-        CK(cudaMemcpyAsync(dstv, src, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-        CK(cudaStreamSynchronize(m->stream));
+        if (shared) {
+            for (int g = 0; g < gn; ++g)
+                CK(cudaMemcpyAsync((double*)dstv + (size_t)g * per, src, (size_t)per * sizeof(double), cudaMemcpyDeviceToHost,
+                                   b->stream));
+        } else {
+            CK(cudaMemcpyAsync(dstv, src + (size_t)g0 * per, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost,
+                               b->stream));
+        }
+        CK(cudaStreamSynchronize(b->stream));
     }
     return RMX_OK;
 }
 
+static double* scalar_slot(RmxParams& P, int id) {
+    switch (id) {
+    case RMX_S_NEGBIN_R_0: return &P.negbin_r[0];
+    case RMX_S_NEGBIN_R_1: return &P.negbin_r[1];
+    case RMX_S_NEGBIN_HDEL_MU: return &P.negbin_hdel_mu;
+    case RMX_S_NEGBIN_HDEL_R_0: return &P.negbin_hdel_r[0];
+    case RMX_S_NEGBIN_HDEL_R_1: return &P.negbin_hdel_r[1];
+    case RMX_S_BETABIN_M_0: return &P.betabin_M[0];
+    case RMX_S_BETABIN_M_1: return &P.betabin_M[1];
+    case RMX_S_BETABIN_LOH_P: return &P.betabin_loh_p;
+    case RMX_S_BETABIN_LOH_M_0: return &P.betabin_loh_M[0];
+    case RMX_S_BETABIN_LOH_M_1: return &P.betabin_loh_M[1];
+    case RMX_S_DIVERGENCE_WEIGHT: return &P.divergence_weight;
+    default: return nullptr;
+    }
+}
+
+// sets the scalar on every fit of the handle
 int rmx_set_scalar(rmx_handle m, int id, double v) {
     if (!m) return RMX_ERR_ARG;
-    RmxParams& P = m->P;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    const int g0 = m->g0, gn = m->gn;
     switch (id) {
-    case RMX_S_NEGBIN_R_0: P.negbin_r[0] = v; break;
-    case RMX_S_NEGBIN_R_1: P.negbin_r[1] = v; break;
-    case RMX_S_NEGBIN_HDEL_MU: P.negbin_hdel_mu = v; break;
-    case RMX_S_NEGBIN_HDEL_R_0: P.negbin_hdel_r[0] = v; break;
-    case RMX_S_NEGBIN_HDEL_R_1: P.negbin_hdel_r[1] = v; break;
-    case RMX_S_BETABIN_M_0: P.betabin_M[0] = v; break;
-    case RMX_S_BETABIN_M_1: P.betabin_M[1] = v; break;
-    case RMX_S_BETABIN_LOH_P: P.betabin_loh_p = v; break;
-    case RMX_S_BETABIN_LOH_M_0: P.betabin_loh_M[0] = v; break;
-    case RMX_S_BETABIN_LOH_M_1: P.betabin_loh_M[1] = v; break;
-    case RMX_S_PRIOR_OUTLIER_TOTAL: m->prior_ot = v; return RMX_OK;
-    case RMX_S_PRIOR_OUTLIER_ALLELE: m->prior_oa = v; return RMX_OK;
-    case RMX_S_TRANSITION_PENALTY: m->pen = v; return RMX_OK;
-    case RMX_S_DIVERGENCE_WEIGHT: P.divergence_weight = v; return RMX_OK;
+    case RMX_S_PRIOR_OUTLIER_TOTAL:
+    case RMX_S_PRIOR_OUTLIER_ALLELE:
+        if (b->G != gn && v != (id == RMX_S_PRIOR_OUTLIER_TOTAL ? b->prior_ot : b->prior_oa))
+            return m->fail(RMX_ERR_UNSUPPORTED, "the outlier priors are shared by the fits of a batch: set them on the batch handle");
+        (id == RMX_S_PRIOR_OUTLIER_TOTAL ? b->prior_ot : b->prior_oa) = v;
+        return RMX_OK;
+    case RMX_S_TRANSITION_PENALTY:
+        if (v != b->pen) return m->fail(RMX_ERR_UNSUPPORTED, "transition_penalty is fixed when the model is created");
+        return RMX_OK;
     case RMX_S_TRANSITION_MODEL:
         if (v != 0. && v != 1.) return m->fail(RMX_ERR_VALUE, "transition_model must be 0 or 1");
-        m->tm = (int)v;
+        for (int g = g0; g < g0 + gn; ++g) b->tm[g] = (int)v;
         return RMX_OK;
-    case RMX_S_HMM_LOG_NORM_CONST: m->logZ = v; return RMX_OK;
-    default: return m->fail(RMX_ERR_ARG, "unknown scalar id");
+    case RMX_S_HMM_LOG_NORM_CONST:
+        for (int g = g0; g < g0 + gn; ++g) b->logZ[g] = v;
+        return RMX_OK;
+    default: break;
     }
-    m->ll_dirty = true;
+    if (!scalar_slot(b->P[g0], id)) return m->fail(RMX_ERR_ARG, "unknown scalar id");
+    for (int g = g0; g < g0 + gn; ++g) {
+        *scalar_slot(b->P[g], id) = v;
+        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[g] = 1;
+    }
+    b->params_dirty = true;
     return RMX_OK;
 }
 
+// one value per fit of the handle
 int rmx_get_scalar(rmx_handle m, int id, double* v) {
     if (!m) return RMX_ERR_ARG;
-    const RmxParams& P = m->P;
-    switch (id) {
-    case RMX_S_NEGBIN_R_0: *v = P.negbin_r[0]; break;
-    case RMX_S_NEGBIN_R_1: *v = P.negbin_r[1]; break;
-    case RMX_S_NEGBIN_HDEL_MU: *v = P.negbin_hdel_mu; break;
-    case RMX_S_NEGBIN_HDEL_R_0: *v = P.negbin_hdel_r[0]; break;
-    case RMX_S_NEGBIN_HDEL_R_1: *v = P.negbin_hdel_r[1]; break;
-    case RMX_S_BETABIN_M_0: *v = P.betabin_M[0]; break;
-    case RMX_S_BETABIN_M_1: *v = P.betabin_M[1]; break;
-    case RMX_S_BETABIN_LOH_P: *v = P.betabin_loh_p; break;
-    case RMX_S_BETABIN_LOH_M_0: *v = P.betabin_loh_M[0]; break;
-    case RMX_S_BETABIN_LOH_M_1: *v = P.betabin_loh_M[1]; break;
-    case RMX_S_PRIOR_OUTLIER_TOTAL: *v = m->prior_ot; break;
-    case RMX_S_PRIOR_OUTLIER_ALLELE: *v = m->prior_oa; break;
-    case RMX_S_TRANSITION_PENALTY: *v = m->pen; break;
-    case RMX_S_DIVERGENCE_WEIGHT: *v = P.divergence_weight; break;
-    case RMX_S_TRANSITION_MODEL: *v = (double)m->tm; break;
-    case RMX_S_HMM_LOG_NORM_CONST: *v = m->logZ; break;
-    default: return m->fail(RMX_ERR_ARG, "unknown scalar id");
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    for (int g = m->g0; g < m->g0 + m->gn; ++g, ++v) {
+        switch (id) {
+        case RMX_S_PRIOR_OUTLIER_TOTAL: *v = b->prior_ot; break;
+        case RMX_S_PRIOR_OUTLIER_ALLELE: *v = b->prior_oa; break;
+        case RMX_S_TRANSITION_PENALTY: *v = b->pen; break;
+        case RMX_S_TRANSITION_MODEL: *v = (double)b->tm[g]; break;
+        case RMX_S_HMM_LOG_NORM_CONST: *v = b->logZ[g]; break;
+        default: {
+            double* s = scalar_slot(b->P[g], id);
+            if (!s) return m->fail(RMX_ERR_ARG, "unknown scalar id");
+            *v = *s;
+        }
+        }
     }
     return RMX_OK;
 }
 
+// identical for every fit of a batch: filled once (not per fit)
 int rmx_get_derived(rmx_handle m, int which, int64_t* dst, int64_t count) {
     if (!m) return RMX_ERR_ARG;
-    const RmxDims& d = m->d;
+    Batch* b = m->b.get();
+    const RmxDims& d = b->d;
     int64_t want = which == 0 ? (int64_t)d.N * d.S * d.M : (int64_t)d.N * d.S;
     if (which < 0 || which > 3) return m->fail(RMX_ERR_ARG, "unknown derived table");
     if (want != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements");
     for (int n = 0; n < d.N; ++n) {
-        int n0 = m->h_nrm[2 * n], n1 = m->h_nrm[2 * n + 1];
+        int n0 = b->h_nrm[2 * n], n1 = b->h_nrm[2 * n + 1];
         for (int s = 0; s < d.S; ++s) {
             int a0 = n0, a1 = n1;
             for (int mm = 1; mm < d.M; ++mm) {
-                a0 += m->h_tab[((size_t)s * d.M + mm) * 2];
-                a1 += m->h_tab[((size_t)s * d.M + mm) * 2 + 1];
+                a0 += b->h_tab[((size_t)s * d.M + mm) * 2];
+                a1 += b->h_tab[((size_t)s * d.M + mm) * 2 + 1];
             }
             int64_t o = (int64_t)n * d.S + s;
             if (which == 0) {
                 dst[o * d.M] = n0 + n1;
                 for (int mm = 1; mm < d.M; ++mm)
-                    dst[o * d.M + mm] = m->h_tab[((size_t)s * d.M + mm) * 2] + m->h_tab[((size_t)s * d.M + mm) * 2 + 1];
-            } else if (which == 1) dst[o] = m->h_nsub[s];
+                    dst[o * d.M + mm] = b->h_tab[((size_t)s * d.M + mm) * 2] + b->h_tab[((size_t)s * d.M + mm) * 2 + 1];
+            } else if (which == 1) dst[o] = b->h_nsub[s];
             else if (which == 2) dst[o] = (a0 + a1) == 0;
             else dst[o] = (a0 == 0) || (a1 == 0);
         }
@@ -879,20 +1091,29 @@ int rmx_get_derived(rmx_handle m, int which, int64_t* dst, int64_t count) {
     return RMX_OK;
 }
 
+static void take_logz(Model* m) {
+    Batch* b = m->b.get();
+    for (int g = m->g0; g < m->g0 + m->gn; ++g) b->logZ[g] = b->hp[(size_t)g * Batch::RED + 15];
+}
+
 int rmx_update(rmx_handle m, int id) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
     int rc = do_update(m, id);
     if (rc) return rc;
     rc = sync_check(m);
     if (rc) return rc;
-    if (id == RMX_U_CN) m->logZ = m->hp[15];
+    if (id == RMX_U_CN) take_logz(m);
     return RMX_OK;
 }
 
 int rmx_variational_update(rmx_handle m, int n_iter) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
     static const int order[5] = {RMX_U_ALLELE_SWAP, RMX_U_CN, RMX_U_BREAKPOINT, RMX_U_OUTLIER_TOTAL,
                                  RMX_U_OUTLIER_ALLELE};
     for (int it = 0; it < n_iter; ++it)
@@ -902,233 +1123,310 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
         }
     int rc = sync_check(m);
     if (rc) return rc;
-    if (n_iter > 0) m->logZ = m->hp[15];
+    if (n_iter > 0) take_logz(m);
     return RMX_OK;
 }
 
-// launches the ELBO reductions; results land in hp[0..9] after sync
-static int elbo_terms(Model* m) {
-    int rc = ensure_ll(m);
+// launches the ELBO reductions of the handle's fits; results land in hp[g][0..9] after sync.
+// full = false: only the ELBO is wanted, so of sum joint*cached_T - sum joint*T only the breakend rows are
+// evaluated (everywhere else the two transition matrices are identical and the terms cancel exactly).
+static int elbo_terms(Model* m, bool full) {
+    Batch* b = m->b.get();
+    const int g0 = m->g0, gn = m->gn;
+    int rc = ensure_asum(m, g0, gn);
     if (rc) return rc;
-    const RmxDims& d = m->d;
-    RmxTables T = tables(m);
-    rmx_launch_elbo_rows(m->stream, T, d, m->P, m->LL, m->post, m->F, m->q_ot, m->q_oa, m->q_sw, m->prior_ot,
-                         m->prior_oa, m->rowv);
-    rmx_launch_reduce_cols(m->stream, m->rowv, d.N, 7, m->red_out);
-    m->count(2);
+    rc = push_params(m);
+    if (rc) return rc;
+    const RmxDims& d = b->d;
+    RmxTables T = tables(b);
+    const int RED = Batch::RED;
+    rmx_launch_elbo_rows(b->stream, T, d, b->dP, g0, gn, b->Asum, b->post, b->F, b->q_ot, b->q_oa, b->q_sw, b->prior_ot,
+                         b->prior_oa, b->rowv);
+    rmx_launch_reduce_cols(b->stream, b->rowv, d.N, 7, g0, gn, (int64_t)8 * d.N, b->red_out, RED);
+    b->count(2);
     // entropy of p_breakpoint
-    double* pl = m->rowv + (size_t)d.N * 8;
-    int64_t kb = (int64_t)d.K * d.B;
+    double* pl = b->rowv + (size_t)b->G * 8 * d.N;
+    const int64_t kb = (int64_t)d.K * d.B;
     if (kb > 0) {
-        rmx_launch_plogp(m->stream, m->p_brk, kb, pl);
-        rmx_launch_reduce_cols(m->stream, pl, kb, 1, m->red_out + 7);
-        m->count(2);
-    } else {
-        CK(cudaMemsetAsync(m->red_out + 7, 0, sizeof(double), m->stream));
+        rmx_launch_plogp(b->stream, b->p_brk, kb, g0, gn, pl, kb);
+        rmx_launch_reduce_cols(b->stream, pl, kb, 1, g0, gn, kb, b->red_out + 7, RED);
+        b->count(2);
     }
-    // transition terms
+    // transition terms -> red_out[g][8] (energy side) and [9] (entropy side)
+    for (int g = g0; g < g0 + gn; ++g)
+        CK(cudaMemsetAsync(b->red_out + (size_t)g * RED + (kb > 0 ? 8 : 7), 0, (kb > 0 ? 2 : 3) * sizeof(double), b->stream));
     if (d.N > 1) {
-        rc = ensure_mats(m, m->tm_cached, m->pen_cached);
+        std::vector<int> key(b->G, 0);
+        for (int g = g0; g < g0 + gn; ++g) key[g] = (b->cn_updated[g] ? 4 : 0) | (b->tm_used[g] << 1) | b->tm_cached[g];
+        for_runs(g0, gn, key, nullptr, [&](int g, int n) {
+            if (rc) return;
+            rc = ensure_mats(m, b->tm_cached[g]);
+            if (!rc) rc = ensure_mats(m, b->tm_used[g]);
+            if (rc) return;
+            RmxTransSpec used = spec_of(b, false, b->tm_used[g]), cached = spec_of(b, true, b->tm_cached[g]);
+            const bool upd = b->cn_updated[g] != 0;
+            if (upd && !full) {
+                if (b->R > 0) {
+                    rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
+                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                    rmx_launch_reduce_cols(b->stream, b->rowsum, b->R, 1, g, n, d.N, b->red_out + 8, RED);
+                    b->count(2);
+                }
+            } else {
+                rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, cached, 0, b->rmd, nullptr, d.N - 1,
+                                   upd ? 0 : 1, b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                rmx_launch_reduce_cols(b->stream, b->rowsum, d.N - 1, 1, g, n, d.N, b->red_out + 8, RED);
+                b->count(2);
+                if (upd) {
+                    rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, used, used, 0, b->rmd, nullptr, d.N - 1, 0,
+                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                    rmx_launch_reduce_cols(b->stream, b->rowsum, d.N - 1, 1, g, n, d.N, b->red_out + 9, RED);
+                    b->count(2);
+                }
+            }
+        });
         if (rc) return rc;
-        rc = ensure_mats(m, m->tm_used, m->pen_used);
-        if (rc) return rc;
-        RmxTransSpec used = spec_of(m, false), cached = spec_of(m, true);
-        int uniform = m->cn_updated ? 0 : 1;
-        rmx_launch_pairsum(m->stream, T, d, rowsof(m), used, cached, uniform, m->ahat, m->bhat, m->fexp, m->rowsum);
-        rmx_launch_reduce_cols(m->stream, m->rowsum, d.N - 1, 1, m->red_out + 8);
-        m->count(2);
-        if (m->cn_updated) {
-            rmx_launch_pairsum(m->stream, T, d, rowsof(m), used, used, 0, m->ahat, m->bhat, m->fexp, m->rowsum);
-            rmx_launch_reduce_cols(m->stream, m->rowsum, d.N - 1, 1, m->red_out + 9);
-            m->count(2);
-        } else {
-            CK(cudaMemsetAsync(m->red_out + 9, 0, sizeof(double), m->stream));
-        }
-    } else {
-        CK(cudaMemsetAsync(m->red_out + 8, 0, 2 * sizeof(double), m->stream));
     }
-    CK(cudaMemcpyAsync(m->hp, m->red_out, 10 * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaMemcpyAsync(b->hp + (size_t)g0 * RED, b->red_out + (size_t)g0 * RED, sizeof(double) * RED * gn,
+                       cudaMemcpyDeviceToHost, b->stream));
     return sync_check(m);
 }
 
-static double energy_of(const Model* m) {
-    const double* r = m->hp;
+static double energy_of(const Batch* b, int g) {
+    const double* r = b->hp + (size_t)g * Batch::RED;
     // prior, total (+ outlier prior), allele (+ outlier prior), transitions  (bpmodel.pyx:1068-1115)
     return r[0] + (r[1] + r[3]) + (r[2] + r[4]) + r[8];
 }
-static double entropy_of(const Model* m) {
-    const double* r = m->hp;
+static double entropy_of(const Batch* b, int g) {
+    const double* r = b->hp + (size_t)g * Batch::RED;
     // bpmodel.pyx:1050-1056
-    return -m->logZ + r[5] + r[9] + r[7] + r[6];
+    return -b->logZ[g] + r[5] + r[9] + r[7] + r[6];
 }
 
-int rmx_variational_energy(rmx_handle m, double* out) {
+static int elbo_like(rmx_handle m, double* out, int what) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    int rc = elbo_terms(m);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    // the logZ copy of an update may still be in hp: elbo_terms overwrites hp[15] with the same device value
+    int rc = elbo_terms(m, what != 2);
     if (rc) return rc;
-    *out = energy_of(m);
+    for (int g = m->g0; g < m->g0 + m->gn; ++g)
+        out[g - m->g0] = what == 0 ? energy_of(b, g) : (what == 1 ? entropy_of(b, g) : energy_of(b, g) - entropy_of(b, g));
     return RMX_OK;
 }
-int rmx_variational_entropy(rmx_handle m, double* out) {
-    if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    int rc = elbo_terms(m);
-    if (rc) return rc;
-    *out = entropy_of(m);
-    return RMX_OK;
-}
-int rmx_elbo(rmx_handle m, double* out) {
-    if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    int rc = elbo_terms(m);
-    if (rc) return rc;
-    *out = energy_of(m) - entropy_of(m);
-    return RMX_OK;
-}
+int rmx_variational_energy(rmx_handle m, double* out) { return elbo_like(m, out, 0); }
+int rmx_variational_entropy(rmx_handle m, double* out) { return elbo_like(m, out, 1); }
+int rmx_elbo(rmx_handle m, double* out) { return elbo_like(m, out, 2); }
 
-// sample mask -> row list on the device; returns R and sets *rows (nullptr = identity)
-static int stage_rows(Model* m, const int64_t* sample, int* R, const int** rows) {
-    const int N = m->d.N;
-    int cnt = 0;
-    for (int n = 0; n < N; ++n)
-        if (sample[n] != 0) m->hrows[cnt++] = n;
-    *R = cnt;
-    if (cnt == N) {
+// sample masks (gn, N) -> per-fit row lists on the device; *rows = nullptr when every fit takes all segments
+static int stage_rows(Model* m, const int64_t* sample, int* Rmax, const int** rows) {
+    Batch* b = m->b.get();
+    const int N = b->d.N, g0 = m->g0, gn = m->gn;
+    int rmax = 0;
+    bool all = true;
+    for (int g = 0; g < gn; ++g) {
+        int cnt = 0;
+        int* hr = b->hrows + (size_t)(g0 + g) * N;
+        const int64_t* s = sample + (size_t)g * N;
+        for (int n = 0; n < N; ++n)
+            if (s[n] != 0) hr[cnt++] = n;
+        b->hRn[g0 + g] = cnt;
+        all &= cnt == N;
+        rmax = cnt > rmax ? cnt : rmax;
+    }
+    *Rmax = rmax;
+    if (all) {
         *rows = nullptr;
         return RMX_OK;
     }
-    if (cnt > 0) CK(cudaMemcpyAsync(m->d_rows, m->hrows, (size_t)cnt * sizeof(int), cudaMemcpyHostToDevice, m->stream));
-    *rows = m->d_rows;
+    CK(cudaMemcpyAsync(b->d_rows + (size_t)g0 * N, b->hrows + (size_t)g0 * N, (size_t)gn * N * sizeof(int),
+                       cudaMemcpyHostToDevice, b->stream));
+    CK(cudaMemcpyAsync(b->d_Rn + g0, b->hRn + g0, (size_t)gn * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    *rows = b->d_rows;
     return RMX_OK;
 }
 
-static int launch_ell(Model* m, const int* rows, int R, double* out_dev) {
-    RmxTables T = tables(m);
-    rmx_launch_segconst(m->stream, T, m->P, rows, R, m->segc_s);
-    int nb = rmx_ell_blocks(m->d, R);
-    rmx_launch_ell(m->stream, T, m->d, m->P, rows, R, m->segc_s, m->post, m->q_ot, m->q_oa, m->q_sw, m->part,
-                   m->dflags);
-    rmx_launch_reduce_cols(m->stream, m->part, nb, 1, out_dev);
-    m->count(3);
+// E[LL] of the handle's fits on the staged rows -> red_out[g][slot]
+static int launch_ell(Model* m, const int* rows, int Rmax, int slot) {
+    Batch* b = m->b.get();
+    int rc = push_params(m);
+    if (rc) return rc;
+    RmxTables T = tables(b);
+    const int g0 = m->g0, gn = m->gn;
+    rmx_launch_segconst(b->stream, T, b->d, b->dP, g0, gn, rows, b->d_Rn, Rmax, b->segc_s);
+    const int nb = rmx_ell_blocks(b->d, Rmax);
+    rmx_launch_ell(b->stream, T, b->d, b->dP, g0, gn, rows, b->d_Rn, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
+                   b->part, b->part_stride, b->dflags);
+    rmx_launch_reduce_cols(b->stream, b->part, nb, 1, g0, gn, b->part_stride, b->red_out + slot, Batch::RED);
+    b->count(3);
     return RMX_OK;
+}
+
+static int fetch_red(Model* m) {
+    Batch* b = m->b.get();
+    CK(cudaMemcpyAsync(b->hp + (size_t)m->g0 * Batch::RED, b->red_out + (size_t)m->g0 * Batch::RED,
+                       sizeof(double) * Batch::RED * m->gn, cudaMemcpyDeviceToHost, b->stream));
+    return sync_check(m);
 }
 
 int rmx_expected_log_likelihood(rmx_handle m, const int64_t* sample, double* out) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    int R;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    int Rmax;
     const int* rows;
-    int rc = stage_rows(m, sample, &R, &rows);
+    int rc = stage_rows(m, sample, &Rmax, &rows);
     if (rc) return rc;
-    if (R == 0) { *out = 0.; return RMX_OK; }
-    launch_ell(m, rows, R, m->red_out + 16);
-    CK(cudaMemcpyAsync(m->hp + 16, m->red_out + 16, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-    rc = sync_check(m);
+    for (int g = 0; g < m->gn; ++g) out[g] = 0.;
+    if (Rmax == 0) return RMX_OK;
+    rc = launch_ell(m, rows, Rmax, 16);
     if (rc) return rc;
-    *out = m->hp[16];
+    rc = fetch_red(m);
+    if (rc) return rc;
+    for (int g = 0; g < m->gn; ++g)
+        out[g] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 16] : 0.;
     return RMX_OK;
 }
 
 int rmx_expected_log_likelihood_grid(rmx_handle m, const int64_t* sample, int scalar_id, const double* values,
                                      int n_values, double* out) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
     if (n_values < 0 || n_values > 32) return m->fail(RMX_ERR_ARG, "n_values must be in [0, 32]");
     if (scalar_id < RMX_S_NEGBIN_R_0 || scalar_id > RMX_S_BETABIN_LOH_M_1)
         return m->fail(RMX_ERR_ARG, "scalar_id must name a likelihood parameter");
-    int R;
+    int Rmax;
     const int* rows;
-    int rc = stage_rows(m, sample, &R, &rows);
+    int rc = stage_rows(m, sample, &Rmax, &rows);
     if (rc) return rc;
-    // the per-launch partial buffer is reused, which is safe because launches are stream ordered
-    for (int g = 0; g < n_values; ++g) {
-        rc = rmx_set_scalar(m, scalar_id, values[g]);
+    // values is (gn, n_values): fit g evaluates values[g][v]; launches are stream ordered, so the per-launch
+    // scratch (segc_s, part) is reused safely
+    for (int v = 0; v < n_values; ++v) {
+        for (int g = 0; g < m->gn; ++g) {
+            *scalar_slot(b->P[m->g0 + g], scalar_id) = values[(size_t)g * n_values + v];
+            b->ll_dirty[m->g0 + g] = 1;
+        }
+        b->params_dirty = true;
+        if (Rmax == 0) continue;
+        rc = launch_ell(m, rows, Rmax, 16 + v);
         if (rc) return rc;
-        if (R == 0) { out[g] = 0.; continue; }
-        launch_ell(m, rows, R, m->red_out + 16 + g);
     }
-    if (R == 0 || n_values == 0) return RMX_OK;
-    CK(cudaMemcpyAsync(m->hp + 16, m->red_out + 16, n_values * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-    rc = sync_check(m);
+    for (int e = 0; e < m->gn * n_values; ++e) out[e] = 0.;
+    if (Rmax == 0 || n_values == 0) return RMX_OK;
+    rc = fetch_red(m);
     if (rc) return rc;
-    for (int g = 0; g < n_values; ++g) out[g] = m->hp[16 + g];
+    for (int g = 0; g < m->gn; ++g)
+        for (int v = 0; v < n_values; ++v)
+            out[(size_t)g * n_values + v] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 16 + v] : 0.;
     return RMX_OK;
 }
 
 int rmx_expected_log_likelihood_partial_h(rmx_handle m, const int64_t* sample, double* out) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    int R;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const int M = b->d.M;
+    int Rmax;
     const int* rows;
-    int rc = stage_rows(m, sample, &R, &rows);
+    int rc = stage_rows(m, sample, &Rmax, &rows);
     if (rc) return rc;
-    for (int k = 0; k < m->d.M; ++k) out[k] = 0.;
-    if (R == 0) return RMX_OK;
-    int nb = rmx_ell_blocks(m->d, R);
-    rmx_launch_ell_grad(m->stream, tables(m), m->d, m->P, rows, R, m->post, m->q_ot, m->q_oa, m->q_sw, m->part,
-                        m->dflags);
-    rmx_launch_reduce_cols(m->stream, m->part, nb, RMX_MAXM, m->red_out + 48);
-    m->count(2);
-    CK(cudaMemcpyAsync(m->hp + 48, m->red_out + 48, RMX_MAXM * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-    rc = sync_check(m);
+    for (int e = 0; e < m->gn * M; ++e) out[e] = 0.;
+    if (Rmax == 0) return RMX_OK;
+    rc = push_params(m);
     if (rc) return rc;
-    for (int k = 0; k < m->d.M; ++k) out[k] = m->hp[48 + k];
+    const int nb = rmx_ell_blocks(b->d, Rmax);
+    rmx_launch_ell_grad(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, rows, b->d_Rn, Rmax, b->post, b->q_ot, b->q_oa,
+                        b->q_sw, b->part, b->part_stride, b->dflags);
+    rmx_launch_reduce_cols(b->stream, b->part, nb, RMX_MAXM, m->g0, m->gn, b->part_stride, b->red_out + 48, Batch::RED);
+    b->count(2);
+    rc = fetch_red(m);
+    if (rc) return rc;
+    for (int g = 0; g < m->gn; ++g)
+        for (int k = 0; k < M; ++k)
+            out[(size_t)g * M + k] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 48 + k] : 0.;
     return RMX_OK;
 }
 
 int rmx_infer_cn(rmx_handle m, int64_t* cn) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    const RmxDims& d = m->d;
-    m->h_path.assign(d.N, 0);
-    if (m->cn_updated) {
-        // max_product(self.framelogprob, self.log_transmat) (bpmodel.pyx:1203): both as of the last update_p_cn
-        if (!m->lattice) {
-            cudaError_t e = dalloc(m, &m->lattice, (size_t)d.N * d.S);
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const RmxDims& d = b->d;
+    const int g0 = m->g0, gn = m->gn, N = d.N;
+    // max_product(self.framelogprob, self.log_transmat) (bpmodel.pyx:1203): both as of the last update_p_cn;
+    // constructor state (framelogprob == 1, log_transmat == 0) gives the all-zero path (first max)
+    for (int g = g0; g < g0 + gn; ++g)
+        for (int n = 0; n < N; ++n) b->h_path[(size_t)g * N + n] = 0;
+    bool any = false;
+    for (int g = g0; g < g0 + gn; ++g) any |= b->cn_updated[g] != 0;
+    if (any) {
+        if (b->lattice_fits < gn) {
+            // scratch sized for the largest range decoded so far (old one is freed with the batch)
+            cudaError_t e = dalloc(b, &b->lattice, (size_t)gn * N * d.S);
             if (e != cudaSuccess) return m->fail(RMX_ERR_CUDA, "out of device memory for the Viterbi lattice");
+            b->lattice_fits = gn;
         }
-        int rc = ensure_mats(m, m->tm_used, m->pen_used);
+        int rc = RMX_OK;
+        for_runs(g0, gn, b->tm_used, &b->cn_updated, [&](int g, int n) {
+            if (rc) return;
+            rc = ensure_mats(m, b->tm_used[g]);
+            if (rc) return;
+            rmx_launch_viterbi(b->stream, tables(b), d, g, n, chainsof(b), rowsof(b), spec_of(b, false, b->tm_used[g]),
+                               b->rmd, b->F, b->lattice, b->path);
+            b->count();
+        });
         if (rc) return rc;
-        rmx_launch_viterbi(m->stream, tables(m), d, chainsof(m), rowsof(m), spec_of(m, false), m->F, m->lattice,
-                           m->path);
-        m->count();
-        CK(cudaMemcpyAsync(m->h_path.data(), m->path, sizeof(int) * d.N, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(b->hrows + (size_t)g0 * N, b->path + (size_t)g0 * N, sizeof(int) * (size_t)gn * N,
+                           cudaMemcpyDeviceToHost, b->stream));
         rc = sync_check(m);
         if (rc) return rc;
+        for (int g = g0; g < g0 + gn; ++g)
+            if (b->cn_updated[g])
+                for (int n = 0; n < N; ++n) b->h_path[(size_t)g * N + n] = b->hrows[(size_t)g * N + n];
     }
-    // constructor state: framelogprob == 1 and log_transmat == 0 give the all-zero path (first max)
-    m->path_valid = true;
     // cn[n, m, ell] = cn_states[n, path[n], m, ell]; the allele-swap branch of bpmodel.pyx:1208-1209
     // indexes both sides with the swapped ell, so it does not change the output
-    for (int n = 0; n < d.N; ++n) {
-        int s = m->h_path[n];
-        int64_t* o = cn + (size_t)n * d.M * 2;
-        o[0] = m->h_nrm[2 * n];
-        o[1] = m->h_nrm[2 * n + 1];
-        for (int e = 2; e < d.M * 2; ++e) o[e] = m->h_tab[(size_t)s * d.M * 2 + e];
+    for (int g = 0; g < gn; ++g) {
+        b->path_valid[g0 + g] = 1;
+        for (int n = 0; n < N; ++n) {
+            int s = b->h_path[(size_t)(g0 + g) * N + n];
+            int64_t* o = cn + ((size_t)g * N + n) * d.M * 2;
+            o[0] = b->h_nrm[2 * n];
+            o[1] = b->h_nrm[2 * n + 1];
+            for (int e = 2; e < d.M * 2; ++e) o[e] = b->h_tab[(size_t)s * d.M * 2 + e];
+        }
     }
     return RMX_OK;
 }
 
 int rmx_calculate_log_transmat(rmx_handle m, double* out) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    // calculate_log_transmat(out) evaluates with the CURRENT p_breakpoint / transition_model
-    // (bpmodel.pyx:640); borrow the `used` slot's scratch tables without disturbing its snapshot.
-    const RmxDims& d = m->d;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    if (m->gn != 1) return m->fail(RMX_ERR_ARG, "calculate_log_transmat works on a single-fit handle");
+    // calculate_log_transmat(out) evaluates with the CURRENT p_breakpoint / transition_model (bpmodel.pyx:640),
+    // without disturbing the `used` / `cached` snapshots
+    const RmxDims& d = b->d;
+    const int g = m->g0, tm = b->tm[g];
     if (d.N <= 1) return RMX_OK;
-    size_t rmd = (size_t)m->R * d.M * d.D;
     double *pd = nullptr, *we = nullptr;
-    CK(cudaMalloc((void**)&pd, (rmd ? rmd : 1) * sizeof(double)));
-    CK(cudaMalloc((void**)&we, (rmd ? rmd : 1) * sizeof(double)));
-    int rc = ensure_mats(m, m->tm, m->pen);
+    CK(cudaMalloc((void**)&pd, (size_t)b->rmd * sizeof(double)));
+    CK(cudaMalloc((void**)&we, (size_t)b->rmd * sizeof(double)));
+    int rc = ensure_mats(m, tm);
     if (rc == RMX_OK) {
-        rmx_launch_prep_brk(m->stream, d, m->R, m->brk_rows, m->bidx, m->borient, m->brk, m->p_brk, m->pen, m->tm, pd, we);
-        RmxTransSpec s;
-        ClassMats& cm = m->mats[m->tm];
-        s.pd = pd; s.wexp = we; s.Tmat = cm.Tmat; s.Emat = cm.Emat; s.flipc = cm.flipc; s.flipE = cm.flipE;
-        s.pen = m->pen; s.tm = m->tm;
+        // fit_stride 0 with the fit's own p_breakpoint slice: kernel indexes p_brk by absolute fit, tables by stride
+        rmx_launch_prep_brk(b->stream, d, g, 1, b->R, b->brk_rows, b->bidx, b->borient, b->brk, b->p_brk, b->pen, tm, 0,
+                            pd - 0, we - 0);
+        RmxTransSpec s = spec_of(b, false, tm);
+        s.pd = pd;
+        s.wexp = we;
         const int64_t SS = (int64_t)d.S * d.S, nrows = d.N - 1;
         int64_t chunk = (int64_t)(64 << 20) / (SS * 8);
         if (chunk < 1) chunk = 1;
@@ -1138,15 +1436,15 @@ int rmx_calculate_log_transmat(rmx_handle m, double* out) {
         if (e != cudaSuccess) rc = m->fail(RMX_ERR_CUDA, cudaGetErrorString(e));
         for (int64_t r0 = 0; r0 < nrows && rc == RMX_OK; r0 += chunk) {
             int64_t nr = nrows - r0 < chunk ? nrows - r0 : chunk;
-            rmx_launch_materialize_T(m->stream, tables(m), d, rowsof(m), s, r0, nr, buf);
-            m->count();
-            e = cudaMemcpyAsync(out + r0 * SS, buf, (size_t)(nr * SS) * sizeof(double), cudaMemcpyDeviceToHost, m->stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+            rmx_launch_materialize_T(b->stream, tables(b), d, rowsof(b), s, r0, nr, buf);
+            b->count();
+            e = cudaMemcpyAsync(out + r0 * SS, buf, (size_t)(nr * SS) * sizeof(double), cudaMemcpyDeviceToHost, b->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
             if (e != cudaSuccess) rc = m->fail(RMX_ERR_CUDA, cudaGetErrorString(e));
         }
         if (buf) cudaFree(buf);
     }
-    cudaStreamSynchronize(m->stream);
+    cudaStreamSynchronize(b->stream);
     cudaFree(pd);
     cudaFree(we);
     return rc;
@@ -1154,17 +1452,23 @@ int rmx_calculate_log_transmat(rmx_handle m, double* out) {
 
 int rmx_eval(rmx_handle m, int what, int n, int s, int u, int v, int w, double* out) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
-    const RmxDims& d = m->d;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const RmxDims& d = b->d;
+    if (m->gn != 1) return m->fail(RMX_ERR_ARG, "the per-(n,s) accessors work on a single-fit handle");
     if (n < 0 || n >= d.N || s < 0 || s >= d.S || u < 0 || u > 1 || v < 0 || v > 1 || w < 0 || w > 1)
         return m->fail(RMX_ERR_ARG, "index out of range");
     if (what < 0 || what > 8) return m->fail(RMX_ERR_ARG, "unknown eval id");
-    rmx_launch_eval(m->stream, tables(m), d, m->P, what, n, s, u, v, w, m->evalbuf, m->dflags);
-    m->count();
-    CK(cudaMemcpyAsync(m->hp + 32, m->evalbuf, RMX_MAXM * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-    int rc = sync_check(m);
+    int rc = push_params(m);
     if (rc) return rc;
-    for (int k = 0; k < RMX_MAXM; ++k) out[k] = m->hp[32 + k];
+    rmx_launch_eval(b->stream, tables(b), d, b->dP, m->g0, what, n, s, u, v, w, b->evalbuf, b->dflags);
+    b->count();
+    double* hp = b->hp + (size_t)m->g0 * Batch::RED + 32;
+    CK(cudaMemcpyAsync(hp, b->evalbuf, RMX_MAXM * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+    rc = sync_check(m);
+    if (rc) return rc;
+    for (int k = 0; k < RMX_MAXM; ++k) out[k] = hp[k];
     return RMX_OK;
 }
 
@@ -1251,7 +1555,7 @@ int rmx_max_product(int device, int64_t N, int64_t S, const double* F, const dou
 // ---- instrumentation
 int rmx_launch_count(rmx_handle m, int64_t* count) {
     if (!m) return RMX_ERR_ARG;
-    *count = m->launches;
+    *count = m->b->launches;
     return RMX_OK;
 }
 int rmx_global_launch_count(int64_t* count) {
@@ -1260,35 +1564,38 @@ int rmx_global_launch_count(int64_t* count) {
 }
 int rmx_chain_timing(rmx_handle m, int enable, double* total_ms, int64_t* launches) {
     if (!m) return RMX_ERR_ARG;
-    if (total_ms) *total_ms = m->chain_ms;
-    if (launches) *launches = m->chain_launches;
-    m->chain_ms = 0.;
-    m->chain_launches = 0;
-    m->timing = enable != 0;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    if (total_ms) *total_ms = b->chain_ms;
+    if (launches) *launches = b->chain_launches;
+    b->chain_ms = 0.;
+    b->chain_launches = 0;
+    b->timing = enable != 0;
     return RMX_OK;
 }
 int rmx_synchronize(rmx_handle m) {
     if (!m) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Lock lk(m->b->mu);
+    cudaSetDevice(m->b->device);
     return sync_check(m);
 }
 int rmx_stream(rmx_handle m, void** stream) {
     if (!m) return RMX_ERR_ARG;
-    *stream = (void*)m->stream;
+    *stream = (void*)m->b->stream;
     return RMX_OK;
 }
-
 int rmx_event_record(rmx_handle m, int slot) {
     if (!m || slot < 0 || slot >= 16) return RMX_ERR_ARG;
-    cudaSetDevice(m->device);
+    Lock lk(m->b->mu);
+    cudaSetDevice(m->b->device);
     if (!m->ev[slot]) CK(cudaEventCreate(&m->ev[slot]));
-    CK(cudaEventRecord(m->ev[slot], m->stream));
+    CK(cudaEventRecord(m->ev[slot], m->b->stream));
     return RMX_OK;
 }
 int rmx_event_elapsed(rmx_handle m, int slot0, rmx_handle m1, int slot1, double* ms) {
     if (!m || !m1 || slot0 < 0 || slot0 >= 16 || slot1 < 0 || slot1 >= 16) return RMX_ERR_ARG;
     if (!m->ev[slot0] || !m1->ev[slot1]) return m->fail(RMX_ERR_ARG, "event was never recorded");
-    cudaSetDevice(m->device);
+    cudaSetDevice(m->b->device);
     CK(cudaEventSynchronize(m->ev[slot0]));
     CK(cudaEventSynchronize(m1->ev[slot1]));
     float f = 0.f;

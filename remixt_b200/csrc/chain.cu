@@ -1,9 +1,9 @@
-// Chain kernels: the structured part of the variational update.
+// Chain kernels: the structured part of the variational update, batched over the fits of a grid.
 //
 //   k_build_class  : the S x S log-transition matrix of "plain" rows, exp'd once     (bpmodel.pyx:640-684)
 //   k_prep_brk     : per-breakend-row expected transition tables under p_breakpoint  (bpmodel.pyx:658-664)
-//   k_chain        : forward / backward sum-product messages, one CTA per chromosome
-//                    chain and direction, in the scaled probability domain            (bpmodel.pyx:1213-1246)
+//   k_chain        : forward / backward sum-product messages; one CTA per (chromosome chain,
+//                    direction, tile of GT fits), in the scaled probability domain    (bpmodel.pyx:1213-1246)
 //   k_post         : posterior marginals                                              (bpmodel.pyx:948-950)
 //   k_hist         : joint-marginal histograms by total-copy difference at breakend
 //                    rows                                                             (bpmodel.pyx:619-633, 954-960)
@@ -13,10 +13,12 @@
 //
 // The reference materialises three (N-1,S,S) arrays; nothing here does.  A log-domain message
 //   alpha[n,j] = LSE_i(alpha[n-1,i] + T[i,j]) + F[n,j]
-// is evaluated as a scaled matrix-vector product  a_n = (a_{n-1}^T E) .* f_n / c_n  with
-// E = exp(T) held in registers across the whole chain, f_n = exp(F[n]-max F[n]); the chain's
-// log normaliser is sum_n (log c_n + max F[n]).  Chromosomes are coupled only through telomere
-// rows whose log_transmat is identically zero, so chains are exactly independent.
+// is evaluated as a scaled matrix-vector product  u_n = ((u_{n-1} / s_{n-1})^T E) .* f_n  with
+// E = exp(T) held in registers across the whole chain, f_n = exp(F[n]-max F[n]), s_n = sum(u_n); the
+// chain's log normaliser is sum_n (log s_n + max F[n]).  Every fit of an initialisation grid has the same
+// E (it depends on the state table and the penalty only), so one CTA advances GT fits in lock step and
+// each E entry loaded into a register is used GT times per step.  Chromosomes are coupled only through
+// telomere rows whose log_transmat is identically zero, so chains are exactly independent.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -66,10 +68,14 @@ __global__ void __launch_bounds__(256) k_build_class(const int8_t* __restrict__ 
 }
 
 // pd[r][m][slot] = sum_b p_breakpoint[k,b] * f(d - orient*brk[b,m]), d = slot - doff (bpmodel.pyx:660-664)
-__global__ void k_prep_brk(RmxDims d, const int* __restrict__ brk_rows, const int* __restrict__ bidx,
+__global__ void k_prep_brk(RmxDims d, int g0, const int* __restrict__ brk_rows, const int* __restrict__ bidx,
                            const int* __restrict__ borient, const int8_t* __restrict__ brk,
-                           const double* __restrict__ p_brk, double pen, int tm, double* __restrict__ pd,
-                           double* __restrict__ wexp) {
+                           const double* __restrict__ p_brk_all, double pen, int tm, int64_t fit_stride,
+                           double* __restrict__ pd_all, double* __restrict__ wexp_all) {
+    const int g = RMX_FIT();
+    const double* p_brk = p_brk_all + (int64_t)g * d.K * d.B;
+    double* pd = pd_all + (int64_t)g * fit_stride;
+    double* wexp = wexp_all + (int64_t)g * fit_stride;
     int r = blockIdx.x;
     int n = brk_rows[r];
     int k = bidx[n], o = borient[n];
@@ -103,176 +109,267 @@ __device__ __forceinline__ double brk_E(const double* __restrict__ wr, const int
     return e;
 }
 
+
 // ---------------------------------------------------------------------------------------------
-// K2: forward / backward messages.  grid = (chains, 2); thread t -> (column j = t % S, slice q = t / S);
-// slice q owns input indices [q*RR, (q+1)*RR).  REG: the thread's RR entries of E live in registers for
-// the whole chain (reloaded only when the row's transition class changes, which is rare); otherwise E is
-// streamed from L2 each step.  Shared memory: vec[2][Sp] (double buffered message), part[Q][Sp]
-// (slice partial sums), red[32], wtab[M*D] (breakend-row table), tots[S*M] (int8 totals).
+// K2: forward / backward messages for GT fits in lock step.
+//
+// grid.x = ((chain_rank * 2 + dir) * ntiles + tile): chains are ranked longest first so the long
+// sequential jobs start first.  Thread t -> (column group jg = t % NJ, row slice q = t / NJ); the
+// thread owns the RR x CW tile E[q*RR .. q*RR+RR) x [jg*CW .. jg*CW+CW) of the transition matrix, in
+// registers for the whole chain (REG) or streamed from L2 every step (!REG, large state spaces).
+//
+// Per step, for every fit g of the tile:  acc[g][c] = sum_k u[g][i0+k] * E[i0+k][j0+c]   (main loop),
+// partial sums of the Q row slices are combined through shared memory, multiplied by 1/s_prev[g]
+// (the LAGGED normaliser: the sum of the previous message, reduced while the main loop runs) and by
+// f_n; the new message goes to shared memory (next step's input) and to HBM (ahat / bhat).
+// Messages are stored un-normalised by their own sum; every consumer normalises (k_post, pair
+// weights), and logZ accumulates log s_n.
+//
+// shared: u[2][GT][Sp] | part[Q][GT][CW][NJ] | red[2][GT][NCH] | wtab[GT][M*D] | tots[S*M] (int8)
 // ---------------------------------------------------------------------------------------------
-template <int RR, bool REG>
-__global__ void __launch_bounds__(REG ? 512 : 1024)
-k_chain(RmxDims d, RmxChains ch, RmxRows rows, RmxTransSpec sp, const int8_t* __restrict__ tab, int Q, int rr_rt,
-        const double* __restrict__ fexp, const double* __restrict__ mF, double* __restrict__ ahat,
-        double* __restrict__ bhat, double* __restrict__ cnorm, double* __restrict__ chain_logz,
-        int* __restrict__ dflags) {
+struct ChainArgs {
+    RmxDims d;
+    RmxChains ch;
+    RmxRows rows;
+    RmxTransSpec sp;       // pd / wexp are per fit: fit stride sp_fit_stride
+    int64_t sp_fit_stride;
+    const int8_t* tab;
+    int g0, gn;            // fits of this launch
+    int ntiles;
+    int Q, NJ, rr;         // thread layout (rr = rows per slice; == RR when REG)
+    const double* fexp;    // (G,N,S)
+    const double* mF;      // (G,N)
+    double* ahat;          // (G,N,S)
+    double* bhat;          // (G,N,S)
+    double* chain_logz;    // (G,NC)
+    int* dflags;
+};
+
+template <int RR, int CW, int GT, bool REG>
+__global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int S = d.S, M = d.M;
-    const int rr = REG ? RR : rr_rt;
-    const int Sp = Q * rr;
-    double* vec = reinterpret_cast<double*>(smem_raw);   // [2][Sp]
-    double* part = vec + 2 * Sp;                          // [Q][Sp]
-    double* red = part + Q * Sp;                          // [32]
-    double* wtab = red + 32;                              // [M*D]
-    int8_t* tots = reinterpret_cast<int8_t*>(wtab + M * d.D);   // [S*M]
+    const RmxDims& d = A.d;
+    const int S = d.S, M = d.M, Q = A.Q, NJ = A.NJ;
+    const int rr = REG ? RR : A.rr;
+    const int Sp = Q * rr;                 // padded number of rows (>= S)
+    const int SJ = (S + 31) & ~31;         // epilogue slots per fit
+    const int NCH = SJ >> 5;               // warps (chunks) per fit in the epilogue
+    double* u = reinterpret_cast<double*>(smem_raw);        // [2][GT][Sp]
+    double* part = u + 2 * GT * Sp;                          // [Q][GT][CW][NJ]
+    double* red = part + Q * GT * CW * NJ;                   // [2][GT][NCH]
+    double* wtab = red + 2 * GT * NCH;                       // [GT][M*D]
+    int8_t* tots = reinterpret_cast<int8_t*>(wtab + GT * M * d.D);   // [S*M]
 
-    const int chain = blockIdx.x, dir = blockIdx.y;
-    const int s0 = ch.start[chain], s1 = ch.end[chain];
+    const int tile = blockIdx.x % A.ntiles;
+    const int cd = blockIdx.x / A.ntiles;
+    const int dir = cd & 1, chain = A.ch.order[cd >> 1];
+    const int s0 = A.ch.start[chain], s1 = A.ch.end[chain];
     const int t = threadIdx.x;
-    const int j = t % S, q = t / S;
+    const int jg = t % NJ, q = t / NJ;
     const bool act = q < Q;
-    const int i0 = act ? q * rr : 0;
-    const int lane = t & 31, wid = t >> 5;
-    const int nwS = (S + 31) >> 5;   // warps that hold the S output lanes (t < S)
+    const int i0 = q * rr, j0 = jg * CW;
+    const int lane = t & 31;
     const int64_t SS = (int64_t)S * S;
+    const int64_t NS = (int64_t)d.N * S;
+    const int gbase = A.g0 + tile * GT;                      // first fit of the tile
+    const int gcount = min(GT, A.g0 + A.gn - gbase);         // live fits in the tile
 
-    for (int e = t; e < 2 * Sp; e += blockDim.x) vec[e] = 0.;
+    for (int e = t; e < 2 * GT * Sp; e += blockDim.x) u[e] = 0.;
+    for (int e = t; e < 2 * GT * NCH; e += blockDim.x) red[e] = 0.;
     for (int e = t; e < S * M; e += blockDim.x) {
         int s = e / M, m = e - s * M;
-        tots[e] = (m == 0) ? 0 : (int8_t)(tab[(s * M + m) * 2] + tab[(s * M + m) * 2 + 1]);
+        tots[e] = (m == 0) ? 0 : (int8_t)(A.tab[(s * M + m) * 2] + A.tab[(s * M + m) * 2 + 1]);
     }
     __syncthreads();
 
-    double ereg[REG ? RR : 1];
-    int cur_class = -1;
-    int cur = 0;
-    double logz = 0.;
-    int bad = 0;
-
-    // ---- first segment of the sweep
+    // ---- first segment of the sweep: u = f (forward) or u = f, bhat = 1 (backward)
     {
-        double v = 0.;
-        if (dir == 0) {
-            if (t < S) v = fexp[(int64_t)s0 * S + t];
+        const int n = dir == 0 ? s0 : s1;
+        for (int slot = t; slot < GT * SJ; slot += blockDim.x) {
+            const int g = slot / SJ, j = slot - g * SJ;
+            double v = 0.;
+            if (j < S && g < gcount) {
+                const int64_t o = (int64_t)(gbase + g) * NS + (int64_t)n * S + j;
+                v = A.fexp[o];
+                if (dir == 0) A.ahat[o] = v; else A.bhat[o] = 1.;
+                u[g * Sp + j] = v;
+            }
             double w = warp_sum(v);
-            if (lane == 0 && wid < 32) red[wid] = w;
-            __syncthreads();
-            double c = 0.;
-            for (int w2 = 0; w2 < nwS; ++w2) c += red[w2];
-            if (t < S) {
-                double a = v / c;
-                ahat[(int64_t)s0 * S + t] = a;
-                vec[t] = a;
-            }
-            if (t == 0) {
-                cnorm[s0] = c;
-                logz = log(c) + mF[s0];
-                if (!(c > 0.)) bad = 1;
-            }
-        } else {
-            if (t < S) {
-                bhat[(int64_t)s1 * S + t] = 1.;
-                vec[t] = fexp[(int64_t)s1 * S + t];
-            }
+            if (lane == 0) red[g * NCH + (j >> 5)] = w;
         }
         __syncthreads();
     }
+
+    double ereg[REG ? RR : 1][REG ? CW : 1];
+    int cur_class = -1;
+    int cur = 0;
+    double logz = 0.;     // thread g < GT of warp 0 accumulates fit g's log normaliser
+    int bad = 0;
 
     const int nsteps = s1 - s0;
     for (int step = 0; step < nsteps; ++step) {
         const int n = dir == 0 ? s0 + 1 + step : s1 - 1 - step;   // segment being produced
         const int row = dir == 0 ? n - 1 : n;                     // transition row n -> n+1
-        const int cls = rows.tclass[row];
-        const int br = rows.brow[row];
-        double fn = (t < S) ? fexp[(int64_t)n * S + t] : 0.;      // issued early, used in the epilogue
-        const double* vin = vec + cur * Sp;
-        double acc0 = 0., acc1 = 0.;
+        const int prev = dir == 0 ? n - 1 : n + 1;                // segment whose message is the input
+        const int cls = A.rows.tclass[row];
+        const int br = A.rows.brow[row];
+        const double* uin = u + cur * GT * Sp;
+
+        // this step's f, fetched early (used in the epilogue)
+        double fpre[3];
+#pragma unroll
+        for (int e = 0; e < 3; ++e) {
+            const int slot = t + e * blockDim.x;
+            const int g = slot / SJ, j = slot - g * SJ;
+            fpre[e] = (slot < GT * SJ && j < S && g < gcount) ? A.fexp[(int64_t)(gbase + g) * NS + (int64_t)n * S + j] : 0.;
+        }
+
+        double acc[GT][CW];
+#pragma unroll
+        for (int g = 0; g < GT; ++g)
+#pragma unroll
+            for (int c = 0; c < CW; ++c) acc[g][c] = 0.;
+
         if (br < 0) {
+            const double* E = A.sp.Emat + (int64_t)cls * SS;   // symmetric: E[i][j] == E[j][i]
             if (REG) {
                 if (cls != cur_class) {
-                    const double* E = sp.Emat + (int64_t)cls * SS;   // symmetric: E[i][j] == E[j][i]
 #pragma unroll
-                    for (int k = 0; k < RR; ++k) {
-                        int i = i0 + k;
-                        ereg[REG ? k : 0] = (act && i < S) ? E[(int64_t)i * S + j] : 0.;
-                    }
+                    for (int k = 0; k < RR; ++k)
+#pragma unroll
+                        for (int c = 0; c < CW; ++c) {
+                            const int i = i0 + k, j = j0 + c;
+                            ereg[REG ? k : 0][REG ? c : 0] = (act && i < S && j < S) ? E[(int64_t)i * S + j] : 0.;
+                        }
                     cur_class = cls;
                 }
 #pragma unroll
-                for (int k = 0; k < RR; k += 2) {
-                    acc0 = fma(vin[i0 + k], ereg[REG ? k : 0], acc0);
-                    if (k + 1 < RR) acc1 = fma(vin[i0 + k + 1], ereg[REG ? k + 1 : 0], acc1);
+                for (int k = 0; k < RR; ++k) {
+                    double v[GT];
+#pragma unroll
+                    for (int g = 0; g < GT; ++g) v[g] = uin[g * Sp + i0 + k];
+#pragma unroll
+                    for (int g = 0; g < GT; ++g)
+#pragma unroll
+                        for (int c = 0; c < CW; ++c) acc[g][c] = fma(v[g], ereg[REG ? k : 0][REG ? c : 0], acc[g][c]);
                 }
             } else if (act) {
-                const double* E = sp.Emat + (int64_t)cls * SS;
-                int kmax = min(rr, S - i0);
-                for (int k = 0; k < kmax; ++k) acc0 = fma(vin[i0 + k], E[(int64_t)(i0 + k) * S + j], acc0);
+                const int kmax = min(rr, S - i0);
+                for (int k = 0; k < kmax; ++k) {
+                    double e[CW];
+#pragma unroll
+                    for (int c = 0; c < CW; ++c) e[c] = (j0 + c < S) ? E[(int64_t)(i0 + k) * S + j0 + c] : 0.;
+#pragma unroll
+                    for (int g = 0; g < GT; ++g) {
+                        const double v = uin[g * Sp + i0 + k];
+#pragma unroll
+                        for (int c = 0; c < CW; ++c) acc[g][c] = fma(v, e[c], acc[g][c]);
+                    }
+                }
             }
         } else {
-            // breakend row: E_n[i][jj] = flipE[cls][i][jj] * prod_m wexp[r][m][tot_i - tot_jj]
-            for (int e = t; e < M * d.D; e += blockDim.x) wtab[e] = sp.wexp[(int64_t)br * M * d.D + e];
+            // breakend row: E_n[from][to] = flipE[cls][from][to] * prod_m wexp[g][r][m][tot_from - tot_to], per fit
+            for (int e = t; e < GT * M * d.D; e += blockDim.x) {
+                const int g = e / (M * d.D), o = e - g * (M * d.D);
+                const int gg = gbase + min(g, gcount - 1);
+                wtab[e] = A.sp.wexp[(int64_t)gg * A.sp_fit_stride + (int64_t)br * M * d.D + o];
+            }
             __syncthreads();
             if (act) {
-                const double* FE = sp.flipE + (int64_t)cls * SS;
-                const int d0 = rows.d0[row];
-                int kmax = min(rr, S - i0);
+                const double* FE = A.sp.flipE + (int64_t)cls * SS;
+                const int d0 = A.rows.d0[row];
+                const int kmax = min(rr, S - i0);
                 for (int k = 0; k < kmax; ++k) {
-                    int o = i0 + k;
-                    // forward: from-state o, to-state j ; backward: from-state j, to-state o
-                    double e = dir == 0 ? brk_E(wtab, tots, M, d.D, d.doff, d0, o, j, FE[(int64_t)o * S + j])
-                                        : brk_E(wtab, tots, M, d.D, d.doff, d0, j, o, FE[(int64_t)o * S + j]);
-                    acc0 = fma(vin[o], e, acc0);
+                    const int ir = i0 + k;
+#pragma unroll
+                    for (int c = 0; c < CW; ++c) {
+                        const int jc = j0 + c;
+                        if (jc < S) {
+                            const double fe = FE[(int64_t)ir * S + jc];
+#pragma unroll
+                            for (int g = 0; g < GT; ++g) {
+                                const double* wt = wtab + g * M * d.D;
+                                // forward: from-state ir (summed), to-state jc; backward: from-state jc, to-state ir
+                                const double e = dir == 0 ? brk_E(wt, tots, M, d.D, d.doff, d0, ir, jc, fe)
+                                                          : brk_E(wt, tots, M, d.D, d.doff, d0, jc, ir, fe);
+                                acc[g][c] = fma(uin[g * Sp + ir], e, acc[g][c]);
+                            }
+                        }
+                    }
                 }
             }
         }
-        if (act) part[q * Sp + j] = acc0 + acc1;
-        __syncthreads();
-        double v = 0.;
-        if (t < S) {
-            for (int qq = 0; qq < Q; ++qq) v += part[qq * Sp + t];
-            if (dir == 0) v *= fn;
-        }
-        {
-            double w = warp_sum(v);
-            if (lane == 0 && wid < nwS) red[wid] = w;
+        if (act) {
+#pragma unroll
+            for (int g = 0; g < GT; ++g)
+#pragma unroll
+                for (int c = 0; c < CW; ++c) part[((q * GT + g) * CW + c) * NJ + jg] = acc[g][c];
         }
         __syncthreads();
-        double c = 0.;
-        for (int w2 = 0; w2 < nwS; ++w2) c += red[w2];
-        double* vout = vec + (cur ^ 1) * Sp;
-        if (t < S) {
-            double o = v / c;
-            if (dir == 0) {
-                ahat[(int64_t)n * S + t] = o;
-                vout[t] = o;
-            } else {
-                bhat[(int64_t)n * S + t] = o;
-                vout[t] = o * fn;
+
+        // ---- epilogue: slot -> (fit g, column j), consecutive j per lane
+        double* uout = u + (cur ^ 1) * GT * Sp;
+        const double* redp = red + cur * GT * NCH;
+        double* redn = red + (cur ^ 1) * GT * NCH;
+#pragma unroll
+        for (int e = 0; e < 3; ++e) {
+            const int slot = t + e * blockDim.x;
+            if (slot < GT * SJ) {                                  // warp-uniform: GT*SJ is a multiple of 32
+                const int g = slot / SJ, j = slot - g * SJ;
+                double sprev = 0.;
+                for (int c2 = 0; c2 < NCH; ++c2) sprev += redp[g * NCH + c2];
+                double v = 0., un = 0.;
+                if (j < S && g < gcount) {
+                    const int c = j % CW, jj = j / CW;
+                    double a = 0.;
+                    for (int qq = 0; qq < Q; ++qq) a += part[((qq * GT + g) * CW + c) * NJ + jj];
+                    v = a / sprev;
+                    const int64_t o = (int64_t)(gbase + g) * NS + (int64_t)n * S + j;
+                    if (dir == 0) {
+                        v *= fpre[e];
+                        un = v;
+                        A.ahat[o] = v;
+                    } else {
+                        un = v * fpre[e];
+                        A.bhat[o] = v;
+                    }
+                    uout[g * Sp + j] = un;
+                }
+                const double w = warp_sum(un);
+                if (lane == 0) redn[g * NCH + (j >> 5)] = w;
+                if (j == 0 && g < gcount) {
+                    // s_prev is the sum of the message of segment `prev`: log normaliser of the forward sweep
+                    if (dir == 0) logz += log(sprev) + A.mF[(int64_t)(gbase + g) * d.N + prev];
+                    if (!(sprev > 0.) || isinf(sprev)) bad = 1;
+                }
             }
-        }
-        if (t == 0) {
-            if (dir == 0) {
-                cnorm[n] = c;
-                logz += log(c) + mF[n];
-            }
-            if (!(c > 0.) || isinf(c)) bad = 1;
         }
         cur ^= 1;
         __syncthreads();
     }
-    if (t == 0) {
-        if (dir == 0) chain_logz[chain] = logz;
-        if (bad || isnan(logz)) atomicOr(dflags, RMX_F_MSG_NAN);
+    // the last message's own sum closes the forward log normaliser
+    for (int slot = t; slot < GT * SJ; slot += blockDim.x) {
+        const int g = slot / SJ, j = slot - g * SJ;
+        if (j == 0 && g < gcount) {
+            double slast = 0.;
+            for (int c2 = 0; c2 < NCH; ++c2) slast += red[cur * GT * NCH + g * NCH + c2];
+            const int last = dir == 0 ? s1 : s0;
+            if (dir == 0) {
+                logz += log(slast) + A.mF[(int64_t)(gbase + g) * d.N + last];
+                A.chain_logz[(int64_t)(gbase + g) * A.ch.NC + chain] = logz;
+            }
+            if (!(slast > 0.) || isinf(slast) || isnan(logz)) bad = 1;
+            if (bad) atomicOr(A.dflags, RMX_F_MSG_NAN);
+        }
     }
 }
-
-// posterior marginals: post[n] = normalise(ahat[n] .* bhat[n]); zp[n] = the normaliser
-__global__ void __launch_bounds__(256) k_post(RmxDims d, const double* __restrict__ ahat, const double* __restrict__ bhat,
-                                              double* __restrict__ post, double* __restrict__ zp,
+// posterior marginals: post[g,n] = normalise(ahat[g,n] .* bhat[g,n]), one warp per (fit, segment)
+__global__ void __launch_bounds__(256) k_post(RmxDims d, int g0, const double* __restrict__ ahat,
+                                              const double* __restrict__ bhat, double* __restrict__ post,
                                               int* __restrict__ dflags) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= d.N) return;
-    int64_t base = (int64_t)warp * d.S;
+    int64_t base = ((int64_t)RMX_FIT() * d.N + warp) * d.S;
     double z = 0.;
     for (int s = lane; s < d.S; s += 32) z += ahat[base + s] * bhat[base + s];
     z = warp_sum(z);
@@ -282,7 +379,6 @@ __global__ void __launch_bounds__(256) k_post(RmxDims d, const double* __restric
         post[base + s] = p;
         bad |= isnan(p);
     }
-    if (lane == 0) zp[warp] = z;
     if (bad) atomicOr(dflags, RMX_F_POST_NAN);
 }
 
@@ -310,6 +406,7 @@ __device__ __forceinline__ double pair_w(const PairCtx& c, const RmxDims& d, int
 __device__ __forceinline__ void pair_setup(PairCtx& c, unsigned char* smem_raw, const RmxDims& d, const RmxRows& rows,
                                            const RmxTransSpec& sp, const int8_t* tab, int uniform, int n,
                                            const double* ahat, const double* bhat, const double* fexp) {
+    // ahat / bhat / fexp and sp.pd / sp.wexp point at the fit's own slice
     const int S = d.S, M = d.M;
     double* a = reinterpret_cast<double*>(smem_raw);
     double* g = a + S;
@@ -360,10 +457,17 @@ __device__ __forceinline__ double block_sum_all(double v, double* red) {
 // K-hist: per breakend row r and clone m, hist[r][m][slot] = sum_{ij: tot_i[m]-tot_j[m] = d} joint[n,i,j]
 // (bpmodel.pyx:628-633).  Accumulated in 2^-62 fixed point with integer shared-memory atomics so the
 // result does not depend on the order in which threads arrive.
-__global__ void __launch_bounds__(256) k_hist(RmxDims d, RmxRows rows, RmxTransSpec sp, const int8_t* __restrict__ tab,
-                                              int uniform, const double* __restrict__ ahat,
-                                              const double* __restrict__ bhat, const double* __restrict__ fexp,
-                                              double* __restrict__ hist, int* __restrict__ dflags) {
+__global__ void __launch_bounds__(256) k_hist(RmxDims d, int g0, RmxRows rows, RmxTransSpec sp, int64_t sp_fit_stride,
+                                              const int8_t* __restrict__ tab, int uniform,
+                                              const double* __restrict__ ahat_all, const double* __restrict__ bhat_all,
+                                              const double* __restrict__ fexp_all, double* __restrict__ hist_all,
+                                              int* __restrict__ dflags) {
+    const int g = RMX_FIT();
+    const int64_t NSo = (int64_t)g * d.N * d.S;
+    const double *ahat = ahat_all + NSo, *bhat = bhat_all + NSo, *fexp = fexp_all + NSo;
+    double* hist = hist_all + (int64_t)g * sp_fit_stride;
+    sp.pd += (int64_t)g * sp_fit_stride;
+    sp.wexp += (int64_t)g * sp_fit_stride;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double red[32];
     __shared__ unsigned long long hacc[RMX_MAXM * 64];
@@ -399,43 +503,56 @@ __global__ void __launch_bounds__(256) k_hist(RmxDims d, RmxRows rows, RmxTransS
         hist[(int64_t)r * M * d.D + e] = (double)hacc[e] * 2.168404344971008868e-19;   // 2^-62
 }
 
-// update_p_breakpoint (bpmodel.pyx:964-983): one thread per breakpoint, reference accumulation order.
-__global__ void k_brk_update(RmxDims d, const int* __restrict__ krow_ptr, const int* __restrict__ krow_idx,
-                             const int* __restrict__ brk_rows, const int* __restrict__ borient,
-                             const int8_t* __restrict__ brk, const double* __restrict__ hist, double pen, int tm,
-                             double* __restrict__ p_brk, double* __restrict__ logq_scratch) {
-    int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= d.K) return;
-    double* lq = logq_scratch + (int64_t)k * d.B;
-    for (int b = 0; b < d.B; ++b) lq[b] = 0.;
+// update_p_breakpoint (bpmodel.pyx:964-983): one CTA per (fit, breakpoint), one thread per breakpoint
+// state (B <= 64).  Each thread accumulates its log q in the reference's order (breakend rows ascending,
+// clones, copy-number differences); thread 0 then does the two sequential sums of _exp_normalize
+// (bpmodel.pyx:120-128) so the result does not depend on a reduction tree.
+__global__ void __launch_bounds__(64) k_brk_update(RmxDims d, int g0, const int* __restrict__ krow_ptr,
+                                                   const int* __restrict__ krow_idx, const int* __restrict__ brk_rows,
+                                                   const int* __restrict__ borient, const int8_t* __restrict__ brk,
+                                                   const double* __restrict__ hist_all, int64_t hist_fit_stride,
+                                                   double pen, int tm, double* __restrict__ p_brk_all) {
+    __shared__ double buf[64];
+    __shared__ double stat;
+    const int g = RMX_FIT();
+    const int k = blockIdx.x, b = threadIdx.x;
+    const double* hist = hist_all + (int64_t)g * hist_fit_stride;
+    double* p = p_brk_all + ((int64_t)g * d.K + k) * d.B;
     const double mult = -pen;
-    for (int e = krow_ptr[k]; e < krow_ptr[k + 1]; ++e) {
-        int r = krow_idx[e];
-        int o = borient[brk_rows[r]];
-        for (int m = 0; m < d.M; ++m) {
-            const double* h = hist + ((int64_t)r * d.M + m) * d.D;
-            for (int b = 0; b < d.B; ++b) {
-                double acc = lq[b];
-                int bs = brk[b * d.M + m];
+    double acc = 0.;
+    if (b < d.B) {
+        for (int e = krow_ptr[k]; e < krow_ptr[k + 1]; ++e) {
+            const int r = krow_idx[e];
+            const int o = borient[brk_rows[r]];
+            for (int m = 0; m < d.M; ++m) {
+                const double* h = hist + ((int64_t)r * d.M + m) * d.D;
+                const int bs = brk[b * d.M + m];
                 for (int slot = 0; slot < d.D; ++slot)
                     acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(mult, h[slot]), ftrans(slot - d.doff - o * bs, tm)));
-                lq[b] = acc;
             }
         }
+        buf[b] = acc;
     }
-    // _exp_normalize (bpmodel.pyx:120-128)
-    double mx = -INFINITY;
-    for (int b = 0; b < d.B; ++b) if (lq[b] > mx) mx = lq[b];
-    double ps = 0.;
-    for (int b = 0; b < d.B; ++b) ps += exp(lq[b] - mx);
-    double lse = log(ps) + mx;
-    double z = 0.;
-    double* p = p_brk + (int64_t)k * d.B;
-    for (int b = 0; b < d.B; ++b) {
-        p[b] = exp(lq[b] - lse);
-        z += p[b];
+    __syncthreads();
+    if (b == 0) {
+        double mx = -INFINITY;
+        for (int i = 0; i < d.B; ++i) if (buf[i] > mx) mx = buf[i];
+        double ps = 0.;
+        for (int i = 0; i < d.B; ++i) ps += exp(buf[i] - mx);
+        stat = log(ps) + mx;
     }
-    for (int b = 0; b < d.B; ++b) p[b] /= z;
+    __syncthreads();
+    const double e = b < d.B ? exp(acc - stat) : 0.;
+    __syncthreads();
+    if (b < d.B) buf[b] = e;
+    __syncthreads();
+    if (b == 0) {
+        double z = 0.;
+        for (int i = 0; i < d.B; ++i) z += buf[i];
+        stat = z;
+    }
+    __syncthreads();
+    if (b < d.B) p[b] = e / stat;
 }
 
 // exact log transition T_spec[n,i,j] for pair sums / materialisation / Viterbi
@@ -476,22 +593,35 @@ __device__ __forceinline__ double logT(const LogTCtx& c, const RmxDims& d, int i
 }
 
 // rowsum[n] = sum_ij joint[n,i,j] * T_spec[n,i,j]; joint from (joint_sp, messages), T from t_sp.
-__global__ void __launch_bounds__(256) k_pairsum(RmxDims d, RmxRows rows, RmxTransSpec jsp, RmxTransSpec tsp,
-                                                 const int8_t* __restrict__ tab, int uniform,
-                                                 const double* __restrict__ ahat, const double* __restrict__ bhat,
-                                                 const double* __restrict__ fexp, double* __restrict__ rowsum) {
+// rowlist != nullptr: only those rows (the breakend rows), rowsum indexed by position in the list, and the
+// value is sum joint * (T_tsp - T_t2sp) -- the only rows where cached and used transitions differ.
+__global__ void __launch_bounds__(256) k_pairsum(RmxDims d, int g0, RmxRows rows, RmxTransSpec jsp, RmxTransSpec tsp,
+                                                 RmxTransSpec t2sp, int diff, int64_t sp_fit_stride,
+                                                 const int* __restrict__ rowlist, const int8_t* __restrict__ tab,
+                                                 int uniform, const double* __restrict__ ahat_all,
+                                                 const double* __restrict__ bhat_all, const double* __restrict__ fexp_all,
+                                                 double* __restrict__ rowsum_all, int64_t rowsum_fit_stride) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double red[32];
-    int n = blockIdx.x;
-    LogTCtx lt;
+    const int g = RMX_FIT();
+    const int64_t NSo = (int64_t)g * d.N * d.S;
+    const double *ahat = ahat_all + NSo, *bhat = bhat_all + NSo, *fexp = fexp_all + NSo;
+    double* rowsum = rowsum_all + (int64_t)g * rowsum_fit_stride;
+    jsp.pd += (int64_t)g * sp_fit_stride; jsp.wexp += (int64_t)g * sp_fit_stride;
+    tsp.pd += (int64_t)g * sp_fit_stride; tsp.wexp += (int64_t)g * sp_fit_stride;
+    t2sp.pd += (int64_t)g * sp_fit_stride; t2sp.wexp += (int64_t)g * sp_fit_stride;
+    const int n = rowlist ? rowlist[blockIdx.x] : blockIdx.x;
+    const int orow = blockIdx.x;
+    LogTCtx lt, lt2;
     // T of the row under t_sp; rows whose T is identically zero contribute nothing
     if (rows.tclass[n] < 0) {
-        if (threadIdx.x == 0) rowsum[n] = 0.;
+        if (threadIdx.x == 0) rowsum[orow] = 0.;
         return;
     }
     PairCtx c;
     pair_setup(c, smem_raw, d, rows, jsp, tab, uniform, n, ahat, bhat, fexp);
     logT_setup(lt, d, rows, tsp, c.tots, n);
+    logT_setup(lt2, d, rows, t2sp, c.tots, n);
     const int S = d.S;
     const int64_t SS = (int64_t)S * S;
     double z = 0., num = 0.;
@@ -499,11 +629,13 @@ __global__ void __launch_bounds__(256) k_pairsum(RmxDims d, RmxRows rows, RmxTra
         int i = (int)(idx / S), j = (int)(idx - (int64_t)i * S);
         double w = pair_w(c, d, i, j);
         z += w;
-        num += w * logT(lt, d, i, j);
+        double tv = logT(lt, d, i, j);
+        if (diff) tv -= logT(lt2, d, i, j);
+        num += w * tv;
     }
     z = block_sum_all(z, red);
     num = block_sum_all(num, red);
-    if (threadIdx.x == 0) rowsum[n] = num / z;
+    if (threadIdx.x == 0) rowsum[orow] = num / z;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -511,9 +643,16 @@ __global__ void __launch_bounds__(256) k_pairsum(RmxDims d, RmxRows rows, RmxTra
 // Telomere rows are all-zero so the lattice of a chain only differs from the reference's by an
 // additive constant; the traceback at a telomere is argmax of the lattice row itself.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, RmxChains ch, RmxRows rows, RmxTransSpec sp,
-                                                  const int8_t* __restrict__ tab, const double* __restrict__ F,
-                                                  double* __restrict__ lattice, int* __restrict__ path) {
+__global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, RmxChains ch, RmxRows rows, RmxTransSpec sp,
+                                                  int64_t sp_fit_stride, const int8_t* __restrict__ tab,
+                                                  const double* __restrict__ F_all, double* __restrict__ lattice_all,
+                                                  int* __restrict__ path_all) {
+    const int g = RMX_FIT();
+    const double* F = F_all + (int64_t)g * d.N * d.S;
+    double* lattice = lattice_all + (int64_t)blockIdx.y * d.N * d.S;    // scratch holds the launched fits only
+    int* path = path_all + (int64_t)g * d.N;
+    sp.pd += (int64_t)g * sp_fit_stride;
+    sp.wexp += (int64_t)g * sp_fit_stride;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double rv[32];
     __shared__ int ri[32];
@@ -805,97 +944,107 @@ void rmx_launch_build_class(cudaStream_t st, const RmxTables& T, const RmxDims& 
     k_build_class<<<grid, 256, 0, st>>>(T.tab, d.S, d.M, class_nrm, pen, tm, Tmat, Emat, flipc, flipE);
 }
 
-void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int R, const int* brk_rows, const int* bidx,
-                         const int* borient, const int8_t* brk, const double* p_brk, double pen, int tm, double* pd,
-                         double* wexp) {
-    if (R <= 0) return;
-    k_prep_brk<<<R, 64, 0, st>>>(d, brk_rows, bidx, borient, brk, p_brk, pen, tm, pd, wexp);
+void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int g0, int gn, int R, const int* brk_rows, const int* bidx,
+                         const int* borient, const int8_t* brk, const double* p_brk, double pen, int tm,
+                         int64_t fit_stride, double* pd, double* wexp) {
+    if (R <= 0 || gn <= 0) return;
+    k_prep_brk<<<dim3(R, gn), 64, 0, st>>>(d, g0, brk_rows, bidx, borient, brk, p_brk, pen, tm, fit_stride, pd, wexp);
 }
 
-template <int RR>
-static int launch_chain_reg(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch,
-                            const RmxRows& rows, const RmxTransSpec& sp, int Q, const double* fexp, const double* mF,
-                            double* ahat, double* bhat, double* cnorm, double* chain_logz, int* dflags) {
-    int Sp = Q * RR;
-    size_t smem = sizeof(double) * (2 * Sp + Q * Sp + 32 + d.M * d.D) + (size_t)d.S * d.M + 16;
-    int threads = ((d.S * Q + 31) / 32) * 32;
-    auto kern = k_chain<RR, true>;
+template <int RR, int CW, int GT, bool REG>
+static int launch_chain_cfg(cudaStream_t st, ChainArgs& A, int Q, int rr) {
+    const RmxDims& d = A.d;
+    const int NJ = (d.S + CW - 1) / CW;
+    A.Q = Q; A.NJ = NJ; A.rr = rr;
+    A.ntiles = (A.gn + GT - 1) / GT;
+    const int Sp = Q * rr, SJ = (d.S + 31) & ~31, NCH = SJ >> 5;
+    const int threads = ((Q * NJ + 31) / 32) * 32;
+    if (threads > (REG ? 256 : 512) || 3 * threads < GT * SJ) return 2;
+    size_t smem = sizeof(double) * ((size_t)2 * GT * Sp + (size_t)Q * GT * CW * NJ + 2 * GT * NCH + (size_t)GT * d.M * d.D) +
+                  (size_t)d.S * d.M + 16;
+    auto kern = k_chain<RR, CW, GT, REG>;
     if (smem > 48 * 1024) {
+        if (smem > 227 * 1024) return 2;
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;
     }
-    dim3 grid(ch.NC, 2);
-    kern<<<grid, threads, smem, st>>>(d, ch, rows, sp, T.tab, Q, RR, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
+    kern<<<A.ch.NC * 2 * A.ntiles, threads, smem, st>>>(A);
     return 0;
 }
 
-int rmx_launch_chain(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const RmxRows& rows,
-                     const RmxTransSpec& sp, const double* fexp, const double* mF, double* ahat, double* bhat,
-                     double* cnorm, double* chain_logz, int* dflags) {
-    if (ch.NC <= 0) return 0;
-    const int S = d.S;
-    if (S <= 16) return launch_chain_reg<4>(st, T, d, ch, rows, sp, 4, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
-    if (S <= 64) return launch_chain_reg<16>(st, T, d, ch, rows, sp, 4, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
-    if (S <= 100) return launch_chain_reg<25>(st, T, d, ch, rows, sp, 4, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
-    if (S <= 128) return launch_chain_reg<32>(st, T, d, ch, rows, sp, 4, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
-    // generic: E streamed from L2
-    int Q = 1024 / S;
-    if (Q < 1) Q = 1;
+template <int GT>
+static int launch_chain_gt(cudaStream_t st, ChainArgs& A) {
+    const int S = A.d.S;
+    if (S <= 16) return launch_chain_cfg<4, 4, GT, true>(st, A, 4, 4);
+    if (S <= 64) return launch_chain_cfg<8, 4, GT, true>(st, A, 8, 8);
+    if (S <= 104) return launch_chain_cfg<13, 4, GT, true>(st, A, 8, 13);
+    if (S <= 128) return launch_chain_cfg<16, 4, GT, true>(st, A, 8, 16);
+    // large state spaces: E streamed from L2 every step
+    const int NJ = (S + 3) / 4;
+    int Q = 512 / NJ;
     if (Q > 8) Q = 8;
-    int threads, rr;
-    if (S > 1024) return 2;   // would need a column loop; not a supported state-space size
-    rr = (S + Q - 1) / Q;
-    threads = ((S * Q + 31) / 32) * 32;
-    if (threads > 1024) { Q = 1024 / S; rr = (S + Q - 1) / Q; threads = ((S * Q + 31) / 32) * 32; }
-    int Sp = Q * rr;
-    size_t smem = sizeof(double) * (2 * Sp + Q * Sp + 32 + d.M * d.D) + (size_t)d.S * d.M + 16;
-    auto kern = k_chain<1, false>;
-    if (smem > 48 * 1024) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;
-    }
-    dim3 grid(ch.NC, 2);
-    kern<<<grid, threads, smem, st>>>(d, ch, rows, sp, T.tab, Q, rr, fexp, mF, ahat, bhat, cnorm, chain_logz, dflags);
-    return 0;
+    if (Q < 1) return 2;
+    const int rr = (S + Q - 1) / Q;
+    return launch_chain_cfg<1, 4, GT, false>(st, A, Q, rr);
 }
 
-void rmx_launch_post(cudaStream_t st, const RmxDims& d, const double* ahat, const double* bhat, double* post,
-                     double* zp, int* dflags) {
-    if (d.N <= 0) return;
-    k_post<<<cdiv64((int64_t)d.N * 32, 256), 256, 0, st>>>(d, ahat, bhat, post, zp, dflags);
+// returns 0 on success, 1 if the shared-memory configuration failed, 2 if the state space is unsupported
+int rmx_launch_chain(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const RmxRows& rows,
+                     const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp, const double* mF,
+                     double* ahat, double* bhat, double* chain_logz, int* dflags) {
+    if (ch.NC <= 0 || gn <= 0) return 0;
+    ChainArgs A;
+    A.d = d; A.ch = ch; A.rows = rows; A.sp = sp; A.sp_fit_stride = sp_fit_stride; A.tab = T.tab;
+    A.g0 = g0; A.gn = gn; A.fexp = fexp; A.mF = mF; A.ahat = ahat; A.bhat = bhat; A.chain_logz = chain_logz;
+    A.dflags = dflags;
+    const int SJ = (d.S + 31) & ~31;
+    if (gn >= 3 && SJ <= 256) return launch_chain_gt<4>(st, A);
+    if (gn >= 2 && SJ <= 512) return launch_chain_gt<2>(st, A);
+    return launch_chain_gt<1>(st, A);
+}
+
+void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* ahat, const double* bhat,
+                     double* post, int* dflags) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_post<<<dim3(cdiv64((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, ahat, bhat, post, dflags);
 }
 
 static size_t pair_smem(const RmxDims& d) {
     return sizeof(double) * (2 * (size_t)d.S + (size_t)d.M * d.D) + (size_t)d.S * d.M + 16;
 }
 
-void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int R, const RmxRows& rows,
-                     const RmxTransSpec& sp, int uniform, const double* ahat, const double* bhat, const double* fexp,
-                     double* hist, int* dflags) {
-    if (R <= 0) return;
-    k_hist<<<R, 256, pair_smem(d), st>>>(d, rows, sp, T.tab, uniform, ahat, bhat, fexp, hist, dflags);
+void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
+                     const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
+                     const double* fexp, double* hist, int* dflags) {
+    if (R <= 0 || gn <= 0) return;
+    k_hist<<<dim3(R, gn), 256, pair_smem(d), st>>>(d, g0, rows, sp, sp_fit_stride, T.tab, uniform, ahat, bhat, fexp, hist,
+                                                  dflags);
 }
 
-void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, const int* krow_ptr, const int* krow_idx,
-                           const int* brk_rows, const int* borient, const int8_t* brk, const double* hist, double pen,
-                           int tm, double* p_brk, double* logq_scratch) {
-    if (d.K <= 0) return;
-    k_brk_update<<<cdiv64(d.K, 64), 64, 0, st>>>(d, krow_ptr, krow_idx, brk_rows, borient, brk, hist, pen, tm, p_brk,
-                                                 logq_scratch);
+void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, int g0, int gn, const int* krow_ptr, const int* krow_idx,
+                           const int* brk_rows, const int* borient, const int8_t* brk, const double* hist,
+                           int64_t hist_fit_stride, double pen, int tm, double* p_brk) {
+    if (d.K <= 0 || gn <= 0) return;
+    k_brk_update<<<dim3(d.K, gn), 64, 0, st>>>(d, g0, krow_ptr, krow_idx, brk_rows, borient, brk, hist, hist_fit_stride,
+                                               pen, tm, p_brk);
 }
 
-void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
-                        const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, int uniform, const double* ahat,
-                        const double* bhat, const double* fexp, double* rowsum) {
-    if (d.N <= 1) return;
-    k_pairsum<<<d.N - 1, 256, pair_smem(d), st>>>(d, rows, joint_sp, t_sp, T.tab, uniform, ahat, bhat, fexp, rowsum);
+void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxRows& rows,
+                        const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, const RmxTransSpec& t2_sp, int diff,
+                        int64_t sp_fit_stride, const int* rowlist, int nrows, int uniform, const double* ahat,
+                        const double* bhat, const double* fexp, double* rowsum, int64_t rowsum_fit_stride) {
+    if (nrows <= 0 || gn <= 0) return;
+    k_pairsum<<<dim3(nrows, gn), 256, pair_smem(d), st>>>(d, g0, rows, joint_sp, t_sp, t2_sp, diff, sp_fit_stride, rowlist,
+                                                         T.tab, uniform, ahat, bhat, fexp, rowsum, rowsum_fit_stride);
 }
 
-void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch,
-                        const RmxRows& rows, const RmxTransSpec& sp, const double* F, double* lattice, int* path) {
-    if (ch.NC <= 0) return;
+void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
+                        const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
+                        double* lattice, int* path) {
+    if (ch.NC <= 0 || gn <= 0) return;
     int threads = ((d.S + 31) / 32) * 32;
     if (threads > 1024) threads = 1024;
     size_t smem = sizeof(double) * d.S + (size_t)d.S * d.M + 16;
-    k_viterbi<<<ch.NC, threads, smem, st>>>(d, ch, rows, sp, T.tab, F, lattice, path);
+    k_viterbi<<<dim3(ch.NC, gn), threads, smem, st>>>(d, g0, ch, rows, sp, sp_fit_stride, T.tab, F, lattice, path);
 }
 
 void rmx_launch_materialize_T(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,

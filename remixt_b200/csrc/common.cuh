@@ -44,7 +44,12 @@ struct RmxParams {
     int normal_contamination;
 };
 
-// Read-only per-model tables in HBM.
+// A launch covers the fits [g0, g0 + gridDim.y) of a batch; every per-fit array is laid out with the
+// fit index as its leading dimension.
+#define RMX_FIT() (g0 + (int)blockIdx.y)
+
+// Read-only tables in HBM, shared by every fit of a batch (the fits of an initialisation grid see the
+// same data and state space; only h, the dispersions, divergence_weight and the variational state differ).
 struct RmxTables {
     const int8_t* tab;      // (S,M,2) clone copy number per state; clone 0 row is zero
     const int8_t* nrm;      // (N,2)  normal copies per segment (cn_states[n,:,0,:])
@@ -53,8 +58,8 @@ struct RmxTables {
     const double* x;        // (N)
     const double* y0;       // (N)  y[:,0]
     const double* y1;       // (N)  y[:,1]
-    const uint8_t* tmask;   // (N)  total_likelihood_mask != 0
-    const uint8_t* amask;   // (N)  allele_likelihood_mask != 0
+    const uint8_t* tmask;   // (G,N)  total_likelihood_mask != 0   (per fit)
+    const uint8_t* amask;   // (G,N)  allele_likelihood_mask != 0  (per fit)
 };
 
 // ---------------------------------------------------------------------------------------------

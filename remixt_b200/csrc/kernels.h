@@ -10,8 +10,8 @@
 //   plain     : one of C class matrices Tmat[c]             (bpmodel.pyx:652-656, 670-684)
 //   breakend  : -pen*(sum_m pd[r][m][dtot_m] + flipc[c])    (bpmodel.pyx:658-668, 670-684)
 struct RmxTransSpec {
-    const double* pd;     // (R,M,D) expected |d - orient*brk| under p_breakpoint, per breakend row
-    const double* wexp;   // (R,M,D) exp(-pen*pd)
+    const double* pd;     // (G)(R,M,D) expected |d - orient*brk| under p_breakpoint, per fit and breakend row
+    const double* wexp;   // (G)(R,M,D) exp(-pen*pd)
     const double* Tmat;   // (C,S,S) exact reference-order log transition of plain rows
     const double* Emat;   // (C,S,S) exp(Tmat); symmetric in (i,j) because the cost is even in the difference
     const double* flipc;  // (C,S,S) min-over-allele-flip excess cost (integer valued)
@@ -30,56 +30,68 @@ struct RmxRows {
 struct RmxChains {
     const int* start;     // (NC) first segment of chain c
     const int* end;       // (NC) last segment of chain c (inclusive)
+    const int* order;     // (NC) chain ids, longest chain first (launch order of the chain kernel)
     int NC;
 };
 
-// ---- likelihood.cu
-void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxParams& P, const int* rows, int R, double* segc);
-void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams& P,
-                        const double* segc, double* LL, int* dflags);
-void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
-                      const double* q_ot, const double* q_oa, const double* q_sw, double* F, double* fexp, double* mF,
-                      int* dflags);
-void rmx_launch_qfactor(cudaStream_t st, const RmxDims& d, int which, const double* LL, const double* post,
+// ---- likelihood.cu   (every launcher covers the fits [g0, g0+gn) of a batch; P is the per-fit parameter array)
+void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                         const int* rows_all, const int* Rn, int Rmax, double* segc);
+void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
+                        int gn, const double* segc, double* LL, int* dflags);
+void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                      const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
+                      double* fexp, double* mF, int* dflags);
+void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
+                      double* A);
+void rmx_launch_qupdate(cudaStream_t st, const RmxDims& d, int g0, int gn, int which, const double* A,
                         const double* q_oa, const double* q_sw, double prior, double* out);
-void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, double* out);
-void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
-                          const double* post, const double* F, const double* q_ot, const double* q_oa,
+void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, int g0, int gn,
+                            int64_t in_fit_stride, double* out, int out_fit_stride);
+void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                          const double* A, const double* post, const double* F, const double* q_ot, const double* q_oa,
                           const double* q_sw, double prior_ot, double prior_oa, double* rowv);
-void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, double* out);
+void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int gn, double* out, int64_t out_fit_stride);
 int rmx_ell_blocks(const RmxDims& d, int R);
-void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows, int R,
-                    const double* segc, const double* post, const double* q_ot, const double* q_oa,
-                    const double* q_sw, double* part, int* dflags);
-void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows,
-                         int R, const double* post, const double* q_ot, const double* q_oa, const double* q_sw,
-                         double* part, int* dflags);
-void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, int what, int n, int s,
-                     int u, int v, int w, double* out, int* dflags);
+void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                    const int* rows_all, const int* Rn, int Rmax, const double* segc, const double* post,
+                    const double* q_ot, const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride,
+                    int* dflags);
+void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                         const int* rows_all, const int* Rn, int Rmax, const double* post, const double* q_ot,
+                         const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride, int* dflags);
+void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g, int what, int n,
+                     int s, int u, int v, int w, double* out, int* dflags);
+// DFMA micro-benchmark; returns nullptr on success, else an error string
+const char* rmx_measure_fp64_peak(int device, double* tflops);
 
 // ---- chain.cu
 void rmx_launch_build_class(cudaStream_t st, const RmxTables& T, const RmxDims& d, int C, const int8_t* class_nrm,
                             double pen, int tm, double* Tmat, double* Emat, double* flipc, double* flipE);
-void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int R, const int* brk_rows, const int* bidx,
-                         const int* borient, const int8_t* brk, const double* p_brk, double pen, int tm, double* pd,
-                         double* wexp);
-// returns 0 on success, nonzero if the shared-memory configuration failed
+void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int g0, int gn, int R, const int* brk_rows, const int* bidx,
+                         const int* borient, const int8_t* brk, const double* p_brk, double pen, int tm,
+                         int64_t fit_stride, double* pd, double* wexp);
+// returns 0 on success, 1 if the shared-memory configuration failed, 2 if the state space is unsupported
 int rmx_launch_chain(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const RmxRows& rows,
-                     const RmxTransSpec& sp, const double* fexp, const double* mF, double* ahat, double* bhat,
-                     double* cnorm, double* chain_logz, int* dflags);
-void rmx_launch_post(cudaStream_t st, const RmxDims& d, const double* ahat, const double* bhat, double* post,
-                     double* zp, int* dflags);
-void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int R, const RmxRows& rows,
-                     const RmxTransSpec& sp, int uniform, const double* ahat, const double* bhat, const double* fexp,
-                     double* hist, int* dflags);
-void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, const int* krow_ptr, const int* krow_idx,
-                           const int* brk_rows, const int* borient, const int8_t* brk, const double* hist, double pen,
-                           int tm, double* p_brk, double* logq_scratch);
-void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
-                        const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, int uniform, const double* ahat,
-                        const double* bhat, const double* fexp, double* rowsum);
-void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch,
-                        const RmxRows& rows, const RmxTransSpec& sp, const double* F, double* lattice, int* path);
+                     const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp, const double* mF,
+                     double* ahat, double* bhat, double* chain_logz, int* dflags);
+void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* ahat, const double* bhat,
+                     double* post, int* dflags);
+void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
+                     const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
+                     const double* fexp, double* hist, int* dflags);
+void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, int g0, int gn, const int* krow_ptr, const int* krow_idx,
+                           const int* brk_rows, const int* borient, const int8_t* brk, const double* hist,
+                           int64_t hist_fit_stride, double pen, int tm, double* p_brk);
+// rowsum[g][r] = sum_ij joint[n,i,j] * (T_tsp - (diff ? T_t2sp : 0))[n,i,j]; rowlist == nullptr: n = r over N-1 rows
+void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxRows& rows,
+                        const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, const RmxTransSpec& t2_sp, int diff,
+                        int64_t sp_fit_stride, const int* rowlist, int nrows, int uniform, const double* ahat,
+                        const double* bhat, const double* fexp, double* rowsum, int64_t rowsum_fit_stride);
+void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
+                        const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
+                        double* lattice, int* path);
+// single fit: pointers (and sp.pd / sp.wexp) already offset to that fit
 void rmx_launch_materialize_T(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
                               const RmxTransSpec& sp, int64_t row0, int64_t nrows, double* out);
 void rmx_launch_materialize_joint(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
@@ -91,6 +103,3 @@ void rmx_launch_sum_product_2p(cudaStream_t st, int64_t N, int S, const double* 
                                double e0, double e1);
 void rmx_launch_max_product(cudaStream_t st, int64_t N, int S, const double* F, const double* Tm, double* lattice,
                             int64_t* path, double* logprob);
-
-// DFMA micro-benchmark; returns nullptr on success, else an error string
-const char* rmx_measure_fp64_peak(int device, double* tflops);

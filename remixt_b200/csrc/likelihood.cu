@@ -1,6 +1,7 @@
 // Likelihood kernels: the per-(segment,state) negative-binomial / beta-binomial expected
 // log-likelihood table, the frame log-probability, the 2-way q-factor posteriors
-// (allele swap, outliers), and the M-step / ELBO reductions.
+// (allele swap, outliers), and the M-step / ELBO reductions.  Every kernel serves a range of
+// fits of a batch in one launch (blockIdx.y = fit within the range).
 //
 // Reference: remixt/bpmodel.pyx
 //   negbin_log_likelihood :238-272      betabin_log_likelihood :304-347
@@ -16,49 +17,18 @@
 //   NB (u):    lgamma(x+r_u) - lgamma(x+1) - lgamma(r_u)
 //   BB (v,w):  lgamma(n+1) - lgamma(k_w+1) - lgamma(n-k_w+1) - lgamma(n+M_v) + lgamma(M_v)
 // plus the same with the hdel / LOH dispersions (only used when normal_contamination is off).
-// Layout: segc[c * R + r], c in [0,12), r = position in the row list.
+// Layout per fit: segc[c * R + r], c in [0,12), r = position in the row list; fit stride given.
 // ---------------------------------------------------------------------------------------------
-__global__ void k_segconst(RmxTables T, RmxParams P, const int* __restrict__ rows, int R,
-                           double* __restrict__ segc) {
-    int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= R) return;
-    int n = rows ? rows[r] : r;
-    double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n];
-    double na = y0 + y1;
-    double lgx1 = lgamma(x + 1.);
-#pragma unroll
-    for (int u = 0; u < 2; ++u) {
-        double rr = P.negbin_r[u];
-        segc[(0 + u) * R + r] = lgamma(x + rr) - lgx1 - lgamma(rr);
-        double rh = P.negbin_hdel_r[u];
-        segc[(2 + u) * R + r] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
-    }
-    double lgn1 = lgamma(na + 1.);
-    double comb[2];
-    comb[0] = lgn1 - lgamma(y0 + 1.) - lgamma(na - y0 + 1.);
-    comb[1] = lgn1 - lgamma(y1 + 1.) - lgamma(na - y1 + 1.);
-#pragma unroll
-    for (int v = 0; v < 2; ++v) {
-        double Mv = P.betabin_M[v];
-        double t = -lgamma(na + Mv) + lgamma(Mv);
-        double Ml = P.betabin_loh_M[v];
-        double tl = P.normal_contamination ? 0. : (-lgamma(na + Ml) + lgamma(Ml));
-#pragma unroll
-        for (int w = 0; w < 2; ++w) {
-            segc[(4 + v * 2 + w) * R + r] = comb[w] + t;
-            segc[(8 + v * 2 + w) * R + r] = comb[w] + tl;
-        }
-    }
-}
+// (kernel: k_segconst_rows below)
 
 // Six log-likelihood terms of one (segment, state): ll[0..1] total (u), ll[2..5] allele (v*2+w).
-__device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P,
-                                         const double* __restrict__ segc, int R, int r, int n, int s,
+__device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P, bool tmask,
+                                         bool amask, const double* __restrict__ segc, int R, int r, int n, int s,
                                          double* ll, int* flags) {
     StateCN c = load_state(T, d, n, s);
     const bool special = !P.normal_contamination;
     // ---- total reads: negative binomial (bpmodel.pyx:751-776, :238-272)
-    if (T.tmask[n]) {
+    if (tmask) {
         double x = T.x[n];
         bool hd = special && c.hdel;
         double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, T.l[n]);
@@ -77,7 +47,7 @@ __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, c
     }
     // ---- allele reads: beta binomial (bpmodel.pyx:809-853, :304-347)
     ll[2] = ll[3] = ll[4] = ll[5] = 0.;
-    if (T.amask[n]) {
+    if (amask) {
         double p;
         if (c.hdel) {
             p = 0.;
@@ -121,39 +91,50 @@ __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, c
     }
 }
 
-// K1: the likelihood table, LL[t][n*S+s], one thread per (n,s), fully coalesced planar writes.
-__global__ void __launch_bounds__(256) k_lltable(RmxTables T, RmxDims d, RmxParams P,
-                                                  const double* __restrict__ segc,
-                                                  double* __restrict__ LL, int* __restrict__ dflags) {
-    int64_t NS = (int64_t)d.N * d.S;
+// K1: the likelihood table, LL[g][t][n*S+s], one thread per (n,s), fully coalesced planar writes.
+__global__ void __launch_bounds__(256) k_lltable(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                  const double* __restrict__ segc_all,
+                                                  double* __restrict__ LL_all, int* __restrict__ dflags) {
+    const int g = RMX_FIT();
+    const RmxParams P = Pg[g];
+    const int64_t NS = (int64_t)d.N * d.S;
+    const double* segc = segc_all + (int64_t)g * 12 * d.N;
+    double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
+    const uint8_t* tm = T.tmask + (int64_t)g * d.N;
+    const uint8_t* am = T.amask + (int64_t)g * d.N;
     int flags = 0;
     for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < NS;
          idx += (int64_t)gridDim.x * blockDim.x) {
         int n = (int)(idx / d.S), s = (int)(idx - (int64_t)n * d.S);
         double ll[RMX_NTERM];
-        ll_terms(T, d, P, segc, d.N, n, n, s, ll, &flags);
+        ll_terms(T, d, P, tm[n] != 0, am[n] != 0, segc, d.N, n, n, s, ll, &flags);
 #pragma unroll
         for (int t = 0; t < RMX_NTERM; ++t) LL[(int64_t)t * NS + idx] = ll[t];
     }
     if (flags) atomicOr(dflags, flags);
 }
 
-// Frame log-probability (bpmodel.pyx:898-919) from the LL table, one warp per segment.
+// Frame log-probability (bpmodel.pyx:898-919) from the LL table, one warp per (fit, segment).
 // Also writes the row max mF[n] and fexp[n,s] = exp(F[n,s] - mF[n]) for the scaled chain messages.
-__global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, RmxParams P,
-                                               const double* __restrict__ LL,
-                                               const double* __restrict__ q_ot, const double* __restrict__ q_oa,
-                                               const double* __restrict__ q_sw,
-                                               double* __restrict__ F, double* __restrict__ fexp,
-                                               double* __restrict__ mF, int* __restrict__ dflags) {
+__global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                               const double* __restrict__ LL_all,
+                                               const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
+                                               const double* __restrict__ q_sw_all,
+                                               double* __restrict__ F_all, double* __restrict__ fexp_all,
+                                               double* __restrict__ mF_all, int* __restrict__ dflags) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= d.N) return;
-    int n = warp;
-    int64_t NS = (int64_t)d.N * d.S;
-    double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
-    double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
-    double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
-    double ln = T.l[n];
+    const int g = RMX_FIT();
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
+    const int64_t q = ((int64_t)g * d.N + n) * 2;
+    double ot0 = q_ot_all[q], ot1 = q_ot_all[q + 1];
+    double oa0 = q_oa_all[q], oa1 = q_oa_all[q + 1];
+    double sw0 = q_sw_all[q], sw1 = q_sw_all[q + 1];
+    double ln = T.l[n], dw = Pg[g].divergence_weight;
+    double* F = F_all + (int64_t)g * NS;
+    double* fexp = fexp_all + (int64_t)g * NS;
     double mx = -INFINITY;
     bool bad = false;
     for (int s = lane; s < d.S; s += 32) {
@@ -165,7 +146,7 @@ __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, RmxParams
         f += oa0 * sw1 * LL[3 * NS + i];
         f += oa1 * sw0 * LL[4 * NS + i];
         f += oa1 * sw1 * LL[5 * NS + i];
-        f += -1.0 * (double)T.nsub[s] * ln * P.divergence_weight;   // bpmodel.pyx:746-749
+        f += -1.0 * (double)T.nsub[s] * ln * dw;   // bpmodel.pyx:746-749
         F[i] = f;
         bad |= isnan(f);
         mx = fmax(mx, f);
@@ -173,9 +154,9 @@ __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, RmxParams
     mx = warp_max(mx);
     for (int s = lane; s < d.S; s += 32) {
         int64_t i = (int64_t)n * d.S + s;
-        fexp[i] = exp(F[i] - mx);
+        fexp[i] = exp(F[i] - mx);   // own store, L1/L2 hit
     }
-    if (lane == 0) mF[n] = mx;
+    if (lane == 0) mF_all[(int64_t)g * d.N + n] = mx;
     if (bad) atomicOr(dflags, RMX_F_FRAME_NAN);
 }
 
@@ -189,66 +170,78 @@ __device__ __forceinline__ void exp_normalize2(double a, double b, double* out) 
     out[1] = eb / z;
 }
 
-// The three 2-way factor updates, one warp per segment, reading the LL table and the posterior.
+// Posterior-weighted likelihood sums A[g][n][t] = sum_s post[g,n,s] * LL[g,t,n,s], t in [0,6): the
+// sufficient statistic of all three 2-way factor updates and of the ELBO's likelihood terms.
+// One warp per (fit, segment); one pass over post + the six LL planes (56 B per (n,s)).
+__global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* __restrict__ LL_all,
+                                               const double* __restrict__ post_all, double* __restrict__ A_all) {
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    const int g = RMX_FIT();
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
+    const double* post = post_all + (int64_t)g * NS;
+    double a[RMX_NTERM];
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t) a[t] = 0.;
+    for (int s = lane; s < d.S; s += 32) {
+        int64_t i = (int64_t)n * d.S + s;
+        double p = post[i];
+#pragma unroll
+        for (int t = 0; t < RMX_NTERM; ++t) a[t] = fma(p, LL[(int64_t)t * NS + i], a[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t) a[t] = warp_sum(a[t]);
+    if (lane < RMX_NTERM) {
+        double v = a[0];
+#pragma unroll
+        for (int t = 1; t < RMX_NTERM; ++t) v = lane == t ? a[t] : v;
+        A_all[((int64_t)g * d.N + n) * RMX_NTERM + lane] = v;
+    }
+}
+
+// The three 2-way factor updates from the sums A, one thread per (fit, segment).
 //   which = 0: update_p_allele_swap   (bpmodel.pyx:1025-1042)
 //   which = 1: update_p_outlier_total (bpmodel.pyx:987-1003)
 //   which = 2: update_p_outlier_allele(bpmodel.pyx:1005-1023)
-__global__ void __launch_bounds__(256) k_qfactor(RmxDims d, int which, const double* __restrict__ LL,
-                                                 const double* __restrict__ post,
-                                                 const double* __restrict__ q_oa, const double* __restrict__ q_sw,
-                                                 double prior, double* __restrict__ out) {
-    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (warp >= d.N) return;
-    int n = warp;
-    int64_t NS = (int64_t)d.N * d.S;
-    double a0 = 0., a1 = 0.;
+__global__ void __launch_bounds__(256) k_qupdate(RmxDims d, int g0, int which, const double* __restrict__ A_all,
+                                                 const double* __restrict__ q_oa_all, const double* __restrict__ q_sw_all,
+                                                 double prior, double* __restrict__ out_all) {
+    int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= d.N) return;
+    const int g = RMX_FIT();
+    const int64_t gn = (int64_t)g * d.N + n;
+    const double* A = A_all + gn * RMX_NTERM;
+    double a0, a1;
     if (which == 1) {
-        for (int s = lane; s < d.S; s += 32) {
-            int64_t i = (int64_t)n * d.S + s;
-            double p = post[i];
-            a0 += p * LL[i];
-            a1 += p * LL[NS + i];
-        }
+        a0 = A[0] + log(1. - prior);
+        a1 = A[1] + log(prior);
     } else if (which == 0) {
-        double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
-        for (int s = lane; s < d.S; s += 32) {
-            int64_t i = (int64_t)n * d.S + s;
-            double p = post[i];
-            a0 += oa0 * p * LL[2 * NS + i] + oa1 * p * LL[4 * NS + i];
-            a1 += oa0 * p * LL[3 * NS + i] + oa1 * p * LL[5 * NS + i];
-        }
+        double oa0 = q_oa_all[gn * 2], oa1 = q_oa_all[gn * 2 + 1];
+        a0 = oa0 * A[2] + oa1 * A[4];
+        a1 = oa0 * A[3] + oa1 * A[5];
     } else {
-        double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
-        for (int s = lane; s < d.S; s += 32) {
-            int64_t i = (int64_t)n * d.S + s;
-            double p = post[i];
-            a0 += sw0 * p * LL[2 * NS + i] + sw1 * p * LL[3 * NS + i];
-            a1 += sw0 * p * LL[4 * NS + i] + sw1 * p * LL[5 * NS + i];
-        }
+        double sw0 = q_sw_all[gn * 2], sw1 = q_sw_all[gn * 2 + 1];
+        a0 = sw0 * A[2] + sw1 * A[3] + log(1. - prior);
+        a1 = sw0 * A[4] + sw1 * A[5] + log(prior);
     }
-    a0 = warp_sum(a0);
-    a1 = warp_sum(a1);
-    if (lane == 0) {
-        if (which != 0) {
-            a0 += log(1. - prior);
-            a1 += log(prior);
-        }
-        exp_normalize2(a0, a1, out + 2 * n);
-    }
+    exp_normalize2(a0, a1, out_all + gn * 2);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Reductions.  Every scalar the host reads is produced by the same two-stage scheme: per-row
-// values (one warp per segment, fixed lane order) then one CTA summing the row values in a fixed
-// strided order, so results are reproducible run to run.
+// values (fixed lane order) then one CTA per (column, fit) summing the row values in a fixed strided
+// order, so results are reproducible run to run.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_reduce_cols(const double* __restrict__ in, int64_t n, int ncol,
-                                                      double* __restrict__ out) {
-    // out[c] = sum_i in[c*n + i], one CTA per column
+__global__ void __launch_bounds__(1024) k_reduce_cols(const double* __restrict__ in_all, int64_t n, int ncol, int g0,
+                                                      int64_t in_fit_stride, double* __restrict__ out_all,
+                                                      int out_fit_stride) {
+    // out[g][c] = sum_i in[g][c*n + i]
     __shared__ double sm[32];
-    int c = blockIdx.x;
-    if (c >= ncol) return;
-    const double* p = in + (int64_t)c * n;
+    const int c = blockIdx.x;
+    const int g = RMX_FIT();
+    const double* p = in_all + (int64_t)g * in_fit_stride + (int64_t)c * n;
     double acc = 0.;
     for (int64_t i = threadIdx.x; i < n; i += blockDim.x) acc += p[i];
     acc = warp_sum(acc);
@@ -257,49 +250,50 @@ __global__ void __launch_bounds__(1024) k_reduce_cols(const double* __restrict__
     if (threadIdx.x < 32) {
         double v = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.;
         v = warp_sum(v);
-        if (threadIdx.x == 0) out[c] = v;
+        if (threadIdx.x == 0) out_all[(int64_t)g * out_fit_stride + c] = v;
     }
 }
 
 __device__ __forceinline__ double plogp(double p) { return p > 0. ? p * log(p) : 0.; }
 
-// Per-segment ELBO terms from the LL table (bpmodel.pyx:1044-1117), one warp per segment.
-// rowv columns (each length N):
+// Per-segment ELBO terms (bpmodel.pyx:1044-1117), one warp per (fit, segment), from post, F and the sums A.
+// rowv columns (each length N, fit stride 8*N):
 //   0: sum_s post*prior_cn          1: sum_s post * sum_u q_ot*LLtot   2: sum_s post * sum_vw q_oa q_sw LLal
 //   3: q_ot . log prior            4: q_oa . log prior                 5: sum_s post*F
 //   6: entropy terms of q_ot,q_oa,q_sw  (sum p log p)
-__global__ void __launch_bounds__(256) k_elbo_rows(RmxTables T, RmxDims d, RmxParams P, const double* __restrict__ LL,
-                                                   const double* __restrict__ post, const double* __restrict__ F,
-                                                   const double* __restrict__ q_ot, const double* __restrict__ q_oa,
-                                                   const double* __restrict__ q_sw, double prior_ot, double prior_oa,
-                                                   double* __restrict__ rowv) {
+__global__ void __launch_bounds__(256) k_elbo_rows(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                   const double* __restrict__ A_all, const double* __restrict__ post_all,
+                                                   const double* __restrict__ F_all, const double* __restrict__ q_ot_all,
+                                                   const double* __restrict__ q_oa_all, const double* __restrict__ q_sw_all,
+                                                   double prior_ot, double prior_oa, double* __restrict__ rowv_all) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= d.N) return;
-    int n = warp;
-    int64_t NS = (int64_t)d.N * d.S;
-    double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
-    double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
-    double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
-    double ln = T.l[n];
-    double e0 = 0., e1 = 0., e2 = 0., e5 = 0.;
+    const int g = RMX_FIT();
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const int64_t gn = (int64_t)g * d.N + n;
+    const double* post = post_all + (int64_t)g * NS;
+    const double* F = F_all + (int64_t)g * NS;
+    double ln = T.l[n], dw = Pg[g].divergence_weight;
+    double e0 = 0., e5 = 0.;
     for (int s = lane; s < d.S; s += 32) {
         int64_t i = (int64_t)n * d.S + s;
         double p = post[i];
-        e0 += p * (-1.0 * (double)T.nsub[s] * ln * P.divergence_weight);
-        e1 += p * ot0 * LL[i] + p * ot1 * LL[NS + i];
-        e2 += p * oa0 * sw0 * LL[2 * NS + i] + p * oa0 * sw1 * LL[3 * NS + i] +
-              p * oa1 * sw0 * LL[4 * NS + i] + p * oa1 * sw1 * LL[5 * NS + i];
+        e0 += p * (-1.0 * (double)T.nsub[s] * ln * dw);
         e5 += p * F[i];
     }
     e0 = warp_sum(e0);
-    e1 = warp_sum(e1);
-    e2 = warp_sum(e2);
     e5 = warp_sum(e5);
     if (lane == 0) {
+        const double* A = A_all + gn * RMX_NTERM;
+        double ot0 = q_ot_all[gn * 2], ot1 = q_ot_all[gn * 2 + 1];
+        double oa0 = q_oa_all[gn * 2], oa1 = q_oa_all[gn * 2 + 1];
+        double sw0 = q_sw_all[gn * 2], sw1 = q_sw_all[gn * 2 + 1];
+        double* rowv = rowv_all + (int64_t)g * 8 * d.N;
         int64_t N = d.N;
         rowv[0 * N + n] = e0;
-        rowv[1 * N + n] = e1;
-        rowv[2 * N + n] = e2;
+        rowv[1 * N + n] = ot0 * A[0] + ot1 * A[1];
+        rowv[2 * N + n] = oa0 * sw0 * A[2] + oa0 * sw1 * A[3] + oa1 * sw0 * A[4] + oa1 * sw1 * A[5];
         rowv[3 * N + n] = ot0 * log(1. - prior_ot) + ot1 * log(prior_ot);
         rowv[4 * N + n] = oa0 * log(1. - prior_oa) + oa1 * log(prior_oa);
         rowv[5 * N + n] = e5;
@@ -307,17 +301,20 @@ __global__ void __launch_bounds__(256) k_elbo_rows(RmxTables T, RmxDims d, RmxPa
     }
 }
 
-// sum p log p over a flat array (p_breakpoint) -> rowv[i]
-__global__ void k_plogp(const double* __restrict__ p, int64_t n, double* __restrict__ out) {
+// p log p over a flat per-fit array (p_breakpoint)
+__global__ void k_plogp(const double* __restrict__ p_all, int64_t n, int g0, double* __restrict__ out_all,
+                        int64_t out_fit_stride) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = plogp(p[i]);
+    const int g = RMX_FIT();
+    if (i < n) out_all[(int64_t)g * out_fit_stride + i] = plogp(p_all[(int64_t)g * n + i]);
 }
 
 // ---------------------------------------------------------------------------------------------
-// M-step objective on a row list: E_q[log lik] (bpmodel.pyx:1125-1157) and its gradient in h
+// M-step objective on per-fit row lists: E_q[log lik] (bpmodel.pyx:1125-1157) and its gradient in h
 // (bpmodel.pyx:1159-1195), with the LL terms evaluated for the CURRENT parameters (the LL table
 // belongs to the E-step generation and is not touched).  One thread per (row, state); the CTA
-// sum goes to part[blockIdx.x] (ELL) or part[m*gridDim.x + blockIdx.x] (gradient).
+// sum goes to part[g][blockIdx.x] (ELL) or part[g][m*gridDim.x + blockIdx.x] (gradient).
+// rows_all == nullptr: every segment of every fit; else fit g uses rows_all[g*N .. g*N + Rn[g]).
 // ---------------------------------------------------------------------------------------------
 template <int NV>
 __device__ __forceinline__ void block_sum_store(double* v, double* __restrict__ part, int stride) {
@@ -337,36 +334,92 @@ __device__ __forceinline__ void block_sum_store(double* v, double* __restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, RmxParams P, const int* __restrict__ rows, int R,
-                                             const double* __restrict__ segc, const double* __restrict__ post,
-                                             const double* __restrict__ q_ot, const double* __restrict__ q_oa,
-                                             const double* __restrict__ q_sw, double* __restrict__ part,
-                                             int* __restrict__ dflags) {
+// segconst for the row lists of the M-step (same contents as k_segconst, per-fit row count)
+__global__ void k_segconst_rows(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                                double* __restrict__ segc_all) {
+    const int g = RMX_FIT();
+    const int R = rows_all ? Rn[g] : d.N;
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    const RmxParams& P = Pg[g];
+    double* segc = segc_all + (int64_t)g * 12 * d.N;
+    int n = rows_all ? rows_all[(int64_t)g * d.N + r] : r;
+    double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n];
+    double na = y0 + y1;
+    double lgx1 = lgamma(x + 1.);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        double rr = P.negbin_r[u];
+        segc[(0 + u) * R + r] = lgamma(x + rr) - lgx1 - lgamma(rr);
+        double rh = P.negbin_hdel_r[u];
+        segc[(2 + u) * R + r] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
+    }
+    double lgn1 = lgamma(na + 1.);
+    double comb[2];
+    comb[0] = lgn1 - lgamma(y0 + 1.) - lgamma(na - y0 + 1.);
+    comb[1] = lgn1 - lgamma(y1 + 1.) - lgamma(na - y1 + 1.);
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+        double Mv = P.betabin_M[v];
+        double t = -lgamma(na + Mv) + lgamma(Mv);
+        double Ml = P.betabin_loh_M[v];
+        double tl = P.normal_contamination ? 0. : (-lgamma(na + Ml) + lgamma(Ml));
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            segc[(4 + v * 2 + w) * R + r] = comb[w] + t;
+            segc[(8 + v * 2 + w) * R + r] = comb[w] + tl;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                             const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                                             const double* __restrict__ segc_all, const double* __restrict__ post_all,
+                                             const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
+                                             const double* __restrict__ q_sw_all, double* __restrict__ part_all,
+                                             int64_t part_fit_stride, int* __restrict__ dflags) {
+    const int g = RMX_FIT();
+    const int R = rows_all ? Rn[g] : d.N;
     int64_t RS = (int64_t)R * d.S;
     int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     double acc[1] = {0.};
     int flags = 0;
     if (idx < RS) {
         int r = (int)(idx / d.S), s = (int)(idx - (int64_t)r * d.S);
-        int n = rows ? rows[r] : r;
+        int n = rows_all ? rows_all[(int64_t)g * d.N + r] : r;
+        const int64_t gn = (int64_t)g * d.N + n;
         double ll[RMX_NTERM];
-        ll_terms(T, d, P, segc, R, r, n, s, ll, &flags);
-        double p = post[(int64_t)n * d.S + s];
-        double ot0 = q_ot[2 * n], ot1 = q_ot[2 * n + 1];
-        double oa0 = q_oa[2 * n], oa1 = q_oa[2 * n + 1];
-        double sw0 = q_sw[2 * n], sw1 = q_sw[2 * n + 1];
+        ll_terms(T, d, Pg[g], T.tmask[gn] != 0, T.amask[gn] != 0, segc_all + (int64_t)g * 12 * d.N, R, r, n, s, ll,
+                 &flags);
+        double p = post_all[gn * d.S + s];
+        double ot0 = q_ot_all[2 * gn], ot1 = q_ot_all[2 * gn + 1];
+        double oa0 = q_oa_all[2 * gn], oa1 = q_oa_all[2 * gn + 1];
+        double sw0 = q_sw_all[2 * gn], sw1 = q_sw_all[2 * gn + 1];
         acc[0] = p * ot0 * ll[0] + p * ot1 * ll[1] + p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3] +
                  p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
     }
-    block_sum_store<1>(acc, part, gridDim.x);
+    block_sum_store<1>(acc, part_all + (int64_t)g * part_fit_stride, gridDim.x);
     if (flags) atomicOr(dflags, flags);
 }
 
-__global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, RmxParams P, const int* __restrict__ rows,
-                                                  int R, const double* __restrict__ post,
-                                                  const double* __restrict__ q_ot, const double* __restrict__ q_oa,
-                                                  const double* __restrict__ q_sw, double* __restrict__ part,
-                                                  int* __restrict__ dflags) {
+__global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                  const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                                                  const double* __restrict__ post_all,
+                                                  const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
+                                                  const double* __restrict__ q_sw_all, double* __restrict__ part_all,
+                                                  int64_t part_fit_stride, int* __restrict__ dflags) {
+    const int gf = RMX_FIT();
+    const RmxParams& P = Pg[gf];
+    const int R = rows_all ? Rn[gf] : d.N;
+    const int* rows = rows_all ? rows_all + (int64_t)gf * d.N : nullptr;
+    const double* post = post_all + (int64_t)gf * d.N * d.S;
+    const double* q_ot = q_ot_all + (int64_t)gf * d.N * 2;
+    const double* q_oa = q_oa_all + (int64_t)gf * d.N * 2;
+    const double* q_sw = q_sw_all + (int64_t)gf * d.N * 2;
+    const uint8_t* tmask = T.tmask + (int64_t)gf * d.N;
+    const uint8_t* amask = T.amask + (int64_t)gf * d.N;
+    double* part = part_all + (int64_t)gf * part_fit_stride;
     int64_t RS = (int64_t)R * d.S;
     int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     double g[RMX_MAXM];
@@ -380,7 +433,7 @@ __global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, RmxPar
         const bool special = !P.normal_contamination;
         double p = post[(int64_t)n * d.S + s];
         // total reads (bpmodel.pyx:778-807, :275-301)
-        if (T.tmask[n] && !(special && c.hdel)) {
+        if (tmask[n] && !(special && c.hdel)) {
             double l = T.l[n], x = T.x[n];
             double mu = expected_total_reads(P, d, c, l);
 #pragma unroll
@@ -395,7 +448,7 @@ __global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, RmxPar
             }
         }
         // allele reads (bpmodel.pyx:855-896, :350-394, :726-744)
-        if (T.amask[n] && !(special && c.loh)) {
+        if (amask[n] && !(special && c.loh)) {
             double md, td;
             double pr = expected_allele_ratio(P, d, c, &md, &td);
             if (td <= 0.) {
@@ -438,10 +491,13 @@ __global__ void __launch_bounds__(256) k_ell_grad(RmxTables T, RmxDims d, RmxPar
 }
 
 // Single-(n,s) scalar accessors (bpmodel.pyx:686-896), evaluated on the device.
-__global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int s, int u, int v, int w,
+__global__ void k_eval(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g, int what, int n, int s, int u, int v, int w,
                        double* __restrict__ out, int* __restrict__ dflags) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     int flags = 0;
+    const RmxParams& P = Pg[g];
+    const uint8_t* tmask = T.tmask + (int64_t)g * d.N;
+    const uint8_t* amask = T.amask + (int64_t)g * d.N;
     for (int m = 0; m < RMX_MAXM; ++m) out[m] = 0.;
     StateCN c = load_state(T, d, n, s);
     const bool special = !P.normal_contamination;
@@ -460,7 +516,7 @@ __global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int
     }
     case 4: out[0] = -1.0 * (double)T.nsub[s] * l * P.divergence_weight; break;
     case 5: {
-        if (!T.tmask[n]) break;
+        if (!tmask[n]) break;
         bool hd = special && c.hdel;
         double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, l);
         double rr = hd ? P.negbin_hdel_r[u] : P.negbin_r[u];
@@ -473,7 +529,7 @@ __global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int
         break;
     }
     case 6: {
-        if (!T.tmask[n] || (special && c.hdel)) break;
+        if (!tmask[n] || (special && c.hdel)) break;
         double mu = expected_total_reads(P, d, c, l);
         double rr = P.negbin_r[u], x = T.x[n];
         double dmu = x / mu - (rr + x) / (rr + mu);
@@ -482,7 +538,7 @@ __global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int
         break;
     }
     case 7: {
-        if (!T.amask[n]) break;
+        if (!amask[n]) break;
         double p = 0.;
         if (!c.hdel) {
             double md, td;
@@ -508,7 +564,7 @@ __global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int
         break;
     }
     case 8: {
-        if (!T.amask[n] || (special && c.loh)) break;
+        if (!amask[n] || (special && c.loh)) break;
         double md, td;
         double pr = expected_allele_ratio(P, d, c, &md, &td);
         if (td <= 0.) { flags |= RMX_F_TOTAL_DEPTH; break; }
@@ -526,76 +582,6 @@ __global__ void k_eval(RmxTables T, RmxDims d, RmxParams P, int what, int n, int
     default: break;
     }
     if (flags) atomicOr(dflags, flags);
-}
-
-// ---------------------------------------------------------------------------------------------
-// launchers
-// ---------------------------------------------------------------------------------------------
-static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
-
-void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxParams& P, const int* rows, int R, double* segc) {
-    if (R <= 0) return;
-    k_segconst<<<cdiv(R, 128), 128, 0, st>>>(T, P, rows, R, segc);
-}
-
-void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams& P,
-                        const double* segc, double* LL, int* dflags) {
-    int64_t NS = (int64_t)d.N * d.S;
-    if (NS <= 0) return;
-    int64_t want = (NS + 255) / 256;
-    int64_t cap = (int64_t)sm_count * 8;           // grid sized in multiples of the SM count
-    int grid = (int)(want < cap ? want : cap);
-    k_lltable<<<grid, 256, 0, st>>>(T, d, P, segc, LL, dflags);
-}
-
-void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
-                      const double* q_ot, const double* q_oa, const double* q_sw, double* F, double* fexp, double* mF,
-                      int* dflags) {
-    if (d.N <= 0) return;
-    k_frame<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(T, d, P, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
-}
-
-void rmx_launch_qfactor(cudaStream_t st, const RmxDims& d, int which, const double* LL, const double* post,
-                        const double* q_oa, const double* q_sw, double prior, double* out) {
-    if (d.N <= 0) return;
-    k_qfactor<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(d, which, LL, post, q_oa, q_sw, prior, out);
-}
-
-void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, double* out) {
-    if (ncol <= 0) return;
-    k_reduce_cols<<<ncol, 1024, 0, st>>>(in, n, ncol, out);
-}
-
-void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const double* LL,
-                          const double* post, const double* F, const double* q_ot, const double* q_oa,
-                          const double* q_sw, double prior_ot, double prior_oa, double* rowv) {
-    if (d.N <= 0) return;
-    k_elbo_rows<<<cdiv((int64_t)d.N * 32, 256), 256, 0, st>>>(T, d, P, LL, post, F, q_ot, q_oa, q_sw, prior_ot,
-                                                              prior_oa, rowv);
-}
-
-void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, double* out) {
-    if (n <= 0) return;
-    k_plogp<<<cdiv(n, 256), 256, 0, st>>>(p, n, out);
-}
-
-int rmx_ell_blocks(const RmxDims& d, int R) { return cdiv((int64_t)R * d.S, 256); }
-
-void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows, int R,
-                    const double* segc, const double* post, const double* q_ot, const double* q_oa,
-                    const double* q_sw, double* part, int* dflags) {
-    k_ell<<<rmx_ell_blocks(d, R), 256, 0, st>>>(T, d, P, rows, R, segc, post, q_ot, q_oa, q_sw, part, dflags);
-}
-
-void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, const int* rows,
-                         int R, const double* post, const double* q_ot, const double* q_oa, const double* q_sw,
-                         double* part, int* dflags) {
-    k_ell_grad<<<rmx_ell_blocks(d, R), 256, 0, st>>>(T, d, P, rows, R, post, q_ot, q_oa, q_sw, part, dflags);
-}
-
-void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams& P, int what, int n, int s,
-                     int u, int v, int w, double* out, int* dflags) {
-    k_eval<<<1, 32, 0, st>>>(T, d, P, what, n, s, u, v, w, out, dflags);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -641,4 +627,88 @@ const char* rmx_measure_fp64_peak(int device, double* tflops) {
     if (e != cudaSuccess) return cudaGetErrorString(e);
     *tflops = best;
     return nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers (g0 = first fit, gn = number of fits; blockIdx.y = fit)
+// ---------------------------------------------------------------------------------------------
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                         const int* rows_all, const int* Rn, int Rmax, double* segc) {
+    if (Rmax <= 0 || gn <= 0) return;
+    k_segconst_rows<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, P, g0, rows_all, Rn, segc);
+}
+
+void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
+                        int gn, const double* segc, double* LL, int* dflags) {
+    int64_t NS = (int64_t)d.N * d.S;
+    if (NS <= 0 || gn <= 0) return;
+    int64_t want = (NS + 255) / 256;
+    int64_t cap = ((int64_t)sm_count * 8 + gn - 1) / gn;    // whole grid sized in multiples of the SM count
+    if (cap < 1) cap = 1;
+    int grid = (int)(want < cap ? want : cap);
+    k_lltable<<<dim3(grid, gn), 256, 0, st>>>(T, d, P, g0, segc, LL, dflags);
+}
+
+void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                      const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
+                      double* fexp, double* mF, int* dflags) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_frame<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+}
+
+void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
+                      double* A) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A);
+}
+
+void rmx_launch_qupdate(cudaStream_t st, const RmxDims& d, int g0, int gn, int which, const double* A,
+                        const double* q_oa, const double* q_sw, double prior, double* out) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_qupdate<<<dim3(cdiv(d.N, 256), gn), 256, 0, st>>>(d, g0, which, A, q_oa, q_sw, prior, out);
+}
+
+void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, int g0, int gn,
+                            int64_t in_fit_stride, double* out, int out_fit_stride) {
+    if (ncol <= 0 || gn <= 0) return;
+    k_reduce_cols<<<dim3(ncol, gn), 1024, 0, st>>>(in, n, ncol, g0, in_fit_stride, out, out_fit_stride);
+}
+
+void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                          const double* A, const double* post, const double* F, const double* q_ot, const double* q_oa,
+                          const double* q_sw, double prior_ot, double prior_oa, double* rowv) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_elbo_rows<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(T, d, P, g0, A, post, F, q_ot, q_oa, q_sw,
+                                                                        prior_ot, prior_oa, rowv);
+}
+
+void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int gn, double* out, int64_t out_fit_stride) {
+    if (n <= 0 || gn <= 0) return;
+    k_plogp<<<dim3(cdiv(n, 256), gn), 256, 0, st>>>(p, n, g0, out, out_fit_stride);
+}
+
+int rmx_ell_blocks(const RmxDims& d, int R) { return cdiv((int64_t)R * d.S, 256); }
+
+void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                    const int* rows_all, const int* Rn, int Rmax, const double* segc, const double* post,
+                    const double* q_ot, const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride,
+                    int* dflags) {
+    if (Rmax <= 0 || gn <= 0) return;
+    k_ell<<<dim3(rmx_ell_blocks(d, Rmax), gn), 256, 0, st>>>(T, d, P, g0, rows_all, Rn, segc, post, q_ot, q_oa, q_sw,
+                                                            part, part_fit_stride, dflags);
+}
+
+void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                         const int* rows_all, const int* Rn, int Rmax, const double* post, const double* q_ot,
+                         const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride, int* dflags) {
+    if (Rmax <= 0 || gn <= 0) return;
+    k_ell_grad<<<dim3(rmx_ell_blocks(d, Rmax), gn), 256, 0, st>>>(T, d, P, g0, rows_all, Rn, post, q_ot, q_oa, q_sw, part,
+                                                                 part_fit_stride, dflags);
+}
+
+void rmx_launch_eval(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g, int what, int n,
+                     int s, int u, int v, int w, double* out, int* dflags) {
+    k_eval<<<1, 32, 0, st>>>(T, d, P, g, what, n, s, u, v, w, out, dflags);
 }

@@ -237,3 +237,100 @@ def fit_grid_distributed(experiment, init_params_by_id, config, dist=None, devic
     ordered = dict((i, all_stats[i]) for i in ids if i in all_stats)
     best = select_solution(ordered, config) if ordered else None
     return results, ordered, best
+
+
+def _fit_results(model, experiment, init_params, config, cn):
+    """The ``fit_results`` dict of ``analysis/pipeline.py:195-228`` from a fitted driver and its MAP copy number."""
+    brk_cn = model.decode_breakpoints(cn)
+    cn = cn[model.seg_fwd_remap]
+    if get_param(config, 'disable_breakpoints'):
+        brk_cn = cn_model.decode_breakpoints_naive(cn, experiment.adjacencies, experiment.breakpoints)
+    results = dict()
+    results['h'] = model.h
+    results['cn'] = cn
+    results['brk_cn'] = brk_cn
+    results['p_outlier_total'] = model.p_outlier_total
+    results['p_outlier_allele'] = model.p_outlier_allele
+    results['total_likelihood_mask'] = model.total_likelihood_mask
+    results['allele_likelihood_mask'] = model.allele_likelihood_mask
+    stats = dict()
+    stats['elbo'] = model.prev_elbo
+    stats['elbo_diff'] = model.prev_elbo_diff
+    stats['error_message'] = ''
+    stats.update(model.get_likelihood_param_values())
+    l = experiment.l
+    stats['num_clones'] = len(model.h)
+    stats['num_segments'] = len(experiment.x)
+    stats['ploidy'] = (cn[:, 1:, :].mean(axis=1).T * l).sum() / l.sum()
+    divergent = (cn[:, 1:, :].max(axis=1) != cn[:, 1:, :].min(axis=1)) * 1.
+    stats['proportion_divergent'] = (divergent.T * l).sum() / (2. * l.sum())
+    stats['mode_idx'] = init_params.get('mode_idx', 0)
+    stats['divergence_weight'] = init_params['divergence_weight']
+    results['stats'] = stats
+    return results
+
+
+def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_seed=1234, num_threads=8,
+                     init_ids=None):
+    """The whole initialisation grid as ONE batch on one GPU: every E-step kernel launch serves all fits
+    (``bpmodel.RemixtBatch``); the M-steps stay the reference's per-fit scipy optimisers
+    (``cn_model.py:482-569``), run from ``num_threads`` host threads on views of the batch.
+
+    Per fit this performs exactly the calls ``fit`` performs, in the same order, with the M-step
+    subsamples drawn from ``RandomState(random_seed)`` per fit (the stream a process that called
+    ``numpy.random.seed(random_seed)`` before ``pipeline.fit`` would see).  Returns ``(results, best, errors)``
+    like :func:`fit_grid`.
+    """
+    from . import bpmodel
+    ids = list(init_params_by_id.keys()) if init_ids is None else list(init_ids)
+    drivers = [build_model(experiment, init_params_by_id[i], config, random_state=np.random.RandomState(random_seed))
+               for i in ids]
+    h = np.array([init_h(init_params_by_id[i]) for i in ids])
+    dw = np.array([init_params_by_id[i]['divergence_weight'] for i in ids], dtype=float)
+    kwargs = {} if device is None else {'device': device}
+    batch = bpmodel.RemixtBatch(*(drivers[0].model_args(h) + (dw,)), **kwargs)
+    for g, d in enumerate(drivers):
+        d.attach(batch.fit(g))
+    elbo = batch.calculate_elbo()
+    for g, d in enumerate(drivers):
+        d.prev_elbo = float(elbo[g])
+    num_em_iter = get_param(config, 'num_em_iter')
+    num_update_iter = get_param(config, 'num_update_iter')
+    errors = {}
+
+    def m_step(slot):
+        for g in range(slot, len(drivers), num_threads):
+            if ids[g] in errors:
+                continue
+            try:
+                if drivers[g].do_h_update:
+                    drivers[g].em_update_h()
+                drivers[g].em_update_params()
+            except Exception as e:   # a failed initialisation must not take the grid down
+                errors[ids[g]] = e
+
+    nt = max(1, min(num_threads, len(drivers)))
+    for i in range(num_em_iter):
+        batch.variational_update(num_update_iter)
+        if nt == 1:
+            m_step(0)
+        else:
+            threads = [threading.Thread(target=m_step, args=(s,)) for s in range(nt)]
+            for t in threads:
+                t.start()
+            for t in threads:
+                t.join()
+        elbo = batch.calculate_elbo()
+        for g, d in enumerate(drivers):
+            d.record_iteration(i, float(elbo[g]))
+    cn = np.zeros((len(drivers), batch.num_segments, batch.num_clones, 2), dtype=np.int64)
+    batch.infer_cn(cn)
+    results = {}
+    for g, d in enumerate(drivers):
+        if ids[g] not in errors:
+            results[ids[g]] = _fit_results(d, experiment, init_params_by_id[ids[g]], config, cn[g])
+    if errors and not results:
+        raise next(iter(errors.values()))
+    stats = dict((i, results[i]['stats']) for i in ids if i in results)
+    best = select_solution(stats, config) if stats else None
+    return results, best, errors

@@ -1,0 +1,116 @@
+"""Batches (G fits advanced by one set of launches) against single-fit models on the B200: the fits of a
+batch must evolve exactly as the same fits run alone, through the C-ABI."""
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+FITS = [0, 5, 9, 17, 22, 40, 47]     # 7 fits: a full tile of 4 and a ragged one, different h / divergence weights
+
+
+def _batch_and_singles(name='small'):
+    from remixt_b200 import bpmodel, pipeline
+    exp = util.load_experiment(name)
+    ips = [util.init_params(name, i) for i in FITS]
+    cfg = {'max_copy_number': 6}
+    drivers = [pipeline.build_model(exp, ip, cfg) for ip in ips]
+    h = np.array([pipeline.init_h(ip) for ip in ips])
+    dw = np.array([ip['divergence_weight'] for ip in ips])
+    batch = bpmodel.RemixtBatch(*(drivers[0].model_args(h) + (dw,)))
+    for g, d in enumerate(drivers):
+        d.attach(batch.fit(g))
+    singles = [util.make_driver(exp, ip).model for ip in ips]
+    return batch, singles, drivers
+
+
+def test_batch_equals_single_fits():
+    batch, singles, _ = _batch_and_singles()
+    G = len(singles)
+    assert batch.num_fits == G
+    e = batch.calculate_elbo()
+    assert np.array_equal(e, np.array([m.calculate_elbo() for m in singles]))
+    for r in range(2):
+        for step in util.STEPS:
+            getattr(batch, step)()
+            for m in singles:
+                getattr(m, step)()
+            for a in ('p_allele_swap', 'p_outlier_total', 'p_outlier_allele', 'p_breakpoint', 'posterior_marginals',
+                      'framelogprob'):
+                A = getattr(batch, a)
+                for g, m in enumerate(singles):
+                    assert np.array_equal(A[g], getattr(m, a)), (r, step, a, g)
+            assert np.array_equal(batch.hmm_log_norm_const, np.array([m.hmm_log_norm_const for m in singles]))
+            for f in ('calculate_elbo', 'calculate_variational_energy', 'calculate_variational_entropy'):
+                assert np.array_equal(getattr(batch, f)(), np.array([getattr(m, f)() for m in singles])), (step, f)
+    # fused rounds
+    batch.variational_update(2)
+    for m in singles:
+        m.variational_update(2)
+    assert np.array_equal(batch.posterior_marginals, np.array([m.posterior_marginals for m in singles]))
+    cn = np.zeros((G, batch.num_segments, 3, 2), dtype=np.int64)
+    batch.infer_cn(cn)
+    for g, m in enumerate(singles):
+        c = np.zeros((m.num_segments, 3, 2), dtype=np.int64)
+        m.infer_cn(c)
+        assert np.array_equal(cn[g], c)
+
+
+def test_views_share_state_and_isolate_parameters():
+    batch, singles, _ = _batch_and_singles()
+    batch.variational_update(1)
+    for m in singles:
+        m.variational_update(1)
+    v = batch.fit(3)
+    assert np.array_equal(v.posterior_marginals, batch.posterior_marginals[3])
+    rs = np.random.RandomState(1)
+    sample = np.zeros(v.num_segments, dtype=int)
+    sample[rs.choice(v.num_segments, size=20, replace=False)] = 1
+    # a parameter set through a view changes that fit only
+    v.h = np.array([0.03, 0.04, 0.02])
+    v.negbin_r_0 = 77.
+    singles[3].h = np.array([0.03, 0.04, 0.02])
+    singles[3].negbin_r_0 = 77.
+    ell = batch.calculate_expected_log_likelihood(sample)
+    for g, m in enumerate(singles):
+        assert ell[g] == m.calculate_expected_log_likelihood(sample), g
+    assert v.calculate_expected_log_likelihood(sample) == ell[3]
+    grad = np.zeros((len(singles), 3))
+    batch.calculate_expected_log_likelihood_partial_h(sample, grad)
+    for g, m in enumerate(singles):
+        gg = np.zeros(3)
+        m.calculate_expected_log_likelihood_partial_h(sample, gg)
+        assert np.array_equal(grad[g], gg)
+    # per-fit samples and a per-fit parameter grid in one call
+    samples = np.zeros((len(singles), v.num_segments), dtype=int)
+    for g in range(len(singles)):
+        samples[g, rs.choice(v.num_segments, size=15 + g, replace=False)] = 1
+    vals = np.linspace(10., 2000., 5)
+    grid = batch.calculate_expected_log_likelihood_grid(samples, 'betabin_M_0', vals)
+    for g, m in enumerate(singles):
+        for k, val in enumerate(vals):
+            m.betabin_M_0 = val
+            assert grid[g, k] == m.calculate_expected_log_likelihood(samples[g]), (g, k)
+    assert np.all(batch.betabin_M_0 == vals[-1])
+    # the E-step sees the new parameters of every fit
+    batch.variational_update(1)
+    for m in singles:
+        m.variational_update(1)
+    assert np.array_equal(batch.calculate_elbo(), np.array([m.calculate_elbo() for m in singles]))
+
+
+def test_fit_grid_batched_equals_per_fit_fits():
+    from remixt_b200 import pipeline
+    exp = util.load_experiment('small')
+    inits = dict((i, util.init_params('small', i)) for i in FITS[:5])
+    cfg = {'max_copy_number': 6, 'num_em_iter': 2, 'num_update_iter': 3}
+    res_b, best_b, err_b = pipeline.fit_grid_batched(exp, inits, cfg, num_threads=4)
+    res_s, best_s, err_s = pipeline.fit_grid(exp, inits, cfg, num_threads=1)
+    assert not err_b and not err_s
+    assert best_b == best_s
+    for i in inits:
+        assert res_b[i]['stats']['elbo'] == res_s[i]['stats']['elbo'], i
+        assert np.array_equal(res_b[i]['h'], res_s[i]['h'])
+        assert np.array_equal(res_b[i]['cn'], res_s[i]['cn'])
+        assert all(np.array_equal(res_b[i]['brk_cn'][k], res_s[i]['brk_cn'][k]) for k in res_s[i]['brk_cn'])
