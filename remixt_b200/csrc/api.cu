@@ -1129,7 +1129,8 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
 
 // launches the ELBO reductions of the handle's fits; results land in hp[g][0..9] after sync.
 // full = false: only the ELBO is wanted, so of sum joint*cached_T - sum joint*T only the breakend rows are
-// evaluated (everywhere else the two transition matrices are identical and the terms cancel exactly).
+// evaluated (everywhere else the two transition matrices are identical and the terms cancel exactly;
+// this needs both snapshots to have been taken under the same transition_model).
 static int elbo_terms(Model* m, bool full) {
     Batch* b = m->b.get();
     const int g0 = m->g0, gn = m->gn;
@@ -1165,7 +1166,7 @@ static int elbo_terms(Model* m, bool full) {
             if (rc) return;
             RmxTransSpec used = spec_of(b, false, b->tm_used[g]), cached = spec_of(b, true, b->tm_cached[g]);
             const bool upd = b->cn_updated[g] != 0;
-            if (upd && !full) {
+            if (upd && !full && b->tm_used[g] == b->tm_cached[g]) {
                 if (b->R > 0) {
                     rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
                                        b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
