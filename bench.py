@@ -195,6 +195,44 @@ def run_threads(fns):
         raise errs[0]
 
 
+def build_batch(exp, inits, device):
+    """One RemixtBatch for the given initialisations, built from HOST arrays through the public constructor
+    (the H2D copies happen inside), with the per-fit likelihood masks and transition model applied."""
+    from remixt_b200 import bpmodel, pipeline
+    drivers = [pipeline.build_model(exp, ip, CONFIG) for ip in inits]
+    h = np.array([pipeline.init_h(ip) for ip in inits])
+    dw = np.array([ip['divergence_weight'] for ip in inits], dtype=float)
+    args = drivers[0].model_args(h) + (dw,)
+    batch = bpmodel.RemixtBatch(*args, device=device)
+    same_masks = all(np.array_equal(d._total_likelihood_mask, drivers[0]._total_likelihood_mask) and
+                     np.array_equal(d._allele_likelihood_mask, drivers[0]._allele_likelihood_mask) for d in drivers)
+    if same_masks:       # max_depth is shared by the grid (analysis/pipeline.py:90-96): one upload for all fits
+        batch.total_likelihood_mask = drivers[0]._total_likelihood_mask.astype(int)
+        batch.allele_likelihood_mask = drivers[0]._allele_likelihood_mask.astype(int)
+        batch.transition_model = drivers[0].transition_model
+        for g, d in enumerate(drivers):
+            d.model = batch.fit(g)
+    else:
+        for g, d in enumerate(drivers):
+            d.attach(batch.fit(g))
+    h2d = sum(int(np.asarray(a).nbytes) for a in args if isinstance(a, np.ndarray)) + 2 * 8 * batch.num_segments * len(inits)
+    return batch, drivers, h2d
+
+
+# algorithmic work per (segment, state) of each kernel class: (bound, bytes, fp64 ops)  -- DESIGN.md, Kernels
+def kernel_models(N1, S, NC, G, R):
+    ns = float(N1) * S * G
+    return {
+        'chain': ('fp64', 32. * ns, 2. * 2. * S * S * (N1 - NC) * G),
+        'lltable': ('fp64', 48. * ns, 900. * ns),
+        'frame': ('hbm', 64. * ns, 14. * ns),
+        'qsums': ('hbm', 56. * ns, 12. * ns),
+        'post': ('hbm', 24. * ns, 3. * ns),
+        'hist': ('fp64', 0., 2. * 8. * S * S * R * G),
+        'elbo_rows': ('hbm', 16. * ns, 4. * ns),
+    }
+
+
 def gpu_arm(args):
     rank, world, local, dist = dist_setup(args.gpus)
     from remixt_b200 import _lib
@@ -207,78 +245,59 @@ def gpu_arm(args):
     my_inits = [inits[(rank * G + g) % len(inits)] for g in range(G)]
     peaks, peak_src = measured_peaks()
 
-    # ---------------- resident arm: models built once, inputs live in HBM
-    drivers = [make_driver(exp, ip, device=local) for ip in my_inits]
-    from remixt_b200 import pipeline
-    run_threads([(lambda d=d, ip=ip: d.prepare(pipeline.init_h(ip))) for d, ip in zip(drivers, my_inits)])
-    models = [d.model for d in drivers]
-    N1, S = models[0].num_segments, models[0].num_cn_states
-    elbos = [0.] * G
+    # ---------------- resident arm: batch built once, inputs live in HBM
+    batch, drivers, h2d = build_batch(exp, my_inits, local)
+    N1, S = batch.num_segments, batch.num_cn_states
+    NC = int(np.sum(np.asarray(batch.is_telomere)[:-1] > 0)) + 1
+    R = int(np.sum(np.asarray(batch.breakpoint_idx)[:-1] >= 0))
+    state = {}
 
-    def estep(g):
-        models[g].variational_update(NUM_UPDATE_ITER)
-        elbos[g] = models[g].calculate_elbo()
+    def estep():
+        batch.variational_update(NUM_UPDATE_ITER)
+        state['elbo'] = batch.calculate_elbo()
 
     def barrier():
-        for m in models:
-            m.synchronize()
+        batch.synchronize()
         if dist is not None:
             dist.barrier()
             import torch
             torch.cuda.synchronize()
 
-    def timed(nsteps, body):
-        barrier()
-        models[0].event_record(0)
-        for _ in range(nsteps):
-            body()
-        for m in models:
-            m.event_record(1)
-        barrier()
-        return max(models[0].event_elapsed(0, m, 1) for m in models)
-
-    step = lambda: run_threads([(lambda g=g: estep(g)) for g in range(G)])
     for _ in range(args.warmup):
-        step()
+        estep()
     sampler = ClockSampler(local)
     sampler.start()
+    barrier()
+    batch.kernel_timing(True)
     l0 = _lib.global_launch_count()
-    ms = timed(args.steps, step)
+    batch.event_record(0)
+    for _ in range(args.steps):
+        estep()
+    batch.event_record(1)
+    barrier()
+    ms = batch.event_elapsed(0, batch, 1)
     launches = _lib.global_launch_count() - l0
+    ktime = batch.kernel_timing(False)
     clocks = sampler.stop()
 
-    # ---------------- dominant kernel alone (chain messages), CUDA events on its stream
-    m0 = models[0]
-    m0.chain_timing(True)
-    for _ in range(3):
-        m0.update_p_cn()
-    m0.chain_timing(True)
-    for _ in range(5):
-        m0.update_p_cn()
-    chain_ms, chain_n = m0.chain_timing(False)
-    chain_ms_per = chain_ms / max(chain_n, 1)
+    # ---------------- e2e arm: the batch rebuilt from host arrays every step, results read back to the host
+    def e2e_step():
+        b2, d2, _ = build_batch(exp, my_inits, local)
+        b2.variational_update(NUM_UPDATE_ITER)
+        elbo = b2.calculate_elbo()
+        cn = np.zeros((G, b2.num_segments, b2.num_clones, 2), dtype=np.int64)
+        b2.infer_cn(cn)
+        out = (elbo, cn, b2.p_outlier_total, b2.p_outlier_allele, b2.h)
+        return sum(int(np.asarray(o).nbytes) for o in out)
 
-    # ---------------- e2e arm: models rebuilt from host arrays every step, results read back
-    h2d = d2h = 0
-
-    def e2e_fit(g):
-        d = make_driver(exp, my_inits[g], device=local)
-        d.prepare(pipeline.init_h(my_inits[g]))
-        d.model.variational_update(NUM_UPDATE_ITER)
-        out = (d.model.calculate_elbo(), d.model.p_outlier_total, d.model.p_outlier_allele,
-               d.model.posterior_marginals)
-        return out
-
-    e2e_step = lambda: run_threads([(lambda g=g: e2e_fit(g)) for g in range(G)])
-    e2e_step()
+    del state['elbo']
+    d2h = e2e_step()
     e2e_steps = max(1, min(args.steps, 3))
+    barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
-    nseg = m0.num_segments
-    h2d = G * (nseg * S * 3 * 2 * 8 + nseg * 8 * 9)          # cn_states (N1,S,M,2) i64 + per-segment arrays
-    d2h = G * (nseg * S * 8 + nseg * 4 * 8 + 8)
 
     if dist is not None:
         import torch
@@ -292,30 +311,54 @@ def gpu_arm(args):
     evals = float(N1) * S * NUM_UPDATE_ITER * G * world
     value = evals / (ms_per_step * 1e-3)
 
-    # roofline of the dominant kernel (chain messages): FP64 FMA work 2*S*S per segment per direction
-    flops = 2.0 * 2.0 * S * S * (N1 - 1)
+    # ---------------- rooflines from the CUDA-event durations of the timed region
     try:
         fp64_peak = _lib.fp64_peak(local)
     except Exception:
         fp64_peak = None
-    ach = flops / (chain_ms_per * 1e-3) / 1e12 if chain_ms_per > 0 else 0.
-    roofline = {'kernel': 'k_chain', 'bound': 'fp64', 'achieved': ach, 'peak': fp64_peak, 'unit': 'TFLOP/s',
-                'frac': (ach / fp64_peak) if fp64_peak else None, 'traffic': None,
-                'peak_source': 'DFMA micro-benchmark run in this process (rmx_fp64_peak)',
-                'hbm_peak_gbs': peaks.get('hbm_gbs'), 'hbm_peak_source': peak_src,
-                'launch_ms': chain_ms_per}
+    hbm_peak = peaks.get('hbm_gbs')
+    models = kernel_models(N1, S, NC, G, R)
+    total_kernel_ms = sum(v[0] for v in ktime.values())
+    kernels = {}
+    for k, (tot, n) in ktime.items():
+        if n == 0:
+            continue
+        ent = {'launches': n, 'ms_per_launch': tot / n, 'share_of_kernel_time': tot / total_kernel_ms}
+        if k in models:
+            bound, nbytes, flops = models[k]
+            t_s = tot / n * 1e-3
+            ent['bound'] = bound
+            ent['gbs'] = nbytes / t_s / 1e9
+            ent['tflops'] = flops / t_s / 1e12
+            ent['hbm_frac'] = ent['gbs'] / hbm_peak if hbm_peak else None
+            ent['fp64_frac'] = ent['tflops'] / fp64_peak if fp64_peak else None
+        kernels[k] = ent
+    dom = max(kernels, key=lambda k: kernels[k]['share_of_kernel_time'] if k in models else -1.)
+    de = kernels[dom]
+    if de['bound'] == 'hbm':
+        roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': de['gbs'], 'peak': hbm_peak, 'unit': 'GB/s',
+                    'frac': de['hbm_frac'], 'traffic': None, 'peak_source': 'MEASURED_PEAKS.json (%s)' % peak_src}
+    else:
+        roofline = {'kernel': dom, 'bound': 'fp64', 'achieved': de['tflops'], 'peak': fp64_peak, 'unit': 'TFLOP/s',
+                    'frac': de['fp64_frac'], 'traffic': None,
+                    'peak_source': 'FP64 FMA micro-benchmark run in this process (rmx_fp64_peak); not in MEASURED_PEAKS.json',
+                    'hbm_achieved_gbs': de['gbs'], 'hbm_peak_gbs': hbm_peak, 'hbm_frac': de['hbm_frac']}
+    roofline['launch_ms'] = de['ms_per_launch']
+    roofline['share_of_step'] = de['ms_per_launch'] * de['launches'] / ms
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f64', 'data': 'synthetic (remixt.simulations genome, fixture exp_%s.npz)' % name,
         'config': {'workload': name, 'segments': int(exp.x.shape[0]), 'model_segments': int(N1), 'cn_states': int(S),
-                   'breakpoints': int(models[0].num_breakpoints), 'fits_per_gpu': G, 'vi_updates_per_step': NUM_UPDATE_ITER,
-                   'l2': 'per-step working set %.1f GB > 126 MB L2' % (G * N1 * S * 8 * 11 / 1e9)},
+                   'breakpoints': int(batch.num_breakpoints), 'chains': NC, 'fits_per_gpu': G,
+                   'vi_updates_per_step': NUM_UPDATE_ITER,
+                   'l2': 'inputs larger than L2: per-step working set %.1f GB vs 126 MB' % (G * N1 * S * 8 * 11 / 1e9)},
+        'em_iterations_per_s': G * world / (ms_per_step * 1e-3),
         'clocks': clocks, 'gpu_launches': int(launches),
         'e2e': {'value': evals / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
                 'ms_per_step': e2e_s * 1e3},
-        'roofline': roofline,
-        'elbo_checksum': float(np.sum(elbos)),
+        'roofline': roofline, 'kernels': kernels,
+        'elbo_checksum': float(np.sum(batch.calculate_elbo())),
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(exp, inits, args.cpu_sample_segments, budget_s=20.)

@@ -198,8 +198,16 @@ int rmx_max_product(int device, int64_t n_obs, int64_t n_comp, const double* fra
 int rmx_launch_count(rmx_handle h, int64_t* count);
 /* Number of kernels launched by the whole library in this process. */
 int rmx_global_launch_count(int64_t* count);
-/* Device-side duration (CUDA events on the handle's stream) of the chain-message kernel
- * launches since the last reset: total milliseconds and number of launches. */
+/* Kernel classes of rmx_kernel_timing. */
+typedef enum {
+    RMX_K_CHAIN = 0, RMX_K_LLTABLE = 1, RMX_K_FRAME = 2, RMX_K_QSUMS = 3, RMX_K_POST = 4, RMX_K_HIST = 5,
+    RMX_K_BRK_UPDATE = 6, RMX_K_ELBO_ROWS = 7, RMX_K_PAIRSUM = 8, RMX_K_ELL = 9, RMX_K_COUNT_ = 10
+} rmx_kernel_class;
+/* Device-side duration (CUDA events on the batch's stream around every launch) of each kernel class since
+ * the last call: total milliseconds and number of launches, arrays of RMX_K_COUNT_; then switches the
+ * timing on or off.  Durations are collected at the next synchronising call. */
+int rmx_kernel_timing(rmx_handle h, int enable, double* total_ms, int64_t* launches);
+/* The same for the chain-message kernel alone (scalars). */
 int rmx_chain_timing(rmx_handle h, int enable, double* total_ms, int64_t* launches);
 int rmx_synchronize(rmx_handle h);
 /* The cudaStream_t the handle launches on (for CUDA-event timing by the caller). */

@@ -25,6 +25,8 @@ SCALAR_IDS = {
     'divergence_weight': 13, 'transition_model': 14, 'hmm_log_norm_const': 15,
 }
 
+KERNEL_CLASSES = ['chain', 'lltable', 'frame', 'qsums', 'post', 'hist', 'brk_update', 'elbo_rows', 'pairsum', 'ell']
+
 # rmx_update_id
 U_ALLELE_SWAP, U_CN, U_BREAKPOINT, U_OUTLIER_TOTAL, U_OUTLIER_ALLELE, U_FRAMELOGPROB = range(6)
 
@@ -38,7 +40,7 @@ EXPORTS = [
     'rmx_expected_log_likelihood_grid',
     'rmx_infer_cn', 'rmx_calculate_log_transmat', 'rmx_eval',
     'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product',
-    'rmx_launch_count', 'rmx_global_launch_count', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
+    'rmx_launch_count', 'rmx_global_launch_count', 'rmx_kernel_timing', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
     'rmx_event_record', 'rmx_event_elapsed', 'rmx_fp64_peak',
 ]
 
@@ -91,6 +93,7 @@ def _load():
         'rmx_max_product': [I, I64, I64, P, P, P, C.POINTER(D)],
         'rmx_launch_count': [H, C.POINTER(I64)],
         'rmx_global_launch_count': [C.POINTER(I64)],
+        'rmx_kernel_timing': [H, I, P, P],
         'rmx_chain_timing': [H, I, C.POINTER(D), C.POINTER(I64)],
         'rmx_synchronize': [H],
         'rmx_stream': [H, C.POINTER(P)],

@@ -376,6 +376,14 @@ class _ModelBase(object):
         check(lib.rmx_chain_timing(self._handle, 1 if enable else 0, C.byref(ms), C.byref(n)), self._handle)
         return ms.value, n.value
 
+    def kernel_timing(self, enable=True):
+        """``{kernel class: (total_ms, launches)}`` of the batch's launches since the last call (CUDA events on
+        its stream); switches the timing on or off."""
+        ms = np.zeros(len(_lib.KERNEL_CLASSES))
+        n = np.zeros(len(_lib.KERNEL_CLASSES), dtype=np.int64)
+        check(lib.rmx_kernel_timing(self._handle, 1 if enable else 0, _ptr(ms), _ptr(n)), self._handle)
+        return dict((k, (float(ms[i]), int(n[i]))) for i, k in enumerate(_lib.KERNEL_CLASSES))
+
     def synchronize(self):
         check(lib.rmx_synchronize(self._handle), self._handle)
 

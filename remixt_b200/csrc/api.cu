@@ -85,17 +85,31 @@ struct Batch {
     int* hrows = nullptr;       // G*N ints
     int* hRn = nullptr;         // G ints
 
-    // chain timing (CUDA events around the chain kernel)
+    // per-kernel-class timing (CUDA events on the stream around each launch, when enabled)
     bool timing = false;
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> tev;
-    double chain_ms = 0.;
-    int64_t chain_launches = 0;
+    struct Tev { int cls; cudaEvent_t e0, e1; };
+    std::vector<Tev> tev;
+    double cls_ms[RMX_K_COUNT_] = {};
+    int64_t cls_n[RMX_K_COUNT_] = {};
     int64_t launches = 0;
+    cudaEvent_t tbegin(int cls) {
+        if (!timing) return nullptr;
+        Tev t;
+        t.cls = cls;
+        cudaEventCreate(&t.e0);
+        cudaEventCreate(&t.e1);
+        cudaEventRecord(t.e0, stream);
+        tev.push_back(t);
+        return t.e1;
+    }
+    void tend(cudaEvent_t e1) {
+        if (e1) cudaEventRecord(e1, stream);
+    }
 
     ~Batch() {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);
-        for (auto& pr : tev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        for (auto& t : tev) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
         for (void* p : allocs) cudaFree(p);
         if (hp) cudaFreeHost(hp);
         if (hflags) cudaFreeHost(hflags);
@@ -249,7 +263,7 @@ static int ensure_ll(Model* m, int g0, int gn) {
     std::vector<int> key(b->G, 0);
     for_runs(g0, gn, key, &b->ll_dirty, [&](int g, int n) {
         rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc);
-        rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags);
+        { cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE); rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags); b->tend(te_); }
         b->count(2);
         for (int k = g; k < g + n; ++k) { b->ll_dirty[k] = 0; b->asum_valid[k] = 0; }
     });
@@ -265,7 +279,7 @@ static int ensure_asum(Model* m, int g0, int gn) {
     std::vector<char> need(b->G, 0);
     for (int g = g0; g < g0 + gn; ++g) need[g] = !b->asum_valid[g];
     for_runs(g0, gn, key, &need, [&](int g, int n) {
-        rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum);
+        { cudaEvent_t te_ = b->tbegin(RMX_K_QSUMS); rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum); b->tend(te_); }
         b->count();
         for (int k = g; k < g + n; ++k) b->asum_valid[k] = 1;
     });
@@ -300,14 +314,14 @@ static int sync_check(Model* m) {
         snprintf(buf, sizeof buf, "CUDA error %s: %s", cudaGetErrorName(e), cudaGetErrorString(e));
         return m->fail(RMX_ERR_CUDA, buf);
     }
-    for (auto& pr : b->tev) {
+    for (auto& t : b->tev) {
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) {
-            b->chain_ms += ms;
-            b->chain_launches += 1;
+        if (cudaEventElapsedTime(&ms, t.e0, t.e1) == cudaSuccess) {
+            b->cls_ms[t.cls] += ms;
+            b->cls_n[t.cls] += 1;
         }
-        cudaEventDestroy(pr.first);
-        cudaEventDestroy(pr.second);
+        cudaEventDestroy(t.e0);
+        cudaEventDestroy(t.e1);
     }
     b->tev.clear();
     int f = *b->hflags;
@@ -327,8 +341,8 @@ static int do_update_framelogprob(Model* m) {
     Batch* b = m->b.get();
     int rc = ensure_ll(m, m->g0, m->gn);
     if (rc) return rc;
-    rmx_launch_frame(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->q_ot, b->q_oa, b->q_sw, b->F, b->fexp,
-                     b->mF, b->dflags);
+    { cudaEvent_t te_ = b->tbegin(RMX_K_FRAME); rmx_launch_frame(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->q_ot, b->q_oa, b->q_sw, b->F, b->fexp,
+                     b->mF, b->dflags); b->tend(te_); }
     b->count();
     return RMX_OK;
 }
@@ -344,29 +358,21 @@ static int do_update_p_cn(Model* m) {
     for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
         if (lc) return;
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
-        cudaEvent_t e0 = nullptr, e1 = nullptr;
-        if (b->timing) {
-            cudaEventCreate(&e0);
-            cudaEventCreate(&e1);
-            cudaEventRecord(e0, b->stream);
-        }
+        cudaEvent_t te = b->tbegin(RMX_K_CHAIN);
         lc = rmx_launch_chain(b->stream, tables(b), b->d, chainsof(b), rowsof(b), sp, b->rmd, g, n, b->fexp, b->mF,
                               b->ahat, b->bhat, b->chain_logz, b->dflags);
-        if (b->timing) {
-            cudaEventRecord(e1, b->stream);
-            b->tev.push_back({e0, e1});
-        }
+        b->tend(te);
         b->count();
     });
     if (lc == 2) return m->fail(RMX_ERR_UNSUPPORTED, "this number of copy number states is not supported by the chain kernel");
     if (lc) return m->fail(RMX_ERR_CUDA, "could not configure shared memory for the chain kernel");
     rmx_launch_reduce_cols(b->stream, b->chain_logz, b->NC, 1, g0, gn, b->NC, b->red_out + 15, Batch::RED);
-    rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags);
+    { cudaEvent_t te_ = b->tbegin(RMX_K_POST); rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags); b->tend(te_); }
     b->count(2);
     for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
-        rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
-                        b->dflags);
+        { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
+                        b->dflags); b->tend(te_); }
         if (b->R > 0) b->count();
     });
     for (int g = g0; g < g0 + gn; ++g) {
@@ -389,16 +395,16 @@ static int do_update_p_breakpoint(Model* m) {
         for (int g = g0; g < g0 + gn; ++g) need[g] = !b->hist_valid[g];
         for_runs(g0, gn, b->tm_cached, &need, [&](int g, int n) {
             RmxTransSpec sp = spec_of(b, true, b->tm_cached[g]);
-            rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 1, b->ahat, b->bhat, b->fexp,
-                            b->hist, b->dflags);
+            { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 1, b->ahat, b->bhat, b->fexp,
+                            b->hist, b->dflags); b->tend(te_); }
             b->count();
             for (int k = g; k < g + n; ++k) b->hist_valid[k] = 1;
         });
     }
     if (b->d.K > 0) {
         for_runs(g0, gn, b->tm, nullptr, [&](int g, int n) {
-            rmx_launch_brk_update(b->stream, b->d, g, n, b->krow_ptr, b->krow_idx, b->brk_rows, b->borient, b->brk, b->hist,
-                                  b->rmd, b->pen, b->tm[g], b->p_brk);
+            { cudaEvent_t te_ = b->tbegin(RMX_K_BRK_UPDATE); rmx_launch_brk_update(b->stream, b->d, g, n, b->krow_ptr, b->krow_idx, b->brk_rows, b->borient, b->brk, b->hist,
+                                  b->rmd, b->pen, b->tm[g], b->p_brk); b->tend(te_); }
             b->count();
         });
     }
@@ -1141,8 +1147,8 @@ static int elbo_terms(Model* m, bool full) {
     const RmxDims& d = b->d;
     RmxTables T = tables(b);
     const int RED = Batch::RED;
-    rmx_launch_elbo_rows(b->stream, T, d, b->dP, g0, gn, b->Asum, b->post, b->F, b->q_ot, b->q_oa, b->q_sw, b->prior_ot,
-                         b->prior_oa, b->rowv);
+    { cudaEvent_t te_ = b->tbegin(RMX_K_ELBO_ROWS); rmx_launch_elbo_rows(b->stream, T, d, b->dP, g0, gn, b->Asum, b->post, b->F, b->q_ot, b->q_oa, b->q_sw, b->prior_ot,
+                         b->prior_oa, b->rowv); b->tend(te_); }
     rmx_launch_reduce_cols(b->stream, b->rowv, d.N, 7, g0, gn, (int64_t)8 * d.N, b->red_out, RED);
     b->count(2);
     // entropy of p_breakpoint
@@ -1168,19 +1174,19 @@ static int elbo_terms(Model* m, bool full) {
             const bool upd = b->cn_updated[g] != 0;
             if (upd && !full && b->tm_used[g] == b->tm_cached[g]) {
                 if (b->R > 0) {
-                    rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
-                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                    { cudaEvent_t te_ = b->tbegin(RMX_K_PAIRSUM); rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
+                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N); b->tend(te_); }
                     rmx_launch_reduce_cols(b->stream, b->rowsum, b->R, 1, g, n, d.N, b->red_out + 8, RED);
                     b->count(2);
                 }
             } else {
-                rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, cached, 0, b->rmd, nullptr, d.N - 1,
-                                   upd ? 0 : 1, b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                { cudaEvent_t te_ = b->tbegin(RMX_K_PAIRSUM); rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, cached, 0, b->rmd, nullptr, d.N - 1,
+                                   upd ? 0 : 1, b->ahat, b->bhat, b->fexp, b->rowsum, d.N); b->tend(te_); }
                 rmx_launch_reduce_cols(b->stream, b->rowsum, d.N - 1, 1, g, n, d.N, b->red_out + 8, RED);
                 b->count(2);
                 if (upd) {
-                    rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, used, used, 0, b->rmd, nullptr, d.N - 1, 0,
-                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                    { cudaEvent_t te_ = b->tbegin(RMX_K_PAIRSUM); rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, used, used, 0, b->rmd, nullptr, d.N - 1, 0,
+                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N); b->tend(te_); }
                     rmx_launch_reduce_cols(b->stream, b->rowsum, d.N - 1, 1, g, n, d.N, b->red_out + 9, RED);
                     b->count(2);
                 }
@@ -1257,8 +1263,8 @@ static int launch_ell(Model* m, const int* rows, int Rmax, int slot) {
     const int g0 = m->g0, gn = m->gn;
     rmx_launch_segconst(b->stream, T, b->d, b->dP, g0, gn, rows, b->d_Rn, Rmax, b->segc_s);
     const int nb = rmx_ell_blocks(b->d, Rmax);
-    rmx_launch_ell(b->stream, T, b->d, b->dP, g0, gn, rows, b->d_Rn, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
-                   b->part, b->part_stride, b->dflags);
+    { cudaEvent_t te_ = b->tbegin(RMX_K_ELL); rmx_launch_ell(b->stream, T, b->d, b->dP, g0, gn, rows, b->d_Rn, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
+                   b->part, b->part_stride, b->dflags); b->tend(te_); }
     rmx_launch_reduce_cols(b->stream, b->part, nb, 1, g0, gn, b->part_stride, b->red_out + slot, Batch::RED);
     b->count(3);
     return RMX_OK;
@@ -1563,15 +1569,26 @@ int rmx_global_launch_count(int64_t* count) {
     *count = g_launches.load();
     return RMX_OK;
 }
-int rmx_chain_timing(rmx_handle m, int enable, double* total_ms, int64_t* launches) {
+int rmx_kernel_timing(rmx_handle m, int enable, double* total_ms, int64_t* launches) {
     if (!m) return RMX_ERR_ARG;
     Batch* b = m->b.get();
     Lock lk(b->mu);
-    if (total_ms) *total_ms = b->chain_ms;
-    if (launches) *launches = b->chain_launches;
-    b->chain_ms = 0.;
-    b->chain_launches = 0;
+    for (int c = 0; c < RMX_K_COUNT_; ++c) {
+        if (total_ms) total_ms[c] = b->cls_ms[c];
+        if (launches) launches[c] = b->cls_n[c];
+        b->cls_ms[c] = 0.;
+        b->cls_n[c] = 0;
+    }
     b->timing = enable != 0;
+    return RMX_OK;
+}
+int rmx_chain_timing(rmx_handle m, int enable, double* total_ms, int64_t* launches) {
+    double ms[RMX_K_COUNT_];
+    int64_t n[RMX_K_COUNT_];
+    int rc = rmx_kernel_timing(m, enable, ms, n);
+    if (rc) return rc;
+    if (total_ms) *total_ms = ms[RMX_K_CHAIN];
+    if (launches) *launches = n[RMX_K_CHAIN];
     return RMX_OK;
 }
 int rmx_synchronize(rmx_handle m) {
