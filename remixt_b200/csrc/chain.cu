@@ -145,6 +145,13 @@ struct ChainArgs {
     int* dflags;
 };
 
+// biased exponent field of a non-negative double (0 for zero / denormal, 2047 for inf / NaN)
+__device__ __forceinline__ int dexp_field(double v) { return (__double2hiint(v) >> 20) & 0x7ff; }
+// 2^(1023 - be): the power of two that brings a value with exponent field be into [1, 2)
+__device__ __forceinline__ double pow2_scale(int be) { return __hiloint2double((2046 - be) << 20, 0); }
+
+#define RMX_EPI 3    // epilogue slots per thread (3 * threads >= GT * SJ, checked by the launcher)
+
 template <int RR, int CW, int GT, bool REG>
 __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -154,11 +161,13 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     const int Sp = Q * rr;                 // padded number of rows (>= S)
     const int SJ = (S + 31) & ~31;         // epilogue slots per fit
     const int NCH = SJ >> 5;               // warps (chunks) per fit in the epilogue
-    double* u = reinterpret_cast<double*>(smem_raw);        // [2][GT][Sp]
-    double* part = u + 2 * GT * Sp;                          // [Q][GT][CW][NJ]
-    double* red = part + Q * GT * CW * NJ;                   // [2][GT][NCH]
-    double* wtab = red + 2 * GT * NCH;                       // [GT][M*D]
-    int8_t* tots = reinterpret_cast<int8_t*>(wtab + GT * M * d.D);   // [S*M]
+    const int MD = M * d.D;
+    double* u = reinterpret_cast<double*>(smem_raw);        // [2][GT][Sp]   messages (double buffered)
+    double* part = u + 2 * GT * Sp;                          // [Q][GT][CW][NJ] slice partial sums
+    double* wtab = part + Q * GT * CW * NJ;                  // [GT][M*D]     breakend tables of the step
+    double* redd = wtab + GT * MD;                           // [GT][NCH]     sums of the last message
+    int* redi = reinterpret_cast<int*>(redd + GT * NCH);     // [2][GT][NCH]  max exponent fields
+    int8_t* tots = reinterpret_cast<int8_t*>(redi + 2 * GT * NCH);   // [S*M]
 
     const int tile = blockIdx.x % A.ntiles;
     const int cd = blockIdx.x / A.ntiles;
@@ -168,42 +177,59 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     const int jg = t % NJ, q = t / NJ;
     const bool act = q < Q;
     const int i0 = q * rr, j0 = jg * CW;
-    const int lane = t & 31;
     const int64_t SS = (int64_t)S * S;
     const int64_t NS = (int64_t)d.N * S;
     const int gbase = A.g0 + tile * GT;                      // first fit of the tile
     const int gcount = min(GT, A.g0 + A.gn - gbase);         // live fits in the tile
+    const int QS = GT * CW * NJ;                             // part stride between row slices
 
     for (int e = t; e < 2 * GT * Sp; e += blockDim.x) u[e] = 0.;
-    for (int e = t; e < 2 * GT * NCH; e += blockDim.x) red[e] = 0.;
+    for (int e = t; e < 2 * GT * NCH; e += blockDim.x) redi[e] = 1023;   // first message: max f = 1
     for (int e = t; e < S * M; e += blockDim.x) {
         int s = e / M, m = e - s * M;
         tots[e] = (m == 0) ? 0 : (int8_t)(A.tab[(s * M + m) * 2] + A.tab[(s * M + m) * 2 + 1]);
     }
+
+    // ---- per-thread epilogue slots: slot -> (fit g, column j), consecutive j per lane, one fit per warp
+    int sl_u[RMX_EPI], sl_p[RMX_EPI], sl_r[RMX_EPI];
+    int64_t sl_g[RMX_EPI];
+    bool sl_ok[RMX_EPI], sl_lead[RMX_EPI];
+#pragma unroll
+    for (int e = 0; e < RMX_EPI; ++e) {
+        const int slot = t + e * blockDim.x;
+        const int g = slot / SJ, j = slot - g * SJ;
+        sl_ok[e] = slot < GT * SJ && j < S && g < gcount;
+        sl_lead[e] = sl_ok[e] && j == 0;
+        sl_u[e] = g * Sp + j;
+        sl_p[e] = (g * CW + (j % CW)) * NJ + j / CW;
+        sl_r[e] = slot < GT * SJ ? g * NCH + (j >> 5) : -1;
+        sl_g[e] = (int64_t)(gbase + g) * NS + j;
+    }
     __syncthreads();
 
-    // ---- first segment of the sweep: u = f (forward) or u = f, bhat = 1 (backward)
+    // ---- first segment of the sweep: u = f (forward: ahat = f; backward: bhat = 1)
     {
         const int n = dir == 0 ? s0 : s1;
-        for (int slot = t; slot < GT * SJ; slot += blockDim.x) {
-            const int g = slot / SJ, j = slot - g * SJ;
-            double v = 0.;
-            if (j < S && g < gcount) {
-                const int64_t o = (int64_t)(gbase + g) * NS + (int64_t)n * S + j;
-                v = A.fexp[o];
+#pragma unroll
+        for (int e = 0; e < RMX_EPI; ++e)
+            if (sl_ok[e]) {
+                const int64_t o = sl_g[e] + (int64_t)n * S;
+                const double v = A.fexp[o];
                 if (dir == 0) A.ahat[o] = v; else A.bhat[o] = 1.;
-                u[g * Sp + j] = v;
+                u[sl_u[e]] = v;
             }
-            double w = warp_sum(v);
-            if (lane == 0) red[g * NCH + (j >> 5)] = w;
-        }
         __syncthreads();
     }
 
     double ereg[REG ? RR : 1][REG ? CW : 1];
     int cur_class = -1;
     int cur = 0;
-    double logz = 0.;     // thread g < GT of warp 0 accumulates fit g's log normaliser
+    // the lead thread of fit g (slot with j == 0) accumulates the fit's log normaliser:
+    // logZ = log(sum of the last message) + ln2 * esum + sum_n max F[n]
+    double mfsum[RMX_EPI];
+    int esum[RMX_EPI];
+#pragma unroll
+    for (int e = 0; e < RMX_EPI; ++e) { mfsum[e] = 0.; esum[e] = 0; }
     int bad = 0;
 
     const int nsteps = s1 - s0;
@@ -213,16 +239,12 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
         const int prev = dir == 0 ? n - 1 : n + 1;                // segment whose message is the input
         const int cls = A.rows.tclass[row];
         const int br = A.rows.brow[row];
-        const double* uin = u + cur * GT * Sp;
+        const double* uin = u + cur * GT * Sp + i0;
 
         // this step's f, fetched early (used in the epilogue)
-        double fpre[3];
+        double fpre[RMX_EPI];
 #pragma unroll
-        for (int e = 0; e < 3; ++e) {
-            const int slot = t + e * blockDim.x;
-            const int g = slot / SJ, j = slot - g * SJ;
-            fpre[e] = (slot < GT * SJ && j < S && g < gcount) ? A.fexp[(int64_t)(gbase + g) * NS + (int64_t)n * S + j] : 0.;
-        }
+        for (int e = 0; e < RMX_EPI; ++e) fpre[e] = sl_ok[e] ? A.fexp[sl_g[e] + (int64_t)n * S] : 0.;
 
         double acc[GT][CW];
 #pragma unroll
@@ -247,7 +269,7 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
                 for (int k = 0; k < RR; ++k) {
                     double v[GT];
 #pragma unroll
-                    for (int g = 0; g < GT; ++g) v[g] = uin[g * Sp + i0 + k];
+                    for (int g = 0; g < GT; ++g) v[g] = uin[g * Sp + k];
 #pragma unroll
                     for (int g = 0; g < GT; ++g)
 #pragma unroll
@@ -255,76 +277,93 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
                 }
             } else if (act) {
                 const int kmax = min(rr, S - i0);
+#pragma unroll 1
                 for (int k = 0; k < kmax; ++k) {
                     double e[CW];
 #pragma unroll
                     for (int c = 0; c < CW; ++c) e[c] = (j0 + c < S) ? E[(int64_t)(i0 + k) * S + j0 + c] : 0.;
 #pragma unroll
                     for (int g = 0; g < GT; ++g) {
-                        const double v = uin[g * Sp + i0 + k];
+                        const double v = uin[g * Sp + k];
 #pragma unroll
                         for (int c = 0; c < CW; ++c) acc[g][c] = fma(v, e[c], acc[g][c]);
                     }
                 }
             }
         } else {
-            // breakend row: E_n[from][to] = flipE[cls][from][to] * prod_m wexp[g][r][m][tot_from - tot_to], per fit
-            for (int e = t; e < GT * M * d.D; e += blockDim.x) {
-                const int g = e / (M * d.D), o = e - g * (M * d.D);
+            // breakend row (rare): E_n[from][to] = flipE[cls][from][to] * prod_m wexp[g][r][m][tot_from - tot_to].
+            // The m = 0 factor (normal copies) does not depend on the states: applied once at the end.
+            for (int e = t; e < GT * MD; e += blockDim.x) {
+                const int g = e / MD, o = e - g * MD;
                 const int gg = gbase + min(g, gcount - 1);
-                wtab[e] = A.sp.wexp[(int64_t)gg * A.sp_fit_stride + (int64_t)br * M * d.D + o];
+                wtab[e] = A.sp.wexp[(int64_t)gg * A.sp_fit_stride + (int64_t)br * MD + o];
             }
             __syncthreads();
             if (act) {
                 const double* FE = A.sp.flipE + (int64_t)cls * SS;
-                const int d0 = A.rows.d0[row];
                 const int kmax = min(rr, S - i0);
+                const int sgn = dir == 0 ? 1 : -1;    // forward: from = row index; backward: from = column index
+#pragma unroll 1
                 for (int k = 0; k < kmax; ++k) {
                     const int ir = i0 + k;
-#pragma unroll
+#pragma unroll 1
                     for (int c = 0; c < CW; ++c) {
                         const int jc = j0 + c;
-                        if (jc < S) {
-                            const double fe = FE[(int64_t)ir * S + jc];
+                        if (jc >= S) break;
+                        const double fe = FE[(int64_t)ir * S + jc];
+                        double w[GT];
 #pragma unroll
-                            for (int g = 0; g < GT; ++g) {
-                                const double* wt = wtab + g * M * d.D;
-                                // forward: from-state ir (summed), to-state jc; backward: from-state jc, to-state ir
-                                const double e = dir == 0 ? brk_E(wt, tots, M, d.D, d.doff, d0, ir, jc, fe)
-                                                          : brk_E(wt, tots, M, d.D, d.doff, d0, jc, ir, fe);
-                                acc[g][c] = fma(uin[g * Sp + ir], e, acc[g][c]);
-                            }
+                        for (int g = 0; g < GT; ++g) w[g] = fe * uin[g * Sp + k];
+                        for (int m = 1; m < M; ++m) {
+                            const int dd = m * d.D + sgn * ((int)tots[ir * M + m] - (int)tots[jc * M + m]) + d.doff;
+#pragma unroll
+                            for (int g = 0; g < GT; ++g) w[g] *= wtab[g * MD + dd];
                         }
+                        // acc[g][c] with a runtime c: select through a switch-free unrolled compare
+#pragma unroll
+                        for (int cc = 0; cc < CW; ++cc)
+                            if (cc == c) {
+#pragma unroll
+                                for (int g = 0; g < GT; ++g) acc[g][cc] += w[g];
+                            }
                     }
+                }
+                const int d0 = A.rows.d0[row];
+#pragma unroll
+                for (int g = 0; g < GT; ++g) {
+                    const double w0 = wtab[g * MD + d0 + d.doff];
+#pragma unroll
+                    for (int c = 0; c < CW; ++c) acc[g][c] *= w0;
                 }
             }
         }
         if (act) {
+            double* pp = part + q * QS + jg;
 #pragma unroll
             for (int g = 0; g < GT; ++g)
 #pragma unroll
-                for (int c = 0; c < CW; ++c) part[((q * GT + g) * CW + c) * NJ + jg] = acc[g][c];
+                for (int c = 0; c < CW; ++c) pp[(g * CW + c) * NJ] = acc[g][c];
         }
         __syncthreads();
 
-        // ---- epilogue: slot -> (fit g, column j), consecutive j per lane
+        // ---- epilogue: combine the Q slices, rescale by the power of two that brought the PREVIOUS message's
+        // largest entry into [1, 2) (exact; its exponent goes to the log normaliser), multiply by f_n
         double* uout = u + (cur ^ 1) * GT * Sp;
-        const double* redp = red + cur * GT * NCH;
-        double* redn = red + (cur ^ 1) * GT * NCH;
+        const int* redp = redi + cur * GT * NCH;
+        int* redn = redi + (cur ^ 1) * GT * NCH;
 #pragma unroll
-        for (int e = 0; e < 3; ++e) {
-            const int slot = t + e * blockDim.x;
-            if (slot < GT * SJ) {                                  // warp-uniform: GT*SJ is a multiple of 32
-                const int g = slot / SJ, j = slot - g * SJ;
-                double sprev = 0.;
-                for (int c2 = 0; c2 < NCH; ++c2) sprev += redp[g * NCH + c2];
-                double v = 0., un = 0.;
-                if (j < S && g < gcount) {
-                    const int c = j % CW, jj = j / CW;
-                    double a = 0.;
-                    for (int qq = 0; qq < Q; ++qq) a += part[((qq * GT + g) * CW + c) * NJ + jj];
-                    v = a / sprev;
-                    const int64_t o = (int64_t)(gbase + g) * NS + (int64_t)n * S + j;
+        for (int e = 0; e < RMX_EPI; ++e) {
+            if (sl_r[e] >= 0) {                                    // warp-uniform (GT*SJ is a multiple of 32)
+                const int rbase = sl_r[e] - (sl_r[e] % NCH);
+                int be = redp[rbase];
+                for (int c2 = 1; c2 < NCH; ++c2) be = max(be, redp[rbase + c2]);
+                double un = 0.;
+                if (sl_ok[e]) {
+                    const double* pq = part + sl_p[e];
+                    double a = pq[0];
+                    for (int qq = 1; qq < Q; ++qq) a += pq[qq * QS];
+                    double v = a * pow2_scale(be);
+                    const int64_t o = sl_g[e] + (int64_t)n * S;
                     if (dir == 0) {
                         v *= fpre[e];
                         un = v;
@@ -333,36 +372,45 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
                         un = v * fpre[e];
                         A.bhat[o] = v;
                     }
-                    uout[g * Sp + j] = un;
+                    uout[sl_u[e]] = un;
                 }
-                const double w = warp_sum(un);
-                if (lane == 0) redn[g * NCH + (j >> 5)] = w;
-                if (j == 0 && g < gcount) {
-                    // s_prev is the sum of the message of segment `prev`: log normaliser of the forward sweep
-                    if (dir == 0) logz += log(sprev) + A.mF[(int64_t)(gbase + g) * d.N + prev];
-                    if (!(sprev > 0.) || isinf(sprev)) bad = 1;
+                const int mx = __reduce_max_sync(0xffffffffu, dexp_field(un));
+                if ((t & 31) == 0) redn[sl_r[e]] = mx;
+                if (sl_lead[e]) {
+                    esum[e] += be - 1023;
+                    mfsum[e] += A.mF[(int64_t)(sl_g[e] / NS) * d.N + prev];
+                    if (be <= 0 || be >= 2047) bad = 1;
                 }
             }
         }
         cur ^= 1;
         __syncthreads();
     }
-    // the last message's own sum closes the forward log normaliser
-    for (int slot = t; slot < GT * SJ; slot += blockDim.x) {
-        const int g = slot / SJ, j = slot - g * SJ;
-        if (j == 0 && g < gcount) {
+    // ---- the last message's own sum closes the forward log normaliser
+#pragma unroll
+    for (int e = 0; e < RMX_EPI; ++e)
+        if (sl_r[e] >= 0) {
+            const double w = warp_sum(sl_ok[e] ? u[cur * GT * Sp + sl_u[e]] : 0.);
+            if ((t & 31) == 0) redd[sl_r[e]] = w;
+        }
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < RMX_EPI; ++e)
+        if (sl_lead[e]) {
             double slast = 0.;
-            for (int c2 = 0; c2 < NCH; ++c2) slast += red[cur * GT * NCH + g * NCH + c2];
+            for (int c2 = 0; c2 < NCH; ++c2) slast += redd[sl_r[e] + c2];
+            const int g = (int)(sl_g[e] / NS);
             const int last = dir == 0 ? s1 : s0;
             if (dir == 0) {
-                logz += log(slast) + A.mF[(int64_t)(gbase + g) * d.N + last];
-                A.chain_logz[(int64_t)(gbase + g) * A.ch.NC + chain] = logz;
+                const double logz = log(slast) + 0.693147180559945309417 * (double)esum[e] + mfsum[e] + A.mF[(int64_t)g * d.N + last];
+                A.chain_logz[(int64_t)g * A.ch.NC + chain] = logz;
+                if (isnan(logz)) bad = 1;
             }
-            if (!(slast > 0.) || isinf(slast) || isnan(logz)) bad = 1;
+            if (!(slast > 0.) || isinf(slast)) bad = 1;
             if (bad) atomicOr(A.dflags, RMX_F_MSG_NAN);
         }
-    }
 }
+
 // posterior marginals: post[g,n] = normalise(ahat[g,n] .* bhat[g,n]), one warp per (fit, segment)
 __global__ void __launch_bounds__(256) k_post(RmxDims d, int g0, const double* __restrict__ ahat,
                                               const double* __restrict__ bhat, double* __restrict__ post,
@@ -959,9 +1007,9 @@ static int launch_chain_cfg(cudaStream_t st, ChainArgs& A, int Q, int rr) {
     A.ntiles = (A.gn + GT - 1) / GT;
     const int Sp = Q * rr, SJ = (d.S + 31) & ~31, NCH = SJ >> 5;
     const int threads = ((Q * NJ + 31) / 32) * 32;
-    if (threads > (REG ? 256 : 512) || 3 * threads < GT * SJ) return 2;
-    size_t smem = sizeof(double) * ((size_t)2 * GT * Sp + (size_t)Q * GT * CW * NJ + 2 * GT * NCH + (size_t)GT * d.M * d.D) +
-                  (size_t)d.S * d.M + 16;
+    if (threads > (REG ? 256 : 512) || RMX_EPI * threads < GT * SJ) return 2;
+    size_t smem = sizeof(double) * ((size_t)2 * GT * Sp + (size_t)Q * GT * CW * NJ + (size_t)GT * d.M * d.D + GT * NCH) +
+                  sizeof(int) * 2 * GT * NCH + (size_t)d.S * d.M + 16;
     auto kern = k_chain<RR, CW, GT, REG>;
     if (smem > 48 * 1024) {
         if (smem > 227 * 1024) return 2;
