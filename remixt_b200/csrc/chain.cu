@@ -137,6 +137,7 @@ struct ChainArgs {
     int g0, gn;            // fits of this launch
     int ntiles;
     int Q, NJ, rr;         // thread layout (rr = rows per slice; == RR when REG)
+    int fast_brk;          // breakend fast path allowed (flip costs fit the table)
     const double* fexp;    // (G,N,S)
     const double* mF;      // (G,N)
     double* ahat;          // (G,N,S)
@@ -151,23 +152,32 @@ __device__ __forceinline__ int dexp_field(double v) { return (__double2hiint(v) 
 __device__ __forceinline__ double pow2_scale(int be) { return __hiloint2double((2046 - be) << 20, 0); }
 
 #define RMX_EPI 3    // epilogue slots per thread (3 * threads >= GT * SJ, checked by the launcher)
+#define RMX_FETAB 64 // flip-cost table entries of the breakend fast path
 
-template <int RR, int CW, int GT, bool REG>
+// QT > 0: the number of row slices is the compile-time constant QT (register-resident E); QT == 0: A.Q.
+template <int RR, int CW, int GT, int QT, bool REG>
 __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const RmxDims& d = A.d;
-    const int S = d.S, M = d.M, Q = A.Q, NJ = A.NJ;
+    const int S = d.S, M = d.M, NJ = A.NJ;
+    const int Q = QT > 0 ? QT : A.Q;
     const int rr = REG ? RR : A.rr;
     const int Sp = Q * rr;                 // padded number of rows (>= S)
     const int SJ = (S + 31) & ~31;         // epilogue slots per fit
     const int NCH = SJ >> 5;               // warps (chunks) per fit in the epilogue
     const int MD = M * d.D;
+    const int T = blockDim.x;
+    // breakend fast path: two tumour clones, combined (d1,d2) table index fits a byte
+    const bool fast_brk = REG && M == 3 && d.D * d.D <= 256 && A.fast_brk;
     double* u = reinterpret_cast<double*>(smem_raw);        // [2][GT][Sp]   messages (double buffered)
     double* part = u + 2 * GT * Sp;                          // [Q][GT][CW][NJ] slice partial sums
     double* wtab = part + Q * GT * CW * NJ;                  // [GT][M*D]     breakend tables of the step
     double* redd = wtab + GT * MD;                           // [GT][NCH]     sums of the last message
-    int* redi = reinterpret_cast<int*>(redd + GT * NCH);     // [2][GT][NCH]  max exponent fields
-    int8_t* tots = reinterpret_cast<int8_t*>(redi + 2 * GT * NCH);   // [S*M]
+    double* w2 = redd + GT * NCH;                            // [GT][256]     fast path: w1[d1]*w2[d2]
+    double* fetab = w2 + (fast_brk ? GT * 256 : 0);          // [RMX_FETAB]   fast path: exp(-pen*flipcost)
+    int* redi = reinterpret_cast<int*>(fetab + (fast_brk ? RMX_FETAB : 0));   // [2][GT][NCH] max exponent fields
+    unsigned short* bix = reinterpret_cast<unsigned short*>(redi + 2 * GT * NCH);   // [RR*CW][T] fast path
+    int8_t* tots = reinterpret_cast<int8_t*>(bix + (fast_brk ? RR * CW * T : 0));   // [S*M]
 
     const int tile = blockIdx.x % A.ntiles;
     const int cd = blockIdx.x / A.ntiles;
@@ -183,27 +193,32 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     const int gcount = min(GT, A.g0 + A.gn - gbase);         // live fits in the tile
     const int QS = GT * CW * NJ;                             // part stride between row slices
 
-    for (int e = t; e < 2 * GT * Sp; e += blockDim.x) u[e] = 0.;
-    for (int e = t; e < 2 * GT * NCH; e += blockDim.x) redi[e] = 1023;   // first message: max f = 1
-    for (int e = t; e < S * M; e += blockDim.x) {
+    for (int e = t; e < 2 * GT * Sp; e += T) u[e] = 0.;
+    for (int e = t; e < 2 * GT * NCH; e += T) redi[e] = 1023;   // first message: max f = 1
+    for (int e = t; e < S * M; e += T) {
         int s = e / M, m = e - s * M;
         tots[e] = (m == 0) ? 0 : (int8_t)(A.tab[(s * M + m) * 2] + A.tab[(s * M + m) * 2 + 1]);
     }
+    if (fast_brk)
+        for (int e = t; e < RMX_FETAB; e += T) fetab[e] = exp(__dmul_rn(-A.sp.pen, (double)e));
 
     // ---- per-thread epilogue slots: slot -> (fit g, column j), consecutive j per lane, one fit per warp
-    int sl_u[RMX_EPI], sl_p[RMX_EPI], sl_r[RMX_EPI];
+    int sl_u[RMX_EPI], sl_p[RMX_EPI], sl_r[RMX_EPI], sl_rb[RMX_EPI];
     int64_t sl_g[RMX_EPI];
+    const double* sl_mf[RMX_EPI];
     bool sl_ok[RMX_EPI], sl_lead[RMX_EPI];
 #pragma unroll
     for (int e = 0; e < RMX_EPI; ++e) {
-        const int slot = t + e * blockDim.x;
+        const int slot = t + e * T;
         const int g = slot / SJ, j = slot - g * SJ;
         sl_ok[e] = slot < GT * SJ && j < S && g < gcount;
         sl_lead[e] = sl_ok[e] && j == 0;
         sl_u[e] = g * Sp + j;
         sl_p[e] = (g * CW + (j % CW)) * NJ + j / CW;
         sl_r[e] = slot < GT * SJ ? g * NCH + (j >> 5) : -1;
+        sl_rb[e] = g * NCH;
         sl_g[e] = (int64_t)(gbase + g) * NS + j;
+        sl_mf[e] = A.mF + (int64_t)(gbase + min(g, GT - 1)) * d.N;
     }
     __syncthreads();
 
@@ -222,7 +237,7 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     }
 
     double ereg[REG ? RR : 1][REG ? CW : 1];
-    int cur_class = -1;
+    int cur_class = -1, bix_class = -1;
     int cur = 0;
     // the lead thread of fit g (slot with j == 0) accumulates the fit's log normaliser:
     // logZ = log(sum of the last message) + ln2 * esum + sum_n max F[n]
@@ -293,16 +308,56 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
         } else {
             // breakend row (rare): E_n[from][to] = flipE[cls][from][to] * prod_m wexp[g][r][m][tot_from - tot_to].
             // The m = 0 factor (normal copies) does not depend on the states: applied once at the end.
-            for (int e = t; e < GT * MD; e += blockDim.x) {
+            const int sgn = dir == 0 ? 1 : -1;    // forward: from = row index; backward: from = column index
+            for (int e = t; e < GT * MD; e += T) {
                 const int g = e / MD, o = e - g * MD;
                 const int gg = gbase + min(g, gcount - 1);
                 wtab[e] = A.sp.wexp[(int64_t)gg * A.sp_fit_stride + (int64_t)br * MD + o];
             }
+            if (fast_brk && cls != bix_class) {
+                // per-entry table of this thread's tile: low byte = combined (d1,d2) index, high byte = flip cost
+                const double* FC = A.sp.flipc + (int64_t)cls * SS;
+#pragma unroll 1
+                for (int kc = 0; kc < RR * CW; ++kc) {
+                    const int ir = i0 + kc / CW, jc = j0 + kc % CW;
+                    unsigned short v = 0xff00;                       // out of range: flip cost 255 -> weight 0
+                    if (act && ir < S && jc < S) {
+                        const int d1 = sgn * ((int)tots[ir * M + 1] - (int)tots[jc * M + 1]) + d.doff;
+                        const int d2 = sgn * ((int)tots[ir * M + 2] - (int)tots[jc * M + 2]) + d.doff;
+                        int fc = (int)FC[(int64_t)ir * S + jc];
+                        fc = fc < RMX_FETAB - 1 ? fc : RMX_FETAB - 1;
+                        v = (unsigned short)((fc << 8) | (d1 * d.D + d2));
+                    }
+                    bix[kc * T + t] = v;
+                }
+                bix_class = cls;
+            }
             __syncthreads();
-            if (act) {
+            if (fast_brk) {
+                for (int e = t; e < GT * 256; e += T) {
+                    const int g = e >> 8, ix = e & 255;
+                    const int d1 = ix / d.D, d2 = ix - d1 * d.D;
+                    w2[e] = d1 < d.D ? wtab[g * MD + d.D + d1] * wtab[g * MD + 2 * d.D + d2] : 0.;
+                }
+                __syncthreads();
+#pragma unroll 1
+                for (int k = 0; k < RR; ++k) {
+                    double v[GT];
+#pragma unroll
+                    for (int g = 0; g < GT; ++g) v[g] = uin[g * Sp + k];
+#pragma unroll
+                    for (int c = 0; c < CW; ++c) {
+                        const int code = bix[(k * CW + c) * T + t];
+                        const int fc = code >> 8;
+                        const double fe = fc < RMX_FETAB ? fetab[fc] : 0.;
+                        const double* wp = w2 + (code & 255);
+#pragma unroll
+                        for (int g = 0; g < GT; ++g) acc[g][c] = fma(fe * v[g], wp[g * 256], acc[g][c]);
+                    }
+                }
+            } else if (act) {
                 const double* FE = A.sp.flipE + (int64_t)cls * SS;
                 const int kmax = min(rr, S - i0);
-                const int sgn = dir == 0 ? 1 : -1;    // forward: from = row index; backward: from = column index
 #pragma unroll 1
                 for (int k = 0; k < kmax; ++k) {
                     const int ir = i0 + k;
@@ -319,7 +374,6 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
 #pragma unroll
                             for (int g = 0; g < GT; ++g) w[g] *= wtab[g * MD + dd];
                         }
-                        // acc[g][c] with a runtime c: select through a switch-free unrolled compare
 #pragma unroll
                         for (int cc = 0; cc < CW; ++cc)
                             if (cc == c) {
@@ -328,13 +382,13 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
                             }
                     }
                 }
-                const int d0 = A.rows.d0[row];
+            }
+            const int d0 = A.rows.d0[row];
 #pragma unroll
-                for (int g = 0; g < GT; ++g) {
-                    const double w0 = wtab[g * MD + d0 + d.doff];
+            for (int g = 0; g < GT; ++g) {
+                const double w0 = wtab[g * MD + d0 + d.doff];
 #pragma unroll
-                    for (int c = 0; c < CW; ++c) acc[g][c] *= w0;
-                }
+                for (int c = 0; c < CW; ++c) acc[g][c] *= w0;
             }
         }
         if (act) {
@@ -354,15 +408,28 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
 #pragma unroll
         for (int e = 0; e < RMX_EPI; ++e) {
             if (sl_r[e] >= 0) {                                    // warp-uniform (GT*SJ is a multiple of 32)
-                const int rbase = sl_r[e] - (sl_r[e] % NCH);
-                int be = redp[rbase];
-                for (int c2 = 1; c2 < NCH; ++c2) be = max(be, redp[rbase + c2]);
+                int be = redp[sl_rb[e]];
+                if (REG) {                                         // S <= 128: at most 4 chunks
+#pragma unroll
+                    for (int c2 = 1; c2 < 4; ++c2)
+                        if (c2 < NCH) be = max(be, redp[sl_rb[e] + c2]);
+                } else {
+                    for (int c2 = 1; c2 < NCH; ++c2) be = max(be, redp[sl_rb[e] + c2]);
+                }
                 double un = 0.;
                 if (sl_ok[e]) {
                     const double* pq = part + sl_p[e];
-                    double a = pq[0];
-                    for (int qq = 1; qq < Q; ++qq) a += pq[qq * QS];
-                    double v = a * pow2_scale(be);
+                    double a0 = pq[0], a1 = 0.;
+                    if (QT > 0) {
+#pragma unroll
+                        for (int qq = 1; qq < (QT > 0 ? QT : 1); qq += 2) {
+                            a1 += pq[qq * QS];
+                            if (qq + 1 < QT) a0 += pq[(qq + 1) * QS];
+                        }
+                    } else {
+                        for (int qq = 1; qq < Q; ++qq) a0 += pq[qq * QS];
+                    }
+                    double v = (a0 + a1) * pow2_scale(be);
                     const int64_t o = sl_g[e] + (int64_t)n * S;
                     if (dir == 0) {
                         v *= fpre[e];
@@ -378,7 +445,7 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
                 if ((t & 31) == 0) redn[sl_r[e]] = mx;
                 if (sl_lead[e]) {
                     esum[e] += be - 1023;
-                    mfsum[e] += A.mF[(int64_t)(sl_g[e] / NS) * d.N + prev];
+                    mfsum[e] += sl_mf[e][prev];
                     if (be <= 0 || be >= 2047) bad = 1;
                 }
             }
@@ -398,11 +465,11 @@ __global__ void __launch_bounds__(REG ? 256 : 512) k_chain(ChainArgs A) {
     for (int e = 0; e < RMX_EPI; ++e)
         if (sl_lead[e]) {
             double slast = 0.;
-            for (int c2 = 0; c2 < NCH; ++c2) slast += redd[sl_r[e] + c2];
-            const int g = (int)(sl_g[e] / NS);
+            for (int c2 = 0; c2 < NCH; ++c2) slast += redd[sl_rb[e] + c2];
+            const int g = gbase + sl_rb[e] / NCH;
             const int last = dir == 0 ? s1 : s0;
             if (dir == 0) {
-                const double logz = log(slast) + 0.693147180559945309417 * (double)esum[e] + mfsum[e] + A.mF[(int64_t)g * d.N + last];
+                const double logz = log(slast) + 0.693147180559945309417 * (double)esum[e] + mfsum[e] + sl_mf[e][last];
                 A.chain_logz[(int64_t)g * A.ch.NC + chain] = logz;
                 if (isnan(logz)) bad = 1;
             }
@@ -999,18 +1066,22 @@ void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int g0, int gn, int 
     k_prep_brk<<<dim3(R, gn), 64, 0, st>>>(d, g0, brk_rows, bidx, borient, brk, p_brk, pen, tm, fit_stride, pd, wexp);
 }
 
-template <int RR, int CW, int GT, bool REG>
+template <int RR, int CW, int GT, int QT, bool REG>
 static int launch_chain_cfg(cudaStream_t st, ChainArgs& A, int Q, int rr) {
     const RmxDims& d = A.d;
     const int NJ = (d.S + CW - 1) / CW;
     A.Q = Q; A.NJ = NJ; A.rr = rr;
     A.ntiles = (A.gn + GT - 1) / GT;
+    A.fast_brk = 1;
     const int Sp = Q * rr, SJ = (d.S + 31) & ~31, NCH = SJ >> 5;
     const int threads = ((Q * NJ + 31) / 32) * 32;
     if (threads > (REG ? 256 : 512) || RMX_EPI * threads < GT * SJ) return 2;
-    size_t smem = sizeof(double) * ((size_t)2 * GT * Sp + (size_t)Q * GT * CW * NJ + (size_t)GT * d.M * d.D + GT * NCH) +
-                  sizeof(int) * 2 * GT * NCH + (size_t)d.S * d.M + 16;
-    auto kern = k_chain<RR, CW, GT, REG>;
+    const bool fast = REG && d.M == 3 && d.D * d.D <= 256;
+    size_t smem = sizeof(double) * ((size_t)2 * GT * Sp + (size_t)Q * GT * CW * NJ + (size_t)GT * d.M * d.D + GT * NCH +
+                                    (fast ? GT * 256 + RMX_FETAB : 0)) +
+                  sizeof(int) * 2 * GT * NCH + (fast ? sizeof(unsigned short) * RR * CW * threads : 0) +
+                  (size_t)d.S * d.M + 16;
+    auto kern = k_chain<RR, CW, GT, QT, REG>;
     if (smem > 48 * 1024) {
         if (smem > 227 * 1024) return 2;
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 1;
@@ -1022,17 +1093,17 @@ static int launch_chain_cfg(cudaStream_t st, ChainArgs& A, int Q, int rr) {
 template <int GT>
 static int launch_chain_gt(cudaStream_t st, ChainArgs& A) {
     const int S = A.d.S;
-    if (S <= 16) return launch_chain_cfg<4, 4, GT, true>(st, A, 4, 4);
-    if (S <= 64) return launch_chain_cfg<8, 4, GT, true>(st, A, 8, 8);
-    if (S <= 104) return launch_chain_cfg<13, 4, GT, true>(st, A, 8, 13);
-    if (S <= 128) return launch_chain_cfg<16, 4, GT, true>(st, A, 8, 16);
+    if (S <= 16) return launch_chain_cfg<4, 4, GT, 4, true>(st, A, 4, 4);
+    if (S <= 64) return launch_chain_cfg<8, 4, GT, 8, true>(st, A, 8, 8);
+    if (S <= 104) return launch_chain_cfg<13, 4, GT, 8, true>(st, A, 8, 13);
+    if (S <= 128) return launch_chain_cfg<16, 4, GT, 8, true>(st, A, 8, 16);
     // large state spaces: E streamed from L2 every step
     const int NJ = (S + 3) / 4;
     int Q = 512 / NJ;
     if (Q > 8) Q = 8;
     if (Q < 1) return 2;
     const int rr = (S + Q - 1) / Q;
-    return launch_chain_cfg<1, 4, GT, false>(st, A, Q, rr);
+    return launch_chain_cfg<1, 4, GT, 0, false>(st, A, Q, rr);
 }
 
 // returns 0 on success, 1 if the shared-memory configuration failed, 2 if the state space is unsupported
