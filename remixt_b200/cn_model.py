@@ -115,7 +115,7 @@ class BreakpointModel(object):
         self.transition_model = kwargs.get('transition_model', 0)
         self.disable_breakpoints = kwargs.get('disable_breakpoints', False)
         self.breakpoint_init = kwargs.get('breakpoint_init', None)
-        self.normal_copies = kwargs.get('normal_copies', np.array([[1, 1]] * self.N))
+        self.normal_copies = kwargs['normal_copies'] if 'normal_copies' in kwargs else np.ones((self.N, 2), dtype=int)
         self.do_h_update = kwargs.get('do_h_update', True)
         self.model_class = kwargs.get('model_class', None) or _bpmodel.RemixtModel
         self.model_kwargs = kwargs.get('model_kwargs', {})
@@ -130,7 +130,14 @@ class BreakpointModel(object):
         if not self.normal_contamination:
             self.normal_copies = self.normal_copies * 0
 
-        self._build_segmentation(x, l, adjacencies)
+        # extension: ``segmentation=`` another BreakpointModel built from the SAME (x, l, adjacencies,
+        # breakpoints); its dummy-segment layout is adopted instead of being rebuilt (the fits of an
+        # initialisation grid differ in max_depth / divergence_weight only)
+        donor = kwargs.get('segmentation', None)
+        if donor is not None and donor.N == self.N and donor.breakpoint_ids == self.breakpoint_ids:
+            self._adopt_segmentation(donor)
+        else:
+            self._build_segmentation(x, l, adjacencies)
 
         # likelihood masks for poorly modelled segments (cn_model.py:169-184)
         long_enough = self.l1 >= self.min_segment_length
@@ -141,6 +148,8 @@ class BreakpointModel(object):
         self._allele_likelihood_mask = long_enough & (genotyped >= self.min_proportion_genotyped) & not_amplified
 
         if self.disable_breakpoints:
+            for f in ('num_breakpoints', 'breakpoint_idx', 'breakpoint_orient'):
+                setattr(self, '_seg_' + f, getattr(self, f))
             self.num_breakpoints = 0
             self.breakpoint_idx = -np.ones(self.breakpoint_idx.shape, dtype=int)
             self.breakpoint_orient = np.zeros(self.breakpoint_orient.shape, dtype=int)
@@ -209,6 +218,14 @@ class BreakpointModel(object):
         self.l1 = np.zeros((self.N1,), dtype=float)
         self.x1[fwd, :] = x
         self.l1[fwd] = l
+
+    _SEG_FIELDS = ('N1', 'seg_fwd_remap', 'seg_rev_remap', 'seg_is_original', 'num_breakpoints', 'is_telomere',
+                   'breakpoint_idx', 'breakpoint_orient', 'x1', 'l1')
+
+    def _adopt_segmentation(self, donor):
+        # arrays are shared read-only between the fits (disable_breakpoints rebinds, never writes in place)
+        for f in self._SEG_FIELDS:
+            setattr(self, f, getattr(donor, '_seg_' + f, getattr(donor, f)))
 
     # kept as methods for API compatibility with the reference class
     def create_cn_states(self, num_clones, num_alleles, cn_max, cn_diff_max):

@@ -23,6 +23,7 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
 #include "../../include/remixt_b200.h"
 #include "kernels.h"
 
@@ -59,7 +60,7 @@ struct Batch {
     // device: shared tables
     int8_t *tab = nullptr, *nrm = nullptr, *nsub = nullptr, *brk = nullptr, *d0 = nullptr, *class_nrm = nullptr;
     double *l = nullptr, *x = nullptr, *y0 = nullptr, *y1 = nullptr;
-    int *bidx = nullptr, *borient = nullptr, *tclass = nullptr, *brow = nullptr, *brk_rows = nullptr;
+    int *bidx = nullptr, *borient = nullptr, *tclass = nullptr, *brow = nullptr, *brk_rows = nullptr, *rinfo = nullptr;
     int *krow_ptr = nullptr, *krow_idx = nullptr, *ch_start = nullptr, *ch_end = nullptr, *ch_order = nullptr;
     int NC = 0, C = 0, R = 0;
     int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
@@ -359,13 +360,18 @@ static int do_update_p_cn(Model* m) {
         if (lc) return;
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
         cudaEvent_t te = b->tbegin(RMX_K_CHAIN);
-        lc = rmx_launch_chain(b->stream, tables(b), b->d, chainsof(b), rowsof(b), sp, b->rmd, g, n, b->fexp, b->mF,
-                              b->ahat, b->bhat, b->chain_logz, b->dflags);
+        static const bool force_streamed = getenv("RMX_CHAIN_STREAMED") != nullptr;   // A/B measurements only
+        lc = force_streamed ? 2
+                            : rmx_launch_chain_mma(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp,
+                                                b->mF, b->ahat, b->bhat, b->chain_logz, b->dflags);
+        if (lc == 2)    // state spaces above 128: transition matrix streamed from L2 (chain.cu)
+            lc = rmx_launch_chain(b->stream, tables(b), b->d, chainsof(b), rowsof(b), sp, b->rmd, g, n, b->fexp, b->mF,
+                                  b->ahat, b->bhat, b->chain_logz, b->dflags);
         b->tend(te);
         b->count();
     });
     if (lc == 2) return m->fail(RMX_ERR_UNSUPPORTED, "this number of copy number states is not supported by the chain kernel");
-    if (lc) return m->fail(RMX_ERR_CUDA, "could not configure shared memory for the chain kernel");
+    if (lc) return m->fail(RMX_ERR_CUDA, "could not configure or launch the chain kernel");
     rmx_launch_reduce_cols(b->stream, b->chain_logz, b->NC, 1, g0, gn, b->NC, b->red_out + 15, Batch::RED);
     { cudaEvent_t te_ = b->tbegin(RMX_K_POST); rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags); b->tend(te_); }
     b->count(2);
@@ -672,6 +678,12 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(upload(b, &b->borient, borient));
     CCK(upload(b, &b->tclass, tclass));
     CCK(upload(b, &b->brow, brow));
+    if (b->C <= 254 && b->R < (1 << 19)) {     // packed row info of the one-barrier chain kernel (chain_mma.cu)
+        std::vector<int> rinfo(tclass.size());
+        for (size_t n = 0; n < tclass.size(); ++n)
+            rinfo[n] = (tclass[n] + 1) | ((d0[n] + 8) << 8) | ((brow[n] + 1) << 12);
+        CCK(upload(b, &b->rinfo, rinfo));
+    }
     CCK(upload(b, &b->brk_rows, brk_rows));
     CCK(upload(b, &b->krow_ptr, krow_ptr));
     CCK(upload(b, &b->krow_idx, krow_idx));

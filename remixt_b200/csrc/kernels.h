@@ -75,6 +75,11 @@ void rmx_launch_prep_brk(cudaStream_t st, const RmxDims& d, int g0, int gn, int 
 int rmx_launch_chain(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const RmxRows& rows,
                      const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp, const double* mF,
                      double* ahat, double* bhat, double* chain_logz, int* dflags);
+// S <= 128: eight fits per CTA on the FP64 tensor path, one barrier per segment (chain_mma.cu); returns 2 if the
+// shape is not covered
+int rmx_launch_chain_mma(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
+                         const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
+                         const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags);
 void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* ahat, const double* bhat,
                      double* post, int* dflags);
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,

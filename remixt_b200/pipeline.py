@@ -64,15 +64,18 @@ class ArrayExperiment(object):
 def build_model(experiment, init_params, config, **model_kwargs):
     """The ``BreakpointModel`` construction of ``analysis/pipeline.py:164-189``."""
     is_female = get_param(config, 'is_female')
-    normal_copies = np.array([[1, 1]] * experiment.l.shape[0])
+    normal_copies = np.ones((experiment.l.shape[0], 2), dtype=int)
     if not is_female:
         on_x = experiment.segment_chromosome_id == 'X'
         normal_copies[on_x, :] = np.array([1, 0])
         if np.any(experiment.x[on_x, 0:2] > 0):
             raise Exception('inconsistent allele read counts for chromosome X')
 
+    # the dummy-segment layout depends on the experiment only: built once, adopted by every later fit
+    donor = getattr(experiment, '_rmx_segmentation', None)
     model = cn_model.BreakpointModel(
         experiment.x, experiment.l, experiment.adjacencies, experiment.breakpoints,
+        segmentation=donor,
         max_copy_number=get_param(config, 'max_copy_number'),
         normal_contamination=get_param(config, 'normal_contamination'),
         divergence_weight=init_params['divergence_weight'],
@@ -86,6 +89,11 @@ def build_model(experiment, init_params, config, **model_kwargs):
         **model_kwargs)
     model.num_em_iter = get_param(config, 'num_em_iter')
     model.num_update_iter = get_param(config, 'num_update_iter')
+    if donor is None:
+        try:
+            experiment._rmx_segmentation = model
+        except AttributeError:      # experiment types with __slots__
+            pass
     return model
 
 
