@@ -5,8 +5,9 @@
 Workload: a simulated whole genome (tests/golden/exp_<workload>.npz, produced by the reference's own
 simulator, oracle/make_inputs.py) fitted from every initialisation of the reference's (h, ploidy) grid
 (stored in the same fixture by oracle/make_golden.py init).  One *step* is one E-step of the EM loop for
-the whole grid: `num_update_iter` (5, remixt/defaults.py:157) rounds of the five coordinate updates
-(cn_model.py:444-460) followed by the ELBO (cn_model.py:418), for all G fits.
+the whole grid: the likelihood table for the current (h, dispersions), `num_update_iter` (5,
+remixt/defaults.py:157) rounds of the five coordinate updates (cn_model.py:444-460) and the ELBO
+(cn_model.py:418), for all G fits.
 
     value = N1 * S * num_update_iter * G_total / step_time      [segment-state evals / s]
 
@@ -252,7 +253,12 @@ def gpu_arm(args):
     R = int(np.sum(np.asarray(batch.breakpoint_idx)[:-1] >= 0))
     state = {}
 
+    h_cur = np.array(batch.h)
+
     def estep():
+        # every EM iteration of the reference starts from a new h / dispersions (cn_model.py:411-416), so the
+        # likelihood table of every fit is rebuilt once per step: writing h marks it stale
+        batch.h = h_cur
         batch.variational_update(NUM_UPDATE_ITER)
         state['elbo'] = batch.calculate_elbo()
 

@@ -495,6 +495,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     if (N < 1 || S < 1 || B < 1) CREATE_FAIL(RMX_ERR_VALUE, "num_segments, num_cn_states and num_brk_states must be positive");
     if (M < 2 || M > RMX_MAXM) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_clones must be between 2 and 8");
     if (S > 1024) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_cn_states > 1024 is not supported");
+    if ((int64_t)N * S >= (int64_t)1 << 31) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_segments * num_cn_states must be below 2^31");
     if (B > 64) CREATE_FAIL(RMX_ERR_UNSUPPORTED, "num_brk_states > 64 is not supported");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
@@ -761,21 +762,15 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(cudaMallocHost((void**)&b->hRn, (size_t)G * sizeof(int)));
     *b->hflags = 0;
 
-    {   // initial factors (bpmodel.pyx:546-584), the same for every fit
-        std::vector<double> v(GNS, 1.0);
-        CCK(cudaMemcpy(b->F, v.data(), GNS * sizeof(double), cudaMemcpyHostToDevice));
-        {   // posterior_marginals[:] = 1; /= sum  (bpmodel.pyx:564-565)
-            double sum = 0.;
-            for (int s = 0; s < S; ++s) sum += 1.0;
-            std::fill(v.begin(), v.end(), 1.0 / sum);
-        }
-        CCK(cudaMemcpy(b->post, v.data(), GNS * sizeof(double), cudaMemcpyHostToDevice));
-        std::vector<double> q(2 * GN);
-        for (size_t n = 0; n < GN; ++n) { q[2 * n] = 0.5; q[2 * n + 1] = 0.5; }
-        CCK(cudaMemcpy(b->q_sw, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
-        for (size_t n = 0; n < GN; ++n) { q[2 * n] = 1. - 0.01; q[2 * n + 1] = 0.01; }
-        CCK(cudaMemcpy(b->q_ot, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
-        CCK(cudaMemcpy(b->q_oa, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice));
+    {   // initial factors (bpmodel.pyx:546-584), the same for every fit, filled on the device
+        double sum = 0.;    // posterior_marginals[:] = 1; /= sum  (bpmodel.pyx:564-565)
+        for (int s = 0; s < S; ++s) sum += 1.0;
+        rmx_launch_fill2(b->stream, b->F, (int64_t)GNS, 1.0, 1.0);
+        rmx_launch_fill2(b->stream, b->post, (int64_t)GNS, 1.0 / sum, 1.0 / sum);
+        rmx_launch_fill2(b->stream, b->q_sw, (int64_t)(2 * GN), 0.5, 0.5);
+        rmx_launch_fill2(b->stream, b->q_ot, (int64_t)(2 * GN), 1. - 0.01, 0.01);
+        rmx_launch_fill2(b->stream, b->q_oa, (int64_t)(2 * GN), 1. - 0.01, 0.01);
+        b->count(5);
         // p_breakpoint favours states with at most one copy in every clone (bpmodel.pyx:546-554)
         std::vector<double> pb((size_t)G * K * B, 0.);
         double cnt = 0.;

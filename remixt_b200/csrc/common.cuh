@@ -86,16 +86,20 @@ struct StateCN {
     bool loh;            // some allele has zero copies in every clone (bpmodel.pyx:507)
 };
 
+__device__ __forceinline__ StateCN load_state2(const int8_t* __restrict__ tab, const RmxDims& d, int n0, int n1, int s);
 __device__ __forceinline__ StateCN load_state(const RmxTables& T, const RmxDims& d, int n, int s) {
+    return load_state2(T.tab, d, T.nrm[2 * n], T.nrm[2 * n + 1], s);
+}
+// tab may point to shared memory (a staged copy of the state table)
+__device__ __forceinline__ StateCN load_state2(const int8_t* __restrict__ tab, const RmxDims& d, int n0, int n1, int s) {
     StateCN c;
-    int n0 = T.nrm[2 * n], n1 = T.nrm[2 * n + 1];
     c.tot[0] = n0 + n1;
     c.a0[0] = n0;
     int s0 = n0, s1 = n1;
 #pragma unroll
     for (int m = 1; m < RMX_MAXM; ++m) {
         if (m < d.M) {
-            int v0 = T.tab[(s * d.M + m) * 2], v1 = T.tab[(s * d.M + m) * 2 + 1];
+            int v0 = tab[(s * d.M + m) * 2], v1 = tab[(s * d.M + m) * 2 + 1];
             c.tot[m] = v0 + v1;
             c.a0[m] = v0;
             s0 += v0;
@@ -133,6 +137,75 @@ __device__ __forceinline__ double expected_allele_ratio(const RmxParams& P, cons
     *md = minor;
     *td = total;
     return minor / total;
+}
+
+// ---------------------------------------------------------------------------------------------
+// log / lgamma for the likelihood table.  CUDA's double log costs ~54 FP64-pipe slots and lgamma 85-260
+// (measured, scripts/micro/lgam_rate.cu); the likelihood kernel is FP64-pipe bound and calls them 16 times per
+// (segment, state).  rmx_log: argument reduction to m in [0.75, 1.5), a 96-entry table of (1/c, -log(1/c)) at the
+// bucket centres c (shared memory, built per CTA with the library log) and a degree-7 series in r = m/c - 1,
+// |r| <= 5.3e-3: ~12 FP64 operations, absolute error < 3e-16 * max(1, |log x|).  rmx_lgamma_pos: Stirling series
+// with 7 terms above 8 (truncation < 1e-15), upward recurrence below; agrees with glibc's lgamma to 8e-15 *
+// max(1, |lgamma|) over [1e-3, 1.6e5] (scripts/micro/lgam_test.cpp).  Positive finite normal arguments only.
+// ---------------------------------------------------------------------------------------------
+#define RMX_LOGTAB 96
+__device__ __forceinline__ void rmx_logtab_init(double2* tab) {      // all threads call; includes the barrier
+    for (int i = threadIdx.x; i < RMX_LOGTAB; i += blockDim.x) {
+        const double c = 0.75 + ((double)i + 0.5) * (1.0 / 128.0);
+        const double inv = 1.0 / c;
+        tab[i] = make_double2(inv, -log(inv));
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ double rmx_log(double x, const double2* __restrict__ tab) {
+    int hi = __double2hiint(x);
+    if (hi < 0x00100000 || hi >= 0x7ff00000) return log(x);   // zero, denormal, negative, inf, NaN: library semantics
+    const int lo = __double2loint(x);
+    int e = (hi >> 20) - 1023;
+    int mh = (hi & 0x000fffff) | 0x3ff00000;                 // m in [1, 2)
+    if (mh >= 0x3ff80000) { mh -= 0x00100000; e += 1; }      // m >= 1.5: halve -> m in [0.75, 1.5)
+    const int idx = mh < 0x3ff00000 ? ((mh >> 14) & 63) - 32 : 32 + ((mh >> 13) & 127);
+    const double m = __hiloint2double(mh, lo);
+    const double2 t = tab[idx];
+    const double r = fma(m, t.x, -1.0);
+    double p = 1.0 / 7.0;
+    p = fma(p, r, -1.0 / 6.0);
+    p = fma(p, r, 0.2);
+    p = fma(p, r, -0.25);
+    p = fma(p, r, 1.0 / 3.0);
+    p = fma(p, r, -0.5);
+    p = fma(p * r, r, r);
+    const double ed = (double)e;
+    return fma(ed, 6.93147180369123816490e-01, t.y) + fma(ed, 1.90821492927058770002e-10, p);
+}
+// 1/z for positive normal z well inside the exponent range: hardware seed + two Newton steps (5 instructions)
+__device__ __forceinline__ double rmx_rcp(double z) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(z));
+    double e = fma(-z, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-z, r, 1.0);
+    return fma(r, e, r);
+}
+__device__ __forceinline__ double rmx_lgamma_pos(double z, const double2* __restrict__ tab) {
+    double lp = 0.;
+    if (z < 8.) {
+        double p = z;
+        z += 1.;
+        while (z < 8.) { p *= z; z += 1.; }
+        lp = rmx_log(p, tab);
+    }
+    // z in [8, 1e300): the seed's exponent handling is safe; larger arguments go through the library
+    if (!(z < 1e300)) return lgamma(z);
+    const double r = rmx_rcp(z), r2 = r * r;
+    double s = 6.4102564102564102564e-3;                 //  1/156
+    s = fma(s, r2, -1.9175269175269175269e-3);           // -691/360360
+    s = fma(s, r2, 8.4175084175084175084e-4);            //  1/1188
+    s = fma(s, r2, -5.9523809523809523810e-4);           // -1/1680
+    s = fma(s, r2, 7.9365079365079365079e-4);            //  1/1260
+    s = fma(s, r2, -2.7777777777777777778e-3);           // -1/360
+    s = fma(s, r2, 8.3333333333333333333e-2);            //  1/12
+    return (z - 0.5) * rmx_log(z, tab) - z + 0.91893853320467274178 + s * r - lp;
 }
 
 // AS 103 digamma (J. Bernardo 1976), the algorithm bpmodel.pyx:162-235 uses.

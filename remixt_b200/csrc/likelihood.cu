@@ -22,22 +22,41 @@
 // (kernel: k_segconst_rows below)
 
 // Six log-likelihood terms of one (segment, state): ll[0..1] total (u), ll[2..5] allele (v*2+w).
-__device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P, bool tmask,
-                                         bool amask, const double* __restrict__ segc, int R, int r, int n, int s,
-                                         double* ll, int* flags) {
-    StateCN c = load_state(T, d, n, s);
+// Per-segment inputs of ll_core: either read straight from HBM (ll_terms) or staged in shared memory (k_lltable).
+struct SegIn {
+    const double* segc;   // hoisted constants c = 0..11 at segc[c * sstride]
+    int sstride;
+    double x, l, y0, y1;
+    int nrm0, nrm1;
+};
+
+__device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const RmxDims& d, const RmxParams& P, bool tmask,
+                                        bool amask, const SegIn& in, int s, double* ll, int* flags,
+                                        const double2* __restrict__ ltab, const double* lnr = nullptr) {
+    StateCN c = load_state2(tab, d, in.nrm0, in.nrm1, s);
     const bool special = !P.normal_contamination;
     // ---- total reads: negative binomial (bpmodel.pyx:751-776, :238-272)
     if (tmask) {
-        double x = T.x[n];
+        double x = in.x;
         bool hd = special && c.hdel;
-        double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, T.l[n]);
+        double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, in.l);
+        // x log p + r log(1-p) with p = mu/(r+mu) is x (log mu - log(r+mu)) + r (log r - log(r+mu)): three logs for
+        // the two dispersions instead of four and no division; log r comes hoisted (lnr).  Only for 0 < mu < inf
+        // (p strictly inside (0,1)); anything else takes the reference's literal form, clamp included.
+        const bool plain = lnr != nullptr && mu > 0. && mu < 1e300;
+        const double lmu = plain ? rmx_log(mu, ltab) : 0.;
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
             double rr = hd ? P.negbin_hdel_r[u] : P.negbin_r[u];
-            double p = mu / (rr + mu);
-            if (p < 0. || p > 1.) p = 0.5;
-            double v = segc[((hd ? 2 : 0) + u) * R + r] + x * log(p) + rr * log(1. - p);
+            double v;
+            if (plain) {
+                const double lrm = rmx_log(rr + mu, ltab);
+                v = in.segc[((hd ? 2 : 0) + u) * in.sstride] + x * (lmu - lrm) + rr * (lnr[(hd ? 2 : 0) + u] - lrm);
+            } else {
+                double p = mu / (rr + mu);
+                if (p < 0. || p > 1.) p = 0.5;
+                v = in.segc[((hd ? 2 : 0) + u) * in.sstride] + x * rmx_log(p, ltab) + rr * rmx_log(1. - p, ltab);
+            }
             if (isnan(v)) *flags |= RMX_F_NB_NAN;
             ll[u] = v;
         }
@@ -68,7 +87,7 @@ __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, c
                 return;
             }
         }
-        double y0 = T.y0[n], y1 = T.y1[n];
+        double y0 = in.y0, y1 = in.y1;
         double na = y0 + y1;
         if (na == 0.) return;
         if (p <= 0. || (1. - p) <= 0.) {
@@ -79,11 +98,11 @@ __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, c
         for (int v = 0; v < 2; ++v) {
             double Mv = loh ? P.betabin_loh_M[v] : P.betabin_M[v];
             double a = Mv * p, b = Mv * (1. - p);
-            double base = -lgamma(a) - lgamma(b);
+            double base = -rmx_lgamma_pos(a, ltab) - rmx_lgamma_pos(b, ltab);
 #pragma unroll
             for (int w = 0; w < 2; ++w) {
                 double k = w ? y1 : y0;
-                double val = segc[((loh ? 8 : 4) + v * 2 + w) * R + r] + lgamma(k + a) + lgamma(na - k + b) + base;
+                double val = in.segc[((loh ? 8 : 4) + v * 2 + w) * in.sstride] + rmx_lgamma_pos(k + a, ltab) + rmx_lgamma_pos(na - k + b, ltab) + base;
                 if (isnan(val)) *flags |= RMX_F_BB_NAN;
                 ll[2 + v * 2 + w] = val;
             }
@@ -91,25 +110,79 @@ __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, c
     }
 }
 
-// K1: the likelihood table, LL[g][t][n*S+s], one thread per (n,s), fully coalesced planar writes.
-__global__ void __launch_bounds__(256) k_lltable(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+// the same, per-segment inputs read from HBM (row lists of the M-step)
+__device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P, bool tmask,
+                                         bool amask, const double* __restrict__ segc, int R, int r, int n, int s,
+                                         double* ll, int* flags, const double2* __restrict__ ltab) {
+    SegIn in;
+    in.segc = segc + r;
+    in.sstride = R;
+    in.x = T.x[n]; in.l = T.l[n]; in.y0 = T.y0[n]; in.y1 = T.y1[n];
+    in.nrm0 = T.nrm[2 * n]; in.nrm1 = T.nrm[2 * n + 1];
+    ll_core(T.tab, d, P, tmask, amask, in, s, ll, flags, ltab);
+}
+
+// K1: the likelihood table, LL[g][t][n*S+s], one thread per (n,s), fully coalesced planar writes.  A CTA takes
+// 256 consecutive (n,s) at a time -- a handful of segments -- and stages their per-segment inputs (12 hoisted
+// constants, x, l, y, masks, normal copies) and the state table in shared memory, so a thread's ~20 per-segment
+// reads are one cooperative round trip instead of 20 dependent broadcast loads.
+#define LLT_SEGW 16      // doubles per staged segment: 12 constants, x, l, y0, y1
+__global__ void __launch_bounds__(256, 3) k_lltable(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                   const double* __restrict__ segc_all,
-                                                  double* __restrict__ LL_all, int* __restrict__ dflags) {
+                                                  double* __restrict__ LL_all, int* __restrict__ dflags, int segmax) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ double2 ltab[RMX_LOGTAB];
+    double* segs = reinterpret_cast<double*>(smem_raw);                 // [segmax][LLT_SEGW]
+    int* segi = reinterpret_cast<int*>(segs + (size_t)segmax * LLT_SEGW);   // [segmax] masks + normal copies, packed
+    int8_t* stab = reinterpret_cast<int8_t*>(segi + segmax);            // [S*M*2]
+    const int t = threadIdx.x;
+    for (int e = t; e < d.S * d.M * 2; e += blockDim.x) stab[e] = T.tab[e];
+    rmx_logtab_init(ltab);
     const int g = RMX_FIT();
     const RmxParams P = Pg[g];
-    const int64_t NS = (int64_t)d.N * d.S;
+    const int NS = d.N * d.S;                                           // per fit, < 2^31 (checked at creation)
     const double* segc = segc_all + (int64_t)g * 12 * d.N;
     double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
     const uint8_t* tm = T.tmask + (int64_t)g * d.N;
     const uint8_t* am = T.amask + (int64_t)g * d.N;
     int flags = 0;
-    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < NS;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        int n = (int)(idx / d.S), s = (int)(idx - (int64_t)n * d.S);
-        double ll[RMX_NTERM];
-        ll_terms(T, d, P, tm[n] != 0, am[n] != 0, segc, d.N, n, n, s, ll, &flags);
+    // log of the four negative-binomial dispersions of this fit (plain u = 0, 1; hdel u = 0, 1)
+    const double lnr[4] = {log(P.negbin_r[0]), log(P.negbin_r[1]), log(P.negbin_hdel_r[0]), log(P.negbin_hdel_r[1])};
+    for (int base = blockIdx.x * blockDim.x; base < NS; base += gridDim.x * blockDim.x) {
+        const int nfirst = base / d.S;
+        const int last = min(base + (int)blockDim.x, NS) - 1;
+        const int nseg = last / d.S - nfirst + 1;
+        for (int e = t; e < nseg * LLT_SEGW; e += blockDim.x) {
+            const int sg = e / LLT_SEGW, c = e - sg * LLT_SEGW, n = nfirst + sg;
+            double v;
+            if (c < 12) v = segc[(int64_t)c * d.N + n];
+            else if (c == 12) v = T.x[n];
+            else if (c == 13) v = T.l[n];
+            else if (c == 14) v = T.y0[n];
+            else v = T.y1[n];
+            segs[e] = v;
+        }
+        for (int sg = t; sg < nseg; sg += blockDim.x) {
+            const int n = nfirst + sg;
+            segi[sg] = (tm[n] != 0 ? 1 : 0) | (am[n] != 0 ? 2 : 0) | ((int)T.nrm[2 * n] << 8) | ((int)T.nrm[2 * n + 1] << 16);
+        }
+        __syncthreads();
+        const int idx = base + t;
+        if (idx < NS) {
+            const int n = idx / d.S, s = idx - n * d.S, sg = n - nfirst;
+            const double* sp = segs + sg * LLT_SEGW;
+            const int si = segi[sg];
+            SegIn in;
+            in.segc = sp;
+            in.sstride = 1;
+            in.x = sp[12]; in.l = sp[13]; in.y0 = sp[14]; in.y1 = sp[15];
+            in.nrm0 = (si >> 8) & 0xff; in.nrm1 = (si >> 16) & 0xff;
+            double ll[RMX_NTERM];
+            ll_core(stab, d, P, (si & 1) != 0, (si & 2) != 0, in, s, ll, &flags, ltab, lnr);
 #pragma unroll
-        for (int t = 0; t < RMX_NTERM; ++t) LL[(int64_t)t * NS + idx] = ll[t];
+            for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
+        }
+        __syncthreads();
     }
     if (flags) atomicOr(dflags, flags);
 }
@@ -379,6 +452,8 @@ __global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxPa
                                              const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
                                              const double* __restrict__ q_sw_all, double* __restrict__ part_all,
                                              int64_t part_fit_stride, int* __restrict__ dflags) {
+    __shared__ double2 ltab[RMX_LOGTAB];
+    rmx_logtab_init(ltab);
     const int g = RMX_FIT();
     const int R = rows_all ? Rn[g] : d.N;
     int64_t RS = (int64_t)R * d.S;
@@ -391,7 +466,7 @@ __global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxPa
         const int64_t gn = (int64_t)g * d.N + n;
         double ll[RMX_NTERM];
         ll_terms(T, d, Pg[g], T.tmask[gn] != 0, T.amask[gn] != 0, segc_all + (int64_t)g * 12 * d.N, R, r, n, s, ll,
-                 &flags);
+                 &flags, ltab);
         double p = post_all[gn * d.S + s];
         double ot0 = q_ot_all[2 * gn], ot1 = q_ot_all[2 * gn + 1];
         double oa0 = q_oa_all[2 * gn], oa1 = q_oa_all[2 * gn + 1];
@@ -634,6 +709,18 @@ const char* rmx_measure_fp64_peak(int device, double* tflops) {
 // ---------------------------------------------------------------------------------------------
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// constructor state: out[i] = (i & 1) ? v1 : v0 (v0 == v1 for a plain fill), grid-stride
+__global__ void k_fill2(double* __restrict__ out, int64_t n, double v0, double v1) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = (i & 1) ? v1 : v0;
+}
+
+void rmx_launch_fill2(cudaStream_t st, double* out, int64_t n, double v0, double v1) {
+    if (n <= 0) return;
+    int64_t want = (n + 255) / 256;
+    k_fill2<<<(int)(want < 148 * 16 ? want : 148 * 16), 256, 0, st>>>(out, n, v0, v1);
+}
+
 void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                          const int* rows_all, const int* Rn, int Rmax, double* segc) {
     if (Rmax <= 0 || gn <= 0) return;
@@ -648,7 +735,9 @@ void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const
     int64_t cap = ((int64_t)sm_count * 8 + gn - 1) / gn;    // whole grid sized in multiples of the SM count
     if (cap < 1) cap = 1;
     int grid = (int)(want < cap ? want : cap);
-    k_lltable<<<dim3(grid, gn), 256, 0, st>>>(T, d, P, g0, segc, LL, dflags);
+    const int segmax = 256 / d.S + 2;
+    const size_t smem = (size_t)segmax * (LLT_SEGW * sizeof(double) + sizeof(int)) + (size_t)d.S * d.M * 2 + 16;
+    k_lltable<<<dim3(grid, gn), 256, smem, st>>>(T, d, P, g0, segc, LL, dflags, segmax);
 }
 
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
