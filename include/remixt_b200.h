@@ -84,7 +84,10 @@ typedef enum {
     RMX_A_CACHED_LOG_TRANSMAT = 10,   /* f64 (N1-1,S,S) :425, get only, materialised on demand */
     RMX_A_JOINT_POSTERIOR_MARGINALS = 11, /* f64 (N1-1,S,S) :427, get only, materialised on demand */
     RMX_A_L = 12, RMX_A_X = 13, RMX_A_Y = 14,   /* f64, get only (:436-438) */
-    RMX_A_STATE_PATH = 15             /* i64 (N1): Viterbi path of the last rmx_infer_cn, get only */
+    RMX_A_STATE_PATH = 15,            /* i64 (N1): Viterbi path of the last rmx_infer_cn, get only */
+    RMX_A_LL_TABLE = 16               /* f64 (6,N1,S): the cached likelihood terms calculate_log_likelihood_total(n,s,u)
+                                         (:751, planes 0-1) and calculate_log_likelihood_allele(n,s,v,w) (:809, planes
+                                         2+2v+w) for the current h / dispersions / masks; get only */
 } rmx_array_id;
 
 /* Scalar attributes (`cdef public` doubles / ints, bpmodel.pyx:417-456). */

@@ -16,6 +16,7 @@ A_H, A_P_BREAKPOINT, A_P_ALLELE_SWAP, A_P_OUTLIER_TOTAL, A_P_OUTLIER_ALLELE = 0,
 A_POSTERIOR_MARGINALS, A_FRAMELOGPROB, A_TOTAL_LIKELIHOOD_MASK, A_ALLELE_LIKELIHOOD_MASK = 5, 6, 7, 8
 A_LOG_TRANSMAT, A_CACHED_LOG_TRANSMAT, A_JOINT_POSTERIOR_MARGINALS = 9, 10, 11
 A_L, A_X, A_Y, A_STATE_PATH = 12, 13, 14, 15
+A_LL_TABLE = 16
 
 # rmx_scalar_id
 SCALAR_IDS = {

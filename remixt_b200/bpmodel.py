@@ -326,6 +326,13 @@ class _ModelBase(object):
     def state_sequence(self):
         return self._get(_lib.A_STATE_PATH, (self.num_segments,), np.int64)
 
+    @property
+    def log_likelihood_table(self):
+        """(6, N1, S): ``calculate_log_likelihood_total(n, s, u)`` in planes u and
+        ``calculate_log_likelihood_allele(n, s, v, w)`` in planes 2 + 2 v + w (``bpmodel.pyx:751,809``), as the
+        device caches them for the current h / dispersions / masks.  Not a reference attribute; diagnostic."""
+        return self._get(_lib.A_LL_TABLE, (6, self.num_segments, self.num_cn_states))
+
     def calculate_log_transmat(self, log_transmat):
         out = np.empty(self._NSS, dtype=np.float64)
         check(lib.rmx_calculate_log_transmat(self._handle, _ptr(out)), self._handle)

@@ -63,6 +63,13 @@ struct Batch {
     int *bidx = nullptr, *borient = nullptr, *tclass = nullptr, *brow = nullptr, *brk_rows = nullptr, *rinfo = nullptr;
     int *krow_ptr = nullptr, *krow_idx = nullptr, *ch_start = nullptr, *ch_end = nullptr, *ch_order = nullptr;
     int NC = 0, C = 0, R = 0;
+    // likelihood-table fast path: normal-copy kinds, wide log table, per-(fit, kind, state) table
+    uint8_t *nkind = nullptr, *sflag = nullptr;
+    int8_t* kind_nrm = nullptr;
+    double2* logw = nullptr;
+    double* stab = nullptr;
+    int Q = 0;
+    bool fast_ll = false;
     int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
     ClassMats mats[2];
 
@@ -264,7 +271,16 @@ static int ensure_ll(Model* m, int g0, int gn) {
     std::vector<int> key(b->G, 0);
     for_runs(g0, gn, key, &b->ll_dirty, [&](int g, int n) {
         rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc);
-        { cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE); rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags); b->tend(te_); }
+        cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE);
+        if (b->fast_ll) {
+            RmxFast Fp;
+            Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag;
+            rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, Fp, b->LL, b->dflags);
+            b->count(1);
+        } else {
+            rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags);
+        }
+        b->tend(te_);
         b->count(2);
         for (int k = g; k < g + n; ++k) { b->ll_dirty[k] = 0; b->asum_valid[k] = 0; }
     });
@@ -726,6 +742,40 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(upload(b, &b->amask, std::vector<uint8_t>(GN, 1)));
     CCK(dalloc(b, &b->LL, GNS * RMX_NTERM));
     CCK(dalloc(b, &b->segc, GN * 12));
+    {
+        // distinct normal-copy pairs (kinds) and the wide log table of the fast path (common.cuh)
+        std::vector<uint8_t> nkind(N);
+        std::vector<int8_t> kind_nrm;
+        std::map<int, int> kind_of;
+        bool ok = true;
+        for (int n = 0; n < N; ++n) {
+            int key = ((int)(uint8_t)b->h_nrm[2 * n] << 8) | (int)(uint8_t)b->h_nrm[2 * n + 1];
+            auto it = kind_of.find(key);
+            if (it == kind_of.end()) {
+                if (kind_of.size() >= 255) { ok = false; break; }
+                it = kind_of.emplace(key, (int)kind_of.size()).first;
+                kind_nrm.push_back(b->h_nrm[2 * n]);
+                kind_nrm.push_back(b->h_nrm[2 * n + 1]);
+            }
+            nkind[n] = (uint8_t)it->second;
+        }
+        b->Q = (int)kind_of.size();
+        b->fast_ll = ok && b->Q > 0 && rmx_lltable2_ok(d, b->Q);
+        if (b->fast_ll) {
+            std::vector<double2> lw(RMX_LW_SIZE);
+            for (int o = 0; o < RMX_LW_NOCT; ++o)
+                for (int j = 0; j < 128; ++j) {
+                    const long double c = ldexpl(1.0L + ((long double)j + 0.5L) / 128.0L, RMX_LW_E0 + o);
+                    const double inv = (double)(1.0L / c);
+                    lw[o * 128 + j] = make_double2(inv, (double)(-logl((long double)inv)));
+                }
+            CCK(upload(b, &b->nkind, nkind));
+            CCK(upload(b, &b->kind_nrm, kind_nrm));
+            CCK(upload(b, &b->logw, lw));
+            CCK(dalloc(b, &b->stab, (size_t)G * 8 * b->Q * S));
+            CCK(dalloc(b, &b->sflag, (size_t)G * b->Q * S));
+        }
+    }
     CCK(dalloc(b, &b->F, GNS));
     CCK(dalloc(b, &b->fexp, GNS));
     CCK(dalloc(b, &b->mF, GN));
@@ -838,6 +888,7 @@ static int64_t array_count(Batch* b, int id, bool* is_i64) {
     case RMX_A_X: return d.N;
     case RMX_A_Y: return (int64_t)d.N * 2;
     case RMX_A_STATE_PATH: *is_i64 = true; return d.N;
+    case RMX_A_LL_TABLE: return (int64_t)RMX_NTERM * d.N * d.S;
     default: return -1;
     }
 }
@@ -957,6 +1008,14 @@ int rmx_get_array(rmx_handle m, int id, void* dstv, int64_t count) {
     case RMX_A_P_OUTLIER_ALLELE: src = b->q_oa; break;
     case RMX_A_POSTERIOR_MARGINALS: src = b->post; break;
     case RMX_A_FRAMELOGPROB: src = b->F; break;
+    case RMX_A_LL_TABLE: {
+        int rc = ensure_ll(m, g0, gn);
+        if (rc) return rc;
+        rc = sync_check(m);
+        if (rc) return rc;
+        src = b->LL;
+        break;
+    }
     case RMX_A_TOTAL_LIKELIHOOD_MASK: memcpy(dstv, b->h_tmask.data() + (size_t)g0 * N, sizeof(int64_t) * N * gn); return RMX_OK;
     case RMX_A_ALLELE_LIKELIHOOD_MASK: memcpy(dstv, b->h_amask.data() + (size_t)g0 * N, sizeof(int64_t) * N * gn); return RMX_OK;
     case RMX_A_LOG_TRANSMAT:

@@ -62,6 +62,16 @@ struct RmxTables {
     const uint8_t* amask;   // (G,N)  allele_likelihood_mask != 0  (per fit)
 };
 
+// Inputs of the likelihood table's fast path (likelihood.cu: k_statetab, k_lltable2)
+struct RmxFast {
+    const uint8_t* nkind;     // (N) index of the segment's normal-copy pair among the distinct pairs
+    const int8_t* kind_nrm;   // (Q,2) the distinct normal-copy pairs
+    int Q;
+    const double2* logw;      // (RMX_LW_SIZE) wide log table
+    double* stab;             // (G)(8,Q,S) per-(fit, kind, state) quantities
+    uint8_t* sflag;           // (G)(Q,S)   bit 0: total-read fast path valid, bit 1: allele fast path valid
+};
+
 // ---------------------------------------------------------------------------------------------
 // warp / block helpers
 // ---------------------------------------------------------------------------------------------
@@ -206,6 +216,78 @@ __device__ __forceinline__ double rmx_lgamma_pos(double z, const double2* __rest
     s = fma(s, r2, -2.7777777777777777778e-3);           // -1/360
     s = fma(s, r2, 8.3333333333333333333e-2);            //  1/12
     return (z - 0.5) * rmx_log(z, tab) - z + 0.91893853320467274178 + s * r - lp;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Wide log table (fast path of the likelihood table).  One entry per (binary exponent, top 7 mantissa bits) for
+// arguments in [2^RMX_LW_E0, 2^(RMX_LW_E0+RMX_LW_NOCT)): (1/c, -log(1/c)) at the bucket centre c, built on the host
+// in long double (api.cu) and copied to shared memory by each CTA.  log z = -log(1/c) + log1p(z/c - 1) with
+// |z/c - 1| <= 2^-8: no exponent / mantissa surgery, one FMA for the reduced argument, a degree-6 series
+// (truncation < 2e-18).  8 FP64 operations per log.  Arguments outside the table take the library.
+// ---------------------------------------------------------------------------------------------
+#define RMX_LW_E0 4
+#define RMX_LW_NOCT 18
+#define RMX_LW_SIZE (RMX_LW_NOCT * 128)
+#define RMX_LW_BASE ((1023 + RMX_LW_E0) << 7)
+__device__ __forceinline__ bool rmx_lw_in(double z, int* idx) {
+    *idx = (__double2hiint(z) >> 13) - RMX_LW_BASE;
+    return (unsigned)*idx < (unsigned)RMX_LW_SIZE;
+}
+__device__ __forceinline__ double rmx_lw_log(double z, const double2 t) {
+    const double r = fma(z, t.x, -1.0);
+    double p = -1.0 / 6.0;
+    p = fma(p, r, 0.2);
+    p = fma(p, r, -0.25);
+    p = fma(p, r, 1.0 / 3.0);
+    p = fma(p, r, -0.5);
+    p = fma(p * r, r, r);
+    return t.y + p;
+}
+// Stirling core of lgamma for z in the table range (z >= 16): (z - 1/2) log z + series(1/z), i.e. lgamma(z) + z -
+// log(2 pi)/2.  Five series terms (next term 1.9e-3 / z^11 < 1.1e-16 at 16); 1/z from the hardware seed and one
+// Newton step (relative 1e-12 on a term below 5.3e-3).  18 FP64 operations.
+__device__ __forceinline__ double rmx_lw_lgcore(double z, const double2 t) {
+    const double L = rmx_lw_log(z, t);
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(z));
+    r = fma(r, fma(-z, r, 1.0), r);
+    const double r2 = r * r;
+    double s = 8.4175084175084175084e-4;                 //  1/1188
+    s = fma(s, r2, -5.9523809523809523810e-4);           // -1/1680
+    s = fma(s, r2, 7.9365079365079365079e-4);            //  1/1260
+    s = fma(s, r2, -2.7777777777777777778e-3);           // -1/360
+    s = fma(s, r2, 8.3333333333333333333e-2);            //  1/12
+    return fma(z - 0.5, L, s * r);
+}
+// the same quantity for any positive finite z (library log, upward recurrence below 16): the out-of-table branch
+static __device__ __noinline__ double rmx_lgcore_slow(double z) {
+    double lp = 0.;
+    const double z0 = z;
+    if (z < 16.) {
+        double p = z;
+        z += 1.;
+        while (z < 16.) { p *= z; z += 1.; }
+        lp = log(p);
+    }
+    if (!(z < 1e300)) return lgamma(z0) + z0 - 0.91893853320467274178;
+    const double r = 1.0 / z, r2 = r * r;
+    double s = 8.4175084175084175084e-4;
+    s = fma(s, r2, -5.9523809523809523810e-4);
+    s = fma(s, r2, 7.9365079365079365079e-4);
+    s = fma(s, r2, -2.7777777777777777778e-3);
+    s = fma(s, r2, 8.3333333333333333333e-2);
+    // lgamma(z0) = lgamma(z) - lp ; core(z0) = lgamma(z0) + z0 - c
+    return fma(z - 0.5, log(z), s * r) - z - lp + z0;
+}
+__device__ __forceinline__ double rmx_lgcore(double z, const double2* __restrict__ lw) {
+    int idx;
+    if (rmx_lw_in(z, &idx)) return rmx_lw_lgcore(z, lw[idx]);
+    return rmx_lgcore_slow(z);
+}
+__device__ __forceinline__ double rmx_wlog(double z, const double2* __restrict__ lw) {
+    int idx;
+    if (rmx_lw_in(z, &idx)) return rmx_lw_log(z, lw[idx]);
+    return log(z);
 }
 
 // AS 103 digamma (J. Bernardo 1976), the algorithm bpmodel.pyx:162-235 uses.

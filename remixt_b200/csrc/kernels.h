@@ -39,6 +39,10 @@ void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, 
                          const int* rows_all, const int* Rn, int Rmax, double* segc);
 void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
                         int gn, const double* segc, double* LL, int* dflags);
+// fast path (per-state tables + wide log table); rmx_lltable2_ok says whether the shape fits its shared memory
+int rmx_lltable2_ok(const RmxDims& d, int Q);
+void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags);
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
                       double* fexp, double* mF, int* dflags);

@@ -187,6 +187,168 @@ __global__ void __launch_bounds__(256, 3) k_lltable(RmxTables T, RmxDims d, cons
     if (flags) atomicOr(dflags, flags);
 }
 
+// ---------------------------------------------------------------------------------------------
+// K1 fast path.  Everything of a (segment, state) term that depends only on (fit, normal-copy kind, state) is
+// tabulated once per likelihood-table build by k_statetab: haploid depth sum_m h_m tot_m and its log, the
+// beta-binomial shape parameters a_v = M_v p, b_v = M_v (1-p) and -lgamma(a_v) - lgamma(b_v).  What remains per
+// (n,s) is 2 logs (negative binomial) and 8 lgammas of arguments k + a (beta binomial), evaluated with the wide
+// log table and the Stirling core above: ~190 FP64 operations instead of ~540.  Entries the fast path does not
+// cover (hdel / LOH special parameters, p outside (0,1), zero depth, non-finite or negative data, zero allele
+// reads) are flagged and go through ll_core, which also raises the reference's error conditions.
+// stab layout per fit: [field f in 0..8)[kind q][state s]; sflag per fit: [q][s], bit 0 total ok, bit 1 allele ok.
+// ---------------------------------------------------------------------------------------------
+#define ST_NF 8
+__global__ void k_statetab(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0, RmxFast Fp) {
+    const int g = RMX_FIT();
+    const int QS = Fp.Q * d.S;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= QS) return;
+    const int q = e / d.S, s = e - q * d.S;
+    const RmxParams& P = Pg[g];
+    const StateCN c = load_state2(T.tab, d, Fp.kind_nrm[2 * q], Fp.kind_nrm[2 * q + 1], s);
+    const bool special = !P.normal_contamination;
+    double* st = Fp.stab + (int64_t)g * ST_NF * QS;
+    double depth = 0.;
+#pragma unroll
+    for (int m = 0; m < RMX_MAXM; ++m)
+        if (m < d.M) depth += P.h[m] * (double)c.tot[m];
+    int flag = 0;
+    if (!(special && c.hdel) && depth > 0. && depth < 1e300) flag |= 1;
+    double v[ST_NF] = {depth, flag & 1 ? log(depth) : 0., 1., 1., 1., 1., 0., 0.};
+    if (!c.hdel && !(special && c.loh)) {
+        double md, td;
+        const double p = expected_allele_ratio(P, d, c, &md, &td);
+        if (td > 0. && p > 0. && (1. - p) > 0.) {
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const double a = P.betabin_M[k] * p, b = P.betabin_M[k] * (1. - p);
+                ok = ok && a > 0. && b > 0. && a < 1e300 && b < 1e300;
+                v[2 + 2 * k] = a;
+                v[3 + 2 * k] = b;
+                v[6 + k] = -lgamma(a) - lgamma(b);
+            }
+            if (ok) flag |= 2;
+            else { v[2] = v[3] = v[4] = v[5] = 1.; v[6] = v[7] = 0.; }
+        }
+    }
+#pragma unroll
+    for (int f = 0; f < ST_NF; ++f) st[f * QS + e] = v[f];
+    Fp.sflag[(int64_t)g * QS + e] = (uint8_t)flag;
+}
+
+// slow branch of k_lltable2: the general evaluation with every reference special case
+__device__ __noinline__ void ll_slow(const RmxTables& T, const RmxDims& d, const RmxParams& P, int si,
+                                     const double* __restrict__ segc, int n, int s, double* ll, int* flags,
+                                     const double2* __restrict__ ltab) {
+    ll_terms(T, d, P, (si & 1) != 0, (si & 2) != 0, segc, d.N, n, n, s, ll, flags, ltab);
+}
+
+#define LLT2_SEGW 12     // doubles per staged segment
+__global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                   const double* __restrict__ segc_all, RmxFast Fp,
+                                                   double* __restrict__ LL_all, int* __restrict__ dflags, int segmax) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ double2 ltab[RMX_LOGTAB];
+    const int QS = Fp.Q * d.S;
+    double2* lw = reinterpret_cast<double2*>(smem_raw);                          // [RMX_LW_SIZE]
+    double* st = reinterpret_cast<double*>(lw + RMX_LW_SIZE);                   // [ST_NF][QS]
+    double* segs = st + (size_t)ST_NF * QS;                                     // [segmax][LLT2_SEGW]
+    int* segi = reinterpret_cast<int*>(segs + (size_t)segmax * LLT2_SEGW);      // [segmax]
+    uint8_t* sfl = reinterpret_cast<uint8_t*>(segi + segmax);                   // [QS]
+    const int t = threadIdx.x;
+    const int g = RMX_FIT();
+    for (int e = t; e < RMX_LW_SIZE; e += blockDim.x) lw[e] = Fp.logw[e];
+    {
+        const double* sg = Fp.stab + (int64_t)g * ST_NF * QS;
+        for (int e = t; e < ST_NF * QS; e += blockDim.x) st[e] = sg[e];
+        const uint8_t* fg = Fp.sflag + (int64_t)g * QS;
+        for (int e = t; e < QS; e += blockDim.x) sfl[e] = fg[e];
+    }
+    rmx_logtab_init(ltab);
+    const RmxParams& P = Pg[g];
+    const int NS = d.N * d.S;
+    const double* segc = segc_all + (int64_t)g * 12 * d.N;
+    double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
+    const uint8_t* tm = T.tmask + (int64_t)g * d.N;
+    const uint8_t* am = T.amask + (int64_t)g * d.N;
+    int flags = 0;
+    const double r0 = P.negbin_r[0], r1 = P.negbin_r[1];
+    const double lnr0 = log(r0), lnr1 = log(r1);
+    const double M0 = P.betabin_M[0], M1 = P.betabin_M[1];
+    for (int base = blockIdx.x * blockDim.x; base < NS; base += gridDim.x * blockDim.x) {
+        const int nfirst = base / d.S;
+        const int last = min(base + (int)blockDim.x, NS) - 1;
+        const int nseg = last / d.S - nfirst + 1;
+        for (int e = t; e < nseg * LLT2_SEGW; e += blockDim.x) {
+            const int sg = e / LLT2_SEGW, c = e - sg * LLT2_SEGW, n = nfirst + sg;
+            double v = 0.;
+            if (c < 2) v = segc[(int64_t)c * d.N + n];
+            else if (c < 6) {
+                // beta-binomial constant of (v,w) with the Stirling cores' -z + log(2 pi)/2 of its two lgammas folded in
+                const double na = T.y0[n] + T.y1[n];
+                v = segc[(int64_t)(c + 2) * d.N + n] - (na + (c < 4 ? M0 : M1)) + 2. * 0.91893853320467274178;
+            } else if (c == 6) { const double lv = T.l[n]; v = lv > 0. ? log(lv) : 0.; }
+            else if (c == 7) v = T.x[n];
+            else if (c == 8) v = T.l[n];
+            else if (c == 9) v = T.y0[n];
+            else if (c == 10) v = T.y1[n];
+            segs[e] = v;
+        }
+        for (int sg = t; sg < nseg; sg += blockDim.x) {
+            const int n = nfirst + sg;
+            const double xv = T.x[n], lv = T.l[n], a0 = T.y0[n], a1 = T.y1[n];
+            const bool okT = xv >= 0. && xv < 1e300 && lv > 0. && lv < 1e300;
+            const bool okA = a0 >= 0. && a1 >= 0. && (a0 + a1) > 0. && (a0 + a1) < 1e300;
+            segi[sg] = (tm[n] != 0 ? 1 : 0) | (am[n] != 0 ? 2 : 0) | (okT ? 4 : 0) | (okA ? 8 : 0) | ((int)Fp.nkind[n] << 8);
+        }
+        __syncthreads();
+        const int idx = base + t;
+        if (idx < NS) {
+            const int n = idx / d.S, s = idx - n * d.S, sg = n - nfirst;
+            const double* sp = segs + sg * LLT2_SEGW;
+            const int si = segi[sg];
+            const int e = (si >> 8) * d.S + s;
+            const int sf = sfl[e];
+            const bool tmk = (si & 1) != 0, amk = (si & 2) != 0;
+            double ll[RMX_NTERM];
+            if ((tmk && !((si & 4) && (sf & 1))) || (amk && !((si & 8) && (sf & 2)))) {
+                ll_slow(T, d, P, si, segc, n, s, ll, &flags, ltab);
+            } else {
+#pragma unroll
+                for (int k = 0; k < RMX_NTERM; ++k) ll[k] = 0.;
+                if (tmk) {
+                    const double x = sp[7];
+                    const double mu = st[e] * sp[8];
+                    const double lmu = st[QS + e] + sp[6];
+                    const double l0 = rmx_wlog(r0 + mu, lw), l1 = rmx_wlog(r1 + mu, lw);
+                    ll[0] = sp[0] + fma(x, lmu - l0, r0 * (lnr0 - l0));
+                    ll[1] = sp[1] + fma(x, lmu - l1, r1 * (lnr1 - l1));
+                }
+                if (amk) {
+                    const double y0 = sp[9], y1 = sp[10];
+#pragma unroll
+                    for (int v = 0; v < 2; ++v) {
+                        const double a = st[(2 + 2 * v) * QS + e], b = st[(3 + 2 * v) * QS + e];
+                        const double bs = st[(6 + v) * QS + e];
+                        const double c0 = rmx_lgcore(y0 + a, lw) + rmx_lgcore(y1 + b, lw);
+                        const double c1 = rmx_lgcore(y1 + a, lw) + rmx_lgcore(y0 + b, lw);
+                        ll[2 + 2 * v] = (sp[2 + 2 * v] + bs) + c0;
+                        ll[3 + 2 * v] = (sp[3 + 2 * v] + bs) + c1;
+                    }
+                }
+                // finite inputs cannot produce NaN here; parameters can (bpmodel.pyx:269, :344)
+                if (isnan(ll[0] + ll[1])) flags |= RMX_F_NB_NAN;
+                if (isnan((ll[2] + ll[3]) + (ll[4] + ll[5]))) flags |= RMX_F_BB_NAN;
+            }
+#pragma unroll
+            for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
+        }
+        __syncthreads();
+    }
+    if (flags) atomicOr(dflags, flags);
+}
+
 // Frame log-probability (bpmodel.pyx:898-919) from the LL table, one warp per (fit, segment).
 // Also writes the row max mF[n] and fexp[n,s] = exp(F[n,s] - mF[n]) for the scaled chain messages.
 __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
@@ -738,6 +900,32 @@ void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const
     const int segmax = 256 / d.S + 2;
     const size_t smem = (size_t)segmax * (LLT_SEGW * sizeof(double) + sizeof(int)) + (size_t)d.S * d.M * 2 + 16;
     k_lltable<<<dim3(grid, gn), 256, smem, st>>>(T, d, P, g0, segc, LL, dflags, segmax);
+}
+
+int rmx_lltable2_ok(const RmxDims& d, int Q) {
+    const int segmax = 256 / d.S + 2;
+    const size_t smem = (size_t)RMX_LW_SIZE * 16 + (size_t)ST_NF * Q * d.S * 8 + (size_t)segmax * (LLT2_SEGW * 8 + 4) + (size_t)Q * d.S + 16;
+    return smem <= 72 * 1024;
+}
+
+void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags) {
+    int64_t NS = (int64_t)d.N * d.S;
+    if (NS <= 0 || gn <= 0) return;
+    const int QS = Fp.Q * d.S;
+    k_statetab<<<dim3(cdiv(QS, 128), gn), 128, 0, st>>>(T, d, P, g0, Fp);
+    int64_t want = (NS + 255) / 256;
+    int64_t cap = ((int64_t)sm_count * 12 + gn - 1) / gn;   // whole grid sized in multiples of the SM count
+    if (cap < 1) cap = 1;
+    int grid = (int)(want < cap ? want : cap);
+    const int segmax = 256 / d.S + 2;
+    const size_t smem = (size_t)RMX_LW_SIZE * 16 + (size_t)ST_NF * QS * 8 + (size_t)segmax * (LLT2_SEGW * 8 + 4) + (size_t)QS + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_lltable2, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
+        attr_set = true;
+    }
+    k_lltable2<<<dim3(grid, gn), 256, smem, st>>>(T, d, P, g0, segc, Fp, LL, dflags, segmax);
 }
 
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
