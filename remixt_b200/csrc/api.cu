@@ -68,6 +68,7 @@ struct Batch {
     int8_t* kind_nrm = nullptr;
     double2* logw = nullptr;
     double* stab = nullptr;
+    double* segf = nullptr;
     int Q = 0;
     bool fast_ll = false;
     int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
@@ -274,9 +275,9 @@ static int ensure_ll(Model* m, int g0, int gn) {
         cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE);
         if (b->fast_ll) {
             RmxFast Fp;
-            Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag;
+            Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag; Fp.segf = b->segf;
             rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, Fp, b->LL, b->dflags);
-            b->count(1);
+            b->count(2);
         } else {
             rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags);
         }
@@ -774,6 +775,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
             CCK(upload(b, &b->logw, lw));
             CCK(dalloc(b, &b->stab, (size_t)G * 8 * b->Q * S));
             CCK(dalloc(b, &b->sflag, (size_t)G * b->Q * S));
+            CCK(dalloc(b, &b->segf, GN * 12));
         }
     }
     CCK(dalloc(b, &b->F, GNS));

@@ -70,6 +70,7 @@ struct RmxFast {
     const double2* logw;      // (RMX_LW_SIZE) wide log table
     double* stab;             // (G)(8,Q,S) per-(fit, kind, state) quantities
     uint8_t* sflag;           // (G)(Q,S)   bit 0: total-read fast path valid, bit 1: allele fast path valid
+    double* segf;             // (G)(N,12)  per-(fit, segment) inputs of the fast path (k_segfast)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -283,6 +284,52 @@ __device__ __forceinline__ double rmx_lgcore(double z, const double2* __restrict
     int idx;
     if (rmx_lw_in(z, &idx)) return rmx_lw_lgcore(z, lw[idx]);
     return rmx_lgcore_slow(z);
+}
+// W Stirling cores at once: one range test for all of them, then straight-line code the scheduler can interleave
+// (W independent dependency chains per thread; a branch per evaluation serialises them).
+template <int W>
+__device__ __forceinline__ void rmx_lgcore_n(const double (&z)[W], const double2* __restrict__ lw, double (&out)[W]) {
+    int idx[W];
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < W; ++i) ok = rmx_lw_in(z[i], &idx[i]) && ok;
+    if (ok) {
+        double2 t[W];
+        double r[W], p[W], q[W], s[W];
+#pragma unroll
+        for (int i = 0; i < W; ++i) t[i] = lw[idx[i]];
+#pragma unroll
+        for (int i = 0; i < W; ++i) asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(q[i]) : "d"(z[i]));
+#pragma unroll
+        for (int i = 0; i < W; ++i) r[i] = fma(z[i], t[i].x, -1.0);
+#pragma unroll
+        for (int i = 0; i < W; ++i) q[i] = fma(q[i], fma(-z[i], q[i], 1.0), q[i]);
+#pragma unroll
+        for (int i = 0; i < W; ++i) p[i] = fma(-1.0 / 6.0, r[i], 0.2);
+#pragma unroll
+        for (int i = 0; i < W; ++i) s[i] = q[i] * q[i];
+#pragma unroll
+        for (int i = 0; i < W; ++i) p[i] = fma(p[i], r[i], -0.25);
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = fma(8.4175084175084175084e-4, s[i], -5.9523809523809523810e-4);
+#pragma unroll
+        for (int i = 0; i < W; ++i) p[i] = fma(p[i], r[i], 1.0 / 3.0);
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = fma(out[i], s[i], 7.9365079365079365079e-4);
+#pragma unroll
+        for (int i = 0; i < W; ++i) p[i] = fma(p[i], r[i], -0.5);
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = fma(out[i], s[i], -2.7777777777777777778e-3);
+#pragma unroll
+        for (int i = 0; i < W; ++i) p[i] = fma(p[i] * r[i], r[i], r[i]);
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = fma(out[i], s[i], 8.3333333333333333333e-2);
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = fma(z[i] - 0.5, t[i].y + p[i], out[i] * q[i]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < W; ++i) out[i] = rmx_lgcore_slow(z[i]);
+    }
 }
 __device__ __forceinline__ double rmx_wlog(double z, const double2* __restrict__ lw) {
     int idx;

@@ -244,18 +244,50 @@ __device__ __noinline__ void ll_slow(const RmxTables& T, const RmxDims& d, const
     ll_terms(T, d, P, (si & 1) != 0, (si & 2) != 0, segc, d.N, n, n, s, ll, flags, ltab);
 }
 
-#define LLT2_SEGW 12     // doubles per staged segment
+// Per-(fit, segment) inputs of the fast path, 12 doubles each (segf[g][n][12], three 32-byte sectors):
+//   0-1 negative-binomial constants (u)     2-5 beta-binomial constants (v,w) with the Stirling cores'
+//   -z + log(2 pi)/2 of their two lgammas folded in      6 log l     7 x   8 l   9 y0   10 y1
+//   11 (as an integer) bit 0 total mask, bit 1 allele mask, bit 2 / 3 total / allele data valid for the fast
+//   path, bits 8.. normal-copy kind
+#define LLT2_SEGW 12
+__global__ void k_segfast(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                          const double* __restrict__ segc_all, RmxFast Fp) {
+    const int g = RMX_FIT();
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= d.N) return;
+    const RmxParams& P = Pg[g];
+    const double* segc = segc_all + (int64_t)g * 12 * d.N;
+    double* o = Fp.segf + ((int64_t)g * d.N + n) * LLT2_SEGW;
+    const double xv = T.x[n], lv = T.l[n], a0 = T.y0[n], a1 = T.y1[n];
+    const double na = a0 + a1;
+    const bool okT = xv >= 0. && xv < 1e300 && lv > 0. && lv < 1e300;
+    const bool okA = a0 >= 0. && a1 >= 0. && na > 0. && na < 1e300;
+    const int si = (T.tmask[(int64_t)g * d.N + n] != 0 ? 1 : 0) | (T.amask[(int64_t)g * d.N + n] != 0 ? 2 : 0) |
+                   (okT ? 4 : 0) | (okA ? 8 : 0) | ((int)Fp.nkind[n] << 8);
+    o[0] = segc[n];
+    o[1] = segc[(int64_t)d.N + n];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        o[2 + c] = segc[(int64_t)(4 + c) * d.N + n] - (na + P.betabin_M[c >> 1]) + 2. * 0.91893853320467274178;
+    o[6] = lv > 0. ? log(lv) : 0.;
+    o[7] = xv;
+    o[8] = lv;
+    o[9] = a0;
+    o[10] = a1;
+    o[11] = __longlong_as_double((long long)si);
+}
+
+// No barrier inside the unit loop: every thread reads its segment's 96 bytes itself (three sectors, shared by the
+// 97 consecutive units of the segment, so L1 hits after the first touch) and warps proceed independently.
 __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                    const double* __restrict__ segc_all, RmxFast Fp,
-                                                   double* __restrict__ LL_all, int* __restrict__ dflags, int segmax) {
+                                                   double* __restrict__ LL_all, int* __restrict__ dflags) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double2 ltab[RMX_LOGTAB];
     const int QS = Fp.Q * d.S;
     double2* lw = reinterpret_cast<double2*>(smem_raw);                          // [RMX_LW_SIZE]
     double* st = reinterpret_cast<double*>(lw + RMX_LW_SIZE);                   // [ST_NF][QS]
-    double* segs = st + (size_t)ST_NF * QS;                                     // [segmax][LLT2_SEGW]
-    int* segi = reinterpret_cast<int*>(segs + (size_t)segmax * LLT2_SEGW);      // [segmax]
-    uint8_t* sfl = reinterpret_cast<uint8_t*>(segi + segmax);                   // [QS]
+    uint8_t* sfl = reinterpret_cast<uint8_t*>(st + (size_t)ST_NF * QS);         // [QS]
     const int t = threadIdx.x;
     const int g = RMX_FIT();
     for (int e = t; e < RMX_LW_SIZE; e += blockDim.x) lw[e] = Fp.logw[e];
@@ -269,82 +301,67 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
     const RmxParams& P = Pg[g];
     const int NS = d.N * d.S;
     const double* segc = segc_all + (int64_t)g * 12 * d.N;
+    const double2* segf = reinterpret_cast<const double2*>(Fp.segf + (int64_t)g * d.N * LLT2_SEGW);
     double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
-    const uint8_t* tm = T.tmask + (int64_t)g * d.N;
-    const uint8_t* am = T.amask + (int64_t)g * d.N;
     int flags = 0;
     const double r0 = P.negbin_r[0], r1 = P.negbin_r[1];
     const double lnr0 = log(r0), lnr1 = log(r1);
-    const double M0 = P.betabin_M[0], M1 = P.betabin_M[1];
-    for (int base = blockIdx.x * blockDim.x; base < NS; base += gridDim.x * blockDim.x) {
-        const int nfirst = base / d.S;
-        const int last = min(base + (int)blockDim.x, NS) - 1;
-        const int nseg = last / d.S - nfirst + 1;
-        for (int e = t; e < nseg * LLT2_SEGW; e += blockDim.x) {
-            const int sg = e / LLT2_SEGW, c = e - sg * LLT2_SEGW, n = nfirst + sg;
-            double v = 0.;
-            if (c < 2) v = segc[(int64_t)c * d.N + n];
-            else if (c < 6) {
-                // beta-binomial constant of (v,w) with the Stirling cores' -z + log(2 pi)/2 of its two lgammas folded in
-                const double na = T.y0[n] + T.y1[n];
-                v = segc[(int64_t)(c + 2) * d.N + n] - (na + (c < 4 ? M0 : M1)) + 2. * 0.91893853320467274178;
-            } else if (c == 6) { const double lv = T.l[n]; v = lv > 0. ? log(lv) : 0.; }
-            else if (c == 7) v = T.x[n];
-            else if (c == 8) v = T.l[n];
-            else if (c == 9) v = T.y0[n];
-            else if (c == 10) v = T.y1[n];
-            segs[e] = v;
-        }
-        for (int sg = t; sg < nseg; sg += blockDim.x) {
-            const int n = nfirst + sg;
-            const double xv = T.x[n], lv = T.l[n], a0 = T.y0[n], a1 = T.y1[n];
-            const bool okT = xv >= 0. && xv < 1e300 && lv > 0. && lv < 1e300;
-            const bool okA = a0 >= 0. && a1 >= 0. && (a0 + a1) > 0. && (a0 + a1) < 1e300;
-            segi[sg] = (tm[n] != 0 ? 1 : 0) | (am[n] != 0 ? 2 : 0) | (okT ? 4 : 0) | (okA ? 8 : 0) | ((int)Fp.nkind[n] << 8);
-        }
-        __syncthreads();
-        const int idx = base + t;
-        if (idx < NS) {
-            const int n = idx / d.S, s = idx - n * d.S, sg = n - nfirst;
-            const double* sp = segs + sg * LLT2_SEGW;
-            const int si = segi[sg];
-            const int e = (si >> 8) * d.S + s;
-            const int sf = sfl[e];
-            const bool tmk = (si & 1) != 0, amk = (si & 2) != 0;
-            double ll[RMX_NTERM];
-            if ((tmk && !((si & 4) && (sf & 1))) || (amk && !((si & 8) && (sf & 2)))) {
-                ll_slow(T, d, P, si, segc, n, s, ll, &flags, ltab);
-            } else {
+    for (int idx = blockIdx.x * blockDim.x + t; idx < NS; idx += gridDim.x * blockDim.x) {
+        const int n = idx / d.S, s = idx - n * d.S;
+        const double2* sp = segf + (int64_t)n * (LLT2_SEGW / 2);
+        const double2 s45 = __ldg(sp + 5);                       // y1, flags
+        const int si = (int)__double_as_longlong(s45.y);
+        const int e = (si >> 8) * d.S + s;
+        const int sf = sfl[e];
+        const bool tmk = (si & 1) != 0, amk = (si & 2) != 0;
+        double ll[RMX_NTERM];
+        if ((tmk && !((si & 4) && (sf & 1))) || (amk && !((si & 8) && (sf & 2)))) {
+            ll_slow(T, d, P, si, segc, n, s, ll, &flags, ltab);
+        } else {
 #pragma unroll
-                for (int k = 0; k < RMX_NTERM; ++k) ll[k] = 0.;
-                if (tmk) {
-                    const double x = sp[7];
-                    const double mu = st[e] * sp[8];
-                    const double lmu = st[QS + e] + sp[6];
-                    const double l0 = rmx_wlog(r0 + mu, lw), l1 = rmx_wlog(r1 + mu, lw);
-                    ll[0] = sp[0] + fma(x, lmu - l0, r0 * (lnr0 - l0));
-                    ll[1] = sp[1] + fma(x, lmu - l1, r1 * (lnr1 - l1));
-                }
-                if (amk) {
-                    const double y0 = sp[9], y1 = sp[10];
-#pragma unroll
-                    for (int v = 0; v < 2; ++v) {
-                        const double a = st[(2 + 2 * v) * QS + e], b = st[(3 + 2 * v) * QS + e];
-                        const double bs = st[(6 + v) * QS + e];
-                        const double c0 = rmx_lgcore(y0 + a, lw) + rmx_lgcore(y1 + b, lw);
-                        const double c1 = rmx_lgcore(y1 + a, lw) + rmx_lgcore(y0 + b, lw);
-                        ll[2 + 2 * v] = (sp[2 + 2 * v] + bs) + c0;
-                        ll[3 + 2 * v] = (sp[3 + 2 * v] + bs) + c1;
+            for (int k = 0; k < RMX_NTERM; ++k) ll[k] = 0.;
+            if (tmk) {
+                const double2 c01 = __ldg(sp), lx = __ldg(sp + 3), ly = __ldg(sp + 4);   // (c0,c1) (logl,x) (l,y0)
+                const double x = lx.y;
+                const double mu = st[e] * ly.x;
+                const double lmu = st[QS + e] + lx.x;
+                double l0, l1;
+                {
+                    const double z0 = r0 + mu, z1 = r1 + mu;
+                    int i0, i1;
+                    const bool in0 = rmx_lw_in(z0, &i0), in1 = rmx_lw_in(z1, &i1);
+                    if (in0 && in1) {
+                        const double2 t0 = lw[i0], t1 = lw[i1];
+                        l0 = rmx_lw_log(z0, t0);
+                        l1 = rmx_lw_log(z1, t1);
+                    } else {
+                        l0 = log(z0);
+                        l1 = log(z1);
                     }
                 }
-                // finite inputs cannot produce NaN here; parameters can (bpmodel.pyx:269, :344)
-                if (isnan(ll[0] + ll[1])) flags |= RMX_F_NB_NAN;
-                if (isnan((ll[2] + ll[3]) + (ll[4] + ll[5]))) flags |= RMX_F_BB_NAN;
+                ll[0] = c01.x + fma(x, lmu - l0, r0 * (lnr0 - l0));
+                ll[1] = c01.y + fma(x, lmu - l1, r1 * (lnr1 - l1));
             }
+            if (amk) {
+                const double y0 = __ldg(sp + 4).y, y1 = s45.x;
+                const double2 cb0 = __ldg(sp + 1), cb1 = __ldg(sp + 2);
 #pragma unroll
-            for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
+                for (int v = 0; v < 2; ++v) {
+                    const double a = st[(2 + 2 * v) * QS + e], b = st[(3 + 2 * v) * QS + e];
+                    const double bs = st[(6 + v) * QS + e];
+                    const double z[4] = {y0 + a, y1 + b, y1 + a, y0 + b};
+                    double c[4];
+                    rmx_lgcore_n<4>(z, lw, c);
+                    ll[2 + 2 * v] = ((v ? cb1.x : cb0.x) + bs) + (c[0] + c[1]);
+                    ll[3 + 2 * v] = ((v ? cb1.y : cb0.y) + bs) + (c[2] + c[3]);
+                }
+            }
+            // finite inputs cannot produce NaN here; parameters can (bpmodel.pyx:269, :344)
+            if (isnan(ll[0] + ll[1])) flags |= RMX_F_NB_NAN;
+            if (isnan((ll[2] + ll[3]) + (ll[4] + ll[5]))) flags |= RMX_F_BB_NAN;
         }
-        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
     }
     if (flags) atomicOr(dflags, flags);
 }
@@ -902,11 +919,10 @@ void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const
     k_lltable<<<dim3(grid, gn), 256, smem, st>>>(T, d, P, g0, segc, LL, dflags, segmax);
 }
 
-int rmx_lltable2_ok(const RmxDims& d, int Q) {
-    const int segmax = 256 / d.S + 2;
-    const size_t smem = (size_t)RMX_LW_SIZE * 16 + (size_t)ST_NF * Q * d.S * 8 + (size_t)segmax * (LLT2_SEGW * 8 + 4) + (size_t)Q * d.S + 16;
-    return smem <= 72 * 1024;
+static size_t lltable2_smem(const RmxDims& d, int Q) {
+    return (size_t)RMX_LW_SIZE * 16 + (size_t)ST_NF * Q * d.S * 8 + (size_t)Q * d.S + 16;
 }
+int rmx_lltable2_ok(const RmxDims& d, int Q) { return lltable2_smem(d, Q) <= 72 * 1024; }
 
 void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
                          int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags) {
@@ -914,18 +930,17 @@ void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, cons
     if (NS <= 0 || gn <= 0) return;
     const int QS = Fp.Q * d.S;
     k_statetab<<<dim3(cdiv(QS, 128), gn), 128, 0, st>>>(T, d, P, g0, Fp);
+    k_segfast<<<dim3(cdiv(d.N, 128), gn), 128, 0, st>>>(T, d, P, g0, segc, Fp);
     int64_t want = (NS + 255) / 256;
     int64_t cap = ((int64_t)sm_count * 12 + gn - 1) / gn;   // whole grid sized in multiples of the SM count
     if (cap < 1) cap = 1;
     int grid = (int)(want < cap ? want : cap);
-    const int segmax = 256 / d.S + 2;
-    const size_t smem = (size_t)RMX_LW_SIZE * 16 + (size_t)ST_NF * QS * 8 + (size_t)segmax * (LLT2_SEGW * 8 + 4) + (size_t)QS + 16;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(k_lltable2, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
         attr_set = true;
     }
-    k_lltable2<<<dim3(grid, gn), 256, smem, st>>>(T, d, P, g0, segc, Fp, LL, dflags, segmax);
+    k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags);
 }
 
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
