@@ -138,6 +138,9 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
 int rmx_batch_view(rmx_handle h, int first_fit, int num_fits, rmx_handle* out);
 int rmx_num_fits(rmx_handle h, int* num_fits);
 int rmx_destroy(rmx_handle h);
+/* Device blocks of destroyed batches are kept for the next batch of the same shapes (cudaMalloc / cudaFree of a
+ * whole-genome init grid cost more than its E-step); this returns them to the driver (device < 0: every device). */
+int rmx_release_cached_memory(int device);
 /* Message of the last failure on this handle (or of rmx_create when h == NULL). */
 const char* rmx_last_error(rmx_handle h);
 int rmx_device_count(int* count);

@@ -33,7 +33,8 @@ U_ALLELE_SWAP, U_CN, U_BREAKPOINT, U_OUTLIER_TOTAL, U_OUTLIER_ALLELE, U_FRAMELOG
 
 # every symbol include/remixt_b200.h declares
 EXPORTS = [
-    'rmx_create', 'rmx_batch_create', 'rmx_batch_view', 'rmx_num_fits', 'rmx_destroy', 'rmx_last_error', 'rmx_device_count',
+    'rmx_create', 'rmx_batch_create', 'rmx_batch_view', 'rmx_num_fits', 'rmx_destroy', 'rmx_release_cached_memory', 'rmx_last_error',
+    'rmx_device_count',
     'rmx_set_array', 'rmx_get_array', 'rmx_set_scalar', 'rmx_get_scalar', 'rmx_get_derived',
     'rmx_update', 'rmx_variational_update',
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
@@ -72,6 +73,7 @@ def _load():
         'rmx_batch_view': [H, I, I, C.POINTER(H)],
         'rmx_num_fits': [H, C.POINTER(I)],
         'rmx_destroy': [H],
+        'rmx_release_cached_memory': [I],
         'rmx_device_count': [C.POINTER(I)],
         'rmx_set_array': [H, I, P, I64],
         'rmx_get_array': [H, I, P, I64],
@@ -137,6 +139,11 @@ def device_count():
     n = C.c_int(0)
     lib.rmx_device_count(C.byref(n))
     return n.value
+
+
+def release_cached_memory(device=-1):
+    """Return the device blocks kept from destroyed batches to the driver."""
+    lib.rmx_release_cached_memory(int(device))
 
 
 def global_launch_count():

@@ -28,6 +28,58 @@
 #include "kernels.h"
 
 static thread_local std::string g_create_error;
+
+// Device-memory pool.  A fit of one sample is followed by the fit of the next with the same shapes (init grids,
+// restarts, batches of genomes), and cudaMalloc / cudaFree of a 12 GB working set costs more than the E-step it
+// serves.  Freed blocks are kept per (device, size) and handed back to the next batch; rmx_release_cached_memory
+// returns them to the driver, and the pool gives way when an allocation fails.
+struct DevPool {
+    std::mutex mu;
+    std::multimap<std::pair<int, size_t>, void*> free_blocks;
+    size_t cached = 0;
+    cudaError_t get(int device, size_t bytes, void** p) {
+        *p = nullptr;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            auto it = free_blocks.find({device, bytes});
+            if (it != free_blocks.end()) {
+                *p = it->second;
+                free_blocks.erase(it);
+                cached -= bytes;
+            }
+        }
+        if (*p) {   // a recycled block starts zeroed, as nothing may depend on the previous owner's contents
+            cudaError_t e = cudaMemsetAsync(*p, 0, bytes, 0);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+            return e;
+        }
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            release(device);
+            e = cudaMalloc(p, bytes);
+        }
+        return e;
+    }
+    void put(int device, size_t bytes, void* p) {
+        std::lock_guard<std::mutex> lk(mu);
+        free_blocks.insert({{device, bytes}, p});
+        cached += bytes;
+    }
+    void release(int device) {
+        std::lock_guard<std::mutex> lk(mu);
+        for (auto it = free_blocks.begin(); it != free_blocks.end();) {
+            if (device < 0 || it->first.first == device) {
+                cudaFree(it->second);
+                cached -= it->first.second;
+                it = free_blocks.erase(it);
+            } else {
+                ++it;
+            }
+        }
+    }
+};
+static DevPool g_pool;
 static std::atomic<int64_t> g_launches{0};
 
 struct ClassMats {
@@ -43,7 +95,7 @@ struct Batch {
     RmxDims d{};
     int G = 1;
     double pen = 0., prior_ot = 0.01, prior_oa = 0.01;
-    std::vector<void*> allocs;
+    std::vector<std::pair<void*, size_t>> allocs;
 
     // per-fit host state
     std::vector<RmxParams> P;
@@ -119,7 +171,7 @@ struct Batch {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);
         for (auto& t : tev) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
-        for (void* p : allocs) cudaFree(p);
+        for (auto& p : allocs) g_pool.put(device, p.second, p.first);
         if (hp) cudaFreeHost(hp);
         if (hflags) cudaFreeHost(hflags);
         if (hrows) cudaFreeHost(hrows);
@@ -159,8 +211,8 @@ typedef std::lock_guard<std::recursive_mutex> Lock;
 template <typename T>
 static cudaError_t dalloc(Batch* b, T** p, size_t n) {
     if (n == 0) n = 1;
-    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
-    if (e == cudaSuccess) b->allocs.push_back((void*)*p);
+    cudaError_t e = g_pool.get(b->device, n * sizeof(T), (void**)p);
+    if (e == cudaSuccess) b->allocs.push_back({(void*)*p, n * sizeof(T)});
     return e;
 }
 template <typename T>
@@ -470,6 +522,11 @@ int rmx_device_count(int* count) {
         g_create_error = std::string("cudaGetDeviceCount failed: ") + cudaGetErrorString(e);
         return RMX_ERR_CUDA;
     }
+    return RMX_OK;
+}
+
+int rmx_release_cached_memory(int device) {
+    g_pool.release(device);
     return RMX_OK;
 }
 
