@@ -121,6 +121,8 @@ struct Batch {
     double2* logw = nullptr;
     double* stab = nullptr;
     double* segf = nullptr;
+    uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
+    int* hgstart = nullptr;
     int Q = 0;
     bool fast_ll = false;
     int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
@@ -447,7 +449,7 @@ static int do_update_p_cn(Model* m) {
     for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
         { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
-                        b->dflags); b->tend(te_); }
+                        b->dflags, b->hord, b->hgstart); b->tend(te_); }
         if (b->R > 0) b->count();
     });
     for (int g = g0; g < g0 + gn; ++g) {
@@ -471,7 +473,7 @@ static int do_update_p_breakpoint(Model* m) {
         for_runs(g0, gn, b->tm_cached, &need, [&](int g, int n) {
             RmxTransSpec sp = spec_of(b, true, b->tm_cached[g]);
             { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 1, b->ahat, b->bhat, b->fexp,
-                            b->hist, b->dflags); b->tend(te_); }
+                            b->hist, b->dflags, b->hord, b->hgstart); b->tend(te_); }
             b->count();
             for (int k = g; k < g + n; ++k) b->hist_valid[k] = 1;
         });
@@ -834,6 +836,11 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
             CCK(dalloc(b, &b->sflag, (size_t)G * b->Q * S));
             CCK(dalloc(b, &b->segf, GN * 12));
         }
+    }
+    if (rmx_hist2_ok(d)) {
+        CCK(dalloc(b, &b->hord, (size_t)M * S));
+        CCK(dalloc(b, &b->hgstart, (size_t)rmx_hist2_gstart_count(d)));
+        rmx_launch_hist_prep(b->stream, tables(b), d, b->hord, b->hgstart);
     }
     CCK(dalloc(b, &b->F, GNS));
     CCK(dalloc(b, &b->fexp, GNS));

@@ -618,6 +618,155 @@ __global__ void __launch_bounds__(256) k_hist(RmxDims d, int g0, RmxRows rows, R
         hist[(int64_t)r * M * d.D + e] = (double)hacc[e] * 2.168404344971008868e-19;   // 2^-62
 }
 
+// K-hist, state spaces up to 128: no atomics.  The order of the states by each tumour clone's total copy number
+// (ord) and the start of every total's group in that order (gstart) depend on the state table only and are built
+// once per batch (k_hist_prep).  Per breakend row: (1) the S x S pair weights go to shared memory once (warp per
+// row i, lanes along j; Z by a fixed-order CTA sum); (2) warp per (clone m, total t): column sums over the rows of
+// that group, colsum[m][t][j] = sum_{i: tot_i[m] = t} W[i][j]; (3) warp per (m, slot):
+// hist[m][slot] = sum_j colsum[m][tot_j[m] + slot - doff][j] / Z.  Every sum has a fixed order.
+#define HIST2_TV 16     // totals per clone covered (cn_max + 2 <= 16)
+#define HIST2_SP 128    // padded state count
+__global__ void k_hist_prep(const int8_t* __restrict__ tab, int S, int M, uint8_t* __restrict__ ord,
+                            int* __restrict__ gstart) {
+    for (int e = threadIdx.x; e < M * S; e += blockDim.x) {
+        const int m = e / S, j = e - m * S;
+        if (m == 0) { ord[e] = (uint8_t)j; continue; }
+        const int tj = tab[(j * M + m) * 2] + tab[(j * M + m) * 2 + 1];
+        int rank = 0;
+        for (int k = 0; k < S; ++k) {
+            const int tk = tab[(k * M + m) * 2] + tab[(k * M + m) * 2 + 1];
+            rank += (tk < tj || (tk == tj && k < j)) ? 1 : 0;
+        }
+        ord[m * S + rank] = (uint8_t)j;
+    }
+    for (int e = threadIdx.x; e < M * (HIST2_TV + 1); e += blockDim.x) {
+        const int m = e / (HIST2_TV + 1), tv = e - m * (HIST2_TV + 1);
+        int cnt = 0;
+        for (int k = 0; k < S; ++k) cnt += (m > 0 && tab[(k * M + m) * 2] + tab[(k * M + m) * 2 + 1] < tv) ? 1 : 0;
+        gstart[e] = cnt;
+    }
+}
+
+// pair weights of the row in place over the staged transition factor: lanes keep their columns' g_j and table
+// offsets in registers, the row's a_i and totals are warp-uniform; same operation order as pair_w / brk_E.
+// MM = number of clones at compile time (0: any, loops not unrolled).
+template <int MM>
+__device__ __forceinline__ double hist2_weights(const PairCtx& c, const RmxDims& d, double* __restrict__ W, int lane,
+                                                int wid, int nw) {
+    const int S = d.S, M = MM > 0 ? MM : d.M;
+    constexpr int MR = MM > 0 ? MM : RMX_MAXM;
+    double gj[HIST2_SP / 32];
+    int bj[HIST2_SP / 32][MR];
+#pragma unroll
+    for (int kk = 0; kk < HIST2_SP / 32; ++kk) {
+        const int j = lane + 32 * kk;
+        gj[kk] = j < S ? c.g[j] : 0.;
+#pragma unroll
+        for (int m = 1; m < MR; ++m)
+            if (m < M) bj[kk][m] = m * d.D + d.doff - (j < S ? (int)c.tots[j * M + m] : 0);
+    }
+    const double w0 = c.kind == 2 ? c.wtab[c.d0 + d.doff] : 1.;
+    double z = 0.;
+    for (int i = wid; i < S; i += nw) {
+        const double ai = c.a[i];
+        int ti[MR];
+#pragma unroll
+        for (int m = 1; m < MR; ++m)
+            if (m < M) ti[m] = (int)c.tots[i * M + m];
+#pragma unroll
+        for (int kk = 0; kk < HIST2_SP / 32; ++kk) {
+            const int j = lane + 32 * kk;
+            if (j < S) {
+                double e = 1.;
+                if (c.kind == 1) {
+                    e = W[i * S + j];
+                } else if (c.kind == 2) {
+                    e = W[i * S + j] * w0;
+#pragma unroll
+                    for (int m = 1; m < MR; ++m)
+                        if (m < M) e *= c.wtab[bj[kk][m] + ti[m]];
+                }
+                const double w = ai * e * gj[kk];
+                W[i * S + j] = w;
+                z += w;
+            }
+        }
+    }
+    return z;
+}
+
+__global__ void __launch_bounds__(256, 2) k_hist2(RmxDims d, int g0, RmxRows rows, RmxTransSpec sp, int64_t sp_fit_stride,
+                                                 const int8_t* __restrict__ tab, const uint8_t* __restrict__ ord,
+                                                 const int* __restrict__ gstart, int uniform,
+                                                 const double* __restrict__ ahat_all, const double* __restrict__ bhat_all,
+                                                 const double* __restrict__ fexp_all, double* __restrict__ hist_all,
+                                                 int* __restrict__ dflags) {
+    const int g = RMX_FIT();
+    const int64_t NSo = (int64_t)g * d.N * d.S;
+    const double *ahat = ahat_all + NSo, *bhat = bhat_all + NSo, *fexp = fexp_all + NSo;
+    double* hist = hist_all + (int64_t)g * sp_fit_stride;
+    sp.pd += (int64_t)g * sp_fit_stride;
+    sp.wexp += (int64_t)g * sp_fit_stride;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ double red[32];
+    const int S = d.S, M = d.M;
+    const int r = blockIdx.x;
+    const int n = rows.brk_rows[r];
+    PairCtx c;
+    pair_setup(c, smem_raw, d, rows, sp, tab, uniform, n, ahat, bhat, fexp);
+    size_t off = (sizeof(double) * (2 * (size_t)S + (size_t)M * d.D) + (size_t)S * M + 15) & ~(size_t)15;
+    double* W = reinterpret_cast<double*>(smem_raw + off);              // [S][S]
+    double* colsum = W + (size_t)S * S;                                 // [M-1][HIST2_TV][HIST2_SP]
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
+    // the row's S x S transition factor (class matrix, shared by every CTA: L2) lands in W asynchronously, one
+    // round trip for the whole matrix instead of one per pair; the weights are then formed in place
+    if (c.kind != 0) {
+        const unsigned wbase = (unsigned)__cvta_generic_to_shared(W);
+        for (int e = t; e < S * S; e += blockDim.x)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(wbase + 8u * (unsigned)e), "l"(c.E + e) : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    double z;
+    switch (M) {
+    case 2: z = hist2_weights<2>(c, d, W, lane, wid, nw); break;
+    case 3: z = hist2_weights<3>(c, d, W, lane, wid, nw); break;
+    case 4: z = hist2_weights<4>(c, d, W, lane, wid, nw); break;
+    default: z = hist2_weights<0>(c, d, W, lane, wid, nw); break;
+    }
+    z = block_sum_all(z, red);      // includes the barrier that publishes W
+    if (!(z > 0.) || isinf(z)) {
+        if (t == 0) atomicOr(dflags, RMX_F_JOINT_NAN);
+    }
+    for (int q = wid; q < (M - 1) * HIST2_TV; q += nw) {
+        const int m = 1 + q / HIST2_TV, tv = q - (m - 1) * HIST2_TV;
+        const int k0 = gstart[m * (HIST2_TV + 1) + tv], k1 = gstart[m * (HIST2_TV + 1) + tv + 1];
+        double acc[HIST2_SP / 32] = {0., 0., 0., 0.};
+        for (int k = k0; k < k1; ++k) {
+            const double* Wi = W + (int)ord[m * S + k] * S;
+#pragma unroll
+            for (int kk = 0; kk < HIST2_SP / 32; ++kk)
+                if (lane + 32 * kk < S) acc[kk] += Wi[lane + 32 * kk];
+        }
+#pragma unroll
+        for (int kk = 0; kk < HIST2_SP / 32; ++kk) colsum[q * HIST2_SP + lane + 32 * kk] = acc[kk];
+    }
+    __syncthreads();
+    const double inv = 1. / z;
+    for (int q = wid; q < (M - 1) * d.D; q += nw) {
+        const int m = 1 + q / d.D, slot = q - (m - 1) * d.D;
+        const int dd = slot - d.doff;
+        double v = 0.;
+        for (int j = lane; j < S; j += 32) {
+            const int tv = (int)c.tots[j * M + m] + dd;
+            if (tv >= 0 && tv < HIST2_TV) v += colsum[((m - 1) * HIST2_TV + tv) * HIST2_SP + j];
+        }
+        v = warp_sum(v);
+        if (lane == 0) hist[((int64_t)r * M + m) * d.D + slot] = v * inv;
+    }
+    for (int e = t; e < d.D; e += blockDim.x) hist[(int64_t)r * M * d.D + e] = (e == c.d0 + d.doff) ? 1. : 0.;
+}
+
 // update_p_breakpoint (bpmodel.pyx:964-983): one CTA per (fit, breakpoint), one thread per breakpoint
 // state (B <= 64).  Each thread accumulates its log q in the reference's order (breakend rows ascending,
 // clones, copy-number differences); thread 0 then does the two sequential sums of _exp_normalize
@@ -1131,10 +1280,29 @@ static size_t pair_smem(const RmxDims& d) {
     return sizeof(double) * (2 * (size_t)d.S + (size_t)d.M * d.D) + (size_t)d.S * d.M + 16;
 }
 
+int rmx_hist2_ok(const RmxDims& d) { return d.S <= 128 && d.cn_max + 2 <= HIST2_TV && d.M >= 2; }
+int rmx_hist2_gstart_count(const RmxDims& d) { return d.M * (HIST2_TV + 1); }
+void rmx_launch_hist_prep(cudaStream_t st, const RmxTables& T, const RmxDims& d, uint8_t* hord, int* hgstart) {
+    k_hist_prep<<<1, 256, 0, st>>>(T.tab, d.S, d.M, hord, hgstart);
+}
+
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
                      const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
-                     const double* fexp, double* hist, int* dflags) {
+                     const double* fexp, double* hist, int* dflags, const uint8_t* hord, const int* hgstart) {
     if (R <= 0 || gn <= 0) return;
+    // S <= 128 and totals below HIST2_TV: the atomic-free kernel
+    const size_t base = (pair_smem(d) + 15) & ~(size_t)15;
+    const size_t smem2 = base + sizeof(double) * ((size_t)d.S * d.S + (size_t)(d.M - 1) * HIST2_TV * HIST2_SP) + 16;
+    if (hord != nullptr && rmx_hist2_ok(d) && smem2 <= 200 * 1024) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaFuncSetAttribute(k_hist2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            attr_set = true;
+        }
+        k_hist2<<<dim3(R, gn), 256, smem2, st>>>(d, g0, rows, sp, sp_fit_stride, T.tab, hord, hgstart, uniform, ahat, bhat,
+                                                 fexp, hist, dflags);
+        return;
+    }
     k_hist<<<dim3(R, gn), 256, pair_smem(d), st>>>(d, g0, rows, sp, sp_fit_stride, T.tab, uniform, ahat, bhat, fexp, hist,
                                                   dflags);
 }

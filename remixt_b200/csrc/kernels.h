@@ -89,7 +89,12 @@ void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const do
                      double* post, int* dflags);
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
                      const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
-                     const double* fexp, double* hist, int* dflags);
+                     const double* fexp, double* hist, int* dflags, const uint8_t* hord = nullptr,
+                     const int* hgstart = nullptr);
+// atomic-free histogram kernel (S <= 128): per-batch state order tables
+int rmx_hist2_ok(const RmxDims& d);
+int rmx_hist2_gstart_count(const RmxDims& d);
+void rmx_launch_hist_prep(cudaStream_t st, const RmxTables& T, const RmxDims& d, uint8_t* hord, int* hgstart);
 void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, int g0, int gn, const int* krow_ptr, const int* krow_idx,
                            const int* brk_rows, const int* borient, const int8_t* brk, const double* hist,
                            int64_t hist_fit_stride, double pen, int tm, double* p_brk);
