@@ -44,6 +44,10 @@ typedef enum {
     RMX_ERR_ARG = 5          /* bad id / size passed through this C-ABI                  */
 } rmx_status;
 
+/* rmx_desc.flags: the model is one shard of a chromosome-sharded fit: it holds a subset of the chromosomes and
+ * all K breakpoints, breakpoint_idx marks the breakends on its own chromosomes only. */
+#define RMX_DESC_SHARD 1
+
 /* Constructor arguments: RemixtModel.__cinit__ (bpmodel.pyx:461-476), same order/meaning. */
 typedef struct {
     int32_t num_clones;            /* M  (bpmodel.pyx:462) */
@@ -53,7 +57,7 @@ typedef struct {
     int32_t num_cn_states;         /* S = cn_states.shape[1] */
     int32_t num_brk_states;        /* B = brk_states.shape[0] */
     int32_t device;                /* CUDA device ordinal the model lives on */
-    int32_t reserved;
+    int32_t flags;                 /* RMX_DESC_* bits; 0 = the reference's constructor exactly */
     const int64_t* cn_states;      /* (N1,S,M,2) (bpmodel.pyx:466); may be NULL if the compact pair below is given */
     const int64_t* cn_table;       /* optional compact form: (S,M,2), clone 0 row ignored */
     const int64_t* normal_copies;  /* optional compact form: (N1,2) = cn_states[n,:,0,:]  */
@@ -162,6 +166,13 @@ int rmx_update(rmx_handle h, int update_id);
 /* n_iter rounds of swap -> cn -> breakpoint -> outlier_total -> outlier_allele, the order of
  * cn_model.py:444-460, on the handle's stream with ONE host synchronisation at the end. */
 int rmx_variational_update(rmx_handle h, int n_iter);
+/* update_p_breakpoint (bpmodel.pyx:964-985) split around its one reduction, for a fit whose chromosomes are
+ * sharded over several models / GPUs: rmx_breakpoint_logq returns this model's partial
+ * log q (gn,K,B), the sums of bpmodel.pyx:971-980 over ITS breakend rows; the caller adds the shards' partials
+ * (an allreduce of K*B doubles) and hands the total to rmx_breakpoint_apply_logq on every shard, which does the
+ * exp-normalise (:982) and refreshes the cached transition expectation (:985). */
+int rmx_breakpoint_logq(rmx_handle h, double* logq);
+int rmx_breakpoint_apply_logq(rmx_handle h, const double* logq);
 
 /* ---- objective / M-step reductions ---------------------------------------------------- */
 int rmx_variational_energy(rmx_handle h, double* energy);    /* bpmodel.pyx:1060 */

@@ -209,7 +209,7 @@ class RemixtModel(object):
 
     def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination, cn_states, brk_states,
                  h_init, l, x, y, is_telomere, breakpoint_idx, breakpoint_orient, transition_penalty,
-                 divergence_weight):
+                 divergence_weight, shard=False):
         # bpmodel.pyx:478-491
         self.num_clones = int(num_clones)
         self.num_segments = int(num_segments)
@@ -246,7 +246,8 @@ class RemixtModel(object):
                           ('breakpoint_orient', breakpoint_orient)):
             if np.asarray(arr).shape[0] != N:
                 raise ValueError('%s must have length equal to num_segments' % name)
-        if np.asarray(breakpoint_idx).max() + 1 != K:
+        # shard=True: one chromosome group of a sharded fit (all K breakpoints, its own breakends); test-only
+        if (np.asarray(breakpoint_idx).max() + 1 > K) if shard else (np.asarray(breakpoint_idx).max() + 1 != K):
             raise ValueError('breakpoint_idx must have maximum of num_breakpoints positive indices')
         self.is_telomere = np.asarray(is_telomere)
         self.breakpoint_idx = np.asarray(breakpoint_idx)
@@ -455,6 +456,16 @@ class RemixtModel(object):
 
     def update_p_breakpoint(self):
         """``bpmodel.pyx:964-985`` with ``add_log_breakpoint_p_expectation_cn`` (``:619-637``)."""
+        self.apply_breakpoint_logq(self.breakpoint_logq())
+
+    def apply_breakpoint_logq(self, log_p):
+        """The tail of ``update_p_breakpoint`` (``bpmodel.pyx:982-985``)."""
+        if self.num_breakpoints > 0:
+            self.p_breakpoint = exp_normalize(np.asarray(log_p, dtype=float), axes=(-1,))
+        self.calculate_log_transmat(self.cached_log_transmat)
+
+    def breakpoint_logq(self):
+        """The accumulation of ``update_p_breakpoint`` (``bpmodel.pyx:966-980``) over this model's breakend rows."""
         log_p = np.zeros((self.num_breakpoints, self.num_brk_states))
         tot = self.cn_states_total
         d = np.arange(-self.cn_max - 1, self.cn_max + 2)
@@ -468,9 +479,7 @@ class RemixtModel(object):
                 for s_b in range(self.num_brk_states):
                     f = self.calc_transition(d - self.breakpoint_orient[n] * self.brk_states[s_b, m])
                     log_p[self.breakpoint_idx[n], s_b] += np.sum(-self.transition_penalty * p_d * f)
-        if self.num_breakpoints > 0:
-            self.p_breakpoint = exp_normalize(log_p, axes=(-1,))
-        self.calculate_log_transmat(self.cached_log_transmat)
+        return log_p
 
     def update_p_outlier_total(self):
         """``bpmodel.pyx:987-1003``."""

@@ -17,6 +17,7 @@ A_POSTERIOR_MARGINALS, A_FRAMELOGPROB, A_TOTAL_LIKELIHOOD_MASK, A_ALLELE_LIKELIH
 A_LOG_TRANSMAT, A_CACHED_LOG_TRANSMAT, A_JOINT_POSTERIOR_MARGINALS = 9, 10, 11
 A_L, A_X, A_Y, A_STATE_PATH = 12, 13, 14, 15
 A_LL_TABLE = 16
+DESC_SHARD = 1
 
 # rmx_scalar_id
 SCALAR_IDS = {
@@ -36,7 +37,7 @@ EXPORTS = [
     'rmx_create', 'rmx_batch_create', 'rmx_batch_view', 'rmx_num_fits', 'rmx_destroy', 'rmx_release_cached_memory', 'rmx_last_error',
     'rmx_device_count',
     'rmx_set_array', 'rmx_get_array', 'rmx_set_scalar', 'rmx_get_scalar', 'rmx_get_derived',
-    'rmx_update', 'rmx_variational_update',
+    'rmx_update', 'rmx_variational_update', 'rmx_breakpoint_logq', 'rmx_breakpoint_apply_logq',
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
     'rmx_expected_log_likelihood', 'rmx_expected_log_likelihood_partial_h',
     'rmx_expected_log_likelihood_grid',
@@ -51,7 +52,7 @@ class RmxDesc(C.Structure):
     _fields_ = [
         ('num_clones', C.c_int32), ('num_segments', C.c_int32), ('num_breakpoints', C.c_int32),
         ('normal_contamination', C.c_int32), ('num_cn_states', C.c_int32), ('num_brk_states', C.c_int32),
-        ('device', C.c_int32), ('reserved', C.c_int32),
+        ('device', C.c_int32), ('flags', C.c_int32),
         ('cn_states', C.c_void_p), ('cn_table', C.c_void_p), ('normal_copies', C.c_void_p),
         ('brk_states', C.c_void_p), ('h_init', C.c_void_p), ('l', C.c_void_p), ('x', C.c_void_p),
         ('y', C.c_void_p), ('is_telomere', C.c_void_p), ('breakpoint_idx', C.c_void_p),
@@ -73,6 +74,8 @@ def _load():
         'rmx_batch_view': [H, I, I, C.POINTER(H)],
         'rmx_num_fits': [H, C.POINTER(I)],
         'rmx_destroy': [H],
+        'rmx_breakpoint_logq': [H, P],
+        'rmx_breakpoint_apply_logq': [H, P],
         'rmx_release_cached_memory': [I],
         'rmx_device_count': [C.POINTER(I)],
         'rmx_set_array': [H, I, P, I64],

@@ -63,7 +63,7 @@ class _ModelBase(object):
 
     def _setup(self, num_clones, num_segments, num_breakpoints, normal_contamination,
                cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
-               breakpoint_orient, transition_penalty, divergence_weight, device, num_fits):
+               breakpoint_orient, transition_penalty, divergence_weight, device, num_fits, shard=False):
         cn_states = _typed(cn_states, np.int64, 4, 'cn_states')
         brk_states = _typed(brk_states, np.int64, 2, 'brk_states')
         h_init = _typed(h_init, np.float64, 1 if num_fits is None else 2, 'h_init')
@@ -99,7 +99,8 @@ class _ModelBase(object):
             raise ValueError('breakpoint_idx must have length equal to num_segments')
         if breakpoint_orient.shape[0] != num_segments:
             raise ValueError('breakpoint_orient must have length equal to num_segments')
-        if breakpoint_idx.max() + 1 != num_breakpoints:
+        # a shard of a chromosome-sharded fit (remixt_b200/sharded.py) sees the breakends of its own chromosomes only
+        if (breakpoint_idx.max() + 1 > num_breakpoints) if shard else (breakpoint_idx.max() + 1 != num_breakpoints):
             raise ValueError('breakpoint_idx must have maximum of num_breakpoints positive indices')
         if l.shape[0] != num_segments or x.shape[0] != num_segments or y.shape != (num_segments, 2):
             raise ValueError('l, x, y must have num_segments rows')
@@ -117,6 +118,7 @@ class _ModelBase(object):
         desc.num_cn_states = self.num_cn_states
         desc.num_brk_states = self.num_brk_states
         desc.device = self.device
+        desc.flags = _lib.DESC_SHARD if shard else 0
         desc.cn_states = _ptr(cn_states)
         desc.cn_table = None
         desc.normal_copies = None
@@ -326,6 +328,22 @@ class _ModelBase(object):
     def state_sequence(self):
         return self._get(_lib.A_STATE_PATH, (self.num_segments,), np.int64)
 
+    # update_p_breakpoint split around its reduction (chromosome-sharded fits, remixt_b200/sharded.py)
+    def breakpoint_logq(self):
+        """(K, B) partial ``log q`` of ``update_p_breakpoint`` (``bpmodel.pyx:971-980``) over this model's own
+        breakend rows, before the exp-normalise."""
+        out = np.zeros((self._gn, self.num_breakpoints, self.num_brk_states), dtype=np.float64)
+        check(lib.rmx_breakpoint_logq(self._handle, _ptr(out)), self._handle)
+        return self._out(out)
+
+    def apply_breakpoint_logq(self, logq):
+        """``p_breakpoint = exp_normalize(logq)`` and the cached transition expectation
+        (``bpmodel.pyx:982-985``); ``logq`` is the sum of the shards' :meth:`breakpoint_logq`."""
+        shape = (self._gn, self.num_breakpoints, self.num_brk_states)
+        a = np.ascontiguousarray(np.broadcast_to(np.asarray(logq, dtype=np.float64).reshape(
+            shape if np.size(logq) == np.prod(shape) else shape[1:]), shape))
+        check(lib.rmx_breakpoint_apply_logq(self._handle, _ptr(a)), self._handle)
+
     @property
     def log_likelihood_table(self):
         """(6, N1, S): ``calculate_log_likelihood_total(n, s, u)`` in planes u and
@@ -409,10 +427,10 @@ class RemixtModel(_ModelBase):
 
     def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination,
                  cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
-                 breakpoint_orient, transition_penalty, divergence_weight, device=None):
+                 breakpoint_orient, transition_penalty, divergence_weight, device=None, shard=False):
         self._setup(num_clones, num_segments, num_breakpoints, normal_contamination, cn_states, brk_states,
                     h_init, l, x, y, is_telomere, breakpoint_idx, breakpoint_orient, transition_penalty,
-                    divergence_weight, device, None)
+                    divergence_weight, device, None, shard=shard)
 
 
 class RemixtBatch(_ModelBase):
@@ -428,14 +446,14 @@ class RemixtBatch(_ModelBase):
 
     def __init__(self, num_clones, num_segments, num_breakpoints, normal_contamination,
                  cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
-                 breakpoint_orient, transition_penalty, divergence_weight, device=None):
+                 breakpoint_orient, transition_penalty, divergence_weight, device=None, shard=False):
         h_init = np.ascontiguousarray(h_init, dtype=np.float64)
         if h_init.ndim != 2:
             raise ValueError('h_init of a batch must be (num_fits, num_clones)')
         self._gn = h_init.shape[0]
         self._setup(num_clones, num_segments, num_breakpoints, normal_contamination, cn_states, brk_states,
                     h_init, l, x, y, is_telomere, breakpoint_idx, breakpoint_orient, transition_penalty,
-                    divergence_weight, device, self._gn)
+                    divergence_weight, device, self._gn, shard=shard)
         self._views = {}
 
     @property

@@ -121,6 +121,7 @@ struct Batch {
     double2* logw = nullptr;
     double* stab = nullptr;
     double* segf = nullptr;
+    double* logq = nullptr;      // (G,K,B) log q of update_p_breakpoint before normalisation (sharded fits)
     uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
     int* hgstart = nullptr;
     int Q = 0;
@@ -463,10 +464,12 @@ static int do_update_p_cn(Model* m) {
     return RMX_OK;
 }
 
-static int do_update_p_breakpoint(Model* m) {
+// mode 0: update_p_breakpoint; 1: partial log q of this model's breakend rows into b->logq; 2: p_breakpoint from
+// the log q in b->logq (sharded fits: modes 1 and 2 around the allreduce of the shards' partial sums)
+static int do_update_p_breakpoint(Model* m, int mode = 0) {
     Batch* b = m->b.get();
     const int g0 = m->g0, gn = m->gn;
-    if (b->d.K > 0 && b->R > 0) {
+    if (mode != 2 && b->d.K > 0 && b->R > 0) {
         // fits still in the constructor state take the histogram of the uniform joint (bpmodel.pyx:566-567)
         std::vector<char> need(b->G, 0);
         for (int g = g0; g < g0 + gn; ++g) need[g] = !b->hist_valid[g];
@@ -481,10 +484,11 @@ static int do_update_p_breakpoint(Model* m) {
     if (b->d.K > 0) {
         for_runs(g0, gn, b->tm, nullptr, [&](int g, int n) {
             { cudaEvent_t te_ = b->tbegin(RMX_K_BRK_UPDATE); rmx_launch_brk_update(b->stream, b->d, g, n, b->krow_ptr, b->krow_idx, b->brk_rows, b->borient, b->brk, b->hist,
-                                  b->rmd, b->pen, b->tm[g], b->p_brk); b->tend(te_); }
+                                  b->rmd, b->pen, b->tm[g], b->p_brk, mode, b->logq); b->tend(te_); }
             b->count();
         });
     }
+    if (mode == 1) return RMX_OK;
     return snapshot_spec(m, g0, gn, true);
 }
 
@@ -689,7 +693,8 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
         borient[n] = (int)desc->breakpoint_orient[n];
         if (desc->breakpoint_idx[n] > max_bidx) max_bidx = desc->breakpoint_idx[n];
     }
-    if (max_bidx + 1 != K)
+    // a shard of a chromosome-sharded fit holds the breakends of its own chromosomes only (RMX_DESC_SHARD)
+    if ((desc->flags & RMX_DESC_SHARD) ? (max_bidx + 1 > K) : (max_bidx + 1 != K))
         CREATE_FAIL(RMX_ERR_VALUE, "breakpoint_idx must have maximum of num_breakpoints positive indices");
     std::map<uint32_t, int> class_of;
     ch_start.push_back(0);
@@ -853,6 +858,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->q_ot, GN * 2));
     CCK(dalloc(b, &b->q_oa, GN * 2));
     CCK(dalloc(b, &b->p_brk, (size_t)G * K * B));
+    CCK(dalloc(b, &b->logq, (size_t)G * K * B));
     const size_t grmd = (size_t)G * b->rmd;
     CCK(dalloc(b, &b->pd_used, grmd));
     CCK(dalloc(b, &b->wexp_used, grmd));
@@ -1245,6 +1251,35 @@ int rmx_update(rmx_handle m, int id) {
     if (rc) return rc;
     if (id == RMX_U_CN) take_logz(m);
     return RMX_OK;
+}
+
+int rmx_breakpoint_logq(rmx_handle m, double* out) {
+    if (!m || !out) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const size_t kb = (size_t)b->d.K * b->d.B;
+    if (kb == 0) return RMX_OK;
+    CK(cudaMemsetAsync(b->logq + (size_t)m->g0 * kb, 0, sizeof(double) * kb * m->gn, b->stream));
+    int rc = do_update_p_breakpoint(m, 1);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out, b->logq + (size_t)m->g0 * kb, sizeof(double) * kb * m->gn, cudaMemcpyDeviceToHost, b->stream));
+    return sync_check(m);
+}
+
+int rmx_breakpoint_apply_logq(rmx_handle m, const double* logq) {
+    if (!m || !logq) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const size_t kb = (size_t)b->d.K * b->d.B;
+    if (kb > 0) {
+        CK(cudaMemcpyAsync(b->logq + (size_t)m->g0 * kb, logq, sizeof(double) * kb * m->gn, cudaMemcpyHostToDevice, b->stream));
+        CK(cudaStreamSynchronize(b->stream));   // the caller's buffer is free when this returns
+    }
+    int rc = do_update_p_breakpoint(m, 2);
+    if (rc) return rc;
+    return sync_check(m);
 }
 
 int rmx_variational_update(rmx_handle m, int n_iter) {

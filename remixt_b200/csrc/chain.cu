@@ -775,7 +775,11 @@ __global__ void __launch_bounds__(64) k_brk_update(RmxDims d, int g0, const int*
                                                    const int* __restrict__ krow_idx, const int* __restrict__ brk_rows,
                                                    const int* __restrict__ borient, const int8_t* __restrict__ brk,
                                                    const double* __restrict__ hist_all, int64_t hist_fit_stride,
-                                                   double pen, int tm, double* __restrict__ p_brk_all) {
+                                                   double pen, int tm, double* __restrict__ p_brk_all, int mode,
+                                                   double* __restrict__ logq_all) {
+    // mode 0: the whole update; mode 1: only this model's partial log q (its own breakend rows) to logq_all
+    // (G,K,B); mode 2: log q taken from logq_all (the sum over the shards of a chromosome-sharded fit) and
+    // normalised.  Modes 1 + 2 around an allreduce are mode 0 for a model that holds a subset of the chains.
     __shared__ double buf[64];
     __shared__ double stat;
     const int g = RMX_FIT();
@@ -784,7 +788,11 @@ __global__ void __launch_bounds__(64) k_brk_update(RmxDims d, int g0, const int*
     double* p = p_brk_all + ((int64_t)g * d.K + k) * d.B;
     const double mult = -pen;
     double acc = 0.;
-    if (b < d.B) {
+    double* lq = logq_all ? logq_all + ((int64_t)g * d.K + k) * d.B : nullptr;
+    if (b < d.B && mode == 2) {
+        acc = lq[b];
+        buf[b] = acc;
+    } else if (b < d.B) {
         for (int e = krow_ptr[k]; e < krow_ptr[k + 1]; ++e) {
             const int r = krow_idx[e];
             const int o = borient[brk_rows[r]];
@@ -796,7 +804,9 @@ __global__ void __launch_bounds__(64) k_brk_update(RmxDims d, int g0, const int*
             }
         }
         buf[b] = acc;
+        if (mode == 1) lq[b] = acc;
     }
+    if (mode == 1) return;
     __syncthreads();
     if (b == 0) {
         double mx = -INFINITY;
@@ -1309,10 +1319,10 @@ void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int 
 
 void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, int g0, int gn, const int* krow_ptr, const int* krow_idx,
                            const int* brk_rows, const int* borient, const int8_t* brk, const double* hist,
-                           int64_t hist_fit_stride, double pen, int tm, double* p_brk) {
+                           int64_t hist_fit_stride, double pen, int tm, double* p_brk, int mode, double* logq) {
     if (d.K <= 0 || gn <= 0) return;
     k_brk_update<<<dim3(d.K, gn), 64, 0, st>>>(d, g0, krow_ptr, krow_idx, brk_rows, borient, brk, hist, hist_fit_stride,
-                                               pen, tm, p_brk);
+                                               pen, tm, p_brk, mode, logq);
 }
 
 void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxRows& rows,

@@ -97,7 +97,8 @@ int rmx_hist2_gstart_count(const RmxDims& d);
 void rmx_launch_hist_prep(cudaStream_t st, const RmxTables& T, const RmxDims& d, uint8_t* hord, int* hgstart);
 void rmx_launch_brk_update(cudaStream_t st, const RmxDims& d, int g0, int gn, const int* krow_ptr, const int* krow_idx,
                            const int* brk_rows, const int* borient, const int8_t* brk, const double* hist,
-                           int64_t hist_fit_stride, double pen, int tm, double* p_brk);
+                           int64_t hist_fit_stride, double pen, int tm, double* p_brk, int mode = 0,
+                           double* logq = nullptr);
 // rowsum[g][r] = sum_ij joint[n,i,j] * (T_tsp - (diff ? T_t2sp : 0))[n,i,j]; rowlist == nullptr: n = r over N-1 rows
 void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxRows& rows,
                         const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, const RmxTransSpec& t2_sp, int diff,
