@@ -231,6 +231,7 @@ def kernel_models(N1, S, NC, G, R):
         'post': ('hbm', 24. * ns, 3. * ns),
         'hist': ('fp64', 0., 2. * 8. * S * S * R * G),
         'elbo_rows': ('hbm', 16. * ns, 4. * ns),
+        'round': ('hbm', 88. * ns, 29. * ns),
     }
 
 

@@ -218,7 +218,7 @@ int rmx_global_launch_count(int64_t* count);
 /* Kernel classes of rmx_kernel_timing. */
 typedef enum {
     RMX_K_CHAIN = 0, RMX_K_LLTABLE = 1, RMX_K_FRAME = 2, RMX_K_QSUMS = 3, RMX_K_POST = 4, RMX_K_HIST = 5,
-    RMX_K_BRK_UPDATE = 6, RMX_K_ELBO_ROWS = 7, RMX_K_PAIRSUM = 8, RMX_K_ELL = 9, RMX_K_COUNT_ = 10
+    RMX_K_BRK_UPDATE = 6, RMX_K_ELBO_ROWS = 7, RMX_K_PAIRSUM = 8, RMX_K_ELL = 9, RMX_K_ROUND = 10, RMX_K_COUNT_ = 11
 } rmx_kernel_class;
 /* Device-side duration (CUDA events on the batch's stream around every launch) of each kernel class since
  * the last call: total milliseconds and number of launches, arrays of RMX_K_COUNT_; then switches the

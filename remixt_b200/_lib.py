@@ -27,7 +27,7 @@ SCALAR_IDS = {
     'divergence_weight': 13, 'transition_model': 14, 'hmm_log_norm_const': 15,
 }
 
-KERNEL_CLASSES = ['chain', 'lltable', 'frame', 'qsums', 'post', 'hist', 'brk_update', 'elbo_rows', 'pairsum', 'ell']
+KERNEL_CLASSES = ['chain', 'lltable', 'frame', 'qsums', 'post', 'hist', 'brk_update', 'elbo_rows', 'pairsum', 'ell', 'round']
 
 # rmx_update_id
 U_ALLELE_SWAP, U_CN, U_BREAKPOINT, U_OUTLIER_TOTAL, U_OUTLIER_ALLELE, U_FRAMELOGPROB = range(6)

@@ -420,10 +420,12 @@ static int do_update_framelogprob(Model* m) {
     return RMX_OK;
 }
 
-static int do_update_p_cn(Model* m) {
+// have_frame: F / fexp / mF of this update were already produced (by k_round at the end of the previous round);
+// defer_post: the posterior marginals are left to the k_round that follows (rmx_variational_update's fused loop)
+static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = false) {
     Batch* b = m->b.get();
     const int g0 = m->g0, gn = m->gn;
-    int rc = do_update_framelogprob(m);
+    int rc = have_frame ? ensure_ll(m, g0, gn) : do_update_framelogprob(m);
     if (rc) return rc;
     rc = snapshot_spec(m, g0, gn, false);
     if (rc) return rc;
@@ -445,8 +447,13 @@ static int do_update_p_cn(Model* m) {
     if (lc == 2) return m->fail(RMX_ERR_UNSUPPORTED, "this number of copy number states is not supported by the chain kernel");
     if (lc) return m->fail(RMX_ERR_CUDA, "could not configure or launch the chain kernel");
     rmx_launch_reduce_cols(b->stream, b->chain_logz, b->NC, 1, g0, gn, b->NC, b->red_out + 15, Batch::RED);
-    { cudaEvent_t te_ = b->tbegin(RMX_K_POST); rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags); b->tend(te_); }
-    b->count(2);
+    if (!defer_post) {
+        cudaEvent_t te_ = b->tbegin(RMX_K_POST);
+        rmx_launch_post(b->stream, b->d, g0, gn, b->ahat, b->bhat, b->post, b->dflags);
+        b->tend(te_);
+        b->count();
+    }
+    b->count();
     for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
         { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
@@ -1289,11 +1296,35 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
     cudaSetDevice(b->device);
     static const int order[5] = {RMX_U_ALLELE_SWAP, RMX_U_CN, RMX_U_BREAKPOINT, RMX_U_OUTLIER_TOTAL,
                                  RMX_U_OUTLIER_ALLELE};
-    for (int it = 0; it < n_iter; ++it)
-        for (int k = 0; k < 5; ++k) {
-            int rc = do_update(m, order[k]);
+    static const bool no_fuse = getenv("RMX_NO_FUSED_ROUND") != nullptr;     // A/B measurements only
+    bool fuse = !no_fuse && rmx_round_ok(b->d);
+    if (fuse) {
+        // swap -> cn -> breakpoint -> outlier_total -> outlier_allele per round (cn_model.py:444-460); the posterior
+        // marginals, both outlier updates and the next round's swap update and frame log-probability are one
+        // kernel (k_round)
+        for (int it = 0; it < n_iter; ++it) {
+            int rc = RMX_OK;
+            if (it == 0) rc = do_update_q(m, 0);
             if (rc) return rc;
+            rc = do_update_p_cn(m, it > 0, true);
+            if (rc) return rc;
+            rc = do_update_p_breakpoint(m);
+            if (rc) return rc;
+            cudaEvent_t te_ = b->tbegin(RMX_K_ROUND);
+            rmx_launch_round(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->ahat, b->bhat, b->post, b->Asum,
+                             b->q_ot, b->q_oa, b->q_sw, b->prior_ot, b->prior_oa, it + 1 < n_iter ? 1 : 0, b->F, b->fexp,
+                             b->mF, b->dflags);
+            b->tend(te_);
+            b->count();
+            for (int g = m->g0; g < m->g0 + m->gn; ++g) b->asum_valid[g] = 1;
         }
+    } else {
+        for (int it = 0; it < n_iter; ++it)
+            for (int k = 0; k < 5; ++k) {
+                int rc = do_update(m, order[k]);
+                if (rc) return rc;
+            }
+    }
     int rc = sync_check(m);
     if (rc) return rc;
     if (n_iter > 0) take_logz(m);

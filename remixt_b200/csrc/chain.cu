@@ -486,11 +486,11 @@ __global__ void __launch_bounds__(256) k_post(RmxDims d, int g0, const double* _
     if (warp >= d.N) return;
     int64_t base = ((int64_t)RMX_FIT() * d.N + warp) * d.S;
     double z = 0.;
-    for (int s = lane; s < d.S; s += 32) z += ahat[base + s] * bhat[base + s];
+    for (int s = lane; s < d.S; s += 32) z = __dadd_rn(z, __dmul_rn(ahat[base + s], bhat[base + s]));
     z = warp_sum(z);
     bool bad = !(z > 0.);
     for (int s = lane; s < d.S; s += 32) {
-        double p = ahat[base + s] * bhat[base + s] / z;
+        double p = __ddiv_rn(__dmul_rn(ahat[base + s], bhat[base + s]), z);
         post[base + s] = p;
         bad |= isnan(p);
     }

@@ -337,6 +337,47 @@ __device__ __forceinline__ double rmx_wlog(double z, const double2* __restrict__
     return log(z);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Arithmetic shared by the separate update kernels and the fused round kernel (likelihood.cu: k_round), written
+// with explicit roundings so that both paths give the same bits whatever the compiler would contract.
+// ---------------------------------------------------------------------------------------------
+// framelogprob term of one (segment, state) (bpmodel.pyx:898-919); l = the six likelihood terms
+__device__ __forceinline__ double rmx_frame_value(double ot0, double ot1, double oa0, double oa1, double sw0, double sw1,
+                                                  double l0, double l1, double l2, double l3, double l4, double l5,
+                                                  double nsub, double ln, double dw) {
+    double f = __dmul_rn(ot0, l0);
+    f = fma(ot1, l1, f);
+    f = fma(__dmul_rn(oa0, sw0), l2, f);
+    f = fma(__dmul_rn(oa0, sw1), l3, f);
+    f = fma(__dmul_rn(oa1, sw0), l4, f);
+    f = fma(__dmul_rn(oa1, sw1), l5, f);
+    return __dadd_rn(f, __dmul_rn(__dmul_rn(-nsub, ln), dw));      // bpmodel.pyx:746-749
+}
+// exp-normalise of a 2-vector as bpmodel.pyx:120-128 does it
+__device__ __forceinline__ void rmx_exp_normalize2(double a, double b, double* out) {
+    const double m = fmax(a, b);
+    const double lse = __dadd_rn(log(__dadd_rn(exp(__dadd_rn(a, -m)), exp(__dadd_rn(b, -m)))), m);
+    const double ea = exp(__dadd_rn(a, -lse)), eb = exp(__dadd_rn(b, -lse));
+    const double z = __dadd_rn(ea, eb);
+    out[0] = __ddiv_rn(ea, z);
+    out[1] = __ddiv_rn(eb, z);
+}
+// arguments of the three 2-way factor updates from the sums A[0..6) (bpmodel.pyx:987-1042)
+// lp0 = log(1 - prior), lp1 = log(prior), evaluated once on the host
+__device__ __forceinline__ void rmx_q_args(int which, const double* A, double q0, double q1, double lp0, double lp1,
+                                           double* a) {
+    if (which == 1) {            // outlier total
+        a[0] = __dadd_rn(A[0], lp0);
+        a[1] = __dadd_rn(A[1], lp1);
+    } else if (which == 0) {     // allele swap; q = p_outlier_allele
+        a[0] = fma(q1, A[4], __dmul_rn(q0, A[2]));
+        a[1] = fma(q1, A[5], __dmul_rn(q0, A[3]));
+    } else {                     // outlier allele; q = p_allele_swap
+        a[0] = __dadd_rn(fma(q1, A[3], __dmul_rn(q0, A[2])), lp0);
+        a[1] = __dadd_rn(fma(q1, A[5], __dmul_rn(q0, A[4])), lp1);
+    }
+}
+
 // AS 103 digamma (J. Bernardo 1976), the algorithm bpmodel.pyx:162-235 uses.
 __device__ __forceinline__ double digamma_as103(double x, int* flags) {
     if (x <= 0.0) {

@@ -391,14 +391,8 @@ __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, const Rmx
     bool bad = false;
     for (int s = lane; s < d.S; s += 32) {
         int64_t i = (int64_t)n * d.S + s;
-        double f = 0.;
-        f += ot0 * LL[i];
-        f += ot1 * LL[NS + i];
-        f += oa0 * sw0 * LL[2 * NS + i];
-        f += oa0 * sw1 * LL[3 * NS + i];
-        f += oa1 * sw0 * LL[4 * NS + i];
-        f += oa1 * sw1 * LL[5 * NS + i];
-        f += -1.0 * (double)T.nsub[s] * ln * dw;   // bpmodel.pyx:746-749
+        const double f = rmx_frame_value(ot0, ot1, oa0, oa1, sw0, sw1, LL[i], LL[NS + i], LL[2 * NS + i], LL[3 * NS + i],
+                                         LL[4 * NS + i], LL[5 * NS + i], (double)T.nsub[s], ln, dw);
         F[i] = f;
         bad |= isnan(f);
         mx = fmax(mx, f);
@@ -413,14 +407,7 @@ __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, const Rmx
 }
 
 // exp-normalise of a 2-vector as bpmodel.pyx:120-128 does it.
-__device__ __forceinline__ void exp_normalize2(double a, double b, double* out) {
-    double m = fmax(a, b);
-    double lse = log(exp(a - m) + exp(b - m)) + m;
-    double ea = exp(a - lse), eb = exp(b - lse);
-    double z = ea + eb;
-    out[0] = ea / z;
-    out[1] = eb / z;
-}
+__device__ __forceinline__ void exp_normalize2(double a, double b, double* out) { rmx_exp_normalize2(a, b, out); }
 
 // Posterior-weighted likelihood sums A[g][n][t] = sum_s post[g,n,s] * LL[g,t,n,s], t in [0,6): the
 // sufficient statistic of all three 2-way factor updates and of the ELBO's likelihood terms.
@@ -453,31 +440,138 @@ __global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* 
     }
 }
 
+// The tail of one coordinate-ascent round and the head of the next in ONE pass over the likelihood table, inside
+// rmx_variational_update's loop (cn_model.py:444-460 order): after the chain messages of update_p_cn,
+//   post = normalise(ahat .* bhat)                       (k_post; bpmodel.pyx:946-952)
+//   A[t] = sum_s post * LL[t]                            (k_qsums)
+//   update_p_outlier_total, update_p_outlier_allele      (k_qupdate 1, 2; :987-1023)
+// and, when another round follows,
+//   update_p_allele_swap of that round                   (k_qupdate 0; :1025-1042)
+//   framelogprob of that round, its row max and exp      (k_frame; :898-919)
+// One warp per (fit, segment), the segment's post and six LL rows in registers: 88 bytes per (n,s) instead of the
+// 144 of the four separate passes.  Expressions and summation orders are the separate kernels' (results agree with
+// the unfused sequence to the last bits; FMA contraction may differ).  KS = ceil(S / 32).
+template <int KS>
+__global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                               const double* __restrict__ LL_all, const double* __restrict__ ahat_all,
+                                               const double* __restrict__ bhat_all, double* __restrict__ post_all,
+                                               double* __restrict__ A_all, double* __restrict__ q_ot_all,
+                                               double* __restrict__ q_oa_all, double* __restrict__ q_sw_all,
+                                               double lpt0, double lpt1, double lpa0, double lpa1, int next,
+                                               double* __restrict__ F_all,
+                                               double* __restrict__ fexp_all, double* __restrict__ mF_all,
+                                               int* __restrict__ dflags) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    const int g = RMX_FIT();
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const int64_t row = (int64_t)n * d.S;
+    const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS + row;
+    const double* ah = ahat_all + (int64_t)g * NS + row;
+    const double* bh = bhat_all + (int64_t)g * NS + row;
+    double ll[RMX_NTERM][KS], p[KS];
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+        const int s = lane + 32 * k;
+#pragma unroll
+        for (int t = 0; t < RMX_NTERM; ++t) ll[t][k] = s < d.S ? LL[(int64_t)t * NS + s] : 0.;
+        p[k] = s < d.S ? __dmul_rn(ah[s], bh[s]) : 0.;
+    }
+    // ---- posterior marginals
+    double z = 0.;
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) z = __dadd_rn(z, p[k]);
+    z = warp_sum(z);
+    bool bad = !(z > 0.);
+    double* post = post_all + (int64_t)g * NS + row;
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) {
+            p[k] = __ddiv_rn(p[k], z);
+            post[lane + 32 * k] = p[k];
+            bad |= isnan(p[k]);
+        }
+    if (bad) atomicOr(dflags, RMX_F_POST_NAN);
+    // ---- posterior-weighted likelihood sums
+    double a[RMX_NTERM];
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t) a[t] = 0.;
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) {
+#pragma unroll
+            for (int t = 0; t < RMX_NTERM; ++t) a[t] = fma(p[k], ll[t][k], a[t]);
+        }
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t) a[t] = warp_sum(a[t]);
+    const int64_t gn = (int64_t)g * d.N + n;
+    if (lane < RMX_NTERM) {
+        double v = a[0];
+#pragma unroll
+        for (int t = 1; t < RMX_NTERM; ++t) v = lane == t ? a[t] : v;
+        A_all[gn * RMX_NTERM + lane] = v;
+    }
+    // ---- outlier factors (every lane holds the same sums; lane 0 stores)
+    double ot[2], oa[2], sw[2], qa[2];
+    rmx_q_args(1, a, 0., 0., lpt0, lpt1, qa);
+    exp_normalize2(qa[0], qa[1], ot);
+    sw[0] = q_sw_all[gn * 2];
+    sw[1] = q_sw_all[gn * 2 + 1];
+    rmx_q_args(2, a, sw[0], sw[1], lpa0, lpa1, qa);
+    exp_normalize2(qa[0], qa[1], oa);
+    if (lane == 0) {
+        q_ot_all[gn * 2] = ot[0]; q_ot_all[gn * 2 + 1] = ot[1];
+        q_oa_all[gn * 2] = oa[0]; q_oa_all[gn * 2 + 1] = oa[1];
+    }
+    if (!next) return;
+    // ---- next round: allele swap factor, frame log-probability
+    rmx_q_args(0, a, oa[0], oa[1], 0., 0., qa);
+    exp_normalize2(qa[0], qa[1], sw);
+    if (lane == 0) { q_sw_all[gn * 2] = sw[0]; q_sw_all[gn * 2 + 1] = sw[1]; }
+    const double ln = T.l[n], dw = Pg[g].divergence_weight;
+    double* F = F_all + (int64_t)g * NS + row;
+    double* fexp = fexp_all + (int64_t)g * NS + row;
+    double mx = -INFINITY;
+    bad = false;
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+        const int s = lane + 32 * k;
+        if (s < d.S) {
+            const double f = rmx_frame_value(ot[0], ot[1], oa[0], oa[1], sw[0], sw[1], ll[0][k], ll[1][k], ll[2][k],
+                                             ll[3][k], ll[4][k], ll[5][k], (double)T.nsub[s], ln, dw);
+            F[s] = f;
+            p[k] = f;
+            bad |= isnan(f);
+            mx = fmax(mx, f);
+        }
+    }
+    mx = warp_max(mx);
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) fexp[lane + 32 * k] = exp(p[k] - mx);
+    if (lane == 0) mF_all[gn] = mx;
+    if (bad) atomicOr(dflags, RMX_F_FRAME_NAN);
+}
+
 // The three 2-way factor updates from the sums A, one thread per (fit, segment).
 //   which = 0: update_p_allele_swap   (bpmodel.pyx:1025-1042)
 //   which = 1: update_p_outlier_total (bpmodel.pyx:987-1003)
 //   which = 2: update_p_outlier_allele(bpmodel.pyx:1005-1023)
 __global__ void __launch_bounds__(256) k_qupdate(RmxDims d, int g0, int which, const double* __restrict__ A_all,
                                                  const double* __restrict__ q_oa_all, const double* __restrict__ q_sw_all,
-                                                 double prior, double* __restrict__ out_all) {
+                                                 double lp0, double lp1, double* __restrict__ out_all) {
     int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= d.N) return;
     const int g = RMX_FIT();
     const int64_t gn = (int64_t)g * d.N + n;
     const double* A = A_all + gn * RMX_NTERM;
-    double a0, a1;
-    if (which == 1) {
-        a0 = A[0] + log(1. - prior);
-        a1 = A[1] + log(prior);
-    } else if (which == 0) {
-        double oa0 = q_oa_all[gn * 2], oa1 = q_oa_all[gn * 2 + 1];
-        a0 = oa0 * A[2] + oa1 * A[4];
-        a1 = oa0 * A[3] + oa1 * A[5];
-    } else {
-        double sw0 = q_sw_all[gn * 2], sw1 = q_sw_all[gn * 2 + 1];
-        a0 = sw0 * A[2] + sw1 * A[3] + log(1. - prior);
-        a1 = sw0 * A[4] + sw1 * A[5] + log(prior);
-    }
+    double a[2];
+    if (which == 0) rmx_q_args(0, A, q_oa_all[gn * 2], q_oa_all[gn * 2 + 1], lp0, lp1, a);
+    else if (which == 1) rmx_q_args(1, A, 0., 0., lp0, lp1, a);
+    else rmx_q_args(2, A, q_sw_all[gn * 2], q_sw_all[gn * 2 + 1], lp0, lp1, a);
+    const double a0 = a[0], a1 = a[1];
     exp_normalize2(a0, a1, out_all + gn * 2);
 }
 
@@ -956,10 +1050,28 @@ void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const d
     k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A);
 }
 
+int rmx_round_ok(const RmxDims& d) { return d.S <= 128; }
+
+void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                      const double* LL, const double* ahat, const double* bhat, double* post, double* A, double* q_ot,
+                      double* q_oa, double* q_sw, double prior_ot, double prior_oa, int next, double* F, double* fexp,
+                      double* mF, int* dflags) {
+    if (d.N <= 0 || gn <= 0) return;
+    const dim3 grid(cdiv((int64_t)d.N * 32, 256), gn);
+    const int ks = (d.S + 31) / 32;
+#define RMX_ROUND(KS) k_round<KS><<<grid, 256, 0, st>>>(T, d, P, g0, LL, ahat, bhat, post, A, q_ot, q_oa, q_sw, \
+                                                       log(1. - prior_ot), log(prior_ot), log(1. - prior_oa), log(prior_oa), next, F, fexp, mF, dflags)
+    if (ks <= 1) RMX_ROUND(1);
+    else if (ks == 2) RMX_ROUND(2);
+    else if (ks == 3) RMX_ROUND(3);
+    else RMX_ROUND(4);
+#undef RMX_ROUND
+}
+
 void rmx_launch_qupdate(cudaStream_t st, const RmxDims& d, int g0, int gn, int which, const double* A,
                         const double* q_oa, const double* q_sw, double prior, double* out) {
     if (d.N <= 0 || gn <= 0) return;
-    k_qupdate<<<dim3(cdiv(d.N, 256), gn), 256, 0, st>>>(d, g0, which, A, q_oa, q_sw, prior, out);
+    k_qupdate<<<dim3(cdiv(d.N, 256), gn), 256, 0, st>>>(d, g0, which, A, q_oa, q_sw, log(1. - prior), log(prior), out);
 }
 
 void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, int g0, int gn,
