@@ -203,7 +203,7 @@ def build_batch(exp, inits, device):
     drivers = [pipeline.build_model(exp, ip, CONFIG) for ip in inits]
     h = np.array([pipeline.init_h(ip) for ip in inits])
     dw = np.array([ip['divergence_weight'] for ip in inits], dtype=float)
-    args = drivers[0].model_args(h) + (dw,)
+    args = drivers[0].model_args(h, compact=True) + (dw,)
     batch = bpmodel.RemixtBatch(*args, device=device)
     same_masks = all(np.array_equal(d._total_likelihood_mask, drivers[0]._total_likelihood_mask) and
                      np.array_equal(d._allele_likelihood_mask, drivers[0]._allele_likelihood_mask) for d in drivers)
@@ -217,6 +217,7 @@ def build_batch(exp, inits, device):
         for g, d in enumerate(drivers):
             d.attach(batch.fit(g))
     h2d = sum(int(np.asarray(a).nbytes) for a in args if isinstance(a, np.ndarray)) + 2 * 8 * batch.num_segments * len(inits)
+    h2d += sum(int(a.table.nbytes + a.normal_copies.nbytes) for a in args if isinstance(a, bpmodel.CompactCnStates))
     return batch, drivers, h2d
 
 

@@ -36,6 +36,40 @@ def set_default_device(device):
     default_device = int(device)
 
 
+class CompactCnStates(object):
+    """``cn_states`` ``(N1, S, M, 2)`` held as the two factors the reference builds it from (``cn_model.py:360-364``):
+    the state table ``(S, M, 2)`` shared by every segment and the per-segment normal copies ``(N1, 2)`` that replace
+    clone 0.  Converts to the full int64 array on demand (``np.asarray``); the CUDA models take the factors as they
+    are (``rmx_desc.cn_table`` / ``normal_copies``), which spares building, scanning and copying 140 MB per
+    whole-genome fit."""
+    ndim = 4
+    dtype = np.dtype(np.int64)
+
+    def __init__(self, table, normal_copies):
+        self.table = np.ascontiguousarray(table, dtype=np.int64)
+        self.normal_copies = np.ascontiguousarray(normal_copies, dtype=np.int64)
+        if self.table.ndim != 3 or self.normal_copies.ndim != 2 or self.normal_copies.shape[1] != self.table.shape[2]:
+            raise ValueError('table must be (S, M, num_alleles) and normal_copies (N1, num_alleles)')
+        self.shape = (self.normal_copies.shape[0],) + self.table.shape
+
+    def __array__(self, dtype=None, copy=None):
+        a = np.empty(self.shape, dtype=np.int64)
+        a[:] = self.table[np.newaxis]
+        a[:, :, 0, :] = self.normal_copies[:, np.newaxis, :]
+        return a if dtype is None else a.astype(dtype)
+
+    def max(self):
+        return max(int(self.table[:, 1:, :].max()) if self.table.shape[1] > 1 else 0, int(self.normal_copies.max()))
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __getitem__(self, idx):
+        if isinstance(idx, slice):
+            return CompactCnStates(self.table, self.normal_copies[idx])
+        return np.asarray(self)[idx]
+
+
 def _typed(a, dtype, ndim, name):
     # Cython's typed buffer arguments reject other dtypes / ranks (bpmodel.pyx:466-474)
     if not isinstance(a, np.ndarray):
@@ -52,6 +86,8 @@ def _ptr(a):
 
 
 class _ModelBase(object):
+    accepts_compact_cn_states = True
+
     """Shared plumbing of :class:`RemixtModel` (one fit) and :class:`RemixtBatch` (G fits in one set of
     launches).  ``_gn`` is the number of fits the handle covers; with ``_single`` the leading fit
     dimension is dropped so the object looks exactly like the reference's ``RemixtModel``."""
@@ -64,7 +100,9 @@ class _ModelBase(object):
     def _setup(self, num_clones, num_segments, num_breakpoints, normal_contamination,
                cn_states, brk_states, h_init, l, x, y, is_telomere, breakpoint_idx,
                breakpoint_orient, transition_penalty, divergence_weight, device, num_fits, shard=False):
-        cn_states = _typed(cn_states, np.int64, 4, 'cn_states')
+        compact = isinstance(cn_states, CompactCnStates)
+        if not compact:
+            cn_states = _typed(cn_states, np.int64, 4, 'cn_states')
         brk_states = _typed(brk_states, np.int64, 2, 'brk_states')
         h_init = _typed(h_init, np.float64, 1 if num_fits is None else 2, 'h_init')
         l = _typed(l, np.float64, 1, 'l')
@@ -119,9 +157,14 @@ class _ModelBase(object):
         desc.num_brk_states = self.num_brk_states
         desc.device = self.device
         desc.flags = _lib.DESC_SHARD if shard else 0
-        desc.cn_states = _ptr(cn_states)
-        desc.cn_table = None
-        desc.normal_copies = None
+        if compact:
+            desc.cn_states = None
+            desc.cn_table = _ptr(cn_states.table)
+            desc.normal_copies = _ptr(cn_states.normal_copies)
+        else:
+            desc.cn_states = _ptr(cn_states)
+            desc.cn_table = None
+            desc.normal_copies = None
         desc.brk_states = _ptr(brk_states)
         desc.h_init = _ptr(h_init)
         desc.l = _ptr(l)

@@ -275,7 +275,7 @@ class BreakpointModel(object):
             print('nothing for ' + name)
         return None
 
-    def model_args(self, h_init):
+    def model_args(self, h_init, compact=False):
         """Positional arguments of the ``RemixtModel`` constructor for this segmentation
         (``cn_model.py:359-384``); ``h_init`` is ``(M,)``, or ``(G, M)`` for a ``RemixtBatch``."""
         M = np.asarray(h_init).shape[-1]
@@ -283,9 +283,14 @@ class BreakpointModel(object):
         brk_states = create_brk_states(M, self.max_copy_number, self.max_copy_number_diff)
         # (N1, S, M, 2): the shared state table with clone 0 replaced by the segment's germline
         # copies, rows taken through the remap (index -1 wraps to the last segment, cn_model.py:364)
-        cn_states = np.empty((self.N1,) + table.shape, dtype=table.dtype)
-        cn_states[:] = table[np.newaxis]
-        cn_states[:, :, 0, :] = np.asarray(self.normal_copies)[self.seg_rev_remap][:, np.newaxis, :]
+        normal = np.asarray(self.normal_copies)[self.seg_rev_remap]
+        if compact:     # the same array as its two factors, for model classes that take them (bpmodel.CompactCnStates)
+            from remixt_b200.bpmodel import CompactCnStates
+            cn_states = CompactCnStates(table, normal)
+        else:
+            cn_states = np.empty((self.N1,) + table.shape, dtype=table.dtype)
+            cn_states[:] = table[np.newaxis]
+            cn_states[:, :, 0, :] = normal[:, np.newaxis, :]
         return (M, self.N1, self.num_breakpoints, self.normal_contamination,
                 cn_states, brk_states, h_init,
                 self.l1, self.x1[:, 2], self.x1[:, 0:2],
@@ -293,7 +298,9 @@ class BreakpointModel(object):
                 self.transition_log_prob)
 
     def _make_model(self, h_init):
-        return self.model_class(*(self.model_args(h_init) + (self.divergence_weight,)), **self.model_kwargs)
+        compact = bool(getattr(self.model_class, 'accepts_compact_cn_states', False))
+        return self.model_class(*(self.model_args(h_init, compact=compact) + (self.divergence_weight,)),
+                                **self.model_kwargs)
 
     def attach(self, model):
         """Adopt ``model`` (a fresh ``RemixtModel``, or a view of one fit of a ``RemixtBatch``) and apply the

@@ -1583,7 +1583,7 @@ int rmx_infer_cn(rmx_handle m, int64_t* cn) {
             rc = ensure_mats(m, b->tm_used[g]);
             if (rc) return;
             rmx_launch_viterbi(b->stream, tables(b), d, g, n, chainsof(b), rowsof(b), spec_of(b, false, b->tm_used[g]),
-                               b->rmd, b->F, b->lattice, b->path);
+                               b->rmd, b->F, b->lattice, b->path, b->C);
             b->count();
         });
         if (rc) return rc;

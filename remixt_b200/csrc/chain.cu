@@ -917,93 +917,177 @@ __global__ void __launch_bounds__(256) k_pairsum(RmxDims d, int g0, RmxRows rows
 // Telomere rows are all-zero so the lattice of a chain only differs from the reference's by an
 // additive constant; the traceback at a telomere is argmax of the lattice row itself.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, RmxChains ch, RmxRows rows, RmxTransSpec sp,
+__device__ __forceinline__ void logT_from(LogTCtx& c, const RmxDims& d, const RmxTransSpec& sp, const int8_t* tots,
+                                          int cls, int br, int d0) {
+    // logT_setup with the row's class / breakend row / normal-copy difference already loaded
+    c.kind = 0;
+    c.tots = tots;
+    c.d0 = d0;
+    c.pen = sp.pen;
+    c.Tm = c.fc = c.pdr = nullptr;
+    if (cls >= 0) {
+        if (br >= 0) {
+            c.kind = 2;
+            c.fc = sp.flipc + (int64_t)cls * d.S * d.S;
+            c.pdr = sp.pd + (int64_t)br * d.M * d.D;
+        } else {
+            c.kind = 1;
+            c.Tm = sp.Tmat + (int64_t)cls * d.S * d.S;
+        }
+    }
+}
+
+// One CTA decodes chain blockIdx.x of `fpc` fits: the fits share the class transition matrices staged in shared
+// memory (classes 0 .. staged-1), each fit has its own group of blockDim.x / fpc threads (thread per state) and its
+// own named barrier, so the groups advance independently.  Row descriptors and the next frame row are loaded one
+// segment ahead; the traceback is done by the first warp of each group without block barriers.
+__global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, RmxChains ch, RmxRows rows, RmxTransSpec sp,
                                                   int64_t sp_fit_stride, const int8_t* __restrict__ tab,
                                                   const double* __restrict__ F_all, double* __restrict__ lattice_all,
-                                                  int* __restrict__ path_all) {
-    const int g = RMX_FIT();
-    const double* F = F_all + (int64_t)g * d.N * d.S;
-    double* lattice = lattice_all + (int64_t)blockIdx.y * d.N * d.S;    // scratch holds the launched fits only
-    int* path = path_all + (int64_t)g * d.N;
-    sp.pd += (int64_t)g * sp_fit_stride;
-    sp.wexp += (int64_t)g * sp_fit_stride;
+                                                  int* __restrict__ path_all, int staged, int fpc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ double rv[32];
-    __shared__ int ri[32];
-    __shared__ int s_next;
     const int S = d.S, M = d.M;
-    double* prev = reinterpret_cast<double*>(smem_raw);   // [S]
-    int8_t* tots = reinterpret_cast<int8_t*>(prev + S);   // [S*M]
-    const int chain = blockIdx.x;
-    const int s0 = ch.start[chain], s1 = ch.end[chain];
-    const int t = threadIdx.x;
-    for (int e = t; e < S * M; e += blockDim.x) {
+    const int tpf = blockDim.x / fpc;                     // threads per fit, a multiple of 32
+    const int grp = threadIdx.x / tpf, t = threadIdx.x - grp * tpf;
+    double* prev_all = reinterpret_cast<double*>(smem_raw);                      // [fpc][S]
+    double* Tsm = prev_all + (size_t)fpc * S;                                   // [staged][S*S]
+    int8_t* tots = reinterpret_cast<int8_t*>(Tsm + (size_t)staged * S * S);     // [S*M]
+    for (int e = threadIdx.x; e < S * M; e += blockDim.x) {
         int s = e / M, m = e - s * M;
         tots[e] = (m == 0) ? 0 : (int8_t)(tab[(s * M + m) * 2] + tab[(s * M + m) * 2 + 1]);
     }
-    for (int jj = t; jj < S; jj += blockDim.x) {
+    for (int e = threadIdx.x; e < staged * S * S; e += blockDim.x) Tsm[e] = sp.Tmat[e];
+    __syncthreads();
+    const int lf = (int)blockIdx.y * fpc + grp;           // fit within the launched range
+    if (lf >= gn) return;
+    const int g = g0 + lf;
+    const double* F = F_all + (int64_t)g * d.N * d.S;
+    double* lattice = lattice_all + (int64_t)lf * d.N * d.S;    // scratch holds the launched fits only
+    int* path = path_all + (int64_t)g * d.N;
+    sp.pd += (int64_t)g * sp_fit_stride;
+    sp.wexp += (int64_t)g * sp_fit_stride;
+    double* prev = prev_all + (size_t)grp * S;
+    const int chain = blockIdx.x;
+    const int s0 = ch.start[chain], s1 = ch.end[chain];
+#define VIT_BAR() asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(tpf) : "memory")
+    for (int jj = t; jj < S; jj += tpf) {
         double v = F[(int64_t)s0 * S + jj];
         lattice[(int64_t)s0 * S + jj] = v;
         prev[jj] = v;
     }
-    __syncthreads();
+    VIT_BAR();
+    // row n-1 -> n; descriptors of the next row and the next frame value (first column) one segment ahead
+    int cls = s0 < s1 ? rows.tclass[s0] : -1, br = s0 < s1 ? rows.brow[s0] : -1, dd0 = s0 < s1 ? rows.d0[s0] : 0;
+    double fcur = (s0 < s1 && t < S) ? F[(int64_t)(s0 + 1) * S + t] : 0.;
     for (int n = s0 + 1; n <= s1; ++n) {
         LogTCtx lt;
-        logT_setup(lt, d, rows, sp, tots, n - 1);
-        double out[4];   // up to 4 columns per thread (S <= 4096)
-        int cnt = 0;
-        for (int jj = t; jj < S; jj += blockDim.x) {
-            double vmax = -INFINITY;
-            for (int i = 0; i < S; ++i) {
-                double v = __dadd_rn(prev[i], logT(lt, d, i, jj));
-                if (v > vmax) vmax = v;
-            }
-            out[cnt++] = __dadd_rn(vmax, F[(int64_t)n * S + jj]);
+        logT_from(lt, d, sp, tots, cls, br, dd0);
+        const double* Ts = (lt.kind == 1 && cls < staged) ? Tsm + (size_t)cls * S * S : nullptr;
+        const double fn0 = fcur;
+        if (n < s1) {
+            cls = rows.tclass[n]; br = rows.brow[n]; dd0 = rows.d0[n];
+            if (t < S) fcur = F[(int64_t)(n + 1) * S + t];
         }
-        __syncthreads();
+        double out[4];   // up to 4 columns per thread
+        int cnt = 0;
+        for (int jj = t; jj < S; jj += tpf) {
+            double vmax = -INFINITY;
+            const double fn = jj == t ? fn0 : F[(int64_t)n * S + jj];
+            if (Ts) {
+#pragma unroll 8
+                for (int i = 0; i < S; ++i) {
+                    double v = __dadd_rn(prev[i], Ts[i * S + jj]);
+                    if (v > vmax) vmax = v;
+                }
+            } else if (lt.kind == 0) {
+                for (int i = 0; i < S; ++i)
+                    if (prev[i] > vmax) vmax = prev[i];
+            } else {
+                for (int i = 0; i < S; ++i) {
+                    double v = __dadd_rn(prev[i], logT(lt, d, i, jj));
+                    if (v > vmax) vmax = v;
+                }
+            }
+            out[cnt++] = __dadd_rn(vmax, fn);
+        }
+        VIT_BAR();
         cnt = 0;
-        for (int jj = t; jj < S; jj += blockDim.x) {
+        for (int jj = t; jj < S; jj += tpf) {
             prev[jj] = out[cnt];
             lattice[(int64_t)n * S + jj] = out[cnt];
             ++cnt;
         }
-        __syncthreads();
+        VIT_BAR();
     }
-    // traceback
-    for (int n = s1; n >= s0; --n) {
-        LogTCtx lt;
+#undef VIT_BAR
+    // traceback by the group's first warp: no barriers on the sequential path; the lattice row and the row
+    // descriptors of the next step are loaded before the current step's reduction
+    if (t < 32) {
+        constexpr int KP = 4;                 // rows of up to 128 states are prefetched in registers
+        const bool pre = S <= 32 * KP;
         int nxt = 0;
-        if (n < s1) {
-            logT_setup(lt, d, rows, sp, tots, n);
-            nxt = s_next;
+        double lv[KP] = {0., 0., 0., 0.};
+        int pc = -1, pb = -1, pd0 = 0;
+        if (pre) {
+#pragma unroll
+            for (int k = 0; k < KP; ++k) lv[k] = (t + 32 * k < S) ? lattice[(int64_t)s1 * S + t + 32 * k] : 0.;
         }
-        double bv = -INFINITY;
-        int bi = 0x7fffffff;
-        for (int i = t; i < S; i += blockDim.x) {
-            double v = lattice[(int64_t)n * S + i];
-            if (n < s1) v = __dadd_rn(v, logT(lt, d, i, nxt));
-            if (v > bv) { bv = v; bi = i; }   // ascending i per thread: first max kept
+        for (int n = s1; n >= s0; --n) {
+            // on entry: lv = lattice row n, (pc, pb, pd0) = descriptors of row n (transition n -> n+1, n < s1)
+            LogTCtx lt;
+            const double* Ts = nullptr;
+            lt.kind = 0;
+            double cur[KP];
+#pragma unroll
+            for (int k = 0; k < KP; ++k) cur[k] = lv[k];
+            if (n < s1) {
+                logT_from(lt, d, sp, tots, pc, pb, pd0);
+                if (lt.kind == 1 && pc < staged) Ts = Tsm + (size_t)pc * S * S;
+            }
+            int nc = -1, nb = -1, nd0 = 0;
+            if (n > s0) {       // the next step's inputs, in flight during this step's reduction
+                if (pre) {
+#pragma unroll
+                    for (int k = 0; k < KP; ++k) lv[k] = (t + 32 * k < S) ? lattice[(int64_t)(n - 1) * S + t + 32 * k] : 0.;
+                }
+                nc = rows.tclass[n - 1]; nb = rows.brow[n - 1]; nd0 = rows.d0[n - 1];
+            }
+            double bv = -INFINITY;
+            int bi = 0x7fffffff;
+            if (pre) {
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    const int i = t + 32 * k;
+                    if (i < S) {
+                        double v = cur[k];
+                        if (n < s1) {
+                            if (Ts) v = __dadd_rn(v, Ts[i * S + nxt]);
+                            else v = __dadd_rn(v, logT(lt, d, i, nxt));
+                        }
+                        if (v > bv) { bv = v; bi = i; }   // ascending i per lane: first max kept
+                    }
+                }
+            } else {
+                for (int i = t; i < S; i += 32) {
+                    double v = lattice[(int64_t)n * S + i];
+                    if (n < s1) {
+                        if (Ts) v = __dadd_rn(v, Ts[i * S + nxt]);
+                        else v = __dadd_rn(v, logT(lt, d, i, nxt));
+                    }
+                    if (v > bv) { bv = v; bi = i; }
+                }
+            }
+            // warp argmax with lowest-index tie break
+            for (int o = 16; o > 0; o >>= 1) {
+                double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (bi == 0x7fffffff) bi = 0;   // all -inf / NaN: _argmax returns 0
+            if (t == 0) path[n] = bi;
+            nxt = bi;
+            pc = nc; pb = nb; pd0 = nd0;
         }
-        // warp argmax with lowest-index tie break
-        for (int o = 16; o > 0; o >>= 1) {
-            double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-        }
-        __syncthreads();
-        if ((t & 31) == 0) { rv[t >> 5] = bv; ri[t >> 5] = bi; }
-        __syncthreads();
-        if (t == 0) {
-            int nw = (blockDim.x + 31) >> 5;
-            double fv = rv[0];
-            int fi = ri[0];
-            for (int w = 1; w < nw; ++w)
-                if (rv[w] > fv || (rv[w] == fv && ri[w] < fi)) { fv = rv[w]; fi = ri[w]; }
-            if (fi == 0x7fffffff) fi = 0;   // all -inf / NaN: _argmax returns 0
-            path[n] = fi;
-            s_next = fi;
-        }
-        __syncthreads();
     }
 }
 
@@ -1336,12 +1420,24 @@ void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
 
 void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
                         const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
-                        double* lattice, int* path) {
+                        double* lattice, int* path, int nclass) {
     if (ch.NC <= 0 || gn <= 0) return;
-    int threads = ((d.S + 31) / 32) * 32;
-    if (threads > 1024) threads = 1024;
-    size_t smem = sizeof(double) * d.S + (size_t)d.S * d.M + 16;
-    k_viterbi<<<dim3(ch.NC, gn), threads, smem, st>>>(d, g0, ch, rows, sp, sp_fit_stride, T.tab, F, lattice, path);
+    int tpf = ((d.S + 31) / 32) * 32;
+    if (tpf > 1024) tpf = 1024;
+    int fpc = 1024 / tpf;                 // fits per CTA: they share the staged class matrices
+    if (fpc > 4) fpc = 4;
+    if (fpc > gn) fpc = gn;
+    // class matrices of the plain rows in shared memory, as many as fit (class ids are dense from 0)
+    int staged = 0;
+    while (staged < nclass && sizeof(double) * (size_t)(staged + 1) * d.S * d.S <= 160 * 1024) ++staged;
+    size_t smem = sizeof(double) * ((size_t)fpc * d.S + (size_t)staged * d.S * d.S) + (size_t)d.S * d.M + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_viterbi, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    k_viterbi<<<dim3(ch.NC, (gn + fpc - 1) / fpc), tpf * fpc, smem, st>>>(d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F,
+                                                                          lattice, path, staged, fpc);
 }
 
 void rmx_launch_materialize_T(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,

@@ -112,7 +112,7 @@ void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
                         const double* bhat, const double* fexp, double* rowsum, int64_t rowsum_fit_stride);
 void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
                         const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
-                        double* lattice, int* path);
+                        double* lattice, int* path, int nclass);
 // single fit: pointers (and sp.pd / sp.wexp) already offset to that fit
 void rmx_launch_materialize_T(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
                               const RmxTransSpec& sp, int64_t row0, int64_t nrows, double* out);

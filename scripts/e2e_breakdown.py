@@ -26,7 +26,7 @@ for rep in range(2):
     t = tick('build_model x%d' % G, t)
     h = np.array([pipeline.init_h(ip) for ip in inits])
     dw = np.array([ip['divergence_weight'] for ip in inits], dtype=float)
-    args = drivers[0].model_args(h) + (dw,)
+    args = drivers[0].model_args(h, compact=True) + (dw,)
     t = tick('model_args', t)
     batch = bpmodel.RemixtBatch(*args, device=0)
     t = tick('RemixtBatch()', t)

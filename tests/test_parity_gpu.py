@@ -376,3 +376,23 @@ def test_determinism_and_properties_genome(cuda_bpmodel):
     m1.variational_update(3)
     assert np.array_equal(m1.posterior_marginals, post)
     assert m1.calculate_elbo() == elbos[-1]
+
+
+def test_compact_cn_states_equals_full(cuda_bpmodel):
+    """``cn_states`` given as its two factors (CompactCnStates) or as the reference's (N1,S,M,2) array: same model."""
+    exp = util.load_experiment('small')
+    ip = util.init_params('small', 4)
+    drv = util.make_driver(exp, ip)
+    h = np.asarray(drv.model.h)
+    full = drv.model_args(h) + (ip['divergence_weight'],)
+    comp = drv.model_args(h, compact=True) + (ip['divergence_weight'],)
+    assert isinstance(full[4], np.ndarray) and isinstance(comp[4], cuda_bpmodel.CompactCnStates)
+    assert np.array_equal(np.asarray(comp[4]), full[4]) and comp[4].max() == full[4].max()
+    assert np.array_equal(np.asarray(comp[4][3:9]), full[4][3:9])
+    a, b = cuda_bpmodel.RemixtModel(*full), cuda_bpmodel.RemixtModel(*comp)
+    for m in (a, b):
+        drv.attach(m)       # likelihood masks (dummy segments have no data)
+        m.variational_update(2)
+    assert a.calculate_elbo() == b.calculate_elbo()
+    assert np.array_equal(a.posterior_marginals, b.posterior_marginals)
+    assert np.array_equal(a.is_loh, b.is_loh) and np.array_equal(a.cn_states_total, b.cn_states_total)
