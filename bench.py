@@ -221,12 +221,18 @@ def build_batch(exp, inits, device):
     return batch, drivers, h2d
 
 
+LLTABLE_CONVENTION_OPS = 900.
+
+
 # algorithmic work per (segment, state) of each kernel class: (bound, bytes, fp64 ops)  -- DESIGN.md, Kernels
 def kernel_models(N1, S, NC, G, R):
     ns = float(N1) * S * G
     return {
         'chain': ('fp64', 32. * ns, 2. * 2. * S * S * (N1 - NC) * G),
-        'lltable': ('fp64', 48. * ns, 900. * ns),
+        # 200 executed FP64-pipe instructions per (n,s) (ncu: dadd + dmul + dfma thread instructions of k_lltable2,
+        # profiles/r01_summary.md), each counted as one FMA = 2 flop; SURVEY.md 8d's convention for the reference-minimal
+        # evaluation (12 lgamma + 4 log = 900 op-equivalents) is reported next to it (LLTABLE_CONVENTION_OPS)
+        'lltable': ('fp64', 48. * ns, 400. * ns),
         'frame': ('hbm', 64. * ns, 14. * ns),
         'qsums': ('hbm', 56. * ns, 12. * ns),
         'post': ('hbm', 24. * ns, 3. * ns),
@@ -340,6 +346,8 @@ def gpu_arm(args):
             ent['tflops'] = flops / t_s / 1e12
             ent['hbm_frac'] = ent['gbs'] / hbm_peak if hbm_peak else None
             ent['fp64_frac'] = ent['tflops'] / fp64_peak if fp64_peak else None
+            if k == 'lltable' and fp64_peak:
+                ent['fp64_frac_survey_convention_900'] = ent['tflops'] * (LLTABLE_CONVENTION_OPS / 400.) / fp64_peak
         kernels[k] = ent
     dom = max(kernels, key=lambda k: kernels[k]['share_of_kernel_time'] if k in models else -1.)
     de = kernels[dom]
