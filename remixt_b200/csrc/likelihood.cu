@@ -309,7 +309,9 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
     for (int idx = blockIdx.x * blockDim.x + t; idx < NS; idx += gridDim.x * blockDim.x) {
         const int n = idx / d.S, s = idx - n * d.S;
         const double2* sp = segf + (int64_t)n * (LLT2_SEGW / 2);
-        const double2 s45 = __ldg(sp + 5);                       // y1, flags
+        // all six sectors of the segment's record at once: one latency round instead of three dependent ones
+        const double2 c01 = __ldg(sp), cb0 = __ldg(sp + 1), cb1 = __ldg(sp + 2), lx = __ldg(sp + 3), ly = __ldg(sp + 4),
+                      s45 = __ldg(sp + 5);                       // (c0,c1) (cb00,cb01) (cb10,cb11) (logl,x) (l,y0) (y1,flags)
         const int si = (int)__double_as_longlong(s45.y);
         const int e = (si >> 8) * d.S + s;
         const int sf = sfl[e];
@@ -321,7 +323,6 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
 #pragma unroll
             for (int k = 0; k < RMX_NTERM; ++k) ll[k] = 0.;
             if (tmk) {
-                const double2 c01 = __ldg(sp), lx = __ldg(sp + 3), ly = __ldg(sp + 4);   // (c0,c1) (logl,x) (l,y0)
                 const double x = lx.y;
                 const double mu = st[e] * ly.x;
                 const double lmu = st[QS + e] + lx.x;
@@ -343,8 +344,7 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
                 ll[1] = c01.y + fma(x, lmu - l1, r1 * (lnr1 - l1));
             }
             if (amk) {
-                const double y0 = __ldg(sp + 4).y, y1 = s45.x;
-                const double2 cb0 = __ldg(sp + 1), cb1 = __ldg(sp + 2);
+                const double y0 = ly.y, y1 = s45.x;
 #pragma unroll
                 for (int v = 0; v < 2; ++v) {
                     const double a = st[(2 + 2 * v) * QS + e], b = st[(3 + 2 * v) * QS + e];
@@ -402,6 +402,58 @@ __global__ void __launch_bounds__(256) k_frame(RmxTables T, RmxDims d, const Rmx
         int64_t i = (int64_t)n * d.S + s;
         fexp[i] = exp(F[i] - mx);   // own store, L1/L2 hit
     }
+    if (lane == 0) mF_all[(int64_t)g * d.N + n] = mx;
+    if (bad) atomicOr(dflags, RMX_F_FRAME_NAN);
+}
+
+// k_frame for state spaces up to 128: the six likelihood rows of the segment in registers (all loads in flight at
+// once), one pass.  Same arithmetic as k_frame (rmx_frame_value), so the results are bit-identical.
+template <int KS>
+__global__ void __launch_bounds__(256) k_frame_reg(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                   const double* __restrict__ LL_all,
+                                                   const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
+                                                   const double* __restrict__ q_sw_all,
+                                                   double* __restrict__ F_all, double* __restrict__ fexp_all,
+                                                   double* __restrict__ mF_all, int* __restrict__ dflags) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    const int g = RMX_FIT();
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const int64_t row = (int64_t)n * d.S;
+    const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS + row;
+    double ll[RMX_NTERM][KS];
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+        const int s = lane + 32 * k;
+#pragma unroll
+        for (int t = 0; t < RMX_NTERM; ++t) ll[t][k] = s < d.S ? LL[(int64_t)t * NS + s] : 0.;
+    }
+    const int64_t q = ((int64_t)g * d.N + n) * 2;
+    const double ot0 = q_ot_all[q], ot1 = q_ot_all[q + 1];
+    const double oa0 = q_oa_all[q], oa1 = q_oa_all[q + 1];
+    const double sw0 = q_sw_all[q], sw1 = q_sw_all[q + 1];
+    const double ln = T.l[n], dw = Pg[g].divergence_weight;
+    double* F = F_all + (int64_t)g * NS + row;
+    double* fexp = fexp_all + (int64_t)g * NS + row;
+    double f[KS];
+    double mx = -INFINITY;
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+        const int s = lane + 32 * k;
+        if (s < d.S) {
+            f[k] = rmx_frame_value(ot0, ot1, oa0, oa1, sw0, sw1, ll[0][k], ll[1][k], ll[2][k], ll[3][k], ll[4][k], ll[5][k],
+                                   (double)T.nsub[s], ln, dw);
+            F[s] = f[k];
+            bad |= isnan(f[k]);
+            mx = fmax(mx, f[k]);
+        }
+    }
+    mx = warp_max(mx);
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) fexp[lane + 32 * k] = exp(f[k] - mx);
     if (lane == 0) mF_all[(int64_t)g * d.N + n] = mx;
     if (bad) atomicOr(dflags, RMX_F_FRAME_NAN);
 }
@@ -1041,7 +1093,13 @@ void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, con
                       const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
                       double* fexp, double* mF, int* dflags) {
     if (d.N <= 0 || gn <= 0) return;
-    k_frame<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+    const dim3 grid(cdiv((int64_t)d.N * 32, 256), gn);
+    const int ks = (d.S + 31) / 32;
+    if (ks == 1) k_frame_reg<1><<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+    else if (ks == 2) k_frame_reg<2><<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+    else if (ks == 3) k_frame_reg<3><<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+    else if (ks == 4) k_frame_reg<4><<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
+    else k_frame<<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
 }
 
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
