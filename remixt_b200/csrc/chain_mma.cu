@@ -53,12 +53,18 @@ __device__ __forceinline__ int cm_pos(int g, int i) { return ((i >> 2) << 5) + (
 
 // one CTA per SM, at most 8 warps: up to 232 registers per thread
 #define CM_NH 2     // column blocks (of 8 states) per warp
+#define CM_FST 4    // stages of the f ring (cp.async prefetch distance + 1)
 
 template <int KB>
 struct CmCfg {
     static constexpr int NB = (KB + 1) / 2;                 // column blocks covering 4*KB >= S states
     static constexpr int NWARPS = (NB + CM_NH - 1) / CM_NH;
     static constexpr int MAXT = NWARPS * 32;
+    // B fragments (the transition matrix) per column block: KREG in registers, the rest in a per-thread shared-memory
+    // slot.  With all of them declared as registers the compiler ran out at 255 and re-loaded ~10 from L2 every
+    // segment (LDG in front of the first DMMA: 24 % of the kernel's stall samples, profiles/r01_summary.md).
+    static constexpr int KREG = KB < 19 ? KB : 19;
+    static constexpr int KSM = KB - KREG;
 };
 
 template <int KB>
@@ -72,6 +78,13 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
     double* redd = wtab + CM_GT * MD;                                 // [8][NWMAX] + [8] mF sums
     int* redi = reinterpret_cast<int*>(redd + CM_GT * CM_NWMAX + CM_GT);   // [2][8][NWMAX] max exponent fields
     int8_t* tots = reinterpret_cast<int8_t*>(redi + 2 * CM_GT * CM_NWMAX); // [S*M]
+    constexpr int KREG = CmCfg<KB>::KREG, KSM = CmCfg<KB>::KSM;
+    // [CM_NH * KSM][T] doubles after tots (16-byte aligned): this thread's overflow B fragments
+    double* esm = reinterpret_cast<double*>(smem_raw + ((sizeof(double) * ((size_t)2 * KB * 32 + (size_t)CM_GT * MD + CM_GT * CM_NWMAX + CM_GT) +
+                                                         sizeof(int) * 2 * CM_GT * CM_NWMAX + (size_t)S * M + 15) & ~(size_t)15)) + threadIdx.x;
+    // f ring: [CM_FST stages][CM_NH][2][T] doubles after the B-fragment slots; every thread copies its own entries
+    // with cp.async several segments ahead (no registers held across the copy, no barrier: own slots only)
+    double* fring = esm + (size_t)CM_NH * KSM * T;
 
     const int tile = blockIdx.x % A.ntiles;
     const int cd = blockIdx.x / A.ntiles;
@@ -124,54 +137,39 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
     }
     auto seg_of = [&](int k) { return dir == 0 ? s0 + 1 + k : s1 - 1 - k; };   // segment produced at step k
     auto row_of = [&](int k) { return dir == 0 ? s0 + k : s1 - 1 - k; };       // its transition row
-    // software pipeline: f two segments ahead, row info two rows ahead
-    double fa[CM_NH][2], fb[CM_NH][2];
+    // software pipeline: f CM_FST - 1 segments ahead through the shared-memory ring, row info two rows ahead
     int ri0 = 0, ri1 = 0;
+    const unsigned fring_s = (unsigned)__cvta_generic_to_shared(fring);
+    auto f_issue = [&](int k) {
+        if (k < nsteps) {
+            const int64_t o = (int64_t)seg_of(k) * S;
+            const unsigned base = fring_s + 8u * (unsigned)(((k % CM_FST) * CM_NH * 2) * T);
 #pragma unroll
-    for (int h = 0; h < CM_NH; ++h) fa[h][0] = fa[h][1] = fb[h][0] = fb[h][1] = 0.;
-    if (nsteps > 0) {
-        const int64_t o = (int64_t)seg_of(0) * S;
-#pragma unroll
-        for (int h = 0; h < CM_NH; ++h) {
-            if (ok0[h]) fa[h][0] = fp[o + 8 * h];
-            if (ok1[h]) fa[h][1] = fp[o + 8 * h + 1];
+            for (int h = 0; h < CM_NH; ++h) {
+                if (ok0[h]) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(base + 8u * (unsigned)((h * 2) * T)), "l"(fp + o + 8 * h) : "memory");
+                if (ok1[h]) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(base + 8u * (unsigned)((h * 2 + 1) * T)), "l"(fp + o + 8 * h + 1) : "memory");
+            }
         }
-        ri0 = A.rinfo[row_of(0)];
-    }
-    if (nsteps > 1) {
-        const int64_t o = (int64_t)seg_of(1) * S;
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
 #pragma unroll
-        for (int h = 0; h < CM_NH; ++h) {
-            if (ok0[h]) fb[h][0] = fp[o + 8 * h];
-            if (ok1[h]) fb[h][1] = fp[o + 8 * h + 1];
-        }
-        ri1 = A.rinfo[row_of(1)];
-    }
+    for (int e = 0; e < CM_FST * CM_NH * 2; ++e) fring[e * T] = 0.;     // entries outside the state space stay zero
+#pragma unroll
+    for (int k = 0; k < CM_FST - 1; ++k) f_issue(k);
+    if (nsteps > 0) ri0 = A.rinfo[row_of(0)];
+    if (nsteps > 1) ri1 = A.rinfo[row_of(1)];
     __syncthreads();
 
-    double ereg[CM_NH][KB];
+    double ereg[CM_NH][KREG];
     int cur_class = -1;
     int cur = 0, esum = 0, bad = 0;
 
     for (int step = 0; step < nsteps; ++step) {
         const int64_t on = (int64_t)seg_of(step) * S;
         const int ri = ri0;
-        double f[CM_NH][2];
-#pragma unroll
-        for (int h = 0; h < CM_NH; ++h) {
-            f[h][0] = fa[h][0]; f[h][1] = fa[h][1];
-            fa[h][0] = fb[h][0]; fa[h][1] = fb[h][1];
-        }
         ri0 = ri1;
-        if (step + 2 < nsteps) {
-            const int64_t o = (int64_t)seg_of(step + 2) * S;
-#pragma unroll
-            for (int h = 0; h < CM_NH; ++h) {
-                if (ok0[h]) fb[h][0] = fp[o + 8 * h];
-                if (ok1[h]) fb[h][1] = fp[o + 8 * h + 1];
-            }
-            ri1 = A.rinfo[row_of(step + 2)];
-        }
+        if (step + 2 < nsteps) ri1 = A.rinfo[row_of(step + 2)];
+        f_issue(step + CM_FST - 1);       // into the ring stage the previous step consumed
         const int cls = (ri & 0xff) - 1;
         const int br = (ri >> 12) - 1;
         // exponents of the largest entry of the input message of fit gid, per warp (written before the last barrier)
@@ -190,7 +188,10 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
 #pragma unroll
                     for (int kb = 0; kb < KB; ++kb) {
                         const int i = kb * 4 + tig, jb = jbase + 8 * h + gid;
-                        ereg[h][kb] = (i < S && jb < S) ? E[(int64_t)i * S + jb] : 0.;
+                        double ev = (i < S && jb < S) ? E[(int64_t)i * S + jb] : 0.;
+                        asm volatile("" : "+d"(ev));     // opaque: keep the value, do not re-load it every segment
+                        if (kb < KREG) ereg[h][kb < KREG ? kb : 0] = ev;
+                        else esm[(h * KSM + (kb - KREG)) * T] = ev;
                     }
                 cur_class = cls;
             }
@@ -202,8 +203,9 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
                 const double a = uc[kb * 32 + lane];
 #pragma unroll
                 for (int h = 0; h < CM_NH; ++h) {
-                    if (kb & 1) cm_dmma(e[h][0], e[h][1], a, ereg[h][kb]);
-                    else cm_dmma(c[h][0], c[h][1], a, ereg[h][kb]);
+                    const double eb = kb < KREG ? ereg[h][kb < KREG ? kb : 0] : esm[(h * KSM + (kb - KREG)) * T];
+                    if (kb & 1) cm_dmma(e[h][0], e[h][1], a, eb);
+                    else cm_dmma(c[h][0], c[h][1], a, eb);
                 }
             }
 #pragma unroll
@@ -259,6 +261,13 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
             }
         }
         // ---- epilogue (C-fragment layout)
+        double f[CM_NH][2];
+        asm volatile("cp.async.wait_group %0;" ::"n"(CM_FST - 1) : "memory");     // this step's f has landed
+        {
+            const double* fr = fring + ((step % CM_FST) * CM_NH * 2) * T;
+#pragma unroll
+            for (int h = 0; h < CM_NH; ++h) { f[h][0] = fr[(h * 2) * T]; f[h][1] = fr[(h * 2 + 1) * T]; }
+        }
         int be = max(max(max(r0.x, r0.y), max(r0.z, r0.w)), max(max(r1.x, r1.y), max(r1.z, r1.w)));
         esum += be - 1023;
         if (be <= 0 || be >= 2047) bad = 1;
@@ -326,6 +335,7 @@ static int launch_chain_mma_cfg(cudaStream_t st, ChainMmaArgs& A) {
     if (threads > CmCfg<KB>::MAXT || NW > CM_NWMAX || 4 * KB < d.S) return 2;
     size_t smem = sizeof(double) * ((size_t)2 * KB * 32 + (size_t)CM_GT * d.M * d.D + CM_GT * CM_NWMAX + CM_GT) +
                   sizeof(int) * 2 * CM_GT * CM_NWMAX + (size_t)d.S * d.M + 16;
+    smem = ((smem + 15) & ~(size_t)15) + sizeof(double) * ((size_t)CM_NH * CmCfg<KB>::KSM + (size_t)CM_FST * CM_NH * 2) * threads + 16;
     auto kern = k_chain_mma<KB>;
     if (smem > 48 * 1024) {
         if (smem > 227 * 1024) return 2;
