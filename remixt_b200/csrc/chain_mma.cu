@@ -174,7 +174,12 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
         const int br = (ri >> 12) - 1;
         // exponents of the largest entry of the input message of fit gid, per warp (written before the last barrier)
         const int4* rp = reinterpret_cast<const int4*>(redi + (cur * CM_GT + gid) * CM_NWMAX);
-        const int4 r0 = rp[0], r1 = rp[1];
+        int4 r0 = rp[0], r1 = rp[1];
+        if (CmCfg<KB>::NWARPS > 8) {        // more than eight warps: fold the upper half of the per-warp maxima in
+            const int4 r2 = rp[2], r3 = rp[3];
+            r0.x = max(r0.x, r2.x); r0.y = max(r0.y, r2.y); r0.z = max(r0.z, r2.z); r0.w = max(r0.w, r2.w);
+            r1.x = max(r1.x, r3.x); r1.y = max(r1.y, r3.y); r1.z = max(r1.z, r3.z); r1.w = max(r1.w, r3.w);
+        }
         const double* uc = u + cur * KB * 32;
 
         double c[CM_NH][2];
