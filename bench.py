@@ -306,12 +306,16 @@ def gpu_arm(args):
 
     del state['elbo']
     d2h = e2e_step()
-    e2e_steps = max(1, min(args.steps, 3))
+    e2e_steps = max(1, min(args.steps, 5))
     barrier()
-    t0 = time.perf_counter()
+    e2e_times = []
     for _ in range(e2e_steps):
+        t0 = time.perf_counter()
         e2e_step()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+        e2e_times.append(time.perf_counter() - t0)
+    # the median step: a host hiccup (page faults of a fresh box, another tenant on the host cores) lands on one step
+    # of a handful and would otherwise own the mean; all step times are reported next to it
+    e2e_s = float(np.median(e2e_times))
 
     if dist is not None:
         import torch
@@ -372,7 +376,8 @@ def gpu_arm(args):
         'em_iterations_per_s': G * world / (ms_per_step * 1e-3),
         'clocks': clocks, 'gpu_launches': int(launches),
         'e2e': {'value': evals / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
-                'ms_per_step': e2e_s * 1e3},
+                'ms_per_step': e2e_s * 1e3, 'statistic': 'median of %d steps' % e2e_steps,
+                'ms_all_steps': [round(t * 1e3, 1) for t in e2e_times]},
         'roofline': roofline, 'kernels': kernels,
         'elbo_checksum': float(np.sum(batch.calculate_elbo())),
     }
