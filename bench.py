@@ -171,7 +171,19 @@ def dist_setup(n_gpus):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
-        dist.init_process_group(backend='nccl')
+        # NCCL announces its version on stdout when the first communicator comes up; stdout carries the one JSON
+        # line only, so the start-up (init + first collective) runs with fd 1 pointed at stderr
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group(backend='nccl', device_id=torch.device('cuda', local))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
         return rank, world, local, dist
     return 0, 1, 0, None
 

@@ -1304,16 +1304,25 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
         // kernel (k_round)
         for (int it = 0; it < n_iter; ++it) {
             int rc = RMX_OK;
-            if (it == 0) rc = do_update_q(m, 0);
-            if (rc) return rc;
-            rc = do_update_p_cn(m, it > 0, true);
+            if (it == 0) {
+                // update_p_allele_swap and the frame log-probability of the first round: the same kernel in its
+                // head mode (likelihood sums of the stored posterior, swap update, frame) instead of three passes
+                rc = ensure_ll(m, m->g0, m->gn);
+                if (rc) return rc;
+                cudaEvent_t th_ = b->tbegin(RMX_K_ROUND);
+                rmx_launch_round(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->ahat, b->bhat, b->post, b->Asum,
+                                 b->q_ot, b->q_oa, b->q_sw, b->prior_ot, b->prior_oa, 1, 1, b->F, b->fexp, b->mF, b->dflags);
+                b->tend(th_);
+                b->count();
+            }
+            rc = do_update_p_cn(m, true, true);
             if (rc) return rc;
             rc = do_update_p_breakpoint(m);
             if (rc) return rc;
             cudaEvent_t te_ = b->tbegin(RMX_K_ROUND);
             rmx_launch_round(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, b->LL, b->ahat, b->bhat, b->post, b->Asum,
-                             b->q_ot, b->q_oa, b->q_sw, b->prior_ot, b->prior_oa, it + 1 < n_iter ? 1 : 0, b->F, b->fexp,
-                             b->mF, b->dflags);
+                             b->q_ot, b->q_oa, b->q_sw, b->prior_ot, b->prior_oa, it + 1 < n_iter ? 1 : 0, 0, b->F,
+                             b->fexp, b->mF, b->dflags);
             b->tend(te_);
             b->count();
             for (int g = m->g0; g < m->g0 + m->gn; ++g) b->asum_valid[g] = 1;

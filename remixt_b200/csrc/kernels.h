@@ -52,8 +52,8 @@ void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const d
 int rmx_round_ok(const RmxDims& d);
 void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* ahat, const double* bhat, double* post, double* A, double* q_ot,
-                      double* q_oa, double* q_sw, double prior_ot, double prior_oa, int next, double* F, double* fexp,
-                      double* mF, int* dflags);
+                      double* q_oa, double* q_sw, double prior_ot, double prior_oa, int next, int head, double* F,
+                      double* fexp, double* mF, int* dflags);
 void rmx_launch_qupdate(cudaStream_t st, const RmxDims& d, int g0, int gn, int which, const double* A,
                         const double* q_oa, const double* q_sw, double prior, double* out);
 void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int ncol, int g0, int gn,

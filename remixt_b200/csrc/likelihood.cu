@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const 
                                                const double* __restrict__ bhat_all, double* __restrict__ post_all,
                                                double* __restrict__ A_all, double* __restrict__ q_ot_all,
                                                double* __restrict__ q_oa_all, double* __restrict__ q_sw_all,
-                                               double lpt0, double lpt1, double lpa0, double lpa1, int next,
+                                               double lpt0, double lpt1, double lpa0, double lpa1, int next, int head,
                                                double* __restrict__ F_all,
                                                double* __restrict__ fexp_all, double* __restrict__ mF_all,
                                                int* __restrict__ dflags) {
@@ -528,15 +528,20 @@ __global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const 
         const int s = lane + 32 * k;
 #pragma unroll
         for (int t = 0; t < RMX_NTERM; ++t) ll[t][k] = s < d.S ? LL[(int64_t)t * NS + s] : 0.;
-        p[k] = s < d.S ? __dmul_rn(ah[s], bh[s]) : 0.;
+        p[k] = s < d.S ? (head ? post_all[(int64_t)g * NS + row + s] : __dmul_rn(ah[s], bh[s])) : 0.;
     }
+    // head = 1: the first round of a loop.  The posterior marginals are the stored ones (previous EM iteration or
+    // the constructor's), only the swap update and the frame log-probability follow (update_p_allele_swap and the
+    // head of update_p_cn, cn_model.py:447-449): k_qsums + k_qupdate(0) + k_frame in one pass.
     // ---- posterior marginals
     double z = 0.;
+    bool bad = false;
+    if (!head) {
 #pragma unroll
     for (int k = 0; k < KS; ++k)
         if (lane + 32 * k < d.S) z = __dadd_rn(z, p[k]);
     z = warp_sum(z);
-    bool bad = !(z > 0.);
+    bad = !(z > 0.);
     double* post = post_all + (int64_t)g * NS + row;
 #pragma unroll
     for (int k = 0; k < KS; ++k)
@@ -546,6 +551,7 @@ __global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const 
             bad |= isnan(p[k]);
         }
     if (bad) atomicOr(dflags, RMX_F_POST_NAN);
+    }
     // ---- posterior-weighted likelihood sums
     double a[RMX_NTERM];
 #pragma unroll
@@ -567,15 +573,20 @@ __global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const 
     }
     // ---- outlier factors (every lane holds the same sums; lane 0 stores)
     double ot[2], oa[2], sw[2], qa[2];
-    rmx_q_args(1, a, 0., 0., lpt0, lpt1, qa);
-    exp_normalize2(qa[0], qa[1], ot);
-    sw[0] = q_sw_all[gn * 2];
-    sw[1] = q_sw_all[gn * 2 + 1];
-    rmx_q_args(2, a, sw[0], sw[1], lpa0, lpa1, qa);
-    exp_normalize2(qa[0], qa[1], oa);
-    if (lane == 0) {
-        q_ot_all[gn * 2] = ot[0]; q_ot_all[gn * 2 + 1] = ot[1];
-        q_oa_all[gn * 2] = oa[0]; q_oa_all[gn * 2 + 1] = oa[1];
+    if (head) {
+        ot[0] = q_ot_all[gn * 2]; ot[1] = q_ot_all[gn * 2 + 1];
+        oa[0] = q_oa_all[gn * 2]; oa[1] = q_oa_all[gn * 2 + 1];
+    } else {
+        rmx_q_args(1, a, 0., 0., lpt0, lpt1, qa);
+        exp_normalize2(qa[0], qa[1], ot);
+        sw[0] = q_sw_all[gn * 2];
+        sw[1] = q_sw_all[gn * 2 + 1];
+        rmx_q_args(2, a, sw[0], sw[1], lpa0, lpa1, qa);
+        exp_normalize2(qa[0], qa[1], oa);
+        if (lane == 0) {
+            q_ot_all[gn * 2] = ot[0]; q_ot_all[gn * 2 + 1] = ot[1];
+            q_oa_all[gn * 2] = oa[0]; q_oa_all[gn * 2 + 1] = oa[1];
+        }
     }
     if (!next) return;
     // ---- next round: allele swap factor, frame log-probability
@@ -1112,13 +1123,13 @@ int rmx_round_ok(const RmxDims& d) { return d.S <= 128; }
 
 void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* ahat, const double* bhat, double* post, double* A, double* q_ot,
-                      double* q_oa, double* q_sw, double prior_ot, double prior_oa, int next, double* F, double* fexp,
-                      double* mF, int* dflags) {
+                      double* q_oa, double* q_sw, double prior_ot, double prior_oa, int next, int head, double* F,
+                      double* fexp, double* mF, int* dflags) {
     if (d.N <= 0 || gn <= 0) return;
     const dim3 grid(cdiv((int64_t)d.N * 32, 256), gn);
     const int ks = (d.S + 31) / 32;
 #define RMX_ROUND(KS) k_round<KS><<<grid, 256, 0, st>>>(T, d, P, g0, LL, ahat, bhat, post, A, q_ot, q_oa, q_sw, \
-                                                       log(1. - prior_ot), log(prior_ot), log(1. - prior_oa), log(prior_oa), next, F, fexp, mF, dflags)
+                                                       log(1. - prior_ot), log(prior_ot), log(1. - prior_oa), log(prior_oa), next, head, F, fexp, mF, dflags)
     if (ks <= 1) RMX_ROUND(1);
     else if (ks == 2) RMX_ROUND(2);
     else if (ks == 3) RMX_ROUND(3);
