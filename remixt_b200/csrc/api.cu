@@ -1381,8 +1381,15 @@ static int elbo_terms(Model* m, bool full) {
             const bool upd = b->cn_updated[g] != 0;
             if (upd && !full && b->tm_used[g] == b->tm_cached[g]) {
                 if (b->R > 0) {
-                    { cudaEvent_t te_ = b->tbegin(RMX_K_PAIRSUM); rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
-                                       b->ahat, b->bhat, b->fexp, b->rowsum, d.N); b->tend(te_); }
+                    bool hv = true;
+                    for (int k = g; k < g + n; ++k) hv = hv && b->hist_valid[k];
+                    cudaEvent_t te_ = b->tbegin(RMX_K_PAIRSUM);
+                    if (hv)     // hist = histograms of the current joint (update_p_cn made them for update_p_breakpoint)
+                        rmx_launch_pairsum_hist(b->stream, d, g, n, b->R, rowsof(b), b->hist, cached, used, b->rmd, b->rowsum, d.N);
+                    else
+                        rmx_launch_pairsum(b->stream, T, d, g, n, rowsof(b), used, cached, used, 1, b->rmd, b->brk_rows, b->R, 0,
+                                           b->ahat, b->bhat, b->fexp, b->rowsum, d.N);
+                    b->tend(te_);
                     rmx_launch_reduce_cols(b->stream, b->rowsum, b->R, 1, g, n, d.N, b->red_out + 8, RED);
                     b->count(2);
                 }

@@ -866,6 +866,28 @@ __device__ __forceinline__ double logT(const LogTCtx& c, const RmxDims& d, int i
     return 0.;
 }
 
+// ELBO term sum_ij joint[n,i,j] * (T_cached - T_used)[n,i,j] of the breakend rows from the histograms update_p_cn
+// already made: on a breakend row both transitions are -pen * (sum_m pd[m][d_m(i,j)] + flipc[i,j]) with the same
+// flipc, so the difference depends on the pair only through the clones' total-copy differences d_m, and
+//   sum_ij joint * (T_c - T_u) = -pen * sum_m sum_d hist[m][d] * (pd_c[m][d] - pd_u[m][d]).
+// 45 terms per row instead of two passes over S^2 pairs (k_pairsum).  One thread per (fit, breakend row).
+__global__ void k_pairsum_hist(RmxDims d, int g0, int R, const int* __restrict__ brk_rows, const int* __restrict__ tclass,
+                               const double* __restrict__ hist_all, const double* __restrict__ pd_c_all,
+                               const double* __restrict__ pd_u_all, int64_t fit_stride, double pen,
+                               double* __restrict__ rowsum_all, int64_t rowsum_fit_stride) {
+    const int g = RMX_FIT();
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    const int MD = d.M * d.D;
+    const double* h = hist_all + (int64_t)g * fit_stride + (int64_t)r * MD;
+    const double* pc = pd_c_all + (int64_t)g * fit_stride + (int64_t)r * MD;
+    const double* pu = pd_u_all + (int64_t)g * fit_stride + (int64_t)r * MD;
+    double acc = 0.;
+    if (tclass[brk_rows[r]] >= 0)            // a telomere row's transitions are identically zero
+        for (int e = 0; e < MD; ++e) acc += h[e] * (pc[e] - pu[e]);
+    rowsum_all[(int64_t)g * rowsum_fit_stride + r] = -pen * acc;
+}
+
 // rowsum[n] = sum_ij joint[n,i,j] * T_spec[n,i,j]; joint from (joint_sp, messages), T from t_sp.
 // rowlist != nullptr: only those rows (the breakend rows), rowsum indexed by position in the list, and the
 // value is sum joint * (T_tsp - T_t2sp) -- the only rows where cached and used transitions differ.
@@ -1416,6 +1438,14 @@ void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
     if (nrows <= 0 || gn <= 0) return;
     k_pairsum<<<dim3(nrows, gn), 256, pair_smem(d), st>>>(d, g0, rows, joint_sp, t_sp, t2_sp, diff, sp_fit_stride, rowlist,
                                                          T.tab, uniform, ahat, bhat, fexp, rowsum, rowsum_fit_stride);
+}
+
+void rmx_launch_pairsum_hist(cudaStream_t st, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
+                             const double* hist, const RmxTransSpec& cached, const RmxTransSpec& used,
+                             int64_t sp_fit_stride, double* rowsum, int64_t rowsum_fit_stride) {
+    if (R <= 0 || gn <= 0) return;
+    k_pairsum_hist<<<dim3((R + 127) / 128, gn), 128, 0, st>>>(d, g0, R, rows.brk_rows, rows.tclass, hist, cached.pd, used.pd,
+                                                             sp_fit_stride, cached.pen, rowsum, rowsum_fit_stride);
 }
 
 void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,

@@ -110,6 +110,10 @@ void rmx_launch_pairsum(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
                         const RmxTransSpec& joint_sp, const RmxTransSpec& t_sp, const RmxTransSpec& t2_sp, int diff,
                         int64_t sp_fit_stride, const int* rowlist, int nrows, int uniform, const double* ahat,
                         const double* bhat, const double* fexp, double* rowsum, int64_t rowsum_fit_stride);
+// the breakend rows' sum joint * (T_cached - T_used) from the histograms of the last update_p_cn (same transition model)
+void rmx_launch_pairsum_hist(cudaStream_t st, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
+                             const double* hist, const RmxTransSpec& cached, const RmxTransSpec& used,
+                             int64_t sp_fit_stride, double* rowsum, int64_t rowsum_fit_stride);
 void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
                         const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
                         double* lattice, int* path, int nclass);
