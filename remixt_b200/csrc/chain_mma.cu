@@ -54,6 +54,7 @@ __device__ __forceinline__ int cm_pos(int g, int i) { return ((i >> 2) << 5) + (
 // one CTA per SM, at most 8 warps: up to 232 registers per thread
 #define CM_NH 2     // column blocks (of 8 states) per warp
 #define CM_FST 4    // stages of the f ring (cp.async prefetch distance + 1)
+#define CM_RIMAX 8192   // chains up to this many rows keep their row descriptors in shared memory
 
 template <int KB>
 struct CmCfg {
@@ -85,6 +86,9 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
     // f ring: [CM_FST stages][CM_NH][2][T] doubles after the B-fragment slots; every thread copies its own entries
     // with cp.async several segments ahead (no registers held across the copy, no barrier: own slots only)
     double* fring = esm + (size_t)CM_NH * KSM * T;
+    double* fesm = fring + (size_t)CM_FST * CM_NH * 2 * T;        // [KB][T]: breakend rows' flip factors, own slots
+    const unsigned fesm_s = (unsigned)__cvta_generic_to_shared(fesm);
+    int* rism = reinterpret_cast<int*>(fesm + (size_t)KB * T - threadIdx.x);   // [CM_RIMAX] row info of the chain
 
     const int tile = blockIdx.x % A.ntiles;
     const int cd = blockIdx.x / A.ntiles;
@@ -156,9 +160,13 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
     for (int e = 0; e < CM_FST * CM_NH * 2; ++e) fring[e * T] = 0.;     // entries outside the state space stay zero
 #pragma unroll
     for (int k = 0; k < CM_FST - 1; ++k) f_issue(k);
-    if (nsteps > 0) ri0 = A.rinfo[row_of(0)];
-    if (nsteps > 1) ri1 = A.rinfo[row_of(1)];
+    const bool ri_sm = nsteps <= CM_RIMAX;
+    if (ri_sm)
+        for (int k = t; k < nsteps; k += T) rism[k] = A.rinfo[row_of(k)];
     __syncthreads();
+    auto ri_at = [&](int k) { return ri_sm ? rism[k] : A.rinfo[row_of(k)]; };
+    if (nsteps > 0) ri0 = ri_at(0);
+    if (nsteps > 1) ri1 = ri_at(1);
 
     double ereg[CM_NH][KREG];
     int cur_class = -1;
@@ -168,7 +176,7 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
         const int64_t on = (int64_t)seg_of(step) * S;
         const int ri = ri0;
         ri0 = ri1;
-        if (step + 2 < nsteps) ri1 = A.rinfo[row_of(step + 2)];
+        if (step + 2 < nsteps) ri1 = ri_at(step + 2);
         f_issue(step + CM_FST - 1);       // into the ring stage the previous step consumed
         const int cls = (ri & 0xff) - 1;
         const int br = (ri >> 12) - 1;
@@ -231,12 +239,23 @@ __global__ void __launch_bounds__(CmCfg<KB>::MAXT, 1) k_chain_mma(ChainMmaArgs A
 #pragma unroll
                 for (int g = 0; g < CM_GT; ++g) sum[g] = 0.;
                 if (jb < S) {
+                    // this thread's KB entries of the row's flip factor: one round trip (cp.async into own slots)
+                    // instead of KB dependent L2 loads
                     const double* FE = A.sp.flipE + (int64_t)cls * SS;
+#pragma unroll
+                    for (int kb = 0; kb < KB; ++kb) {
+                        const int i = kb * 4 + tig;
+                        if (i < S)
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(fesm_s + 8u * (unsigned)(kb * T)),
+                                         "l"(FE + (int64_t)i * S + jb) : "memory");
+                    }
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                    asm volatile("cp.async.wait_all;" ::: "memory");
 #pragma unroll 1
                     for (int kb = 0; kb < KB; ++kb) {
                         const int i = kb * 4 + tig;
                         if (i >= S) break;
-                        const double fe = FE[(int64_t)i * S + jb];
+                        const double fe = fesm[kb * T];
                         double v[CM_GT];
 #pragma unroll
                         for (int g = 0; g < CM_GT; ++g) v[g] = fe * uc[kb * 32 + g * 4 + tig];
@@ -340,7 +359,8 @@ static int launch_chain_mma_cfg(cudaStream_t st, ChainMmaArgs& A) {
     if (threads > CmCfg<KB>::MAXT || NW > CM_NWMAX || 4 * KB < d.S) return 2;
     size_t smem = sizeof(double) * ((size_t)2 * KB * 32 + (size_t)CM_GT * d.M * d.D + CM_GT * CM_NWMAX + CM_GT) +
                   sizeof(int) * 2 * CM_GT * CM_NWMAX + (size_t)d.S * d.M + 16;
-    smem = ((smem + 15) & ~(size_t)15) + sizeof(double) * ((size_t)CM_NH * CmCfg<KB>::KSM + (size_t)CM_FST * CM_NH * 2) * threads + 16;
+    smem = ((smem + 15) & ~(size_t)15) + sizeof(double) * ((size_t)CM_NH * CmCfg<KB>::KSM + (size_t)CM_FST * CM_NH * 2 + KB) * threads +
+           sizeof(int) * CM_RIMAX + 16;
     auto kern = k_chain_mma<KB>;
     if (smem > 48 * 1024) {
         if (smem > 227 * 1024) return 2;
