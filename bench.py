@@ -234,6 +234,7 @@ def build_batch(exp, inits, device):
 
 
 LLTABLE_CONVENTION_OPS = 900.
+NCU_DRAM_BYTES_PER_UNIT = {'chain': 29.0, 'lltable': 48.8, 'round': 89.1}
 
 
 # algorithmic work per (segment, state) of each kernel class: (bound, bytes, fp64 ops)  -- DESIGN.md, Kernels
@@ -375,6 +376,11 @@ def gpu_arm(args):
                     'frac': de['fp64_frac'], 'traffic': None,
                     'peak_source': 'FP64 FMA micro-benchmark run in this process (rmx_fp64_peak); not in MEASURED_PEAKS.json',
                     'hbm_achieved_gbs': de['gbs'], 'hbm_peak_gbs': hbm_peak, 'hbm_frac': de['hbm_frac']}
+    # DRAM bytes per launch of the dominant kernel from its `ncu --set full` capture (dram__bytes_read.sum +
+    # dram__bytes_write.sum of an 8-fit launch, profiles/r01_summary.md), carried per (segment, state) unit
+    if dom in NCU_DRAM_BYTES_PER_UNIT:
+        roofline['traffic'] = NCU_DRAM_BYTES_PER_UNIT[dom] * float(N1) * S * G
+        roofline['traffic_source'] = 'ncu capture of an 8-fit launch, %.1f B per (segment, state)' % NCU_DRAM_BYTES_PER_UNIT[dom]
     roofline['launch_ms'] = de['ms_per_launch']
     roofline['share_of_step'] = de['ms_per_launch'] * de['launches'] / ms
     line = {
