@@ -27,7 +27,18 @@ def _now():
     return datetime.datetime.now().time().isoformat()
 
 
+_STATE_TABLES = {}     # the enumerations below are pure functions of small integers; every fit of a grid asks again
+
+
 def create_cn_states(num_clones, num_alleles, cn_max, cn_diff_max):
+    """Allele specific copy number states of one segment, ``(S, M, 2)`` (``cn_model.py:228-253``), memoised."""
+    key = ('cn', int(num_clones), int(num_alleles), int(cn_max), int(cn_diff_max))
+    if key not in _STATE_TABLES:
+        _STATE_TABLES[key] = _create_cn_states(num_clones, num_alleles, cn_max, cn_diff_max)
+    return _STATE_TABLES[key].copy()
+
+
+def _create_cn_states(num_clones, num_alleles, cn_max, cn_diff_max):
     """Allele specific copy number states of one segment, ``(S, M, 2)`` (``cn_model.py:228-253``).
 
     Order and representatives follow the reference exactly: candidates are visited in
@@ -49,6 +60,14 @@ def create_cn_states(num_clones, num_alleles, cn_max, cn_diff_max):
 
 
 def create_brk_states(num_clones, cn_max, cn_diff_max):
+    """Breakpoint copy number states, ``(B, M)`` with clone 0 fixed at 0 (``cn_model.py:255-276``), memoised."""
+    key = ('brk', int(num_clones), int(cn_max), int(cn_diff_max))
+    if key not in _STATE_TABLES:
+        _STATE_TABLES[key] = _create_brk_states(num_clones, cn_max, cn_diff_max)
+    return _STATE_TABLES[key].copy()
+
+
+def _create_brk_states(num_clones, cn_max, cn_diff_max):
     """Breakpoint copy number states, ``(B, M)`` with clone 0 fixed at 0 (``cn_model.py:255-276``)."""
     states = []
     for combo in itertools.product(range(cn_max + 1), repeat=num_clones - 1):
@@ -140,12 +159,21 @@ class BreakpointModel(object):
             self._build_segmentation(x, l, adjacencies)
 
         # likelihood masks for poorly modelled segments (cn_model.py:169-184)
-        long_enough = self.l1 >= self.min_segment_length
-        genotyped = self.x1[:, :2].sum(axis=1).astype(float) / (self.x1[:, 2].astype(float) + 1e-16)
-        depth = self.x1[:, 2].astype(float) / (self.l1.astype(float) + 1e-16)
+        # everything but the depth cut depends on the segmentation and two thresholds only: the fits of an
+        # initialisation grid (which differ in max_depth) take it from the donor
+        key = (float(self.min_segment_length), float(self.min_proportion_genotyped))
+        cached = getattr(donor, '_mask_inputs', None) if donor is not None and donor.N1 == self.N1 else None
+        if cached is not None and cached[0] == key:
+            _, long_enough, genotyped_ok, depth = cached
+        else:
+            long_enough = self.l1 >= self.min_segment_length
+            genotyped = self.x1[:, :2].sum(axis=1).astype(float) / (self.x1[:, 2].astype(float) + 1e-16)
+            depth = self.x1[:, 2].astype(float) / (self.l1.astype(float) + 1e-16)
+            genotyped_ok = genotyped >= self.min_proportion_genotyped
+        self._mask_inputs = (key, long_enough, genotyped_ok, depth)
         not_amplified = depth <= self.max_depth
         self._total_likelihood_mask = long_enough & not_amplified
-        self._allele_likelihood_mask = long_enough & (genotyped >= self.min_proportion_genotyped) & not_amplified
+        self._allele_likelihood_mask = long_enough & genotyped_ok & not_amplified
 
         if self.disable_breakpoints:
             for f in ('num_breakpoints', 'breakpoint_idx', 'breakpoint_orient'):

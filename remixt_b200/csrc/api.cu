@@ -80,6 +80,35 @@ struct DevPool {
     }
 };
 static DevPool g_pool;
+
+// the same for the batch's pinned staging buffers (page-locking a few MB costs milliseconds and is erratic)
+struct PinnedPool {
+    std::mutex mu;
+    std::multimap<size_t, void*> free_blocks;
+    cudaError_t get(size_t bytes, void** p) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            auto it = free_blocks.find(bytes);
+            if (it != free_blocks.end()) {
+                *p = it->second;
+                free_blocks.erase(it);
+                memset(*p, 0, bytes);
+                return cudaSuccess;
+            }
+        }
+        return cudaMallocHost(p, bytes);
+    }
+    void put(size_t bytes, void* p) {
+        std::lock_guard<std::mutex> lk(mu);
+        free_blocks.insert({bytes, p});
+    }
+    void release() {
+        std::lock_guard<std::mutex> lk(mu);
+        for (auto& kv : free_blocks) cudaFreeHost(kv.second);
+        free_blocks.clear();
+    }
+};
+static PinnedPool g_pinned;
 static std::atomic<int64_t> g_launches{0};
 
 struct ClassMats {
@@ -148,6 +177,7 @@ struct Batch {
     int* hflags = nullptr;      // 1 int
     int* hrows = nullptr;       // G*N ints
     int* hRn = nullptr;         // G ints
+    size_t hp_bytes = 0, hrows_bytes = 0, hRn_bytes = 0;
 
     // per-kernel-class timing (CUDA events on the stream around each launch, when enabled)
     bool timing = false;
@@ -175,10 +205,10 @@ struct Batch {
         if (stream) cudaStreamSynchronize(stream);
         for (auto& t : tev) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
         for (auto& p : allocs) g_pool.put(device, p.second, p.first);
-        if (hp) cudaFreeHost(hp);
-        if (hflags) cudaFreeHost(hflags);
-        if (hrows) cudaFreeHost(hrows);
-        if (hRn) cudaFreeHost(hRn);
+        if (hp) g_pinned.put(hp_bytes, hp);
+        if (hflags) g_pinned.put(sizeof(int), hflags);
+        if (hrows) g_pinned.put(hrows_bytes, hrows);
+        if (hRn) g_pinned.put(hRn_bytes, hRn);
         if (stream) cudaStreamDestroy(stream);
     }
     void count(int k = 1) {
@@ -540,6 +570,7 @@ int rmx_device_count(int* count) {
 
 int rmx_release_cached_memory(int device) {
     g_pool.release(device);
+    if (device < 0) g_pinned.release();
     return RMX_OK;
 }
 
@@ -885,10 +916,13 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->d_Rn, (size_t)G));
     CCK(dalloc(b, &b->dflags, 1));
     CCK(cudaMemset(b->dflags, 0, sizeof(int)));
-    CCK(cudaMallocHost((void**)&b->hp, (size_t)G * Batch::RED * sizeof(double)));
-    CCK(cudaMallocHost((void**)&b->hflags, sizeof(int)));
-    CCK(cudaMallocHost((void**)&b->hrows, GN * sizeof(int)));
-    CCK(cudaMallocHost((void**)&b->hRn, (size_t)G * sizeof(int)));
+    b->hp_bytes = (size_t)G * Batch::RED * sizeof(double);
+    b->hrows_bytes = GN * sizeof(int);
+    b->hRn_bytes = (size_t)G * sizeof(int);
+    CCK(g_pinned.get(b->hp_bytes, (void**)&b->hp));
+    CCK(g_pinned.get(sizeof(int), (void**)&b->hflags));
+    CCK(g_pinned.get(b->hrows_bytes, (void**)&b->hrows));
+    CCK(g_pinned.get(b->hRn_bytes, (void**)&b->hRn));
     *b->hflags = 0;
 
     {   // initial factors (bpmodel.pyx:546-584), the same for every fit, filled on the device

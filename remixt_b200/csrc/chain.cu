@@ -19,6 +19,7 @@
 // E (it depends on the state table and the penalty only), so one CTA advances GT fits in lock step and
 // each E entry loaded into a register is used GT times per step.  Chromosomes are coupled only through
 // telomere rows whose log_transmat is identically zero, so chains are exactly independent.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -1016,11 +1017,29 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
             double vmax = -INFINITY;
             const double fn = jj == t ? fn0 : F[(int64_t)n * S + jj];
             if (Ts) {
-#pragma unroll 8
-                for (int i = 0; i < S; ++i) {
-                    double v = __dadd_rn(prev[i], Ts[i * S + jj]);
-                    if (v > vmax) vmax = v;
+                // four independent running maxima (the value of a maximum does not depend on the order; ties only
+                // matter in the traceback): the compare-select chain was the per-segment latency
+                double m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+                int i = 0;
+#pragma unroll 2
+                for (; i + 4 <= S; i += 4) {
+                    const double v0 = __dadd_rn(prev[i], Ts[i * S + jj]);
+                    const double v1 = __dadd_rn(prev[i + 1], Ts[(i + 1) * S + jj]);
+                    const double v2 = __dadd_rn(prev[i + 2], Ts[(i + 2) * S + jj]);
+                    const double v3 = __dadd_rn(prev[i + 3], Ts[(i + 3) * S + jj]);
+                    if (v0 > m0) m0 = v0;
+                    if (v1 > m1) m1 = v1;
+                    if (v2 > m2) m2 = v2;
+                    if (v3 > m3) m3 = v3;
                 }
+                for (; i < S; ++i) {
+                    const double v = __dadd_rn(prev[i], Ts[i * S + jj]);
+                    if (v > m0) m0 = v;
+                }
+                if (m1 > m0) m0 = m1;
+                if (m3 > m2) m2 = m3;
+                if (m2 > m0) m0 = m2;
+                vmax = m0;
             } else if (lt.kind == 0) {
                 for (int i = 0; i < S; ++i)
                     if (prev[i] > vmax) vmax = prev[i];
@@ -1456,6 +1475,10 @@ void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
     if (tpf > 1024) tpf = 1024;
     int fpc = 1024 / tpf;                 // fits per CTA: they share the staged class matrices
     if (fpc > 4) fpc = 4;
+    {
+        static const char* env = getenv("RMX_VITERBI_FPC");     // A/B measurements only
+        if (env && atoi(env) >= 1 && atoi(env) < fpc) fpc = atoi(env);
+    }
     if (fpc > gn) fpc = gn;
     // class matrices of the plain rows in shared memory, as many as fit (class ids are dense from 0)
     int staged = 0;
