@@ -143,6 +143,7 @@ struct Batch {
     double *l = nullptr, *x = nullptr, *y0 = nullptr, *y1 = nullptr;
     int *bidx = nullptr, *borient = nullptr, *tclass = nullptr, *brow = nullptr, *brk_rows = nullptr, *rinfo = nullptr;
     int *krow_ptr = nullptr, *krow_idx = nullptr, *ch_start = nullptr, *ch_end = nullptr, *ch_order = nullptr;
+    int *ch_bin_ptr = nullptr, *ch_bin_idx = nullptr, NB = 0;
     int NC = 0, C = 0, R = 0;
     // likelihood-table fast path: normal-copy kinds, wide log table, per-(fit, kind, state) table
     uint8_t *nkind = nullptr, *sflag = nullptr;
@@ -270,6 +271,7 @@ static RmxRows rowsof(const Batch* b) {
 static RmxChains chainsof(const Batch* b) {
     RmxChains c;
     c.start = b->ch_start; c.end = b->ch_end; c.order = b->ch_order; c.NC = b->NC;
+    c.bin_ptr = b->ch_bin_ptr; c.bin_idx = b->ch_bin_idx; c.NB = b->NB;
     return c;
 }
 
@@ -772,6 +774,36 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     std::stable_sort(ch_order.begin(), ch_order.end(), [&](int a2, int b2) {
         return (ch_end[a2] - ch_start[a2]) > (ch_end[b2] - ch_start[b2]);
     });
+    // bins of about equal total length for the Viterbi kernel: as many as the longest chain allows, filled longest
+    // chain first into the currently shortest bin
+    std::vector<int> bin_ptr, bin_idx;
+    {
+        int64_t total = 0, longest = 1;
+        for (int c = 0; c < b->NC; ++c) {
+            const int64_t len = ch_end[c] - ch_start[c] + 1;
+            total += len;
+            if (len > longest) longest = len;
+        }
+        int nb = (int)(total / longest);
+        if (nb < 1) nb = 1;
+        if (nb > b->NC) nb = b->NC;
+        std::vector<int64_t> load(nb, 0);
+        std::vector<std::vector<int>> members(nb);
+        for (int c : ch_order) {
+            int best = 0;
+            for (int q = 1; q < nb; ++q)
+                if (load[q] < load[best]) best = q;
+            load[best] += ch_end[c] - ch_start[c] + 1;
+            members[best].push_back(c);
+        }
+        bin_ptr.push_back(0);
+        for (int q = 0; q < nb; ++q) {
+            if (members[q].empty()) continue;
+            bin_idx.insert(bin_idx.end(), members[q].begin(), members[q].end());
+            bin_ptr.push_back((int)bin_idx.size());
+        }
+        b->NB = (int)bin_ptr.size() - 1;
+    }
     // breakpoint -> its breakend rows, ascending n (the order bpmodel.pyx:971-980 visits them)
     std::vector<int> krow_ptr(K + 1, 0), krow_idx(b->R);
     for (int r = 0; r < b->R; ++r) krow_ptr[bidx[brk_rows[r]] + 1]++;
@@ -810,6 +842,8 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(upload(b, &b->ch_start, ch_start));
     CCK(upload(b, &b->ch_end, ch_end));
     CCK(upload(b, &b->ch_order, ch_order));
+    CCK(upload(b, &b->ch_bin_ptr, bin_ptr));
+    CCK(upload(b, &b->ch_bin_idx, bin_idx));
 
     // ---- per-fit parameters (bpmodel.pyx:573-597)
     b->P.resize(G);

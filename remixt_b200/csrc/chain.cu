@@ -960,26 +960,58 @@ __device__ __forceinline__ void logT_from(LogTCtx& c, const RmxDims& d, const Rm
     }
 }
 
-// One CTA decodes chain blockIdx.x of `fpc` fits: the fits share the class transition matrices staged in shared
-// memory (classes 0 .. staged-1), each fit has its own group of blockDim.x / fpc threads (thread per state) and its
-// own named barrier, so the groups advance independently.  Row descriptors and the next frame row are loaded one
-// segment ahead; the traceback is done by the first warp of each group without block barriers.
+// One column of a lattice row on the general path (telomere rows, breakend rows, classes that are not staged).
+__device__ __noinline__ double vit_column_general(RmxDims d, RmxTransSpec sp, const int8_t* tots, int cls, int br, int dd0,
+                                                  const double* pc, int jj) {
+    LogTCtx lt;
+    logT_from(lt, d, sp, tots, cls, br, dd0);
+    double vmax = -INFINITY;
+    if (lt.kind == 0) {
+        for (int i = 0; i < d.S; ++i)
+            if (pc[i] > vmax) vmax = pc[i];
+    } else {
+        for (int i = 0; i < d.S; ++i) {
+            double v = __dadd_rn(pc[i], logT(lt, d, i, jj));
+            if (v > vmax) vmax = v;
+        }
+    }
+    return vmax;
+}
+
+// One CTA decodes the chains of bin blockIdx.x (bins of about equal total length, RmxChains::bin_*) of `fpc` fits:
+// the fits share the class transition matrices staged in shared memory (classes 0 .. staged-1), each fit has its own
+// group of blockDim.x / fpc threads (thread per state) and its own named barrier, so the groups advance
+// independently.  The staged matrices are stored transposed, one row per destination state with a row stride
+// SP = roundup(S, 8) + 2 doubles (SP / 2 odd: the 16-byte loads of a quarter warp fall in distinct bank groups); a
+// thread walks its row and the lattice row with 128-bit loads, eight pairs per iteration into four independent
+// running maxima.  Pad entries are -inf in the lattice row and 0 in the matrix, so they never win.  The lattice row
+// is double buffered: one barrier per segment.  Row descriptors and the next frame value are loaded one segment
+// ahead; the traceback is done by the first warp of each group without block barriers.
 __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, RmxChains ch, RmxRows rows, RmxTransSpec sp,
                                                   int64_t sp_fit_stride, const int8_t* __restrict__ tab,
                                                   const double* __restrict__ F_all, double* __restrict__ lattice_all,
                                                   int* __restrict__ path_all, int staged, int fpc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int S = d.S, M = d.M;
+    const int SL = (S + 7) & ~7, SP = SL + 2;
     const int tpf = blockDim.x / fpc;                     // threads per fit, a multiple of 32
     const int grp = threadIdx.x / tpf, t = threadIdx.x - grp * tpf;
-    double* prev_all = reinterpret_cast<double*>(smem_raw);                      // [fpc][S]
-    double* Tsm = prev_all + (size_t)fpc * S;                                   // [staged][S*S]
-    int8_t* tots = reinterpret_cast<int8_t*>(Tsm + (size_t)staged * S * S);     // [S*M]
+    double* prev_all = reinterpret_cast<double*>(smem_raw);                      // [fpc][2][SP]
+    double* Tsm = prev_all + (size_t)fpc * 2 * SP;                              // [staged][S][SP], transposed
+    int8_t* tots = reinterpret_cast<int8_t*>(Tsm + (size_t)staged * S * SP);    // [S*M]
     for (int e = threadIdx.x; e < S * M; e += blockDim.x) {
         int s = e / M, m = e - s * M;
         tots[e] = (m == 0) ? 0 : (int8_t)(tab[(s * M + m) * 2] + tab[(s * M + m) * 2 + 1]);
     }
-    for (int e = threadIdx.x; e < staged * S * S; e += blockDim.x) Tsm[e] = sp.Tmat[e];
+    for (int e = threadIdx.x; e < staged * S * S; e += blockDim.x) {
+        const int c = e / (S * S), r = e - c * S * S, i = r / S, j = r - i * S;
+        Tsm[((size_t)c * S + j) * SP + i] = sp.Tmat[e];
+    }
+    for (int e = threadIdx.x; e < staged * S * (SP - S); e += blockDim.x) {
+        const int row = e / (SP - S), i = S + (e - row * (SP - S));
+        Tsm[(size_t)row * SP + i] = 0.;
+    }
+    for (int e = threadIdx.x; e < fpc * 2 * SP; e += blockDim.x) prev_all[e] = -INFINITY;
     __syncthreads();
     const int lf = (int)blockIdx.y * fpc + grp;           // fit within the launched range
     if (lf >= gn) return;
@@ -989,81 +1021,81 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
     int* path = path_all + (int64_t)g * d.N;
     sp.pd += (int64_t)g * sp_fit_stride;
     sp.wexp += (int64_t)g * sp_fit_stride;
-    double* prev = prev_all + (size_t)grp * S;
-    const int chain = blockIdx.x;
-    const int s0 = ch.start[chain], s1 = ch.end[chain];
+    double* prev = prev_all + (size_t)grp * 2 * SP;
+    const int c_lo = ch.bin_ptr[blockIdx.x], c_hi = ch.bin_ptr[blockIdx.x + 1];
 #define VIT_BAR() asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(tpf) : "memory")
-    for (int jj = t; jj < S; jj += tpf) {
-        double v = F[(int64_t)s0 * S + jj];
-        lattice[(int64_t)s0 * S + jj] = v;
-        prev[jj] = v;
-    }
-    VIT_BAR();
-    // row n-1 -> n; descriptors of the next row and the next frame value (first column) one segment ahead
-    int cls = s0 < s1 ? rows.tclass[s0] : -1, br = s0 < s1 ? rows.brow[s0] : -1, dd0 = s0 < s1 ? rows.d0[s0] : 0;
-    double fcur = (s0 < s1 && t < S) ? F[(int64_t)(s0 + 1) * S + t] : 0.;
-    for (int n = s0 + 1; n <= s1; ++n) {
-        LogTCtx lt;
-        logT_from(lt, d, sp, tots, cls, br, dd0);
-        const double* Ts = (lt.kind == 1 && cls < staged) ? Tsm + (size_t)cls * S * S : nullptr;
-        const double fn0 = fcur;
-        if (n < s1) {
-            cls = rows.tclass[n]; br = rows.brow[n]; dd0 = rows.d0[n];
-            if (t < S) fcur = F[(int64_t)(n + 1) * S + t];
-        }
-        double out[4];   // up to 4 columns per thread
-        int cnt = 0;
+    int cur = 0;
+    for (int ci = c_lo; ci < c_hi; ++ci) {
+        const int chain = ch.bin_idx[ci];
+        const int s0 = ch.start[chain], s1 = ch.end[chain];
         for (int jj = t; jj < S; jj += tpf) {
-            double vmax = -INFINITY;
-            const double fn = jj == t ? fn0 : F[(int64_t)n * S + jj];
-            if (Ts) {
-                // four independent running maxima (the value of a maximum does not depend on the order; ties only
-                // matter in the traceback): the compare-select chain was the per-segment latency
-                double m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-                int i = 0;
-#pragma unroll 2
-                for (; i + 4 <= S; i += 4) {
-                    const double v0 = __dadd_rn(prev[i], Ts[i * S + jj]);
-                    const double v1 = __dadd_rn(prev[i + 1], Ts[(i + 1) * S + jj]);
-                    const double v2 = __dadd_rn(prev[i + 2], Ts[(i + 2) * S + jj]);
-                    const double v3 = __dadd_rn(prev[i + 3], Ts[(i + 3) * S + jj]);
-                    if (v0 > m0) m0 = v0;
-                    if (v1 > m1) m1 = v1;
-                    if (v2 > m2) m2 = v2;
-                    if (v3 > m3) m3 = v3;
+            double v = F[(int64_t)s0 * S + jj];
+            lattice[(int64_t)s0 * S + jj] = v;
+            prev[cur * SP + jj] = v;
+        }
+        VIT_BAR();
+        // row n-1 -> n; descriptors of the next row and the next frame value (first column) one segment ahead
+        int cls = s0 < s1 ? rows.tclass[s0] : -1, br = s0 < s1 ? rows.brow[s0] : -1, dd0 = s0 < s1 ? rows.d0[s0] : 0;
+        const double* Fp = F + (int64_t)(s0 + 1) * S + t;       // this thread's first column of row n
+        double* Lp = lattice + (int64_t)(s0 + 1) * S + t;
+        double fcur = (s0 < s1 && t < S) ? *Fp : 0.;
+        for (int n = s0 + 1; n <= s1; ++n, Fp += S, Lp += S) {
+            const double* pc = prev + cur * SP;
+            double* pn = prev + (cur ^ 1) * SP;
+            const bool fast = cls >= 0 && br < 0 && cls < staged;
+            const int cls0 = cls, br0 = br, dd00 = dd0;
+            const double fn0 = fcur;
+            if (n < s1) {
+                cls = rows.tclass[n]; br = rows.brow[n]; dd0 = rows.d0[n];
+                if (t < S) fcur = Fp[S];
+            }
+            if (fast) {
+                if (t < S) {            // staged classes have S <= tpf: one column per thread
+                    // the value of a maximum does not depend on the order (ties only matter in the traceback)
+                    const double2* pv = reinterpret_cast<const double2*>(pc);
+                    const double2* tv = reinterpret_cast<const double2*>(Tsm + ((size_t)cls0 * S + t) * SP);
+                    const double2* pe = pv + SL / 2;
+                    double m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll 1
+                    for (; pv < pe; pv += 4, tv += 4) {
+                        const double2 p0 = pv[0], p1 = pv[1], p2 = pv[2], p3 = pv[3];
+                        const double2 t0 = tv[0], t1 = tv[1], t2 = tv[2], t3 = tv[3];
+                        double v;
+                        v = __dadd_rn(p0.x, t0.x); if (v > m0) m0 = v;
+                        v = __dadd_rn(p0.y, t0.y); if (v > m1) m1 = v;
+                        v = __dadd_rn(p1.x, t1.x); if (v > m2) m2 = v;
+                        v = __dadd_rn(p1.y, t1.y); if (v > m3) m3 = v;
+                        v = __dadd_rn(p2.x, t2.x); if (v > m0) m0 = v;
+                        v = __dadd_rn(p2.y, t2.y); if (v > m1) m1 = v;
+                        v = __dadd_rn(p3.x, t3.x); if (v > m2) m2 = v;
+                        v = __dadd_rn(p3.y, t3.y); if (v > m3) m3 = v;
+                    }
+                    if (m1 > m0) m0 = m1;
+                    if (m3 > m2) m2 = m3;
+                    if (m2 > m0) m0 = m2;
+                    const double o = __dadd_rn(m0, fn0);
+                    pn[t] = o;
+                    *Lp = o;
                 }
-                for (; i < S; ++i) {
-                    const double v = __dadd_rn(prev[i], Ts[i * S + jj]);
-                    if (v > m0) m0 = v;
-                }
-                if (m1 > m0) m0 = m1;
-                if (m3 > m2) m2 = m3;
-                if (m2 > m0) m0 = m2;
-                vmax = m0;
-            } else if (lt.kind == 0) {
-                for (int i = 0; i < S; ++i)
-                    if (prev[i] > vmax) vmax = prev[i];
             } else {
-                for (int i = 0; i < S; ++i) {
-                    double v = __dadd_rn(prev[i], logT(lt, d, i, jj));
-                    if (v > vmax) vmax = v;
+                for (int jj = t; jj < S; jj += tpf) {
+                    const double fn = jj == t ? fn0 : F[(int64_t)n * S + jj];
+                    const double o = __dadd_rn(vit_column_general(d, sp, tots, cls0, br0, dd00, pc, jj), fn);
+                    pn[jj] = o;
+                    lattice[(int64_t)n * S + jj] = o;
                 }
             }
-            out[cnt++] = __dadd_rn(vmax, fn);
+            VIT_BAR();
+            cur ^= 1;
         }
-        VIT_BAR();
-        cnt = 0;
-        for (int jj = t; jj < S; jj += tpf) {
-            prev[jj] = out[cnt];
-            lattice[(int64_t)n * S + jj] = out[cnt];
-            ++cnt;
-        }
-        VIT_BAR();
     }
 #undef VIT_BAR
     // traceback by the group's first warp: no barriers on the sequential path; the lattice row and the row
     // descriptors of the next step are loaded before the current step's reduction
-    if (t < 32) {
+    if (t >= 32) return;
+    for (int ci = c_lo; ci < c_hi; ++ci) {
+        const int chain = ch.bin_idx[ci];
+        const int s0 = ch.start[chain], s1 = ch.end[chain];
         constexpr int KP = 4;                 // rows of up to 128 states are prefetched in registers
         const bool pre = S <= 32 * KP;
         int nxt = 0;
@@ -1078,12 +1110,12 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
             LogTCtx lt;
             const double* Ts = nullptr;
             lt.kind = 0;
-            double cur[KP];
+            double cur_row[KP];
 #pragma unroll
-            for (int k = 0; k < KP; ++k) cur[k] = lv[k];
+            for (int k = 0; k < KP; ++k) cur_row[k] = lv[k];
             if (n < s1) {
                 logT_from(lt, d, sp, tots, pc, pb, pd0);
-                if (lt.kind == 1 && pc < staged) Ts = Tsm + (size_t)pc * S * S;
+                if (lt.kind == 1 && pc < staged) Ts = Tsm + ((size_t)pc * S + nxt) * SP;
             }
             int nc = -1, nb = -1, nd0 = 0;
             if (n > s0) {       // the next step's inputs, in flight during this step's reduction
@@ -1100,9 +1132,9 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
                 for (int k = 0; k < KP; ++k) {
                     const int i = t + 32 * k;
                     if (i < S) {
-                        double v = cur[k];
+                        double v = cur_row[k];
                         if (n < s1) {
-                            if (Ts) v = __dadd_rn(v, Ts[i * S + nxt]);
+                            if (Ts) v = __dadd_rn(v, Ts[i]);
                             else v = __dadd_rn(v, logT(lt, d, i, nxt));
                         }
                         if (v > bv) { bv = v; bi = i; }   // ascending i per lane: first max kept
@@ -1112,7 +1144,7 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
                 for (int i = t; i < S; i += 32) {
                     double v = lattice[(int64_t)n * S + i];
                     if (n < s1) {
-                        if (Ts) v = __dadd_rn(v, Ts[i * S + nxt]);
+                        if (Ts) v = __dadd_rn(v, Ts[i]);
                         else v = __dadd_rn(v, logT(lt, d, i, nxt));
                     }
                     if (v > bv) { bv = v; bi = i; }
@@ -1482,14 +1514,15 @@ void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
     if (fpc > gn) fpc = gn;
     // class matrices of the plain rows in shared memory, as many as fit (class ids are dense from 0)
     int staged = 0;
-    while (staged < nclass && sizeof(double) * (size_t)(staged + 1) * d.S * d.S <= 160 * 1024) ++staged;
-    size_t smem = sizeof(double) * ((size_t)fpc * d.S + (size_t)staged * d.S * d.S) + (size_t)d.S * d.M + 16;
+    const size_t SP = (size_t)((d.S + 7) & ~7) + 2;       // padded row of a transposed class matrix (see k_viterbi)
+    while (staged < nclass && sizeof(double) * (size_t)(staged + 1) * d.S * SP <= 176 * 1024) ++staged;
+    size_t smem = sizeof(double) * ((size_t)fpc * 2 * SP + (size_t)staged * d.S * SP) + (size_t)d.S * d.M + 16;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(k_viterbi, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k_viterbi, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
         attr_set = true;
     }
-    k_viterbi<<<dim3(ch.NC, (gn + fpc - 1) / fpc), tpf * fpc, smem, st>>>(d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F,
+    k_viterbi<<<dim3(ch.NB, (gn + fpc - 1) / fpc), tpf * fpc, smem, st>>>(d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F,
                                                                           lattice, path, staged, fpc);
 }
 

@@ -32,6 +32,11 @@ struct RmxChains {
     const int* end;       // (NC) last segment of chain c (inclusive)
     const int* order;     // (NC) chain ids, longest chain first (launch order of the chain kernel)
     int NC;
+    // the chains packed into NB bins of about equal total length (longest-first greedy), the unit of work of the
+    // Viterbi kernel: bin b holds the chains bin_idx[bin_ptr[b] .. bin_ptr[b+1])
+    const int* bin_ptr;
+    const int* bin_idx;
+    int NB;
 };
 
 // ---- likelihood.cu   (every launcher covers the fits [g0, g0+gn) of a batch; P is the per-fit parameter array)

@@ -41,6 +41,8 @@ for rep in range(2):
     cn = np.zeros((G, batch.num_segments, batch.num_clones, 2), dtype=np.int64)
     batch.infer_cn(cn)
     t = tick('infer_cn', t)
+    batch.infer_cn(cn)
+    t = tick('infer_cn (output pages resident)', t)
     out = (batch.p_outlier_total, batch.p_outlier_allele, batch.h)
     t = tick('read q', t)
     del batch
