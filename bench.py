@@ -315,6 +315,7 @@ def gpu_arm(args):
         cn = np.zeros((G, b2.num_segments, b2.num_clones, 2), dtype=np.int64)
         b2.infer_cn(cn)
         out = (elbo, cn, b2.p_outlier_total, b2.p_outlier_allele, b2.h)
+        b2.close()      # device blocks back to the pool now: the next step's batch reuses them
         return sum(int(np.asarray(o).nbytes) for o in out)
 
     del state['elbo']

@@ -188,13 +188,22 @@ class _ModelBase(object):
         self._handle = handle
         self._derived = {}
 
-    def __del__(self):
+    def close(self):
+        """Releases the device state now (its blocks go back to the pool) instead of when the object is collected;
+        the per-fit views of a batch hold a reference cycle with it, so collection can be late."""
+        for view in list(getattr(self, '_views', {}).values()):
+            view.close()
+        if getattr(self, '_views', None):
+            self._views.clear()
         h, self._handle = self._handle, None
         if h is not None and lib is not None:
             try:
                 lib.rmx_destroy(h)
             except Exception:
                 pass
+
+    def __del__(self):
+        self.close()
 
     # ------------------------------------------------------------------ attribute plumbing
     def _out(self, a):

@@ -978,26 +978,28 @@ __device__ __noinline__ double vit_column_general(RmxDims d, RmxTransSpec sp, co
     return vmax;
 }
 
-// One CTA decodes the chains of bin blockIdx.x (bins of about equal total length, RmxChains::bin_*) of `fpc` fits:
-// the fits share the class transition matrices staged in shared memory (classes 0 .. staged-1), each fit has its own
-// group of blockDim.x / fpc threads (thread per state) and its own named barrier, so the groups advance
+// One CTA decodes the chains of bin blockIdx.x (bins of about equal total length, RmxChains::bin_*) of `fpc` groups
+// of FR fits: the groups share the class transition matrices staged in shared memory (classes 0 .. staged-1), each
+// group has blockDim.x / fpc threads (thread per state) and its own named barrier, so the groups advance
 // independently.  The staged matrices are stored transposed, one row per destination state with a row stride
 // SP = roundup(S, 8) + 2 doubles (SP / 2 odd: the 16-byte loads of a quarter warp fall in distinct bank groups); a
-// thread walks its row and the lattice row with 128-bit loads, eight pairs per iteration into four independent
-// running maxima.  Pad entries are -inf in the lattice row and 0 in the matrix, so they never win.  The lattice row
-// is double buffered: one barrier per segment.  Row descriptors and the next frame value are loaded one segment
-// ahead; the traceback is done by the first warp of each group without block barriers.
-__global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, RmxChains ch, RmxRows rows, RmxTransSpec sp,
+// thread walks its row with 128-bit loads and uses each matrix value for the lattice rows of its FR fits (the matrix
+// stream is the shared-memory traffic of this kernel: FR = 2 halves it), eight pairs per fit and iteration into four
+// independent running maxima.  Pad entries are -inf in the lattice row and 0 in the matrix, so they never win.  The
+// lattice rows are double buffered: one barrier per segment.  Row descriptors and the next frame values are loaded
+// one segment ahead; the traceback of fit f is done by warp f of the group without block barriers.
+template <int FR, int MAXT>
+__global__ void __launch_bounds__(MAXT) k_viterbi(RmxDims d, int g0, int gn, RmxChains ch, RmxRows rows, RmxTransSpec sp,
                                                   int64_t sp_fit_stride, const int8_t* __restrict__ tab,
                                                   const double* __restrict__ F_all, double* __restrict__ lattice_all,
                                                   int* __restrict__ path_all, int staged, int fpc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int S = d.S, M = d.M;
     const int SL = (S + 7) & ~7, SP = SL + 2;
-    const int tpf = blockDim.x / fpc;                     // threads per fit, a multiple of 32
+    const int tpf = blockDim.x / fpc;                     // threads per group, a multiple of 32
     const int grp = threadIdx.x / tpf, t = threadIdx.x - grp * tpf;
-    double* prev_all = reinterpret_cast<double*>(smem_raw);                      // [fpc][2][SP]
-    double* Tsm = prev_all + (size_t)fpc * 2 * SP;                              // [staged][S][SP], transposed
+    double* prev_all = reinterpret_cast<double*>(smem_raw);                      // [fpc][FR][2][SP]
+    double* Tsm = prev_all + (size_t)fpc * FR * 2 * SP;                         // [staged][S][SP], transposed
     int8_t* tots = reinterpret_cast<int8_t*>(Tsm + (size_t)staged * S * SP);    // [S*M]
     for (int e = threadIdx.x; e < S * M; e += blockDim.x) {
         int s = e / M, m = e - s * M;
@@ -1011,78 +1013,110 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
         const int row = e / (SP - S), i = S + (e - row * (SP - S));
         Tsm[(size_t)row * SP + i] = 0.;
     }
-    for (int e = threadIdx.x; e < fpc * 2 * SP; e += blockDim.x) prev_all[e] = -INFINITY;
+    for (int e = threadIdx.x; e < fpc * FR * 2 * SP; e += blockDim.x) prev_all[e] = -INFINITY;
     __syncthreads();
-    const int lf = (int)blockIdx.y * fpc + grp;           // fit within the launched range
-    if (lf >= gn) return;
-    const int g = g0 + lf;
-    const double* F = F_all + (int64_t)g * d.N * d.S;
-    double* lattice = lattice_all + (int64_t)lf * d.N * d.S;    // scratch holds the launched fits only
-    int* path = path_all + (int64_t)g * d.N;
-    sp.pd += (int64_t)g * sp_fit_stride;
-    sp.wexp += (int64_t)g * sp_fit_stride;
-    double* prev = prev_all + (size_t)grp * 2 * SP;
+    const int lf0 = ((int)blockIdx.y * fpc + grp) * FR;   // first fit of the group within the launched range
+    if (lf0 >= gn) return;
+    // a group at the end of the range may hold fewer than FR fits: the missing ones repeat the last fit's inputs and
+    // store nothing
+    const int64_t NS = (int64_t)d.N * d.S;
+    const double* F[FR];
+    double* lattice[FR];
+    bool live[FR];
+#pragma unroll
+    for (int f = 0; f < FR; ++f) {
+        live[f] = lf0 + f < gn;
+        const int lf = live[f] ? lf0 + f : gn - 1;
+        F[f] = F_all + (int64_t)(g0 + lf) * NS;
+        lattice[f] = lattice_all + (int64_t)lf * NS;      // scratch holds the launched fits only
+    }
+    double* prev = prev_all + (size_t)grp * FR * 2 * SP;  // fit f, buffer c at prev + (f * 2 + c) * SP
     const int c_lo = ch.bin_ptr[blockIdx.x], c_hi = ch.bin_ptr[blockIdx.x + 1];
 #define VIT_BAR() asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(tpf) : "memory")
     int cur = 0;
     for (int ci = c_lo; ci < c_hi; ++ci) {
         const int chain = ch.bin_idx[ci];
         const int s0 = ch.start[chain], s1 = ch.end[chain];
-        for (int jj = t; jj < S; jj += tpf) {
-            double v = F[(int64_t)s0 * S + jj];
-            lattice[(int64_t)s0 * S + jj] = v;
-            prev[cur * SP + jj] = v;
-        }
+#pragma unroll
+        for (int f = 0; f < FR; ++f)
+            for (int jj = t; jj < S; jj += tpf) {
+                double v = F[f][(int64_t)s0 * S + jj];
+                if (live[f]) lattice[f][(int64_t)s0 * S + jj] = v;
+                prev[(f * 2 + cur) * SP + jj] = v;
+            }
         VIT_BAR();
-        // row n-1 -> n; descriptors of the next row and the next frame value (first column) one segment ahead
+        // row n-1 -> n; descriptors of the next row and the next frame values (first column) one segment ahead
         int cls = s0 < s1 ? rows.tclass[s0] : -1, br = s0 < s1 ? rows.brow[s0] : -1, dd0 = s0 < s1 ? rows.d0[s0] : 0;
-        const double* Fp = F + (int64_t)(s0 + 1) * S + t;       // this thread's first column of row n
-        double* Lp = lattice + (int64_t)(s0 + 1) * S + t;
-        double fcur = (s0 < s1 && t < S) ? *Fp : 0.;
-        for (int n = s0 + 1; n <= s1; ++n, Fp += S, Lp += S) {
-            const double* pc = prev + cur * SP;
-            double* pn = prev + (cur ^ 1) * SP;
+        int64_t off = (int64_t)(s0 + 1) * S + t;                // this thread's first column of row n
+        double fcur[FR];
+#pragma unroll
+        for (int f = 0; f < FR; ++f) fcur[f] = (s0 < s1 && t < S) ? F[f][off] : 0.;
+        for (int n = s0 + 1; n <= s1; ++n, off += S) {
             const bool fast = cls >= 0 && br < 0 && cls < staged;
             const int cls0 = cls, br0 = br, dd00 = dd0;
-            const double fn0 = fcur;
+            double fn0[FR];
+#pragma unroll
+            for (int f = 0; f < FR; ++f) fn0[f] = fcur[f];
             if (n < s1) {
                 cls = rows.tclass[n]; br = rows.brow[n]; dd0 = rows.d0[n];
-                if (t < S) fcur = Fp[S];
+                if (t < S) {
+#pragma unroll
+                    for (int f = 0; f < FR; ++f) fcur[f] = F[f][off + S];
+                }
             }
             if (fast) {
                 if (t < S) {            // staged classes have S <= tpf: one column per thread
                     // the value of a maximum does not depend on the order (ties only matter in the traceback)
-                    const double2* pv = reinterpret_cast<const double2*>(pc);
+                    const double2* pv = reinterpret_cast<const double2*>(prev + cur * SP);
                     const double2* tv = reinterpret_cast<const double2*>(Tsm + ((size_t)cls0 * S + t) * SP);
                     const double2* pe = pv + SL / 2;
-                    double m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+                    double mx[FR][4];
+#pragma unroll
+                    for (int f = 0; f < FR; ++f)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) mx[f][k] = -INFINITY;
 #pragma unroll 1
                     for (; pv < pe; pv += 4, tv += 4) {
-                        const double2 p0 = pv[0], p1 = pv[1], p2 = pv[2], p3 = pv[3];
                         const double2 t0 = tv[0], t1 = tv[1], t2 = tv[2], t3 = tv[3];
-                        double v;
-                        v = __dadd_rn(p0.x, t0.x); if (v > m0) m0 = v;
-                        v = __dadd_rn(p0.y, t0.y); if (v > m1) m1 = v;
-                        v = __dadd_rn(p1.x, t1.x); if (v > m2) m2 = v;
-                        v = __dadd_rn(p1.y, t1.y); if (v > m3) m3 = v;
-                        v = __dadd_rn(p2.x, t2.x); if (v > m0) m0 = v;
-                        v = __dadd_rn(p2.y, t2.y); if (v > m1) m1 = v;
-                        v = __dadd_rn(p3.x, t3.x); if (v > m2) m2 = v;
-                        v = __dadd_rn(p3.y, t3.y); if (v > m3) m3 = v;
+#pragma unroll
+                        for (int f = 0; f < FR; ++f) {
+                            const double2* pf = pv + f * SP;     // fit f's buffers start 2 * SP doubles further
+                            const double2 p0 = pf[0], p1 = pf[1], p2 = pf[2], p3 = pf[3];
+                            double v;
+                            v = __dadd_rn(p0.x, t0.x); if (v > mx[f][0]) mx[f][0] = v;
+                            v = __dadd_rn(p0.y, t0.y); if (v > mx[f][1]) mx[f][1] = v;
+                            v = __dadd_rn(p1.x, t1.x); if (v > mx[f][2]) mx[f][2] = v;
+                            v = __dadd_rn(p1.y, t1.y); if (v > mx[f][3]) mx[f][3] = v;
+                            v = __dadd_rn(p2.x, t2.x); if (v > mx[f][0]) mx[f][0] = v;
+                            v = __dadd_rn(p2.y, t2.y); if (v > mx[f][1]) mx[f][1] = v;
+                            v = __dadd_rn(p3.x, t3.x); if (v > mx[f][2]) mx[f][2] = v;
+                            v = __dadd_rn(p3.y, t3.y); if (v > mx[f][3]) mx[f][3] = v;
+                        }
                     }
-                    if (m1 > m0) m0 = m1;
-                    if (m3 > m2) m2 = m3;
-                    if (m2 > m0) m0 = m2;
-                    const double o = __dadd_rn(m0, fn0);
-                    pn[t] = o;
-                    *Lp = o;
+#pragma unroll
+                    for (int f = 0; f < FR; ++f) {
+                        if (mx[f][1] > mx[f][0]) mx[f][0] = mx[f][1];
+                        if (mx[f][3] > mx[f][2]) mx[f][2] = mx[f][3];
+                        if (mx[f][2] > mx[f][0]) mx[f][0] = mx[f][2];
+                        const double o = __dadd_rn(mx[f][0], fn0[f]);
+                        prev[(f * 2 + (cur ^ 1)) * SP + t] = o;
+                        if (live[f]) lattice[f][off] = o;
+                    }
                 }
             } else {
-                for (int jj = t; jj < S; jj += tpf) {
-                    const double fn = jj == t ? fn0 : F[(int64_t)n * S + jj];
-                    const double o = __dadd_rn(vit_column_general(d, sp, tots, cls0, br0, dd00, pc, jj), fn);
-                    pn[jj] = o;
-                    lattice[(int64_t)n * S + jj] = o;
+#pragma unroll
+                for (int f = 0; f < FR; ++f) {
+                    RmxTransSpec spf = sp;
+                    const int64_t fo = (int64_t)(g0 + (live[f] ? lf0 + f : gn - 1)) * sp_fit_stride;
+                    spf.pd += fo;
+                    spf.wexp += fo;
+                    for (int jj = t; jj < S; jj += tpf) {
+                        const double fn = jj == t ? fn0[f] : F[f][(int64_t)n * S + jj];
+                        const double o = __dadd_rn(
+                            vit_column_general(d, spf, tots, cls0, br0, dd00, prev + (f * 2 + cur) * SP, jj), fn);
+                        prev[(f * 2 + (cur ^ 1)) * SP + jj] = o;
+                        if (live[f]) lattice[f][(int64_t)n * S + jj] = o;
+                    }
                 }
             }
             VIT_BAR();
@@ -1090,9 +1124,15 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
         }
     }
 #undef VIT_BAR
-    // traceback by the group's first warp: no barriers on the sequential path; the lattice row and the row
+    // traceback of fit f by warp f of the group: no barriers on the sequential path; the lattice row and the row
     // descriptors of the next step are loaded before the current step's reduction
-    if (t >= 32) return;
+    const int wf = t >> 5;
+    if (wf >= FR || lf0 + wf >= gn) return;
+    const int lane = t & 31;
+    const double* lat = lattice_all + (int64_t)(lf0 + wf) * NS;
+    int* path = path_all + (int64_t)(g0 + lf0 + wf) * d.N;
+    sp.pd += (int64_t)(g0 + lf0 + wf) * sp_fit_stride;
+    sp.wexp += (int64_t)(g0 + lf0 + wf) * sp_fit_stride;
     for (int ci = c_lo; ci < c_hi; ++ci) {
         const int chain = ch.bin_idx[ci];
         const int s0 = ch.start[chain], s1 = ch.end[chain];
@@ -1103,7 +1143,7 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
         int pc = -1, pb = -1, pd0 = 0;
         if (pre) {
 #pragma unroll
-            for (int k = 0; k < KP; ++k) lv[k] = (t + 32 * k < S) ? lattice[(int64_t)s1 * S + t + 32 * k] : 0.;
+            for (int k = 0; k < KP; ++k) lv[k] = (lane + 32 * k < S) ? lat[(int64_t)s1 * S + lane + 32 * k] : 0.;
         }
         for (int n = s1; n >= s0; --n) {
             // on entry: lv = lattice row n, (pc, pb, pd0) = descriptors of row n (transition n -> n+1, n < s1)
@@ -1121,7 +1161,8 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
             if (n > s0) {       // the next step's inputs, in flight during this step's reduction
                 if (pre) {
 #pragma unroll
-                    for (int k = 0; k < KP; ++k) lv[k] = (t + 32 * k < S) ? lattice[(int64_t)(n - 1) * S + t + 32 * k] : 0.;
+                    for (int k = 0; k < KP; ++k)
+                        lv[k] = (lane + 32 * k < S) ? lat[(int64_t)(n - 1) * S + lane + 32 * k] : 0.;
                 }
                 nc = rows.tclass[n - 1]; nb = rows.brow[n - 1]; nd0 = rows.d0[n - 1];
             }
@@ -1130,7 +1171,7 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
             if (pre) {
 #pragma unroll
                 for (int k = 0; k < KP; ++k) {
-                    const int i = t + 32 * k;
+                    const int i = lane + 32 * k;
                     if (i < S) {
                         double v = cur_row[k];
                         if (n < s1) {
@@ -1141,8 +1182,8 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
                     }
                 }
             } else {
-                for (int i = t; i < S; i += 32) {
-                    double v = lattice[(int64_t)n * S + i];
+                for (int i = lane; i < S; i += 32) {
+                    double v = lat[(int64_t)n * S + i];
                     if (n < s1) {
                         if (Ts) v = __dadd_rn(v, Ts[i]);
                         else v = __dadd_rn(v, logT(lt, d, i, nxt));
@@ -1157,7 +1198,7 @@ __global__ void __launch_bounds__(1024) k_viterbi(RmxDims d, int g0, int gn, Rmx
                 if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
             }
             if (bi == 0x7fffffff) bi = 0;   // all -inf / NaN: _argmax returns 0
-            if (t == 0) path[n] = bi;
+            if (lane == 0) path[n] = bi;
             nxt = bi;
             pc = nc; pb = nb; pd0 = nd0;
         }
@@ -1502,28 +1543,43 @@ void rmx_launch_pairsum_hist(cudaStream_t st, const RmxDims& d, int g0, int gn, 
 void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const RmxChains& ch,
                         const RmxRows& rows, const RmxTransSpec& sp, int64_t sp_fit_stride, const double* F,
                         double* lattice, int* path, int nclass) {
-    if (ch.NC <= 0 || gn <= 0) return;
+    if (ch.NB <= 0 || gn <= 0) return;
     int tpf = ((d.S + 31) / 32) * 32;
     if (tpf > 1024) tpf = 1024;
-    int fpc = 1024 / tpf;                 // fits per CTA: they share the staged class matrices
-    if (fpc > 4) fpc = 4;
-    {
-        static const char* env = getenv("RMX_VITERBI_FPC");     // A/B measurements only
-        if (env && atoi(env) >= 1 && atoi(env) < fpc) fpc = atoi(env);
-    }
-    if (fpc > gn) fpc = gn;
     // class matrices of the plain rows in shared memory, as many as fit (class ids are dense from 0)
     int staged = 0;
     const size_t SP = (size_t)((d.S + 7) & ~7) + 2;       // padded row of a transposed class matrix (see k_viterbi)
     while (staged < nclass && sizeof(double) * (size_t)(staged + 1) * d.S * SP <= 176 * 1024) ++staged;
-    size_t smem = sizeof(double) * ((size_t)fpc * 2 * SP + (size_t)staged * d.S * SP) + (size_t)d.S * d.M + 16;
+    // FR = 2 (two fits per thread: the matrix stream is shared by the two) measures the same as FR = 1 at config 2 and
+    // stays an A/B knob; it needs the traceback warps (warp f of a group traces fit f)
+    int fr = 1;
+    const int maxt = tpf <= 512 ? 512 : 1024;   // 512-thread CTAs compile to 128 registers (no spills)
+    {
+        static const char* env2 = getenv("RMX_VITERBI_FR");
+        if (env2 && atoi(env2) == 2 && staged > 0 && gn >= 2 && tpf >= 64 && tpf <= 256) fr = 2;
+    }
+    int fpc = maxt / tpf;                 // groups per CTA: they share the staged class matrices
+    if (fpc > 4 / fr) fpc = 4 / fr;
+    {
+        static const char* env = getenv("RMX_VITERBI_FPC");     // A/B measurements only
+        if (env && atoi(env) >= 1 && atoi(env) < fpc) fpc = atoi(env);
+    }
+    const int groups = (gn + fr - 1) / fr;
+    if (fpc > groups) fpc = groups;
+    size_t smem = sizeof(double) * ((size_t)fpc * fr * 2 * SP + (size_t)staged * d.S * SP) + (size_t)d.S * d.M + 16;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(k_viterbi, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+        cudaFuncSetAttribute(k_viterbi<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+        cudaFuncSetAttribute(k_viterbi<1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+        cudaFuncSetAttribute(k_viterbi<2, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
         attr_set = true;
     }
-    k_viterbi<<<dim3(ch.NB, (gn + fpc - 1) / fpc), tpf * fpc, smem, st>>>(d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F,
-                                                                          lattice, path, staged, fpc);
+    const dim3 grid(ch.NB, (groups + fpc - 1) / fpc);
+#define VIT_ARGS d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F, lattice, path, staged, fpc
+    if (fr == 2) k_viterbi<2, 512><<<grid, tpf * fpc, smem, st>>>(VIT_ARGS);
+    else if (maxt == 512) k_viterbi<1, 512><<<grid, tpf * fpc, smem, st>>>(VIT_ARGS);
+    else k_viterbi<1, 1024><<<grid, tpf * fpc, smem, st>>>(VIT_ARGS);
+#undef VIT_ARGS
 }
 
 void rmx_launch_materialize_T(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxRows& rows,
