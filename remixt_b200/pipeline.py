@@ -337,6 +337,7 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
     for g, d in enumerate(drivers):
         if ids[g] not in errors:
             results[ids[g]] = _fit_results(d, experiment, init_params_by_id[ids[g]], config, cn[g])
+    batch.close()       # results hold host arrays only; the device blocks go back to the pool now
     if errors and not results:
         raise next(iter(errors.values()))
     stats = dict((i, results[i]['stats']) for i in ids if i in results)
