@@ -21,6 +21,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cstdlib>
@@ -1650,8 +1651,6 @@ int rmx_infer_cn(rmx_handle m, int64_t* cn) {
     const int g0 = m->g0, gn = m->gn, N = d.N;
     // max_product(self.framelogprob, self.log_transmat) (bpmodel.pyx:1203): both as of the last update_p_cn;
     // constructor state (framelogprob == 1, log_transmat == 0) gives the all-zero path (first max)
-    for (int g = g0; g < g0 + gn; ++g)
-        for (int n = 0; n < N; ++n) b->h_path[(size_t)g * N + n] = 0;
     bool any = false;
     for (int g = g0; g < g0 + gn; ++g) any |= b->cn_updated[g] != 0;
     if (any) {
@@ -1675,21 +1674,39 @@ int rmx_infer_cn(rmx_handle m, int64_t* cn) {
                            cudaMemcpyDeviceToHost, b->stream));
         rc = sync_check(m);
         if (rc) return rc;
-        for (int g = g0; g < g0 + gn; ++g)
-            if (b->cn_updated[g])
-                for (int n = 0; n < N; ++n) b->h_path[(size_t)g * N + n] = b->hrows[(size_t)g * N + n];
     }
     // cn[n, m, ell] = cn_states[n, path[n], m, ell]; the allele-swap branch of bpmodel.pyx:1208-1209
-    // indexes both sides with the swapped ell, so it does not change the output
-    for (int g = 0; g < gn; ++g) {
-        b->path_valid[g0 + g] = 1;
-        for (int n = 0; n < N; ++n) {
-            int s = b->h_path[(size_t)(g0 + g) * N + n];
-            int64_t* o = cn + ((size_t)g * N + n) * d.M * 2;
-            o[0] = b->h_nrm[2 * n];
-            o[1] = b->h_nrm[2 * n + 1];
-            for (int e = 2; e < d.M * 2; ++e) o[e] = b->h_tab[(size_t)s * d.M * 2 + e];
+    // indexes both sides with the swapped ell, so it does not change the output.  One pass per fit (path kept for
+    // RMX_A_STATE_PATH, states expanded into the caller's array), the fits spread over a few host threads: the
+    // output of a whole grid is tens of MB of fresh pages.
+    auto expand = [&](int gbeg, int gend) {
+        for (int g = gbeg; g < gend; ++g) {
+            const bool dec = any && b->cn_updated[g0 + g];
+            b->path_valid[g0 + g] = 1;
+            for (int n = 0; n < N; ++n) {
+                const int s = dec ? b->hrows[(size_t)(g0 + g) * N + n] : 0;
+                b->h_path[(size_t)(g0 + g) * N + n] = s;
+                int64_t* o = cn + ((size_t)g * N + n) * d.M * 2;
+                o[0] = b->h_nrm[2 * n];
+                o[1] = b->h_nrm[2 * n + 1];
+                for (int e = 2; e < d.M * 2; ++e) o[e] = b->h_tab[(size_t)s * d.M * 2 + e];
+            }
         }
+    };
+    int nthr = 1;
+    if ((int64_t)gn * N >= (1 << 18)) {
+        nthr = (int)std::thread::hardware_concurrency();
+        if (nthr > 8) nthr = 8;
+        if (nthr > gn) nthr = gn;
+        if (nthr < 1) nthr = 1;
+    }
+    if (nthr == 1) {
+        expand(0, gn);
+    } else {
+        std::vector<std::thread> pool;
+        for (int k = 0; k < nthr; ++k)
+            pool.emplace_back(expand, (int)((int64_t)gn * k / nthr), (int)((int64_t)gn * (k + 1) / nthr));
+        for (auto& th : pool) th.join();
     }
     return RMX_OK;
 }
