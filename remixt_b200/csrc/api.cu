@@ -86,14 +86,14 @@ static DevPool g_pool;
 struct PinnedPool {
     std::mutex mu;
     std::multimap<size_t, void*> free_blocks;
-    cudaError_t get(size_t bytes, void** p) {
+    cudaError_t get(size_t bytes, void** p, bool zero = true) {
         {
             std::lock_guard<std::mutex> lk(mu);
             auto it = free_blocks.find(bytes);
             if (it != free_blocks.end()) {
                 *p = it->second;
                 free_blocks.erase(it);
-                memset(*p, 0, bytes);
+                if (zero) memset(*p, 0, bytes);
                 return cudaSuccess;
             }
         }
@@ -1200,6 +1200,30 @@ int rmx_get_array(rmx_handle m, int id, void* dstv, int64_t count) {
             for (int g = 0; g < gn; ++g)
                 CK(cudaMemcpyAsync((double*)dstv + (size_t)g * per, src, (size_t)per * sizeof(double), cudaMemcpyDeviceToHost,
                                    b->stream));
+        } else if ((size_t)count * sizeof(double) >= ((size_t)4 << 20) && (size_t)count * sizeof(double) <= ((size_t)256 << 20)) {
+            // a large (but not huge: the block stays in the pool) read into the caller's pageable, usually fresh array:
+            // through a pooled page-locked block at
+            // link speed, then copied out by a few host threads (the page faults of the destination run in parallel)
+            const size_t bytes = (size_t)count * sizeof(double);
+            void* stage = nullptr;
+            if (g_pinned.get(bytes, &stage, false) != cudaSuccess) return m->fail(RMX_ERR_CUDA, "out of page-locked memory");
+            cudaError_t e = cudaMemcpyAsync(stage, src + (size_t)g0 * per, bytes, cudaMemcpyDeviceToHost, b->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+            if (e != cudaSuccess) {
+                g_pinned.put(bytes, stage);
+                return m->fail(RMX_ERR_CUDA, cudaGetErrorString(e));
+            }
+            int nthr = (int)std::thread::hardware_concurrency();
+            if (nthr > 8) nthr = 8;
+            if (nthr < 1) nthr = 1;
+            std::vector<std::thread> pool;
+            for (int k = 0; k < nthr; ++k) {
+                const size_t lo = bytes * k / nthr, hi = bytes * (k + 1) / nthr;
+                pool.emplace_back([=] { memcpy((char*)dstv + lo, (const char*)stage + lo, hi - lo); });
+            }
+            for (auto& th : pool) th.join();
+            g_pinned.put(bytes, stage);
+            return RMX_OK;
         } else {
             CK(cudaMemcpyAsync(dstv, src + (size_t)g0 * per, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost,
                                b->stream));
