@@ -151,6 +151,7 @@ int rmx_device_count(int* count);
 
 /* ---- attribute access (cdef public attributes, bpmodel.pyx:398-456) ------------------ */
 /* `count` is the number of ELEMENTS of the host buffer: gn times the attribute's size, fit-major.
+ * rmx_set_array also accepts ONE attribute's worth of elements on a multi-fit handle: every fit gets that value.
  * rmx_get_scalar writes gn doubles.  The derived tables are the same for every fit (no leading gn).
  * transition_penalty is fixed at creation; the outlier priors are per batch. */
 int rmx_set_array(rmx_handle h, int array_id, const void* src, int64_t count);

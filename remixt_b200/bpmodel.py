@@ -219,7 +219,8 @@ class _ModelBase(object):
         full = (self._gn,) + tuple(shape)
         if a.shape != tuple(shape) and a.shape != full:
             raise ValueError('array of shape %s expected, got %s' % (tuple(shape), a.shape))
-        a = np.ascontiguousarray(np.broadcast_to(a, full), dtype=dtype)
+        # one attribute's worth of elements on a batch is broadcast to its fits by the library
+        a = np.ascontiguousarray(a, dtype=dtype)
         check(lib.rmx_set_array(self._handle, array_id, _ptr(a), a.size), self._handle)
 
     def _get_scalar(self, name):

@@ -1049,7 +1049,9 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     bool i64;
     const int64_t per = array_count(b, id, &i64);
     if (per < 0) return m->fail(RMX_ERR_ARG, "unknown array id");
-    if (per * m->gn != count) return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
+    const bool bcast = m->gn > 1 && count == per && id != RMX_A_H;      // one value for every fit of the handle
+    if (per * m->gn != count && !bcast)
+        return m->fail(RMX_ERR_VALUE, "array has the wrong number of elements for this attribute");
     const int g0 = m->g0, gn = m->gn;
     double* dst = nullptr;
     switch (id) {
@@ -1074,10 +1076,18 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     case RMX_A_TOTAL_LIKELIHOOD_MASK:
     case RMX_A_ALLELE_LIKELIHOOD_MASK: {
         const int64_t* s = (const int64_t*)src;
-        const size_t n = (size_t)gn * b->d.N, off = (size_t)g0 * b->d.N;
+        const size_t n = (size_t)gn * b->d.N, off = (size_t)g0 * b->d.N, N1 = (size_t)b->d.N;
         std::vector<uint8_t> v(n);
         std::vector<int64_t>& keep = id == RMX_A_TOTAL_LIKELIHOOD_MASK ? b->h_tmask : b->h_amask;
-        for (size_t e = 0; e < n; ++e) { keep[off + e] = s[e]; v[e] = s[e] != 0; }
+        if (bcast) {
+            for (size_t e = 0; e < N1; ++e) { keep[off + e] = s[e]; v[e] = s[e] != 0; }
+            for (int g = 1; g < gn; ++g) {
+                memcpy(&keep[off + (size_t)g * N1], &keep[off], N1 * sizeof(int64_t));
+                memcpy(&v[(size_t)g * N1], &v[0], N1);
+            }
+        } else {
+            for (size_t e = 0; e < n; ++e) { keep[off + e] = s[e]; v[e] = s[e] != 0; }
+        }
         CK(cudaMemcpyAsync((id == RMX_A_TOTAL_LIKELIHOOD_MASK ? b->tmask : b->amask) + off, v.data(), n,
                            cudaMemcpyHostToDevice, b->stream));
         CK(cudaStreamSynchronize(b->stream));
@@ -1087,7 +1097,14 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     default: return m->fail(RMX_ERR_ARG, "this attribute cannot be assigned");
     }
     if (count > 0) {
-        CK(cudaMemcpyAsync(dst + (size_t)g0 * per, src, (size_t)count * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+        if (bcast) {
+            for (int g = 0; g < gn; ++g)
+                CK(cudaMemcpyAsync(dst + (size_t)(g0 + g) * per, src, (size_t)per * sizeof(double), cudaMemcpyHostToDevice,
+                                   b->stream));
+        } else {
+            CK(cudaMemcpyAsync(dst + (size_t)g0 * per, src, (size_t)count * sizeof(double), cudaMemcpyHostToDevice,
+                               b->stream));
+        }
         CK(cudaStreamSynchronize(b->stream));
     }
     return RMX_OK;
