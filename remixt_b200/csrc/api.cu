@@ -38,7 +38,7 @@ struct DevPool {
     std::mutex mu;
     std::multimap<std::pair<int, size_t>, void*> free_blocks;
     size_t cached = 0;
-    cudaError_t get(int device, size_t bytes, void** p) {
+    cudaError_t get(int device, size_t bytes, void** p, cudaStream_t stream) {
         *p = nullptr;
         {
             std::lock_guard<std::mutex> lk(mu);
@@ -49,11 +49,9 @@ struct DevPool {
                 cached -= bytes;
             }
         }
-        if (*p) {   // a recycled block starts zeroed, as nothing may depend on the previous owner's contents
-            cudaError_t e = cudaMemsetAsync(*p, 0, bytes, 0);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(0);
-            return e;
-        }
+        // a recycled block starts zeroed, as nothing may depend on the previous owner's contents: cleared on the new
+        // owner's stream, ahead of everything the owner does with it (no host synchronisation)
+        if (*p) return cudaMemsetAsync(*p, 0, bytes, stream);
         cudaError_t e = cudaMalloc(p, bytes);
         if (e != cudaSuccess) {
             cudaGetLastError();
@@ -246,7 +244,7 @@ typedef std::lock_guard<std::recursive_mutex> Lock;
 template <typename T>
 static cudaError_t dalloc(Batch* b, T** p, size_t n) {
     if (n == 0) n = 1;
-    cudaError_t e = g_pool.get(b->device, n * sizeof(T), (void**)p);
+    cudaError_t e = g_pool.get(b->device, n * sizeof(T), (void**)p, b->stream);
     if (e == cudaSuccess) b->allocs.push_back({(void*)*p, n * sizeof(T)});
     return e;
 }
@@ -254,7 +252,10 @@ template <typename T>
 static cudaError_t upload(Batch* b, T** dptr, const std::vector<T>& v) {
     cudaError_t e = dalloc(b, dptr, v.size());
     if (e != cudaSuccess) return e;
-    if (!v.empty()) e = cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+    if (!v.empty()) {   // on the batch stream (after the block's clearing); the source may be a temporary
+        e = cudaMemcpyAsync(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, b->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+    }
     return e;
 }
 
