@@ -951,7 +951,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->d_rows, GN));
     CCK(dalloc(b, &b->d_Rn, (size_t)G));
     CCK(dalloc(b, &b->dflags, 1));
-    CCK(cudaMemset(b->dflags, 0, sizeof(int)));
+    CCK(cudaMemsetAsync(b->dflags, 0, sizeof(int), b->stream));
     b->hp_bytes = (size_t)G * Batch::RED * sizeof(double);
     b->hrows_bytes = GN * sizeof(int);
     b->hRn_bytes = (size_t)G * sizeof(int);
@@ -981,9 +981,12 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
         }
         for (size_t k = 0; k < (size_t)G * K; ++k)
             for (int bb = 0; bb < B; ++bb) pb[k * B + bb] = rowp[bb] / cnt;
-        if (K > 0) CCK(cudaMemcpy(b->p_brk, pb.data(), pb.size() * sizeof(double), cudaMemcpyHostToDevice));
+        // on the batch stream: a recycled block's clearing is queued there
+        if (K > 0) {
+            CCK(cudaMemcpyAsync(b->p_brk, pb.data(), pb.size() * sizeof(double), cudaMemcpyHostToDevice, b->stream));
+            CCK(cudaStreamSynchronize(b->stream));
+        }
     }
-    CCK(cudaDeviceSynchronize());   // pageable uploads above went through the legacy stream
     // first cached transition expectation (bpmodel.pyx:604), transition_model still 0 here
     if (snapshot_spec(m, 0, G, true) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
     if (snapshot_spec(m, 0, G, false) != RMX_OK) { std::string e = m->err; CREATE_FAIL(RMX_ERR_CUDA, e); }
