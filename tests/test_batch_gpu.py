@@ -114,3 +114,37 @@ def test_fit_grid_batched_equals_per_fit_fits():
         assert np.array_equal(res_b[i]['h'], res_s[i]['h'])
         assert np.array_equal(res_b[i]['cn'], res_s[i]['cn'])
         assert all(np.array_equal(res_b[i]['brk_cn'][k], res_s[i]['brk_cn'][k]) for k in res_s[i]['brk_cn'])
+
+
+def test_close_recycles_blocks_and_broadcast_assignment():
+    """``close()`` hands the device blocks back at once; the next batch of the same shapes gets them cleared on its own
+    stream and must evolve bit-identically.  A mask given once is broadcast to the fits by ``rmx_set_array``."""
+    from remixt_b200 import _lib
+
+    def run():
+        batch, _, drivers = _batch_and_singles()
+        G = batch.num_fits
+        mask = np.asarray(drivers[0]._total_likelihood_mask).astype(np.int64)
+        batch.total_likelihood_mask = mask                           # (N,) -> every fit
+        assert np.array_equal(batch.total_likelihood_mask, np.broadcast_to(mask, (G,) + mask.shape))
+        batch.total_likelihood_mask = np.broadcast_to(mask, (G,) + mask.shape).copy()     # (G, N) as before
+        batch.variational_update(2)
+        out = (batch.calculate_elbo(), batch.posterior_marginals, batch.p_breakpoint)
+        cn = np.zeros((G, batch.num_segments, 3, 2), dtype=np.int64)
+        batch.infer_cn(cn)
+        return batch, out + (cn,)
+
+    b1, r1 = run()
+    b1.close()
+    b1.close()                                                       # idempotent
+    with pytest.raises(Exception):
+        b1.calculate_elbo()
+    b2, r2 = run()                                                   # recycled blocks
+    for a, b in zip(r1, r2):
+        assert np.array_equal(a, b)
+    b2.close()
+    _lib.release_cached_memory()
+    b3, r3 = run()                                                   # fresh blocks
+    for a, b in zip(r1, r3):
+        assert np.array_equal(a, b)
+    b3.close()
