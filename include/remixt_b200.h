@@ -192,6 +192,24 @@ int rmx_expected_log_likelihood_partial_h(rmx_handle h, const int64_t* sample, d
 int rmx_expected_log_likelihood_grid(rmx_handle h, const int64_t* sample, int scalar_id,
                                      const double* values, int n_values, double* out);
 
+/* ---- batched M-step (the call pattern of cn_model.py:482-569, served for all fits of a grid at once) --------
+ * update_h and update_param draw ONE segment sample per call (cn_model.py:475-480) and evaluate the objective on it
+ * some 10-70 times (L-BFGS-B; brute grid + Nelder-Mead).  rmx_mstep_stage_sample uploads the row lists of the
+ * handle's fits once: `sample` is the (gn,N1) int64 mask of rmx_expected_log_likelihood, NULL = every segment.
+ * rmx_mstep_evaluate then evaluates calculate_expected_log_likelihood (bpmodel.pyx:1125) -- and, when grad != NULL,
+ * calculate_expected_log_likelihood_partial_h (:1159) -- on the staged rows with ONE host synchronisation:
+ *   active   (gn) uint8 or NULL (= all): fits that take part; the others are left untouched (outputs 0).
+ *   h_values (gn,M) or NULL: assigned to h of the active fits first (model.h = h, cn_model.py:484).
+ *   scalar_id, values (gn,n_values), n_values: if scalar_id >= 0, ell[g][v] is evaluated with the named likelihood
+ *            parameter set to values[g][v], v ascending; the parameter is LEFT at values[g][n_values-1] as the
+ *            reference's point-by-point evaluation leaves it (cn_model.py:544).  scalar_id < 0: n_values must be 1.
+ *   ell (gn,n_values), grad (gn,M) or NULL. */
+int rmx_mstep_stage_sample(rmx_handle h, const int64_t* sample);
+int rmx_mstep_evaluate(rmx_handle h, const uint8_t* active, const double* h_values, int scalar_id,
+                       const double* values, int n_values, double* ell, double* grad);
+/* setattr(model, name, value) with one value per fit of the handle (values (gn)); active as above. */
+int rmx_set_scalar_array(rmx_handle h, int scalar_id, const uint8_t* active, const double* values);
+
 /* ---- decode ----------------------------------------------------------------------------- */
 /* infer_cn(cn) (bpmodel.pyx:1197): cn is (gn,N1,M,2) int64, filled in place. */
 int rmx_infer_cn(rmx_handle h, int64_t* cn);

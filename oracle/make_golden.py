@@ -237,5 +237,141 @@ def main():
         run_fit(name, init_id, em, vi, tag, h_scale)
 
 
+
+
+# ---------------------------------------------------------------------------------------------------------
+# grid: complete FREE-RUNNING reference fits of every initialisation of a fixture's grid, and the init_id the
+# reference's own selection rule (analysis/pipeline.py:253-259) picks.  python oracle/make_golden.py NAME grid
+#   [--procs P] [--seed S] [--tag T] [--h-scale F] [--inits a,b,c]
+# ---------------------------------------------------------------------------------------------------------
+PARAMS4 = ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')
+
+
+def _grid_fit_one(job):
+    name, init_id, em, vi, seed, h_scale = job
+    refenv.install()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        import remixt.analysis.pipeline as rp
+        import remixt.cn_model as rcn
+    d, exp = load_experiment(name)
+    ip = init_params_of(d, init_id)
+    if h_scale != 1.:
+        ip['h_normal'] *= h_scale
+    cfg = dict(config_for(name))
+    cfg.update({'num_em_iter': em, 'num_update_iter': vi})
+    trace = {'h': [], 'params': [], 'elbo': [], 'accept': []}
+    orig_h, orig_p, orig_up = rcn.BreakpointModel.update_h, rcn.BreakpointModel.update_param, \
+        rcn.BreakpointModel.em_update_params
+
+    # accept / reject of cn_model.py:526-531 and :564-569, read off the model state: a rejected step restores the
+    # value held before the step (an accepted step that lands exactly on the old value is indistinguishable and
+    # equivalent)
+    def update_h(self):
+        before = np.asarray(self.model.h).copy()
+        orig_h(self)
+        trace['accept'].append(not np.array_equal(before, np.asarray(self.model.h)))
+        trace['h'].append(np.asarray(self.model.h).copy())
+
+    def update_param(self, pname):
+        before = getattr(self.model, pname)
+        orig_p(self, pname)
+        trace['accept'].append(before != getattr(self.model, pname))
+
+    def em_update_params(self):
+        orig_up(self)
+        trace['params'].append([getattr(self.model, k) for k in PARAMS4])
+        trace['elbo'].append(self.model.calculate_elbo())
+
+    rcn.BreakpointModel.update_h, rcn.BreakpointModel.update_param = update_h, update_param
+    rcn.BreakpointModel.em_update_params = em_update_params
+    np.random.seed(seed)
+    t0 = time.time()
+    err = ''
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = rp.fit(exp, ip, cfg)
+    except Exception as e:      # the reference's own workflow records a failed init and goes on
+        err = repr(e)
+        res = None
+    finally:
+        rcn.BreakpointModel.update_h, rcn.BreakpointModel.update_param = orig_h, orig_p
+        rcn.BreakpointModel.em_update_params = orig_up
+    out = {'init_id': init_id, 'seconds': time.time() - t0, 'error': err}
+    if res is not None:
+        st = res['stats']
+        ids = sorted(res['brk_cn'].keys())
+        out.update(elbo=st['elbo'], elbo_diff=st['elbo_diff'], h=np.asarray(res['h']),
+                   params=np.array([st[k] for k in PARAMS4]), ploidy=st['ploidy'],
+                   proportion_divergent=st['proportion_divergent'], cn=np.asarray(res['cn']).astype(np.int8),
+                   brk_ids=np.array(ids), brk_cn=np.array([res['brk_cn'][i] for i in ids]).astype(np.int8),
+                   trace_h=np.array(trace['h']), trace_params=np.array(trace['params']),
+                   trace_elbo=np.array(trace['elbo']), accept=np.array(trace['accept']).reshape(em, -1),
+                   p_outlier_total=np.asarray(res['p_outlier_total'])[:, 1].astype(np.float32),
+                   p_outlier_allele=np.asarray(res['p_outlier_allele'])[:, 1].astype(np.float32))
+    return out
+
+
+class _SelectStore(object):
+    """Stand-in for the HDF store of store_optimal_solution: records which solution it copies."""
+    def __init__(self):
+        self.read = []
+
+    def __getitem__(self, key):
+        self.read.append(key)
+        return None
+
+    def __setitem__(self, key, value):
+        pass
+
+
+def reference_selection(stats_rows, config):
+    """init_id the reference's own store_optimal_solution picks (analysis/pipeline.py:253-264)."""
+    refenv.install()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        import pandas as pd
+        import remixt.analysis.pipeline as rp
+    store = _SelectStore()
+    rp.store_optimal_solution(pd.DataFrame(stats_rows), store, config)
+    key = store.read[0]          # '/solutions/solution_{id}/cn'
+    return int(key.split('solution_')[1].split('/')[0])
+
+
+def run_grid(name, procs=6, em=5, vi=5, seed=1234, tag='', h_scale=1., inits=None):
+    import multiprocessing as mp
+    d, _ = load_experiment(name)
+    n = len(d['init_h_normal'])
+    ids = list(range(n)) if inits is None else inits
+    jobs = [(name, i, em, vi, seed, h_scale) for i in ids]
+    t0 = time.time()
+    with mp.get_context('fork').Pool(procs) as pool:
+        fits = pool.map(_grid_fit_one, jobs, chunksize=1)
+    ok = [f for f in fits if not f['error']]
+    rows = [dict(init_id=f['init_id'], elbo=f['elbo'], proportion_divergent=f['proportion_divergent']) for f in ok]
+    best = reference_selection(rows, config_for(name))
+    out = {'init_ids': np.array([f['init_id'] for f in ok]), 'failed_ids': np.array([f['init_id'] for f in fits if f['error']], dtype=np.int64),
+           'best_init_id': best, 'seed': seed, 'num_em_iter': em, 'num_update_iter': vi, 'h_scale': h_scale,
+           'seconds': np.array([f['seconds'] for f in ok]), 'brk_ids': ok[0]['brk_ids']}
+    for k in ('elbo', 'elbo_diff', 'h', 'params', 'ploidy', 'proportion_divergent', 'cn', 'brk_cn', 'trace_h',
+              'trace_params', 'trace_elbo', 'accept', 'p_outlier_total', 'p_outlier_allele'):
+        out[k] = np.array([f[k] for f in ok])
+    np.savez_compressed(os.path.join(GOLDEN, 'grid_%s%s.npz' % (name, tag)), **out)
+    print(name, 'grid: %d fits (%d failed) in %.0f s wall, %.0f s cpu; best init %d, elbo %.6f' % (
+        len(ok), len(fits) - len(ok), time.time() - t0, out['seconds'].sum(), best, out['elbo'][list(out['init_ids']).index(best)]))
+
+
+def _main_grid():
+    args = sys.argv[1:]
+    def opt(flag, default, conv):
+        return conv(args[args.index(flag) + 1]) if flag in args else default
+    run_grid(args[0], procs=opt('--procs', 6, int), em=opt('--em', 5, int), vi=opt('--vi', 5, int),
+             seed=opt('--seed', 1234, int), tag=opt('--tag', '', str), h_scale=opt('--h-scale', 1., float),
+             inits=opt('--inits', None, lambda s: [int(v) for v in s.split(',')]))
+
+
 if __name__ == '__main__':
-    main()
+    if 'grid' in sys.argv[2:]:
+        _main_grid()
+    else:
+        main()

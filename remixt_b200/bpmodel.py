@@ -368,6 +368,42 @@ class _ModelBase(object):
                                                    n, _ptr(out)), self._handle)
         return self._out(out)
 
+    # ------------------------------------------------------------------ batched M-step (RemixtBatch handles)
+    def mstep_stage_sample(self, sample=None):
+        """Uploads the M-step sample of every fit once (``rmx_mstep_stage_sample``); ``sample`` is the ``(gn, N1)``
+        mask of ``calculate_expected_log_likelihood`` or ``None`` for every segment."""
+        if sample is None:
+            check(lib.rmx_mstep_stage_sample(self._handle, None), self._handle)
+        else:
+            s = self._sample(sample)
+            check(lib.rmx_mstep_stage_sample(self._handle, _ptr(s)), self._handle)
+
+    def mstep_evaluate(self, active=None, h=None, name=None, values=None, grad=False):
+        """E[LL] of the staged sample for the active fits with one synchronisation (``rmx_mstep_evaluate``):
+        ``h`` ``(gn, M)`` is assigned first; with ``name`` the dispersion parameter takes ``values`` ``(gn, n)`` in
+        turn.  Returns ``ell (gn, n)`` and, with ``grad``, ``(ell, grad (gn, M))``."""
+        gn = self._gn
+        act = None if active is None else np.ascontiguousarray(active, dtype=np.uint8)
+        hv = None if h is None else np.ascontiguousarray(h, dtype=np.float64).reshape(gn, self.num_clones)
+        if name is None:
+            sid, vals, n = -1, None, 1
+        else:
+            vals = np.ascontiguousarray(np.asarray(values, dtype=np.float64).reshape(gn, -1))
+            sid, n = _lib.SCALAR_IDS[name], vals.shape[1]
+        ell = np.zeros((gn, n), dtype=np.float64)
+        g = np.zeros((gn, self.num_clones), dtype=np.float64) if grad else None
+        check(lib.rmx_mstep_evaluate(self._handle, None if act is None else _ptr(act), None if hv is None else _ptr(hv),
+                                     sid, None if vals is None else _ptr(vals), n, _ptr(ell),
+                                     None if g is None else _ptr(g)), self._handle)
+        return (ell, g) if grad else ell
+
+    def set_scalar_array(self, name, values, active=None):
+        """``setattr(model, name, values[g])`` for every (active) fit of the handle."""
+        v = np.ascontiguousarray(values, dtype=np.float64).reshape(self._gn)
+        act = None if active is None else np.ascontiguousarray(active, dtype=np.uint8)
+        check(lib.rmx_set_scalar_array(self._handle, _lib.SCALAR_IDS[name], None if act is None else _ptr(act), _ptr(v)),
+              self._handle)
+
     # ------------------------------------------------------------------ decode / inspection
     def infer_cn(self, cn):
         shape = (self.num_segments, self.num_clones, self.num_alleles)

@@ -168,6 +168,12 @@ struct Batch {
     double *hist = nullptr, *chain_logz = nullptr, *rowv = nullptr, *rowsum = nullptr;
     double *red_out = nullptr, *part = nullptr, *lattice = nullptr, *segc_s = nullptr, *evalbuf = nullptr;
     int *path = nullptr, *d_rows = nullptr, *d_Rn = nullptr, *dflags = nullptr;
+    // batched M-step: the staged sample (row lists in ms_rows, per-fit counts on the host) and the per-call
+    // effective counts (0 for inactive fits)
+    int *ms_rows = nullptr, *ms_Rn = nullptr;
+    std::vector<int> ms_count;      // (G) staged rows per fit; -1 = nothing staged
+    bool ms_all = false;            // staged sample = every segment of every fit
+    int ms_rmax = 0;
     int64_t part_stride = 0;
     int lattice_fits = 0;
     static const int RED = 64;   // doubles of reduction output per fit
@@ -950,6 +956,9 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->path, GN));
     CCK(dalloc(b, &b->d_rows, GN));
     CCK(dalloc(b, &b->d_Rn, (size_t)G));
+    CCK(dalloc(b, &b->ms_rows, GN));
+    CCK(dalloc(b, &b->ms_Rn, (size_t)G));
+    b->ms_count.assign(G, -1);
     CCK(dalloc(b, &b->dflags, 1));
     CCK(cudaMemsetAsync(b->dflags, 0, sizeof(int), b->stream));
     b->hp_bytes = (size_t)G * Batch::RED * sizeof(double);
@@ -1684,6 +1693,129 @@ int rmx_expected_log_likelihood_partial_h(rmx_handle m, const int64_t* sample, d
     for (int g = 0; g < m->gn; ++g)
         for (int k = 0; k < M; ++k)
             out[(size_t)g * M + k] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 48 + k] : 0.;
+    return RMX_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// batched M-step
+// ---------------------------------------------------------------------------------------------
+int rmx_mstep_stage_sample(rmx_handle m, const int64_t* sample) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const int N = b->d.N, g0 = m->g0, gn = m->gn;
+    if (g0 != 0 || gn != b->G) return m->fail(RMX_ERR_ARG, "the batched M-step works on the handle of the whole batch");
+    if (!sample) {
+        b->ms_all = true;
+        b->ms_rmax = N;
+        for (int g = 0; g < gn; ++g) b->ms_count[g] = N;
+        return RMX_OK;
+    }
+    int rmax = 0;
+    for (int g = 0; g < gn; ++g) {
+        int cnt = 0;
+        int* hr = b->hrows + (size_t)g * N;
+        const int64_t* s = sample + (size_t)g * N;
+        for (int n = 0; n < N; ++n)
+            if (s[n] != 0) hr[cnt++] = n;
+        b->ms_count[g] = cnt;
+        rmax = cnt > rmax ? cnt : rmax;
+    }
+    b->ms_all = false;
+    b->ms_rmax = rmax;
+    // only the filled head of every fit's list travels
+    for (int g = 0; g < gn; ++g)
+        if (b->ms_count[g] > 0)
+            CK(cudaMemcpyAsync(b->ms_rows + (size_t)g * N, b->hrows + (size_t)g * N, (size_t)b->ms_count[g] * sizeof(int),
+                               cudaMemcpyHostToDevice, b->stream));
+    CK(cudaStreamSynchronize(b->stream));   // hrows is reused by the next staging / decode
+    return RMX_OK;
+}
+
+int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_values, int scalar_id,
+                       const double* values, int n_values, double* ell, double* grad) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const int M = b->d.M, G = b->G;
+    if (m->g0 != 0 || m->gn != G) return m->fail(RMX_ERR_ARG, "the batched M-step works on the handle of the whole batch");
+    if (b->ms_count[0] < 0) return m->fail(RMX_ERR_ARG, "rmx_mstep_stage_sample has not been called");
+    if (n_values < 1 || n_values > 32) return m->fail(RMX_ERR_ARG, "n_values must be in [1, 32]");
+    if (scalar_id >= 0 && (scalar_id > RMX_S_BETABIN_LOH_M_1 || !values))
+        return m->fail(RMX_ERR_ARG, "scalar_id must name a likelihood parameter and come with values");
+    if (scalar_id < 0 && n_values != 1) return m->fail(RMX_ERR_ARG, "n_values must be 1 without a parameter");
+    bool any = false;
+    for (int g = 0; g < G; ++g) {
+        const bool on = !active || active[g];
+        b->hRn[g] = on ? b->ms_count[g] : 0;
+        any |= on && b->ms_count[g] > 0;
+        if (on && h_values) {
+            for (int k = 0; k < M; ++k) b->P[g].h[k] = h_values[(size_t)g * M + k];
+            b->ll_dirty[g] = 1;
+            b->params_dirty = true;
+        }
+    }
+    for (int e = 0; e < G * n_values; ++e) ell[e] = 0.;
+    if (grad) for (int e = 0; e < G * M; ++e) grad[e] = 0.;
+    const int Rmax = b->ms_rmax;
+    const int* rows = b->ms_all ? nullptr : b->ms_rows;
+    const bool work = any && Rmax > 0;
+    if (work)   // pageable-style small copy from the pinned block: staged before the call returns to the stream order
+        CK(cudaMemcpyAsync(b->ms_Rn, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    RmxTables T = tables(b);
+    const int nb = work ? rmx_ell_blocks(b->d, Rmax) : 0;
+    for (int v = 0; v < n_values; ++v) {
+        if (scalar_id >= 0) {
+            for (int g = 0; g < G; ++g)
+                if (!active || active[g]) {
+                    *scalar_slot(b->P[g], scalar_id) = values[(size_t)g * n_values + v];
+                    b->ll_dirty[g] = 1;
+                }
+            b->params_dirty = true;
+        }
+        if (!work) continue;
+        int rc = push_params(m);
+        if (rc) return rc;
+        // the full-data form has no row list: inactive fits are skipped through a zero count all the same
+        rmx_launch_segconst(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->segc_s);
+        { cudaEvent_t te_ = b->tbegin(RMX_K_ELL);
+          rmx_launch_ell(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
+                         b->part, b->part_stride, b->dflags);
+          b->tend(te_); }
+        rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 16 + v, Batch::RED);
+        b->count(3);
+    }
+    if (work && grad) {
+        rmx_launch_ell_grad(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->post, b->q_ot, b->q_oa, b->q_sw, b->part,
+                            b->part_stride, b->dflags);
+        rmx_launch_reduce_cols(b->stream, b->part, nb, RMX_MAXM, 0, G, b->part_stride, b->red_out + 48, Batch::RED);
+        b->count(2);
+    }
+    if (!work) return RMX_OK;
+    int rc = fetch_red(m);
+    if (rc) return rc;
+    for (int g = 0; g < G; ++g) {
+        if (b->hRn[g] <= 0) continue;
+        const double* r = b->hp + (size_t)g * Batch::RED;
+        for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = r[16 + v];
+        if (grad) for (int k = 0; k < M; ++k) grad[(size_t)g * M + k] = r[48 + k];
+    }
+    return RMX_OK;
+}
+
+int rmx_set_scalar_array(rmx_handle m, int id, const uint8_t* active, const double* values) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    if (!scalar_slot(b->P[m->g0], id)) return m->fail(RMX_ERR_ARG, "scalar_id must name a per-fit parameter");
+    for (int g = 0; g < m->gn; ++g) {
+        if (active && !active[g]) continue;
+        *scalar_slot(b->P[m->g0 + g], id) = values[g];
+        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[m->g0 + g] = 1;
+    }
+    b->params_dirty = true;
     return RMX_OK;
 }
 

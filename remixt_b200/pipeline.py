@@ -112,34 +112,9 @@ def fit(experiment, init_params, config, **model_kwargs):
     model = build_model(experiment, init_params, config, **model_kwargs)
     model.fit(init_h(init_params))
 
-    cn, brk_cn = model.optimal_cn()
-    if get_param(config, 'disable_breakpoints'):
-        brk_cn = cn_model.decode_breakpoints_naive(cn, experiment.adjacencies, experiment.breakpoints)
-
-    results = dict()
-    results['h'] = model.h
-    results['cn'] = cn
-    results['brk_cn'] = brk_cn
-    results['p_outlier_total'] = model.p_outlier_total
-    results['p_outlier_allele'] = model.p_outlier_allele
-    results['total_likelihood_mask'] = model.total_likelihood_mask
-    results['allele_likelihood_mask'] = model.allele_likelihood_mask
-
-    stats = dict()
-    stats['elbo'] = model.prev_elbo
-    stats['elbo_diff'] = model.prev_elbo_diff
-    stats['error_message'] = ''
-    stats.update(model.get_likelihood_param_values())
-    l = experiment.l
-    stats['num_clones'] = len(model.h)
-    stats['num_segments'] = len(experiment.x)
-    stats['ploidy'] = (cn[:, 1:, :].mean(axis=1).T * l).sum() / l.sum()
-    divergent = (cn[:, 1:, :].max(axis=1) != cn[:, 1:, :].min(axis=1)) * 1.
-    stats['proportion_divergent'] = (divergent.T * l).sum() / (2. * l.sum())
-    stats['mode_idx'] = init_params.get('mode_idx', 0)
-    stats['divergence_weight'] = init_params['divergence_weight']
-    results['stats'] = stats
-    return results
+    cn = np.zeros((model.model.num_segments, model.model.num_clones, model.model.num_alleles), dtype=int)
+    model.model.infer_cn(cn)
+    return _fit_results(model, experiment, init_params, config, cn)
 
 
 def select_solution(stats_by_init, config=None):
@@ -205,46 +180,46 @@ def shard_ids(ids, rank, world_size):
 
 
 def fit_grid_distributed(experiment, init_params_by_id, config, dist=None, device=None, random_seed=1234,
-                         num_threads=4, **fit_kwargs):
+                         grid_fit=None, **fit_kwargs):
     """The init grid over the ranks of a ``torch.distributed`` process group (one process per GPU).
 
     The grid is the unit that shards: fits are independent, so there is no data-path
-    collective; every rank fits ``shard_ids(ids, rank, world)`` on its own device and the per-fit
-    ``stats`` dicts (about ten scalars each) are exchanged once at the end with ``all_gather_object``.
-    Every rank then applies the reference's selection rule (``analysis/pipeline.py:253-259``) to the
-    full table, so all ranks return the same ``best`` id.  Returns ``(local_results, all_stats, best)``.
+    collective; every rank fits ``shard_ids(ids, rank, world)`` on its own device as ONE batch
+    (:func:`fit_grid_batched`: shared data, every kernel launch serves all of the rank's fits, lock-step
+    M-step) and the per-fit ``stats`` dicts (about ten scalars each) are exchanged once at the end with
+    ``all_gather_object``.  Every rank then applies the reference's selection rule
+    (``analysis/pipeline.py:253-259``) to the full table, so all ranks return the same ``best`` id.
+    The reference fans ``init_id`` out one process per initialisation (``workflow.py:329-340``).
+
+    ``grid_fit`` (tests) replaces :func:`fit_grid_batched` as the per-rank grid driver.
+    Returns ``(local_results, all_stats, best, all_errors)``.
     """
     ids = list(init_params_by_id.keys())
     rank = dist.get_rank() if dist is not None else 0
     world = dist.get_world_size() if dist is not None else 1
     mine = shard_ids(ids, rank, world)
-    model_kwargs = {} if device is None else {'device': device}
-    results = {}
-
-    def worker(slot):
-        for pos in range(slot, len(mine), num_threads):
-            init_id = mine[pos]
-            results[init_id] = fit(experiment, init_params_by_id[init_id], config, model_kwargs=model_kwargs,
-                                   random_state=np.random.RandomState(random_seed), **fit_kwargs)
-
-    nt = max(1, min(num_threads, len(mine)))
-    threads = [threading.Thread(target=worker, args=(s,)) for s in range(nt)]
-    for t in threads:
-        t.start()
-    for t in threads:
-        t.join()
+    results, errors = {}, {}
+    if mine:
+        try:
+            results, _, errors = (grid_fit or fit_grid_batched)(
+                experiment, init_params_by_id, config, device=device, random_seed=random_seed, init_ids=mine,
+                **fit_kwargs)
+        except Exception as e:          # every fit of this rank failed: the other ranks' fits still count
+            errors = dict((i, e) for i in mine)
     local_stats = dict((i, results[i]['stats']) for i in mine if i in results)
+    local_errors = dict((i, repr(e)) for i, e in errors.items())
     if dist is not None and world > 1:
         gathered = [None] * world
-        dist.all_gather_object(gathered, local_stats)
-        all_stats = {}
-        for part in gathered:
-            all_stats.update(part)
+        dist.all_gather_object(gathered, (local_stats, local_errors))
+        all_stats, all_errors = {}, {}
+        for st, er in gathered:
+            all_stats.update(st)
+            all_errors.update(er)
     else:
-        all_stats = local_stats
+        all_stats, all_errors = local_stats, local_errors
     ordered = dict((i, all_stats[i]) for i in ids if i in all_stats)
     best = select_solution(ordered, config) if ordered else None
-    return results, ordered, best
+    return results, ordered, best, all_errors
 
 
 def _fit_results(model, experiment, init_params, config, cn):
@@ -275,71 +250,147 @@ def _fit_results(model, experiment, init_params, config, cn):
     stats['mode_idx'] = init_params.get('mode_idx', 0)
     stats['divergence_weight'] = init_params['divergence_weight']
     results['stats'] = stats
+    # extension (not a reference key): the outcome of every M-step acceptance test, in call order
+    results['decisions'] = list(getattr(model, 'decisions', []))
     return results
 
 
-def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_seed=1234, num_threads=8,
-                     init_ids=None):
+class _ModelListGrid(object):
+    """G independent single-fit models behind the part of the ``RemixtBatch`` surface the grid driver uses."""
+
+    def __init__(self, models):
+        self.models = models
+        self.num_segments = models[0].num_segments
+        self.num_clones = models[0].num_clones
+
+    def variational_update(self, n_iter):
+        for m in self.models:
+            for _ in range(n_iter):
+                for step in ('update_p_allele_swap', 'update_p_cn', 'update_p_breakpoint', 'update_p_outlier_total',
+                             'update_p_outlier_allele'):
+                    getattr(m, step)()
+
+    def calculate_elbo(self):
+        return np.array([m.calculate_elbo() for m in self.models])
+
+    def infer_cn(self, cn):
+        for g, m in enumerate(self.models):
+            out = np.zeros(cn.shape[1:], dtype=int)
+            m.infer_cn(out)
+            cn[g] = out
+
+    def close(self):
+        pass
+
+
+def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_seed=1234, init_ids=None,
+                     mstep='lockstep', num_threads=8, profile=None, model_class=None):
     """The whole initialisation grid as ONE batch on one GPU: every E-step kernel launch serves all fits
-    (``bpmodel.RemixtBatch``); the M-steps stay the reference's per-fit scipy optimisers
-    (``cn_model.py:482-569``), run from ``num_threads`` host threads on views of the batch.
+    (``bpmodel.RemixtBatch``) and the M-steps of all fits advance in lock step (``mstep.GridMStep``: every round of
+    objective evaluations of ``cn_model.py:482-569`` is one device call for the whole grid).
 
     Per fit this performs exactly the calls ``fit`` performs, in the same order, with the M-step
     subsamples drawn from ``RandomState(random_seed)`` per fit (the stream a process that called
-    ``numpy.random.seed(random_seed)`` before ``pipeline.fit`` would see).  Returns ``(results, best, errors)``
-    like :func:`fit_grid`.
+    ``numpy.random.seed(random_seed)`` before ``pipeline.fit`` would see).  ``mstep='threads'`` keeps the per-fit
+    scipy drivers of ``cn_model.BreakpointModel`` on ``num_threads`` host threads (A/B measurements).
+    ``profile`` (a dict) receives wall-clock seconds per phase.  ``model_class`` (tests) runs the same driver over G
+    independent models of another ``RemixtModel`` implementation.  Returns ``(results, best, errors)`` like
+    :func:`fit_grid`; a fit that fails is reported in ``errors`` and leaves the grid.
     """
+    import time
     from . import bpmodel
+    from . import mstep as _mstep
+    prof = profile if profile is not None else {}
+    for k in ('build', 'e_step', 'm_step', 'elbo', 'decode', 'results'):
+        prof.setdefault(k, 0.)
+    t0 = time.perf_counter()
     ids = list(init_params_by_id.keys()) if init_ids is None else list(init_ids)
     drivers = [build_model(experiment, init_params_by_id[i], config, random_state=np.random.RandomState(random_seed))
                for i in ids]
     h = np.array([init_h(init_params_by_id[i]) for i in ids])
     dw = np.array([init_params_by_id[i]['divergence_weight'] for i in ids], dtype=float)
     kwargs = {} if device is None else {'device': device}
-    batch = bpmodel.RemixtBatch(*(drivers[0].model_args(h) + (dw,)), **kwargs)
-    for g, d in enumerate(drivers):
-        d.attach(batch.fit(g))
+    d0 = drivers[0]
+    if model_class is not None:
+        # tests: G independent models of another RemixtModel implementation (the compiled reference, the oracle)
+        # behind the same grid driver
+        for d, hg in zip(drivers, h):
+            d.model_class = model_class
+            d.attach(d._make_model(hg))
+        batch = _ModelListGrid([d.model for d in drivers])
+        backend = _mstep.ModelListBackend(batch.models)
+    else:
+        batch = bpmodel.RemixtBatch(*(d0.model_args(h, compact=True) + (dw,)), **kwargs)
+        backend = _mstep.BatchBackend(batch)
+        shared = all(np.array_equal(d._total_likelihood_mask, d0._total_likelihood_mask) and
+                     np.array_equal(d._allele_likelihood_mask, d0._allele_likelihood_mask) and
+                     d.transition_model == d0.transition_model and d.breakpoint_init is None for d in drivers)
+        if shared:      # the grid shares max_depth (analysis/pipeline.py:85-101): one upload serves every fit
+            batch.total_likelihood_mask = d0._total_likelihood_mask.astype(int)
+            batch.allele_likelihood_mask = d0._allele_likelihood_mask.astype(int)
+            batch.transition_model = d0.transition_model
+            for g, d in enumerate(drivers):
+                d.model = batch.fit(g)
+        else:
+            for g, d in enumerate(drivers):
+                d.attach(batch.fit(g))
     elbo = batch.calculate_elbo()
     for g, d in enumerate(drivers):
         d.prev_elbo = float(elbo[g])
     num_em_iter = get_param(config, 'num_em_iter')
     num_update_iter = get_param(config, 'num_update_iter')
-    errors = {}
+    errors = {}         # fit index -> exception
+    lock = _mstep.GridMStep(backend, drivers, errors)
+    prof['build'] += time.perf_counter() - t0
 
-    def m_step(slot):
+    def m_step_threads(slot):
         for g in range(slot, len(drivers), num_threads):
-            if ids[g] in errors:
+            if g in errors:
                 continue
             try:
                 if drivers[g].do_h_update:
                     drivers[g].em_update_h()
                 drivers[g].em_update_params()
             except Exception as e:   # a failed initialisation must not take the grid down
-                errors[ids[g]] = e
+                errors[g] = e
 
-    nt = max(1, min(num_threads, len(drivers)))
     for i in range(num_em_iter):
+        t0 = time.perf_counter()
         batch.variational_update(num_update_iter)
-        if nt == 1:
-            m_step(0)
+        t1 = time.perf_counter()
+        if mstep == 'lockstep':
+            lock.run()
         else:
-            threads = [threading.Thread(target=m_step, args=(s,)) for s in range(nt)]
+            nt = max(1, min(num_threads, len(drivers)))
+            threads = [threading.Thread(target=m_step_threads, args=(s,)) for s in range(nt)]
             for t in threads:
                 t.start()
             for t in threads:
                 t.join()
+        t2 = time.perf_counter()
         elbo = batch.calculate_elbo()
         for g, d in enumerate(drivers):
             d.record_iteration(i, float(elbo[g]))
+        t3 = time.perf_counter()
+        prof['e_step'] += t1 - t0
+        prof['m_step'] += t2 - t1
+        prof['elbo'] += t3 - t2
+    t0 = time.perf_counter()
     cn = np.zeros((len(drivers), batch.num_segments, batch.num_clones, 2), dtype=np.int64)
     batch.infer_cn(cn)
+    t1 = time.perf_counter()
     results = {}
     for g, d in enumerate(drivers):
-        if ids[g] not in errors:
+        if g not in errors:
             results[ids[g]] = _fit_results(d, experiment, init_params_by_id[ids[g]], config, cn[g])
+    prof['mstep_rounds'] = lock.rounds
+    prof['mstep_evaluations'] = lock.evaluations
     batch.close()       # results hold host arrays only; the device blocks go back to the pool now
-    if errors and not results:
-        raise next(iter(errors.values()))
+    errors_by_id = dict((ids[g], e) for g, e in errors.items())
+    if errors_by_id and not results:
+        raise next(iter(errors_by_id.values()))
     stats = dict((i, results[i]['stats']) for i in ids if i in results)
     best = select_solution(stats, config) if stats else None
-    return results, best, errors
+    prof['decode'] += t1 - t0
+    prof['results'] += time.perf_counter() - t1
+    return results, best, errors_by_id

@@ -1,7 +1,8 @@
 """N > 1 path on CPU: the init grid sharded over a world_size-2 gloo process group
-(remixt_b200.pipeline.fit_grid_distributed).  The model class is the compiled reference where
-built, else the numpy oracle -- the distribution logic under test is host code and does not depend
-on which RemixtModel implementation runs."""
+(remixt_b200.pipeline.fit_grid_distributed).  Every rank runs the real per-rank grid driver (fit_grid_batched: one
+grid object per rank, lock-step M-step); the model class is the compiled reference where built, else the numpy
+oracle -- the distribution logic under test is host code and does not depend on which RemixtModel implementation
+runs."""
 import os
 import socket
 import sys
@@ -46,8 +47,9 @@ def _worker(rank, world, port, out_dir):
     dist.init_process_group('gloo', init_method='tcp://127.0.0.1:%d' % port, rank=rank, world_size=world)
     exp = _experiment()
     inits = dict((i, util.init_params('small', i)) for i in IDS)
-    results, stats, best = pipeline.fit_grid_distributed(exp, inits, CFG, dist=dist, num_threads=1,
-                                                         model_class=_model_class())
+    results, stats, best, errors = pipeline.fit_grid_distributed(exp, inits, CFG, dist=dist,
+                                                                 model_class=_model_class())
+    assert not errors
     np.save(os.path.join(out_dir, 'r%d.npy' % rank),
             np.array([best] + [stats[i]['elbo'] for i in IDS] + sorted(results.keys())))
     dist.barrier()
@@ -69,7 +71,6 @@ def test_grid_sharded_over_two_gloo_ranks(tmp_path):
     # and the result equals the single-process grid
     exp = _experiment()
     inits = dict((i, util.init_params('small', i)) for i in IDS)
-    _, stats, best = pipeline.fit_grid_distributed(exp, inits, CFG, dist=None, num_threads=1,
-                                                   model_class=_model_class())
+    _, stats, best, _ = pipeline.fit_grid_distributed(exp, inits, CFG, dist=None, model_class=_model_class())
     assert best == int(r0[0])
     assert np.array_equal(np.array([stats[i]['elbo'] for i in IDS]), r0[1:1 + len(IDS)])

@@ -86,24 +86,31 @@ def test_segment_remap_matches_reference(ref_cn_model, name):
 
 
 @pytest.mark.slow
-def test_host_driver_full_fit_on_reference_model_is_bit_exact(ref_bpmodel):
-    """pipeline.fit of this repo (host driver) on the compiled reference RemixtModel == the reference's
-    own pipeline.fit (golden fit_small.npz): the host side adds no numerical difference of its own."""
+def test_host_grid_driver_full_fits_on_reference_model_are_bit_exact(ref_bpmodel):
+    """This repo's grid driver (pipeline.fit_grid_batched: lock-step M-step, per-fit RandomState) on the compiled
+    reference RemixtModel == the reference's own free-running pipeline.fit per initialisation (golden
+    grid_small.npz): the host side adds no numerical difference of its own, and the initialisation the reference
+    fails on (L-BFGS-B line search, cn_model.py:520) fails here too and leaves the grid."""
     from remixt_b200 import pipeline
-    g = util.golden('fit_small.npz')
+    g = util.golden('grid_small.npz')
     exp = util.load_experiment('small')
-    ip = util.init_params('small', int(g['init_id']))
+    failed = int(g['failed_ids'][0])
+    ids = [1, failed]
+    inits = dict((i, util.init_params('small', i)) for i in ids)
     cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
-    np.random.seed(1234)
-    res = pipeline.fit(exp, ip, cfg, model_class=ref_bpmodel.RemixtModel)
-    assert res['stats']['elbo'] == float(g['elbo'])
-    assert np.array_equal(res['h'], g['h'])
-    assert np.array_equal(res['cn'], g['cn'])
-    ids = [str(i) for i in g['brk_ids']]
-    assert np.array_equal(np.array([res['brk_cn'][i] for i in ids]), g['brk_cn'])
-    for k in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
-        assert res['stats'][k] == float(g[k]), k
-    assert np.array_equal(res['p_outlier_total'], g['p_outlier_total'])
+    res, best, errors = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']),
+                                                  model_class=ref_bpmodel.RemixtModel)
+    assert list(errors) == [failed] and 'optimization failed' in str(errors[failed])
+    assert list(res) == [1] and best == 1
+    k = list(g['init_ids']).index(1)
+    r = res[1]
+    assert r['stats']['elbo'] == float(g['elbo'][k])
+    assert np.array_equal(r['h'], g['h'][k])
+    assert np.array_equal(r['cn'], g['cn'][k])
+    assert np.array_equal(np.array([r['brk_cn'][str(i)] for i in g['brk_ids']]), g['brk_cn'][k])
+    assert [r['stats'][n] for n in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')] == list(g['params'][k])
+    assert [bool(a) for _, a in r['decisions']] == [bool(a) for a in g['accept'][k].ravel()]
+    assert r['stats']['proportion_divergent'] == float(g['proportion_divergent'][k])
 
 
 def test_select_solution_rule():
