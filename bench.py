@@ -4,19 +4,20 @@
 
 Workload: a simulated whole genome (tests/golden/exp_<workload>.npz, produced by the reference's own
 simulator, oracle/make_inputs.py) fitted from every initialisation of the reference's (h, ploidy) grid
-(stored in the same fixture by oracle/make_golden.py init).  One *step* is one E-step of the EM loop for
-the whole grid: the likelihood table for the current (h, dispersions), `num_update_iter` (5,
-remixt/defaults.py:157) rounds of the five coordinate updates (cn_model.py:444-460) and the ELBO
-(cn_model.py:418), for all G fits.
+(stored in the same fixture by oracle/make_golden.py init).  One *step* is one EM iteration of the whole grid
+(cn_model.py:409-419): `num_update_iter` (5, remixt/defaults.py:157) rounds of the five coordinate updates
+(cn_model.py:444-460) on the likelihood table of the current (h, dispersions), the M-step -- update_h (L-BFGS-B) and
+update_param for the four dispersions (brute grid + Nelder-Mead), cn_model.py:482-569 -- and the ELBO, for all G fits.
 
     value = N1 * S * num_update_iter * G_total / step_time      [segment-state evals / s]
 
-`value` has all inputs resident in HBM; `e2e` builds every model from HOST arrays through the public
-RemixtModel constructor (H2D inside the timed region), runs the same E-step and reads ELBO + outlier
-posteriors + posterior marginals back to the host (D2H).
+`value` has the batch resident in HBM (built once, outside the timed region); `e2e` is the COMPLETE fit of the grid
+through the public API from HOST arrays: batch construction (H2D), num_em_iter (5) EM iterations, MAP decode, result
+assembly on the host (D2H) and the selection of the best initialisation; `full_fit` carries its wall time by phase.
 
-N > 1 (torchrun): the init grid is sharded over ranks (`ids[rank::world]`, no data-path collective;
-scaling = weak: every rank fits a full G-sized grid slice of its own).
+N > 1 (torchrun): the init grid is SPLIT over the ranks (`ids[rank::world]`, one RemixtBatch per rank, no data-path
+collective; the per-fit stats are gathered once for the selection): scaling = strong, G_total fixed at the grid size.
+`replicas` repeats the resident measurement with every rank holding the whole grid (weak, round 1's number).
 """
 import argparse
 import json
@@ -34,6 +35,7 @@ if ROOT not in sys.path:
 
 GOLDEN = os.path.join(ROOT, 'tests', 'golden')
 NUM_UPDATE_ITER = 5
+NUM_EM_ITER = 5
 METRIC = 'segment_state_evals_per_s'
 UNIT = 'segment-state evals/s'
 
@@ -48,6 +50,7 @@ def parse_args():
     ap.add_argument('--fits', type=int, default=0, help='fits per GPU (0 = the whole init grid)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--cpu-sample-segments', type=int, default=400)
+    ap.add_argument('--no-replicas', action='store_true', help='N > 1: skip the secondary replica (weak) measurement')
     return ap.parse_args()
 
 
@@ -60,11 +63,28 @@ def pick_workload(name):
     raise SystemExit('no workload fixture under tests/golden')
 
 
+class PlainExperiment(object):
+    """The attributes pipeline.init / pipeline.fit read, over the fixture's plain arrays.  Defined here (and not
+    taken from remixt_b200.pipeline) so that the reference arm never imports the package under test."""
+
+    def __init__(self, x, l, adjacencies, breakpoints, breakpoint_ids, chromosome):
+        self.x = np.asarray(x, dtype=float)
+        self.l = np.asarray(l, dtype=float)
+        self.adjacencies = set((int(a), int(b)) for a, b in np.asarray(adjacencies).reshape(-1, 2))
+        self.breakpoints = dict()
+        for bp_id, (n1, s1, n2, s2) in zip(breakpoint_ids, np.asarray(breakpoints).reshape(-1, 4)):
+            self.breakpoints[str(bp_id)] = frozenset([(int(n1), int(s1)), (int(n2), int(s2))])
+        self.segment_chromosome_id = np.asarray(chromosome)
+        n = self.l.shape[0]
+        self.segment_start = np.zeros(n, dtype=int)
+        self.segment_end = np.maximum(self.l.astype(int) - 1, 0)
+        self.segment_major_is_allele_a = np.ones(n, dtype=int)
+
+
 def load_workload(name):
-    from remixt_b200 import pipeline
     path = os.path.join(GOLDEN, 'exp_%s.npz' % name)
     d = np.load(path, allow_pickle=False)
-    exp = pipeline.ArrayExperiment.from_npz(path)
+    exp = PlainExperiment(d['x'], d['l'], d['adjacencies'], d['breakpoints'], d['breakpoint_ids'], d['chromosome'])
     exp._name = name
     inits = []
     for i in range(len(d['init_h_normal'])):
@@ -75,33 +95,35 @@ def load_workload(name):
     return exp, inits
 
 
-def subsample_experiment(exp, nseg):
-    """The first `nseg` segments of the workload with the adjacencies / breakpoints that lie wholly inside."""
-    from remixt_b200 import pipeline
-    nseg = min(nseg, exp.x.shape[0])
-    adj = np.array([(a, b) for a, b in sorted(exp.adjacencies) if a < nseg and b < nseg], dtype=np.int64).reshape(-1, 2)
-    ids, bps = [], []
-    for bp_id, bp in exp.breakpoints.items():
-        (n1, s1), (n2, s2) = tuple(bp)
-        if n1 < nseg and n2 < nseg and not (n1 == 0 and s1 == 0) and not (n2 == 0 and s2 == 0):
-            ids.append(bp_id)
-            bps.append((n1, s1, n2, s2))
-    return pipeline.ArrayExperiment(exp.x[:nseg], exp.l[:nseg], adj, np.array(bps, dtype=np.int64).reshape(-1, 4),
-                                    breakpoint_ids=ids, chromosome=exp.segment_chromosome_id[:nseg])
+def subsample_experiment(exp, nseg, start=None):
+    """A window of `nseg` consecutive segments of the workload with the adjacencies / breakpoints that lie wholly inside,
+    renumbered from 0.  start=None picks, among the windows starting at multiples of nseg, the one holding the most
+    breakpoints (the reference's BreakpointModel cannot be built without any, cn_model.py:59)."""
+    n_all = exp.x.shape[0]
+    nseg = min(nseg, n_all)
+
+    def inside(s0):
+        out = []
+        for bp_id, bp in exp.breakpoints.items():
+            (n1, s1), (n2, s2) = tuple(bp)
+            if (s0 <= n1 < s0 + nseg and s0 <= n2 < s0 + nseg and not (n1 == s0 and s1 == 0) and
+                    not (n2 == s0 and s2 == 0)):
+                out.append((bp_id, (n1 - s0, s1, n2 - s0, s2)))
+        return out
+
+    if start is None:
+        start = max(range(0, n_all - nseg + 1, nseg), key=lambda s0: (len(inside(s0)), -s0))
+    keep = inside(start)
+    adj = np.array([(a - start, b - start) for a, b in sorted(exp.adjacencies)
+                    if start <= a < start + nseg and start <= b < start + nseg], dtype=np.int64).reshape(-1, 2)
+    sub = PlainExperiment(exp.x[start:start + nseg], exp.l[start:start + nseg], adj,
+                          np.array([b for _, b in keep], dtype=np.int64).reshape(-1, 4), [i for i, _ in keep],
+                          exp.segment_chromosome_id[start:start + nseg])
+    sub._window = (int(start), int(nseg), len(keep))
+    return sub
 
 
-CONFIG = {'max_copy_number': 6, 'num_em_iter': 1, 'num_update_iter': NUM_UPDATE_ITER}
-
-
-def make_driver(exp, ip, model_class=None, device=None):
-    from remixt_b200 import pipeline
-    kw = {}
-    if model_class is not None:
-        kw['model_class'] = model_class
-    if device is not None:
-        kw['model_kwargs'] = {'device': device}
-    bm = pipeline.build_model(exp, ip, CONFIG, **kw)
-    return bm
+CONFIG = {'max_copy_number': 6, 'num_em_iter': NUM_EM_ITER, 'num_update_iter': NUM_UPDATE_ITER}
 
 
 class ClockSampler(object):
@@ -188,64 +210,34 @@ def dist_setup(n_gpus):
     return 0, 1, 0, None
 
 
-def run_threads(fns):
-    if len(fns) == 1:
-        fns[0]()
-        return
-    errs = []
-
-    def wrap(f):
-        try:
-            f()
-        except Exception as e:   # surfaced after join
-            errs.append(e)
-    ts = [threading.Thread(target=wrap, args=(f,)) for f in fns]
-    for t in ts:
-        t.start()
-    for t in ts:
-        t.join()
-    if errs:
-        raise errs[0]
-
-
-def build_batch(exp, inits, device):
-    """One RemixtBatch for the given initialisations, built from HOST arrays through the public constructor
-    (the H2D copies happen inside), with the per-fit likelihood masks and transition model applied."""
-    from remixt_b200 import bpmodel, pipeline
-    drivers = [pipeline.build_model(exp, ip, CONFIG) for ip in inits]
+def grid_batch(exp, inits, device, random_seed=1234):
+    """One RemixtBatch for the given initialisations with its host drivers and lock-step M-step, built from HOST arrays
+    through the public constructor (the H2D copies happen inside) exactly as pipeline.fit_grid_batched builds it."""
+    from remixt_b200 import bpmodel, mstep, pipeline
+    drivers = [pipeline.build_model(exp, ip, CONFIG, random_state=np.random.RandomState(random_seed)) for ip in inits]
     h = np.array([pipeline.init_h(ip) for ip in inits])
     dw = np.array([ip['divergence_weight'] for ip in inits], dtype=float)
     args = drivers[0].model_args(h, compact=True) + (dw,)
     batch = bpmodel.RemixtBatch(*args, device=device)
-    same_masks = all(np.array_equal(d._total_likelihood_mask, drivers[0]._total_likelihood_mask) and
-                     np.array_equal(d._allele_likelihood_mask, drivers[0]._allele_likelihood_mask) for d in drivers)
-    if same_masks:       # max_depth is shared by the grid (analysis/pipeline.py:90-96): one upload for all fits
-        batch.total_likelihood_mask = drivers[0]._total_likelihood_mask.astype(int)
-        batch.allele_likelihood_mask = drivers[0]._allele_likelihood_mask.astype(int)
-        batch.transition_model = drivers[0].transition_model
-        for g, d in enumerate(drivers):
-            d.model = batch.fit(g)
-    else:
-        for g, d in enumerate(drivers):
-            d.attach(batch.fit(g))
-    h2d = sum(int(np.asarray(a).nbytes) for a in args if isinstance(a, np.ndarray)) + 2 * 8 * batch.num_segments * len(inits)
+    batch.total_likelihood_mask = drivers[0]._total_likelihood_mask.astype(int)      # the grid shares max_depth
+    batch.allele_likelihood_mask = drivers[0]._allele_likelihood_mask.astype(int)
+    batch.transition_model = drivers[0].transition_model
+    for g, d in enumerate(drivers):
+        d.model = batch.fit(g)
+    lock = mstep.GridMStep(mstep.BatchBackend(batch), drivers, {})
+    h2d = sum(int(np.asarray(a).nbytes) for a in args if isinstance(a, np.ndarray)) + 2 * 8 * batch.num_segments
     h2d += sum(int(a.table.nbytes + a.normal_copies.nbytes) for a in args if isinstance(a, bpmodel.CompactCnStates))
-    return batch, drivers, h2d
+    return batch, drivers, lock, h2d
 
 
-LLTABLE_CONVENTION_OPS = 900.
-NCU_DRAM_BYTES_PER_UNIT = {'chain': 29.0, 'lltable': 48.8, 'round': 89.1}
-
-
-# algorithmic work per (segment, state) of each kernel class: (bound, bytes, fp64 ops)  -- DESIGN.md, Kernels
+# algorithmic work per launch of each kernel class: (bound, bytes, fp64 flop)  -- DESIGN.md, Kernels
 def kernel_models(N1, S, NC, G, R):
     ns = float(N1) * S * G
     return {
         'chain': ('fp64', 32. * ns, 2. * 2. * S * S * (N1 - NC) * G),
-        # 200 executed FP64-pipe instructions per (n,s) (ncu: dadd + dmul + dfma thread instructions of k_lltable2,
-        # profiles/r01_summary.md), each counted as one FMA = 2 flop; SURVEY.md 8d's convention for the reference-minimal
-        # evaluation (12 lgamma + 4 log = 900 op-equivalents) is reported next to it (LLTABLE_CONVENTION_OPS)
-        'lltable': ('fp64', 48. * ns, 400. * ns),
+        # executed FP64-pipe instructions per (n,s) of the likelihood kernel (ncu: dadd + dmul + dfma thread
+        # instructions, profiles/), each counted as one FMA = 2 flop
+        'lltable': ('fp64', 48. * ns, 2. * LLTABLE_FP64_INSTR * ns),
         'frame': ('hbm', 64. * ns, 14. * ns),
         'qsums': ('hbm', 56. * ns, 12. * ns),
         'post': ('hbm', 24. * ns, 3. * ns),
@@ -255,108 +247,137 @@ def kernel_models(N1, S, NC, G, R):
     }
 
 
+LLTABLE_FP64_INSTR = 200.
+NCU_DRAM_BYTES_PER_UNIT = {'chain': 29.0, 'lltable': 48.8, 'round': 89.1}
+
+
+def result_bytes(results):
+    n = 0
+    for r in results.values():
+        for k in ('h', 'cn', 'p_outlier_total', 'p_outlier_allele', 'total_likelihood_mask', 'allele_likelihood_mask'):
+            n += int(np.asarray(r[k]).nbytes)
+        n += sum(int(np.asarray(v).nbytes) for v in r['brk_cn'].values())
+    return n
+
+
 def gpu_arm(args):
     rank, world, local, dist = dist_setup(args.gpus)
-    from remixt_b200 import _lib
+    from remixt_b200 import _lib, pipeline
     if _lib.device_count() <= 0:
         raise SystemExit('bench.py: no CUDA device; remixt_b200 has no CPU fallback')
     name = pick_workload(args.workload)
     exp, inits = load_workload(name)
-    G = args.fits if args.fits > 0 else len(inits)
-    # weak scaling: every rank fits G initialisations (its own rotation of the grid)
-    my_inits = [inits[(rank * G + g) % len(inits)] for g in range(G)]
+    if args.fits > 0:
+        inits = inits[:args.fits]
+    G_total = len(inits)
+    ids = list(range(G_total))
+    mine = pipeline.shard_ids(ids, rank, world)         # strong scaling: the grid is split over the ranks
+    my_inits = [inits[i] for i in mine]
+    G = len(my_inits)
     peaks, peak_src = measured_peaks()
 
-    # ---------------- resident arm: batch built once, inputs live in HBM
-    batch, drivers, h2d = build_batch(exp, my_inits, local)
-    N1, S = batch.num_segments, batch.num_cn_states
-    NC = int(np.sum(np.asarray(batch.is_telomere)[:-1] > 0)) + 1
-    R = int(np.sum(np.asarray(batch.breakpoint_idx)[:-1] >= 0))
-    state = {}
-
-    h_cur = np.array(batch.h)
-
-    def estep():
-        # every EM iteration of the reference starts from a new h / dispersions (cn_model.py:411-416), so the
-        # likelihood table of every fit is rebuilt once per step: writing h marks it stale
-        batch.h = h_cur
-        batch.variational_update(NUM_UPDATE_ITER)
-        state['elbo'] = batch.calculate_elbo()
-
-    def barrier():
-        batch.synchronize()
+    def barrier(batch=None):
+        if batch is not None:
+            batch.synchronize()
         if dist is not None:
-            dist.barrier()
             import torch
+            dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        estep()
-    sampler = ClockSampler(local)
-    sampler.start()
-    barrier()
-    batch.kernel_timing(True)
-    l0 = _lib.global_launch_count()
-    batch.event_record(0)
-    for _ in range(args.steps):
-        estep()
-    batch.event_record(1)
-    barrier()
-    ms = batch.event_elapsed(0, batch, 1)
-    launches = _lib.global_launch_count() - l0
-    ktime = batch.kernel_timing(False)
-    clocks = sampler.stop()
+    # ---------------- resident arm: the rank's batch built once, every step = one EM iteration of its fits
+    def resident(fit_inits, steps, warmup, sample_clocks):
+        batch, drivers, lock, h2d = grid_batch(exp, fit_inits, local)
 
-    # ---------------- e2e arm: the batch rebuilt from host arrays every step, results read back to the host
-    def e2e_step():
-        b2, d2, _ = build_batch(exp, my_inits, local)
-        b2.variational_update(NUM_UPDATE_ITER)
-        elbo = b2.calculate_elbo()
-        cn = np.zeros((G, b2.num_segments, b2.num_clones, 2), dtype=np.int64)
-        b2.infer_cn(cn)
-        out = (elbo, cn, b2.p_outlier_total, b2.p_outlier_allele, b2.h)
-        b2.close()      # device blocks back to the pool now: the next step's batch reuses them
-        return sum(int(np.asarray(o).nbytes) for o in out)
+        def em_iteration():
+            batch.variational_update(NUM_UPDATE_ITER)
+            t0 = time.perf_counter()
+            lock.run()
+            em_iteration.m_s += time.perf_counter() - t0
+            return batch.calculate_elbo()
+        em_iteration.m_s = 0.
 
-    del state['elbo']
-    d2h = e2e_step()
-    e2e_steps = max(1, min(args.steps, 5))
-    barrier()
-    e2e_times = []
-    for _ in range(e2e_steps):
+        for _ in range(warmup):
+            em_iteration()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        barrier(batch)
+        batch.kernel_timing(True)
+        em_iteration.m_s = 0.
+        r0, e0, l0 = lock.rounds, lock.evaluations, _lib.global_launch_count()
+        batch.event_record(0)
+        for _ in range(steps):
+            elbo = em_iteration()
+        batch.event_record(1)
+        barrier(batch)
+        out = dict(ms=batch.event_elapsed(0, batch, 1), launches=_lib.global_launch_count() - l0,
+                   ktime=batch.kernel_timing(False), clocks=sampler.stop() if sampler else None,
+                   m_step_ms=em_iteration.m_s * 1e3, mstep_rounds=lock.rounds - r0, mstep_evals=lock.evaluations - e0,
+                   N1=batch.num_segments, S=batch.num_cn_states, K=batch.num_breakpoints,
+                   NC=int(np.sum(np.asarray(batch.is_telomere)[:-1] > 0)) + 1,
+                   R=int(np.sum(np.asarray(batch.breakpoint_idx)[:-1] >= 0)), h2d=h2d,
+                   elbo_checksum=float(np.sum(elbo)), errors=len(lock.errors))
+        batch.close()
+        return out
+
+    res = resident(my_inits, args.steps, args.warmup, True)
+    N1, S, NC, R = res['N1'], res['S'], res['NC'], res['R']
+
+    # ---------------- e2e: the complete fit of the rank's share of the grid from host arrays, through the public API
+    full = []
+    n_full = max(1, min(args.steps, 3))
+    for rep in range(n_full + 1):            # first run untimed (pool warm-up)
+        prof = {}
+        barrier()
         t0 = time.perf_counter()
-        e2e_step()
-        e2e_times.append(time.perf_counter() - t0)
-    # the median step: a host hiccup (page faults of a fresh box, another tenant on the host cores) lands on one step
-    # of a handful and would otherwise own the mean; all step times are reported next to it
-    e2e_s = float(np.median(e2e_times))
+        results, stats, best, errors = pipeline.fit_grid_distributed(exp, dict(enumerate(inits)), CONFIG, dist=dist,
+                                                                     device=local, profile=prof)
+        wall = time.perf_counter() - t0
+        if rep > 0:
+            full.append((wall, prof, best, len(errors)))
+    d2h = result_bytes(results)
+    full.sort(key=lambda t: t[0])
+    wall, prof, best, n_err = full[len(full) // 2]
 
+    rep_res = None
+    if world > 1 and not args.no_replicas:
+        rep_res = resident(inits, max(1, min(args.steps, 3)), 1, False)
+
+    ms, launches, m_ms = res['ms'], res['launches'], res['m_step_ms']
     if dist is not None:
         import torch
-        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device='cuda')
+        vals = [ms, wall, m_ms] + ([rep_res['ms']] if rep_res else [])
+        t = torch.tensor(vals, dtype=torch.float64, device='cuda')
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = float(t[0]), float(t[1])
-        tl = torch.tensor([launches], dtype=torch.int64, device='cuda')
+        ms, wall, m_ms = float(t[0]), float(t[1]), float(t[2])
+        if rep_res:
+            rep_res['ms'] = float(t[3])
+        tl = torch.tensor([launches, d2h, res['h2d']], dtype=torch.int64, device='cuda')
         dist.all_reduce(tl)
-        launches = int(tl[0])
+        launches, d2h, h2d = int(tl[0]), int(tl[1]), int(tl[2])
+    else:
+        h2d = res['h2d']
     ms_per_step = ms / args.steps
-    evals = float(N1) * S * NUM_UPDATE_ITER * G * world
-    value = evals / (ms_per_step * 1e-3)
+    evals_step = float(N1) * S * NUM_UPDATE_ITER * G_total
+    value = evals_step / (ms_per_step * 1e-3)
 
-    # ---------------- rooflines from the CUDA-event durations of the timed region
+    # ---------------- rooflines from the CUDA-event durations of the timed region (this rank's launches)
     try:
         fp64_peak = _lib.fp64_peak(local)
     except Exception:
         fp64_peak = None
     hbm_peak = peaks.get('hbm_gbs')
     models = kernel_models(N1, S, NC, G, R)
+    ktime = res['ktime']
     total_kernel_ms = sum(v[0] for v in ktime.values())
     kernels = {}
     for k, (tot, n) in ktime.items():
         if n == 0:
             continue
         ent = {'launches': n, 'ms_per_launch': tot / n, 'share_of_kernel_time': tot / total_kernel_ms}
-        if k in models:
+        # launches of the M-step's full-data evaluations rebuild the table for the fits whose parameters changed
+        # only, so per-launch work varies: rates are quoted for the E-step classes, whose launches are uniform
+        if k in models and k not in ('qsums',):
             bound, nbytes, flops = models[k]
             t_s = tot / n * 1e-3
             ent['bound'] = bound
@@ -364,10 +385,9 @@ def gpu_arm(args):
             ent['tflops'] = flops / t_s / 1e12
             ent['hbm_frac'] = ent['gbs'] / hbm_peak if hbm_peak else None
             ent['fp64_frac'] = ent['tflops'] / fp64_peak if fp64_peak else None
-            if k == 'lltable' and fp64_peak:
-                ent['fp64_frac_survey_convention_900'] = ent['tflops'] * (LLTABLE_CONVENTION_OPS / 400.) / fp64_peak
         kernels[k] = ent
-    dom = max(kernels, key=lambda k: kernels[k]['share_of_kernel_time'] if k in models else -1.)
+    rated = [k for k in kernels if 'bound' in kernels[k] and k != 'lltable']
+    dom = max(rated, key=lambda k: kernels[k]['share_of_kernel_time'])
     de = kernels[dom]
     if de['bound'] == 'hbm':
         roofline = {'kernel': dom, 'bound': 'hbm', 'achieved': de['gbs'], 'peak': hbm_peak, 'unit': 'GB/s',
@@ -377,31 +397,47 @@ def gpu_arm(args):
                     'frac': de['fp64_frac'], 'traffic': None,
                     'peak_source': 'FP64 FMA micro-benchmark run in this process (rmx_fp64_peak); not in MEASURED_PEAKS.json',
                     'hbm_achieved_gbs': de['gbs'], 'hbm_peak_gbs': hbm_peak, 'hbm_frac': de['hbm_frac']}
-    # DRAM bytes per launch of the dominant kernel from its `ncu --set full` capture (dram__bytes_read.sum +
-    # dram__bytes_write.sum of an 8-fit launch, profiles/r01_summary.md), carried per (segment, state) unit
     if dom in NCU_DRAM_BYTES_PER_UNIT:
         roofline['traffic'] = NCU_DRAM_BYTES_PER_UNIT[dom] * float(N1) * S * G
-        roofline['traffic_source'] = 'ncu capture of an 8-fit launch, %.1f B per (segment, state)' % NCU_DRAM_BYTES_PER_UNIT[dom]
+        roofline['traffic_source'] = 'ncu --set full capture, %.1f B per (segment, state)' % NCU_DRAM_BYTES_PER_UNIT[dom]
     roofline['launch_ms'] = de['ms_per_launch']
-    roofline['share_of_step'] = de['ms_per_launch'] * de['launches'] / ms
+    roofline['share_of_step'] = de['ms_per_launch'] * de['launches'] / res['ms']
+    roofline['fits_per_launch'] = G
+
+    e_ms = (res['ms'] - res['m_step_ms']) / args.steps
+    evals_fit = evals_step * NUM_EM_ITER
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None,
         'dtype': 'f64', 'data': 'synthetic (remixt.simulations genome, fixture exp_%s.npz)' % name,
         'config': {'workload': name, 'segments': int(exp.x.shape[0]), 'model_segments': int(N1), 'cn_states': int(S),
-                   'breakpoints': int(batch.num_breakpoints), 'chains': NC, 'fits_per_gpu': G,
+                   'breakpoints': int(res['K']), 'chains': NC, 'fits_total': G_total, 'fits_per_gpu': G,
+                   'step': 'one EM iteration of every fit: %d VI rounds + M-step (h, 4 dispersions) + ELBO' % NUM_UPDATE_ITER,
                    'vi_updates_per_step': NUM_UPDATE_ITER,
                    'l2': 'inputs larger than L2: per-step working set %.1f GB vs 126 MB' % (G * N1 * S * 8 * 11 / 1e9)},
-        'em_iterations_per_s': G * world / (ms_per_step * 1e-3),
-        'clocks': clocks, 'gpu_launches': int(launches),
-        'e2e': {'value': evals / e2e_s, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
-                'ms_per_step': e2e_s * 1e3, 'statistic': 'median of %d steps' % e2e_steps,
-                'ms_all_steps': [round(t * 1e3, 1) for t in e2e_times]},
+        'em_iterations_per_s': G_total / (ms_per_step * 1e-3),
+        'e_step_ms_per_step': e_ms, 'm_step_ms_per_step': m_ms / args.steps,
+        'e_steps_per_s': G_total / (e_ms * 1e-3),
+        'mstep': {'rounds_per_step': res['mstep_rounds'] / args.steps, 'evaluations_per_step': res['mstep_evals'] / args.steps},
+        'clocks': res['clocks'], 'gpu_launches': int(launches),
+        'e2e': {'value': evals_fit / wall, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
+                'ms_per_step': wall * 1e3,
+                'step': 'the complete fit of the grid from host arrays: construction, %d EM iterations, MAP decode, '
+                        'results on the host, selection' % NUM_EM_ITER,
+                'statistic': 'median of %d fits' % n_full, 'wall_s_all': [round(f[0], 4) for f in full]},
+        'full_fit': {'wall_s': wall, 'em_iterations_per_s': G_total * NUM_EM_ITER / wall,
+                     'e_step_share': prof['e_step'] / wall, 'm_step_share': prof['m_step'] / wall,
+                     'phases_s': dict((k, v) for k, v in prof.items() if isinstance(v, float)),
+                     'mstep_seconds': prof.get('mstep_seconds'), 'selected_init': best, 'failed_inits': n_err,
+                     'inits': G_total, 'num_em_iter': NUM_EM_ITER, 'num_update_iter': NUM_UPDATE_ITER},
         'roofline': roofline, 'kernels': kernels,
-        'elbo_checksum': float(np.sum(batch.calculate_elbo())),
+        'elbo_checksum': res['elbo_checksum'],
     }
+    if rep_res:
+        line['replicas'] = {'scaling': 'weak', 'fits_per_gpu': G_total, 'ms_per_step': rep_res['ms'] / max(1, min(args.steps, 3)),
+                            'value': evals_step * world / (rep_res['ms'] / max(1, min(args.steps, 3)) * 1e-3)}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line['cpu_baseline'] = cpu_baseline(exp, inits, args.cpu_sample_segments, budget_s=20.)
+        line['cpu_baseline'] = cpu_baseline(name, args.cpu_sample_segments)
     if rank == 0:
         print(json.dumps(line))
     if dist is not None:
@@ -409,73 +445,106 @@ def gpu_arm(args):
 
 
 # ---------------------------------------------------------------------------------------------
-# reference arm: the compiled UNMODIFIED reference extension (oracle/_ref) on the host cores
+# reference arm: the UNMODIFIED reference (its own cn_model.py driving its own compiled bpmodel.pyx, both under
+# oracle/_ref) on the host cores.  Nothing of remixt_b200 is imported here.
 # ---------------------------------------------------------------------------------------------
 _W = {}
 
 
-def _ref_worker_init(name, nseg, n_workers):
+def _ref_worker_init(name, nseg):
+    import contextlib
+    import io
+    import warnings
     from oracle import refenv
-    from remixt_b200 import pipeline   # host driver only; the model class below is the reference's
-    ref = refenv.load_ref_bpmodel()
     kind = 'reference'
-    if ref is None:
-        from oracle import bpmodel_np as ref   # the oracle port
-        kind = 'port'
+    rcn = None
+    import glob
+    if refenv.available() and glob.glob(os.path.join(refenv.BIN_PKG, 'bpmodel*.so')):
+        refenv.install()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            import remixt.cn_model as rcn
     exp, inits = load_workload(name)
-    sub = subsample_experiment(exp, nseg)
-    _W.update(ref=ref, kind=kind, sub=sub, inits=inits, pipeline=pipeline)
+    _W.update(kind=kind, rcn=rcn, sub=subsample_experiment(exp, nseg), inits=inits, quiet=lambda: contextlib.redirect_stdout(io.StringIO()))
 
 
 def _ref_worker_build(idx):
     ip = _W['inits'][idx % len(_W['inits'])]
-    d = make_driver(_W['sub'], ip, model_class=_W['ref'].RemixtModel)
-    d.prepare(_W['pipeline'].init_h(ip))
-    _W['driver'] = d
-    return (d.model.num_segments, d.model.num_cn_states, _W['kind'])
+    sub = _W['sub']
+    h = np.array([ip['h_normal'], ip['h_tumour'] * ip['mix_frac'], ip['h_tumour'] * (1. - ip['mix_frac'])])
+    kw = dict(max_copy_number=6, normal_contamination=True, divergence_weight=ip['divergence_weight'],
+              min_segment_length=10000, min_proportion_genotyped=0.01, max_depth=ip['max_depth'],
+              normal_copies=np.array([[1, 1]] * sub.l.shape[0]))
+    if _W['rcn'] is not None:
+        bm = _W['rcn'].BreakpointModel(sub.x, sub.l, sub.adjacencies, sub.breakpoints, **kw)
+    else:           # no compiled reference on this box: the oracle port under this repo's host mirror
+        from oracle import bpmodel_np
+        from remixt_b200 import cn_model
+        _W['kind'] = 'port'
+        bm = cn_model.BreakpointModel(sub.x, sub.l, sub.adjacencies, sub.breakpoints, model_class=bpmodel_np.RemixtModel, **kw)
+    bm.num_em_iter = 0
+    np.random.seed(1234)
+    with _W['quiet']():
+        bm.fit(h)           # builds the RemixtModel, masks, first ELBO (cn_model.py:354-407)
+    _W['bm'] = bm
+    return (bm.model.num_segments, bm.model.num_cn_states, _W['kind'])
 
 
 def _ref_worker_step(idx):
-    if 'driver' not in _W:          # pool.map does not pin one build task to every worker
+    """One EM iteration, the loop body of BreakpointModel.fit (cn_model.py:409-419), through the reference's own methods."""
+    if 'bm' not in _W:          # pool.map does not pin one build task to every worker
         _ref_worker_build(idx)
-    m = _W['driver'].model
-    for _ in range(NUM_UPDATE_ITER):
-        m.update_p_allele_swap()
-        m.update_p_cn()
-        m.update_p_breakpoint()
-        m.update_p_outlier_total()
-        m.update_p_outlier_allele()
-    return m.calculate_elbo()
+    bm = _W['bm']
+    t0 = time.perf_counter()
+    with _W['quiet']():
+        for _ in range(NUM_UPDATE_ITER):
+            bm.variational_update()
+        t1 = time.perf_counter()
+        bm.em_update_h()
+        bm.em_update_params()
+        elbo = bm.model.calculate_elbo()
+    return (elbo, t1 - t0, time.perf_counter() - t1)
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def reference_run(name, nseg, steps, warmup, cores=None):
     import multiprocessing as mp
-    if cores is None:
-        try:
-            cores = len(os.sched_getaffinity(0))
-        except AttributeError:
-            cores = os.cpu_count() or 1
+    cores = cores or host_cores()
     # the reference holds 3 (N-1,S,S) arrays per model: ~0.23 MB per segment at S=97
     ctx = mp.get_context('spawn')
-    with ctx.Pool(cores, initializer=_ref_worker_init, initargs=(name, nseg, cores)) as pool:
+    with ctx.Pool(cores, initializer=_ref_worker_init, initargs=(name, nseg)) as pool:
         info = pool.map(_ref_worker_build, range(cores), chunksize=1)
         N1, S, kind = info[0]
         for _ in range(warmup):
             pool.map(_ref_worker_step, range(cores), chunksize=1)
         t0 = time.perf_counter()
+        parts = []
         for _ in range(steps):
-            pool.map(_ref_worker_step, range(cores), chunksize=1)
+            parts += pool.map(_ref_worker_step, range(cores), chunksize=1)
         dt = (time.perf_counter() - t0) / max(steps, 1)
     evals = float(N1) * S * NUM_UPDATE_ITER * cores
+    e_s = float(np.mean([p[1] for p in parts]))
+    m_s = float(np.mean([p[2] for p in parts]))
     return {'value': evals / dt, 'unit': UNIT, 'cores': cores, 'kind': kind, 'ms_per_step': dt * 1e3,
-            'sample': 'first %d segments of %s (%d model segments, S=%d), one fit per core, %d VI rounds + ELBO per step'
-                      % (nseg, name, N1, S, NUM_UPDATE_ITER)}
+            'e_step_s_per_fit': e_s, 'm_step_s_per_fit': m_s,
+            # one fit on one core: the reference is single threaded (its workflow fans inits out over processes)
+            'single_core': {'value': float(N1) * S * NUM_UPDATE_ITER / (e_s + m_s), 'unit': UNIT,
+                            's_per_em_iteration': e_s + m_s},
+            'sample': '%d consecutive segments of %s holding the most breakpoints (%d model segments, S=%d), one fit per '
+                      'core on %d cores, step = one EM iteration (%d VI rounds + M-step + ELBO) by the reference\'s own '
+                      'cn_model.py on its compiled bpmodel' % (nseg, name, N1, S, cores, NUM_UPDATE_ITER)}
 
 
-def cpu_baseline(exp, inits, nseg, budget_s=20.):
+def cpu_baseline(name, nseg):
     """Bounded CPU sample inside the default run: ONE step of the reference on every host core."""
     try:
-        return reference_run(exp._name, nseg, steps=1, warmup=0)
+        return reference_run(name, nseg, steps=1, warmup=0)
     except Exception as e:
         return {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'unavailable', 'sample': repr(e)}
 
@@ -486,14 +555,21 @@ def reference_arm(args):
         return
     name = pick_workload(args.workload)
     r = reference_run(name, args.cpu_sample_segments, args.steps, args.warmup)
+    exp, inits = load_workload(name)
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': r['value'], 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': r['ms_per_step'], 'higher_is_better': True,
-        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
         'data': 'synthetic (remixt.simulations genome, fixture exp_%s.npz)' % name,
-        'config': {'workload': name, 'vi_updates_per_step': NUM_UPDATE_ITER, 'sample_segments': args.cpu_sample_segments},
-        'cpu_baseline': {'value': r['value'], 'unit': UNIT, 'cores': r['cores'], 'kind': r['kind'], 'sample': r['sample']},
+        'config': {'workload': name, 'vi_updates_per_step': NUM_UPDATE_ITER, 'sample_segments': args.cpu_sample_segments,
+                   'step': 'one EM iteration: %d VI rounds + M-step (h, 4 dispersions) + ELBO' % NUM_UPDATE_ITER},
+        'cpu_baseline': dict((k, r[k]) for k in ('value', 'unit', 'cores', 'kind', 'sample', 'single_core',
+                                                 'e_step_s_per_fit', 'm_step_s_per_fit')),
         'e2e': {'value': r['value'], 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        # the full config-2 grid at this rate (stated extrapolation: per-(segment,state) cost of the reference is
+        # flat in N; the M-step's 200-row samples are 42 rows on this sample, which flatters the CPU)
+        'full_fit_extrapolated': {'wall_s': float(exp.x.shape[0]) * 1.0035 * 97 * NUM_UPDATE_ITER * NUM_EM_ITER * len(inits) / r['value'],
+                                  'inits': len(inits), 'cores': r['cores']},
         'gpu_launches': 0,
     }
     print(json.dumps(line))

@@ -205,8 +205,21 @@ int rmx_expected_log_likelihood_grid(rmx_handle h, const int64_t* sample, int sc
  *            reference's point-by-point evaluation leaves it (cn_model.py:544).  scalar_id < 0: n_values must be 1.
  *   ell (gn,n_values), grad (gn,M) or NULL. */
 int rmx_mstep_stage_sample(rmx_handle h, const int64_t* sample);
+/* The same from row lists: rows (gn,max_rows) int32 segment indices, fit g uses its first counts[g] entries, in the
+ * order given (ascending order = the order of the mask form, hence the same rounding of the sums). */
+int rmx_mstep_stage_rows(rmx_handle h, const int32_t* rows, const int32_t* counts, int max_rows);
 int rmx_mstep_evaluate(rmx_handle h, const uint8_t* active, const double* h_values, int scalar_id,
                        const double* values, int n_values, double* ell, double* grad);
+/* The segment samples of the M-step for all fits at once, on HOST threads (no device work): for draw d and fit g,
+ * numpy.random.RandomState.choice(n, size, replace=False, p=weights[d][g]) of cn_model.py:475-480, consuming the fit's
+ * own MT19937 stream exactly as numpy's (frozen) legacy algorithm does.  mt_key (num_fits,624) / mt_pos (num_fits) are the
+ * streams' states (RandomState.get_state()), updated in place; weights (num_draws,num_fits,n) with weighted
+ * (num_draws,num_fits) flags (0 = uniform, p=None); chosen (num_draws,num_fits,size); status (num_draws,num_fits):
+ * 0 ok, 1-5 = the ValueError numpy raises (sum != 1, negative, NaN, fewer non-zero entries than size, size > n),
+ * -1 = not drawn because an earlier draw of the fit failed. */
+int rmx_host_sample_segments(int num_fits, int num_draws, int n, int size, uint32_t* mt_key, int32_t* mt_pos,
+                             const double* weights, const uint8_t* weighted, int64_t* chosen, int32_t* status,
+                             int num_threads);
 /* setattr(model, name, value) with one value per fit of the handle (values (gn)); active as above. */
 int rmx_set_scalar_array(rmx_handle h, int scalar_id, const uint8_t* active, const double* values);
 

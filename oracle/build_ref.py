@@ -27,10 +27,37 @@ def ref_so_path():
     return os.path.join(PKG, "bpmodel" + sysconfig.get_config_var("EXT_SUFFIX"))
 
 
+# the reference's own Python modules on the fit path: staged verbatim NEXT TO the compiled extension in
+# the git-ignored oracle/_ref/ so that the reference arm of bench.py and the drop-in test run the UNMODIFIED
+# reference driver on the GPU box too, where /root/reference does not exist.  Build output, never
+# committed, never imported by remixt_b200/.
+PY_FILES = ["cn_model.py", "likelihood.py", "utils.py", "config.py", "defaults.py", "_version.py",
+            "analysis/__init__.py", "analysis/pipeline.py", "analysis/experiment.py", "analysis/readdepth.py"]
+
+
+def stage_py(verbose=True):
+    """Copies PY_FILES from the reference tree into oracle/_ref/remixt/ (no-op without the reference tree)."""
+    import shutil
+    src_pkg = os.path.join(REF_ROOT, "remixt")
+    if not os.path.isdir(src_pkg):
+        return False
+    for rel in PY_FILES:
+        src, dst = os.path.join(src_pkg, rel), os.path.join(PKG, rel)
+        if not os.path.exists(src):
+            continue
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        if not os.path.exists(dst) or open(src, "rb").read() != open(dst, "rb").read():
+            shutil.copyfile(src, dst)
+            if verbose:
+                print("staged", rel)
+    return True
+
+
 def build(force=False, verbose=True):
     """Returns the path of the built extension, or None when the reference tree is absent."""
     so = ref_so_path()
     if os.path.exists(so) and not force:
+        stage_py(verbose)
         return so
     pyx = os.path.join(REF_ROOT, "remixt", "bpmodel.pyx")
     if not os.path.exists(pyx):
@@ -53,6 +80,7 @@ def build(force=False, verbose=True):
     with open(os.path.join(OUT, "BUILD_INFO.txt"), "w") as f:
         f.write("source: %s\ncython: %s\ncflags: %s\n" % (
             pyx, __import__("Cython").__version__, " ".join(cflags)))
+    stage_py(verbose)
     return so
 
 

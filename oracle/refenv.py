@@ -29,8 +29,15 @@ REF_PKG = os.path.join(REF_ROOT, "remixt")
 BIN_PKG = os.path.join(HERE, "_ref", "remixt")
 
 
+def _staged():
+    # the reference's fit-path modules staged next to the compiled extension by build_ref.stage_py
+    return os.path.exists(os.path.join(BIN_PKG, "cn_model.py"))
+
+
 def available():
-    return os.path.isdir(REF_PKG)
+    """True when the reference's Python modules can be imported: from the reference tree (this container) or from
+    the copies build_ref staged under oracle/_ref (the GPU box)."""
+    return os.path.isdir(REF_PKG) or _staged()
 
 
 def _stub(name, **attrs):
@@ -84,7 +91,7 @@ def install(bpmodel=None):
     _install_stubs()
     if "remixt" not in sys.modules or getattr(sys.modules["remixt"], "_oracle_env", False) is False:
         pkg = types.ModuleType("remixt")
-        pkg.__path__ = [BIN_PKG, REF_PKG]
+        pkg.__path__ = [BIN_PKG, REF_PKG] if os.path.isdir(REF_PKG) else [BIN_PKG]
         pkg.__version__ = "0.5.20-oracle"
         pkg._oracle_env = True
         pkg.__spec__ = importlib.machinery.ModuleSpec("remixt", None, is_package=True)

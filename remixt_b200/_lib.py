@@ -41,7 +41,7 @@ EXPORTS = [
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
     'rmx_expected_log_likelihood', 'rmx_expected_log_likelihood_partial_h',
     'rmx_expected_log_likelihood_grid',
-    'rmx_mstep_stage_sample', 'rmx_mstep_evaluate', 'rmx_set_scalar_array',
+    'rmx_mstep_stage_sample', 'rmx_mstep_stage_rows', 'rmx_mstep_evaluate', 'rmx_set_scalar_array', 'rmx_host_sample_segments',
     'rmx_infer_cn', 'rmx_calculate_log_transmat', 'rmx_eval',
     'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product',
     'rmx_launch_count', 'rmx_global_launch_count', 'rmx_kernel_timing', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
@@ -93,8 +93,10 @@ def _load():
         'rmx_expected_log_likelihood_partial_h': [H, P, P],
         'rmx_expected_log_likelihood_grid': [H, P, I, P, I, P],
         'rmx_mstep_stage_sample': [H, P],
+        'rmx_mstep_stage_rows': [H, P, P, I],
         'rmx_mstep_evaluate': [H, P, P, I, P, I, P, P],
         'rmx_set_scalar_array': [H, I, P, P],
+        'rmx_host_sample_segments': [I, I, I, I, P, P, P, P, P, P, I],
         'rmx_infer_cn': [H, P],
         'rmx_calculate_log_transmat': [H, P],
         'rmx_eval': [H, I, I, I, I, I, I, P],

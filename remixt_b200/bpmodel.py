@@ -378,6 +378,13 @@ class _ModelBase(object):
             s = self._sample(sample)
             check(lib.rmx_mstep_stage_sample(self._handle, _ptr(s)), self._handle)
 
+    def mstep_stage_rows(self, rows, counts):
+        """The same from row lists (``rmx_mstep_stage_rows``): ``rows`` ``(gn, R)`` segment indices, fit ``g`` uses
+        its first ``counts[g]``."""
+        r = np.ascontiguousarray(rows, dtype=np.int32).reshape(self._gn, -1)
+        c = np.ascontiguousarray(counts, dtype=np.int32).reshape(self._gn)
+        check(lib.rmx_mstep_stage_rows(self._handle, _ptr(r), _ptr(c), r.shape[1]), self._handle)
+
     def mstep_evaluate(self, active=None, h=None, name=None, values=None, grad=False):
         """E[LL] of the staged sample for the active fits with one synchronisation (``rmx_mstep_evaluate``):
         ``h`` ``(gn, M)`` is assigned first; with ``name`` the dispersion parameter takes ``values`` ``(gn, n)`` in

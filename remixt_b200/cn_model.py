@@ -183,7 +183,7 @@ class BreakpointModel(object):
             self.breakpoint_orient = np.zeros(self.breakpoint_orient.shape, dtype=int)
 
         self.check_elbo = False
-        # (name, accepted) of every M-step acceptance test, in call order (cn_model.py:526-531, :564-569)
+        # (name, accepted, E[LL] before, E[LL] after) of every M-step acceptance test, in call order (cn_model.py:526-531, :564-569)
         self.decisions = []
         self.prev_elbo = None
         self.prev_elbo_diff = None
@@ -470,7 +470,7 @@ class BreakpointModel(object):
 
         model.h = result.x
         ell_after = model.calculate_expected_log_likelihood(self._all_segments())
-        self.decisions.append(('h', not (ell_after < ell_before)))
+        self.decisions.append(('h', not (ell_after < ell_before), ell_before, ell_after))
         if ell_after < ell_before:
             if self.verbose:
                 print('[{}] h rejected, elbo before: {}, after: {}'.format(_now(), ell_before, ell_after))
@@ -503,7 +503,7 @@ class BreakpointModel(object):
         result_value = float(result[0][0])
 
         ell_after = model.calculate_expected_log_likelihood(self._all_segments())
-        self.decisions.append((name, not (ell_after < ell_before)))
+        self.decisions.append((name, not (ell_after < ell_before), ell_before, ell_after))
         if ell_after < ell_before:
             if self.verbose:
                 print('[{}] {} rejected, elbo before: {}, after: {}'.format(_now(), name, ell_before, ell_after))

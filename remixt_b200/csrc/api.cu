@@ -170,7 +170,12 @@ struct Batch {
     int *path = nullptr, *d_rows = nullptr, *d_Rn = nullptr, *dflags = nullptr;
     // batched M-step: the staged sample (row lists in ms_rows, per-fit counts on the host) and the per-call
     // effective counts (0 for inactive fits)
-    int *ms_rows = nullptr, *ms_Rn = nullptr;
+    int *ms_rows = nullptr, *ms_Rn = nullptr, *ms_Rn_all = nullptr;
+    // E[LL] of one dispersion parameter moves only the likelihood terms that parameter enters: the sum of the other
+    // terms over the staged sample is computed once per (sample, parameter) and added on the host
+    std::vector<double> ms_const;
+    int ms_const_id = -1;
+    bool ms_const_valid = false;
     std::vector<int> ms_count;      // (G) staged rows per fit; -1 = nothing staged
     bool ms_all = false;            // staged sample = every segment of every fit
     int ms_rmax = 0;
@@ -958,7 +963,9 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->d_Rn, (size_t)G));
     CCK(dalloc(b, &b->ms_rows, GN));
     CCK(dalloc(b, &b->ms_Rn, (size_t)G));
+    CCK(dalloc(b, &b->ms_Rn_all, (size_t)G));
     b->ms_count.assign(G, -1);
+    b->ms_const.assign(G, 0.);
     CCK(dalloc(b, &b->dflags, 1));
     CCK(cudaMemsetAsync(b->dflags, 0, sizeof(int), b->stream));
     b->hp_bytes = (size_t)G * Batch::RED * sizeof(double);
@@ -1075,6 +1082,7 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
             b->ll_dirty[g0 + g] = 1;
         }
         b->params_dirty = true;
+        b->ms_const_valid = false;
         return RMX_OK;
     }
     case RMX_A_P_BREAKPOINT: dst = b->p_brk; break;
@@ -1109,6 +1117,7 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     }
     default: return m->fail(RMX_ERR_ARG, "this attribute cannot be assigned");
     }
+    b->ms_const_valid = false;
     if (count > 0) {
         if (bcast) {
             for (int g = 0; g < gn; ++g)
@@ -1311,6 +1320,7 @@ int rmx_set_scalar(rmx_handle m, int id, double v) {
         if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[g] = 1;
     }
     b->params_dirty = true;
+    b->ms_const_valid = false;
     return RMX_OK;
 }
 
@@ -1375,6 +1385,7 @@ int rmx_update(rmx_handle m, int id) {
     Batch* b = m->b.get();
     Lock lk(b->mu);
     cudaSetDevice(b->device);
+    b->ms_const_valid = false;      // the posteriors the M-step sums are weighted with change
     int rc = do_update(m, id);
     if (rc) return rc;
     rc = sync_check(m);
@@ -1417,6 +1428,7 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
     Batch* b = m->b.get();
     Lock lk(b->mu);
     cudaSetDevice(b->device);
+    b->ms_const_valid = false;      // the posteriors the M-step sums are weighted with change
     static const int order[5] = {RMX_U_ALLELE_SWAP, RMX_U_CN, RMX_U_BREAKPOINT, RMX_U_OUTLIER_TOTAL,
                                  RMX_U_OUTLIER_ALLELE};
     static const bool no_fuse = getenv("RMX_NO_FUSED_ROUND") != nullptr;     // A/B measurements only
@@ -1706,6 +1718,7 @@ int rmx_mstep_stage_sample(rmx_handle m, const int64_t* sample) {
     cudaSetDevice(b->device);
     const int N = b->d.N, g0 = m->g0, gn = m->gn;
     if (g0 != 0 || gn != b->G) return m->fail(RMX_ERR_ARG, "the batched M-step works on the handle of the whole batch");
+    b->ms_const_valid = false;
     if (!sample) {
         b->ms_all = true;
         b->ms_rmax = N;
@@ -1729,7 +1742,42 @@ int rmx_mstep_stage_sample(rmx_handle m, const int64_t* sample) {
         if (b->ms_count[g] > 0)
             CK(cudaMemcpyAsync(b->ms_rows + (size_t)g * N, b->hrows + (size_t)g * N, (size_t)b->ms_count[g] * sizeof(int),
                                cudaMemcpyHostToDevice, b->stream));
+    for (int g = 0; g < gn; ++g) b->hRn[g] = b->ms_count[g];
+    CK(cudaMemcpyAsync(b->ms_Rn_all, b->hRn, (size_t)gn * sizeof(int), cudaMemcpyHostToDevice, b->stream));
     CK(cudaStreamSynchronize(b->stream));   // hrows is reused by the next staging / decode
+    return RMX_OK;
+}
+
+int rmx_mstep_stage_rows(rmx_handle m, const int32_t* rows, const int32_t* counts, int max_rows) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    const int N = b->d.N, G = b->G;
+    if (m->g0 != 0 || m->gn != G) return m->fail(RMX_ERR_ARG, "the batched M-step works on the handle of the whole batch");
+    if (!rows || !counts || max_rows < 0 || max_rows > N) return m->fail(RMX_ERR_ARG, "bad row lists");
+    b->ms_const_valid = false;
+    int rmax = 0;
+    for (int g = 0; g < G; ++g) {
+        const int cnt = counts[g];
+        if (cnt < 0 || cnt > max_rows) return m->fail(RMX_ERR_ARG, "counts must lie in [0, max_rows]");
+        for (int r = 0; r < cnt; ++r) {
+            const int n = rows[(size_t)g * max_rows + r];
+            if (n < 0 || n >= N) return m->fail(RMX_ERR_VALUE, "segment index out of range in the sample");
+            b->hrows[(size_t)g * N + r] = n;
+        }
+        b->ms_count[g] = cnt;
+        rmax = cnt > rmax ? cnt : rmax;
+    }
+    b->ms_all = false;
+    b->ms_rmax = rmax;
+    for (int g = 0; g < G; ++g)
+        if (b->ms_count[g] > 0)
+            CK(cudaMemcpyAsync(b->ms_rows + (size_t)g * N, b->hrows + (size_t)g * N, (size_t)b->ms_count[g] * sizeof(int),
+                               cudaMemcpyHostToDevice, b->stream));
+    for (int g = 0; g < G; ++g) b->hRn[g] = b->ms_count[g];
+    CK(cudaMemcpyAsync(b->ms_Rn_all, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    CK(cudaStreamSynchronize(b->stream));
     return RMX_OK;
 }
 
@@ -1746,6 +1794,20 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     if (scalar_id >= 0 && (scalar_id > RMX_S_BETABIN_LOH_M_1 || !values))
         return m->fail(RMX_ERR_ARG, "scalar_id must name a likelihood parameter and come with values");
     if (scalar_id < 0 && n_values != 1) return m->fail(RMX_ERR_ARG, "n_values must be 1 without a parameter");
+    // likelihood terms the parameter enters (bit u: total-read term u; bit 2 + v: the allele terms of v)
+    int planes = 15;
+    switch (scalar_id) {
+    case RMX_S_NEGBIN_R_0: case RMX_S_NEGBIN_HDEL_R_0: planes = 1; break;
+    case RMX_S_NEGBIN_R_1: case RMX_S_NEGBIN_HDEL_R_1: planes = 2; break;
+    case RMX_S_NEGBIN_HDEL_MU: planes = 3; break;
+    case RMX_S_BETABIN_M_0: case RMX_S_BETABIN_LOH_M_0: planes = 4; break;
+    case RMX_S_BETABIN_M_1: case RMX_S_BETABIN_LOH_M_1: planes = 8; break;
+    case RMX_S_BETABIN_LOH_P: planes = 12; break;
+    default: break;
+    }
+    static const bool no_planes = getenv("RMX_MSTEP_ALL_TERMS") != nullptr;      // A/B measurements only
+    if (b->ms_all || grad || h_values || no_planes) planes = 15;
+    if (h_values || scalar_id != b->ms_const_id) b->ms_const_valid = false;
     bool any = false;
     for (int g = 0; g < G; ++g) {
         const bool on = !active || active[g];
@@ -1766,6 +1828,19 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         CK(cudaMemcpyAsync(b->ms_Rn, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
     RmxTables T = tables(b);
     const int nb = work ? rmx_ell_blocks(b->d, Rmax) : 0;
+    bool fetch_const = false;
+    if (work && planes != 15 && !b->ms_const_valid) {
+        // the terms the parameter does not enter, for EVERY fit with staged rows (fits join and leave the active set
+        // from call to call), with the parameters as they stand
+        int rc = push_params(m);
+        if (rc) return rc;
+        rmx_launch_segconst(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn_all, Rmax, b->segc_s);
+        rmx_launch_ell(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn_all, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
+                       b->part, b->part_stride, b->dflags, 15 ^ planes);
+        rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 12, Batch::RED);
+        b->count(3);
+        fetch_const = true;
+    }
     for (int v = 0; v < n_values; ++v) {
         if (scalar_id >= 0) {
             for (int g = 0; g < G; ++g)
@@ -1776,13 +1851,23 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
             b->params_dirty = true;
         }
         if (!work) continue;
+        if (b->ms_all) {
+            // every segment: the likelihood table of the fits whose parameters changed (the kernel of the E-step,
+            // which the next E-step then finds ready), its posterior-weighted sums, and one value per segment
+            int rc = ensure_asum(m, 0, G);
+            if (rc) return rc;
+            double* rowe = b->rowv + 7 * (size_t)b->d.N;
+            rmx_launch_ell_rows_from_sums(b->stream, b->d, 0, G, b->Asum, b->q_ot, b->q_oa, b->q_sw, rowe, (int64_t)8 * b->d.N);
+            rmx_launch_reduce_cols(b->stream, rowe, b->d.N, 1, 0, G, (int64_t)8 * b->d.N, b->red_out + 16 + v, Batch::RED);
+            b->count(2);
+            continue;
+        }
         int rc = push_params(m);
         if (rc) return rc;
-        // the full-data form has no row list: inactive fits are skipped through a zero count all the same
         rmx_launch_segconst(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->segc_s);
         { cudaEvent_t te_ = b->tbegin(RMX_K_ELL);
           rmx_launch_ell(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->segc_s, b->post, b->q_ot, b->q_oa, b->q_sw,
-                         b->part, b->part_stride, b->dflags);
+                         b->part, b->part_stride, b->dflags, planes);
           b->tend(te_); }
         rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 16 + v, Batch::RED);
         b->count(3);
@@ -1796,10 +1881,16 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     if (!work) return RMX_OK;
     int rc = fetch_red(m);
     if (rc) return rc;
+    if (fetch_const) {
+        for (int g = 0; g < G; ++g) b->ms_const[g] = b->ms_count[g] > 0 ? b->hp[(size_t)g * Batch::RED + 12] : 0.;
+        b->ms_const_id = scalar_id;
+        b->ms_const_valid = true;
+    }
     for (int g = 0; g < G; ++g) {
         if (b->hRn[g] <= 0) continue;
         const double* r = b->hp + (size_t)g * Batch::RED;
-        for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = r[16 + v];
+        const double c0 = planes != 15 ? b->ms_const[g] : 0.;
+        for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = r[16 + v] + c0;
         if (grad) for (int k = 0; k < M; ++k) grad[(size_t)g * M + k] = r[48 + k];
     }
     return RMX_OK;
@@ -1816,6 +1907,7 @@ int rmx_set_scalar_array(rmx_handle m, int id, const uint8_t* active, const doub
         if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[m->g0 + g] = 1;
     }
     b->params_dirty = true;
+    b->ms_const_valid = false;
     return RMX_OK;
 }
 

@@ -66,13 +66,15 @@ void rmx_launch_reduce_cols(cudaStream_t st, const double* in, int64_t n, int nc
 void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                           const double* A, const double* post, const double* F, const double* q_ot, const double* q_oa,
                           const double* q_sw, double prior_ot, double prior_oa, double* rowv);
+void rmx_launch_ell_rows_from_sums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* A, const double* q_ot,
+                                   const double* q_oa, const double* q_sw, double* out, int64_t out_fit_stride);
 void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int gn, double* out, int64_t out_fit_stride);
 void rmx_launch_fill2(cudaStream_t st, double* out, int64_t n, double v0, double v1);
 int rmx_ell_blocks(const RmxDims& d, int R);
 void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                     const int* rows_all, const int* Rn, int Rmax, const double* segc, const double* post,
                     const double* q_ot, const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride,
-                    int* dflags);
+                    int* dflags, int planes = 15);
 void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                          const int* rows_all, const int* Rn, int Rmax, const double* post, const double* q_ot,
                          const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride, int* dflags);

@@ -32,11 +32,13 @@ struct SegIn {
 
 __device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const RmxDims& d, const RmxParams& P, bool tmask,
                                         bool amask, const SegIn& in, int s, double* ll, int* flags,
-                                        const double2* __restrict__ ltab, const double* lnr = nullptr) {
+                                        const double2* __restrict__ ltab, const double* lnr = nullptr, int planes = 15) {
     StateCN c = load_state2(tab, d, in.nrm0, in.nrm1, s);
     const bool special = !P.normal_contamination;
+    // planes: bit u = total-read term u, bit 2 + v = the two allele terms of v; terms left out are returned as 0
+    // (the M-step objective of one dispersion parameter moves only the terms that parameter enters)
     // ---- total reads: negative binomial (bpmodel.pyx:751-776, :238-272)
-    if (tmask) {
+    if (tmask && (planes & 3)) {
         double x = in.x;
         bool hd = special && c.hdel;
         double mu = hd ? P.negbin_hdel_mu : expected_total_reads(P, d, c, in.l);
@@ -66,7 +68,7 @@ __device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const Rm
     }
     // ---- allele reads: beta binomial (bpmodel.pyx:809-853, :304-347)
     ll[2] = ll[3] = ll[4] = ll[5] = 0.;
-    if (amask) {
+    if (amask && (planes & 12)) {
         double p;
         if (c.hdel) {
             p = 0.;
@@ -96,6 +98,7 @@ __device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const Rm
         }
 #pragma unroll
         for (int v = 0; v < 2; ++v) {
+            if (!((planes >> (2 + v)) & 1)) continue;
             double Mv = loh ? P.betabin_loh_M[v] : P.betabin_M[v];
             double a = Mv * p, b = Mv * (1. - p);
             double base = -rmx_lgamma_pos(a, ltab) - rmx_lgamma_pos(b, ltab);
@@ -113,13 +116,13 @@ __device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const Rm
 // the same, per-segment inputs read from HBM (row lists of the M-step)
 __device__ __forceinline__ void ll_terms(const RmxTables& T, const RmxDims& d, const RmxParams& P, bool tmask,
                                          bool amask, const double* __restrict__ segc, int R, int r, int n, int s,
-                                         double* ll, int* flags, const double2* __restrict__ ltab) {
+                                         double* ll, int* flags, const double2* __restrict__ ltab, int planes = 15) {
     SegIn in;
     in.segc = segc + r;
     in.sstride = R;
     in.x = T.x[n]; in.l = T.l[n]; in.y0 = T.y0[n]; in.y1 = T.y1[n];
     in.nrm0 = T.nrm[2 * n]; in.nrm1 = T.nrm[2 * n + 1];
-    ll_core(T.tab, d, P, tmask, amask, in, s, ll, flags, ltab);
+    ll_core(T.tab, d, P, tmask, amask, in, s, ll, flags, ltab, nullptr, planes);
 }
 
 // K1: the likelihood table, LL[g][t][n*S+s], one thread per (n,s), fully coalesced planar writes.  A CTA takes
@@ -710,6 +713,26 @@ __global__ void __launch_bounds__(256) k_elbo_rows(RmxTables T, RmxDims d, const
     }
 }
 
+// Full-data E_q[log lik] (bpmodel.pyx:1125-1157 with an all-ones sample) from the posterior-weighted likelihood sums
+// A[n][t] = sum_s post[n,s] LL_t[n,s]: the per-segment value sum_u q_ot A_u + sum_vw q_oa q_sw A_vw, one thread per
+// (fit, segment); k_reduce_cols adds the rows.
+__global__ void __launch_bounds__(256) k_ell_rows_from_sums(RmxDims d, int g0, const double* __restrict__ A_all,
+                                                            const double* __restrict__ q_ot_all,
+                                                            const double* __restrict__ q_oa_all,
+                                                            const double* __restrict__ q_sw_all,
+                                                            double* __restrict__ out_all, int64_t out_fit_stride) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= d.N) return;
+    const int g = RMX_FIT();
+    const int64_t gn = (int64_t)g * d.N + n;
+    const double* A = A_all + gn * RMX_NTERM;
+    const double ot0 = q_ot_all[gn * 2], ot1 = q_ot_all[gn * 2 + 1];
+    const double oa0 = q_oa_all[gn * 2], oa1 = q_oa_all[gn * 2 + 1];
+    const double sw0 = q_sw_all[gn * 2], sw1 = q_sw_all[gn * 2 + 1];
+    out_all[(int64_t)g * out_fit_stride + n] = (ot0 * A[0] + ot1 * A[1]) +
+        (oa0 * sw0 * A[2] + oa0 * sw1 * A[3] + oa1 * sw0 * A[4] + oa1 * sw1 * A[5]);
+}
+
 // p log p over a flat per-fit array (p_breakpoint)
 __global__ void k_plogp(const double* __restrict__ p_all, int64_t n, int g0, double* __restrict__ out_all,
                         int64_t out_fit_stride) {
@@ -787,7 +810,7 @@ __global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxPa
                                              const double* __restrict__ segc_all, const double* __restrict__ post_all,
                                              const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
                                              const double* __restrict__ q_sw_all, double* __restrict__ part_all,
-                                             int64_t part_fit_stride, int* __restrict__ dflags) {
+                                             int64_t part_fit_stride, int* __restrict__ dflags, int planes) {
     __shared__ double2 ltab[RMX_LOGTAB];
     rmx_logtab_init(ltab);
     const int g = RMX_FIT();
@@ -802,13 +825,22 @@ __global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxPa
         const int64_t gn = (int64_t)g * d.N + n;
         double ll[RMX_NTERM];
         ll_terms(T, d, Pg[g], T.tmask[gn] != 0, T.amask[gn] != 0, segc_all + (int64_t)g * 12 * d.N, R, r, n, s, ll,
-                 &flags, ltab);
+                 &flags, ltab, planes);
         double p = post_all[gn * d.S + s];
         double ot0 = q_ot_all[2 * gn], ot1 = q_ot_all[2 * gn + 1];
         double oa0 = q_oa_all[2 * gn], oa1 = q_oa_all[2 * gn + 1];
         double sw0 = q_sw_all[2 * gn], sw1 = q_sw_all[2 * gn + 1];
-        acc[0] = p * ot0 * ll[0] + p * ot1 * ll[1] + p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3] +
-                 p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
+        if (planes == 15) {
+            acc[0] = p * ot0 * ll[0] + p * ot1 * ll[1] + p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3] +
+                     p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
+        } else {        // the same terms in the same order, the ones left out skipped
+            double a = 0.;
+            if (planes & 1) a += p * ot0 * ll[0];
+            if (planes & 2) a += p * ot1 * ll[1];
+            if (planes & 4) a += p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3];
+            if (planes & 8) a += p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
+            acc[0] = a;
+        }
     }
     block_sum_store<1>(acc, part_all + (int64_t)g * part_fit_stride, gridDim.x);
     if (flags) atomicOr(dflags, flags);
@@ -1157,6 +1189,11 @@ void rmx_launch_elbo_rows(cudaStream_t st, const RmxTables& T, const RmxDims& d,
                                                                         prior_ot, prior_oa, rowv);
 }
 
+void rmx_launch_ell_rows_from_sums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* A, const double* q_ot,
+                                   const double* q_oa, const double* q_sw, double* out, int64_t out_fit_stride) {
+    if (d.N <= 0 || gn <= 0) return;
+    k_ell_rows_from_sums<<<dim3(cdiv(d.N, 256), gn), 256, 0, st>>>(d, g0, A, q_ot, q_oa, q_sw, out, out_fit_stride);
+}
 void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int gn, double* out, int64_t out_fit_stride) {
     if (n <= 0 || gn <= 0) return;
     k_plogp<<<dim3(cdiv(n, 256), gn), 256, 0, st>>>(p, n, g0, out, out_fit_stride);
@@ -1167,10 +1204,10 @@ int rmx_ell_blocks(const RmxDims& d, int R) { return cdiv((int64_t)R * d.S, 256)
 void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                     const int* rows_all, const int* Rn, int Rmax, const double* segc, const double* post,
                     const double* q_ot, const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride,
-                    int* dflags) {
+                    int* dflags, int planes) {
     if (Rmax <= 0 || gn <= 0) return;
     k_ell<<<dim3(rmx_ell_blocks(d, Rmax), gn), 256, 0, st>>>(T, d, P, g0, rows_all, Rn, segc, post, q_ot, q_oa, q_sw,
-                                                            part, part_fit_stride, dflags);
+                                                            part, part_fit_stride, dflags, planes);
 }
 
 void rmx_launch_ell_grad(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,

@@ -24,7 +24,10 @@ The evaluator interface (what a *backend* provides) is small so that the same dr
 (:class:`BatchBackend`) and, for tests, on a list of per-fit model objects such as the compiled reference
 (:class:`ModelListBackend`).
 """
+import collections
+import os
 import threading
+import time
 
 import numpy as np
 import scipy.optimize
@@ -144,6 +147,128 @@ def _nanmin(a, b):
 
 
 # ---------------------------------------------------------------------------------------------------------------
+# L-BFGS-B as a coroutine over scipy's own compiled routine
+# ---------------------------------------------------------------------------------------------------------------
+def lbfgsb_coroutine(x0, bounds, maxcor=10, ftol=2.220446049250313e-09, gtol=1e-5, maxfun=15000, maxiter=15000,
+                     maxls=20):
+    """``scipy.optimize.minimize(fun, x0, method='L-BFGS-B', jac=jac, bounds=bounds)`` as a generator: yields the
+    next point, expects ``(f, g)`` through ``send``, returns an ``OptimizeResult`` as the ``StopIteration`` value.
+
+    The algorithm is scipy's own compiled routine (``scipy.optimize._lbfgsb.setulb``, reverse communication), driven
+    by the loop of ``scipy/optimize/_lbfgsb_py.py:_minimize_lbfgsb`` including what its ``ScalarFunction`` wrapper
+    does around the user's callables (clipping ``x0`` into the bounds, evaluating the start point once, not
+    re-evaluating a point it already holds).  ``setulb`` is a private interface: :func:`lbfgsb_coroutine_ok` checks
+    this driver against ``scipy.optimize.minimize`` itself, and :class:`GridMStep` falls back to one blocking
+    scipy call per fit on host threads when the check fails."""
+    from scipy.optimize import OptimizeResult, _lbfgsb
+    from scipy.optimize import _lbfgsb_py as lb
+    m = maxcor
+    factr = ftol / np.finfo(float).eps
+    x0 = np.asarray(x0).ravel()
+    n, = x0.shape
+    lo = np.array([b[0] for b in bounds], dtype=float)
+    hi = np.array([b[1] for b in bounds], dtype=float)
+    x0 = np.clip(x0, lo, hi)
+    int_dtype = np.int64 if getattr(lb, 'HAS_ILP64', False) else np.int32
+    nbd = np.full(n, 2, dtype=int_dtype)        # both bounds finite (the caller's bounds are)
+    assert np.all(np.isfinite(lo)) and np.all(np.isfinite(hi))
+    low_bnd, upper_bnd = lo.copy(), hi.copy()
+    x = np.array(x0, dtype=np.float64)
+    f = np.array(0.0, dtype=np.float64)
+    g = np.zeros((n,), dtype=np.float64)
+    wa = np.zeros(2 * m * n + 5 * n + 11 * m * m + 8 * m, np.float64)
+    iwa = np.zeros(3 * n, dtype=int_dtype)
+    task = np.zeros(2, dtype=int_dtype)
+    ln_task = np.zeros(2, dtype=int_dtype)
+    lsave = np.zeros(4, dtype=int_dtype)
+    isave = np.zeros(44, dtype=int_dtype)
+    dsave = np.zeros(29, dtype=np.float64)
+    # ScalarFunction.__init__ evaluates fun and grad at x0
+    held_x = np.array(x0, dtype=float)
+    held_f, held_g = yield held_x.copy()
+    held_g = np.atleast_1d(held_g)
+    nfev = 1
+    n_iterations = 0
+    while True:
+        g = g.astype(np.float64)
+        _lbfgsb.setulb(m, x, low_bnd, upper_bnd, nbd, f, g, factr, gtol, wa, iwa, task, lsave, isave, dsave, maxls,
+                       ln_task)
+        if task[0] == 3:
+            if not np.array_equal(x, held_x):
+                held_x = np.array(x, dtype=float)
+                held_f, held_g = yield held_x.copy()
+                held_g = np.atleast_1d(held_g)
+                nfev += 1
+            f, g = held_f, held_g
+        elif task[0] == 1:
+            n_iterations += 1
+            if n_iterations >= maxiter:
+                task[0] = 5
+                task[1] = 504
+            elif nfev > maxfun:
+                task[0] = 5
+                task[1] = 502
+        else:
+            break
+    if task[0] == 4:
+        warnflag = 0
+    elif nfev > maxfun or n_iterations >= maxiter:
+        warnflag = 1
+    else:
+        warnflag = 2
+    msg = lb.status_messages[task[0]] + ": " + lb.task_messages[task[1]]
+    return OptimizeResult(fun=f, jac=g, nfev=nfev, njev=nfev, nit=n_iterations, status=warnflag, message=msg, x=x,
+                          success=(warnflag == 0))
+
+
+_LBFGSB_OK = None
+
+
+def lbfgsb_coroutine_ok():
+    """True when :func:`lbfgsb_coroutine` reproduces ``scipy.optimize.minimize(method='L-BFGS-B')`` on this scipy
+    -- every evaluation point, the result and the termination status, bit for bit -- on two bounded test problems
+    (one ends on a bound, one needs many line searches).  Evaluated once per process."""
+    global _LBFGSB_OK
+    if _LBFGSB_OK is not None:
+        return _LBFGSB_OK
+    try:
+        ok = True
+        problems = [
+            (lambda x: (float(np.sum((x - np.array([0.3, -2., 5.])) ** 2) + np.prod(np.cosh(x / 3.))),
+                        2. * (x - np.array([0.3, -2., 5.])) + np.prod(np.cosh(x / 3.)) * np.tanh(x / 3.) / 3.),
+             np.array([1., 1., 1.]), [(1e-8, 10.)] * 3),
+            (lambda x: (float(100. * (x[1] - x[0] ** 2) ** 2 + (1. - x[0]) ** 2 + (x[2] - 0.5) ** 4),
+                        np.array([-400. * x[0] * (x[1] - x[0] ** 2) - 2. * (1. - x[0]), 200. * (x[1] - x[0] ** 2),
+                                  4. * (x[2] - 0.5) ** 3])),
+             np.array([0.1, 3., 9.]), [(1e-8, 10.)] * 3),
+        ]
+        for fg, x0, bounds in problems:
+            trace = []
+
+            def fun(x):
+                trace.append(np.array(x))
+                return fg(x)[0]
+
+            ref = scipy.optimize.minimize(fun, x0, method='L-BFGS-B', jac=lambda x: fg(x)[1], bounds=bounds)
+            gen = lbfgsb_coroutine(x0, bounds)
+            mine = []
+            try:
+                x = next(gen)
+                while True:
+                    mine.append(np.array(x))
+                    x = gen.send(fg(x))
+            except StopIteration as stop:
+                res = stop.value
+            ok = ok and len(mine) == len(trace) and all(np.array_equal(a, b) for a, b in zip(mine, trace))
+            ok = ok and np.array_equal(res.x, ref.x) and res.fun == ref.fun and res.success == ref.success
+            ok = ok and res.message == ref.message and res.nit == ref.nit and res.nfev == ref.nfev
+        _LBFGSB_OK = bool(ok)
+    except Exception:
+        _LBFGSB_OK = False
+    return _LBFGSB_OK
+
+
+# ---------------------------------------------------------------------------------------------------------------
 # backends
 # ---------------------------------------------------------------------------------------------------------------
 class BatchBackend(object):
@@ -164,6 +289,12 @@ class BatchBackend(object):
         if name not in self._cache:
             self._cache[name] = getattr(self.batch, name)
         return self._cache[name]
+
+    def prefetch(self, plan):
+        if any(p.startswith('negbin') for p in plan):
+            self._arr('p_outlier_total')
+        if any(p.startswith('betabin') for p in plan):
+            self._arr('p_outlier_allele')
 
     def get_h(self):
         return np.array(self.batch.h)
@@ -186,11 +317,28 @@ class BatchBackend(object):
         which = 'p_outlier_total' if name.startswith('negbin') else 'p_outlier_allele'
         return self._arr(which)[g][:, int(name[-1])]
 
+    def weights_block(self, name, fits, out):
+        """``get_param_sample_weight(name)`` (``cn_model.py:323-352``) of the fits ``fits`` for an outlier-weighted
+        parameter, written to ``out (len(fits), N)``: the outlier posterior column over its own sum, exactly the
+        per-fit ``weights / weights.sum()`` (``tests/test_mstep_cpu.py`` checks the row sums of the strided block
+        against the per-fit sums).  Returns the flags (0 where the sum is not positive: uniform sample)."""
+        which = 'p_outlier_total' if name.startswith('negbin') else 'p_outlier_allele'
+        col = self._arr(which)[:, :, int(name[-1])]
+        if len(fits) != col.shape[0]:
+            col = col[np.asarray(fits)]
+        norm = col.sum(axis=1)
+        ok = norm > 0.
+        np.divide(col, np.where(ok, norm, 1.)[:, np.newaxis], out=out)
+        return ok.astype(np.uint8)
+
     def state_weights(self, which, g):
         return (self.batch.fit(g).posterior_marginals * (np.asarray(getattr(self.batch, which)) == 1)).sum(axis=-1)
 
-    def stage(self, samples):
-        self.batch.mstep_stage_sample(samples)
+    def stage(self, rows=None, counts=None):
+        if rows is None:
+            self.batch.mstep_stage_sample(None)
+        else:
+            self.batch.mstep_stage_rows(rows, counts)
 
     def evaluate(self, active=None, h=None, name=None, values=None, grad=False):
         return self.batch.mstep_evaluate(active=active, h=h, name=name, values=values, grad=grad)
@@ -209,6 +357,9 @@ class ModelListBackend(object):
         self.log = [[] for _ in self.models]        # per fit: (kind, point, value) of every evaluation, in order
 
     def new_iteration(self):
+        pass
+
+    def prefetch(self, plan):
         pass
 
     def get_h(self):
@@ -235,8 +386,13 @@ class ModelListBackend(object):
         m = self.models[g]
         return (np.asarray(m.posterior_marginals) * (np.asarray(getattr(m, which)) == 1)).sum(axis=-1)
 
-    def stage(self, samples):
-        self.samples = samples
+    def stage(self, rows=None, counts=None):
+        if rows is None:
+            self.samples = None
+        else:
+            self.samples = np.zeros((self.G, self.num_segments), dtype=np.int64)
+            for g in range(self.G):
+                self.samples[g, rows[g, :counts[g]]] = 1
 
     def evaluate(self, active=None, h=None, name=None, values=None, grad=False):
         n = 1 if name is None else np.asarray(values).reshape(self.G, -1).shape[1]
@@ -315,6 +471,58 @@ class _Rendezvous(object):
                 self.wake[g].release()
 
 
+_CHOICE_ERRORS = {1: 'probabilities do not sum to 1', 2: 'probabilities are not non-negative',
+                  3: 'probabilities contain NaN', 4: 'Fewer non-zero entries in p than size',
+                  5: "Cannot take a larger sample than population when 'replace=False'"}
+
+
+def native_choice(random_states, n, size, weights, num_threads=None, buffer=None, block=None):
+    """``rs.choice(n, size=size, replace=False, p=weights[d][g])`` for every stream ``random_states[g]`` (numpy
+    ``RandomState`` objects over MT19937) and draw ``d`` in order, by the library's host threads
+    (``rmx_host_sample_segments``: numpy's legacy algorithm restated, bit for bit).  ``weights[d][g]`` is an ``(n,)``
+    array or ``None`` (uniform); ``block = (w (D, G, n), flags (D, G))`` passes them in place instead.  The streams are advanced in place.  Returns ``chosen (D, G, size)`` and
+    ``status (D, G)`` (see ``_CHOICE_ERRORS``; -1 = skipped after an earlier failure of the fit)."""
+    from . import _lib
+    G, D = len(random_states), len(weights)
+    states = [rs.get_state(legacy=True) for rs in random_states]
+    if any(st[0] != 'MT19937' for st in states):
+        raise TypeError('native_choice needs MT19937 streams')
+    key = np.ascontiguousarray(np.array([st[1] for st in states], dtype=np.uint32).reshape(G, 624))
+    pos = np.ascontiguousarray(np.array([st[2] for st in states], dtype=np.int32))
+    flags = np.zeros((D, G), dtype=np.uint8)
+    w = None
+    if block is not None:       # (D, G, n) weights already in place, with their (D, G) flags
+        w, flags = block
+    elif any(weights[d][g] is not None for d in range(D) for g in range(G)):
+        if buffer is not None and buffer.get('shape') == (D, G, n):
+            w = buffer['w']
+        else:
+            w = np.empty((D, G, n), dtype=np.float64)
+            if buffer is not None:
+                buffer['shape'], buffer['w'] = (D, G, n), w
+        for d in range(D):
+            for g in range(G):
+                if weights[d][g] is not None:
+                    w[d, g] = weights[d][g]
+                    flags[d, g] = 1
+    chosen = np.zeros((D, G, size), dtype=np.int64)
+    status = np.zeros((D, G), dtype=np.int32)
+    ptr = lambda a: a.ctypes.data
+    _lib.check(_lib.lib.rmx_host_sample_segments(G, D, int(n), int(size), ptr(key), ptr(pos), None if w is None else ptr(w),
+                                                 ptr(flags), ptr(chosen), ptr(status),
+                                                 int(num_threads or _host_threads())), None)
+    for g, (rs, st) in enumerate(zip(random_states, states)):
+        rs.set_state((st[0], key[g], int(pos[g])) + tuple(st[3:]))
+    return chosen, status
+
+
+def _host_threads():
+    try:
+        return min(16, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return min(16, os.cpu_count() or 1)
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # the driver
 # ---------------------------------------------------------------------------------------------------------------
@@ -323,26 +531,99 @@ class GridMStep(object):
     objects (they supply the random streams, ``likelihood_params``, bounds, ``do_h_update`` and collect the
     ``decisions``); ``errors`` maps a fit index to the exception that took that fit out of the grid."""
 
-    def __init__(self, backend, drivers, errors=None):
+    def __init__(self, backend, drivers, errors=None, lbfgsb='auto'):
+        self.lbfgsb = lbfgsb    # 'auto' | 'coroutine' | 'threads'
+        self.native_sampling = True
+        self._wbuf = {}         # reusable weight block of the native sampler (fresh pages cost more than the draws)
         self.be = backend
         self.drivers = drivers
         self.G = backend.G
         self.errors = errors if errors is not None else {}
         self.rounds = 0         # lock-step evaluation rounds (device calls) so far
         self.evaluations = 0    # objective evaluations they carried
+        self.seconds = collections.defaultdict(float)      # wall clock by phase
 
     def _alive(self):
         return np.array([g not in self.errors for g in range(self.G)], dtype=bool)
 
-    def _sample(self, g, weights=None):
+    def _choose(self, g, weights=None):
+        # cn_model.py:475-480 (_create_sample): the segments of the sample
         d = self.drivers[g]
         N = self.be.num_segments
         size = int(min(200, N / 10))
         rs = d.random_state if d.random_state is not None else np.random
-        chosen = rs.choice(N, size=size, replace=False, p=weights)
-        sample = np.zeros((N,), dtype=np.int64)
-        sample[chosen] = 1
-        return sample
+        return rs.choice(N, size=size, replace=False, p=weights)
+
+    def _draw_samples(self, plan):
+        """The segment samples of one EM iteration, ``{step: (rows (G, size), counts (G))}``.  Every sample is a function of the
+        E-step's q-factors and of the fit's random stream alone (nothing the M-step changes), so they are all drawn
+        up front -- per fit in the reference's order h, then each parameter, which is what keeps every stream
+        identical to the per-fit driver's -- with the fits spread over host threads (numpy releases the GIL inside
+        the cumulative sums and searches that dominate ``RandomState.choice``).  A fit whose draw raises takes the
+        error at the step that would have raised it."""
+        t0 = time.perf_counter()
+        be = self.be
+        alive = np.flatnonzero(self._alive())
+        shared_stream = any(self.drivers[g].random_state is None for g in alive)
+
+        def draw(g):
+            out = []
+            for step in plan:
+                try:
+                    out.append(self._choose(g, None if step == 'h' else self._weights(step, g)))
+                except Exception as e:      # e.g. fewer non-zero weights than the sample size
+                    out.append(e)
+                    break
+            return out
+
+        native = (self.native_sampling and not shared_stream and len(alive) > 0 and
+                  all(type(self.drivers[g].random_state) is np.random.RandomState for g in alive))
+        if native:
+            # weights on the calling thread (they read the backend), the draws on the library's host threads
+            size = int(min(200, be.num_segments / 10))
+            D, A, N = len(plan), len(alive), be.num_segments
+            if self._wbuf.get('shape') != (D, A, N):
+                self._wbuf['shape'], self._wbuf['w'] = (D, A, N), np.empty((D, A, N), dtype=np.float64)
+            w, flags = self._wbuf['w'], np.zeros((D, A), dtype=np.uint8)
+            for d, step in enumerate(plan):
+                if step == 'h':
+                    continue
+                if hasattr(be, 'weights_block') and step in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
+                    flags[d] = be.weights_block(step, alive, w[d])
+                else:
+                    for k, g in enumerate(alive):
+                        wg = self._weights(step, g)
+                        if wg is not None:
+                            w[d, k], flags[d, k] = wg, 1
+            chosen, status = native_choice([self.drivers[g].random_state for g in alive], N, size, [None] * D,
+                                           block=(w, flags))
+            drawn = []
+            for k in range(len(alive)):
+                out = []
+                for d in range(len(plan)):
+                    if status[d, k] == 0:
+                        out.append(chosen[d, k])
+                    else:
+                        if status[d, k] > 0:
+                            out.append(ValueError(_CHOICE_ERRORS[int(status[d, k])]))
+                        break
+                drawn.append(out)
+        else:
+            drawn = [draw(g) for g in alive]
+        size = int(min(200, be.num_segments / 10))
+        samples = dict((step, (np.zeros((self.G, size), dtype=np.int32), np.zeros(self.G, dtype=np.int32)))
+                       for step in plan)
+        failed = {}
+        for g, out in zip(alive, drawn):
+            for step, chosen in zip(plan, out):
+                if isinstance(chosen, Exception):
+                    failed[(step, int(g))] = chosen
+                else:
+                    # ascending, as the rows of the reference's 0/1 sample mask are visited (bpmodel.pyx:1137)
+                    samples[step][0][g] = np.sort(chosen)
+                    samples[step][1][g] = size
+        self.seconds['sample'] += time.perf_counter() - t0
+        return samples, failed
 
     def _evaluate(self, **kw):
         self.rounds += 1
@@ -351,11 +632,25 @@ class GridMStep(object):
         return self.be.evaluate(**kw)
 
     def _full_ell(self, alive):
+        t0 = time.perf_counter()
         self.be.stage(None)
-        return self._evaluate(active=alive)[:, 0]
+        out = self._evaluate(active=alive)[:, 0]
+        self.seconds['full_data_ell'] += time.perf_counter() - t0
+        return out
 
     # ------------------------------------------------------------------------------------------ update_h
-    def update_h(self):
+    def _take_sample(self, step, samples):
+        """The pre-drawn sample of ``step`` as ``(rows, counts)`` (drawn here when the step runs on its own)."""
+        if samples is None:
+            samples, failed = self._draw_samples([step])
+        else:
+            samples, failed = samples
+        for (st, g), e in failed.items():
+            if st == step:
+                self.errors[g] = e
+        return samples[step]
+
+    def update_h(self, samples=None):
         """``update_h`` (``cn_model.py:482-531``) of every fit."""
         be, M = self.be, self.be.num_clones
         alive = self._alive()
@@ -363,13 +658,16 @@ class GridMStep(object):
             return
         h_before = be.get_h()
         ell_before = self._full_ell(alive)
-        samples = np.zeros((self.G, be.num_segments), dtype=np.int64)
-        for g in np.flatnonzero(alive):
-            samples[g] = self._sample(g)
-        be.stage(samples)
+        rows, counts = self._take_sample('h', samples)
+        alive = self._alive()
+        if not alive.any():
+            return
+        t1 = time.perf_counter()
+        be.stage(rows, counts)
+        t2 = time.perf_counter()
+        self.seconds['stage'] += t2 - t1
 
         workers = [int(g) for g in np.flatnonzero(alive)]
-        rv = _Rendezvous(workers)
         results = {}
 
         def evaluate(batch):
@@ -381,36 +679,26 @@ class GridMStep(object):
             ell, grad = self._evaluate(active=active, h=hv, grad=True)
             return dict((g, (float(ell[g, 0]), grad[g].copy())) for g in batch)
 
-        def optimise(g):
-            cache = {}
-
-            def both(h):
-                key = h.tobytes()
-                if key not in cache:
-                    cache.clear()
-                    cache[key] = rv.request(g, np.array(h, dtype=float))
-                return cache[key]
-
-            def nll(h):
-                return -both(h)[0]
-
-            def nll_grad(h):
-                return -both(h)[1]
-
-            try:
-                results[g] = scipy.optimize.minimize(nll, h_before[g], method='L-BFGS-B', jac=nll_grad,
-                                                     bounds=[(1e-8, 10.)] * M)
-            except BaseException as e:
-                results[g] = e
-            finally:
-                rv.finish(g)
-
-        threads = [threading.Thread(target=optimise, args=(g,)) for g in workers]
-        for t in threads:
-            t.start()
-        rv.serve(evaluate)
-        for t in threads:
-            t.join()
+        bounds = [(1e-8, 10.)] * M
+        if self.lbfgsb == 'coroutine' or (self.lbfgsb == 'auto' and lbfgsb_coroutine_ok()):
+            gens, pending = {}, {}
+            for g in workers:
+                gens[g] = lbfgsb_coroutine(h_before[g], bounds)
+                pending[g] = next(gens[g])
+            while pending:
+                answers = evaluate(pending)
+                nxt = {}
+                for g, (ell, grad) in answers.items():
+                    try:
+                        nxt[g] = gens[g].send((-ell, -grad))
+                    except StopIteration as stop:
+                        results[g] = stop.value
+                    except BaseException as e:
+                        results[g] = e
+                pending = nxt
+        else:
+            self._update_h_threads(workers, evaluate, h_before, bounds, results)
+        self.seconds['lbfgsb'] += time.perf_counter() - t2
 
         h_new = np.array(h_before)
         for g in workers:
@@ -432,10 +720,40 @@ class GridMStep(object):
         final = np.array(h_new)
         for g in np.flatnonzero(alive):
             rejected = ell_after[g] < ell_before[g]
-            self.drivers[g].decisions.append(('h', not rejected))
+            self.drivers[g].decisions.append(('h', not rejected, float(ell_before[g]), float(ell_after[g])))
             if rejected:
                 final[g] = h_before[g]
         be.set_h(final, alive)
+
+    def _update_h_threads(self, workers, evaluate, h_before, bounds, results):
+        """L-BFGS-B of every fit as the unmodified ``scipy.optimize.minimize`` on its own host thread, the objective
+        blocking until the round has been evaluated (used when the coroutine driver is not available)."""
+        rv = _Rendezvous(workers)
+
+        def optimise(g):
+            cache = {}
+
+            def both(h):
+                key = h.tobytes()
+                if key not in cache:
+                    cache.clear()
+                    cache[key] = rv.request(g, np.array(h, dtype=float))
+                return cache[key]
+
+            try:
+                results[g] = scipy.optimize.minimize(lambda h: -both(h)[0], h_before[g], method='L-BFGS-B',
+                                                     jac=lambda h: -both(h)[1], bounds=bounds)
+            except BaseException as e:
+                results[g] = e
+            finally:
+                rv.finish(g)
+
+        threads = [threading.Thread(target=optimise, args=(g,)) for g in workers]
+        for t in threads:
+            t.start()
+        rv.serve(evaluate)
+        for t in threads:
+            t.join()
 
     # ------------------------------------------------------------------------------------------ update_param
     def _weights(self, name, g):
@@ -455,7 +773,7 @@ class GridMStep(object):
         norm = w.sum()
         return w / norm if norm > 0. else None
 
-    def update_param(self, name):
+    def update_param(self, name, samples=None):
         """``update_param(name)`` (``cn_model.py:533-569``) of every fit."""
         be = self.be
         alive = self._alive()
@@ -464,16 +782,14 @@ class GridMStep(object):
         lo, hi = self.drivers[0].likelihood_param_bounds[name]
         value_before = be.get_param(name)
         ell_before = self._full_ell(alive)
-        samples = np.zeros((self.G, be.num_segments), dtype=np.int64)
-        for g in np.flatnonzero(alive):
-            try:
-                samples[g] = self._sample(g, self._weights(name, g))
-            except Exception as e:      # e.g. fewer non-zero weights than the sample size
-                self.errors[g] = e
+        rows, counts = self._take_sample(name, samples)
         alive = self._alive()
         if not alive.any():
             return
-        be.stage(samples)
+        t2 = time.perf_counter()
+        be.stage(rows, counts)
+        t3 = time.perf_counter()
+        self.seconds['stage'] += t3 - t2
 
         # scipy.optimize.brute: the grid, ascending, one call for all fits (values outside the bounds are inf and
         # are not assigned -- cn_model.py:541-543)
@@ -486,6 +802,8 @@ class GridMStep(object):
             self.rounds += len(inside) - 1
             self.evaluations += (len(inside) - 1) * int(alive.sum())
             J[:, [i for i, v in enumerate(grid) if not (v < lo or v > hi)]] = -ell
+        t4 = time.perf_counter()
+        self.seconds['brute_grid'] += t4 - t3
         # fmin from the grid minimum, every fit's simplex advancing one evaluation per round
         gens, pending, result = {}, {}, {}
         for g in np.flatnonzero(alive):
@@ -512,12 +830,13 @@ class GridMStep(object):
                 except StopIteration as stop:
                     result[g] = stop.value[0]
             pending = nxt
+        self.seconds['nelder_mead'] += time.perf_counter() - t4
 
         ell_after = self._full_ell(alive)
         final = np.array(value_before)
         for g in np.flatnonzero(alive):
             rejected = ell_after[g] < ell_before[g]
-            self.drivers[g].decisions.append((name, not rejected))
+            self.drivers[g].decisions.append((name, not rejected, float(ell_before[g]), float(ell_after[g])))
             final[g] = value_before[g] if rejected else result[g]
         be.set_param(name, final, alive)
 
@@ -526,7 +845,12 @@ class GridMStep(object):
         """``em_update_h`` + ``em_update_params`` (``cn_model.py:411-416``) for the whole grid."""
         self.be.new_iteration()
         d0 = self.drivers[0]
+        plan = (['h'] if d0.do_h_update else []) + list(d0.likelihood_params)
+        t0 = time.perf_counter()
+        self.be.prefetch(plan)
+        self.seconds['weights'] += time.perf_counter() - t0
+        samples = self._draw_samples(plan)
         if d0.do_h_update:
-            self.update_h()
+            self.update_h(samples)
         for name in d0.likelihood_params:
-            self.update_param(name)
+            self.update_param(name, samples)

@@ -16,6 +16,8 @@ from . import cn_model
 
 # the fit-relevant subset of remixt/defaults.py:114-163
 DEFAULTS = {
+    'h_normal': None,
+    'h_tumour': None,
     'max_copy_number': 12,
     'tumour_mix_fractions': [0.45, 0.3, 0.2, 0.1],
     'min_ploidy': 1.5,
@@ -40,9 +42,16 @@ def get_param(config, name):
 class ArrayExperiment(object):
     """Experiment container over plain arrays (see ``oracle/make_inputs.py`` for the layout)."""
 
-    def __init__(self, x, l, adjacencies, breakpoints, breakpoint_ids=None, chromosome=None):
+    def __init__(self, x, l, adjacencies, breakpoints, breakpoint_ids=None, chromosome=None, start=None, end=None,
+                 major_is_allele_a=None):
         self.x = np.asarray(x, dtype=float)
         self.l = np.asarray(l, dtype=float)
+        n = self.l.shape[0]
+        # coordinates feed only the result tables and the (unused) high_quality column of the depth table
+        self.segment_start = np.zeros(n, dtype=int) if start is None else np.asarray(start)
+        self.segment_end = np.maximum(self.l.astype(int) - 1, 0) if end is None else np.asarray(end)
+        self.segment_major_is_allele_a = (np.ones(n, dtype=int) if major_is_allele_a is None
+                                          else np.asarray(major_is_allele_a))
         self.adjacencies = set((int(a), int(b)) for a, b in np.asarray(adjacencies).reshape(-1, 2))
         bps = np.asarray(breakpoints).reshape(-1, 4)
         if breakpoint_ids is None:
@@ -59,6 +68,71 @@ class ArrayExperiment(object):
         return cls(d['x'], d['l'], d['adjacencies'], d['breakpoints'],
                    breakpoint_ids=d['breakpoint_ids'] if 'breakpoint_ids' in d else None,
                    chromosome=d['chromosome'] if 'chromosome' in d else None)
+
+
+def init(experiment, config, store=None):
+    """The initialisation grid of one experiment (``analysis/pipeline.py:12-109``): candidate haploid depths from
+    the modes of the minor-allele depth x tumour mix fractions, filtered by the ploidy they imply, x divergence
+    weights, all sharing one ``max_depth``.  Returns ``{init_id: init_params}``.
+
+    ``experiment`` is the object itself (the reference unpickles it from a file name); ``store`` (optional,
+    ``results.open_store``) receives ``read_depth`` and ``minor_modes`` as the reference's HDF5 store does."""
+    import itertools
+    from . import readdepth
+    min_ploidy = get_param(config, 'min_ploidy')
+    max_ploidy = get_param(config, 'max_ploidy')
+    h_normal = get_param(config, 'h_normal')
+    h_tumour = get_param(config, 'h_tumour')
+    tumour_mix_fractions = get_param(config, 'tumour_mix_fractions')
+    divergence_weights = get_param(config, 'divergence_weights')
+    max_copy_number = get_param(config, 'max_copy_number')
+    np.random.seed(config.get('random_seed', 1234))
+
+    read_depth = readdepth.calculate_depth(experiment)
+    minor_modes = readdepth.calculate_minor_modes(read_depth)
+    init_h_mono = readdepth.calculate_candidate_h_monoclonal(minor_modes, h_normal=h_normal, h_tumour=h_tumour)
+
+    candidates = []     # (params, ploidy, max_depth)
+    for mode_idx, h_mono in enumerate(init_h_mono):
+        ploidy = readdepth.estimate_ploidy(h_mono, experiment, read_depth=read_depth)
+        assert not np.isinf(ploidy) and not np.isnan(ploidy)
+        max_depth = 2. * h_mono[0] + (max_copy_number + 0.25) * h_mono[1]
+        for mix_frac in tumour_mix_fractions:
+            candidates.append(({'mode_idx': mode_idx, 'h_normal': h_mono[0], 'h_tumour': h_mono[1],
+                                'mix_frac': mix_frac}, ploidy, max_depth))
+
+    def distance(ploidy):       # how far outside [min_ploidy, max_ploidy]
+        if min_ploidy is not None and ploidy < min_ploidy:
+            return min_ploidy - ploidy
+        if max_ploidy is not None and ploidy > max_ploidy:
+            return ploidy - max_ploidy
+        return 0.
+
+    keep = [distance(p) == 0. for _, p, _ in candidates]
+    if not any(keep):           # bounds too strict: the candidates closest to them
+        dists = [distance(p) for _, p, _ in candidates]
+        keep = [a == min(dists) for a in dists]
+    candidates = [c for c, k in zip(candidates, keep) if k]
+
+    # one depth threshold for all initialisations, so that their objectives are comparable
+    max_depth = min(d for _, _, d in candidates)
+    depth = experiment.x[:, 2] / experiment.l
+    below = np.sum((depth <= max_depth) * experiment.l) / np.sum(experiment.l)
+    if below < 0.75:
+        raise ValueError('Unable to model {} of the genome, consider reducing max ploidy or increasing max copy number'
+                         .format(1. - below))
+
+    init_params = []
+    for (h_p, _, _), w in itertools.product(candidates, divergence_weights):
+        params = h_p.copy()
+        params['divergence_weight'] = w
+        params['max_depth'] = max_depth
+        init_params.append(params)
+    if store is not None:
+        import pandas as pd
+        store['read_depth'] = read_depth
+        store['minor_modes'] = pd.Series(minor_modes, index=range(len(minor_modes)))
+    return dict(enumerate(init_params))
 
 
 def build_model(experiment, init_params, config, **model_kwargs):
@@ -222,30 +296,37 @@ def fit_grid_distributed(experiment, init_params_by_id, config, dist=None, devic
     return results, ordered, best, all_errors
 
 
-def _fit_results(model, experiment, init_params, config, cn):
-    """The ``fit_results`` dict of ``analysis/pipeline.py:195-228`` from a fitted driver and its MAP copy number."""
-    brk_cn = model.decode_breakpoints(cn)
-    cn = cn[model.seg_fwd_remap]
+def _fit_results(model, experiment, init_params, config, cn, pre=None):
+    """The ``fit_results`` dict of ``analysis/pipeline.py:195-228`` from a fitted driver and its MAP copy number.
+    ``pre`` (grid drivers) carries quantities already read for the whole grid in one device call."""
+    pre = pre or {}
+    brk_cn = pre['brk_cn'] if 'brk_cn' in pre else model.decode_breakpoints(cn)
+    fwd = model.seg_fwd_remap
+    cn = cn[fwd]
     if get_param(config, 'disable_breakpoints'):
         brk_cn = cn_model.decode_breakpoints_naive(cn, experiment.adjacencies, experiment.breakpoints)
+    h = pre['h'] if 'h' in pre else model.h
     results = dict()
-    results['h'] = model.h
+    results['h'] = h
     results['cn'] = cn
     results['brk_cn'] = brk_cn
-    results['p_outlier_total'] = model.p_outlier_total
-    results['p_outlier_allele'] = model.p_outlier_allele
-    results['total_likelihood_mask'] = model.total_likelihood_mask
-    results['allele_likelihood_mask'] = model.allele_likelihood_mask
+    results['p_outlier_total'] = pre['p_outlier_total'][fwd] if 'p_outlier_total' in pre else model.p_outlier_total
+    results['p_outlier_allele'] = pre['p_outlier_allele'][fwd] if 'p_outlier_allele' in pre else model.p_outlier_allele
+    results['total_likelihood_mask'] = (pre['total_likelihood_mask'][fwd] if 'total_likelihood_mask' in pre
+                                        else model.total_likelihood_mask)
+    results['allele_likelihood_mask'] = (pre['allele_likelihood_mask'][fwd] if 'allele_likelihood_mask' in pre
+                                         else model.allele_likelihood_mask)
     stats = dict()
     stats['elbo'] = model.prev_elbo
     stats['elbo_diff'] = model.prev_elbo_diff
     stats['error_message'] = ''
-    stats.update(model.get_likelihood_param_values())
+    stats.update(pre['params'] if 'params' in pre else model.get_likelihood_param_values())
     l = experiment.l
-    stats['num_clones'] = len(model.h)
+    stats['num_clones'] = len(h)
     stats['num_segments'] = len(experiment.x)
-    stats['ploidy'] = (cn[:, 1:, :].mean(axis=1).T * l).sum() / l.sum()
-    divergent = (cn[:, 1:, :].max(axis=1) != cn[:, 1:, :].min(axis=1)) * 1.
+    tumour = cn[:, 1:, :]
+    stats['ploidy'] = (tumour.mean(axis=1).T * l).sum() / l.sum()
+    divergent = (tumour.max(axis=1) != tumour.min(axis=1)) * 1.
     stats['proportion_divergent'] = (divergent.T * l).sum() / (2. * l.sum())
     stats['mode_idx'] = init_params.get('mode_idx', 0)
     stats['divergence_weight'] = init_params['divergence_weight']
@@ -253,6 +334,27 @@ def _fit_results(model, experiment, init_params, config, cn):
     # extension (not a reference key): the outcome of every M-step acceptance test, in call order
     results['decisions'] = list(getattr(model, 'decisions', []))
     return results
+
+
+def decode_breakpoints_grid(driver, cn_all, brk_states, transition_penalty):
+    """``BreakpointModel.decode_breakpoints`` (``cn_model.py:578-596``) for all G fits of a grid at once: the
+    breakend rows, orientations and breakpoint states are shared, so the reference's accumulation (rows ascending,
+    clones ascending -- kept, it fixes the rounding of every partial sum) runs once over ``(G, B)`` slabs instead
+    of G times over ``(B,)`` vectors.  Returns one ``{breakpoint_id: brk_states row}`` dict per fit."""
+    G = cn_all.shape[0]
+    bidx, borient = driver.breakpoint_idx, driver.breakpoint_orient
+    K, B, M = driver.num_breakpoints, brk_states.shape[0], brk_states.shape[1]
+    rows = np.flatnonzero(bidx[:cn_all.shape[1] - 1] >= 0)
+    log_p = np.zeros((G, K, B))
+    if rows.size:
+        tot_a = cn_all[:, rows].sum(axis=-1)            # (G, R, M)
+        tot_b = cn_all[:, rows + 1].sum(axis=-1)
+        d = tot_a - tot_b
+        for r, n in enumerate(rows):
+            for m in range(M):
+                log_p[:, bidx[n], :] += -transition_penalty * np.abs(d[:, r, m][:, np.newaxis] - borient[n] * brk_states[:, m])
+    best = log_p.argmax(axis=-1)                        # (G, K), first maximum as the reference's argmax
+    return [dict((driver.breakpoint_ids[k], brk_states[best[g, k]]) for k in range(K)) for g in range(G)]
 
 
 class _ModelListGrid(object):
@@ -284,7 +386,7 @@ class _ModelListGrid(object):
 
 
 def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_seed=1234, init_ids=None,
-                     mstep='lockstep', num_threads=8, profile=None, model_class=None):
+                     mstep='lockstep', num_threads=8, profile=None, model_class=None, trace=None):
     """The whole initialisation grid as ONE batch on one GPU: every E-step kernel launch serves all fits
     (``bpmodel.RemixtBatch``) and the M-steps of all fits advance in lock step (``mstep.GridMStep``: every round of
     objective evaluations of ``cn_model.py:482-569`` is one device call for the whole grid).
@@ -294,7 +396,8 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
     ``numpy.random.seed(random_seed)`` before ``pipeline.fit`` would see).  ``mstep='threads'`` keeps the per-fit
     scipy drivers of ``cn_model.BreakpointModel`` on ``num_threads`` host threads (A/B measurements).
     ``profile`` (a dict) receives wall-clock seconds per phase.  ``model_class`` (tests) runs the same driver over G
-    independent models of another ``RemixtModel`` implementation.  Returns ``(results, best, errors)`` like
+    independent models of another ``RemixtModel`` implementation.  ``trace`` (a list) receives ``(h, dispersions,
+    elbo)`` of all fits after every EM iteration.  Returns ``(results, best, errors)`` like
     :func:`fit_grid`; a fit that fails is reported in ``errors`` and leaves the grid.
     """
     import time
@@ -371,6 +474,9 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         elbo = batch.calculate_elbo()
         for g, d in enumerate(drivers):
             d.record_iteration(i, float(elbo[g]))
+        if trace is not None:       # per EM iteration: h (G,M), the dispersions (G,P), ELBO (G)
+            trace.append((backend.get_h(), np.array([backend.get_param(n) for n in d0.likelihood_params]).T.copy(),
+                          np.array(elbo, dtype=float)))
         t3 = time.perf_counter()
         prof['e_step'] += t1 - t0
         prof['m_step'] += t2 - t1
@@ -380,11 +486,35 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
     batch.infer_cn(cn)
     t1 = time.perf_counter()
     results = {}
-    for g, d in enumerate(drivers):
-        if g not in errors:
-            results[ids[g]] = _fit_results(d, experiment, init_params_by_id[ids[g]], config, cn[g])
+    pre = [dict() for _ in drivers]
+    if model_class is None:
+        # one device read per quantity for the whole grid instead of one per fit
+        brk = decode_breakpoints_grid(d0, cn, np.asarray(batch.brk_states), abs(d0.transition_log_prob))
+        h_all, pot, poa = np.array(batch.h), batch.p_outlier_total, batch.p_outlier_allele
+        par = dict((name, np.array(getattr(batch, name))) for name in d0.likelihood_params)
+        for g, d in enumerate(drivers):
+            pre[g] = dict(brk_cn=brk[g], h=h_all[g], p_outlier_total=pot[g], p_outlier_allele=poa[g],
+                          params=dict((name, float(par[name][g])) for name in d0.likelihood_params),
+                          total_likelihood_mask=d._total_likelihood_mask.astype(int),
+                          allele_likelihood_mask=d._allele_likelihood_mask.astype(int))
+    todo = [g for g in range(len(drivers)) if g not in errors]
+
+    def assemble(g):
+        return _fit_results(drivers[g], experiment, init_params_by_id[ids[g]], config, cn[g], pre[g])
+
+    # index remaps and length-weighted statistics over N segments per fit: numpy releases the GIL inside them
+    nt = min(len(todo), _mstep._host_threads()) if model_class is None else 1
+    if nt > 1:
+        import concurrent.futures
+        with concurrent.futures.ThreadPoolExecutor(nt) as pool:
+            done = list(pool.map(assemble, todo))
+    else:
+        done = [assemble(g) for g in todo]
+    for g, r in zip(todo, done):
+        results[ids[g]] = r
     prof['mstep_rounds'] = lock.rounds
     prof['mstep_evaluations'] = lock.evaluations
+    prof['mstep_seconds'] = dict(lock.seconds)
     batch.close()       # results hold host arrays only; the device blocks go back to the pool now
     errors_by_id = dict((ids[g], e) for g, e in errors.items())
     if errors_by_id and not results:

@@ -36,6 +36,10 @@ def compare(ref, k, cand):
         'decisions_match': bool(acc.shape == acc_ref.shape and np.array_equal(acc, acc_ref)),
         'first_decision_mismatch': (int(np.flatnonzero(acc != acc_ref)[0]) if acc.shape == acc_ref.shape and (acc != acc_ref).any() else None),
         'proportion_divergent_diff': float(abs(cand['proportion_divergent'] - ref['proportion_divergent'][k])),
+        # E[LL] after - before of the acceptance test at the first mismatching decision (a margin at rounding level
+        # means the reference's own decision there is decided by rounding)
+        'margin_at_first_mismatch': (float(cand['margins'][int(np.flatnonzero(acc != acc_ref)[0])])
+                                     if 'margins' in cand and acc.shape == acc_ref.shape and (acc != acc_ref).any() else None),
     }
 
 
@@ -86,7 +90,9 @@ def run(name, mstep='lockstep'):
     cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
     prof = {}
     t0 = time.perf_counter()
-    res, best, errors = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']), mstep=mstep, profile=prof)
+    trace = []
+    res, best, errors = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']), mstep=mstep, profile=prof,
+                                                  trace=trace)
     wall = time.perf_counter() - t0
     gi = [int(i) for i in g['init_ids']]
     rows = []
@@ -95,9 +101,15 @@ def run(name, mstep='lockstep'):
             continue
         cand = dict(elbo=r['stats']['elbo'], h=r['h'], params=[r['stats'][k] for k in PARAMS4], cn=r['cn'],
                     brk_cn=np.array([r['brk_cn'][str(b)] for b in g['brk_ids']]),
-                    accept=[a for _, a in r['decisions']], proportion_divergent=r['stats']['proportion_divergent'])
+                    accept=[d[1] for d in r['decisions']], margins=[d[3] - d[2] for d in r['decisions']], proportion_divergent=r['stats']['proportion_divergent'])
         row = compare(g, gi.index(i), cand)
         row['init_id'] = int(i)
+        # trajectory: relative deviation of (h, dispersions, ELBO) from the reference after every EM iteration
+        k = gi.index(i)
+        rel = lambda a, b: float(np.max(np.abs(np.asarray(a, float) - np.asarray(b, float)) / np.maximum(np.abs(np.asarray(b, float)), 1e-300)))
+        row['trajectory_rel_dev'] = [[rel(t[0][i], g['trace_h'][k][e]), rel(t[1][i], g['trace_params'][k][e]),
+                                      rel(t[2][i], g['trace_elbo'][k][e])] for e, t in enumerate(trace)]
+        row['margins'] = [float(m) for m in cand['margins']]
         rows.append(row)
     out = {
         'fixture': name, 'mstep': mstep, 'wall_s': wall, 'profile': prof,

@@ -109,7 +109,7 @@ def test_host_grid_driver_full_fits_on_reference_model_are_bit_exact(ref_bpmodel
     assert np.array_equal(r['cn'], g['cn'][k])
     assert np.array_equal(np.array([r['brk_cn'][str(i)] for i in g['brk_ids']]), g['brk_cn'][k])
     assert [r['stats'][n] for n in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')] == list(g['params'][k])
-    assert [bool(a) for _, a in r['decisions']] == [bool(a) for a in g['accept'][k].ravel()]
+    assert [bool(d[1]) for d in r['decisions']] == [bool(a) for a in g['accept'][k].ravel()]
     assert r['stats']['proportion_divergent'] == float(g['proportion_divergent'][k])
 
 
@@ -130,3 +130,19 @@ def test_decode_breakpoints_naive():
     brk = {'a': frozenset([(0, 1), (2, 0)])}
     out = cn_model.decode_breakpoints_naive(cn, adj, brk)
     assert np.array_equal(out['a'], [0, 1])
+
+
+def test_decode_breakpoints_grid_equals_per_fit_decode():
+    """pipeline.decode_breakpoints_grid (all fits at once) == BreakpointModel.decode_breakpoints per fit."""
+    from oracle import bpmodel_np
+    from remixt_b200 import pipeline
+    exp = util.load_experiment('small')
+    d = util.make_driver(exp, util.init_params('small', 0), model_class=bpmodel_np.RemixtModel)
+    rng = np.random.RandomState(5)
+    cn = rng.randint(0, 4, size=(4, d.N1, 3, 2)).astype(np.int64)
+    cn[:, :, 0, :] = 1
+    got = pipeline.decode_breakpoints_grid(d, cn, np.asarray(d.model.brk_states), d.model.transition_penalty)
+    for g in range(4):
+        want = d.decode_breakpoints(cn[g])
+        assert list(got[g]) == list(want)
+        assert all(np.array_equal(got[g][k], want[k]) for k in want)

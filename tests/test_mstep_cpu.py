@@ -51,6 +51,61 @@ def test_neldermead_coroutine_equals_scipy_fmin(k, x0):
     assert fval == fopt or (np.isnan(fval) and np.isnan(fopt))
 
 
+def test_native_choice_equals_numpy_randomstate_choice():
+    """rmx_host_sample_segments == RandomState.choice(n, size, replace=False, p) draw by draw, and leaves every stream
+    in the state numpy leaves it in (so all later draws agree too)."""
+    n, size, G = 3011, 200, 5
+    rng = np.random.RandomState(3)
+    plans = []
+    for g in range(G):
+        w1 = rng.rand(n) ** 8          # spiky: many collisions, several rounds of the rejection loop
+        w2 = rng.rand(n)
+        w2[rng.rand(n) < 0.9] = 0.     # barely more non-zero entries than the sample size
+        plans.append([None, w1 / w1.sum(), w2 / w2.sum(), None, w1 / w1.sum()])
+    weights = [[plans[g][d] for g in range(G)] for d in range(5)]
+    mine = [np.random.RandomState(100 + g) for g in range(G)]
+    ref = [np.random.RandomState(100 + g) for g in range(G)]
+    for rs in mine + ref:
+        rs.rand(1000 + 7)              # somewhere inside the stream, position not a multiple of 624
+    chosen, status = mstep.native_choice(mine, n, size, weights, num_threads=3)
+    assert not status.any()
+    for g in range(G):
+        for d in range(5):
+            want = ref[g].choice(n, size=size, replace=False, p=plans[g][d])
+            assert np.array_equal(chosen[d, g], want), (g, d)
+        assert np.array_equal(mine[g].get_state()[1], ref[g].get_state()[1]) and mine[g].get_state()[2] == ref[g].get_state()[2]
+        assert mine[g].rand() == ref[g].rand()
+    # numpy's errors
+    bad = np.zeros(n)
+    bad[:50] = 1. / 50
+    _, st = mstep.native_choice([np.random.RandomState(1)], n, size, [[bad], [None]])
+    assert st[0, 0] == 4 and st[1, 0] == -1
+    with pytest.raises(ValueError, match='Fewer non-zero'):
+        np.random.RandomState(1).choice(n, size=size, replace=False, p=bad)
+    _, st = mstep.native_choice([np.random.RandomState(1)], n, size, [[np.full(n, 2. / n)]])
+    assert st[0, 0] == 1
+
+
+def test_weights_block_equals_per_fit_weights():
+    """BatchBackend.weights_block (one strided (G, N) block) == the per-fit ``w / w.sum()`` of get_param_sample_weight,
+    bit for bit (numpy's pairwise sum runs over the same strided elements in both forms)."""
+    class FakeBatch(object):
+        num_fits, num_segments, num_clones = 6, 30105, 3
+    be = mstep.BatchBackend(FakeBatch())
+    rng = np.random.RandomState(2)
+    be._cache['p_outlier_total'] = rng.rand(6, 30105, 2) ** 3
+    be._cache['p_outlier_total'][4, :, 1] = 0.          # nothing to weight by: uniform sample
+    out = np.empty((6, 30105))
+    flags = be.weights_block('negbin_r_1', list(range(6)), out)
+    assert list(flags) == [1, 1, 1, 1, 0, 1]
+    for g in (0, 1, 2, 3, 5):
+        w = be.outlier_weights('negbin_r_1', g)
+        assert np.array_equal(out[g], w / w.sum())
+    sub = np.empty((2, 30105))
+    be.weights_block('negbin_r_1', [1, 5], sub)
+    assert np.array_equal(sub[0], out[1]) and np.array_equal(sub[1], out[5])
+
+
 def test_rendezvous_batches_every_round():
     import threading
     workers = list(range(7))
@@ -79,8 +134,15 @@ def test_rendezvous_batches_every_round():
     assert seen == [list(range(r, 7)) for r in range(7)]       # round r holds exactly the workers still running
 
 
+def test_lbfgsb_coroutine_reproduces_scipy_minimize():
+    """The generator over scipy's compiled setulb visits the points scipy.optimize.minimize(method='L-BFGS-B') visits
+    and returns its result (checked on this scipy; GridMStep falls back to blocking scipy calls on threads if not)."""
+    assert mstep.lbfgsb_coroutine_ok()
+
+
 @pytest.mark.slow
-def test_lockstep_equals_per_fit_driver_on_reference_model(ref_bpmodel):
+@pytest.mark.parametrize('lbfgsb', ['coroutine', 'threads'])
+def test_lockstep_equals_per_fit_driver_on_reference_model(ref_bpmodel, lbfgsb):
     """G reference models advanced by GridMStep == the same models advanced one by one by BreakpointModel's own
     update_h / update_param: h, dispersions, decisions bit for bit, and the same objective evaluations in order."""
     exp = util.load_experiment('small')
@@ -120,7 +182,7 @@ def test_lockstep_equals_per_fit_driver_on_reference_model(ref_bpmodel):
         d.em_update_h()
         d.em_update_params()
     be = mstep.ModelListBackend([d.model for d in b])
-    ms = mstep.GridMStep(be, b)
+    ms = mstep.GridMStep(be, b, lbfgsb=lbfgsb)
     ms.run()
     assert not ms.errors
     for g in range(G):
