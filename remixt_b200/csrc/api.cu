@@ -1854,7 +1854,19 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         if (b->ms_all) {
             // every segment: the likelihood table of the fits whose parameters changed (the kernel of the E-step,
             // which the next E-step then finds ready), its posterior-weighted sums, and one value per segment
-            int rc = ensure_asum(m, 0, G);
+            // (fits outside the active set keep their stale table until something needs it)
+            int rc = RMX_OK;
+            for (int g = 0; g < G && !rc;) {
+                if (active && !active[g]) { ++g; continue; }
+                int e = g + 1;
+                while (e < G && (!active || active[e])) ++e;
+                Model run = *m;
+                run.g0 = g;
+                run.gn = e - g;
+                rc = ensure_asum(&run, g, e - g);
+                if (rc) m->err = run.err;
+                g = e;
+            }
             if (rc) return rc;
             double* rowe = b->rowv + 7 * (size_t)b->d.N;
             rmx_launch_ell_rows_from_sums(b->stream, b->d, 0, G, b->Asum, b->q_ot, b->q_oa, b->q_sw, rowe, (int64_t)8 * b->d.N);

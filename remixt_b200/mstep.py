@@ -280,6 +280,10 @@ class BatchBackend(object):
         self.num_segments = batch.num_segments
         self.num_clones = batch.num_clones
         self._cache = {}
+        self._param_names = ['negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1']
+        if not getattr(batch, 'normal_contamination', True):
+            self._param_names += ['negbin_hdel_mu', 'negbin_hdel_r_0', 'negbin_hdel_r_1', 'betabin_loh_p',
+                                  'betabin_loh_M_0', 'betabin_loh_M_1']
 
     def new_iteration(self):
         self._cache.clear()
@@ -295,6 +299,12 @@ class BatchBackend(object):
             self._arr('p_outlier_total')
         if any(p.startswith('betabin') for p in plan):
             self._arr('p_outlier_allele')
+
+    def state_keys(self):
+        """Per fit, the bytes of (h, every likelihood parameter): what the full-data E[LL] depends on."""
+        cols = [np.array(self.batch.h)] + [np.array(getattr(self.batch, n)).reshape(self.G, 1) for n in self._param_names]
+        block = np.ascontiguousarray(np.concatenate(cols, axis=1))
+        return [block[g].tobytes() for g in range(self.G)]
 
     def get_h(self):
         return np.array(self.batch.h)
@@ -534,6 +544,7 @@ class GridMStep(object):
     def __init__(self, backend, drivers, errors=None, lbfgsb='auto'):
         self.lbfgsb = lbfgsb    # 'auto' | 'coroutine' | 'threads'
         self.native_sampling = True
+        self._full_cache = {}
         self._wbuf = {}         # reusable weight block of the native sampler (fresh pages cost more than the draws)
         self.be = backend
         self.drivers = drivers
@@ -632,9 +643,26 @@ class GridMStep(object):
         return self.be.evaluate(**kw)
 
     def _full_ell(self, alive):
+        """E[LL] over every segment for the fits ``alive``.  The value is a function of the fit's (h, dispersions)
+        alone while the E-step's factors stand, and the device evaluation is deterministic, so a fit whose parameters
+        are back at a state already evaluated in this M-step (a rejected step restores them) takes the stored value:
+        bit for bit what a fresh evaluation would return."""
         t0 = time.perf_counter()
-        self.be.stage(None)
-        out = self._evaluate(active=alive)[:, 0]
+        keys = self.be.state_keys() if hasattr(self.be, 'state_keys') else None
+        out = np.zeros(self.G)
+        need = np.array(alive, dtype=np.uint8)
+        if keys is not None:
+            for g in np.flatnonzero(alive):
+                v = self._full_cache.get((int(g), keys[g]))
+                if v is not None:
+                    out[g], need[g] = v, 0
+        if need.any():
+            self.be.stage(None)
+            got = self._evaluate(active=need)[:, 0]
+            for g in np.flatnonzero(need):
+                out[g] = got[g]
+                if keys is not None:
+                    self._full_cache[(int(g), keys[g])] = got[g]
         self.seconds['full_data_ell'] += time.perf_counter() - t0
         return out
 
@@ -844,6 +872,7 @@ class GridMStep(object):
     def run(self):
         """``em_update_h`` + ``em_update_params`` (``cn_model.py:411-416``) for the whole grid."""
         self.be.new_iteration()
+        self._full_cache = {}
         d0 = self.drivers[0]
         plan = (['h'] if d0.do_h_update else []) + list(d0.likelihood_params)
         t0 = time.perf_counter()

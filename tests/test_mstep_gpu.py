@@ -1,0 +1,170 @@
+"""Batched M-step and free-running full fits on the GPU (through the C-ABI).
+
+* rmx_mstep_evaluate against the per-fit calculate_expected_log_likelihood[_partial_h] of the same models (and,
+  through the golden steps, the compiled reference);
+* the init grids of `small` (48 inits) and `config1` (36 inits) fitted FREE-RUNNING by pipeline.fit_grid_batched
+  against the reference's own free-running fits (tests/golden/grid_*.npz, oracle/make_golden.py grid): selected
+  init_id equal, MAP copy number / breakpoint copy number of the selected solution bit-exact, and the measured
+  agreement of every other fit (profiles/r02_fullfit_parity.json records the same numbers).
+"""
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+PARAMS4 = ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')
+
+
+def _batch(name, ids, rounds=2):
+    from remixt_b200 import bpmodel, pipeline
+    exp = util.load_experiment(name)
+    cfg = {'max_copy_number': 6}
+    inits = [util.init_params(name, i) for i in ids]
+    drivers = [pipeline.build_model(exp, ip, cfg, random_state=np.random.RandomState(7)) for ip in inits]
+    h = np.array([pipeline.init_h(ip) for ip in inits])
+    dw = np.array([ip['divergence_weight'] for ip in inits])
+    batch = bpmodel.RemixtBatch(*(drivers[0].model_args(h, compact=True) + (dw,)))
+    for g, d in enumerate(drivers):
+        d.attach(batch.fit(g))
+    batch.variational_update(rounds)
+    return batch, drivers
+
+
+def test_mstep_evaluate_equals_per_fit_calls():
+    batch, drivers = _batch('small', [0, 7, 21, 40])
+    G, N = batch.num_fits, batch.num_segments
+    rng = np.random.RandomState(3)
+    masks = np.zeros((G, N), dtype=np.int64)
+    rows = np.zeros((G, 24), dtype=np.int32)
+    for g in range(G):
+        rows[g] = np.sort(rng.choice(N, 24, replace=False))
+        masks[g, rows[g]] = 1
+    # sampled objective and gradient at a new h per fit
+    h = np.array(batch.h) * (1. + 0.05 * rng.rand(G, 3))
+    batch.mstep_stage_rows(rows, np.full(G, 24))
+    ell, grad = batch.mstep_evaluate(h=h, grad=True)
+    for g in range(G):
+        m = batch.fit(g)
+        assert np.array_equal(m.h, h[g])
+        util.assert_close(ell[g, 0], m.calculate_expected_log_likelihood(masks[g]), rtol=1e-12, what='ell')
+        out = np.zeros(3)
+        m.calculate_expected_log_likelihood_partial_h(masks[g], out)
+        util.assert_close(grad[g], out, rtol=1e-12, what='grad')
+    # mask form == row form
+    batch.mstep_stage_sample(masks)
+    assert np.array_equal(batch.mstep_evaluate(), ell)
+    # a parameter grid: only the terms the parameter enters are re-evaluated, the rest comes from the per-sample constant
+    for name in PARAMS4:
+        vals = np.sort(rng.uniform(20., 1500., size=(G, 5)), axis=1)
+        got = batch.mstep_evaluate(name=name, values=vals)
+        assert np.array_equal(np.array(getattr(batch, name)), vals[:, -1])          # left at the last value
+        for g in range(G):
+            m = batch.fit(g)
+            for v in range(5):
+                setattr(m, name, vals[g, v])
+                util.assert_close(got[g, v], m.calculate_expected_log_likelihood(masks[g]), rtol=1e-12, what=name)
+    # active subset: the others untouched
+    before = np.array(batch.negbin_r_0)
+    act = np.array([1, 0, 1, 0], dtype=np.uint8)
+    got = batch.mstep_evaluate(active=act, name='negbin_r_0', values=np.full((G, 1), 333.))
+    assert np.array_equal(np.array(batch.negbin_r_0), np.where(act, 333., before))
+    assert got[1, 0] == 0. and got[3, 0] == 0. and got[0, 0] != 0.
+    # every segment: the likelihood-table path against the per-fit evaluation on an all-ones sample
+    batch.mstep_stage_sample(None)
+    full = batch.mstep_evaluate()[:, 0]
+    ones = np.ones(N, dtype=np.int64)
+    for g in range(G):
+        util.assert_close(full[g], batch.fit(g).calculate_expected_log_likelihood(ones), rtol=1e-11, what='full')
+    vals = np.array([[900.], [40.], [15.], [1999.]])
+    full2 = batch.mstep_evaluate(name='betabin_M_1', values=vals)[:, 0]
+    for g in range(G):
+        util.assert_close(full2[g], batch.fit(g).calculate_expected_log_likelihood(ones), rtol=1e-11, what='full2')
+    batch.close()
+
+
+def test_mstep_evaluate_matches_reference_golden():
+    """The batched objective on the golden sample of steps_small.npz == the compiled reference's value."""
+    g = util.golden('steps_small.npz')
+    batch, drivers = _batch('small', [int(g['init_id'])] * 2, rounds=2)
+    batch.mstep_stage_sample(np.array([g['sample'], g['sample']]))
+    ell, grad = batch.mstep_evaluate(grad=True)
+    util.assert_close(ell[:, 0], [g['ell_sample']] * 2, rtol=1e-9, what='ell_sample')
+    util.assert_close(grad, [g['grad_sample']] * 2, rtol=1e-8, what='grad_sample')
+    batch.mstep_stage_sample(None)
+    util.assert_close(batch.mstep_evaluate()[:, 0], [g['ell_all']] * 2, rtol=1e-9, what='ell_all')
+    batch.close()
+
+
+def _grid(name):
+    from remixt_b200 import pipeline
+    g = util.golden('grid_%s.npz' % name)
+    exp = util.load_experiment(name)
+    inits = dict((i, util.init_params(name, i)) for i in range(util.num_inits(name)))
+    cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
+    res, best, errors = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']))
+    return g, res, best, errors
+
+
+def _agreement(g, res):
+    gi = [int(i) for i in g['init_ids']]
+    rows = {}
+    for i, r in res.items():
+        if i not in gi:
+            continue
+        k = gi.index(i)
+        brk = np.array([r['brk_cn'][str(b)] for b in g['brk_ids']])
+        rows[i] = dict(map_exact=np.array_equal(r['cn'], g['cn'][k]), brk_exact=np.array_equal(brk, g['brk_cn'][k]),
+                       decisions=[bool(d[1]) for d in r['decisions']] == [bool(a) for a in g['accept'][k].ravel()],
+                       elbo=abs(r['stats']['elbo'] - g['elbo'][k]) / abs(g['elbo'][k]),
+                       h=float(np.max(np.abs(r['h'] - g['h'][k]) / g['h'][k])))
+    return rows
+
+
+def test_free_running_grid_small_vs_reference():
+    """48 inits x 5 EM x 5 VI, nothing forced: the selection and EVERY fit's MAP output equal the reference's."""
+    g, res, best, errors = _grid('small')
+    assert best == int(g['best_init_id'])
+    rows = _agreement(g, res)
+    assert len(rows) == len(g['init_ids'])
+    assert all(r['map_exact'] and r['brk_exact'] and r['decisions'] for r in rows.values()), \
+        [i for i, r in rows.items() if not (r['map_exact'] and r['brk_exact'] and r['decisions'])]
+    # north_star: ELBO within 1e-6 relative; h moves by what the reference's own M-step moves under a 1e-13
+    # perturbation of its input (grid_small_perturbed.npz: 1.4e-6), measured here at 3.3e-6
+    assert max(r['elbo'] for r in rows.values()) < 1e-6
+    assert max(r['h'] for r in rows.values()) < 1e-5
+    # the one init the reference loses to an L-BFGS-B line-search failure (and does not lose after the 1e-13
+    # perturbation) may or may not fail here; it must not be the selected one either way
+    assert set(errors) <= set(int(i) for i in g['failed_ids'])
+
+
+def test_free_running_grid_config1_vs_reference():
+    """36 inits of BASELINE config 1 (1000 segments, one chromosome): selected init and its MAP output bit-exact;
+    the other fits agree bit-exactly unless an M-step decision of the reference itself is decided by rounding
+    (measured: 34 of 36 trajectories identical, see profiles/r02_fullfit_parity.json)."""
+    g, res, best, errors = _grid('config1')
+    assert not errors
+    assert best == int(g['best_init_id'])
+    rows = _agreement(g, res)
+    sel = rows[best]
+    assert sel['map_exact'] and sel['brk_exact'] and sel['decisions'] and sel['elbo'] < 1e-6
+    same = [i for i, r in rows.items() if r['decisions']]
+    assert len(same) >= 32
+    for i in same:      # same decisions => same output
+        assert rows[i]['map_exact'] and rows[i]['brk_exact'] and rows[i]['elbo'] < 1e-6, i
+
+
+def test_lockstep_and_per_fit_mstep_agree_on_gpu():
+    """The lock-step grid driver against per-fit scipy drivers on views of the same batch (mstep='threads')."""
+    from remixt_b200 import pipeline
+    exp = util.load_experiment('small')
+    inits = dict((i, util.init_params('small', i)) for i in (1, 9, 29))
+    cfg = {'max_copy_number': 6, 'num_em_iter': 2, 'num_update_iter': 3}
+    a, best_a, _ = pipeline.fit_grid_batched(exp, inits, cfg, mstep='lockstep')
+    b, best_b, _ = pipeline.fit_grid_batched(exp, inits, cfg, mstep='threads', num_threads=2)
+    assert best_a == best_b
+    for i in inits:
+        assert np.array_equal(a[i]['cn'], b[i]['cn'])
+        util.assert_close(a[i]['stats']['elbo'], b[i]['stats']['elbo'], rtol=1e-7, what='elbo')
+        assert [d[1] for d in a[i]['decisions']] == [d[1] for d in b[i]['decisions']]
