@@ -151,6 +151,8 @@ struct Batch {
     double* stab = nullptr;
     double* segf = nullptr;
     double* logq = nullptr;      // (G,K,B) log q of update_p_breakpoint before normalisation (sharded fits)
+    uint8_t* bc_tab = nullptr;   // states grouped by tumour-clone totals: [perm (4 KBB)][kbcls (KBB)][scls (S)][didx (BC,BC)][ddel (ND,M)]
+    int BC = 0, KBB = 0, ND = 0;
     uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
     int* hgstart = nullptr;
     int Q = 0;
@@ -480,9 +482,14 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
         cudaEvent_t te = b->tbegin(RMX_K_CHAIN);
         static const bool force_streamed = getenv("RMX_CHAIN_STREAMED") != nullptr;   // A/B measurements only
-        lc = force_streamed ? 2
-                            : rmx_launch_chain_mma(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp,
-                                                b->mF, b->ahat, b->bhat, b->chain_logz, b->dflags);
+        static const bool force_v1 = getenv("RMX_CHAIN_V1") != nullptr;               // A/B measurements only
+        lc = (force_streamed || force_v1)
+                 ? 2
+                 : rmx_launch_chain_mma2(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp, b->mF,
+                                         b->ahat, b->bhat, b->chain_logz, b->dflags, b->bc_tab, b->BC, b->KBB, b->ND);
+        if (lc == 2 && !force_streamed)
+            lc = rmx_launch_chain_mma(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp,
+                                      b->mF, b->ahat, b->bhat, b->chain_logz, b->dflags);
         if (lc == 2)    // state spaces above 128: transition matrix streamed from L2 (chain.cu)
             lc = rmx_launch_chain(b->stream, tables(b), b->d, chainsof(b), rowsof(b), sp, b->rmd, g, n, b->fexp, b->mF,
                                   b->ahat, b->bhat, b->chain_logz, b->dflags);
@@ -843,7 +850,55 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(upload(b, &b->borient, borient));
     CCK(upload(b, &b->tclass, tclass));
     CCK(upload(b, &b->brow, brow));
-    if (b->C <= 254 && b->R < (1 << 19)) {     // packed row info of the one-barrier chain kernel (chain_mma.cu)
+    bool d0_fits = true;        // the packed row info holds d0 + 8 in four bits
+    for (size_t n = 0; n < d0.size(); ++n) d0_fits = d0_fits && d0[n] >= -8 && d0[n] <= 7;
+    if (S <= 250) {
+        // states grouped by the totals of their tumour clones (the breakend rows of chain_mma2.cu): classes in order of
+        // first appearance, each padded to whole row blocks of four states (255 = padding)
+        std::vector<std::vector<int>> keys;
+        std::vector<uint8_t> scls(S);
+        for (int s2 = 0; s2 < S; ++s2) {
+            std::vector<int> key(M, 0);
+            for (int mm = 1; mm < M; ++mm)
+                key[mm] = b->h_tab[((size_t)s2 * M + mm) * 2] + b->h_tab[((size_t)s2 * M + mm) * 2 + 1];
+            size_t c = 0;
+            while (c < keys.size() && keys[c] != key) ++c;
+            if (c == keys.size()) keys.push_back(key);
+            scls[s2] = (uint8_t)(c < 255 ? c : 255);
+        }
+        if (keys.size() <= 64) {
+            std::vector<uint8_t> perm, kbcls;
+            for (size_t c = 0; c < keys.size(); ++c) {
+                for (int s2 = 0; s2 < S; ++s2)
+                    if (scls[s2] == c) perm.push_back((uint8_t)s2);
+                while (perm.size() % 4) perm.push_back(255);
+                while (kbcls.size() < perm.size() / 4) kbcls.push_back((uint8_t)c);
+            }
+            // the distinct tuples of per-clone total differences between two classes, and which one each pair is
+            std::vector<std::vector<int>> dels;
+            std::vector<uint8_t> didx(keys.size() * keys.size());
+            for (size_t ci = 0; ci < keys.size(); ++ci)
+                for (size_t cj = 0; cj < keys.size(); ++cj) {
+                    std::vector<int> del(M, 0);
+                    for (int mm = 1; mm < M; ++mm) del[mm] = keys[ci][mm] - keys[cj][mm];
+                    size_t q = 0;
+                    while (q < dels.size() && dels[q] != del) ++q;
+                    if (q == dels.size()) dels.push_back(del);
+                    didx[ci * keys.size() + cj] = (uint8_t)(q < 255 ? q : 255);
+                }
+            std::vector<uint8_t> bc(perm);
+            bc.insert(bc.end(), kbcls.begin(), kbcls.end());
+            bc.insert(bc.end(), scls.begin(), scls.end());
+            bc.insert(bc.end(), didx.begin(), didx.end());
+            for (size_t q = 0; q < dels.size(); ++q)
+                for (int mm = 0; mm < M; ++mm) bc.push_back((uint8_t)(dels[q][mm] + 128));
+            b->ND = (int)dels.size();
+            b->BC = (int)keys.size();
+            b->KBB = (int)kbcls.size();
+            CCK(upload(b, &b->bc_tab, bc));
+        }
+    }
+    if (b->C <= 254 && b->R < (1 << 19) && d0_fits) {     // packed row info of the one-barrier chain kernels
         std::vector<int> rinfo(tclass.size());
         for (size_t n = 0; n < tclass.size(); ++n)
             rinfo[n] = (tclass[n] + 1) | ((d0[n] + 8) << 8) | ((brow[n] + 1) << 12);

@@ -98,6 +98,12 @@ int rmx_launch_chain(cudaStream_t st, const RmxTables& T, const RmxDims& d, cons
 int rmx_launch_chain_mma(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
                          const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
                          const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags);
+// second generation of the same (chain_mma2.cu): four DMMA warps with balanced column blocks, the last state of
+// S = 97 on the vector pipe, per-segment bookkeeping inside the DMMA block; returns 2 for shapes it does not cover
+int rmx_launch_chain_mma2(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
+                          const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
+                          const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags,
+                          const uint8_t* bc, int BC, int KBB, int ND);
 void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* ahat, const double* bhat,
                      double* post, int* dflags);
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
