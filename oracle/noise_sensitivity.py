@@ -76,7 +76,8 @@ def main():
            'failed_ids': np.array([f['init_id'] for f in fits if f['error']], dtype=np.int64)}
     for k in ('elbo', 'h', 'params', 'ploidy', 'proportion_divergent', 'cn', 'brk_cn', 'accept'):
         out[k] = np.array([f[k] for f in ok])
-    np.savez_compressed(os.path.join(ROOT, 'tests', 'golden', 'grid_%s_noise.npz' % name), **out)
+    tag = '' if eps == 1e-15 else '_%g' % eps
+    np.savez_compressed(os.path.join(ROOT, 'tests', 'golden', 'grid_%s_noise%s.npz' % (name, tag)), **out)
     print(name, 'noise %g:' % eps, len(ok), 'fits,', len(fits) - len(ok), 'failed, best', best)
 
 

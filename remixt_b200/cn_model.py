@@ -267,14 +267,30 @@ class BreakpointModel(object):
     def get_likelihood_param_values(self):
         return dict((name, getattr(self.model, name)) for name in self.likelihood_params)
 
-    def get_model_data(self):
+    # the reference's ``cdef public`` attributes that are plain values or per-segment / per-breakpoint arrays
+    # (bpmodel.pyx:398-456); the three (N-1, S, S) arrays and ``framelogprob`` / ``posterior_marginals`` are listed
+    # separately because a device model materialises them on demand (gigabytes at whole-genome size)
+    _MODEL_DATA = ('num_clones', 'num_segments', 'num_breakpoints', 'num_alleles', 'cn_max', 'num_cn_states',
+                   'num_brk_states', 'normal_contamination', 'transition_penalty', 'divergence_weight',
+                   'transition_model', 'hmm_log_norm_const', 'prior_outlier_total', 'prior_outlier_allele',
+                   'negbin_r_0', 'negbin_r_1', 'negbin_hdel_mu', 'negbin_hdel_r_0', 'negbin_hdel_r_1',
+                   'betabin_M_0', 'betabin_M_1', 'betabin_loh_p', 'betabin_loh_M_0', 'betabin_loh_M_1',
+                   'h', 'l', 'x', 'y', 'brk_states', 'is_telomere', 'breakpoint_idx', 'breakpoint_orient',
+                   'p_breakpoint', 'p_allele_swap', 'p_outlier_total', 'p_outlier_allele',
+                   'total_likelihood_mask', 'allele_likelihood_mask')
+    _MODEL_DATA_LARGE = ('framelogprob', 'posterior_marginals', 'log_transmat', 'cached_log_transmat',
+                         'joint_posterior_marginals')
+
+    def get_model_data(self, large=False):
+        """The model's public state as a dict (``cn_model.py:286-297``, which walks ``dir(model)``).  On a device model
+        that walk would materialise three (N-1, S, S) arrays (2.3 GB each at whole-genome size) and trip over
+        properties that are undefined before ``infer_cn``; here the attributes are named, and the large ones are
+        included only on request (``large=True``)."""
         data = {}
-        for a in dir(self.model):
-            if a.startswith('_'):
+        for a in self._MODEL_DATA + (self._MODEL_DATA_LARGE if large else ()):
+            if not hasattr(type(self.model), a) and not hasattr(self.model, a):
                 continue
             value = getattr(self.model, a)
-            if callable(value):
-                continue
             data[a] = np.asarray(value) if type(value).__name__ == '_memoryviewslice' else value
         return data
 

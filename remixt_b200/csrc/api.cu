@@ -429,6 +429,8 @@ static int sync_check(Model* m) {
     Batch* b = m->b.get();
     cudaError_t e = cudaMemcpyAsync(b->hflags, b->dflags, sizeof(int), cudaMemcpyDeviceToHost, b->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+    // a launch that could not be configured (the launchers return nothing) leaves its error here
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) {
         char buf[512];
         snprintf(buf, sizeof buf, "CUDA error %s: %s", cudaGetErrorName(e), cudaGetErrorString(e));

@@ -1502,10 +1502,9 @@ void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int 
     const size_t base = (pair_smem(d) + 15) & ~(size_t)15;
     const size_t smem2 = base + sizeof(double) * ((size_t)d.S * d.S + (size_t)(d.M - 1) * HIST2_TV * HIST2_SP) + 16;
     if (hord != nullptr && rmx_hist2_ok(d) && smem2 <= 200 * 1024) {
-        static bool attr_set = false;
-        if (!attr_set) {
+        static RmxPerDeviceOnce attr_once;
+        if (attr_once.need()) {
             cudaFuncSetAttribute(k_hist2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            attr_set = true;
         }
         k_hist2<<<dim3(R, gn), 256, smem2, st>>>(d, g0, rows, sp, sp_fit_stride, T.tab, hord, hgstart, uniform, ahat, bhat,
                                                  fexp, hist, dflags);
@@ -1567,12 +1566,11 @@ void rmx_launch_viterbi(cudaStream_t st, const RmxTables& T, const RmxDims& d, i
     const int groups = (gn + fr - 1) / fr;
     if (fpc > groups) fpc = groups;
     size_t smem = sizeof(double) * ((size_t)fpc * fr * 2 * SP + (size_t)staged * d.S * SP) + (size_t)d.S * d.M + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static RmxPerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaFuncSetAttribute(k_viterbi<1, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
         cudaFuncSetAttribute(k_viterbi<1, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
         cudaFuncSetAttribute(k_viterbi<2, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
-        attr_set = true;
     }
     const dim3 grid(ch.NB, (groups + fpc - 1) / fpc);
 #define VIT_ARGS d, g0, gn, ch, rows, sp, sp_fit_stride, T.tab, F, lattice, path, staged, fpc

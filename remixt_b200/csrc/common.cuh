@@ -73,6 +73,20 @@ struct RmxFast {
     double* segf;             // (G)(N,12)  per-(fit, segment) inputs of the fast path (k_segfast)
 };
 
+// The opt-in to more than 48 KB of dynamic shared memory is a per-DEVICE attribute of a kernel: a flag per process
+// would leave a second device of the same process without it (models take `device=`).  One bit per device ordinal.
+struct RmxPerDeviceOnce {
+    unsigned long long done = 0;
+    bool need() {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const unsigned long long bit = 1ull << (dev & 63);
+        if (done & bit) return false;
+        done |= bit;
+        return true;
+    }
+};
+
 // ---------------------------------------------------------------------------------------------
 // warp / block helpers
 // ---------------------------------------------------------------------------------------------

@@ -1124,10 +1124,9 @@ void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, cons
     int64_t cap = ((int64_t)sm_count * 12 + gn - 1) / gn;   // whole grid sized in multiples of the SM count
     if (cap < 1) cap = 1;
     int grid = (int)(want < cap ? want : cap);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static RmxPerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaFuncSetAttribute(k_lltable2, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
-        attr_set = true;
     }
     k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags);
 }

@@ -1,0 +1,190 @@
+"""Entry points of the C-ABI that had no caller under tests/ (VERDICT r1): the nine per-(n, s) scalar accessors
+(rmx_eval), calculate_log_transmat, update_framelogprob, get_model_data, chains longer than the row-descriptor cache,
+a second kernel path on the same inputs, and the reference's OWN cn_model.py driving this package's RemixtModel."""
+import os
+import subprocess
+import sys
+import warnings
+
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(ref_bpmodel, name='small', init=3, rounds=1, **kw):
+    exp = util.load_experiment(name)
+    ip = util.init_params(name, init)
+    cu = util.make_driver(exp, ip, **kw).model
+    rf = util.make_driver(exp, ip, model_class=ref_bpmodel.RemixtModel, **kw).model
+    for m in (cu, rf):
+        m.h = np.array([0.031, 0.022, 0.017])
+        for _ in range(rounds):
+            for step in util.STEPS:
+                getattr(m, step)()
+    return cu, rf
+
+
+@pytest.mark.parametrize('normal_contamination', [True, False])
+def test_scalar_accessors_equal_reference(ref_bpmodel, normal_contamination):
+    """calculate_expected_total_reads / _allele_ratio / log_prior_cn / log_likelihood_total / _allele and their
+    partial_h forms (bpmodel.pyx:686-896) for a spread of (n, s, u, v, w)."""
+    cu, rf = _pair(ref_bpmodel, normal_contamination=normal_contamination)
+    N, S, M = cu.num_segments, cu.num_cn_states, cu.num_clones
+    rng = np.random.RandomState(1)
+    tm, am = np.asarray(cu.total_likelihood_mask), np.asarray(cu.allele_likelihood_mask)
+    segs = list(rng.choice(np.flatnonzero(tm & am), 6, replace=False)) + list(np.flatnonzero(tm == 0)[:2])
+    checked = 0
+    for n in segs:
+        for s in [0, 1] + list(rng.choice(S, 5, replace=False)):
+            n, s = int(n), int(s)
+            util.assert_close(cu.calculate_expected_total_reads(n, s), rf.calculate_expected_total_reads(n, s), rtol=1e-14)
+            util.assert_close(cu.calculate_log_prior_cn(n, s), rf.calculate_log_prior_cn(n, s), rtol=1e-14)
+            a, b = np.zeros(M), np.zeros(M)
+            cu.calculate_expected_total_reads_partial_h(n, s, a)
+            rf.calculate_expected_total_reads_partial_h(n, s, b)
+            util.assert_close(a, b, rtol=1e-14)
+            try:
+                want = rf.calculate_expected_allele_ratio(n, s)
+            except ValueError:          # total depth 0 (homozygous deletion without normal contamination)
+                with pytest.raises(ValueError):
+                    cu.calculate_expected_allele_ratio(n, s)
+                continue
+            util.assert_close(cu.calculate_expected_allele_ratio(n, s), want, rtol=1e-14)
+            cu.calculate_expected_allele_ratio_partial_h(n, s, a)
+            rf.calculate_expected_allele_ratio_partial_h(n, s, b)
+            util.assert_close(a, b, rtol=1e-12, atol=1e-12)     # (a0 td - md tot) / td^2 cancels to ~1e-15 for balanced states
+            for u in (0, 1):
+                util.assert_close(cu.calculate_log_likelihood_total(n, s, u), rf.calculate_log_likelihood_total(n, s, u),
+                                  rtol=1e-10, atol=1e-9)
+                cu.calculate_log_likelihood_total_partial_h(n, s, u, a)
+                rf.calculate_log_likelihood_total_partial_h(n, s, u, b)
+                util.assert_close(a, b, rtol=1e-10, atol=1e-9)
+            for v in (0, 1):
+                for w in (0, 1):
+                    try:
+                        want = rf.calculate_log_likelihood_allele(n, s, v, w)
+                    except ValueError:
+                        with pytest.raises(ValueError):
+                            cu.calculate_log_likelihood_allele(n, s, v, w)
+                        continue
+                    util.assert_close(cu.calculate_log_likelihood_allele(n, s, v, w), want, rtol=1e-10, atol=1e-9)
+                    try:
+                        rf.calculate_log_likelihood_allele_partial_h(n, s, v, w, b)
+                    except ValueError:
+                        continue
+                    cu.calculate_log_likelihood_allele_partial_h(n, s, v, w, a)
+                    util.assert_close(a, b, rtol=1e-9, atol=1e-8)
+            checked += 1
+    assert checked >= 30
+
+
+def test_calculate_log_transmat_and_update_framelogprob(ref_bpmodel):
+    cu, rf = _pair(ref_bpmodel, rounds=2)
+    shape = (cu.num_segments - 1, cu.num_cn_states, cu.num_cn_states)
+    a, b = np.zeros(shape), np.zeros(shape)
+    cu.p_breakpoint = np.asarray(rf.p_breakpoint).copy()        # the same inputs: the two differ by ~1e-12 after two rounds
+    cu.calculate_log_transmat(a)
+    rf.calculate_log_transmat(b)
+    util.assert_close(a, b, rtol=1e-12, atol=1e-12, what='log_transmat')
+    # with the other transition model too
+    cu.transition_model = 1
+    rf.transition_model = 1
+    cu.calculate_log_transmat(a)
+    rf.calculate_log_transmat(b)
+    util.assert_close(a, b, rtol=1e-12, atol=1e-12, what='log_transmat tm=1')
+    cu.transition_model = 0
+    rf.transition_model = 0
+    # update_framelogprob on its own, after the q-factors moved
+    q = np.asarray(rf.p_outlier_total).copy()
+    q[:, 0], q[:, 1] = 0.7, 0.3
+    cu.p_outlier_total = q
+    rf.p_outlier_total = q
+    cu.update_framelogprob()
+    rf.update_framelogprob()
+    util.assert_close(cu.framelogprob, np.asarray(rf.framelogprob), rtol=1e-9, atol=1e-9, what='framelogprob')
+
+
+def test_get_model_data_on_a_fresh_model():
+    exp = util.load_experiment('small')
+    bm = util.make_driver(exp, util.init_params('small', 0))
+    data = bm.get_model_data()
+    assert data['num_segments'] == bm.model.num_segments and data['h'].shape == (3,)
+    assert 'log_transmat' not in data and 'posterior_marginals' not in data
+    assert data['p_breakpoint'].shape == (bm.model.num_breakpoints, bm.model.num_brk_states)
+    big = bm.get_model_data(large=True)
+    assert big['posterior_marginals'].shape == (bm.model.num_segments, bm.model.num_cn_states)
+
+
+_PATH_SCRIPT = r'''
+import sys, numpy as np
+sys.path.insert(0, %(root)r)
+from remixt_b200 import pipeline, simulate
+exp = simulate.simulate_experiment(dict(N=9000, chromosome_lengths={'1': 249250621}, num_ancestral_events=40,
+                                        num_descendent_events=15, num_false_breakpoints=10, random_seed=11))
+cfg = {'max_copy_number': 6, 'max_ploidy': 5.0}
+grid = pipeline.init(exp, cfg)
+bm = pipeline.build_model(exp, grid[0], cfg)
+bm.prepare(pipeline.init_h(grid[0]))
+assert bm.N1 > 8192 and int(bm.is_telomere.sum()) == 1
+bm.model.variational_update(2)
+cn = np.zeros((bm.model.num_segments, 3, 2), dtype=np.int64)
+bm.model.infer_cn(cn)
+np.savez(sys.argv[1], elbo=bm.model.calculate_elbo(), post=bm.model.posterior_marginals, pb=bm.model.p_breakpoint, cn=cn)
+'''
+
+
+def test_long_chain_same_result_on_every_kernel_path(tmp_path):
+    """One chromosome of 9000+ model segments (longer than the chain kernels' shared-memory row-descriptor cache,
+    8192 rows) with breakends: the second-generation DMMA kernel, the first-generation one and the L2-streamed kernel
+    agree (three independent implementations of the same messages; the environment switches are read once per
+    process, hence subprocesses)."""
+    outs = {}
+    for tag, env in (('v2', {}), ('v1', {'RMX_CHAIN_V1': '1'}), ('streamed', {'RMX_CHAIN_STREAMED': '1'})):
+        path = str(tmp_path / (tag + '.npz'))
+        e = dict(os.environ)
+        e.update(env)
+        subprocess.check_call([sys.executable, '-c', _PATH_SCRIPT % dict(root=util.ROOT), path], env=e)
+        outs[tag] = np.load(path)
+    for tag in ('v1', 'streamed'):
+        util.assert_close(outs['v2']['elbo'], outs[tag]['elbo'], rtol=1e-10, what='elbo ' + tag)
+        util.assert_close(outs['v2']['post'], outs[tag]['post'], rtol=1e-7, atol=1e-12, what='post ' + tag)
+        util.assert_close(outs['v2']['pb'], outs[tag]['pb'], rtol=1e-7, atol=1e-12, what='p_breakpoint ' + tag)
+        assert np.array_equal(outs['v2']['cn'], outs[tag]['cn'])
+
+
+def test_reference_cn_model_drives_this_bpmodel():
+    """the reference's UNMODIFIED cn_model.py / analysis/pipeline.py with
+    remixt.bpmodel aliased to remixt_b200.bpmodel -- a complete reference pipeline.fit on the GPU, against the
+    reference's own result for the same initialisation (golden grid)."""
+    from oracle import refenv
+    if not refenv.available():
+        pytest.skip('reference modules not staged')
+    import remixt_b200
+    from remixt_b200 import bpmodel
+    refenv.uninstall()
+    refenv.install(bpmodel=bpmodel)
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            import remixt.analysis.pipeline as rp
+            import remixt.cn_model as rcn
+        assert rcn.remixt.bpmodel is bpmodel
+        from oracle import make_golden
+        g = util.golden('grid_small.npz')
+        _, exp = make_golden.load_experiment('small')
+        init_id = int(g['best_init_id'])
+        k = list(g['init_ids']).index(init_id)
+        np.random.seed(int(g['seed']))
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            res = rp.fit(exp, util.init_params('small', init_id), {'max_copy_number': 6, 'num_em_iter': 5, 'num_update_iter': 5})
+        assert np.array_equal(res['cn'], g['cn'][k])
+        assert np.array_equal(np.array([res['brk_cn'][str(b)] for b in g['brk_ids']]), g['brk_cn'][k])
+        util.assert_close(res['stats']['elbo'], g['elbo'][k], rtol=1e-6, what='elbo')
+        util.assert_close(res['h'], g['h'][k], rtol=1e-5, what='h')
+    finally:
+        refenv.uninstall()
