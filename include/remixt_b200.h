@@ -175,6 +175,21 @@ int rmx_variational_update(rmx_handle h, int n_iter);
 int rmx_breakpoint_logq(rmx_handle h, double* logq);
 int rmx_breakpoint_apply_logq(rmx_handle h, const double* logq);
 
+/* ---- chromosome-sharded fits over several GPUs ---------------------------------------------
+ * A model created with RMX_DESC_SHARD on every rank (its own chromosomes, all K breakpoints) plus an NCCL communicator
+ * attached to it behaves as ONE model: the (K,B) log q of update_p_breakpoint (bpmodel.pyx:971-980) is summed over the
+ * ranks with ncclAllReduce ON THE MODEL'S STREAM between the shard's partial sums and the normalisation, so
+ * rmx_update / rmx_variational_update run their rounds without a host round trip; hmm_log_norm_const, the ELBO terms,
+ * calculate_expected_log_likelihood[_partial_h] and rmx_mstep_evaluate return the totals over all shards (the entropy
+ * of p_breakpoint, identical on every rank, is counted once).  Every rank must make the same calls in the same order.
+ * NCCL is loaded at run time (dlopen of `nccl_library`, or of libnccl.so.2 as the process already has it when NULL):
+ * the library itself does not link against it.  rmx_comm_unique_id fills the 128-byte ncclUniqueId that rank 0
+ * hands to the others (by any means; the host mirror broadcasts it over torch.distributed). */
+int rmx_comm_load(const char* nccl_library);
+int rmx_comm_unique_id(void* unique_id_128);
+int rmx_comm_init(rmx_handle h, const void* unique_id_128, int rank, int nranks);
+int rmx_comm_destroy(rmx_handle h);
+
 /* ---- objective / M-step reductions ---------------------------------------------------- */
 int rmx_variational_energy(rmx_handle h, double* energy);    /* bpmodel.pyx:1060 */
 int rmx_variational_entropy(rmx_handle h, double* entropy);  /* bpmodel.pyx:1044 */

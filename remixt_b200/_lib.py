@@ -38,6 +38,7 @@ EXPORTS = [
     'rmx_device_count',
     'rmx_set_array', 'rmx_get_array', 'rmx_set_scalar', 'rmx_get_scalar', 'rmx_get_derived',
     'rmx_update', 'rmx_variational_update', 'rmx_breakpoint_logq', 'rmx_breakpoint_apply_logq',
+    'rmx_comm_load', 'rmx_comm_unique_id', 'rmx_comm_init', 'rmx_comm_destroy',
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
     'rmx_expected_log_likelihood', 'rmx_expected_log_likelihood_partial_h',
     'rmx_expected_log_likelihood_grid',
@@ -78,6 +79,10 @@ def _load():
         'rmx_breakpoint_logq': [H, P],
         'rmx_breakpoint_apply_logq': [H, P],
         'rmx_release_cached_memory': [I],
+        'rmx_comm_load': [C.c_char_p],
+        'rmx_comm_unique_id': [P],
+        'rmx_comm_init': [H, P, I, I],
+        'rmx_comm_destroy': [H],
         'rmx_device_count': [C.POINTER(I)],
         'rmx_set_array': [H, I, P, I64],
         'rmx_get_array': [H, I, P, I64],

@@ -424,6 +424,18 @@ class _ModelBase(object):
     def state_sequence(self):
         return self._get(_lib.A_STATE_PATH, (self.num_segments,), np.int64)
 
+    # ------------------------------------------------------------------ multi-GPU shards (remixt_b200/sharded.py)
+    def comm_init(self, unique_id, rank, nranks):
+        """Attaches an NCCL communicator to this shard (``rmx_comm_init``): from here on ``update_p_breakpoint``,
+        ``hmm_log_norm_const``, the ELBO and the M-step objectives are those of the whole fit, reduced in stream."""
+        buf = np.frombuffer(bytes(unique_id), dtype=np.uint8).copy()
+        if buf.size != 128:
+            raise ValueError('unique_id must be the 128 bytes of nccl_unique_id()')
+        check(lib.rmx_comm_init(self._handle, _ptr(buf), int(rank), int(nranks)), self._handle)
+
+    def comm_destroy(self):
+        check(lib.rmx_comm_destroy(self._handle), self._handle)
+
     # update_p_breakpoint split around its reduction (chromosome-sharded fits, remixt_b200/sharded.py)
     def breakpoint_logq(self):
         """(K, B) partial ``log q`` of ``update_p_breakpoint`` (``bpmodel.pyx:971-980``) over this model's own
@@ -579,6 +591,17 @@ class RemixtBatch(_ModelBase):
 
     def __getitem__(self, g):
         return self.fit(g)
+
+
+def nccl_unique_id(nccl_library=None):
+    """128 bytes identifying a new NCCL communicator (``rmx_comm_unique_id``); rank 0 makes it and hands it to the
+    other ranks.  ``nccl_library``: path of ``libnccl.so.2`` when the process has not loaded it yet (a process that
+    imported torch has)."""
+    if nccl_library is not None:
+        check(lib.rmx_comm_load(str(nccl_library).encode()), None)
+    buf = np.zeros(128, dtype=np.uint8)
+    check(lib.rmx_comm_unique_id(_ptr(buf)), None)
+    return buf.tobytes()
 
 
 def _scalar_property(name):

@@ -30,6 +30,39 @@
 
 static thread_local std::string g_create_error;
 
+// ---- NCCL, bound at run time (no link-time dependency): the five entry points the sharded fits need
+#include <dlfcn.h>
+typedef struct ncclComm* rmx_ncclComm_t;
+struct rmx_ncclUniqueId { char internal[128]; };
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(rmx_ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(rmx_ncclComm_t*, int, rmx_ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(rmx_ncclComm_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, rmx_ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    std::string error;
+    bool load(const char* path) {
+        if (lib) return true;
+        const char* names[] = {path, "libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) {
+            if (!nm) continue;
+            lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (lib) break;
+        }
+        if (!lib) { error = std::string("cannot load NCCL: ") + (dlerror() ? dlerror() : "?"); return false; }
+        GetUniqueId = (decltype(GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+        CommInitRank = (decltype(CommInitRank))dlsym(lib, "ncclCommInitRank");
+        CommDestroy = (decltype(CommDestroy))dlsym(lib, "ncclCommDestroy");
+        AllReduce = (decltype(AllReduce))dlsym(lib, "ncclAllReduce");
+        GetErrorString = (decltype(GetErrorString))dlsym(lib, "ncclGetErrorString");
+        if (!GetUniqueId || !CommInitRank || !CommDestroy || !AllReduce) { error = "NCCL symbols missing"; lib = nullptr; return false; }
+        return true;
+    }
+};
+static NcclApi g_nccl;
+static const int RMX_NCCL_DOUBLE = 8, RMX_NCCL_SUM = 0;      // ncclFloat64, ncclSum (nccl.h)
+
 // Device-memory pool.  A fit of one sample is followed by the fit of the next with the same shapes (init grids,
 // restarts, batches of genomes), and cudaMalloc / cudaFree of a 12 GB working set costs more than the E-step it
 // serves.  Freed blocks are kept per (device, size) and handed back to the next batch; rmx_release_cached_memory
@@ -151,6 +184,9 @@ struct Batch {
     double* stab = nullptr;
     double* segf = nullptr;
     double* logq = nullptr;      // (G,K,B) log q of update_p_breakpoint before normalisation (sharded fits)
+    rmx_ncclComm_t comm = nullptr;   // sharded fit over several GPUs: in-stream reductions (rmx_comm_init)
+    int comm_rank = 0, comm_size = 1;
+    bool is_shard = false;
     uint8_t* bc_tab = nullptr;   // states grouped by tumour-clone totals: [perm (4 KBB)][kbcls (KBB)][scls (S)][didx (BC,BC)][ddel (ND,M)]
     int BC = 0, KBB = 0, ND = 0;
     uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
@@ -216,6 +252,7 @@ struct Batch {
     ~Batch() {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);
+        if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
         for (auto& t : tev) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
         for (auto& p : allocs) g_pool.put(device, p.second, p.first);
         if (hp) g_pinned.put(hp_bytes, hp);
@@ -456,6 +493,33 @@ static int sync_check(Model* m) {
     return RMX_OK;
 }
 
+// sharded fit: the reduction outputs red_out[g][0..RED) of the handle's fits summed over the ranks, in stream.
+// Every caller has just produced the slots it will read; slots it does not read may hold anything.
+static int shard_allreduce(Model* m, double* buf, size_t count) {
+    Batch* b = m->b.get();
+    if (!b->comm) return RMX_OK;
+    const int r = g_nccl.AllReduce(buf, buf, count, RMX_NCCL_DOUBLE, RMX_NCCL_SUM, b->comm, b->stream);
+    if (r != 0) return m->fail(RMX_ERR_CUDA, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error"));
+    return RMX_OK;
+}
+static int shard_reduce_red(Model* m, int slot0, int nslots) {
+    Batch* b = m->b.get();
+    if (!b->comm) return RMX_OK;
+    for (int g = m->g0; g < m->g0 + m->gn; ++g) {
+        int rc = shard_allreduce(m, b->red_out + (size_t)g * Batch::RED + slot0, (size_t)nslots);
+        if (rc) return rc;
+    }
+    return RMX_OK;
+}
+// sharded fit: a shard without rows in a sample still takes part in the reduction, with zeros
+static int shard_zero_red(Model* m, int slot0, int nslots) {
+    Batch* b = m->b.get();
+    if (!b->comm) return RMX_OK;
+    for (int g = m->g0; g < m->g0 + m->gn; ++g)
+        CK(cudaMemsetAsync(b->red_out + (size_t)g * Batch::RED + slot0, 0, sizeof(double) * nslots, b->stream));
+    return RMX_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // coordinate updates over the handle's fits (launch only; callers synchronise)
 // ---------------------------------------------------------------------------------------------
@@ -520,6 +584,10 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
         b->path_valid[g] = 0;
         b->asum_valid[g] = 0;
     }
+    {
+        int rc2 = shard_reduce_red(m, 15, 1);      // hmm_log_norm_const = the chains of every shard
+        if (rc2) return rc2;
+    }
     CK(cudaMemcpyAsync(b->hp + (size_t)g0 * Batch::RED, b->red_out + (size_t)g0 * Batch::RED,
                        sizeof(double) * Batch::RED * gn, cudaMemcpyDeviceToHost, b->stream));
     return RMX_OK;
@@ -530,6 +598,16 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
 static int do_update_p_breakpoint(Model* m, int mode = 0) {
     Batch* b = m->b.get();
     const int g0 = m->g0, gn = m->gn;
+    if (mode == 0 && b->comm && b->is_shard && b->d.K > 0) {
+        // this shard's partial sums, the sum over the ranks on the stream, the same normalisation everywhere
+        const size_t kb = (size_t)b->d.K * b->d.B;
+        CK(cudaMemsetAsync(b->logq + (size_t)g0 * kb, 0, sizeof(double) * kb * gn, b->stream));
+        int rc = do_update_p_breakpoint(m, 1);
+        if (rc) return rc;
+        rc = shard_allreduce(m, b->logq + (size_t)g0 * kb, kb * gn);
+        if (rc) return rc;
+        return do_update_p_breakpoint(m, 2);
+    }
     if (mode != 2 && b->d.K > 0 && b->R > 0) {
         // fits still in the constructor state take the histogram of the uniform joint (bpmodel.pyx:566-567)
         std::vector<char> need(b->G, 0);
@@ -756,6 +834,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
         if (desc->breakpoint_idx[n] > max_bidx) max_bidx = desc->breakpoint_idx[n];
     }
     // a shard of a chromosome-sharded fit holds the breakends of its own chromosomes only (RMX_DESC_SHARD)
+    b->is_shard = (desc->flags & RMX_DESC_SHARD) != 0;
     if ((desc->flags & RMX_DESC_SHARD) ? (max_bidx + 1 > K) : (max_bidx + 1 != K))
         CREATE_FAIL(RMX_ERR_VALUE, "breakpoint_idx must have maximum of num_breakpoints positive indices");
     std::map<uint32_t, int> class_of;
@@ -1480,6 +1559,52 @@ int rmx_breakpoint_apply_logq(rmx_handle m, const double* logq) {
     return sync_check(m);
 }
 
+// ---- communicator of a chromosome-sharded fit
+int rmx_comm_load(const char* nccl_library) {
+    if (!g_nccl.load(nccl_library)) { g_create_error = g_nccl.error; return RMX_ERR_CUDA; }
+    return RMX_OK;
+}
+int rmx_comm_unique_id(void* unique_id_128) {
+    if (!unique_id_128) return RMX_ERR_ARG;
+    if (!g_nccl.load(nullptr)) { g_create_error = g_nccl.error; return RMX_ERR_CUDA; }
+    rmx_ncclUniqueId id;
+    const int r = g_nccl.GetUniqueId(&id);
+    if (r != 0) { g_create_error = "ncclGetUniqueId failed"; return RMX_ERR_CUDA; }
+    memcpy(unique_id_128, &id, sizeof id);
+    return RMX_OK;
+}
+int rmx_comm_init(rmx_handle m, const void* unique_id_128, int rank, int nranks) {
+    if (!m || !unique_id_128 || nranks < 1 || rank < 0 || rank >= nranks) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    if (!g_nccl.load(nullptr)) return m->fail(RMX_ERR_CUDA, g_nccl.error);
+    if (b->comm) return m->fail(RMX_ERR_ARG, "a communicator is already attached to this model");
+    if (!b->is_shard) return m->fail(RMX_ERR_ARG, "rmx_comm_init needs a model created with RMX_DESC_SHARD");
+    rmx_ncclUniqueId id;
+    memcpy(&id, unique_id_128, sizeof id);
+    const int r = g_nccl.CommInitRank(&b->comm, nranks, id, rank);
+    if (r != 0) {
+        b->comm = nullptr;
+        return m->fail(RMX_ERR_CUDA, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error"));
+    }
+    b->comm_rank = rank;
+    b->comm_size = nranks;
+    return RMX_OK;
+}
+int rmx_comm_destroy(rmx_handle m) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    Lock lk(b->mu);
+    cudaSetDevice(b->device);
+    if (b->comm) {
+        cudaStreamSynchronize(b->stream);
+        g_nccl.CommDestroy(b->comm);
+        b->comm = nullptr;
+    }
+    return RMX_OK;
+}
+
 int rmx_variational_update(rmx_handle m, int n_iter) {
     if (!m) return RMX_ERR_ARG;
     Batch* b = m->b.get();
@@ -1600,6 +1725,13 @@ static int elbo_terms(Model* m, bool full) {
         });
         if (rc) return rc;
     }
+    if (b->comm) {
+        // the entropy of p_breakpoint is the one term every shard holds in full: counted on rank 0 only
+        if (b->comm_rank != 0)
+            for (int g = g0; g < g0 + gn; ++g) CK(cudaMemsetAsync(b->red_out + (size_t)g * RED + 7, 0, sizeof(double), b->stream));
+        rc = shard_reduce_red(m, 0, 10);
+        if (rc) return rc;
+    }
     CK(cudaMemcpyAsync(b->hp + (size_t)g0 * RED, b->red_out + (size_t)g0 * RED, sizeof(double) * RED * gn,
                        cudaMemcpyDeviceToHost, b->stream));
     return sync_check(m);
@@ -1678,6 +1810,10 @@ static int launch_ell(Model* m, const int* rows, int Rmax, int slot) {
 
 static int fetch_red(Model* m) {
     Batch* b = m->b.get();
+    {
+        int rc = shard_reduce_red(m, 12, Batch::RED - 12);      // constants, E[LL] values, gradient
+        if (rc) return rc;
+    }
     CK(cudaMemcpyAsync(b->hp + (size_t)m->g0 * Batch::RED, b->red_out + (size_t)m->g0 * Batch::RED,
                        sizeof(double) * Batch::RED * m->gn, cudaMemcpyDeviceToHost, b->stream));
     return sync_check(m);
@@ -1693,13 +1829,17 @@ int rmx_expected_log_likelihood(rmx_handle m, const int64_t* sample, double* out
     int rc = stage_rows(m, sample, &Rmax, &rows);
     if (rc) return rc;
     for (int g = 0; g < m->gn; ++g) out[g] = 0.;
-    if (Rmax == 0) return RMX_OK;
-    rc = launch_ell(m, rows, Rmax, 16);
+    if (Rmax == 0 && !b->comm) return RMX_OK;
+    rc = shard_zero_red(m, 16, 1);
     if (rc) return rc;
+    if (Rmax > 0) {
+        rc = launch_ell(m, rows, Rmax, 16);
+        if (rc) return rc;
+    }
     rc = fetch_red(m);
     if (rc) return rc;
     for (int g = 0; g < m->gn; ++g)
-        out[g] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 16] : 0.;
+        out[g] = (b->hRn[m->g0 + g] > 0 || b->comm) ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 16] : 0.;
     return RMX_OK;
 }
 
@@ -1749,19 +1889,23 @@ int rmx_expected_log_likelihood_partial_h(rmx_handle m, const int64_t* sample, d
     int rc = stage_rows(m, sample, &Rmax, &rows);
     if (rc) return rc;
     for (int e = 0; e < m->gn * M; ++e) out[e] = 0.;
-    if (Rmax == 0) return RMX_OK;
+    if (Rmax == 0 && !b->comm) return RMX_OK;
     rc = push_params(m);
     if (rc) return rc;
-    const int nb = rmx_ell_blocks(b->d, Rmax);
-    rmx_launch_ell_grad(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, rows, b->d_Rn, Rmax, b->post, b->q_ot, b->q_oa,
-                        b->q_sw, b->part, b->part_stride, b->dflags);
-    rmx_launch_reduce_cols(b->stream, b->part, nb, RMX_MAXM, m->g0, m->gn, b->part_stride, b->red_out + 48, Batch::RED);
-    b->count(2);
+    rc = shard_zero_red(m, 48, RMX_MAXM);
+    if (rc) return rc;
+    if (Rmax > 0) {
+        const int nb = rmx_ell_blocks(b->d, Rmax);
+        rmx_launch_ell_grad(b->stream, tables(b), b->d, b->dP, m->g0, m->gn, rows, b->d_Rn, Rmax, b->post, b->q_ot, b->q_oa,
+                            b->q_sw, b->part, b->part_stride, b->dflags);
+        rmx_launch_reduce_cols(b->stream, b->part, nb, RMX_MAXM, m->g0, m->gn, b->part_stride, b->red_out + 48, Batch::RED);
+        b->count(2);
+    }
     rc = fetch_red(m);
     if (rc) return rc;
     for (int g = 0; g < m->gn; ++g)
         for (int k = 0; k < M; ++k)
-            out[(size_t)g * M + k] = b->hRn[m->g0 + g] > 0 ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 48 + k] : 0.;
+            out[(size_t)g * M + k] = (b->hRn[m->g0 + g] > 0 || b->comm) ? b->hp[(size_t)(m->g0 + g) * Batch::RED + 48 + k] : 0.;
     return RMX_OK;
 }
 
@@ -1880,13 +2024,20 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     if (grad) for (int e = 0; e < G * M; ++e) grad[e] = 0.;
     const int Rmax = b->ms_rmax;
     const int* rows = b->ms_all ? nullptr : b->ms_rows;
-    const bool work = any && Rmax > 0;
-    if (work)   // pageable-style small copy from the pinned block: staged before the call returns to the stream order
+    // a shard of a multi-GPU fit takes part in every reduction, rows or not
+    const bool launch = any && Rmax > 0;
+    const bool work = launch || b->comm != nullptr;
+    if (b->comm) {
+        int rcz = shard_zero_red(m, 12, Batch::RED - 12);
+        if (rcz) return rcz;
+    }
+    if (launch)   // pageable-style small copy from the pinned block: staged before the call returns to the stream order
         CK(cudaMemcpyAsync(b->ms_Rn, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
     RmxTables T = tables(b);
-    const int nb = work ? rmx_ell_blocks(b->d, Rmax) : 0;
+    const int nb = launch ? rmx_ell_blocks(b->d, Rmax) : 0;
     bool fetch_const = false;
-    if (work && planes != 15 && !b->ms_const_valid) {
+    if (work && planes != 15 && !b->ms_const_valid) fetch_const = true;
+    if (launch && planes != 15 && !b->ms_const_valid) {
         // the terms the parameter does not enter, for EVERY fit with staged rows (fits join and leave the active set
         // from call to call), with the parameters as they stand
         int rc = push_params(m);
@@ -1896,7 +2047,6 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
                        b->part, b->part_stride, b->dflags, 15 ^ planes);
         rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 12, Batch::RED);
         b->count(3);
-        fetch_const = true;
     }
     for (int v = 0; v < n_values; ++v) {
         if (scalar_id >= 0) {
@@ -1907,7 +2057,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
                 }
             b->params_dirty = true;
         }
-        if (!work) continue;
+        if (!launch) continue;
         if (b->ms_all) {
             // every segment: the likelihood table of the fits whose parameters changed (the kernel of the E-step,
             // which the next E-step then finds ready), its posterior-weighted sums, and one value per segment
@@ -1941,7 +2091,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 16 + v, Batch::RED);
         b->count(3);
     }
-    if (work && grad) {
+    if (launch && grad) {
         rmx_launch_ell_grad(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->post, b->q_ot, b->q_oa, b->q_sw, b->part,
                             b->part_stride, b->dflags);
         rmx_launch_reduce_cols(b->stream, b->part, nb, RMX_MAXM, 0, G, b->part_stride, b->red_out + 48, Batch::RED);
@@ -1951,12 +2101,12 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     int rc = fetch_red(m);
     if (rc) return rc;
     if (fetch_const) {
-        for (int g = 0; g < G; ++g) b->ms_const[g] = b->ms_count[g] > 0 ? b->hp[(size_t)g * Batch::RED + 12] : 0.;
+        for (int g = 0; g < G; ++g) b->ms_const[g] = (b->ms_count[g] > 0 || b->comm) ? b->hp[(size_t)g * Batch::RED + 12] : 0.;
         b->ms_const_id = scalar_id;
         b->ms_const_valid = true;
     }
     for (int g = 0; g < G; ++g) {
-        if (b->hRn[g] <= 0) continue;
+        if (b->hRn[g] <= 0 && !(b->comm && (!active || active[g]))) continue;
         const double* r = b->hp + (size_t)g * Batch::RED;
         const double c0 = planes != 15 ? b->ms_const[g] : 0.;
         for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = r[16 + v] + c0;

@@ -20,8 +20,9 @@ The class keeps the reference's constructor signature and method names, so
 ``cn_model.BreakpointModel(..., model_class=ShardedRemixtModel, comm=...)`` drives it unchanged: every
 rank runs the same host code (same RNG stream, same M-step decisions) on its own shards.
 
-``comm`` moves the reductions: :class:`LocalComm` (one process; several shards on one GPU) or
-:class:`TorchDistComm` (``torch.distributed``: NCCL over NVLink between GPUs, gloo in the CPU tests).
+``comm`` moves the reductions: :class:`LocalComm` (one process; several shards on one GPU),
+:class:`TorchDistComm` (``torch.distributed``, operands staged by the host: gloo in the CPU tests) or
+:class:`NcclLibComm` (one shard per GPU, ``ncclAllReduce`` on the model's own stream inside the library).
 """
 import numpy as np
 
@@ -62,6 +63,21 @@ class TorchDistComm(object):
         out = [None] * self.size
         self._dist.all_gather_object(out, obj, group=self._group)
         return out
+
+
+class NcclLibComm(TorchDistComm):
+    """One shard per rank with the reductions INSIDE ``libremixt_b200.so`` (``rmx_comm_init``): the ``(K, B)``
+    ``log q`` allreduce of ``update_p_breakpoint`` and the scalar reductions run as ``ncclAllReduce`` on the model's
+    CUDA stream, so a round of the five updates (or ``variational_update(n)``, fused) needs no host round trip.
+    ``torch.distributed`` only carries the communicator's unique id and the occasional gather of whole-genome arrays
+    for the host driver."""
+    in_library = True
+
+    def attach(self, model):
+        from remixt_b200 import bpmodel
+        ids = [bpmodel.nccl_unique_id() if self.rank == 0 else None]
+        self._dist.broadcast_object_list(ids, src=0, group=self._group)
+        model.comm_init(ids[0], self.rank, self.size)
 
 
 def plan_shards(is_telomere, num_shards, breakpoint_idx=None):
@@ -149,6 +165,11 @@ class ShardedRemixtModel(object):
                 np.ascontiguousarray(self.is_telomere[a:b]), np.ascontiguousarray(self.breakpoint_idx[a:b]),
                 np.ascontiguousarray(self.breakpoint_orient[a:b]), transition_penalty, divergence_weight,
                 **local_kwargs))
+        d['in_library'] = bool(getattr(self.comm, 'in_library', False))
+        if self.in_library:
+            if len(self.shards) != 1 or num_shards != self.comm.size:
+                raise ValueError('in-library reductions need exactly one shard per rank')
+            self.comm.attach(self.shards[0])
 
     # ------------------------------------------------------------------ plumbing
     def _local(self):
@@ -166,6 +187,8 @@ class ShardedRemixtModel(object):
             return getattr(self.shards[0], name)
         if name in _SEGMENT_ARRAYS:
             return self._gather_segments([np.asarray(getattr(m, name)) for m in self.shards])
+        if name == 'hmm_log_norm_const' and self.__dict__.get('in_library'):
+            return float(self.shards[0].hmm_log_norm_const)
         if name == 'hmm_log_norm_const':
             return float(self.comm.allreduce_sum(np.array([sum(float(m.hmm_log_norm_const) for m in self.shards)]))[0])
         if name in ('l', 'x', 'y'):
@@ -198,6 +221,9 @@ class ShardedRemixtModel(object):
     def update_p_breakpoint(self):
         """``bpmodel.pyx:964-985``: partial sums per shard, one allreduce of ``(K, B)`` doubles, the same
         normalisation everywhere."""
+        if self.in_library:
+            self.shards[0].update_p_breakpoint()        # partial sums -> ncclAllReduce on the stream -> normalise
+            return
         partial = np.zeros((self.num_breakpoints, self.num_brk_states))
         for m in self.shards:
             partial += m.breakpoint_logq()
@@ -218,6 +244,9 @@ class ShardedRemixtModel(object):
             m.update_framelogprob()
 
     def variational_update(self, n_iter=1):
+        if self.in_library:
+            self.shards[0].variational_update(n_iter)   # the fused loop, collectives in stream
+            return
         for _ in range(int(n_iter)):
             self.update_p_allele_swap()
             self.update_p_cn()
@@ -227,6 +256,9 @@ class ShardedRemixtModel(object):
 
     # ------------------------------------------------------------------ objective
     def _energy_entropy(self):
+        if self.in_library:
+            m = self.shards[0]
+            return float(m.calculate_variational_energy()), float(m.calculate_variational_entropy())
         hb = _xlogx_sum(self.shards[0].p_breakpoint)     # the one global entropy term, identical on every shard
         loc = np.zeros(2)
         for m in self.shards:
@@ -247,6 +279,9 @@ class ShardedRemixtModel(object):
 
     def calculate_expected_log_likelihood(self, sample):
         sample = np.asarray(sample)
+        if self.in_library:
+            a, b = self.bounds[self.shard_ids[0]]
+            return float(self.shards[0].calculate_expected_log_likelihood(np.ascontiguousarray(sample[a:b])))
         loc = 0.
         for k, m in self._local():
             a, b = self.bounds[k]
@@ -255,6 +290,10 @@ class ShardedRemixtModel(object):
 
     def calculate_expected_log_likelihood_partial_h(self, sample, partial_h):
         sample = np.asarray(sample)
+        if self.in_library:
+            a, b = self.bounds[self.shard_ids[0]]
+            self.shards[0].calculate_expected_log_likelihood_partial_h(np.ascontiguousarray(sample[a:b]), partial_h)
+            return
         loc = np.zeros(self.num_clones)
         g = np.zeros(self.num_clones)
         for k, m in self._local():

@@ -62,3 +62,36 @@ def test_shard_flag_required():
     with pytest.raises(ValueError):
         bpmodel.RemixtModel(*sub)
     bpmodel.RemixtModel(*sub, shard=True)
+
+
+def test_in_library_nccl_single_rank_equals_unsharded():
+    """rmx_comm_init with one rank: every in-stream ncclAllReduce path of a shard (update_p_breakpoint, log
+    normaliser, ELBO terms with the p_breakpoint entropy counted once, M-step objective / gradient / batched
+    evaluation, empty samples) runs and returns what the plain model returns.  The multi-rank case is
+    scripts/sharded_nccl_check.py under torchrun (profiles/r02_sharded_nccl_*.log)."""
+    import torch  # noqa: F401  (brings libnccl.so.2 into the process)
+    from remixt_b200 import bpmodel
+    exp = util.load_experiment('small')
+    ip = util.init_params('small', 4)
+    plain = util.make_driver(exp, ip).model
+    shard = util.make_driver(exp, ip, model_kwargs=dict(shard=True)).model
+    shard.comm_init(bpmodel.nccl_unique_id(), 0, 1)
+    plain.variational_update(2)
+    shard.variational_update(2)
+    assert shard.calculate_elbo() == plain.calculate_elbo()
+    assert shard.hmm_log_norm_const == plain.hmm_log_norm_const
+    assert np.array_equal(shard.p_breakpoint, plain.p_breakpoint)
+    for step in util.STEPS:
+        getattr(plain, step)()
+        getattr(shard, step)()
+    assert shard.calculate_variational_entropy() == plain.calculate_variational_entropy()
+    sample = np.zeros(plain.num_segments, dtype=np.int64)
+    sample[::9] = 1
+    assert shard.calculate_expected_log_likelihood(sample) == plain.calculate_expected_log_likelihood(sample)
+    g1, g2 = np.zeros(3), np.zeros(3)
+    plain.calculate_expected_log_likelihood_partial_h(sample, g1)
+    shard.calculate_expected_log_likelihood_partial_h(sample, g2)
+    assert np.array_equal(g1, g2)
+    none = np.zeros(plain.num_segments, dtype=np.int64)
+    assert shard.calculate_expected_log_likelihood(none) == 0.
+    shard.comm_destroy()
