@@ -162,7 +162,7 @@ struct Batch {
     std::vector<RmxParams> P;
     std::vector<int> tm, tm_used, tm_cached;
     std::vector<double> logZ;
-    std::vector<char> ll_dirty, cn_updated, hist_valid, asum_valid, path_valid;
+    std::vector<char> ll_dirty, cn_updated, hist_valid, asum_dirty, path_valid;   // ll_dirty / asum_dirty: term-group bits
     bool params_dirty = true;
 
     // host copies of the small integer tables
@@ -183,6 +183,7 @@ struct Batch {
     double2* logw = nullptr;
     double* stab = nullptr;
     double* segf = nullptr;
+    double* segk = nullptr;      // (N,3) data-only part of the hoisted constants
     double* logq = nullptr;      // (G,K,B) log q of update_p_breakpoint before normalisation (sharded fits)
     rmx_ncclComm_t comm = nullptr;   // sharded fit over several GPUs: in-stream reductions (rmx_comm_init)
     int comm_rank = 0, comm_size = 1;
@@ -209,6 +210,10 @@ struct Batch {
     // batched M-step: the staged sample (row lists in ms_rows, per-fit counts on the host) and the per-call
     // effective counts (0 for inactive fits)
     int *ms_rows = nullptr, *ms_Rn = nullptr, *ms_Rn_all = nullptr;
+    double* ms_rowc = nullptr;      // (G, 256, 3) parameter-independent constants of the staged rows
+    double* ms_out = nullptr;       // (G, 33, chunks) partial sums of the one-launch sampled objective (slot 32: constants)
+    double* hms = nullptr;          // its pinned mirror
+    size_t hms_bytes = 0;
     // E[LL] of one dispersion parameter moves only the likelihood terms that parameter enters: the sum of the other
     // terms over the staged sample is computed once per (sample, parameter) and added on the host
     std::vector<double> ms_const;
@@ -259,6 +264,7 @@ struct Batch {
         if (hflags) g_pinned.put(sizeof(int), hflags);
         if (hrows) g_pinned.put(hrows_bytes, hrows);
         if (hRn) g_pinned.put(hRn_bytes, hRn);
+        if (hms) g_pinned.put(hms_bytes, hms);
         if (stream) cudaStreamDestroy(stream);
     }
     void count(int k = 1) {
@@ -344,6 +350,19 @@ static void for_runs(int g0, int gn, const std::vector<K>& key, const std::vecto
 // ---------------------------------------------------------------------------------------------
 // cached-quantity maintenance (all launch-only; callers synchronise)
 // ---------------------------------------------------------------------------------------------
+// likelihood term groups a parameter enters (bit u: total-read term u; bit 2 + v: the allele terms of v); 15 = all
+static int planes_of(int scalar_id) {
+    switch (scalar_id) {
+    case RMX_S_NEGBIN_R_0: case RMX_S_NEGBIN_HDEL_R_0: return 1;
+    case RMX_S_NEGBIN_R_1: case RMX_S_NEGBIN_HDEL_R_1: return 2;
+    case RMX_S_NEGBIN_HDEL_MU: return 3;
+    case RMX_S_BETABIN_M_0: case RMX_S_BETABIN_LOH_M_0: return 4;
+    case RMX_S_BETABIN_M_1: case RMX_S_BETABIN_LOH_M_1: return 8;
+    case RMX_S_BETABIN_LOH_P: return 12;
+    default: return 15;
+    }
+}
+
 static int push_params(Model* m) {
     Batch* b = m->b.get();
     if (!b->params_dirty) return RMX_OK;
@@ -408,21 +427,25 @@ static int ensure_ll(Model* m, int g0, int gn) {
     int rc = push_params(m);
     if (rc) return rc;
     RmxTables T = tables(b);
+    // ll_dirty[g] holds the term groups whose parameters changed (planes_of): a run of fits with the same groups is
+    // one launch that rebuilds those planes only (fast path; the general kernel rebuilds all)
     std::vector<int> key(b->G, 0);
+    for (int g = g0; g < g0 + gn; ++g) key[g] = b->fast_ll ? (int)b->ll_dirty[g] : (b->ll_dirty[g] ? 15 : 0);
     for_runs(g0, gn, key, &b->ll_dirty, [&](int g, int n) {
-        rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc);
+        const int pm = key[g];
+        rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc, b->segk, pm);
         cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE);
         if (b->fast_ll) {
             RmxFast Fp;
             Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag; Fp.segf = b->segf;
-            rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, Fp, b->LL, b->dflags);
+            rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, Fp, b->LL, b->dflags, pm);
             b->count(2);
         } else {
             rmx_launch_lltable(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, b->LL, b->dflags);
         }
         b->tend(te_);
         b->count(2);
-        for (int k = g; k < g + n; ++k) { b->ll_dirty[k] = 0; b->asum_valid[k] = 0; }
+        for (int k = g; k < g + n; ++k) { b->ll_dirty[k] = 0; b->asum_dirty[k] |= (char)pm; }
     });
     return RMX_OK;
 }
@@ -434,11 +457,11 @@ static int ensure_asum(Model* m, int g0, int gn) {
     if (rc) return rc;
     std::vector<int> key(b->G, 0);
     std::vector<char> need(b->G, 0);
-    for (int g = g0; g < g0 + gn; ++g) need[g] = !b->asum_valid[g];
+    for (int g = g0; g < g0 + gn; ++g) { need[g] = b->asum_dirty[g] != 0; key[g] = b->asum_dirty[g]; }
     for_runs(g0, gn, key, &need, [&](int g, int n) {
-        { cudaEvent_t te_ = b->tbegin(RMX_K_QSUMS); rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum); b->tend(te_); }
+        { cudaEvent_t te_ = b->tbegin(RMX_K_QSUMS); rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum, key[g]); b->tend(te_); }
         b->count();
-        for (int k = g; k < g + n; ++k) b->asum_valid[k] = 1;
+        for (int k = g; k < g + n; ++k) b->asum_dirty[k] = 0;
     });
     return RMX_OK;
 }
@@ -582,7 +605,7 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
         b->cn_updated[g] = 1;
         b->hist_valid[g] = 1;
         b->path_valid[g] = 0;
-        b->asum_valid[g] = 0;
+        b->asum_dirty[g] = 15;
     }
     {
         int rc2 = shard_reduce_red(m, 15, 1);      // hmm_log_norm_const = the chains of every shard
@@ -1012,10 +1035,10 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     b->tm_used.assign(G, 0);
     b->tm_cached.assign(G, 0);
     b->logZ.assign(G, 0.);
-    b->ll_dirty.assign(G, 1);
+    b->ll_dirty.assign(G, 15);
     b->cn_updated.assign(G, 0);
     b->hist_valid.assign(G, 0);
-    b->asum_valid.assign(G, 0);
+    b->asum_dirty.assign(G, 15);
     b->path_valid.assign(G, 0);
     b->h_tmask.assign((size_t)G * N, 1);
     b->h_amask.assign((size_t)G * N, 1);
@@ -1028,6 +1051,9 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(upload(b, &b->amask, std::vector<uint8_t>(GN, 1)));
     CCK(dalloc(b, &b->LL, GNS * RMX_NTERM));
     CCK(dalloc(b, &b->segc, GN * 12));
+    CCK(dalloc(b, &b->segk, (size_t)N * 3));
+    rmx_launch_segk(b->stream, tables(b), d, b->segk);
+    b->count();
     {
         // distinct normal-copy pairs (kinds) and the wide log table of the fast path (common.cuh)
         std::vector<uint8_t> nkind(N);
@@ -1100,6 +1126,10 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
     CCK(dalloc(b, &b->ms_rows, GN));
     CCK(dalloc(b, &b->ms_Rn, (size_t)G));
     CCK(dalloc(b, &b->ms_Rn_all, (size_t)G));
+    CCK(dalloc(b, &b->ms_rowc, (size_t)G * 256 * 3));
+    CCK(dalloc(b, &b->ms_out, (size_t)G * 33 * rmx_ell_sample_chunks()));
+    b->hms_bytes = (size_t)G * 33 * rmx_ell_sample_chunks() * sizeof(double);
+    CCK(g_pinned.get(b->hms_bytes, (void**)&b->hms));
     b->ms_count.assign(G, -1);
     b->ms_const.assign(G, 0.);
     CCK(dalloc(b, &b->dflags, 1));
@@ -1215,7 +1245,7 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
         const double* s = (const double*)src;
         for (int g = 0; g < gn; ++g) {
             for (int k = 0; k < b->d.M; ++k) b->P[g0 + g].h[k] = s[(size_t)g * b->d.M + k];
-            b->ll_dirty[g0 + g] = 1;
+            b->ll_dirty[g0 + g] = 15;
         }
         b->params_dirty = true;
         b->ms_const_valid = false;
@@ -1227,7 +1257,7 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
     case RMX_A_P_OUTLIER_ALLELE: dst = b->q_oa; break;
     case RMX_A_POSTERIOR_MARGINALS:
         dst = b->post;
-        for (int g = g0; g < g0 + gn; ++g) b->asum_valid[g] = 0;
+        for (int g = g0; g < g0 + gn; ++g) b->asum_dirty[g] = 15;
         break;
     case RMX_A_FRAMELOGPROB: dst = b->F; break;
     case RMX_A_TOTAL_LIKELIHOOD_MASK:
@@ -1248,7 +1278,7 @@ int rmx_set_array(rmx_handle m, int id, const void* src, int64_t count) {
         CK(cudaMemcpyAsync((id == RMX_A_TOTAL_LIKELIHOOD_MASK ? b->tmask : b->amask) + off, v.data(), n,
                            cudaMemcpyHostToDevice, b->stream));
         CK(cudaStreamSynchronize(b->stream));
-        for (int g = g0; g < g0 + gn; ++g) b->ll_dirty[g] = 1;
+        for (int g = g0; g < g0 + gn; ++g) b->ll_dirty[g] = 15;
         return RMX_OK;
     }
     default: return m->fail(RMX_ERR_ARG, "this attribute cannot be assigned");
@@ -1453,7 +1483,7 @@ int rmx_set_scalar(rmx_handle m, int id, double v) {
     if (!scalar_slot(b->P[g0], id)) return m->fail(RMX_ERR_ARG, "unknown scalar id");
     for (int g = g0; g < g0 + gn; ++g) {
         *scalar_slot(b->P[g], id) = v;
-        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[g] = 1;
+        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[g] |= (char)planes_of(id);
     }
     b->params_dirty = true;
     b->ms_const_valid = false;
@@ -1642,7 +1672,7 @@ int rmx_variational_update(rmx_handle m, int n_iter) {
                              b->fexp, b->mF, b->dflags);
             b->tend(te_);
             b->count();
-            for (int g = m->g0; g < m->g0 + m->gn; ++g) b->asum_valid[g] = 1;
+            for (int g = m->g0; g < m->g0 + m->gn; ++g) b->asum_dirty[g] = 0;
         }
     } else {
         for (int it = 0; it < n_iter; ++it)
@@ -1861,7 +1891,7 @@ int rmx_expected_log_likelihood_grid(rmx_handle m, const int64_t* sample, int sc
     for (int v = 0; v < n_values; ++v) {
         for (int g = 0; g < m->gn; ++g) {
             *scalar_slot(b->P[m->g0 + g], scalar_id) = values[(size_t)g * n_values + v];
-            b->ll_dirty[m->g0 + g] = 1;
+            b->ll_dirty[m->g0 + g] |= (char)planes_of(scalar_id);
         }
         b->params_dirty = true;
         if (Rmax == 0) continue;
@@ -1945,6 +1975,10 @@ int rmx_mstep_stage_sample(rmx_handle m, const int64_t* sample) {
                                cudaMemcpyHostToDevice, b->stream));
     for (int g = 0; g < gn; ++g) b->hRn[g] = b->ms_count[g];
     CK(cudaMemcpyAsync(b->ms_Rn_all, b->hRn, (size_t)gn * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    if (rmx_ell_sample_ok(rmax)) {      // the parameter-independent constants of these rows, once
+        rmx_launch_ell_rowcache(b->stream, tables(b), b->d, 0, gn, b->ms_rows, b->ms_Rn_all, rmax, b->ms_rowc);
+        b->count();
+    }
     CK(cudaStreamSynchronize(b->stream));   // hrows is reused by the next staging / decode
     return RMX_OK;
 }
@@ -1978,6 +2012,10 @@ int rmx_mstep_stage_rows(rmx_handle m, const int32_t* rows, const int32_t* count
                                cudaMemcpyHostToDevice, b->stream));
     for (int g = 0; g < G; ++g) b->hRn[g] = b->ms_count[g];
     CK(cudaMemcpyAsync(b->ms_Rn_all, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
+    if (rmx_ell_sample_ok(rmax)) {
+        rmx_launch_ell_rowcache(b->stream, tables(b), b->d, 0, G, b->ms_rows, b->ms_Rn_all, rmax, b->ms_rowc);
+        b->count();
+    }
     CK(cudaStreamSynchronize(b->stream));
     return RMX_OK;
 }
@@ -1996,16 +2034,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         return m->fail(RMX_ERR_ARG, "scalar_id must name a likelihood parameter and come with values");
     if (scalar_id < 0 && n_values != 1) return m->fail(RMX_ERR_ARG, "n_values must be 1 without a parameter");
     // likelihood terms the parameter enters (bit u: total-read term u; bit 2 + v: the allele terms of v)
-    int planes = 15;
-    switch (scalar_id) {
-    case RMX_S_NEGBIN_R_0: case RMX_S_NEGBIN_HDEL_R_0: planes = 1; break;
-    case RMX_S_NEGBIN_R_1: case RMX_S_NEGBIN_HDEL_R_1: planes = 2; break;
-    case RMX_S_NEGBIN_HDEL_MU: planes = 3; break;
-    case RMX_S_BETABIN_M_0: case RMX_S_BETABIN_LOH_M_0: planes = 4; break;
-    case RMX_S_BETABIN_M_1: case RMX_S_BETABIN_LOH_M_1: planes = 8; break;
-    case RMX_S_BETABIN_LOH_P: planes = 12; break;
-    default: break;
-    }
+    int planes = planes_of(scalar_id);
     static const bool no_planes = getenv("RMX_MSTEP_ALL_TERMS") != nullptr;      // A/B measurements only
     if (b->ms_all || grad || h_values || no_planes) planes = 15;
     if (h_values || scalar_id != b->ms_const_id) b->ms_const_valid = false;
@@ -2016,7 +2045,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         any |= on && b->ms_count[g] > 0;
         if (on && h_values) {
             for (int k = 0; k < M; ++k) b->P[g].h[k] = h_values[(size_t)g * M + k];
-            b->ll_dirty[g] = 1;
+            b->ll_dirty[g] = 15;
             b->params_dirty = true;
         }
     }
@@ -2037,6 +2066,41 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     const int nb = launch ? rmx_ell_blocks(b->d, Rmax) : 0;
     bool fetch_const = false;
     if (work && planes != 15 && !b->ms_const_valid) fetch_const = true;
+    // samples (<= 256 rows per fit, one GPU): the whole objective is one launch per value and the partial sums travel
+    // to the host in one copy; otherwise constants + objective + column reduction as three launches per value
+    const int NCH = rmx_ell_sample_chunks();
+    const bool fused = launch && !b->ms_all && !b->comm && rmx_ell_sample_ok(Rmax);
+    if (fused) {
+        if (fetch_const) {
+            int rc = push_params(m);
+            if (rc) return rc;
+            rmx_launch_ell_sample(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn_all, b->post, b->q_ot, b->q_oa, b->q_sw,
+                                  b->ms_rowc, b->ms_out + (size_t)32 * G * NCH, NCH, b->dflags, 15 ^ planes);
+            b->count();
+        }
+        for (int v = 0; v < n_values; ++v) {
+            if (scalar_id >= 0) {
+                for (int g = 0; g < G; ++g)
+                    if (!active || active[g]) {
+                        *scalar_slot(b->P[g], scalar_id) = values[(size_t)g * n_values + v];
+                        b->ll_dirty[g] |= (char)planes_of(scalar_id);
+                    }
+                b->params_dirty = true;
+            }
+            int rc = push_params(m);
+            if (rc) return rc;
+            cudaEvent_t te_ = b->tbegin(RMX_K_ELL);
+            rmx_launch_ell_sample(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, b->post, b->q_ot, b->q_oa, b->q_sw,
+                                  b->ms_rowc, b->ms_out + (size_t)v * G * NCH, NCH, b->dflags, planes);
+            b->tend(te_);
+            b->count();
+        }
+        // only what this call produced travels: the first n_values slots, and the constants' slot when it is new
+        CK(cudaMemcpyAsync(b->hms, b->ms_out, (size_t)n_values * G * NCH * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+        if (fetch_const)
+            CK(cudaMemcpyAsync(b->hms + (size_t)32 * G * NCH, b->ms_out + (size_t)32 * G * NCH, (size_t)G * NCH * sizeof(double),
+                               cudaMemcpyDeviceToHost, b->stream));
+    } else {
     if (launch && planes != 15 && !b->ms_const_valid) {
         // the terms the parameter does not enter, for EVERY fit with staged rows (fits join and leave the active set
         // from call to call), with the parameters as they stand
@@ -2053,7 +2117,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
             for (int g = 0; g < G; ++g)
                 if (!active || active[g]) {
                     *scalar_slot(b->P[g], scalar_id) = values[(size_t)g * n_values + v];
-                    b->ll_dirty[g] = 1;
+                    b->ll_dirty[g] |= (char)planes_of(scalar_id);
                 }
             b->params_dirty = true;
         }
@@ -2091,6 +2155,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         rmx_launch_reduce_cols(b->stream, b->part, nb, 1, 0, G, b->part_stride, b->red_out + 16 + v, Batch::RED);
         b->count(3);
     }
+    }
     if (launch && grad) {
         rmx_launch_ell_grad(b->stream, T, b->d, b->dP, 0, G, rows, b->ms_Rn, Rmax, b->post, b->q_ot, b->q_oa, b->q_sw, b->part,
                             b->part_stride, b->dflags);
@@ -2098,10 +2163,18 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         b->count(2);
     }
     if (!work) return RMX_OK;
-    int rc = fetch_red(m);
+    int rc = (fused && !grad) ? sync_check(m) : fetch_red(m);
     if (rc) return rc;
+    auto chunk_sum = [&](int g, int slot) {      // the partial sums of a fit in chunk order
+        const double* q = b->hms + ((size_t)slot * G + g) * NCH;
+        double acc = 0.;
+        for (int c = 0; c < NCH; ++c) acc += q[c];
+        return acc;
+    };
     if (fetch_const) {
-        for (int g = 0; g < G; ++g) b->ms_const[g] = (b->ms_count[g] > 0 || b->comm) ? b->hp[(size_t)g * Batch::RED + 12] : 0.;
+        for (int g = 0; g < G; ++g)
+            b->ms_const[g] = fused ? (b->ms_count[g] > 0 ? chunk_sum(g, 32) : 0.)
+                                   : ((b->ms_count[g] > 0 || b->comm) ? b->hp[(size_t)g * Batch::RED + 12] : 0.);
         b->ms_const_id = scalar_id;
         b->ms_const_valid = true;
     }
@@ -2109,7 +2182,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
         if (b->hRn[g] <= 0 && !(b->comm && (!active || active[g]))) continue;
         const double* r = b->hp + (size_t)g * Batch::RED;
         const double c0 = planes != 15 ? b->ms_const[g] : 0.;
-        for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = r[16 + v] + c0;
+        for (int v = 0; v < n_values; ++v) ell[(size_t)g * n_values + v] = (fused ? chunk_sum(g, v) : r[16 + v]) + c0;
         if (grad) for (int k = 0; k < M; ++k) grad[(size_t)g * M + k] = r[48 + k];
     }
     return RMX_OK;
@@ -2123,7 +2196,7 @@ int rmx_set_scalar_array(rmx_handle m, int id, const uint8_t* active, const doub
     for (int g = 0; g < m->gn; ++g) {
         if (active && !active[g]) continue;
         *scalar_slot(b->P[m->g0 + g], id) = values[g];
-        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[m->g0 + g] = 1;
+        if (id != RMX_S_DIVERGENCE_WEIGHT) b->ll_dirty[m->g0 + g] |= (char)planes_of(id);
     }
     b->params_dirty = true;
     b->ms_const_valid = false;

@@ -41,18 +41,21 @@ struct RmxChains {
 
 // ---- likelihood.cu   (every launcher covers the fits [g0, g0+gn) of a batch; P is the per-fit parameter array)
 void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
-                         const int* rows_all, const int* Rn, int Rmax, double* segc);
+                         const int* rows_all, const int* Rn, int Rmax, double* segc, const double* segk = nullptr,
+                         int planes = 15);
+// per-segment data-only constants (N,3) the full-table form of the above reuses
+void rmx_launch_segk(cudaStream_t st, const RmxTables& T, const RmxDims& d, double* segk);
 void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
                         int gn, const double* segc, double* LL, int* dflags);
 // fast path (per-state tables + wide log table); rmx_lltable2_ok says whether the shape fits its shared memory
 int rmx_lltable2_ok(const RmxDims& d, int Q);
 void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
-                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags);
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes = 15);
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
                       double* fexp, double* mF, int* dflags);
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
-                      double* A);
+                      double* A, int planes = 15);
 // post + qsums + outlier updates (+ next round's swap update and frame) in one pass; S <= 128
 int rmx_round_ok(const RmxDims& d);
 void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
@@ -71,6 +74,16 @@ void rmx_launch_ell_rows_from_sums(cudaStream_t st, const RmxDims& d, int g0, in
 void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int gn, double* out, int64_t out_fit_stride);
 void rmx_launch_fill2(cudaStream_t st, double* out, int64_t n, double v0, double v1);
 int rmx_ell_blocks(const RmxDims& d, int R);
+// the sampled objective in one launch: out[g * out_fit_stride + chunk], chunk < rmx_ell_sample_chunks()
+int rmx_ell_sample_ok(int Rmax);
+int rmx_ell_sample_chunks();
+void rmx_launch_ell_sample(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                           const int* rows_all, const int* Rn, const double* post, const double* q_ot, const double* q_oa,
+                           const double* q_sw, const double* rowc, double* out, int out_fit_stride, int* dflags,
+                           int planes);
+// rowc[(g * 256 + r) * 3 ...]: the parameter-independent constants of the staged rows (once per staged sample)
+void rmx_launch_ell_rowcache(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const int* rows_all,
+                             const int* Rn, int Rmax, double* rowc);
 void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                     const int* rows_all, const int* Rn, int Rmax, const double* segc, const double* post,
                     const double* q_ot, const double* q_oa, const double* q_sw, double* part, int64_t part_fit_stride,

@@ -284,7 +284,9 @@ __global__ void k_segfast(RmxTables T, RmxDims d, const RmxParams* __restrict__ 
 // 97 consecutive units of the segment, so L1 hits after the first touch) and warps proceed independently.
 __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                    const double* __restrict__ segc_all, RmxFast Fp,
-                                                   double* __restrict__ LL_all, int* __restrict__ dflags) {
+                                                   double* __restrict__ LL_all, int* __restrict__ dflags, int planes) {
+    // planes: which term groups to (re)build -- bit u: total-read term u; bit 2 + v: the two allele terms of v.  The
+    // M-step changes one dispersion at a time, and each enters one group only; the other planes of the table stand.
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double2 ltab[RMX_LOGTAB];
     const int QS = Fp.Q * d.S;
@@ -320,12 +322,12 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
         const int sf = sfl[e];
         const bool tmk = (si & 1) != 0, amk = (si & 2) != 0;
         double ll[RMX_NTERM];
-        if ((tmk && !((si & 4) && (sf & 1))) || (amk && !((si & 8) && (sf & 2)))) {
+        if ((tmk && (planes & 3) && !((si & 4) && (sf & 1))) || (amk && (planes & 12) && !((si & 8) && (sf & 2)))) {
             ll_slow(T, d, P, si, segc, n, s, ll, &flags, ltab);
         } else {
 #pragma unroll
             for (int k = 0; k < RMX_NTERM; ++k) ll[k] = 0.;
-            if (tmk) {
+            if (tmk && (planes & 3)) {
                 const double x = lx.y;
                 const double mu = st[e] * ly.x;
                 const double lmu = st[QS + e] + lx.x;
@@ -350,6 +352,7 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
                 const double y0 = ly.y, y1 = s45.x;
 #pragma unroll
                 for (int v = 0; v < 2; ++v) {
+                    if (!((planes >> (2 + v)) & 1)) continue;
                     const double a = st[(2 + 2 * v) * QS + e], b = st[(3 + 2 * v) * QS + e];
                     const double bs = st[(6 + v) * QS + e];
                     const double z[4] = {y0 + a, y1 + b, y1 + a, y0 + b};
@@ -363,8 +366,15 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
             if (isnan(ll[0] + ll[1])) flags |= RMX_F_NB_NAN;
             if (isnan((ll[2] + ll[3]) + (ll[4] + ll[5]))) flags |= RMX_F_BB_NAN;
         }
+        if (planes == 15) {
 #pragma unroll
-        for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
+            for (int k = 0; k < RMX_NTERM; ++k) LL[(int64_t)k * NS + idx] = ll[k];
+        } else {
+            if (planes & 1) LL[idx] = ll[0];
+            if (planes & 2) LL[NS + idx] = ll[1];
+            if (planes & 4) { LL[2 * NS + idx] = ll[2]; LL[3 * NS + idx] = ll[3]; }
+            if (planes & 8) { LL[4 * NS + idx] = ll[4]; LL[5 * NS + idx] = ll[5]; }
+        }
     }
     if (flags) atomicOr(dflags, flags);
 }
@@ -468,7 +478,7 @@ __device__ __forceinline__ void exp_normalize2(double a, double b, double* out) 
 // sufficient statistic of all three 2-way factor updates and of the ELBO's likelihood terms.
 // One warp per (fit, segment); one pass over post + the six LL planes (56 B per (n,s)).
 __global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* __restrict__ LL_all,
-                                               const double* __restrict__ post_all, double* __restrict__ A_all) {
+                                               const double* __restrict__ post_all, double* __restrict__ A_all, int planes) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= d.N) return;
     const int g = RMX_FIT();
@@ -479,15 +489,19 @@ __global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* 
     double a[RMX_NTERM];
 #pragma unroll
     for (int t = 0; t < RMX_NTERM; ++t) a[t] = 0.;
+    // term t belongs to plane group t (t < 2) or 2 + (t - 2) / 2; only the groups in `planes` are summed and written
+    const int tmask6 = (planes & 1) | (planes & 2) | ((planes & 4) ? 12 : 0) | ((planes & 8) ? 48 : 0);
     for (int s = lane; s < d.S; s += 32) {
         int64_t i = (int64_t)n * d.S + s;
         double p = post[i];
 #pragma unroll
-        for (int t = 0; t < RMX_NTERM; ++t) a[t] = fma(p, LL[(int64_t)t * NS + i], a[t]);
+        for (int t = 0; t < RMX_NTERM; ++t)
+            if ((tmask6 >> t) & 1) a[t] = fma(p, LL[(int64_t)t * NS + i], a[t]);
     }
 #pragma unroll
-    for (int t = 0; t < RMX_NTERM; ++t) a[t] = warp_sum(a[t]);
-    if (lane < RMX_NTERM) {
+    for (int t = 0; t < RMX_NTERM; ++t)
+        if ((tmask6 >> t) & 1) a[t] = warp_sum(a[t]);
+    if (lane < RMX_NTERM && ((tmask6 >> lane) & 1)) {
         double v = a[0];
 #pragma unroll
         for (int t = 1; t < RMX_NTERM; ++t) v = lane == t ? a[t] : v;
@@ -766,26 +780,16 @@ __device__ __forceinline__ void block_sum_store(double* v, double* __restrict__ 
     }
 }
 
-// segconst for the row lists of the M-step (same contents as k_segconst, per-fit row count)
-__global__ void k_segconst_rows(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
-                                const int* __restrict__ rows_all, const int* __restrict__ Rn,
-                                double* __restrict__ segc_all) {
-    const int g = RMX_FIT();
-    const int R = rows_all ? Rn[g] : d.N;
-    int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= R) return;
-    const RmxParams& P = Pg[g];
-    double* segc = segc_all + (int64_t)g * 12 * d.N;
-    int n = rows_all ? rows_all[(int64_t)g * d.N + r] : r;
-    double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n];
+// the twelve hoisted per-segment constants of one row (see the top of this file), written with stride `st`
+__device__ __forceinline__ void segconst_row(const RmxParams& P, double x, double y0, double y1, double* __restrict__ o, int st) {
     double na = y0 + y1;
     double lgx1 = lgamma(x + 1.);
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
         double rr = P.negbin_r[u];
-        segc[(0 + u) * R + r] = lgamma(x + rr) - lgx1 - lgamma(rr);
+        o[(0 + u) * st] = lgamma(x + rr) - lgx1 - lgamma(rr);
         double rh = P.negbin_hdel_r[u];
-        segc[(2 + u) * R + r] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
+        o[(2 + u) * st] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
     }
     double lgn1 = lgamma(na + 1.);
     double comb[2];
@@ -799,10 +803,163 @@ __global__ void k_segconst_rows(RmxTables T, RmxDims d, const RmxParams* __restr
         double tl = P.normal_contamination ? 0. : (-lgamma(na + Ml) + lgamma(Ml));
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
-            segc[(4 + v * 2 + w) * R + r] = comb[w] + t;
-            segc[(8 + v * 2 + w) * R + r] = comb[w] + tl;
+            o[(4 + v * 2 + w) * st] = comb[w] + t;
+            o[(8 + v * 2 + w) * st] = comb[w] + tl;
         }
     }
+}
+
+#define RMX_ELL_CHUNKS 16
+#define RMX_ELL_MAXROWS 16       // rows per chunk held in shared memory (256 sampled rows per fit)
+// The parameter-independent part of those constants for the staged sample rows of the batched M-step, computed once
+// per sample: rowc[(g * 256 + r) * 3 + {0,1,2}] = lgamma(x+1), and the two log binomial coefficients.
+__global__ void k_ell_rowcache(RmxTables T, RmxDims d, int g0, const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                               double* __restrict__ rowc) {
+    const int g = RMX_FIT();
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= Rn[g]) return;
+    const int n = rows_all[(int64_t)g * d.N + r];
+    const double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n], na = y0 + y1;
+    const double lgn1 = lgamma(na + 1.);
+    double* o = rowc + ((int64_t)g * (RMX_ELL_CHUNKS * RMX_ELL_MAXROWS) + r) * 3;
+    o[0] = lgamma(x + 1.);
+    o[1] = lgn1 - lgamma(y0 + 1.) - lgamma(na - y0 + 1.);
+    o[2] = lgn1 - lgamma(y1 + 1.) - lgamma(na - y1 + 1.);
+}
+
+// segconst_row with the cached part given and only the constants of the terms in `planes` (the same operations in the
+// same order on those, hence the same values)
+__device__ __forceinline__ void segconst_row_cached(const RmxParams& P, double x, double na, const double* __restrict__ rc,
+                                                    int planes, double* __restrict__ o, int st) {
+    const double lgx1 = rc[0];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        if (!((planes >> u) & 1)) continue;
+        double rr = P.negbin_r[u];
+        o[(0 + u) * st] = lgamma(x + rr) - lgx1 - lgamma(rr);
+        double rh = P.negbin_hdel_r[u];
+        o[(2 + u) * st] = P.normal_contamination ? 0. : (lgamma(x + rh) - lgx1 - lgamma(rh));
+    }
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+        if (!((planes >> (2 + v)) & 1)) continue;
+        double Mv = P.betabin_M[v];
+        double t = -lgamma(na + Mv) + lgamma(Mv);
+        double Ml = P.betabin_loh_M[v];
+        double tl = P.normal_contamination ? 0. : (-lgamma(na + Ml) + lgamma(Ml));
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            o[(4 + v * 2 + w) * st] = rc[1 + w] + t;
+            o[(8 + v * 2 + w) * st] = rc[1 + w] + tl;
+        }
+    }
+}
+
+// segconst for the row lists of the M-step (same contents as k_segconst, per-fit row count).  With `segk` (the
+// parameter-independent part per segment, k_segk) and no row list, only the constants of the term groups in `planes`
+// are recomputed -- 2 to 8 lgamma per segment instead of 20.
+__global__ void k_segconst_rows(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                                double* __restrict__ segc_all, const double* __restrict__ segk, int planes) {
+    const int g = RMX_FIT();
+    const int R = rows_all ? Rn[g] : d.N;
+    int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    int n = rows_all ? rows_all[(int64_t)g * d.N + r] : r;
+    if (segk && !rows_all)
+        segconst_row_cached(Pg[g], T.x[n], T.y0[n] + T.y1[n], segk + (int64_t)n * 3, planes,
+                            segc_all + (int64_t)g * 12 * d.N + r, R);
+    else
+        segconst_row(Pg[g], T.x[n], T.y0[n], T.y1[n], segc_all + (int64_t)g * 12 * d.N + r, R);
+}
+
+// segk[n][0..2] = lgamma(x+1) and the two log binomial coefficients of segment n: data only, once per batch
+__global__ void k_segk(RmxTables T, RmxDims d, double* __restrict__ segk) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= d.N) return;
+    const double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n], na = y0 + y1;
+    const double lgn1 = lgamma(na + 1.);
+    segk[(int64_t)n * 3] = lgamma(x + 1.);
+    segk[(int64_t)n * 3 + 1] = lgn1 - lgamma(y0 + 1.) - lgamma(na - y0 + 1.);
+    segk[(int64_t)n * 3 + 2] = lgn1 - lgamma(y1 + 1.) - lgamma(na - y1 + 1.);
+}
+
+// The sampled M-step objective in ONE launch (the lock-step M-step evaluates it ~300 times per EM iteration, each a
+// host round trip): CTA (chunk c, fit g) takes a contiguous sixteenth of the fit's sample rows, computes their hoisted
+// constants into shared memory, sums post * q * LL over (row, state) in a fixed order and writes ONE partial;
+// the host adds the RMX_ELL_CHUNKS partials of a fit in order.  `planes` as in ll_core.
+__global__ void __launch_bounds__(256) k_ell_sample(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+                                                    const int* __restrict__ rows_all, const int* __restrict__ Rn,
+                                                    const double* __restrict__ post_all,
+                                                    const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
+                                                    const double* __restrict__ q_sw_all, const double* __restrict__ rowc,
+                                                    double* __restrict__ out, int out_fit_stride,
+                                                    int* __restrict__ dflags, int planes) {
+    __shared__ double2 ltab[RMX_LOGTAB];
+    __shared__ double segc[12 * RMX_ELL_MAXROWS];
+    // per-row inputs staged once (x, l, y0, y1, the six q-factor entries), masks / normal copies, and the state table:
+    // the (row, state) loop then touches global memory for the posterior only
+    __shared__ double rowd[10 * RMX_ELL_MAXROWS];
+    __shared__ int rown[RMX_ELL_MAXROWS], rowi[RMX_ELL_MAXROWS];
+    __shared__ int8_t stab[2 * RMX_MAXM * 128];
+    const int g = RMX_FIT();
+    const int R = Rn[g];
+    const int per = (R + RMX_ELL_CHUNKS - 1) / RMX_ELL_CHUNKS;
+    const int r0 = blockIdx.x * per;
+    const int nr = max(0, min(per, R - r0));
+    const RmxParams& P = Pg[g];
+    const bool tab_sm = d.S <= 128;
+    if (tab_sm)
+        for (int e = threadIdx.x; e < d.S * d.M * 2; e += blockDim.x) stab[e] = T.tab[e];
+    if ((int)threadIdx.x < nr) {
+        const int r = threadIdx.x;
+        const int n = rows_all[(int64_t)g * d.N + r0 + r];
+        const int64_t gn = (int64_t)g * d.N + n;
+        rown[r] = n;
+        const double x = T.x[n], y0 = T.y0[n], y1 = T.y1[n];
+        rowd[0 * RMX_ELL_MAXROWS + r] = x;
+        rowd[1 * RMX_ELL_MAXROWS + r] = T.l[n];
+        rowd[2 * RMX_ELL_MAXROWS + r] = y0;
+        rowd[3 * RMX_ELL_MAXROWS + r] = y1;
+        rowd[4 * RMX_ELL_MAXROWS + r] = q_ot_all[2 * gn];
+        rowd[5 * RMX_ELL_MAXROWS + r] = q_ot_all[2 * gn + 1];
+        rowd[6 * RMX_ELL_MAXROWS + r] = q_oa_all[2 * gn];
+        rowd[7 * RMX_ELL_MAXROWS + r] = q_oa_all[2 * gn + 1];
+        rowd[8 * RMX_ELL_MAXROWS + r] = q_sw_all[2 * gn];
+        rowd[9 * RMX_ELL_MAXROWS + r] = q_sw_all[2 * gn + 1];
+        rowi[r] = (T.tmask[gn] != 0 ? 1 : 0) | (T.amask[gn] != 0 ? 2 : 0) | ((int)T.nrm[2 * n] << 8) | ((int)T.nrm[2 * n + 1] << 16);
+        segconst_row_cached(P, x, y0 + y1, rowc + ((int64_t)g * (RMX_ELL_CHUNKS * RMX_ELL_MAXROWS) + r0 + r) * 3, planes,
+                            segc + r, RMX_ELL_MAXROWS);
+    }
+    rmx_logtab_init(ltab);      // includes the barrier
+    double acc[1] = {0.};
+    int flags = 0;
+    const int units = nr * d.S;
+    const int8_t* tab = tab_sm ? stab : T.tab;
+    for (int idx = threadIdx.x; idx < units; idx += blockDim.x) {
+        const int r = idx / d.S, s = idx - r * d.S;
+        const int n = rown[r], ri = rowi[r];
+        const double p = post_all[((int64_t)g * d.N + n) * d.S + s];
+        SegIn in;
+        in.segc = segc + r;
+        in.sstride = RMX_ELL_MAXROWS;
+        in.x = rowd[r]; in.l = rowd[RMX_ELL_MAXROWS + r]; in.y0 = rowd[2 * RMX_ELL_MAXROWS + r]; in.y1 = rowd[3 * RMX_ELL_MAXROWS + r];
+        in.nrm0 = (int)(int8_t)((ri >> 8) & 0xff); in.nrm1 = (int)(int8_t)((ri >> 16) & 0xff);
+        double ll[RMX_NTERM];
+        ll_core(tab, d, P, (ri & 1) != 0, (ri & 2) != 0, in, s, ll, &flags, ltab, nullptr, planes);
+        const double ot0 = rowd[4 * RMX_ELL_MAXROWS + r], ot1 = rowd[5 * RMX_ELL_MAXROWS + r];
+        const double oa0 = rowd[6 * RMX_ELL_MAXROWS + r], oa1 = rowd[7 * RMX_ELL_MAXROWS + r];
+        const double sw0 = rowd[8 * RMX_ELL_MAXROWS + r], sw1 = rowd[9 * RMX_ELL_MAXROWS + r];
+        double a = 0.;
+        if (planes & 1) a += p * ot0 * ll[0];
+        if (planes & 2) a += p * ot1 * ll[1];
+        if (planes & 4) a += p * oa0 * sw0 * ll[2] + p * oa0 * sw1 * ll[3];
+        if (planes & 8) a += p * oa1 * sw0 * ll[4] + p * oa1 * sw1 * ll[5];
+        acc[0] += a;
+    }
+    // block_sum_store writes part[threadIdx.x * stride + blockIdx.x]: one value per (fit, chunk)
+    block_sum_store<1>(acc, out + (int64_t)g * out_fit_stride, gridDim.x);
+    if (flags) atomicOr(dflags, flags);
 }
 
 __global__ void __launch_bounds__(256) k_ell(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
@@ -1090,9 +1247,13 @@ void rmx_launch_fill2(cudaStream_t st, double* out, int64_t n, double v0, double
 }
 
 void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
-                         const int* rows_all, const int* Rn, int Rmax, double* segc) {
+                         const int* rows_all, const int* Rn, int Rmax, double* segc, const double* segk, int planes) {
     if (Rmax <= 0 || gn <= 0) return;
-    k_segconst_rows<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, P, g0, rows_all, Rn, segc);
+    k_segconst_rows<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, P, g0, rows_all, Rn, segc, segk, planes);
+}
+void rmx_launch_segk(cudaStream_t st, const RmxTables& T, const RmxDims& d, double* segk) {
+    if (d.N <= 0) return;
+    k_segk<<<cdiv(d.N, 128), 128, 0, st>>>(T, d, segk);
 }
 
 void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
@@ -1114,7 +1275,7 @@ static size_t lltable2_smem(const RmxDims& d, int Q) {
 int rmx_lltable2_ok(const RmxDims& d, int Q) { return lltable2_smem(d, Q) <= 72 * 1024; }
 
 void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
-                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags) {
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes) {
     int64_t NS = (int64_t)d.N * d.S;
     if (NS <= 0 || gn <= 0) return;
     const int QS = Fp.Q * d.S;
@@ -1128,7 +1289,7 @@ void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, cons
     if (attr_once.need()) {
         cudaFuncSetAttribute(k_lltable2, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
     }
-    k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags);
+    k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags, planes);
 }
 
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
@@ -1145,9 +1306,9 @@ void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, con
 }
 
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
-                      double* A) {
+                      double* A, int planes) {
     if (d.N <= 0 || gn <= 0) return;
-    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A);
+    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A, planes);
 }
 
 int rmx_round_ok(const RmxDims& d) { return d.S <= 128; }
@@ -1198,6 +1359,21 @@ void rmx_launch_plogp(cudaStream_t st, const double* p, int64_t n, int g0, int g
     k_plogp<<<dim3(cdiv(n, 256), gn), 256, 0, st>>>(p, n, g0, out, out_fit_stride);
 }
 
+int rmx_ell_sample_ok(int Rmax) { return Rmax > 0 && Rmax <= RMX_ELL_CHUNKS * RMX_ELL_MAXROWS; }
+int rmx_ell_sample_chunks() { return RMX_ELL_CHUNKS; }
+void rmx_launch_ell_sample(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
+                           const int* rows_all, const int* Rn, const double* post, const double* q_ot, const double* q_oa,
+                           const double* q_sw, const double* rowc, double* out, int out_fit_stride, int* dflags,
+                           int planes) {
+    if (gn <= 0) return;
+    k_ell_sample<<<dim3(RMX_ELL_CHUNKS, gn), 256, 0, st>>>(T, d, P, g0, rows_all, Rn, post, q_ot, q_oa, q_sw, rowc, out,
+                                                          out_fit_stride, dflags, planes);
+}
+void rmx_launch_ell_rowcache(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, const int* rows_all,
+                             const int* Rn, int Rmax, double* rowc) {
+    if (gn <= 0 || Rmax <= 0) return;
+    k_ell_rowcache<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, g0, rows_all, Rn, rowc);
+}
 int rmx_ell_blocks(const RmxDims& d, int R) { return cdiv((int64_t)R * d.S, 256); }
 
 void rmx_launch_ell(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,

@@ -596,9 +596,10 @@ class GridMStep(object):
             if self._wbuf.get('shape') != (D, A, N):
                 self._wbuf['shape'], self._wbuf['w'] = (D, A, N), np.empty((D, A, N), dtype=np.float64)
             w, flags = self._wbuf['w'], np.zeros((D, A), dtype=np.uint8)
-            for d, step in enumerate(plan):
+            def fill(d):
+                step = plan[d]
                 if step == 'h':
-                    continue
+                    return
                 if hasattr(be, 'weights_block') and step in ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1'):
                     flags[d] = be.weights_block(step, alive, w[d])
                 else:
@@ -606,6 +607,15 @@ class GridMStep(object):
                         wg = self._weights(step, g)
                         if wg is not None:
                             w[d, k], flags[d, k] = wg, 1
+
+            # one strided sum and one division over (fits, N) per parameter: numpy releases the GIL inside both
+            if hasattr(be, 'weights_block') and D > 2:
+                import concurrent.futures
+                with concurrent.futures.ThreadPoolExecutor(min(D, _host_threads())) as pool:
+                    list(pool.map(fill, range(D)))
+            else:
+                for d in range(D):
+                    fill(d)
             chosen, status = native_choice([self.drivers[g].random_state for g in alive], N, size, [None] * D,
                                            block=(w, flags))
             drawn = []

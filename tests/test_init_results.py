@@ -48,7 +48,8 @@ def test_init_grid_equals_fixture_grid(name):
 
 
 def test_readdepth_equals_reference_in_process(ref):
-    """calculate_depth / calculate_minor_modes / candidates / estimate_ploidy == the reference's, bit for bit."""
+    """calculate_depth / candidates / estimate_ploidy == the reference's, bit for bit; calculate_minor_modes to the
+    reproducibility of sklearn's own k-means."""
     from remixt_b200 import readdepth
     exp = util.load_experiment('config1')
     rex = _ref_experiment('config1')
@@ -61,15 +62,16 @@ def test_readdepth_equals_reference_in_process(ref):
     m1 = readdepth.calculate_minor_modes(mine)
     np.random.seed(1234)
     m2 = ref['readdepth'].calculate_minor_modes(theirs)
-    assert np.array_equal(m1, m2)
+    # sklearn's k-means reduces over threads: the same call on the same data is reproducible to an ulp or two only
+    assert m1.shape == m2.shape and np.allclose(m1, m2, rtol=1e-12, atol=0.)
     c1 = readdepth.calculate_candidate_h_monoclonal(m1)
-    c2 = ref['readdepth'].calculate_candidate_h_monoclonal(m2)
+    c2 = ref['readdepth'].calculate_candidate_h_monoclonal(m1)
     assert len(c1) == len(c2) and all(np.array_equal(a, b) for a, b in zip(c1, c2))
     for h in c1[:3]:
         assert readdepth.estimate_ploidy(h, exp) == ref['readdepth'].estimate_ploidy(h, rex)
         assert readdepth.estimate_ploidy(h, exp, read_depth=mine) == ref['readdepth'].estimate_ploidy(h, rex)
     fixed = readdepth.calculate_candidate_h_monoclonal(m1, h_normal=0.03, h_tumour=0.05)
-    assert np.array_equal(fixed, ref['readdepth'].calculate_candidate_h_monoclonal(m2, h_normal=0.03, h_tumour=0.05))
+    assert np.array_equal(fixed, ref['readdepth'].calculate_candidate_h_monoclonal(m1, h_normal=0.03, h_tumour=0.05))
 
 
 def test_init_raises_when_depth_cut_too_strict():
