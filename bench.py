@@ -81,7 +81,23 @@ class PlainExperiment(object):
         self.segment_major_is_allele_a = np.ones(n, dtype=int)
 
 
+# workloads that reuse another workload's genome with a different model configuration
+DERIVED = {
+    # BASELINE config 3: the config-2 genome with max copy number 8 (S = 165 states for 2 tumour clones + normal);
+    # its initialisation grid comes from this repo's pipeline.init (the reference's grid builder, tests/test_init_results.py)
+    'config3': ('config2', {'max_copy_number': 8, 'max_ploidy': 4.0}),
+}
+
+
 def load_workload(name):
+    if name in DERIVED:
+        base, cfg = DERIVED[name]
+        exp, _ = load_workload(base)
+        exp._name = name
+        CONFIG.update(cfg)
+        from remixt_b200 import pipeline
+        grid = pipeline.init(exp, dict(cfg))
+        return exp, [grid[i] for i in sorted(grid)]
     path = os.path.join(GOLDEN, 'exp_%s.npz' % name)
     d = np.load(path, allow_pickle=False)
     exp = PlainExperiment(d['x'], d['l'], d['adjacencies'], d['breakpoints'], d['breakpoint_ids'], d['chromosome'])
@@ -310,8 +326,19 @@ def gpu_arm(args):
             elbo = em_iteration()
         batch.event_record(1)
         barrier(batch)
-        out = dict(ms=batch.event_elapsed(0, batch, 1), launches=_lib.global_launch_count() - l0,
-                   ktime=batch.kernel_timing(False), clocks=sampler.stop() if sampler else None,
+        ms_timed = batch.event_elapsed(0, batch, 1)
+        launches_timed = _lib.global_launch_count() - l0
+        ktime = batch.kernel_timing(True)
+        clocks = sampler.stop() if sampler else None
+        # the likelihood table of ALL fits for a new h, on its own: inside the step the M-step also rebuilds single
+        # planes of it for subsets of fits, so the step's launches of this class are not uniform
+        h_now = np.array(batch.h)
+        for _ in range(3):
+            batch.h = h_now
+            batch.update_framelogprob()
+        ktime['lltable'] = batch.kernel_timing(False)['lltable']
+        out = dict(ms=ms_timed, launches=launches_timed,
+                   ktime=ktime, clocks=clocks,
                    m_step_ms=em_iteration.m_s * 1e3, mstep_rounds=lock.rounds - r0, mstep_evals=lock.evaluations - e0,
                    N1=batch.num_segments, S=batch.num_cn_states, K=batch.num_breakpoints,
                    NC=int(np.sum(np.asarray(batch.is_telomere)[:-1] > 0)) + 1,
@@ -369,12 +396,14 @@ def gpu_arm(args):
     hbm_peak = peaks.get('hbm_gbs')
     models = kernel_models(N1, S, NC, G, R)
     ktime = res['ktime']
-    total_kernel_ms = sum(v[0] for v in ktime.values())
+    total_kernel_ms = sum(v[0] for k, v in ktime.items() if k != 'lltable') + ktime['lltable'][0] / max(ktime['lltable'][1], 1)
     kernels = {}
     for k, (tot, n) in ktime.items():
         if n == 0:
             continue
-        ent = {'launches': n, 'ms_per_launch': tot / n, 'share_of_kernel_time': tot / total_kernel_ms}
+        ent = {'launches': n, 'ms_per_launch': tot / n, 'share_of_kernel_time': (tot / n if k == 'lltable' else tot) / total_kernel_ms}
+        if k == 'lltable':
+            ent['note'] = 'full rebuild for all fits, timed on its own after the timed region (one per EM iteration in the E-step)'
         # launches of the M-step's full-data evaluations rebuild the table for the fits whose parameters changed
         # only, so per-launch work varies: rates are quoted for the E-step classes, whose launches are uniform
         if k in models and k not in ('qsums',):
@@ -464,15 +493,24 @@ def _ref_worker_init(name, nseg):
         with warnings.catch_warnings():
             warnings.simplefilter('ignore')
             import remixt.cn_model as rcn
-    exp, inits = load_workload(name)
-    _W.update(kind=kind, rcn=rcn, sub=subsample_experiment(exp, nseg), inits=inits, quiet=lambda: contextlib.redirect_stdout(io.StringIO()))
+    cn_max = 6
+    if name in DERIVED:         # the base genome and grid with the derived model configuration (no remixt_b200 import here)
+        base, cfg = DERIVED[name]
+        exp, inits = load_workload(base)
+        cn_max = cfg.get('max_copy_number', 6)
+        depth = min(2. * ip['h_normal'] + (cn_max + 0.25) * ip['h_tumour'] for ip in inits)      # analysis/pipeline.py:47,85
+        inits = [dict(ip, max_depth=depth) for ip in inits]
+    else:
+        exp, inits = load_workload(name)
+    _W.update(kind=kind, rcn=rcn, sub=subsample_experiment(exp, nseg), inits=inits, cn_max=cn_max,
+              quiet=lambda: contextlib.redirect_stdout(io.StringIO()))
 
 
 def _ref_worker_build(idx):
     ip = _W['inits'][idx % len(_W['inits'])]
     sub = _W['sub']
     h = np.array([ip['h_normal'], ip['h_tumour'] * ip['mix_frac'], ip['h_tumour'] * (1. - ip['mix_frac'])])
-    kw = dict(max_copy_number=6, normal_contamination=True, divergence_weight=ip['divergence_weight'],
+    kw = dict(max_copy_number=_W['cn_max'], normal_contamination=True, divergence_weight=ip['divergence_weight'],
               min_segment_length=10000, min_proportion_genotyped=0.01, max_depth=ip['max_depth'],
               normal_copies=np.array([[1, 1]] * sub.l.shape[0]))
     if _W['rcn'] is not None:

@@ -86,3 +86,40 @@ def test_four_clones():
     cu, ref = _drive(_sub(30), h, bpmodel_np.RemixtModel)
     assert cu.num_clones == 4 and cu.num_cn_states == 457
     _compare(cu, ref, rounds=1)
+
+
+def _chromosome(name, chrom):
+    """One whole chromosome of a fixture as its own experiment (breakpoints with both ends on it)."""
+    sys.path.insert(0, util.ROOT)
+    import bench
+    exp = util.load_experiment(name)
+    on = np.flatnonzero(np.asarray(exp.segment_chromosome_id).astype(str) == str(chrom))
+    assert on.size and np.all(np.diff(on) == 1)
+    return bench.subsample_experiment(exp, int(on.size), start=int(on[0]))
+
+
+def test_config3_state_space_on_config1_vs_compiled_reference(ref_bpmodel):
+    """BASELINE config 3's state space (max copy number 8, S = 165) on the 1000 segments / 64 breakpoints of config 1,
+    against the COMPILED reference (three (N-1, S, S) arrays of 0.23 GB each): every update of two rounds, MAP path,
+    gradient."""
+    exp = util.load_experiment('config1')
+    ip = util.init_params('config1', 1)
+    from remixt_b200 import pipeline
+    args = dict(max_copy_number=8, max_depth=2. * ip['h_normal'] + 8.25 * ip['h_tumour'],
+                normal_copies=np.array([[1, 1]] * exp.l.shape[0]))
+    cu = util.make_driver(exp, ip, **args).model
+    ref = util.make_driver(exp, ip, model_class=ref_bpmodel.RemixtModel, **args).model
+    assert cu.num_cn_states == 165 and cu.num_segments > 1000
+    _compare(cu, ref, rounds=2)
+
+
+def test_whole_chromosome_of_config2_vs_compiled_reference(ref_bpmodel):
+    """The benched workload at the scale the reference can hold: chromosome 1 of config 2 (about 2.4 k segments,
+    3 x 0.18 GB of transition arrays), GPU against the compiled reference through two rounds and the MAP decode."""
+    exp = _chromosome('config2', '1')
+    assert exp.l.shape[0] > 2000
+    ip = util.init_params('config2', 5)
+    cu = util.make_driver(exp, ip).model
+    ref = util.make_driver(exp, ip, model_class=ref_bpmodel.RemixtModel).model
+    assert cu.num_cn_states == 97 and cu.num_breakpoints >= 5
+    _compare(cu, ref, rounds=2)
