@@ -257,6 +257,24 @@ int rmx_sum_product_2paramtrans(int device, int64_t n_obs, int64_t n_comp, const
 int rmx_max_product(int device, int64_t n_obs, int64_t n_comp, const double* framelogprob,
                     const double* log_transmat, int64_t* state_sequence, double* logprob);
 
+/* Allocation-free Viterbi decode.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernel and same results as rmx_max_product, but
+ *   - framelogprob (n_obs, n_comp), log_transmat (n_obs - 1, n_comp, n_comp), state_sequence (n_obs int64) and
+ *     logprob (1 double) are DEVICE pointers on `device`, owned by the caller;
+ *   - the kernel is enqueued on `stream` (a cudaStream_t; NULL = the default stream) and the call returns without
+ *     synchronising: the outputs are valid once the stream has reached that point;
+ *   - the kernel's scratch (the (n_obs, n_comp) lattice of running maxima) lives in a file-scope device array of
+ *     RMX_NOALLOC_MAX_CELLS doubles (16 MiB) that every GPU that loads the library holds until the process exits.
+ *     n_obs * n_comp > RMX_NOALLOC_MAX_CELLS (or n_comp > 4096) is rejected with RMX_ERR_ARG and a message.
+ * The call performs no cudaMalloc / cudaFree and calls no allocating library routine.  All calls on one device share
+ * the array (it keeps the previous call's contents; the kernel writes every cell before it reads it, so nothing
+ * needs clearing): calls whose kernels can overlap on the GPU (different streams without a dependency) RACE --
+ * serialise them on one stream or with events. */
+#define RMX_NOALLOC_MAX_CELLS (1 << 21)
+int rmx_max_product_noalloc(int device, void* stream, int64_t n_obs, int64_t n_comp, const double* framelogprob,
+                            const double* log_transmat, int64_t* state_sequence, double* logprob);
+
 /* ---- instrumentation ---------------------------------------------------------------------- */
 /* Number of kernels this handle has launched since creation. */
 int rmx_launch_count(rmx_handle h, int64_t* count);

@@ -44,7 +44,7 @@ EXPORTS = [
     'rmx_expected_log_likelihood_grid',
     'rmx_mstep_stage_sample', 'rmx_mstep_stage_rows', 'rmx_mstep_evaluate', 'rmx_set_scalar_array', 'rmx_host_sample_segments',
     'rmx_infer_cn', 'rmx_calculate_log_transmat', 'rmx_eval',
-    'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product',
+    'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product', 'rmx_max_product_noalloc',
     'rmx_launch_count', 'rmx_global_launch_count', 'rmx_kernel_timing', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
     'rmx_event_record', 'rmx_event_elapsed', 'rmx_fp64_peak',
 ]
@@ -108,6 +108,7 @@ def _load():
         'rmx_sum_product': [I, I64, I64, P, P, P, P],
         'rmx_sum_product_2paramtrans': [I, I64, I64, P, P, P, D, D],
         'rmx_max_product': [I, I64, I64, P, P, P, C.POINTER(D)],
+        'rmx_max_product_noalloc': [I, P, I64, I64, P, P, P, P],
         'rmx_launch_count': [H, C.POINTER(I64)],
         'rmx_global_launch_count': [C.POINTER(I64)],
         'rmx_kernel_timing': [H, I, P, P],

@@ -2419,6 +2419,24 @@ int rmx_max_product(int device, int64_t N, int64_t S, const double* F, const dou
     return RMX_OK;
 }
 
+// Viterbi decode without any allocation: device pointers in and out, caller's stream, lattice in the library's
+// file-scope device array (chain.cu).  No reference counterpart; see include/remixt_b200.h.
+int rmx_max_product_noalloc(int device, void* stream, int64_t N, int64_t S, const double* F, const double* Tm,
+                            int64_t* path, double* logprob) {
+    if (N < 1 || S < 1 || S > 4096) { g_create_error = "bad shape"; return RMX_ERR_ARG; }
+    if (N > (int64_t)RMX_NOALLOC_MAX_CELLS / S) {
+        g_create_error = "rmx_max_product_noalloc: n_obs * n_comp = " + std::to_string(N * S) +
+                         " exceeds the static lattice of RMX_NOALLOC_MAX_CELLS = " +
+                         std::to_string((long long)RMX_NOALLOC_MAX_CELLS) + " cells; use rmx_max_product";
+        return RMX_ERR_ARG;
+    }
+    if (!F || !path || !logprob || (N > 1 && !Tm)) { g_create_error = "null pointer"; return RMX_ERR_ARG; }
+    const char* err = rmx_launch_max_product_noalloc((cudaStream_t)stream, device, N, (int)S, F, Tm, path, logprob);
+    if (err) { g_create_error = err; return RMX_ERR_CUDA; }
+    g_launches += 1;
+    return RMX_OK;
+}
+
 // ---- instrumentation
 int rmx_launch_count(rmx_handle m, int64_t* count) {
     if (!m) return RMX_ERR_ARG;

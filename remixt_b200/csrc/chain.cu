@@ -20,6 +20,8 @@
 // each E entry loaded into a register is used GT times per step.  Chromosomes are coupled only through
 // telomere rows whose log_transmat is identically zero, so chains are exactly independent.
 #include <cstdlib>
+#include <mutex>
+#include "../../include/remixt_b200.h"
 #include "common.cuh"
 #include "kernels.h"
 
@@ -1612,4 +1614,42 @@ void rmx_launch_max_product(cudaStream_t st, int64_t N, int S, const double* F, 
     int threads = ((S + 31) / 32) * 32;
     if (threads > 1024) threads = 1024;
     k_max_product<<<1, threads, sizeof(double) * S, st>>>(N, S, F, Tm, lattice, path, logprob);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free Viterbi decode (rmx_max_product_noalloc).  k_max_product needs an (N, S) lattice of running maxima
+// as scratch; here that scratch is a file-scope device array of RMX_NOALLOC_MAX_CELLS doubles (16 MiB, held by every
+// GPU that loads the module until the process exits) instead of a cudaMalloc per call.  In host code the array's
+// name is only a stand-in for the symbol: its device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and that address is what the kernel receives.  The kernel writes
+// every lattice cell it later reads, so nothing has to be cleared between calls; all calls on one device share the
+// array, so two calls whose kernels overlap on the GPU (different streams, no dependency) race.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_lattice[RMX_NOALLOC_MAX_CELLS];
+
+#define RMX_NOALLOC_MAX_DEVICES 64
+static double* g_noalloc_ptr[RMX_NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mu;
+
+const char* rmx_launch_max_product_noalloc(cudaStream_t st, int device, int64_t N, int S, const double* F,
+                                           const double* Tm, int64_t* path, double* logprob) {
+    if (device < 0 || device >= RMX_NOALLOC_MAX_DEVICES) return "device index out of range";
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    double* lattice = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_lattice);
+            if (e != cudaSuccess) return cudaGetErrorString(e);
+            g_noalloc_ptr[device] = static_cast<double*>(p);
+        }
+        lattice = g_noalloc_ptr[device];
+    }
+    int threads = ((S + 31) / 32) * 32;
+    if (threads > 1024) threads = 1024;
+    k_max_product<<<1, threads, sizeof(double) * S, st>>>(N, S, F, Tm, lattice, path, logprob);
+    e = cudaGetLastError();
+    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }

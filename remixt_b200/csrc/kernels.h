@@ -155,3 +155,7 @@ void rmx_launch_sum_product_2p(cudaStream_t st, int64_t N, int S, const double* 
                                double e0, double e1);
 void rmx_launch_max_product(cudaStream_t st, int64_t N, int S, const double* F, const double* Tm, double* lattice,
                             int64_t* path, double* logprob);
+// Viterbi decode with the lattice in the library's file-scope device array (no allocation); DEVICE pointers.  Returns
+// nullptr or an error message.
+const char* rmx_launch_max_product_noalloc(cudaStream_t st, int device, int64_t N, int S, const double* F,
+                                           const double* Tm, int64_t* path, double* logprob);
