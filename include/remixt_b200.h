@@ -225,6 +225,18 @@ int rmx_mstep_stage_sample(rmx_handle h, const int64_t* sample);
 int rmx_mstep_stage_rows(rmx_handle h, const int32_t* rows, const int32_t* counts, int max_rows);
 int rmx_mstep_evaluate(rmx_handle h, const uint8_t* active, const double* h_values, int scalar_id,
                        const double* values, int n_values, double* ell, double* grad);
+/* update_param's optimiser (cn_model.py:533-569: scipy.optimize.brute over `grid`, then scipy.optimize.fmin from the
+ * grid minimum) for every active fit of the batch, driven from inside the library: the `n_grid` (<= 32) grid values
+ * inside [lo, hi] are evaluated on the staged sample in one synchronisation, then the fits' Nelder-Mead simplices
+ * advance in lock step, one evaluation per fit and round (one launch + one synchronisation per round, no host
+ * interpreter in between).  Values outside [lo, hi] count as +inf and are never assigned.  Per fit the evaluation
+ * points, their order and the optimum are those of the per-fit scipy calls; on return the parameter of every fit holds
+ * the LAST value evaluated for it (the state the reference's acceptance test then sees, cn_model.py:561-563).
+ * result (gn): the optimum; evals (gn, optional): fmin evaluations per fit; rounds (2, optional): device rounds and
+ * objective evaluations spent; trace (gn, trace_cap, 2; optional): the fmin evaluations (x, f) of every fit. */
+int rmx_mstep_param_search(rmx_handle h, const uint8_t* active, int scalar_id, double lo, double hi,
+                           const double* grid, int n_grid, double* result, int32_t* evals, int64_t* rounds,
+                           double* trace, int trace_cap);
 /* The segment samples of the M-step for all fits at once, on HOST threads (no device work): for draw d and fit g,
  * numpy.random.RandomState.choice(n, size, replace=False, p=weights[d][g]) of cn_model.py:475-480, consuming the fit's
  * own MT19937 stream exactly as numpy's (frozen) legacy algorithm does.  mt_key (num_fits,624) / mt_pos (num_fits) are the

@@ -42,7 +42,7 @@ EXPORTS = [
     'rmx_variational_energy', 'rmx_variational_entropy', 'rmx_elbo',
     'rmx_expected_log_likelihood', 'rmx_expected_log_likelihood_partial_h',
     'rmx_expected_log_likelihood_grid',
-    'rmx_mstep_stage_sample', 'rmx_mstep_stage_rows', 'rmx_mstep_evaluate', 'rmx_set_scalar_array', 'rmx_host_sample_segments',
+    'rmx_mstep_stage_sample', 'rmx_mstep_stage_rows', 'rmx_mstep_evaluate', 'rmx_mstep_param_search', 'rmx_set_scalar_array', 'rmx_host_sample_segments',
     'rmx_infer_cn', 'rmx_calculate_log_transmat', 'rmx_eval',
     'rmx_sum_product', 'rmx_sum_product_2paramtrans', 'rmx_max_product', 'rmx_max_product_noalloc',
     'rmx_launch_count', 'rmx_global_launch_count', 'rmx_kernel_timing', 'rmx_chain_timing', 'rmx_synchronize', 'rmx_stream',
@@ -100,6 +100,7 @@ def _load():
         'rmx_mstep_stage_sample': [H, P],
         'rmx_mstep_stage_rows': [H, P, P, I],
         'rmx_mstep_evaluate': [H, P, P, I, P, I, P, P],
+        'rmx_mstep_param_search': [H, P, I, D, D, P, I, P, P, P, P, I],
         'rmx_set_scalar_array': [H, I, P, P],
         'rmx_host_sample_segments': [I, I, I, I, P, P, P, P, P, P, I],
         'rmx_infer_cn': [H, P],

@@ -404,6 +404,25 @@ class _ModelBase(object):
                                      None if g is None else _ptr(g)), self._handle)
         return (ell, g) if grad else ell
 
+    def mstep_param_search(self, name, lo, hi, grid, active=None, trace=0):
+        """``scipy.optimize.brute(grid) + fmin`` of ``update_param(name)`` (``cn_model.py:553-558``) for every active fit
+        inside the library (``rmx_mstep_param_search``).  Returns ``(optimum (gn,), (rounds, evaluations))`` and, with
+        ``trace`` > 0, also the per-fit fmin evaluations as a list of ``(k, 2)`` arrays of (x, f)."""
+        gn = self._gn
+        act = None if active is None else np.ascontiguousarray(active, dtype=np.uint8)
+        grid = np.ascontiguousarray(grid, dtype=np.float64).ravel()
+        result = np.zeros(gn, dtype=np.float64)
+        evals = np.zeros(gn, dtype=np.int32)
+        rounds = np.zeros(2, dtype=np.int64)
+        tr = np.zeros((gn, int(trace), 2), dtype=np.float64) if trace else None
+        check(lib.rmx_mstep_param_search(self._handle, None if act is None else _ptr(act), _lib.SCALAR_IDS[name],
+                                         float(lo), float(hi), _ptr(grid), int(grid.shape[0]), _ptr(result), _ptr(evals),
+                                         _ptr(rounds), None if tr is None else _ptr(tr), int(trace)), self._handle)
+        stats = (int(rounds[0]), int(rounds[1]))
+        if trace:
+            return result, stats, [tr[g, :min(int(evals[g]), int(trace))].copy() for g in range(gn)]
+        return result, stats
+
     def set_scalar_array(self, name, values, active=None):
         """``setattr(model, name, values[g])`` for every (active) fit of the handle."""
         v = np.ascontiguousarray(values, dtype=np.float64).reshape(self._gn)

@@ -2188,6 +2188,164 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
     return RMX_OK;
 }
 
+// ---- update_param's optimiser for all fits of a grid, driven from inside the library --------------------------------
+// scipy.optimize.fmin (Nelder-Mead, one variable, default options) as a state machine: next() is the point to
+// evaluate, feed() takes its value.  Statement for statement remixt_b200/mstep.py:neldermead_1d, which
+// tests/test_mstep_cpu.py pins to scipy evaluation by evaluation.
+namespace {
+struct NelderMead1 {
+    enum Phase { INIT0, INIT1, REFLECT, EXPAND, CONTRACT_OUT, CONTRACT_IN, SHRINK, DONE };
+    static constexpr int MAXFUN = 200, MAXITER = 200;
+    static constexpr double XATOL = 1e-4, FATOL = 1e-4;
+    double s0 = 0., s1 = 0., f0 = INFINITY, f1 = INFINITY, x = 0., xr = 0., fxr = 0.;
+    int calls = 0, iterations = 0;
+    Phase phase = DONE;
+
+    static bool second_first(double a, double b) {      // np.argsort([a, b]) == [1, 0]
+        if (b != b) return false;
+        if (a != a) return true;
+        return b < a;
+    }
+    void sort() { if (second_first(f0, f1)) { std::swap(s0, s1); std::swap(f0, f1); } }
+    void start(double x0) {
+        s0 = x0;
+        s1 = x0 != 0. ? 1.05 * x0 : 0.00025;
+        f0 = f1 = INFINITY;
+        calls = 0;
+        iterations = 0;
+        request(INIT0, s0);
+    }
+    bool done() const { return phase == DONE; }
+    double next() const { return x; }
+    // an evaluation is due: out of budget ends the search the way the `aborted` path of the generator does
+    void request(Phase p, double at) {
+        if (calls >= MAXFUN) {
+            if (p != INIT0 && p != INIT1) sort();
+            phase = DONE;
+            return;
+        }
+        ++calls;
+        phase = p;
+        x = at;
+    }
+    void begin_iteration() {
+        if (!(calls < MAXFUN && iterations < MAXITER)) { phase = DONE; return; }
+        if (fabs(s1 - s0) <= XATOL && fabs(f0 - f1) <= FATOL) { phase = DONE; return; }
+        xr = 2 * s0 - 1 * s1;
+        request(REFLECT, xr);
+    }
+    void end_iteration() {
+        ++iterations;
+        sort();
+        begin_iteration();
+    }
+    void feed(double f) {
+        switch (phase) {
+        case INIT0: f0 = f; request(INIT1, s1); break;
+        case INIT1:
+            f1 = f;
+            sort();
+            iterations = 1;
+            begin_iteration();
+            break;
+        case REFLECT:
+            fxr = f;
+            if (fxr < f0) request(EXPAND, 3 * s0 - 2 * s1);
+            else if (fxr < f1) request(CONTRACT_OUT, 1.5 * s0 - 0.5 * s1);
+            else request(CONTRACT_IN, 0.5 * s0 + 0.5 * s1);
+            break;
+        case EXPAND:
+            if (f < fxr) { s1 = x; f1 = f; } else { s1 = xr; f1 = fxr; }
+            end_iteration();
+            break;
+        case CONTRACT_OUT:
+            if (f <= fxr) { s1 = x; f1 = f; end_iteration(); }
+            else { s1 = s0 + 0.5 * (s1 - s0); request(SHRINK, s1); }
+            break;
+        case CONTRACT_IN:
+            if (f < f1) { s1 = x; f1 = f; end_iteration(); }
+            else { s1 = s0 + 0.5 * (s1 - s0); request(SHRINK, s1); }
+            break;
+        case SHRINK: f1 = f; end_iteration(); break;
+        case DONE: break;
+        }
+    }
+};
+}  // namespace
+
+int rmx_mstep_param_search(rmx_handle m, const uint8_t* active, int scalar_id, double lo, double hi, const double* grid,
+                           int n_grid, double* result, int32_t* evals, int64_t* rounds, double* trace, int trace_cap) {
+    if (!m) return RMX_ERR_ARG;
+    Batch* b = m->b.get();
+    const int G = b->G;
+    if (m->g0 != 0 || m->gn != G) return m->fail(RMX_ERR_ARG, "the batched M-step works on the handle of the whole batch");
+    if (n_grid < 1 || n_grid > 32 || !grid || !result) return m->fail(RMX_ERR_ARG, "the grid holds 1 to 32 values");
+    if (scalar_id < 0 || scalar_id > RMX_S_BETABIN_LOH_M_1) return m->fail(RMX_ERR_ARG, "scalar_id must name a likelihood parameter");
+    std::vector<uint8_t> act(G), alive(G);
+    std::vector<double> vals((size_t)G * n_grid), ell((size_t)G * n_grid), J((size_t)G * n_grid, INFINITY);
+    std::vector<NelderMead1> nm(G);
+    int64_t n_rounds = 0, n_evals = 0;
+    int n_alive = 0;
+    for (int g = 0; g < G; ++g) { alive[g] = !active || active[g]; n_alive += alive[g]; if (evals) evals[g] = 0; }
+    // scipy.optimize.brute: the grid in ascending order; values outside the bounds are +inf and never assigned
+    std::vector<int> inside;
+    for (int i = 0; i < n_grid; ++i) if (!(grid[i] < lo || grid[i] > hi)) inside.push_back(i);
+    const int ni = (int)inside.size();
+    if (ni > 0 && n_alive > 0) {
+        for (int g = 0; g < G; ++g) for (int k = 0; k < ni; ++k) vals[(size_t)g * ni + k] = grid[inside[k]];
+        int rc = rmx_mstep_evaluate(m, alive.data(), nullptr, scalar_id, vals.data(), ni, ell.data(), nullptr);
+        if (rc) return rc;
+        for (int g = 0; g < G; ++g) if (alive[g]) for (int k = 0; k < ni; ++k) J[(size_t)g * n_grid + inside[k]] = -ell[(size_t)g * ni + k];
+        n_rounds += ni;
+        n_evals += (int64_t)ni * n_alive;
+    }
+    // fmin from the grid minimum (np.argmin: the first minimum, the first NaN if there is one)
+    int running = 0;
+    for (int g = 0; g < G; ++g) {
+        if (!alive[g]) continue;
+        const double* Jg = J.data() + (size_t)g * n_grid;
+        int best = 0;
+        for (int i = 0; i < n_grid; ++i) {
+            if (Jg[i] != Jg[i]) { best = i; break; }
+            if (Jg[i] < Jg[best]) best = i;
+        }
+        nm[g].start(grid[best]);
+        running += !nm[g].done();
+    }
+    std::vector<double> v1(G, 0.), e1(G, 0.);
+    while (running > 0) {
+        int n_act = 0;
+        for (int g = 0; g < G; ++g) {
+            act[g] = 0;
+            if (!alive[g] || nm[g].done()) continue;
+            const double x = nm[g].next();
+            if (!(x < lo || x > hi)) { act[g] = 1; v1[g] = x; ++n_act; }
+        }
+        if (n_act > 0) {
+            int rc = rmx_mstep_evaluate(m, act.data(), nullptr, scalar_id, v1.data(), 1, e1.data(), nullptr);
+            if (rc) return rc;
+            ++n_rounds;
+            n_evals += n_act;
+        }
+        running = 0;
+        for (int g = 0; g < G; ++g) {
+            if (!alive[g] || nm[g].done()) continue;
+            const double x = nm[g].next();
+            const double f = act[g] ? -e1[g] : INFINITY;
+            if (trace && evals && evals[g] < trace_cap) {
+                trace[((size_t)g * trace_cap + evals[g]) * 2] = x;
+                trace[((size_t)g * trace_cap + evals[g]) * 2 + 1] = f;
+            }
+            if (evals) ++evals[g];
+            nm[g].feed(f);
+            running += !nm[g].done();
+        }
+    }
+    for (int g = 0; g < G; ++g) result[g] = alive[g] ? nm[g].s0 : 0.;
+    if (rounds) { rounds[0] = n_rounds; rounds[1] = n_evals; }
+    return RMX_OK;
+}
+
 int rmx_set_scalar_array(rmx_handle m, int id, const uint8_t* active, const double* values) {
     if (!m) return RMX_ERR_ARG;
     Batch* b = m->b.get();

@@ -353,6 +353,9 @@ class BatchBackend(object):
     def evaluate(self, active=None, h=None, name=None, values=None, grad=False):
         return self.batch.mstep_evaluate(active=active, h=h, name=name, values=values, grad=grad)
 
+    def param_search(self, name, lo, hi, grid, active, trace=0):
+        return self.batch.mstep_param_search(name, lo, hi, grid, active=active, trace=trace)
+
 
 class ModelListBackend(object):
     """The same interface over G independent per-fit model objects (the compiled reference's ``RemixtModel``, the
@@ -544,6 +547,7 @@ class GridMStep(object):
     def __init__(self, backend, drivers, errors=None, lbfgsb='auto'):
         self.lbfgsb = lbfgsb    # 'auto' | 'coroutine' | 'threads'
         self.native_sampling = True
+        self.native_search = True   # update_param's brute + fmin inside the library (BatchBackend.param_search)
         self._full_cache = {}
         self._wbuf = {}         # reusable weight block of the native sampler (fresh pages cost more than the draws)
         self.be = backend
@@ -829,9 +833,17 @@ class GridMStep(object):
         t3 = time.perf_counter()
         self.seconds['stage'] += t3 - t2
 
+        grid = np.mgrid[slice(lo, hi, complex(20))]
+        if self.native_search and hasattr(be, 'param_search'):
+            # the same sequence of evaluations, driven by the library's host loop (no interpreter between rounds)
+            result, (rounds, evaluations) = be.param_search(name, lo, hi, grid, alive.astype(np.uint8))
+            self.rounds += rounds
+            self.evaluations += evaluations
+            self.seconds['param_search'] += time.perf_counter() - t3
+            self._accept_param(name, alive, value_before, ell_before, result)
+            return
         # scipy.optimize.brute: the grid, ascending, one call for all fits (values outside the bounds are inf and
         # are not assigned -- cn_model.py:541-543)
-        grid = np.mgrid[slice(lo, hi, complex(20))]
         inside = [float(v) for v in grid if not (v < lo or v > hi)]
         J = np.full((self.G, grid.shape[0]), np.inf)
         if inside:
@@ -870,13 +882,18 @@ class GridMStep(object):
             pending = nxt
         self.seconds['nelder_mead'] += time.perf_counter() - t4
 
+        self._accept_param(name, alive, value_before, ell_before, result)
+
+    def _accept_param(self, name, alive, value_before, ell_before, result):
+        """The acceptance test of ``update_param`` (``cn_model.py:561-569``): full-data E[LL] with the parameter as the
+        optimiser left it (its last evaluated value) against the value before."""
         ell_after = self._full_ell(alive)
         final = np.array(value_before)
         for g in np.flatnonzero(alive):
             rejected = ell_after[g] < ell_before[g]
             self.drivers[g].decisions.append((name, not rejected, float(ell_before[g]), float(ell_after[g])))
             final[g] = value_before[g] if rejected else result[g]
-        be.set_param(name, final, alive)
+        self.be.set_param(name, final, alive)
 
     # ------------------------------------------------------------------------------------------ one EM iteration
     def run(self):

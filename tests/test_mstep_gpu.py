@@ -169,3 +169,62 @@ def test_lockstep_and_per_fit_mstep_agree_on_gpu():
         assert np.array_equal(a[i]['cn'], b[i]['cn'])
         util.assert_close(a[i]['stats']['elbo'], b[i]['stats']['elbo'], rtol=1e-7, what='elbo')
         assert [d[1] for d in a[i]['decisions']] == [d[1] for d in b[i]['decisions']]
+
+
+def test_library_param_search_is_the_lockstep_python_search():
+    """rmx_mstep_param_search (brute grid + Nelder-Mead inside the library) against the same search driven by the
+    Python generators of mstep.py (which tests/test_mstep_cpu.py pins to scipy): same evaluation points and values in
+    the same order per fit, same optimum, the parameter left at the last evaluated value."""
+    from remixt_b200 import mstep
+    batch, drivers = _batch('small', [0, 7, 21, 40, 29])
+    G, N = batch.num_fits, batch.num_segments
+    rng = np.random.RandomState(11)
+    rows = np.stack([np.sort(rng.choice(N, 60, replace=False)) for _ in range(G)]).astype(np.int32)
+    batch.mstep_stage_rows(rows, np.full(G, 60))
+    alive = np.array([1, 1, 0, 1, 1], dtype=np.uint8)
+    for name in PARAMS4:
+        lo, hi = drivers[0].likelihood_param_bounds[name]
+        grid = np.mgrid[slice(lo, hi, complex(20))]
+        before = np.array(getattr(batch, name))
+        # Python generators on the same staged sample
+        J = -batch.mstep_evaluate(active=alive, name=name, values=np.broadcast_to(grid, (G, 20)))
+        expect, trace_py, last = {}, {}, {}
+        for g in np.flatnonzero(alive):
+            gen = mstep.neldermead_1d(float(grid[int(np.argmin(J[g]))]))
+            x, tr = next(gen), []
+            while True:
+                if x < lo or x > hi:
+                    f = np.inf
+                else:
+                    act = np.zeros(G, dtype=np.uint8)
+                    act[g] = 1
+                    f = -float(batch.mstep_evaluate(active=act, name=name, values=np.full((G, 1), x))[g, 0])
+                    last[g] = x
+                tr.append((x, f))
+                try:
+                    x = gen.send(f)
+                except StopIteration as stop:
+                    expect[g] = stop.value[0]
+                    break
+            trace_py[g] = np.array(tr)
+        batch.set_scalar_array(name, before)
+        result, (rounds, evaluations), traces = batch.mstep_param_search(name, lo, hi, grid, active=alive, trace=200)
+        after = np.array(getattr(batch, name))
+        for g in range(G):
+            if not alive[g]:
+                assert after[g] == before[g] and len(traces[g]) == 0
+                continue
+            assert np.array_equal(traces[g], trace_py[g]), (name, g)
+            assert result[g] == expect[g]
+            assert after[g] == last[g]
+        assert 20 < rounds <= 20 + max(len(t) for t in traces)
+        assert evaluations >= 20 * int(alive.sum())
+        batch.set_scalar_array(name, before)
+    # an upper bound below part of the grid: those values are +inf and never assigned
+    name = 'negbin_r_0'
+    lo, hi = drivers[0].likelihood_param_bounds[name]
+    grid = np.mgrid[slice(lo, hi, complex(20))]
+    cut = float(grid[6]) + 1.
+    result, stats, traces = batch.mstep_param_search(name, lo, cut, grid, trace=200)
+    assert np.all(result <= cut) and np.all(np.array(getattr(batch, name)) <= cut)
+    batch.close()
