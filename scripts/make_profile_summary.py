@@ -22,7 +22,8 @@ tag = sys.argv[1] if len(sys.argv) > 1 else 'r01'
 G = 'gpurun_out'
 P = 'profiles'
 os.makedirs(P, exist_ok=True)
-for f in ('%s_bench_config2.json', '%s_bench_reference.json', '%s_launches_config2.csv', '%s_pytest_gpu.log'):
+for f in ('%s_bench_config2.json', '%s_bench_reference.json', '%s_launches_config2.csv', '%s_pytest_gpu.log', '%s_smoke.log',
+          '%s_fullfit_parity.json', '%s_fullfit_time.log', '%s_noalloc_alone.log'):
     src = os.path.join(G, f % tag)
     if os.path.exists(src):
         shutil.copy(src, os.path.join(P, f % tag))
@@ -66,6 +67,8 @@ if os.path.exists(ref):
         r['value'], r['unit'], r['cpu_baseline']['cores'], r['cpu_baseline']['sample'], b['e2e']['value'] / r['value']))
 
 rep = os.path.join(G, '%s_top4.ncu-rep' % tag)
+if not os.path.exists(rep):
+    rep = os.path.join(G, '%s_top.ncu-rep' % tag)
 if os.path.exists(rep):
     raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
