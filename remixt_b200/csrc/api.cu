@@ -418,26 +418,52 @@ static int snapshot_spec(Model* m, int g0, int gn, bool cached) {
     return rc;
 }
 
-// likelihood table of the fits whose h / dispersions / masks changed since it was last built
-static int ensure_ll(Model* m, int g0, int gn) {
+// likelihood table of the fits whose h / dispersions / masks changed since it was last built (`only`, indexed by the
+// absolute fit, restricts the work to a subset; the others keep their stale planes until something needs them)
+static int ensure_ll(Model* m, int g0, int gn, const uint8_t* only = nullptr) {
     Batch* b = m->b.get();
     bool any = false;
-    for (int g = g0; g < g0 + gn; ++g) any |= b->ll_dirty[g] != 0;
+    for (int g = g0; g < g0 + gn; ++g) any |= b->ll_dirty[g] != 0 && (!only || only[g]);
     if (!any) return RMX_OK;
     int rc = push_params(m);
     if (rc) return rc;
     RmxTables T = tables(b);
-    // ll_dirty[g] holds the term groups whose parameters changed (planes_of): a run of fits with the same groups is
-    // one launch that rebuilds those planes only (fast path; the general kernel rebuilds all)
+    RmxFast Fp;
+    Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag; Fp.segf = b->segf;
+    // ll_dirty[g] holds the term groups whose parameters changed (planes_of); only those planes are rebuilt (fast
+    // path; the general kernel rebuilds all).  Up to RMX_SEL_MAX fits: ONE launch sequence over the list of stale
+    // fits, each with its own groups.  Larger batches: one launch sequence per run of fits with the same groups.
+    if (b->fast_ll && b->G <= RMX_SEL_MAX) {
+        RmxFitSel sel;
+        sel.n = 0;
+        for (int g = g0; g < g0 + gn; ++g)
+            if (b->ll_dirty[g] && (!only || only[g])) {
+                sel.fit[sel.n] = (unsigned char)g;
+                sel.planes[sel.n] = (unsigned char)b->ll_dirty[g];
+                ++sel.n;
+            }
+        rmx_launch_segconst(b->stream, T, b->d, b->dP, 0, sel.n, nullptr, nullptr, b->d.N, b->segc, b->segk, 0, &sel);
+        cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE);
+        rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, 0, sel.n, b->segc, Fp, b->LL, b->dflags, 0, &sel);
+        b->tend(te_);
+        b->count(4);
+        for (int k = 0; k < sel.n; ++k) {
+            b->asum_dirty[sel.fit[k]] |= (char)sel.planes[k];
+            b->ll_dirty[sel.fit[k]] = 0;
+        }
+        return RMX_OK;
+    }
     std::vector<int> key(b->G, 0);
-    for (int g = g0; g < g0 + gn; ++g) key[g] = b->fast_ll ? (int)b->ll_dirty[g] : (b->ll_dirty[g] ? 15 : 0);
-    for_runs(g0, gn, key, &b->ll_dirty, [&](int g, int n) {
+    std::vector<char> need(b->G, 0);
+    for (int g = g0; g < g0 + gn; ++g) {
+        need[g] = b->ll_dirty[g] != 0 && (!only || only[g]);
+        key[g] = b->fast_ll ? (int)b->ll_dirty[g] : (b->ll_dirty[g] ? 15 : 0);
+    }
+    for_runs(g0, gn, key, &need, [&](int g, int n) {
         const int pm = key[g];
         rmx_launch_segconst(b->stream, T, b->d, b->dP, g, n, nullptr, nullptr, b->d.N, b->segc, b->segk, pm);
         cudaEvent_t te_ = b->tbegin(RMX_K_LLTABLE);
         if (b->fast_ll) {
-            RmxFast Fp;
-            Fp.nkind = b->nkind; Fp.kind_nrm = b->kind_nrm; Fp.Q = b->Q; Fp.logw = b->logw; Fp.stab = b->stab; Fp.sflag = b->sflag; Fp.segf = b->segf;
             rmx_launch_lltable2(b->stream, b->sm_count, T, b->d, b->dP, g, n, b->segc, Fp, b->LL, b->dflags, pm);
             b->count(2);
         } else {
@@ -451,13 +477,28 @@ static int ensure_ll(Model* m, int g0, int gn) {
 }
 
 // posterior-weighted likelihood sums of the fits whose posterior or likelihood table changed
-static int ensure_asum(Model* m, int g0, int gn) {
+static int ensure_asum(Model* m, int g0, int gn, const uint8_t* only = nullptr) {
     Batch* b = m->b.get();
-    int rc = ensure_ll(m, g0, gn);
+    int rc = ensure_ll(m, g0, gn, only);
     if (rc) return rc;
+    if (b->G <= RMX_SEL_MAX) {
+        RmxFitSel sel;
+        sel.n = 0;
+        for (int g = g0; g < g0 + gn; ++g)
+            if (b->asum_dirty[g] && (!only || only[g])) {
+                sel.fit[sel.n] = (unsigned char)g;
+                sel.planes[sel.n] = (unsigned char)b->asum_dirty[g];
+                ++sel.n;
+            }
+        if (sel.n == 0) return RMX_OK;
+        { cudaEvent_t te_ = b->tbegin(RMX_K_QSUMS); rmx_launch_qsums(b->stream, b->d, 0, sel.n, b->LL, b->post, b->Asum, 0, &sel); b->tend(te_); }
+        b->count();
+        for (int k = 0; k < sel.n; ++k) b->asum_dirty[sel.fit[k]] = 0;
+        return RMX_OK;
+    }
     std::vector<int> key(b->G, 0);
     std::vector<char> need(b->G, 0);
-    for (int g = g0; g < g0 + gn; ++g) { need[g] = b->asum_dirty[g] != 0; key[g] = b->asum_dirty[g]; }
+    for (int g = g0; g < g0 + gn; ++g) { need[g] = b->asum_dirty[g] != 0 && (!only || only[g]); key[g] = b->asum_dirty[g]; }
     for_runs(g0, gn, key, &need, [&](int g, int n) {
         { cudaEvent_t te_ = b->tbegin(RMX_K_QSUMS); rmx_launch_qsums(b->stream, b->d, g, n, b->LL, b->post, b->Asum, key[g]); b->tend(te_); }
         b->count();
@@ -2126,18 +2167,7 @@ int rmx_mstep_evaluate(rmx_handle m, const uint8_t* active, const double* h_valu
             // every segment: the likelihood table of the fits whose parameters changed (the kernel of the E-step,
             // which the next E-step then finds ready), its posterior-weighted sums, and one value per segment
             // (fits outside the active set keep their stale table until something needs it)
-            int rc = RMX_OK;
-            for (int g = 0; g < G && !rc;) {
-                if (active && !active[g]) { ++g; continue; }
-                int e = g + 1;
-                while (e < G && (!active || active[e])) ++e;
-                Model run = *m;
-                run.g0 = g;
-                run.gn = e - g;
-                rc = ensure_asum(&run, g, e - g);
-                if (rc) m->err = run.err;
-                g = e;
-            }
+            int rc = ensure_asum(m, 0, G, active);
             if (rc) return rc;
             double* rowe = b->rowv + 7 * (size_t)b->d.N;
             rmx_launch_ell_rows_from_sums(b->stream, b->d, 0, G, b->Asum, b->q_ot, b->q_oa, b->q_sw, rowe, (int64_t)8 * b->d.N);

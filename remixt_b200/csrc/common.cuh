@@ -48,6 +48,18 @@ struct RmxParams {
 // fit index as its leading dimension.
 #define RMX_FIT() (g0 + (int)blockIdx.y)
 
+// Some launches address an explicit LIST of fits instead (blockIdx.y -> list entry), each fit with its own mask of
+// likelihood term groups: the full-data evaluations of the M-step touch whichever fits have stale table planes, and
+// one launch per maximal run of equal masks fragments into tens of small launches.  n == 0: the range form above.
+#define RMX_SEL_MAX 256
+struct RmxFitSel {
+    int n;
+    unsigned char fit[RMX_SEL_MAX];
+    unsigned char planes[RMX_SEL_MAX];
+};
+#define RMX_FIT_SEL(sel) ((sel).n ? (int)(sel).fit[blockIdx.y] : g0 + (int)blockIdx.y)
+#define RMX_PLANES_SEL(sel, all_) ((sel).n ? (int)(sel).planes[blockIdx.y] : (all_))
+
 // Read-only tables in HBM, shared by every fit of a batch (the fits of an initialisation grid see the
 // same data and state space; only h, the dispersions, divergence_weight and the variational state differ).
 struct RmxTables {

@@ -42,7 +42,7 @@ struct RmxChains {
 // ---- likelihood.cu   (every launcher covers the fits [g0, g0+gn) of a batch; P is the per-fit parameter array)
 void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                          const int* rows_all, const int* Rn, int Rmax, double* segc, const double* segk = nullptr,
-                         int planes = 15);
+                         int planes = 15, const RmxFitSel* sel = nullptr);
 // per-segment data-only constants (N,3) the full-table form of the above reuses
 void rmx_launch_segk(cudaStream_t st, const RmxTables& T, const RmxDims& d, double* segk);
 void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
@@ -50,12 +50,13 @@ void rmx_launch_lltable(cudaStream_t st, int sm_count, const RmxTables& T, const
 // fast path (per-state tables + wide log table); rmx_lltable2_ok says whether the shape fits its shared memory
 int rmx_lltable2_ok(const RmxDims& d, int Q);
 void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
-                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes = 15);
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes = 15,
+                         const RmxFitSel* sel = nullptr);
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* q_ot, const double* q_oa, const double* q_sw, double* F,
                       double* fexp, double* mF, int* dflags);
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
-                      double* A, int planes = 15);
+                      double* A, int planes = 15, const RmxFitSel* sel = nullptr);
 // post + qsums + outlier updates (+ next round's swap update and frame) in one pass; S <= 128
 int rmx_round_ok(const RmxDims& d);
 void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,

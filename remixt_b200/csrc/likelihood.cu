@@ -201,8 +201,9 @@ __global__ void __launch_bounds__(256, 3) k_lltable(RmxTables T, RmxDims d, cons
 // stab layout per fit: [field f in 0..8)[kind q][state s]; sflag per fit: [q][s], bit 0 total ok, bit 1 allele ok.
 // ---------------------------------------------------------------------------------------------
 #define ST_NF 8
-__global__ void k_statetab(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0, RmxFast Fp) {
-    const int g = RMX_FIT();
+__global__ void k_statetab(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0, RmxFast Fp,
+                           const __grid_constant__ RmxFitSel sel) {
+    const int g = RMX_FIT_SEL(sel);
     const int QS = Fp.Q * d.S;
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= QS) return;
@@ -254,8 +255,8 @@ __device__ __noinline__ void ll_slow(const RmxTables& T, const RmxDims& d, const
 //   path, bits 8.. normal-copy kind
 #define LLT2_SEGW 12
 __global__ void k_segfast(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
-                          const double* __restrict__ segc_all, RmxFast Fp) {
-    const int g = RMX_FIT();
+                          const double* __restrict__ segc_all, RmxFast Fp, const __grid_constant__ RmxFitSel sel) {
+    const int g = RMX_FIT_SEL(sel);
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= d.N) return;
     const RmxParams& P = Pg[g];
@@ -284,7 +285,8 @@ __global__ void k_segfast(RmxTables T, RmxDims d, const RmxParams* __restrict__ 
 // 97 consecutive units of the segment, so L1 hits after the first touch) and warps proceed independently.
 __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                    const double* __restrict__ segc_all, RmxFast Fp,
-                                                   double* __restrict__ LL_all, int* __restrict__ dflags, int planes) {
+                                                   double* __restrict__ LL_all, int* __restrict__ dflags, int planes_all,
+                                                   const __grid_constant__ RmxFitSel sel) {
     // planes: which term groups to (re)build -- bit u: total-read term u; bit 2 + v: the two allele terms of v.  The
     // M-step changes one dispersion at a time, and each enters one group only; the other planes of the table stand.
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -294,7 +296,8 @@ __global__ void __launch_bounds__(256, 3) k_lltable2(RmxTables T, RmxDims d, con
     double* st = reinterpret_cast<double*>(lw + RMX_LW_SIZE);                   // [ST_NF][QS]
     uint8_t* sfl = reinterpret_cast<uint8_t*>(st + (size_t)ST_NF * QS);         // [QS]
     const int t = threadIdx.x;
-    const int g = RMX_FIT();
+    const int g = RMX_FIT_SEL(sel);
+    const int planes = RMX_PLANES_SEL(sel, planes_all);
     for (int e = t; e < RMX_LW_SIZE; e += blockDim.x) lw[e] = Fp.logw[e];
     {
         const double* sg = Fp.stab + (int64_t)g * ST_NF * QS;
@@ -478,10 +481,12 @@ __device__ __forceinline__ void exp_normalize2(double a, double b, double* out) 
 // sufficient statistic of all three 2-way factor updates and of the ELBO's likelihood terms.
 // One warp per (fit, segment); one pass over post + the six LL planes (56 B per (n,s)).
 __global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* __restrict__ LL_all,
-                                               const double* __restrict__ post_all, double* __restrict__ A_all, int planes) {
+                                               const double* __restrict__ post_all, double* __restrict__ A_all, int planes_all,
+                                               const __grid_constant__ RmxFitSel sel) {
     int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= d.N) return;
-    const int g = RMX_FIT();
+    const int g = RMX_FIT_SEL(sel);
+    const int planes = RMX_PLANES_SEL(sel, planes_all);
     const int n = warp;
     const int64_t NS = (int64_t)d.N * d.S;
     const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS;
@@ -860,8 +865,10 @@ __device__ __forceinline__ void segconst_row_cached(const RmxParams& P, double x
 // are recomputed -- 2 to 8 lgamma per segment instead of 20.
 __global__ void k_segconst_rows(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                 const int* __restrict__ rows_all, const int* __restrict__ Rn,
-                                double* __restrict__ segc_all, const double* __restrict__ segk, int planes) {
-    const int g = RMX_FIT();
+                                double* __restrict__ segc_all, const double* __restrict__ segk, int planes_all,
+                                const __grid_constant__ RmxFitSel sel) {
+    const int g = RMX_FIT_SEL(sel);
+    const int planes = RMX_PLANES_SEL(sel, planes_all);
     const int R = rows_all ? Rn[g] : d.N;
     int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= R) return;
@@ -1246,10 +1253,14 @@ void rmx_launch_fill2(cudaStream_t st, double* out, int64_t n, double v0, double
     k_fill2<<<(int)(want < 148 * 16 ? want : 148 * 16), 256, 0, st>>>(out, n, v0, v1);
 }
 
+static const RmxFitSel g_no_sel = {};      // n == 0: the launch addresses the range [g0, g0 + gn)
+
 void rmx_launch_segconst(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
-                         const int* rows_all, const int* Rn, int Rmax, double* segc, const double* segk, int planes) {
+                         const int* rows_all, const int* Rn, int Rmax, double* segc, const double* segk, int planes,
+                         const RmxFitSel* sel) {
     if (Rmax <= 0 || gn <= 0) return;
-    k_segconst_rows<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, P, g0, rows_all, Rn, segc, segk, planes);
+    k_segconst_rows<<<dim3(cdiv(Rmax, 128), gn), 128, 0, st>>>(T, d, P, g0, rows_all, Rn, segc, segk, planes,
+                                                               sel ? *sel : g_no_sel);
 }
 void rmx_launch_segk(cudaStream_t st, const RmxTables& T, const RmxDims& d, double* segk) {
     if (d.N <= 0) return;
@@ -1275,12 +1286,14 @@ static size_t lltable2_smem(const RmxDims& d, int Q) {
 int rmx_lltable2_ok(const RmxDims& d, int Q) { return lltable2_smem(d, Q) <= 72 * 1024; }
 
 void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0,
-                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes) {
+                         int gn, const double* segc, const RmxFast& Fp, double* LL, int* dflags, int planes,
+                         const RmxFitSel* selp) {
     int64_t NS = (int64_t)d.N * d.S;
     if (NS <= 0 || gn <= 0) return;
     const int QS = Fp.Q * d.S;
-    k_statetab<<<dim3(cdiv(QS, 128), gn), 128, 0, st>>>(T, d, P, g0, Fp);
-    k_segfast<<<dim3(cdiv(d.N, 128), gn), 128, 0, st>>>(T, d, P, g0, segc, Fp);
+    const RmxFitSel& sel = selp ? *selp : g_no_sel;
+    k_statetab<<<dim3(cdiv(QS, 128), gn), 128, 0, st>>>(T, d, P, g0, Fp, sel);
+    k_segfast<<<dim3(cdiv(d.N, 128), gn), 128, 0, st>>>(T, d, P, g0, segc, Fp, sel);
     int64_t want = (NS + 255) / 256;
     int64_t cap = ((int64_t)sm_count * 12 + gn - 1) / gn;   // whole grid sized in multiples of the SM count
     if (cap < 1) cap = 1;
@@ -1289,7 +1302,7 @@ void rmx_launch_lltable2(cudaStream_t st, int sm_count, const RmxTables& T, cons
     if (attr_once.need()) {
         cudaFuncSetAttribute(k_lltable2, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
     }
-    k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags, planes);
+    k_lltable2<<<dim3(grid, gn), 256, lltable2_smem(d, Fp.Q), st>>>(T, d, P, g0, segc, Fp, LL, dflags, planes, sel);
 }
 
 void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
@@ -1306,9 +1319,9 @@ void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, con
 }
 
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
-                      double* A, int planes) {
+                      double* A, int planes, const RmxFitSel* sel) {
     if (d.N <= 0 || gn <= 0) return;
-    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A, planes);
+    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A, planes, sel ? *sel : g_no_sel);
 }
 
 int rmx_round_ok(const RmxDims& d) { return d.S <= 128; }

@@ -547,6 +547,7 @@ class GridMStep(object):
     def __init__(self, backend, drivers, errors=None, lbfgsb='auto'):
         self.lbfgsb = lbfgsb    # 'auto' | 'coroutine' | 'threads'
         self.native_sampling = True
+        self.overlap_sampling = True
         self.native_search = True   # update_param's brute + fmin inside the library (BatchBackend.param_search)
         self._full_cache = {}
         self._wbuf = {}         # reusable weight block of the native sampler (fresh pages cost more than the draws)
@@ -569,7 +570,7 @@ class GridMStep(object):
         rs = d.random_state if d.random_state is not None else np.random
         return rs.choice(N, size=size, replace=False, p=weights)
 
-    def _draw_samples(self, plan):
+    def _draw_samples(self, plan, alive=None, timed=True):
         """The segment samples of one EM iteration, ``{step: (rows (G, size), counts (G))}``.  Every sample is a function of the
         E-step's q-factors and of the fit's random stream alone (nothing the M-step changes), so they are all drawn
         up front -- per fit in the reference's order h, then each parameter, which is what keeps every stream
@@ -578,7 +579,7 @@ class GridMStep(object):
         error at the step that would have raised it."""
         t0 = time.perf_counter()
         be = self.be
-        alive = np.flatnonzero(self._alive())
+        alive = np.flatnonzero(self._alive() if alive is None else alive)
         shared_stream = any(self.drivers[g].random_state is None for g in alive)
 
         def draw(g):
@@ -597,9 +598,10 @@ class GridMStep(object):
             # weights on the calling thread (they read the backend), the draws on the library's host threads
             size = int(min(200, be.num_segments / 10))
             D, A, N = len(plan), len(alive), be.num_segments
-            if self._wbuf.get('shape') != (D, A, N):
-                self._wbuf['shape'], self._wbuf['w'] = (D, A, N), np.empty((D, A, N), dtype=np.float64)
-            w, flags = self._wbuf['w'], np.zeros((D, A), dtype=np.uint8)
+            weighted = any(step != 'h' for step in plan)
+            if weighted and (D, A, N) not in self._wbuf:
+                self._wbuf[(D, A, N)] = np.empty((D, A, N), dtype=np.float64)
+            w, flags = self._wbuf.get((D, A, N)) if weighted else None, np.zeros((D, A), dtype=np.uint8)
             def fill(d):
                 step = plan[d]
                 if step == 'h':
@@ -620,8 +622,9 @@ class GridMStep(object):
             else:
                 for d in range(D):
                     fill(d)
-            chosen, status = native_choice([self.drivers[g].random_state for g in alive], N, size, [None] * D,
-                                           block=(w, flags))
+            chosen, status = native_choice([self.drivers[g].random_state for g in alive], N, size,
+                                           [None] * D if weighted else [[None] * A] * D,
+                                           block=(w, flags) if weighted else None)
             drawn = []
             for k in range(len(alive)):
                 out = []
@@ -647,7 +650,8 @@ class GridMStep(object):
                     # ascending, as the rows of the reference's 0/1 sample mask are visited (bpmodel.pyx:1137)
                     samples[step][0][g] = np.sort(chosen)
                     samples[step][1][g] = size
-        self.seconds['sample'] += time.perf_counter() - t0
+        if timed:
+            self.seconds['sample'] += time.perf_counter() - t0
         return samples, failed
 
     def _evaluate(self, **kw):
@@ -905,8 +909,23 @@ class GridMStep(object):
         t0 = time.perf_counter()
         self.be.prefetch(plan)
         self.seconds['weights'] += time.perf_counter() - t0
-        samples = self._draw_samples(plan)
-        if d0.do_h_update:
-            self.update_h(samples)
+        # the parameters' samples depend on the E-step's q-factors (read above) and on the fits' random streams only:
+        # they are drawn on a host thread while update_h runs, after h's own draw (each stream keeps its order)
+        standard = ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')
+        if (self.overlap_sampling and self.native_sampling and d0.do_h_update and len(plan) > 1 and
+                hasattr(self.be, 'weights_block') and all(p in standard for p in plan[1:])):
+            import concurrent.futures
+            samples = self._draw_samples(['h'])
+            alive = self._alive()
+            with concurrent.futures.ThreadPoolExecutor(1) as pool:
+                rest = pool.submit(self._draw_samples, plan[1:], alive, False)
+                self.update_h(samples)
+                t1 = time.perf_counter()
+                samples = rest.result()
+                self.seconds['sample'] += time.perf_counter() - t1
+        else:
+            samples = self._draw_samples(plan)
+            if d0.do_h_update:
+                self.update_h(samples)
         for name in d0.likelihood_params:
             self.update_param(name, samples)
