@@ -190,6 +190,7 @@ struct Batch {
     bool is_shard = false;
     uint8_t* bc_tab = nullptr;   // states grouped by tumour-clone totals: [perm (4 KBB)][kbcls (KBB)][scls (S)][didx (BC,BC)][ddel (ND,M)]
     int BC = 0, KBB = 0, ND = 0;
+    uint16_t* bc_didx16 = nullptr;   // the same (BC,BC) table with 16-bit entries (more than 255 difference tuples: chain_mma3.cu)
     uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
     int* hgstart = nullptr;
     int Q = 0;
@@ -617,6 +618,9 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
                  ? 2
                  : rmx_launch_chain_mma2(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp, b->mF,
                                          b->ahat, b->bhat, b->chain_logz, b->dflags, b->bc_tab, b->BC, b->KBB, b->ND);
+        if (lc == 2 && !force_streamed && !force_v1)      // 129 .. 168 states: matrix split between registers and shared memory
+            lc = rmx_launch_chain_mma3(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp, b->mF,
+                                       b->ahat, b->bhat, b->chain_logz, b->dflags, b->bc_tab, b->bc_didx16, b->BC, b->KBB, b->ND);
         if (lc == 2 && !force_streamed)
             lc = rmx_launch_chain_mma(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp,
                                       b->mF, b->ahat, b->bhat, b->chain_logz, b->dflags);
@@ -1022,6 +1026,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
             // the distinct tuples of per-clone total differences between two classes, and which one each pair is
             std::vector<std::vector<int>> dels;
             std::vector<uint8_t> didx(keys.size() * keys.size());
+            std::vector<uint16_t> didx16(keys.size() * keys.size());
             for (size_t ci = 0; ci < keys.size(); ++ci)
                 for (size_t cj = 0; cj < keys.size(); ++cj) {
                     std::vector<int> del(M, 0);
@@ -1030,6 +1035,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
                     while (q < dels.size() && dels[q] != del) ++q;
                     if (q == dels.size()) dels.push_back(del);
                     didx[ci * keys.size() + cj] = (uint8_t)(q < 255 ? q : 255);
+                    didx16[ci * keys.size() + cj] = (uint16_t)(q < 65535 ? q : 65535);
                 }
             std::vector<uint8_t> bc(perm);
             bc.insert(bc.end(), kbcls.begin(), kbcls.end());
@@ -1041,6 +1047,7 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
             b->BC = (int)keys.size();
             b->KBB = (int)kbcls.size();
             CCK(upload(b, &b->bc_tab, bc));
+            CCK(upload(b, &b->bc_didx16, didx16));
         }
     }
     if (b->C <= 254 && b->R < (1 << 19) && d0_fits) {     // packed row info of the one-barrier chain kernels
