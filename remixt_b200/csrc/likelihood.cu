@@ -526,7 +526,7 @@ __global__ void __launch_bounds__(256) k_qsums(RmxDims d, int g0, const double* 
 // 144 of the four separate passes.  Expressions and summation orders are the separate kernels' (results agree with
 // the unfused sequence to the last bits; FMA contraction may differ).  KS = ceil(S / 32).
 template <int KS>
-__global__ void __launch_bounds__(256, 3) k_round(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+__global__ void __launch_bounds__(256, KS <= 4 ? 3 : 2) k_round(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                const double* __restrict__ LL_all, const double* __restrict__ ahat_all,
                                                const double* __restrict__ bhat_all, double* __restrict__ post_all,
                                                double* __restrict__ A_all, double* __restrict__ q_ot_all,
@@ -1324,7 +1324,7 @@ void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const d
     k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A, planes, sel ? *sel : g_no_sel);
 }
 
-int rmx_round_ok(const RmxDims& d) { return d.S <= 128; }
+int rmx_round_ok(const RmxDims& d) { return d.S <= 192; }
 
 void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxParams* P, int g0, int gn,
                       const double* LL, const double* ahat, const double* bhat, double* post, double* A, double* q_ot,
@@ -1338,7 +1338,8 @@ void rmx_launch_round(cudaStream_t st, const RmxTables& T, const RmxDims& d, con
     if (ks <= 1) RMX_ROUND(1);
     else if (ks == 2) RMX_ROUND(2);
     else if (ks == 3) RMX_ROUND(3);
-    else RMX_ROUND(4);
+    else if (ks == 4) RMX_ROUND(4);
+    else RMX_ROUND(6);       // 129 .. 192 states (max copy number 8: S = 165), two CTAs per SM
 #undef RMX_ROUND
 }
 
