@@ -49,6 +49,7 @@ __device__ __forceinline__ void ll_core(const int8_t* __restrict__ tab, const Rm
         const double lmu = plain ? rmx_log(mu, ltab) : 0.;
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
+            if (!((planes >> u) & 1)) { ll[u] = 0.; continue; }
             double rr = hd ? P.negbin_hdel_r[u] : P.negbin_r[u];
             double v;
             if (plain) {
@@ -815,6 +816,7 @@ __device__ __forceinline__ void segconst_row(const RmxParams& P, double x, doubl
 }
 
 #define RMX_ELL_CHUNKS 16
+#define RMX_ELL_PF 7             // posterior entries a thread of k_ell_sample fetches ahead (16 rows x 97 states / 256)
 #define RMX_ELL_MAXROWS 16       // rows per chunk held in shared memory (256 sampled rows per fit)
 // The parameter-independent part of those constants for the staged sample rows of the batched M-step, computed once
 // per sample: rowc[(g * 256 + r) * 3 + {0,1,2}] = lgamma(x+1), and the two log binomial coefficients.
@@ -895,7 +897,7 @@ __global__ void k_segk(RmxTables T, RmxDims d, double* __restrict__ segk) {
 // host round trip): CTA (chunk c, fit g) takes a contiguous sixteenth of the fit's sample rows, computes their hoisted
 // constants into shared memory, sums post * q * LL over (row, state) in a fixed order and writes ONE partial;
 // the host adds the RMX_ELL_CHUNKS partials of a fit in order.  `planes` as in ll_core.
-__global__ void __launch_bounds__(256) k_ell_sample(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
+__global__ void __launch_bounds__(256, 3) k_ell_sample(RmxTables T, RmxDims d, const RmxParams* __restrict__ Pg, int g0,
                                                     const int* __restrict__ rows_all, const int* __restrict__ Rn,
                                                     const double* __restrict__ post_all,
                                                     const double* __restrict__ q_ot_all, const double* __restrict__ q_oa_all,
@@ -916,6 +918,19 @@ __global__ void __launch_bounds__(256) k_ell_sample(RmxTables T, RmxDims d, cons
     const int nr = max(0, min(per, R - r0));
     const RmxParams& P = Pg[g];
     const bool tab_sm = d.S <= 128;
+    // this thread's posterior entries first: two dependent global loads each (row list, then the posterior), in flight
+    // under the set-up below instead of inside the unit loop (up to RMX_ELL_PF units; further ones load in the loop)
+    const int units = nr * d.S;
+    double ppf[RMX_ELL_PF];
+#pragma unroll
+    for (int k = 0; k < RMX_ELL_PF; ++k) {
+        const int idx = threadIdx.x + k * 256;
+        ppf[k] = 0.;
+        if (idx < units) {
+            const int r = idx / d.S, s = idx - r * d.S;
+            ppf[k] = post_all[((int64_t)g * d.N + rows_all[(int64_t)g * d.N + r0 + r]) * d.S + s];
+        }
+    }
     if (tab_sm)
         for (int e = threadIdx.x; e < d.S * d.M * 2; e += blockDim.x) stab[e] = T.tab[e];
     if ((int)threadIdx.x < nr) {
@@ -941,12 +956,19 @@ __global__ void __launch_bounds__(256) k_ell_sample(RmxTables T, RmxDims d, cons
     rmx_logtab_init(ltab);      // includes the barrier
     double acc[1] = {0.};
     int flags = 0;
-    const int units = nr * d.S;
     const int8_t* tab = tab_sm ? stab : T.tab;
-    for (int idx = threadIdx.x; idx < units; idx += blockDim.x) {
+    int kpf = 0;
+    for (int idx = threadIdx.x; idx < units; idx += blockDim.x, ++kpf) {
         const int r = idx / d.S, s = idx - r * d.S;
         const int n = rown[r], ri = rowi[r];
-        const double p = post_all[((int64_t)g * d.N + n) * d.S + s];
+        double p;
+        if (kpf < RMX_ELL_PF) {
+            p = ppf[0];
+#pragma unroll
+            for (int k = 1; k < RMX_ELL_PF; ++k) p = kpf == k ? ppf[k] : p;
+        } else {
+            p = post_all[((int64_t)g * d.N + n) * d.S + s];
+        }
         SegIn in;
         in.segc = segc + r;
         in.sstride = RMX_ELL_MAXROWS;
