@@ -189,15 +189,20 @@ def lbfgsb_coroutine(x0, bounds, maxcor=10, ftol=2.220446049250313e-09, gtol=1e-
     held_g = np.atleast_1d(held_g)
     nfev = 1
     n_iterations = 0
+    held_key = held_x.tobytes()
+    setulb = _lbfgsb.setulb
     while True:
-        g = g.astype(np.float64)
-        _lbfgsb.setulb(m, x, low_bnd, upper_bnd, nbd, f, g, factr, gtol, wa, iwa, task, lsave, isave, dsave, maxls,
-                       ln_task)
+        if g.dtype != np.float64:
+            g = g.astype(np.float64)
+        setulb(m, x, low_bnd, upper_bnd, nbd, f, g, factr, gtol, wa, iwa, task, lsave, isave, dsave, maxls, ln_task)
         if task[0] == 3:
-            if not np.array_equal(x, held_x):
-                held_x = np.array(x, dtype=float)
+            key = x.tobytes()
+            if key != held_key and not np.array_equal(x, held_x):   # bytes differ and values differ (-0. == 0.)
+                held_x = x.copy()
+                held_key = key
                 held_f, held_g = yield held_x.copy()
-                held_g = np.atleast_1d(held_g)
+                if getattr(held_g, 'ndim', 0) != 1:
+                    held_g = np.atleast_1d(held_g)
                 nfev += 1
             f, g = held_f, held_g
         elif task[0] == 1:
