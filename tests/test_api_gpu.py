@@ -124,7 +124,7 @@ sys.path.insert(0, %(root)r)
 from remixt_b200 import pipeline, simulate
 exp = simulate.simulate_experiment(dict(N=9000, chromosome_lengths={'1': 249250621}, num_ancestral_events=40,
                                         num_descendent_events=15, num_false_breakpoints=10, random_seed=11))
-cfg = {'max_copy_number': 6, 'max_ploidy': 5.0}
+cfg = {'max_copy_number': %(cnmax)d, 'max_ploidy': 5.0}
 grid = pipeline.init(exp, cfg)
 bm = pipeline.build_model(exp, grid[0], cfg)
 bm.prepare(pipeline.init_h(grid[0]))
@@ -146,13 +146,30 @@ def test_long_chain_same_result_on_every_kernel_path(tmp_path):
         path = str(tmp_path / (tag + '.npz'))
         e = dict(os.environ)
         e.update(env)
-        subprocess.check_call([sys.executable, '-c', _PATH_SCRIPT % dict(root=util.ROOT), path], env=e)
+        subprocess.check_call([sys.executable, '-c', _PATH_SCRIPT % dict(root=util.ROOT, cnmax=6), path], env=e)
         outs[tag] = np.load(path)
     for tag in ('v1', 'streamed'):
         util.assert_close(outs['v2']['elbo'], outs[tag]['elbo'], rtol=1e-10, what='elbo ' + tag)
         util.assert_close(outs['v2']['post'], outs[tag]['post'], rtol=1e-7, atol=1e-12, what='post ' + tag)
         util.assert_close(outs['v2']['pb'], outs[tag]['pb'], rtol=1e-7, atol=1e-12, what='p_breakpoint ' + tag)
         assert np.array_equal(outs['v2']['cn'], outs[tag]['cn'])
+
+
+def test_long_chain_165_states_tensor_path_vs_streamed(tmp_path):
+    """The same chromosome at max copy number 8 (S = 165): chain_mma3.cu (class matrix split between registers and
+    shared memory; the chain is longer than ITS row-descriptor cache of 4096 rows) against the L2-streamed kernel."""
+    outs = {}
+    for tag, env in (('v3', {}), ('streamed', {'RMX_CHAIN_STREAMED': '1'})):
+        path = str(tmp_path / (tag + '.npz'))
+        e = dict(os.environ)
+        e.update(env)
+        subprocess.check_call([sys.executable, '-c', _PATH_SCRIPT % dict(root=util.ROOT, cnmax=8), path], env=e)
+        outs[tag] = np.load(path)
+    assert outs['v3']['post'].shape[1] == 165
+    util.assert_close(outs['v3']['elbo'], outs['streamed']['elbo'], rtol=1e-10, what='elbo')
+    util.assert_close(outs['v3']['post'], outs['streamed']['post'], rtol=1e-7, atol=1e-12, what='post')
+    util.assert_close(outs['v3']['pb'], outs['streamed']['pb'], rtol=1e-7, atol=1e-12, what='p_breakpoint')
+    assert np.array_equal(outs['v3']['cn'], outs['streamed']['cn'])
 
 
 def test_reference_cn_model_drives_this_bpmodel():
