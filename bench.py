@@ -86,6 +86,9 @@ DERIVED = {
     # BASELINE config 3: the config-2 genome with max copy number 8 (S = 165 states for 2 tumour clones + normal);
     # its initialisation grid comes from this repo's pipeline.init (the reference's grid builder, tests/test_init_results.py)
     'config3': ('config2', {'max_copy_number': 8, 'max_ploidy': 4.0}),
+    # the reference's DEFAULT max_copy_number (analysis/pipeline.py defaults: 12 -> S = 355 states): above every
+    # tensor-path chain kernel and above k_hist2 -- the L2-streamed chain kernel and the first-generation histograms
+    'cn12': ('config2', {'max_copy_number': 12, 'max_ploidy': 4.0}),
 }
 
 

@@ -248,7 +248,8 @@ PARAMS4 = ('negbin_r_0', 'negbin_r_1', 'betabin_M_0', 'betabin_M_1')
 
 
 def _grid_fit_one(job):
-    name, init_id, em, vi, seed, h_scale = job
+    name, init_id, em, vi, seed, h_scale = job[:6]
+    extra = job[6] if len(job) > 6 else {}
     refenv.install()
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
@@ -259,6 +260,7 @@ def _grid_fit_one(job):
     if h_scale != 1.:
         ip['h_normal'] *= h_scale
     cfg = dict(config_for(name))
+    cfg.update(extra)
     cfg.update({'num_em_iter': em, 'num_update_iter': vi})
     trace = {'h': [], 'params': [], 'elbo': [], 'accept': []}
     orig_h, orig_p, orig_up = rcn.BreakpointModel.update_h, rcn.BreakpointModel.update_param, \
@@ -338,21 +340,22 @@ def reference_selection(stats_rows, config):
     return int(key.split('solution_')[1].split('/')[0])
 
 
-def run_grid(name, procs=6, em=5, vi=5, seed=1234, tag='', h_scale=1., inits=None):
+def run_grid(name, procs=6, em=5, vi=5, seed=1234, tag='', h_scale=1., inits=None, extra=None):
     import multiprocessing as mp
     d, _ = load_experiment(name)
     n = len(d['init_h_normal'])
     ids = list(range(n)) if inits is None else inits
-    jobs = [(name, i, em, vi, seed, h_scale) for i in ids]
+    jobs = [(name, i, em, vi, seed, h_scale, dict(extra or {})) for i in ids]
     t0 = time.time()
     with mp.get_context('fork').Pool(procs) as pool:
         fits = pool.map(_grid_fit_one, jobs, chunksize=1)
     ok = [f for f in fits if not f['error']]
     rows = [dict(init_id=f['init_id'], elbo=f['elbo'], proportion_divergent=f['proportion_divergent']) for f in ok]
-    best = reference_selection(rows, config_for(name))
+    best = reference_selection(rows, dict(config_for(name), **(extra or {})))
     out = {'init_ids': np.array([f['init_id'] for f in ok]), 'failed_ids': np.array([f['init_id'] for f in fits if f['error']], dtype=np.int64),
            'best_init_id': best, 'seed': seed, 'num_em_iter': em, 'num_update_iter': vi, 'h_scale': h_scale,
-           'seconds': np.array([f['seconds'] for f in ok]), 'brk_ids': ok[0]['brk_ids']}
+           'seconds': np.array([f['seconds'] for f in ok]), 'brk_ids': ok[0]['brk_ids'],
+           'max_copy_number': int(dict(config_for(name), **(extra or {}))['max_copy_number'])}
     for k in ('elbo', 'elbo_diff', 'h', 'params', 'ploidy', 'proportion_divergent', 'cn', 'brk_cn', 'trace_h',
               'trace_params', 'trace_elbo', 'accept', 'p_outlier_total', 'p_outlier_allele'):
         out[k] = np.array([f[k] for f in ok])
@@ -367,7 +370,8 @@ def _main_grid():
         return conv(args[args.index(flag) + 1]) if flag in args else default
     run_grid(args[0], procs=opt('--procs', 6, int), em=opt('--em', 5, int), vi=opt('--vi', 5, int),
              seed=opt('--seed', 1234, int), tag=opt('--tag', '', str), h_scale=opt('--h-scale', 1., float),
-             inits=opt('--inits', None, lambda s: [int(v) for v in s.split(',')]))
+             inits=opt('--inits', None, lambda s: [int(v) for v in s.split(',')]),
+             extra=({'max_copy_number': opt('--cnmax', 6, int)} if '--cnmax' in args else None))
 
 
 if __name__ == '__main__':

@@ -418,3 +418,296 @@ int rmx_launch_chain_mma3(cudaStream_t st, const RmxTables& T, const RmxDims& d,
     if (d.S > 128 && d.S <= 168) return launch_chain_mma3_cfg<42, 7, 3, 24>(st, A);     // max copy number 8, M = 3: S = 165
     return 2;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// K2 for 169 .. 360 states (the reference's DEFAULT max copy number 12: S = 355 with two tumour clones): the class
+// matrix is 1 MB and lives in L2 only, but it is still a tensor-path product.  The L2-streamed kernel this replaces
+// (chain.cu) serves FOUR fits per matrix read with scalar FMAs; here a CTA serves EIGHT fits per read: eight DMMA warps
+// own six column blocks each (48 x 8 = 384 columns) and load their B fragments (8 bytes per lane, 32-byte sectors fully
+// used) straight from L2 under the DMMA stream -- no transition operand on chip at all, 540 loads + 540 DMMAs per warp
+// and segment.  Messages, scaling, f ring and bookkeeping as in k_chain_mma3.  Breakend rows (1.8 % of rows) take a
+// scalar path: every thread sums its own two columns per block over all S input states.
+// ---------------------------------------------------------------------------------------------------------------------
+struct C3sLayout {
+    size_t u, wtab, redd, redi, tots, fring, rism, total;
+};
+__host__ __device__ inline C3sLayout c3s_layout(int KB, int T, int NSLOT, int S, int M, int MD) {
+    C3sLayout L;
+    size_t o = 0;
+    L.u = o;     o = c3_al(o + sizeof(double) * 2 * KB * 32);
+    L.wtab = o;  o = c3_al(o + sizeof(double) * C3_GT * MD);
+    L.redd = o;  o = c3_al(o + sizeof(double) * (C3_GT * C3_NW + C3_GT));
+    L.redi = o;  o = c3_al(o + sizeof(int) * 2 * C3_GT * C3_NW);
+    L.tots = o;  o = c3_al(o + (size_t)S * M);
+    L.fring = o; o = c3_al(o + sizeof(double) * C3_FST * NSLOT * T);
+    L.rism = o;  o = c3_al(o + sizeof(int) * C3_RIMAX);
+    L.total = o;
+    return L;
+}
+
+template <int KB, int NW, int NBW>
+__global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int T = NW * 32, NSLOT = 2 * NBW;
+    const RmxDims& d = A.d;
+    const int S = d.S, M = d.M, MD = M * d.D;
+    const C3sLayout L = c3s_layout(KB, T, NSLOT, S, M, MD);
+    double* u = reinterpret_cast<double*>(smem_raw + L.u);             // [2][KB*32]
+    double* wtab = reinterpret_cast<double*>(smem_raw + L.wtab);       // [8][MD]   breakend tables of the step
+    double* redd = reinterpret_cast<double*>(smem_raw + L.redd);       // [8][C3_NW] + [8] mF sums
+    int* redi = reinterpret_cast<int*>(smem_raw + L.redi);             // [2][8][C3_NW] max exponent fields
+    int8_t* tots = reinterpret_cast<int8_t*>(smem_raw + L.tots);       // [S*M]
+    double* fring = reinterpret_cast<double*>(smem_raw + L.fring) + threadIdx.x;   // [C3_FST][NSLOT][T], own column
+    int* rism = reinterpret_cast<int*>(smem_raw + L.rism);             // [C3_RIMAX] row info of the chain
+
+    const int tile = blockIdx.x % A.ntiles;
+    const int cd = blockIdx.x / A.ntiles;
+    const int dir = cd & 1, chain = A.ch.order[cd >> 1];
+    const int s0 = A.ch.start[chain], s1 = A.ch.end[chain];
+    const int t = threadIdx.x, w = t >> 5, lane = t & 31;
+    const int gid = lane >> 2, tig = lane & 3;     // mma fragment coordinates
+    const int gbase = A.g0 + tile * C3_GT;
+    const int gcount = min(C3_GT, A.g0 + A.gn - gbase);
+    const int64_t SS = (int64_t)S * S;
+    const int64_t NS = (int64_t)d.N * S;
+    const int sgn = dir == 0 ? 1 : -1;
+    const int jbase = w * (8 * NBW);
+    const bool fit_ok = gid < gcount;
+    const int gfit = gbase + min(gid, gcount - 1);
+    int upos[NBW];
+    bool ok0[NBW], ok1[NBW];
+#pragma unroll
+    for (int h = 0; h < NBW; ++h) {
+        const int j0 = jbase + 8 * h + 2 * tig;
+        ok0[h] = fit_ok && j0 < S;
+        ok1[h] = fit_ok && j0 + 1 < S;
+        upos[h] = c3_pos(gid, j0);
+    }
+    // column blocks of this warp inside the state space (warp-uniform): the others issue nothing
+    int nbw = 0;
+#pragma unroll
+    for (int h = 0; h < NBW; ++h) nbw += (jbase + 8 * h < S) ? 1 : 0;
+
+    for (int e = t; e < 2 * KB * 32; e += T) u[e] = 0.;
+    for (int e = t; e < 2 * C3_GT * C3_NW; e += T) redi[e] = ((e % C3_NW) == 0) ? 1023 : 0;   // first message: max f = 1
+    for (int e = t; e < S * M; e += T) {
+        int s = e / M, m = e - s * M;
+        tots[e] = (m == 0) ? 0 : (int8_t)(A.tab[(s * M + m) * 2] + A.tab[(s * M + m) * 2 + 1]);
+    }
+    __syncthreads();
+
+    const int nsteps = s1 - s0;
+    const int seg_first = dir == 0 ? s0 : s1;
+    const double* fp = A.fexp + (int64_t)gfit * NS + (int64_t)seg_first * S + jbase + 2 * tig;
+    double* outp = (dir == 0 ? A.ahat : A.bhat) + (int64_t)gfit * NS + (int64_t)seg_first * S + jbase + 2 * tig;
+    const int rowstep = sgn * S;
+
+    double un[NBW][2];
+#pragma unroll
+    for (int h = 0; h < NBW; ++h) {
+        un[h][0] = un[h][1] = 0.;
+        if (ok0[h]) { un[h][0] = fp[8 * h]; outp[8 * h] = dir == 0 ? un[h][0] : 1.; }
+        if (ok1[h]) { un[h][1] = fp[8 * h + 1]; outp[8 * h + 1] = dir == 0 ? un[h][1] : 1.; }
+        if (ok0[h]) *reinterpret_cast<double2*>(u + upos[h]) = make_double2(un[h][0], un[h][1]);
+    }
+    auto row_of = [&](int k) { return dir == 0 ? s0 + k : s1 - 1 - k; };
+    const unsigned fring_s = (unsigned)__cvta_generic_to_shared(fring);
+    const double* fsrc = fp + rowstep;
+    int f_next = 0;
+    auto f_issue = [&]() {
+        if (f_next < nsteps) {
+            const unsigned base = fring_s + 8u * (unsigned)(((f_next % C3_FST) * NSLOT) * T);
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) {
+                if (ok0[h]) c3_cp8(base + 8u * (unsigned)((h * 2) * T), fsrc + 8 * h);
+                if (ok1[h]) c3_cp8(base + 8u * (unsigned)((h * 2 + 1) * T), fsrc + 8 * h + 1);
+            }
+            fsrc += rowstep;
+        }
+        ++f_next;
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int e = 0; e < C3_FST * NSLOT; ++e) fring[e * T] = 0.;
+#pragma unroll
+    for (int k = 0; k < C3_FST - 1; ++k) f_issue();
+    const bool ri_sm = nsteps <= C3_RIMAX;
+    if (ri_sm)
+        for (int k = t; k < nsteps; k += T) rism[k] = A.rinfo[row_of(k)];
+    __syncthreads();
+    auto ri_at = [&](int k) { return ri_sm ? rism[k] : A.rinfo[row_of(k)]; };
+    int ri0 = nsteps > 0 ? ri_at(0) : 0, ri1 = nsteps > 1 ? ri_at(1) : 0;
+    int cur = 0, esum = 0, bad = 0;
+
+    for (int step = 0; step < nsteps; ++step) {
+        outp += rowstep;
+        const int ri = ri0;
+        ri0 = ri1;
+        const int cls = (ri & 0xff) - 1;
+        const int br = (ri >> 12) - 1;
+        const double* uc = u + cur * KB * 32;
+        double c[NBW][2], f[NBW][2];
+        int be = 1023;
+#pragma unroll
+        for (int h = 0; h < NBW; ++h) c[h][0] = c[h][1] = f[h][0] = f[h][1] = 0.;
+        {   // bookkeeping of the segment (the loads below hide it)
+            const int4* rp = reinterpret_cast<const int4*>(redi + (cur * C3_GT + gid) * C3_NW);
+            const int4 r0 = rp[0], r1 = rp[1];
+            be = max(max(max(r0.x, r0.y), max(r0.z, r0.w)), max(max(r1.x, r1.y), max(r1.z, r1.w)));
+        }
+        if (br < 0) {
+            // B fragment of (row block kb, column block h): E[4 kb + tig][jbase + 8 h + gid]; rows and columns outside the
+            // state space are read inside the (N-1 class) matrix and multiplied by zero message entries / never stored
+            const double* Eb = A.sp.Emat + (int64_t)cls * SS + (int64_t)tig * S + jbase + gid;
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) {
+                if (h < nbw) {
+                    const bool jin = jbase + 8 * h + gid < S;
+                    const double* Eh = Eb + 8 * h;
+                    double c0 = 0., c1 = 0., e0 = 0., e1 = 0.;
+#pragma unroll 18
+                    for (int kb = 0; kb < KB; ++kb) {
+                        const double a = uc[kb * 32 + lane];
+                        const double bf = (jin && kb * 4 + tig < S) ? __ldg(Eh + (int64_t)kb * 4 * S) : 0.;
+                        if (kb & 1) c3_dmma(e0, e1, a, bf);
+                        else c3_dmma(c0, c1, a, bf);
+                    }
+                    c[h][0] = c0 + e0;
+                    c[h][1] = c1 + e1;
+                }
+            }
+        } else {
+            // ---- breakend row, scalar: out[g][j] = w0 sum_i u[g][i] flipE[i][j] prod_m wexp[g][m][tot_i[m] - tot_j[m]]
+            // (backward sweep: the summed state is the LATER one, so the difference is tot_j[m] - tot_i[m])
+            for (int e = t; e < C3_GT * MD; e += T) {
+                const int g = e / MD, o = e - g * MD;
+                const int gg = gbase + min(g, gcount - 1);
+                wtab[e] = A.sp.wexp[(int64_t)gg * A.sp_fit_stride + (int64_t)br * MD + o];
+            }
+            __syncthreads();
+            const double* FE = A.sp.flipE + (int64_t)cls * SS;
+            const int d0 = ((ri >> 8) & 15) - 8 + d.doff;
+            const double* wg = wtab + gid * MD;
+            const double w0 = wg[d0];
+            const double* ug = uc + gid * 4;
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) {
+                if (h < nbw) {
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int j = jbase + 8 * h + 2 * tig + q;
+                        if (j < S) {
+                            int off[RMX_MAXM];
+#pragma unroll
+                            for (int m = 1; m < RMX_MAXM; ++m)
+                                if (m < M) off[m] = m * d.D + d.doff - sgn * (int)tots[j * M + m];
+                            double acc = 0.;
+#pragma unroll 4
+                            for (int i = 0; i < S; ++i) {
+                                double e = __ldg(FE + (int64_t)i * S + j);
+#pragma unroll
+                                for (int m = 1; m < RMX_MAXM; ++m)
+                                    if (m < M) e *= wg[off[m] + sgn * (int)tots[i * M + m]];
+                                acc = fma(ug[((i >> 2) << 5) + (i & 3)], e, acc);
+                            }
+                            c[h][q] = acc * w0;
+                        }
+                    }
+                }
+            }
+        }
+        // ---- the segment's f (landed long ago), the next copies, the next row descriptor
+        asm volatile("cp.async.wait_group %0;" ::"n"(C3_FST - 2) : "memory");
+        {
+            const double* fr = fring + ((step % C3_FST) * NSLOT) * T;
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) { f[h][0] = fr[(h * 2) * T]; f[h][1] = fr[(h * 2 + 1) * T]; }
+        }
+        f_issue();
+        if (step + 2 < nsteps) ri1 = ri_at(step + 2);
+        esum += be - 1023;
+        if (be <= 0 || be >= 2047) bad = 1;
+        int mx = 0;
+        const double sc = c3_pow2(be);
+#pragma unroll
+        for (int h = 0; h < NBW; ++h) {
+            double v0 = c[h][0] * sc, v1 = c[h][1] * sc;
+            if (dir == 0) {
+                v0 *= f[h][0]; v1 *= f[h][1];
+                un[h][0] = v0; un[h][1] = v1;
+            } else {
+                un[h][0] = v0 * f[h][0]; un[h][1] = v1 * f[h][1];
+            }
+            if (!ok0[h]) un[h][0] = 0.;
+            if (!ok1[h]) un[h][1] = 0.;
+            if (ok0[h]) outp[8 * h] = v0;
+            if (ok1[h]) outp[8 * h + 1] = v1;
+            if (ok0[h]) *reinterpret_cast<double2*>(u + (cur ^ 1) * KB * 32 + upos[h]) = make_double2(un[h][0], un[h][1]);
+            mx = max(mx, max(c3_expfield(un[h][0]), c3_expfield(un[h][1])));
+        }
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        if (tig == 0) redi[((cur ^ 1) * C3_GT + gid) * C3_NW + w] = mx;
+        cur ^= 1;
+        __syncthreads();
+    }
+
+    {
+        double sv = 0.;
+#pragma unroll
+        for (int h = 0; h < NBW; ++h) sv += un[h][0] + un[h][1];
+        sv += __shfl_xor_sync(0xffffffffu, sv, 1);
+        sv += __shfl_xor_sync(0xffffffffu, sv, 2);
+        if (tig == 0) redd[gid * C3_NW + w] = sv;
+        for (int g = w; g < gcount; g += NW) {
+            const double* mf = A.mF + (int64_t)(gbase + g) * d.N;
+            double ms = 0.;
+            for (int n = s0 + lane; n <= s1; n += 32) ms += mf[n];
+            ms = warp_sum(ms);
+            if (lane == 0) redd[C3_GT * C3_NW + g] = ms;
+        }
+    }
+    __syncthreads();
+    if (w == 0 && tig == 0 && fit_ok) {
+        double slast = 0.;
+        for (int c2 = 0; c2 < NW; ++c2) slast += redd[gid * C3_NW + c2];
+        if (dir == 0) {
+            const double logz = log(slast) + 0.693147180559945309417 * (double)esum + redd[C3_GT * C3_NW + gid];
+            A.chain_logz[(int64_t)(gbase + gid) * A.ch.NC + chain] = logz;
+            if (isnan(logz)) bad = 1;
+        }
+        if (!(slast > 0.) || isinf(slast)) bad = 1;
+        if (bad) atomicOr(A.dflags, RMX_F_MSG_NAN);
+    }
+}
+
+template <int KB, int NW, int NBW>
+static int launch_chain_mma_s_cfg(cudaStream_t st, Chain3Args& A) {
+    const RmxDims& d = A.d;
+    const C3sLayout L = c3s_layout(KB, NW * 32, 2 * NBW, d.S, d.M, d.M * d.D);
+    auto kern = k_chain_mma_s<KB, NW, NBW>;
+    if (L.total > 227 * 1024) return 2;
+    if (L.total > 48 * 1024) {
+        static RmxPerDeviceOnce once;
+        if (once.need())
+            if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) return 1;
+    }
+    A.ntiles = (A.gn + C3_GT - 1) / C3_GT;
+    kern<<<A.ch.NC * 2 * A.ntiles, NW * 32, L.total, st>>>(A);
+    return cudaPeekAtLastError() == cudaSuccess ? 0 : 1;
+}
+
+// returns 0 on success, 1 if the configuration or the launch failed, 2 if this kernel does not cover the shape
+int rmx_launch_chain_mma_s(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
+                           const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
+                           const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags) {
+    if (ch.NC <= 0 || gn <= 0) return 0;
+    if (rinfo == nullptr || d.M > RMX_MAXM) return 2;
+    Chain3Args A;
+    A.d = d; A.ch = ch; A.rinfo = rinfo; A.sp = sp; A.sp_fit_stride = sp_fit_stride; A.tab = T.tab;
+    A.g0 = g0; A.gn = gn; A.ntiles = 1; A.fexp = fexp; A.mF = mF; A.ahat = ahat; A.bhat = bhat;
+    A.chain_logz = chain_logz; A.dflags = dflags;
+    A.bc = nullptr; A.didx = nullptr; A.BC = 0; A.KBB = 0; A.ND = 0;
+    if (d.S > 168 && d.S <= 360) return launch_chain_mma_s_cfg<90, 8, 6>(st, A);     // max copy number 9 .. 12, M = 3
+    return 2;
+}

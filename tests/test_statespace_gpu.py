@@ -78,6 +78,18 @@ def test_max_copy_number_8():
     assert np.array_equal(cu2.posterior_marginals, cu.posterior_marginals)
 
 
+def test_max_copy_number_12(ref_bpmodel):
+    """The reference's DEFAULT max_copy_number (12): M = 3 -> S = 355.  The chain messages take k_chain_mma_s (eight fits
+    per read of the L2-resident class matrix, B fragments loaded under the DMMAs, scalar breakend rows); against the
+    COMPILED reference on 120 segments with their breakpoints (three (N-1, S, S) arrays of 0.12 GB each)."""
+    ip = util.init_params('small', 1)
+    from remixt_b200 import pipeline
+    cu, ref = _drive(_sub(120), pipeline.init_h(ip), ref_bpmodel.RemixtModel, max_copy_number=12,
+                     max_depth=2. * ip['h_normal'] + 12.25 * ip['h_tumour'])
+    assert cu.num_cn_states == 355 and cu.num_breakpoints > 0
+    _compare(cu, ref)
+
+
 def test_four_clones():
     """Three tumour clones + normal: M = 4, max_copy_number = 6 -> S = 457."""
     from oracle import bpmodel_np
