@@ -97,12 +97,14 @@ def test_mstep_evaluate_matches_reference_golden():
     batch.close()
 
 
-def _grid(name):
+def _grid(name, tag=''):
     from remixt_b200 import pipeline
-    g = util.golden('grid_%s.npz' % name)
+    g = util.golden('grid_%s%s.npz' % (name, tag))
     exp = util.load_experiment(name)
-    inits = dict((i, util.init_params(name, i)) for i in range(util.num_inits(name)))
-    cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
+    ids = range(util.num_inits(name)) if not tag else sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))
+    inits = dict((i, util.init_params(name, i)) for i in ids)
+    cfg = {'max_copy_number': int(g['max_copy_number']) if 'max_copy_number' in g.files else 6,
+           'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
     res, best, errors = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']))
     return g, res, best, errors
 
@@ -155,6 +157,22 @@ def test_free_running_grid_config1_vs_reference():
     same = [i for i, r in rows.items() if r['decisions']]
     assert len(same) >= 30
     for i in same:      # same decisions => same output
+        assert rows[i]['map_exact'] and rows[i]['brk_exact'] and rows[i]['elbo'] < 1e-6, i
+
+
+def test_free_running_fits_at_the_reference_default_max_copy_number():
+    """max_copy_number = 12, the reference's default (S = 355: L2-streamed DMMA chain kernel, unfused round,
+    first-generation histograms): six initialisations of `small` fitted free-running by the reference
+    (tests/golden/grid_small_cn12.npz, oracle/make_golden.py small grid --cnmax 12) and here."""
+    g, res, best, errors = _grid('small', '_cn12')
+    assert len(errors) <= 1 and best not in errors
+    assert best == int(g['best_init_id'])
+    rows = _agreement(g, res)
+    sel = rows[best]
+    assert sel['map_exact'] and sel['brk_exact'] and sel['decisions'] and sel['elbo'] < 1e-6
+    same = [i for i, r in rows.items() if r['decisions']]
+    assert len(same) >= len(rows) - 1
+    for i in same:
         assert rows[i]['map_exact'] and rows[i]['brk_exact'] and rows[i]['elbo'] < 1e-6, i
 
 
