@@ -379,7 +379,7 @@ static int ensure_mats(Model* m, int tm) {
     ClassMats& cm = b->mats[tm];
     size_t n = (size_t)b->C * b->d.S * b->d.S;
     if (!cm.Tmat) {
-        if (dalloc(b, &cm.Tmat, n) != cudaSuccess || dalloc(b, &cm.Emat, n) != cudaSuccess ||
+        if (dalloc(b, &cm.Tmat, n) != cudaSuccess || dalloc(b, &cm.Emat, n + 64) != cudaSuccess ||
             dalloc(b, &cm.flipc, n) != cudaSuccess || dalloc(b, &cm.flipE, n) != cudaSuccess)
             return m->fail(RMX_ERR_CUDA, "out of device memory for transition class matrices");
     }

@@ -556,25 +556,59 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
             be = max(max(max(r0.x, r0.y), max(r0.z, r0.w)), max(max(r1.x, r1.y), max(r1.z, r1.w)));
         }
         if (br < 0) {
-            // B fragment of (row block kb, column block h): E[4 kb + tig][jbase + 8 h + gid]; rows and columns outside the
-            // state space are read inside the (N-1 class) matrix and multiplied by zero message entries / never stored
-            const double* Eb = A.sp.Emat + (int64_t)cls * SS + (int64_t)tig * S + jbase + gid;
+            // B fragment of (row block kb, column block h): E[4 kb + tig][jbase + 8 h + gid].  Row blocks outermost: the A
+            // fragment is read once per row block, the six B fragments sit at constant offsets from ONE pointer that
+            // advances four rows per block -- 2.5 instructions per DMMA (the first version of this loop spent 18 on
+            // predicates and 64-bit index products and was issue-bound at 53 k cycles per segment against the DMMA
+            // floor of 17 k; ncu: 10 k warp instructions per warp and segment, issue slots 36 % busy).  Columns beyond
+            // the state space are read (inside the allocation, padded) and feed output columns that are never stored;
+            // rows beyond it exist in the last row block only and are zeroed there.
+            const double* Ep = A.sp.Emat + (int64_t)cls * SS + (int64_t)tig * S + jbase + gid;
+            const int kfull = S >> 2;
+            // register pipeline, four row blocks deep: the loads of block kb + 4 are issued before the DMMAs of block kb
+            // (an L2 hit takes ~300 cycles, a row block of DMMAs ~190 with two warps per sub-partition; left to itself
+            // the compiler put each load six instructions ahead of its DMMA: 46 % of all stall samples long-scoreboard)
+            double q0[NBW], q1[NBW], q2[NBW], q3[NBW];
+            auto ldblk = [&](double* q, const double* p) {
 #pragma unroll
-            for (int h = 0; h < NBW; ++h) {
-                if (h < nbw) {
-                    const bool jin = jbase + 8 * h + gid < S;
-                    const double* Eh = Eb + 8 * h;
-                    double c0 = 0., c1 = 0., e0 = 0., e1 = 0.;
-#pragma unroll 18
-                    for (int kb = 0; kb < KB; ++kb) {
-                        const double a = uc[kb * 32 + lane];
-                        const double bf = (jin && kb * 4 + tig < S) ? __ldg(Eh + (int64_t)kb * 4 * S) : 0.;
-                        if (kb & 1) c3_dmma(e0, e1, a, bf);
-                        else c3_dmma(c0, c1, a, bf);
-                    }
-                    c[h][0] = c0 + e0;
-                    c[h][1] = c1 + e1;
+                for (int h = 0; h < NBW; ++h) q[h] = (h < nbw) ? __ldg(p + 8 * h) : 0.;
+            };
+            auto mmablk = [&](const double* q, int kb) {
+                const double a = uc[kb * 32 + lane];
+#pragma unroll
+                for (int h = 0; h < NBW; ++h)
+                    if (h < nbw) c3_dmma(c[h][0], c[h][1], a, q[h]);
+            };
+            const int64_t rs = 4 * (int64_t)S;
+            const int k4 = kfull & ~3;
+            if (k4 > 0) {
+                ldblk(q0, Ep); ldblk(q1, Ep + rs); ldblk(q2, Ep + 2 * rs); ldblk(q3, Ep + 3 * rs);
+                const double* En = Ep + 4 * rs;
+                for (int kb = 0; kb < k4; kb += 4) {
+                    const bool more = kb + 4 < k4;
+                    mmablk(q0, kb);
+                    if (more) ldblk(q0, En);
+                    mmablk(q1, kb + 1);
+                    if (more) ldblk(q1, En + rs);
+                    mmablk(q2, kb + 2);
+                    if (more) ldblk(q2, En + 2 * rs);
+                    mmablk(q3, kb + 3);
+                    if (more) ldblk(q3, En + 3 * rs);
+                    En += 4 * rs;
                 }
+            }
+            Ep += (int64_t)k4 * rs;
+            for (int kb = k4; kb < kfull; ++kb) {
+                ldblk(q0, Ep);
+                mmablk(q0, kb);
+                Ep += rs;
+            }
+            if (kfull * 4 < S) {
+                const double a = uc[kfull * 32 + lane];
+                const bool rin = kfull * 4 + tig < S;
+#pragma unroll
+                for (int h = 0; h < NBW; ++h)
+                    if (h < nbw) c3_dmma(c[h][0], c[h][1], a, rin ? __ldg(Ep + 8 * h) : 0.);
             }
         } else {
             // ---- breakend row, scalar: out[g][j] = w0 sum_i u[g][i] flipE[i][j] prod_m wexp[g][m][tot_i[m] - tot_j[m]]
@@ -590,6 +624,9 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
             const double* wg = wtab + gid * MD;
             const double w0 = wg[d0];
             const double* ug = uc + gid * 4;
+            // (measured alternative: input states outermost with the thread's 2 NBW columns side by side -- twelve
+            // independent chains instead of one -- is SLOWER, 20 ms against 16.5 ms of the 65 ms launch: the two factor
+            // look-ups per pair then hit shared memory from eight different per-fit tables at once)
 #pragma unroll
             for (int h = 0; h < NBW; ++h) {
                 if (h < nbw) {
