@@ -193,6 +193,10 @@ struct Batch {
     uint16_t* bc_didx16 = nullptr;   // the same (BC,BC) table with 16-bit entries (more than 255 difference tuples: chain_mma3.cu)
     uint8_t* hord = nullptr;     // (M,S) states ordered by each clone's total (k_hist2)
     int* hgstart = nullptr;
+    uint16_t* hord16 = nullptr;  // the same order for any S (k_hist4), with the group starts hgs16 (M, TVN + 1)
+    int* hgs16 = nullptr;
+    int TVN = 0;                 // number of distinct totals of a clone (0 .. max total)
+    int NGS = 0;                 // entries of hgs16: [number of classes, class starts ..., S]
     int Q = 0;
     bool fast_ll = false;
     int64_t rmd = 1;          // R*M*D, fit stride of the breakend-row tables
@@ -646,7 +650,7 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
     for_runs(g0, gn, b->tm_used, nullptr, [&](int g, int n) {
         RmxTransSpec sp = spec_of(b, false, b->tm_used[g]);
         { cudaEvent_t te_ = b->tbegin(RMX_K_HIST); rmx_launch_hist(b->stream, tables(b), b->d, g, n, b->R, rowsof(b), sp, b->rmd, 0, b->ahat, b->bhat, b->fexp, b->hist,
-                        b->dflags, b->hord, b->hgstart); b->tend(te_); }
+                        b->dflags, b->hord, b->hgstart, b->hord16, b->hgs16, b->TVN, b->NGS); b->tend(te_); }
         if (b->R > 0) b->count();
     });
     for (int g = g0; g < g0 + gn; ++g) {
@@ -1139,6 +1143,37 @@ int rmx_batch_create(const rmx_desc* desc, int num_fits, const double* h_init, c
             CCK(dalloc(b, &b->sflag, (size_t)G * b->Q * S));
             CCK(dalloc(b, &b->segf, GN * 12));
         }
+    }
+    if (M >= 2 && S <= 65535) {
+        // states ordered by each clone's total copy number, and where every total's group starts (k_hist4)
+        int maxtot = 0;
+        for (int s2 = 0; s2 < S; ++s2)
+            for (int mm = 1; mm < M; ++mm)
+                maxtot = std::max(maxtot, (int)b->h_tab[((size_t)s2 * M + mm) * 2] + (int)b->h_tab[((size_t)s2 * M + mm) * 2 + 1]);
+        const int TVN = maxtot + 1;
+        // class order: states sorted (stably) by the tuple of their tumour-clone totals; gs = [number of classes,
+        // class starts ..., S]
+        auto key_of = [&](int s2) {
+            std::vector<int> key(M, 0);
+            for (int mm = 1; mm < M; ++mm)
+                key[mm] = (int)b->h_tab[((size_t)s2 * M + mm) * 2] + (int)b->h_tab[((size_t)s2 * M + mm) * 2 + 1];
+            return key;
+        };
+        std::vector<int> order(S);
+        for (int s2 = 0; s2 < S; ++s2) order[s2] = s2;
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return key_of(x) < key_of(y); });
+        std::vector<uint16_t> ord16((size_t)M * S, 0);
+        std::vector<int> gs(1, 0);
+        for (int k = 0; k < S; ++k) {
+            ord16[k] = (uint16_t)order[k];
+            if (k == 0 || key_of(order[k]) != key_of(order[k - 1])) gs.push_back(k);
+        }
+        gs[0] = (int)gs.size() - 1;
+        gs.push_back(S);
+        b->NGS = (int)gs.size();
+        CCK(upload(b, &b->hord16, ord16));
+        CCK(upload(b, &b->hgs16, gs));
+        b->TVN = TVN;
     }
     if (rmx_hist2_ok(d)) {
         CCK(dalloc(b, &b->hord, (size_t)M * S));

@@ -19,6 +19,7 @@
 // E (it depends on the state table and the penalty only), so one CTA advances GT fits in lock step and
 // each E entry loaded into a register is used GT times per step.  Chromosomes are coupled only through
 // telomere rows whose log_transmat is identically zero, so chains are exactly independent.
+#include <algorithm>
 #include <cstdlib>
 #include <mutex>
 #include "../../include/remixt_b200.h"
@@ -770,6 +771,103 @@ __global__ void __launch_bounds__(256, 2) k_hist2(RmxDims d, int g0, RmxRows row
     for (int e = t; e < d.D; e += blockDim.x) hist[(int64_t)r * M * d.D + e] = (e == c.d0 + d.doff) ? 1. : 0.;
 }
 
+// K-hist, third generation, any state space (S = 97: 1.32 -> 0.87 ms per 48-fit launch against k_hist2; S = 165: 5.0 ->
+// 2.2 ms and S = 355: 23.5 -> 6.8 ms against k_hist): no atomics, no S x S buffer.  A thread
+// owns a column j and walks the rows grouped by the tuple of their tumour-clone totals ("classes"; order and class
+// starts built on the host once per batch): within a class the per-fit factor is constant, so a class costs its
+// sum_i a_i flipE[i][j] (one L2 load, coalesced along j, and one FMA per pair), one factor and one add per clone into
+// colsum[m][total][j] (the thread's own column: no conflicts).  The histogram slot of (m, delta) is then the sum over
+// the columns of colsum[m][tot_j[m] + delta][j], as in k_hist2.  ONE pass over the S^2 pairs.  (The first-generation kernel adds every pair to M shared-memory counters with 64-bit atomics: 256
+// threads on at most D addresses per clone -- 23.5 ms per 48-fit launch at S = 355, 5.0 ms at S = 165.)
+#define HIST4_T 384
+__global__ void __launch_bounds__(HIST4_T, 2) k_hist4(RmxDims d, int g0, RmxRows rows, RmxTransSpec sp, int64_t sp_fit_stride,
+                                                   const int8_t* __restrict__ tab, const uint16_t* __restrict__ ord_g,
+                                                   const int* __restrict__ gstart_g, int TVN, int NGS,
+                                                   const double* __restrict__ ahat_all, const double* __restrict__ bhat_all,
+                                                   const double* __restrict__ fexp_all, double* __restrict__ hist_all,
+                                                   int* __restrict__ dflags) {
+    const int g = RMX_FIT();
+    const int64_t NSo = (int64_t)g * d.N * d.S;
+    const double *ahat = ahat_all + NSo, *bhat = bhat_all + NSo, *fexp = fexp_all + NSo;
+    double* hist = hist_all + (int64_t)g * sp_fit_stride;
+    sp.pd += (int64_t)g * sp_fit_stride;
+    sp.wexp += (int64_t)g * sp_fit_stride;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ double red[32];
+    const int S = d.S, M = d.M, D = d.D;
+    const int r = blockIdx.x;
+    const int n = rows.brk_rows[r];
+    PairCtx c;
+    pair_setup(c, smem_raw, d, rows, sp, tab, 0, n, ahat, bhat, fexp);      // a, g, wtab, tots (includes the barrier)
+    size_t off = (sizeof(double) * (2 * (size_t)S + (size_t)M * D) + (size_t)S * M + 15) & ~(size_t)15;
+    double* colsum = reinterpret_cast<double*>(smem_raw + off);              // [M-1][TVN][S]
+    uint16_t* ord = reinterpret_cast<uint16_t*>(colsum + (size_t)(M - 1) * TVN * S);     // [M][S]
+    int* gstart = reinterpret_cast<int*>(ord + (((size_t)M * S + 1) & ~(size_t)1));    // [NCLS + 2] class starts
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
+    for (int e = t; e < M * S; e += blockDim.x) ord[e] = ord_g[e];
+    for (int e = t; e < NGS; e += blockDim.x) gstart[e] = gstart_g[e];
+    __syncthreads();
+    const double w0 = c.kind == 2 ? c.wtab[c.d0 + d.doff] : 1.;
+    // ord row 0: the states ordered by the tuple of their tumour-clone totals ("classes"); gstart row 0: the class
+    // starts, gstart[0][TVN] = number of classes is stored by the host in the last used entry + 1 ... see api.cu.
+    const uint16_t* co = ord;                 // [S] class-ordered states
+    const int* cs = gstart;                   // cs[0] = number of classes NC, cs[1 .. NC + 1] = class starts
+    const int NCLS = cs[0];
+    for (int j = t; j < S; j += blockDim.x) {
+        const double gj = c.g[j];
+        int bj[RMX_MAXM];
+#pragma unroll
+        for (int m = 1; m < RMX_MAXM; ++m) bj[m] = (m < M) ? m * D + d.doff - (int)c.tots[j * M + m] : 0;
+        const double* Ej = c.E + j;
+        for (int m = 1; m < M; ++m)
+            for (int tv = 0; tv < TVN; ++tv) colsum[((size_t)(m - 1) * TVN + tv) * S + j] = 0.;
+        for (int cl = 0; cl < NCLS; ++cl) {
+            // the per-fit factor depends on (i, j) through the totals only: it is the same for every row of a class
+            double acc = 0.;
+            const int k1 = cs[cl + 2];
+#pragma unroll 4
+            for (int k = cs[cl + 1]; k < k1; ++k) {
+                const int i = co[k];
+                acc = fma(c.a[i], c.kind == 0 ? 1. : __ldg(Ej + (int64_t)i * S), acc);
+            }
+            const int irep = co[cs[cl + 1]];
+            double e = acc;
+            if (c.kind == 2) {
+                e *= w0;
+#pragma unroll
+                for (int m = 1; m < RMX_MAXM; ++m)
+                    if (m < M) e *= c.wtab[bj[m] + (int)c.tots[irep * M + m]];
+            }
+            e *= gj;
+#pragma unroll
+            for (int m = 1; m < RMX_MAXM; ++m)
+                if (m < M) colsum[((size_t)(m - 1) * TVN + (int)c.tots[irep * M + m]) * S + j] += e;
+        }
+    }
+    __syncthreads();
+    // Z: every pair once, from the first tumour clone's column sums in a fixed order
+    double z = 0.;
+    for (int j = t; j < S; j += blockDim.x)
+        for (int tv = 0; tv < TVN; ++tv) z += colsum[(size_t)tv * S + j];
+    z = block_sum_all(z, red);
+    if (!(z > 0.) || isinf(z)) {
+        if (t == 0) atomicOr(dflags, RMX_F_JOINT_NAN);
+    }
+    const double inv = 1. / z;
+    for (int q = wid; q < (M - 1) * D; q += nw) {
+        const int m = 1 + q / D, slot = q - (m - 1) * D;
+        const int dd = slot - d.doff;
+        double v = 0.;
+        for (int j = lane; j < S; j += 32) {
+            const int tv = (int)c.tots[j * M + m] + dd;
+            if (tv >= 0 && tv < TVN) v += colsum[((size_t)(m - 1) * TVN + tv) * S + j];
+        }
+        v = warp_sum(v);
+        if (lane == 0) hist[((int64_t)r * M + m) * D + slot] = v * inv;
+    }
+    for (int e = t; e < D; e += blockDim.x) hist[(int64_t)r * M * D + e] = (e == c.d0 + d.doff) ? 1. : 0.;
+}
+
 // update_p_breakpoint (bpmodel.pyx:964-983): one CTA per (fit, breakpoint), one thread per breakpoint
 // state (B <= 64).  Each thread accumulates its log q in the reference's order (breakend rows ascending,
 // clones, copy-number differences); thread 0 then does the two sequential sums of _exp_normalize
@@ -1498,12 +1596,29 @@ void rmx_launch_hist_prep(cudaStream_t st, const RmxTables& T, const RmxDims& d,
 
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
                      const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
-                     const double* fexp, double* hist, int* dflags, const uint8_t* hord, const int* hgstart) {
+                     const double* fexp, double* hist, int* dflags, const uint8_t* hord, const int* hgstart,
+                     const uint16_t* hord16, const int* hgs16, int TVN, int NGS) {
     if (R <= 0 || gn <= 0) return;
-    // S <= 128 and totals below HIST2_TV: the atomic-free kernel
+    // fitted models, any state space: class-wise column sums (k_hist4).  RMX_HIST2 / RMX_HIST1 force the older kernels
+    // (A/B measurements only).
+    static const bool no_hist4 = getenv("RMX_HIST1") != nullptr || getenv("RMX_HIST2") != nullptr;
+    if (!uniform && !no_hist4 && hord16 != nullptr && TVN > 0 && d.M >= 2) {
+        const size_t base4 = (pair_smem(d) + 15) & ~(size_t)15;
+        const size_t smem4 = base4 + sizeof(double) * (size_t)(d.M - 1) * TVN * d.S +
+                             sizeof(uint16_t) * (((size_t)d.M * d.S + 1) & ~(size_t)1) + sizeof(int) * (size_t)NGS + 16;
+        if (smem4 <= 200 * 1024) {
+            static RmxPerDeviceOnce attr4_once;
+            if (attr4_once.need()) cudaFuncSetAttribute(k_hist4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            k_hist4<<<dim3(R, gn), std::min(HIST4_T, ((d.S + 31) / 32) * 32), smem4, st>>>(
+                d, g0, rows, sp, sp_fit_stride, T.tab, hord16, hgs16, TVN, NGS, ahat, bhat, fexp, hist, dflags);
+            return;
+        }
+    }
+    // S <= 128 and totals below HIST2_TV: the pair weights staged in shared memory (constructor state, A/B)
+    static const bool no_hist2 = getenv("RMX_HIST1") != nullptr;
     const size_t base = (pair_smem(d) + 15) & ~(size_t)15;
     const size_t smem2 = base + sizeof(double) * ((size_t)d.S * d.S + (size_t)(d.M - 1) * HIST2_TV * HIST2_SP) + 16;
-    if (hord != nullptr && rmx_hist2_ok(d) && smem2 <= 200 * 1024) {
+    if (!no_hist2 && hord != nullptr && rmx_hist2_ok(d) && smem2 <= 200 * 1024) {
         static RmxPerDeviceOnce attr_once;
         if (attr_once.need()) {
             cudaFuncSetAttribute(k_hist2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);

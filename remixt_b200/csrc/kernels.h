@@ -133,7 +133,8 @@ void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const do
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
                      const RmxTransSpec& sp, int64_t sp_fit_stride, int uniform, const double* ahat, const double* bhat,
                      const double* fexp, double* hist, int* dflags, const uint8_t* hord = nullptr,
-                     const int* hgstart = nullptr);
+                     const int* hgstart = nullptr, const uint16_t* hord16 = nullptr, const int* hgs16 = nullptr, int TVN = 0,
+                     int NGS = 0);
 // atomic-free histogram kernel (S <= 128): per-batch state order tables
 int rmx_hist2_ok(const RmxDims& d);
 int rmx_hist2_gstart_count(const RmxDims& d);
