@@ -627,7 +627,7 @@ static int do_update_p_cn(Model* m, bool have_frame = false, bool defer_post = f
                                        b->ahat, b->bhat, b->chain_logz, b->dflags, b->bc_tab, b->bc_didx16, b->BC, b->KBB, b->ND);
         if (lc == 2 && !force_streamed && !force_v1)      // 169 .. 360 states: B fragments streamed from L2 under the DMMAs
             lc = rmx_launch_chain_mma_s(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp, b->mF,
-                                        b->ahat, b->bhat, b->chain_logz, b->dflags);
+                                        b->ahat, b->bhat, b->chain_logz, b->dflags, b->hord16, b->hgs16);
         if (lc == 2 && !force_streamed)
             lc = rmx_launch_chain_mma(b->stream, tables(b), b->d, chainsof(b), b->rinfo, sp, b->rmd, g, n, b->fexp,
                                       b->mF, b->ahat, b->bhat, b->chain_logz, b->dflags);

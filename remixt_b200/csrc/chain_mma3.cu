@@ -50,6 +50,8 @@ struct Chain3Args {
     const uint8_t* bc;     // [perm (4 KBB)] [kbcls (KBB)] [scls (S)] [didx8 (BC, BC), unused here] [ddel (ND, M)]
     const uint16_t* didx;  // (BC, BC): which difference tuple is class ci minus class cj
     int BC, KBB, ND;
+    const uint16_t* cord;  // k_chain_mma_s: states in class order (S)
+    const int* cstart;     // k_chain_mma_s: [number of classes, class starts ..., S]
 };
 
 // message in fragment order: state i of fit g lives at (i/4)*32 + g*4 + i%4
@@ -415,6 +417,7 @@ int rmx_launch_chain_mma3(cudaStream_t st, const RmxTables& T, const RmxDims& d,
     A.g0 = g0; A.gn = gn; A.ntiles = 1; A.fexp = fexp; A.mF = mF; A.ahat = ahat; A.bhat = bhat;
     A.chain_logz = chain_logz; A.dflags = dflags;
     A.bc = bc; A.didx = didx; A.BC = BC; A.KBB = KBB; A.ND = ND;
+    A.cord = nullptr; A.cstart = nullptr;
     if (d.S > 128 && d.S <= 168) return launch_chain_mma3_cfg<42, 7, 3, 24>(st, A);     // max copy number 8, M = 3: S = 165
     return 2;
 }
@@ -624,34 +627,63 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
             const double* wg = wtab + gid * MD;
             const double w0 = wg[d0];
             const double* ug = uc + gid * 4;
-            // (measured alternative: input states outermost with the thread's 2 NBW columns side by side -- twelve
-            // independent chains instead of one -- is SLOWER, 20 ms against 16.5 ms of the 65 ms launch: the two factor
-            // look-ups per pair then hit shared memory from eight different per-fit tables at once)
+            // Rows in class order (states grouped by the tuple of their tumour-clone totals: A.cord / A.cstart, the
+            // tables of k_hist4): the per-fit factor is constant within a class, so a class costs its
+            // sum_i u[g][i] flipE[i][j] -- one L2 load and one FMA per pair -- and ONE factor per output column.
+            // (Per pair with two table look-ups each, this path was 25 % of the launch for 1.8 % of the rows; the
+            // twelve columns of a thread side by side were slower still: eight per-fit tables hit at once.)
+            const uint16_t* co = A.cord;
+            const int* cs = A.cstart;
+            const int NCLS = cs[0];
+            int bj[NBW][2][RMX_MAXM];
+            const double* fcol[NBW][2];
 #pragma unroll
-            for (int h = 0; h < NBW; ++h) {
-                if (h < nbw) {
+            for (int h = 0; h < NBW; ++h)
 #pragma unroll
-                    for (int q = 0; q < 2; ++q) {
-                        const int j = jbase + 8 * h + 2 * tig + q;
-                        if (j < S) {
-                            int off[RMX_MAXM];
+                for (int q = 0; q < 2; ++q) {
+                    const int j = min(jbase + 8 * h + 2 * tig + q, S - 1);      // columns outside: a valid address, never stored
+                    fcol[h][q] = FE + j;
+#pragma unroll
+                    for (int m = 1; m < RMX_MAXM; ++m) bj[h][q][m] = (m < M) ? m * d.D + d.doff - sgn * (int)tots[j * M + m] : 0;
+                }
+            double o[NBW][2];
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) o[h][0] = o[h][1] = 0.;
+            for (int cl = 0; cl < NCLS; ++cl) {
+                double acc[NBW][2];
+#pragma unroll
+                for (int h = 0; h < NBW; ++h) acc[h][0] = acc[h][1] = 0.;
+                const int k0 = __ldg(cs + cl + 1), k1 = __ldg(cs + cl + 2);
+                for (int k = k0; k < k1; ++k) {
+                    const int i = __ldg(co + k);
+                    const double ui = ug[((i >> 2) << 5) + (i & 3)];
+                    const int64_t ro = (int64_t)i * S;
+#pragma unroll
+                    for (int h = 0; h < NBW; ++h)
+                        if (h < nbw) {
+                            acc[h][0] = fma(ui, __ldg(fcol[h][0] + ro), acc[h][0]);
+                            acc[h][1] = fma(ui, __ldg(fcol[h][1] + ro), acc[h][1]);
+                        }
+                }
+                const int irep = __ldg(co + k0);
+                int ti[RMX_MAXM];
+#pragma unroll
+                for (int m = 1; m < RMX_MAXM; ++m) ti[m] = (m < M) ? sgn * (int)tots[irep * M + m] : 0;
+#pragma unroll
+                for (int h = 0; h < NBW; ++h)
+                    if (h < nbw) {
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            double e = acc[h][q];
 #pragma unroll
                             for (int m = 1; m < RMX_MAXM; ++m)
-                                if (m < M) off[m] = m * d.D + d.doff - sgn * (int)tots[j * M + m];
-                            double acc = 0.;
-#pragma unroll 4
-                            for (int i = 0; i < S; ++i) {
-                                double e = __ldg(FE + (int64_t)i * S + j);
-#pragma unroll
-                                for (int m = 1; m < RMX_MAXM; ++m)
-                                    if (m < M) e *= wg[off[m] + sgn * (int)tots[i * M + m]];
-                                acc = fma(ug[((i >> 2) << 5) + (i & 3)], e, acc);
-                            }
-                            c[h][q] = acc * w0;
+                                if (m < M) e *= wg[bj[h][q][m] + ti[m]];
+                            o[h][q] += e;
                         }
                     }
-                }
             }
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) { c[h][0] = o[h][0] * w0; c[h][1] = o[h][1] * w0; }
         }
         // ---- the segment's f (landed long ago), the next copies, the next row descriptor
         asm volatile("cp.async.wait_group %0;" ::"n"(C3_FST - 2) : "memory");
@@ -737,14 +769,16 @@ static int launch_chain_mma_s_cfg(cudaStream_t st, Chain3Args& A) {
 // returns 0 on success, 1 if the configuration or the launch failed, 2 if this kernel does not cover the shape
 int rmx_launch_chain_mma_s(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
                            const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
-                           const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags) {
+                           const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags,
+                           const uint16_t* cord, const int* cstart) {
     if (ch.NC <= 0 || gn <= 0) return 0;
-    if (rinfo == nullptr || d.M > RMX_MAXM) return 2;
+    if (rinfo == nullptr || d.M > RMX_MAXM || cord == nullptr || cstart == nullptr) return 2;
     Chain3Args A;
     A.d = d; A.ch = ch; A.rinfo = rinfo; A.sp = sp; A.sp_fit_stride = sp_fit_stride; A.tab = T.tab;
     A.g0 = g0; A.gn = gn; A.ntiles = 1; A.fexp = fexp; A.mF = mF; A.ahat = ahat; A.bhat = bhat;
     A.chain_logz = chain_logz; A.dflags = dflags;
     A.bc = nullptr; A.didx = nullptr; A.BC = 0; A.KBB = 0; A.ND = 0;
+    A.cord = cord; A.cstart = cstart;
     if (d.S > 168 && d.S <= 360) return launch_chain_mma_s_cfg<90, 8, 6>(st, A);     // max copy number 9 .. 12, M = 3
     return 2;
 }

@@ -127,7 +127,8 @@ int rmx_launch_chain_mma3(cudaStream_t st, const RmxTables& T, const RmxDims& d,
 // loaded under the DMMA stream
 int rmx_launch_chain_mma_s(cudaStream_t st, const RmxTables& T, const RmxDims& d, const RmxChains& ch, const int* rinfo,
                            const RmxTransSpec& sp, int64_t sp_fit_stride, int g0, int gn, const double* fexp,
-                           const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags);
+                           const double* mF, double* ahat, double* bhat, double* chain_logz, int* dflags,
+                           const uint16_t* cord, const int* cstart);
 void rmx_launch_post(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* ahat, const double* bhat,
                      double* post, int* dflags);
 void rmx_launch_hist(cudaStream_t st, const RmxTables& T, const RmxDims& d, int g0, int gn, int R, const RmxRows& rows,
