@@ -2092,10 +2092,11 @@ int rmx_mstep_stage_rows(rmx_handle m, const int32_t* rows, const int32_t* count
     }
     b->ms_all = false;
     b->ms_rmax = rmax;
-    for (int g = 0; g < G; ++g)
-        if (b->ms_count[g] > 0)
-            CK(cudaMemcpyAsync(b->ms_rows + (size_t)g * N, b->hrows + (size_t)g * N, (size_t)b->ms_count[g] * sizeof(int),
-                               cudaMemcpyHostToDevice, b->stream));
+    // one strided copy for all fits (the caller's (G, max_rows) block into the (G, N) row lists; entries beyond a fit's
+    // count are not read); the stream is synchronised before this call returns
+    if (rmax > 0)
+        CK(cudaMemcpy2DAsync(b->ms_rows, (size_t)N * sizeof(int), rows, (size_t)max_rows * sizeof(int32_t),
+                             (size_t)rmax * sizeof(int), (size_t)G, cudaMemcpyHostToDevice, b->stream));
     for (int g = 0; g < G; ++g) b->hRn[g] = b->ms_count[g];
     CK(cudaMemcpyAsync(b->ms_Rn_all, b->hRn, (size_t)G * sizeof(int), cudaMemcpyHostToDevice, b->stream));
     if (rmx_ell_sample_ok(rmax)) {

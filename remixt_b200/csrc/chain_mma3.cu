@@ -568,10 +568,9 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
             // rows beyond it exist in the last row block only and are zeroed there.
             const double* Ep = A.sp.Emat + (int64_t)cls * SS + (int64_t)tig * S + jbase + gid;
             const int kfull = S >> 2;
-            // register pipeline, four row blocks deep: the loads of block kb + 4 are issued before the DMMAs of block kb
-            // (an L2 hit takes ~300 cycles, a row block of DMMAs ~190 with two warps per sub-partition; left to itself
-            // the compiler put each load six instructions ahead of its DMMA: 46 % of all stall samples long-scoreboard)
-            double q0[NBW], q1[NBW], q2[NBW], q3[NBW];
+            // register pipeline: the loads of block kb + 8 are issued before the DMMAs of block kb (left to itself the
+            // compiler put each load six instructions ahead of its DMMA: 46 % of all stall samples long-scoreboard)
+            double q0[NBW], q1[NBW], q2[NBW], q3[NBW], q4[NBW], q5[NBW], q6[NBW], q7[NBW];
             auto ldblk = [&](double* q, const double* p) {
 #pragma unroll
                 for (int h = 0; h < NBW; ++h) q[h] = (h < nbw) ? __ldg(p + 8 * h) : 0.;
@@ -583,12 +582,15 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
                     if (h < nbw) c3_dmma(c[h][0], c[h][1], a, q[h]);
             };
             const int64_t rs = 4 * (int64_t)S;
-            const int k4 = kfull & ~3;
+            // eight row blocks deep (four were not enough: ncu put 27 % of all stall samples on the first DMMA of a
+            // block waiting for its operand -- under this load an L2 hit outlasts four blocks of DMMAs, ~770 cycles)
+            const int k4 = kfull & ~7;
             if (k4 > 0) {
                 ldblk(q0, Ep); ldblk(q1, Ep + rs); ldblk(q2, Ep + 2 * rs); ldblk(q3, Ep + 3 * rs);
-                const double* En = Ep + 4 * rs;
-                for (int kb = 0; kb < k4; kb += 4) {
-                    const bool more = kb + 4 < k4;
+                ldblk(q4, Ep + 4 * rs); ldblk(q5, Ep + 5 * rs); ldblk(q6, Ep + 6 * rs); ldblk(q7, Ep + 7 * rs);
+                const double* En = Ep + 8 * rs;
+                for (int kb = 0; kb < k4; kb += 8) {
+                    const bool more = kb + 8 < k4;
                     mmablk(q0, kb);
                     if (more) ldblk(q0, En);
                     mmablk(q1, kb + 1);
@@ -597,7 +599,15 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma_s(Chain3Args A) {
                     if (more) ldblk(q2, En + 2 * rs);
                     mmablk(q3, kb + 3);
                     if (more) ldblk(q3, En + 3 * rs);
-                    En += 4 * rs;
+                    mmablk(q4, kb + 4);
+                    if (more) ldblk(q4, En + 4 * rs);
+                    mmablk(q5, kb + 5);
+                    if (more) ldblk(q5, En + 5 * rs);
+                    mmablk(q6, kb + 6);
+                    if (more) ldblk(q6, En + 6 * rs);
+                    mmablk(q7, kb + 7);
+                    if (more) ldblk(q7, En + 7 * rs);
+                    En += 8 * rs;
                 }
             }
             Ep += (int64_t)k4 * rs;

@@ -22,6 +22,7 @@ def main():
     st = pstats.Stats(pr)
     st.sort_stats('cumulative').print_stats(45)
     st.sort_stats('tottime').print_stats(25)
+    st.sort_stats('cumulative').print_stats('pipeline.py|cn_model.py|bpmodel.py|results.py|_lib.py')
 
 
 if __name__ == '__main__':
