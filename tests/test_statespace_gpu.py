@@ -100,6 +100,19 @@ def test_four_clones():
     _compare(cu, ref, rounds=1)
 
 
+def test_four_clones_max_copy_number_8():
+    """SURVEY.md section 8's stress state space: three tumour clones + normal at max_copy_number 8 -> S = 805, B = 57
+    (the literal reading of BASELINE config 3).  24 segments against the numpy oracle (three (N-1, S, S) arrays of
+    0.12 GB): the vector-pipe chain kernel, the first-generation histograms, the unfused round."""
+    from oracle import bpmodel_np
+    ip = util.init_params('small', 1)
+    h = np.array([ip['h_normal'], 0.5 * ip['h_tumour'], 0.3 * ip['h_tumour'], 0.2 * ip['h_tumour']])
+    cu, ref = _drive(_sub(24), h, bpmodel_np.RemixtModel, max_copy_number=8,
+                     max_depth=2. * ip['h_normal'] + 8.25 * ip['h_tumour'])
+    assert cu.num_clones == 4 and cu.num_cn_states == 805
+    _compare(cu, ref, rounds=1)
+
+
 def _chromosome(name, chrom):
     """One whole chromosome of a fixture as its own experiment (breakpoints with both ends on it)."""
     sys.path.insert(0, util.ROOT)
