@@ -437,11 +437,19 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         else:
             for g, d in enumerate(drivers):
                 d.attach(batch.fit(g))
-    elbo = batch.calculate_elbo()
-    for g, d in enumerate(drivers):
-        d.prev_elbo = float(elbo[g])
     num_em_iter = get_param(config, 'num_em_iter')
     num_update_iter = get_param(config, 'num_update_iter')
+    # The ELBO of the starting state (cn_model.py:407) only ever enters the FIRST iteration's `elbo_diff`; with two or
+    # more EM iterations nothing `fit` returns depends on it.  On the GPU it is the one expensive ELBO of a fit (the
+    # uniform pair posteriors of the constructor state take the general pair sums over every row: 42 ms for the
+    # 48-fit config-2 grid, 6 % of the whole fit), so it is evaluated only when it is observable.
+    if model_class is not None or num_em_iter < 2 or trace is not None or any(d.verbose for d in drivers):
+        elbo = batch.calculate_elbo()
+        for g, d in enumerate(drivers):
+            d.prev_elbo = float(elbo[g])
+    else:
+        for d in drivers:
+            d.prev_elbo = float('nan')
     errors = {}         # fit index -> exception
     lock = _mstep.GridMStep(backend, drivers, errors)
     prof['build'] += time.perf_counter() - t0
