@@ -500,11 +500,19 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         brk = decode_breakpoints_grid(d0, cn, np.asarray(batch.brk_states), abs(d0.transition_log_prob))
         h_all, pot, poa = np.array(batch.h), batch.p_outlier_total, batch.p_outlier_allele
         par = dict((name, np.array(getattr(batch, name))) for name in d0.likelihood_params)
+        as_int = {}          # the masks are usually the same for the whole grid: convert each distinct one once
+
+        def mask_int(a):
+            key = a.tobytes()
+            if key not in as_int:
+                as_int[key] = a.astype(int)
+            return as_int[key]
+
         for g, d in enumerate(drivers):
             pre[g] = dict(brk_cn=brk[g], h=h_all[g], p_outlier_total=pot[g], p_outlier_allele=poa[g],
                           params=dict((name, float(par[name][g])) for name in d0.likelihood_params),
-                          total_likelihood_mask=d._total_likelihood_mask.astype(int),
-                          allele_likelihood_mask=d._allele_likelihood_mask.astype(int))
+                          total_likelihood_mask=mask_int(d._total_likelihood_mask),
+                          allele_likelihood_mask=mask_int(d._allele_likelihood_mask))
     todo = [g for g in range(len(drivers)) if g not in errors]
 
     def assemble(g):
