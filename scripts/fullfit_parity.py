@@ -82,12 +82,20 @@ def reference_self_sensitivity(name):
 
 
 def run(name, mstep='lockstep'):
+    """`name` is a fixture (`small`, `config1`) or a fixture with the tag of a golden grid at another maximum copy
+    number (`small_cn8`, `small_cn12`: tests/golden/grid_small_cn8.npz ...), fitted on the initialisations it holds."""
     from remixt_b200 import pipeline
-    g = util.golden('grid_%s.npz' % name)
+    full = name
+    g = util.golden('grid_%s.npz' % full)
+    name = full.split('_cn')[0]
     exp = util.load_experiment(name)
-    n = util.num_inits(name)
-    inits = dict((i, util.init_params(name, i)) for i in range(n))
-    cfg = {'max_copy_number': 6, 'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
+    if full == name:
+        ids = range(util.num_inits(name))
+    else:
+        ids = sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))
+    inits = dict((i, util.init_params(name, i)) for i in ids)
+    cfg = {'max_copy_number': int(g['max_copy_number']) if 'max_copy_number' in g.files else 6,
+           'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
     prof = {}
     t0 = time.perf_counter()
     trace = []
@@ -107,17 +115,18 @@ def run(name, mstep='lockstep'):
         # trajectory: relative deviation of (h, dispersions, ELBO) from the reference after every EM iteration
         k = gi.index(i)
         rel = lambda a, b: float(np.max(np.abs(np.asarray(a, float) - np.asarray(b, float)) / np.maximum(np.abs(np.asarray(b, float)), 1e-300)))
-        row['trajectory_rel_dev'] = [[rel(t[0][i], g['trace_h'][k][e]), rel(t[1][i], g['trace_params'][k][e]),
-                                      rel(t[2][i], g['trace_elbo'][k][e])] for e, t in enumerate(trace)]
+        pos = list(ids).index(i)      # position of the fit in the batch (the trace rows)
+        row['trajectory_rel_dev'] = [[rel(t[0][pos], g['trace_h'][k][e]), rel(t[1][pos], g['trace_params'][k][e]),
+                                      rel(t[2][pos], g['trace_elbo'][k][e])] for e, t in enumerate(trace)]
         row['margins'] = [float(m) for m in cand['margins']]
         rows.append(row)
     out = {
-        'fixture': name, 'mstep': mstep, 'wall_s': wall, 'profile': prof,
+        'fixture': full, 'max_copy_number': cfg['max_copy_number'], 'mstep': mstep, 'wall_s': wall, 'profile': prof,
         'selected_init': {'reference': int(g['best_init_id']), 'b200': None if best is None else int(best),
                           'equal': best is not None and int(best) == int(g['best_init_id'])},
         'failed_inits': {'reference': [int(i) for i in g['failed_ids']], 'b200': sorted(int(i) for i in errors)},
         'summary': summarise(rows),
-        'reference_self_sensitivity': reference_self_sensitivity(name),
+        'reference_self_sensitivity': reference_self_sensitivity(full),
         'fits': rows,
     }
     sel = [r for r in rows if r['init_id'] == int(g['best_init_id'])]
