@@ -89,10 +89,7 @@ def run(name, mstep='lockstep'):
     g = util.golden('grid_%s.npz' % full)
     name = full.split('_cn')[0]
     exp = util.load_experiment(name)
-    if full == name:
-        ids = range(util.num_inits(name))
-    else:
-        ids = sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))
+    ids = sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))        # what the reference fitted
     inits = dict((i, util.init_params(name, i)) for i in ids)
     cfg = {'max_copy_number': int(g['max_copy_number']) if 'max_copy_number' in g.files else 6,
            'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}

@@ -101,7 +101,7 @@ def _grid(name, tag=''):
     from remixt_b200 import pipeline
     g = util.golden('grid_%s%s.npz' % (name, tag))
     exp = util.load_experiment(name)
-    ids = range(util.num_inits(name)) if not tag else sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))
+    ids = sorted(int(i) for i in list(g['init_ids']) + list(g['failed_ids']))     # the initialisations the reference fitted
     inits = dict((i, util.init_params(name, i)) for i in ids)
     cfg = {'max_copy_number': int(g['max_copy_number']) if 'max_copy_number' in g.files else 6,
            'num_em_iter': int(g['num_em_iter']), 'num_update_iter': int(g['num_update_iter'])}
@@ -168,6 +168,22 @@ def test_free_running_fits_in_larger_state_spaces(tag):
     --cnmax 8 | 12) and here: same selected initialisation, its MAP output bit-exact, and every fit whose M-step
     decisions match the reference's agrees bit-exactly."""
     g, res, best, errors = _grid('small', tag)
+    assert len(errors) <= 1 and best not in errors
+    assert best == int(g['best_init_id'])
+    rows = _agreement(g, res)
+    sel = rows[best]
+    assert sel['map_exact'] and sel['brk_exact'] and sel['decisions'] and sel['elbo'] < 1e-6
+    same = [i for i, r in rows.items() if r['decisions']]
+    assert len(same) >= len(rows) - 2
+    for i in same:
+        assert rows[i]['map_exact'] and rows[i]['brk_exact'] and rows[i]['elbo'] < 1e-6, i
+
+
+def test_free_running_fits_on_a_whole_chromosome_of_config2():
+    """Chromosome 1 of the config-2 genome (2522 segments, the longest chain of the benched workload) as its own
+    experiment (oracle/make_chromosome_fixture.py): six initialisations of config 2's grid fitted free-running by the
+    reference (about six minutes each) and here."""
+    g, res, best, errors = _grid('config2chr1')
     assert len(errors) <= 1 and best not in errors
     assert best == int(g['best_init_id'])
     rows = _agreement(g, res)
