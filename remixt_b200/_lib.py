@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libremixt_b200.so")
+# REMIXT_B200_LIB names another build of the same library (A/B measurements of a kernel change on one GPU box)
+LIB_PATH = os.environ.get("REMIXT_B200_LIB") or os.path.join(_HERE, "libremixt_b200.so")
 
 RMX_OK, RMX_ERR_CUDA, RMX_ERR_VALUE, RMX_ERR_ASSERT, RMX_ERR_UNSUPPORTED, RMX_ERR_ARG = range(6)
 

@@ -68,9 +68,12 @@ struct C2Cfg {
     static constexpr int NSLOT = 2 * NBW;       // f values per thread and segment (the helper warp uses slot 0)
 };
 
-template <int KB, int NBW, bool LONE>
-__global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain2Args A) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+// The sweep of one (chain, direction, tile of 8 fits).  The direction is a template parameter: every "forward or
+// backward" choice of the per-segment code (what is stored, which way the pointers walk, how the class-difference table
+// is indexed) is folded at compile time instead of costing selects and moves on the serial path of the one warp a
+// sub-partition has.
+template <int KB, int NBW, bool LONE, int DIR>
+__device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* smem_raw) {
     using Cfg = C2Cfg<KB, NBW, LONE>;
     constexpr int T = Cfg::T, NSLOT = Cfg::NSLOT;
     const RmxDims& d = A.d;
@@ -99,7 +102,8 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
 
     const int tile = blockIdx.x % A.ntiles;
     const int cd = blockIdx.x / A.ntiles;
-    const int dir = cd & 1, chain = A.ch.order[cd >> 1];
+    constexpr int dir = DIR;
+    const int chain = A.ch.order[cd >> 1];
     const int s0 = A.ch.start[chain], s1 = A.ch.end[chain];
     const int t = threadIdx.x, w = t >> 5, lane = t & 31;
     const int gid = lane >> 2, tig = lane & 3;     // mma fragment coordinates
@@ -109,21 +113,24 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
     const int gcount = min(C2_GT, A.g0 + A.gn - gbase);
     const int64_t SS = (int64_t)S * S;
     const int64_t NS = (int64_t)d.N * S;
-    const int sgn = dir == 0 ? 1 : -1;
+    constexpr int sgn = dir == 0 ? 1 : -1;
     const int jbase = helper ? jl : w * (8 * NBW);
     const bool fit_ok = gid < gcount;
     const int gfit = gbase + min(gid, gcount - 1);
-    // DMMA warps: C fragment = fit gid, columns j0[h], j0[h] + 1 of column block h; helper: fit gid, column jl (tig 0)
+    // DMMA warps: C fragment = fit gid, columns j0[h], j0[h] + 1 of column block h; helper: fit gid, column jl (tig 0).
+    // Rows of a partial tile beyond its last fit repeat that fit (gfit is clamped): they are computed like the others and
+    // only their stores to global memory are dropped, so the per-segment code carries no per-fit masking.  With a lone
+    // last state (LONE) the 32 NBW columns of the DMMA warps are all inside the state space and no column masking either.
     int upos[NBW];
     bool ok0[NBW], ok1[NBW];
 #pragma unroll
     for (int h = 0; h < NBW; ++h) {
         const int j0 = jbase + 8 * h + 2 * tig;
-        ok0[h] = !helper && fit_ok && j0 < S;
-        ok1[h] = !helper && fit_ok && j0 + 1 < S;
+        ok0[h] = !helper && (LONE || j0 < S);
+        ok1[h] = !helper && (LONE || j0 + 1 < S);
         upos[h] = c2_pos(gid, j0);                 // j0 even: j0, j0+1 adjacent, 16-byte aligned
     }
-    const bool hok = helper && fit_ok && tig == 0;
+    const bool hok = helper && tig == 0;
 
     for (int e = t; e < 2 * KB * 32; e += T) u[e] = 0.;
     for (int e = t; e < 2 * C2_GT * C2_NW; e += T) redi[e] = ((e % C2_NW) == 0) ? 1023 : 0;   // first message: max f = 1
@@ -142,18 +149,19 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
     const int rowstep = sgn * S;
 
     // ---- first segment of the sweep: u = f (forward: ahat = f; backward: bhat = 1)
-    double un[NBW][2];
 #pragma unroll
     for (int h = 0; h < NBW; ++h) {
-        un[h][0] = un[h][1] = 0.;
-        if (ok0[h]) { un[h][0] = fp[8 * h]; outp[8 * h] = dir == 0 ? un[h][0] : 1.; }
-        if (ok1[h]) { un[h][1] = fp[8 * h + 1]; outp[8 * h + 1] = dir == 0 ? un[h][1] : 1.; }
-        if (ok0[h]) *reinterpret_cast<double2*>(u + upos[h]) = make_double2(un[h][0], un[h][1]);
+        double u0 = 0., u1 = 0.;
+        if (ok0[h]) u0 = fp[8 * h];
+        if (ok1[h]) u1 = fp[8 * h + 1];
+        if (ok0[h] && fit_ok) outp[8 * h] = dir == 0 ? u0 : 1.;
+        if (ok1[h] && fit_ok) outp[8 * h + 1] = dir == 0 ? u1 : 1.;
+        if (ok0[h]) *reinterpret_cast<double2*>(u + upos[h]) = make_double2(u0, u1);
     }
     if (hok) {
-        un[0][0] = fp[0];
-        outp[0] = dir == 0 ? un[0][0] : 1.;
-        u[c2_pos(gid, jl)] = un[0][0];
+        const double u0 = fp[0];
+        if (fit_ok) outp[0] = dir == 0 ? u0 : 1.;
+        u[c2_pos(gid, jl)] = u0;
     }
     auto row_of = [&](int k) { return dir == 0 ? s0 + k : s1 - 1 - k; };       // transition row of step k
     // software pipeline: f C2_FST - 1 segments ahead through the shared-memory ring, row info two rows ahead
@@ -235,18 +243,14 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
         auto finish_block = [&](int h, double c0, double c1) {
             const double sc = c2_pow2(be);
             double v0 = c0 * sc, v1 = c1 * sc;
-            if (dir == 0) {
-                v0 *= f[h][0]; v1 *= f[h][1];
-                un[h][0] = v0; un[h][1] = v1;
-            } else {
-                un[h][0] = v0 * f[h][0]; un[h][1] = v1 * f[h][1];
-            }
-            if (!ok0[h]) un[h][0] = 0.;
-            if (!ok1[h]) un[h][1] = 0.;
-            if (ok0[h]) outp[8 * h] = v0;
-            if (ok1[h]) outp[8 * h + 1] = v1;
-            if (ok0[h]) *reinterpret_cast<double2*>(u + (cur ^ 1) * KB * 32 + upos[h]) = make_double2(un[h][0], un[h][1]);
-            mx = max(mx, max(c2_expfield(un[h][0]), c2_expfield(un[h][1])));
+            double u0 = v0 * f[h][0], u1 = v1 * f[h][1];      // the message passed on; forward it is also what is stored
+            if (dir == 0) { v0 = u0; v1 = u1; }
+            if (!ok0[h]) u0 = 0.;
+            if (!ok1[h]) u1 = 0.;
+            if (ok0[h] && fit_ok) outp[8 * h] = v0;
+            if (ok1[h] && fit_ok) outp[8 * h + 1] = v1;
+            if (ok0[h]) *reinterpret_cast<double2*>(u + (cur ^ 1) * KB * 32 + upos[h]) = make_double2(u0, u1);
+            mx = max(mx, max(c2_expfield(u0), c2_expfield(u1)));
         };
 
         if (br < 0) {
@@ -274,26 +278,28 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
                 cur_class = cls;
             }
             if (!helper) {
-                // column block after column block: the epilogue of block h runs under the DMMAs of block h + 1, so only
-                // the last block's epilogue is exposed; the bookkeeping sits under the DMMAs of block 0
-                double pc0 = 0., pc1 = 0.;
+                // Row blocks outermost: one A fragment (one shared-memory load) feeds the DMMAs of all NBW column blocks,
+                // so consecutive DMMAs belong to different accumulators by construction.  (Column block after column
+                // block, with the even and odd row blocks of a block on two accumulators, let the epilogue of block h
+                // run under the DMMAs of block h + 1 -- but ptxas re-ordered the DMMAs of a block into its two dependent
+                // chains, 26 instead of 16 cycles per DMMA; a last block lagging behind the others was clumped the same
+                // way.)  The bookkeeping sits under the first DMMAs; the NBW epilogues are independent of each other and
+                // pipeline after the last DMMA.  Every accumulator sums the row blocks it summed before (even / odd row
+                // blocks of a column block, added at the end): same values bit for bit.
+                double acc[NBW][2][2];
 #pragma unroll
-                for (int h = 0; h < NBW; ++h) {
-                    double c0 = 0., c1 = 0., e0 = 0., e1 = 0.;
+                for (int h = 0; h < NBW; ++h) acc[h][0][0] = acc[h][0][1] = acc[h][1][0] = acc[h][1][1] = 0.;
 #pragma unroll
-                    for (int kb = 0; kb < KB; ++kb) {
-                        const double a = uc[kb * 32 + lane];
-                        if (kb & 1) c2_dmma(e0, e1, a, ereg[h][kb]);
-                        else c2_dmma(c0, c1, a, ereg[h][kb]);
-                        if (h == 0 && kb == (KB > 6 ? 2 : 0)) chores(0);
-                        if (h == 0 && kb == (KB > 12 ? 6 : 0)) chores(1);
-                        if (h == 0 && kb == (KB > 18 ? 12 : 0)) chores(2);
-                        if (h > 0 && kb == (KB > 6 ? 3 : 0)) finish_block(h - 1, pc0, pc1);   // under this block's DMMAs
-                    }
-                    pc0 = c0 + e0;
-                    pc1 = c1 + e1;
+                for (int kb = 0; kb < KB; ++kb) {
+                    const double a = uc[kb * 32 + lane];
+#pragma unroll
+                    for (int h = 0; h < NBW; ++h) c2_dmma(acc[h][kb & 1][0], acc[h][kb & 1][1], a, ereg[h][kb]);
+                    if (kb == (KB > 6 ? 2 : 0)) chores(0);
+                    if (kb == (KB > 12 ? 6 : 0)) chores(1);
+                    if (kb == (KB > 18 ? 12 : 0)) chores(2);
                 }
-                finish_block(NBW - 1, pc0, pc1);
+#pragma unroll
+                for (int h = 0; h < NBW; ++h) finish_block(h, acc[h][0][0] + acc[h][1][0], acc[h][0][1] + acc[h][1][1]);
             } else {
                 // the lone last state: out[g][jl] = sum_i u[g][i] E[i][jl], lane (g, q) takes rows i = q mod 4
                 chores(0);
@@ -410,14 +416,14 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
             }
         } else {
             double v0 = c[0][0] * c2_pow2(be);
-            if (dir == 0) { v0 *= f[0][0]; un[0][0] = v0; }
-            else un[0][0] = v0 * f[0][0];
-            if (!hok) un[0][0] = 0.;
+            double u0 = v0 * f[0][0];
+            if (dir == 0) v0 = u0;
+            if (!hok) u0 = 0.;
             if (hok) {
-                outp[0] = v0;
-                u[(cur ^ 1) * KB * 32 + c2_pos(gid, jl)] = un[0][0];
+                if (fit_ok) outp[0] = v0;
+                u[(cur ^ 1) * KB * 32 + c2_pos(gid, jl)] = u0;
             }
-            mx = c2_expfield(un[0][0]);
+            mx = c2_expfield(u0);
         }
         mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
         mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
@@ -428,12 +434,20 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
 
     // ---- log normaliser of the forward sweep: log(sum of the last message) + ln2 * esum + sum_n max F[n]
     {
+        // the last message, read back from its shared-memory copy (entries outside the state space are zero there):
+        // keeping it in registers through the sweep costs twelve registers the per-segment code needs
+        const double* ul = u + cur * KB * 32;
         double sv = 0.;
         if (!helper) {
 #pragma unroll
-            for (int h = 0; h < NBW; ++h) sv += un[h][0] + un[h][1];
+            for (int h = 0; h < NBW; ++h) {
+                if (ok0[h]) {
+                    const double2 q = *reinterpret_cast<const double2*>(ul + upos[h]);
+                    sv += q.x + q.y;
+                }
+            }
         } else {
-            sv = tig == 0 ? un[0][0] : 0.;
+            sv = tig == 0 ? ul[c2_pos(gid, jl)] : 0.;
         }
         sv += __shfl_xor_sync(0xffffffffu, sv, 1);
         sv += __shfl_xor_sync(0xffffffffu, sv, 2);
@@ -458,6 +472,13 @@ __global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain
         if (!(slast > 0.) || isinf(slast)) bad = 1;
         if (bad) atomicOr(A.dflags, RMX_F_MSG_NAN);
     }
+}
+
+template <int KB, int NBW, bool LONE>
+__global__ void __launch_bounds__(C2Cfg<KB, NBW, LONE>::T, 1) k_chain_mma2(Chain2Args A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (((blockIdx.x / A.ntiles) & 1) == 0) c2_sweep<KB, NBW, LONE, 0>(A, smem_raw);
+    else c2_sweep<KB, NBW, LONE, 1>(A, smem_raw);
 }
 
 template <int KB, int NBW, bool LONE>
