@@ -21,14 +21,16 @@
 //   * pointers advance by one row per segment instead of 64-bit index products.
 // The arithmetic (scaling by exact powers of two, order of the accumulations over row blocks) is that of chain_mma.cu.
 #include "common.cuh"
+#ifdef C2_PROFILE
+#include <cstdio>
+#endif
 #include "kernels.h"
 
 #define C2_GT 8          // fits per CTA (the M dimension of m8n8k4)
-#define C2_NW 8          // slots of the per-warp exponent maxima
+#define C2_NW 20         // slots of a fit's exponent maxima: one per (warp, thread of the quad), up to 5 warps
 #define C2_FST 4         // stages of the f ring (cp.async prefetch distance + 1)
 #define C2_RIMAX 8192    // chains up to this many rows keep their row descriptors in shared memory
 
-__device__ __forceinline__ int c2_expfield(double v) { return (__double2hiint(v) >> 20) & 0x7ff; }
 __device__ __forceinline__ double c2_pow2(int be) { return __hiloint2double((2046 - be) << 20, 0); }
 __device__ __forceinline__ void c2_dmma(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -81,7 +83,7 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
     double* u = reinterpret_cast<double*>(smem_raw);                  // [2][KB*32]
     double* wtab = u + 2 * KB * 32;                                    // [8][MD]   breakend tables of the step
     double* redd = wtab + C2_GT * MD;                                  // [8][C2_NW] + [8] mF sums
-    int* redi = reinterpret_cast<int*>(redd + C2_GT * C2_NW + C2_GT);  // [2][8][C2_NW] max exponent fields
+    unsigned* redi = reinterpret_cast<unsigned*>(redd + C2_GT * C2_NW + C2_GT);  // [2][8][C2_NW] largest high words (as unsigned: a NaN is the largest)
     int8_t* tots = reinterpret_cast<int8_t*>(redi + 2 * C2_GT * C2_NW);   // [S*M]
     // f ring: [C2_FST stages][NSLOT][T] doubles, every thread copies its own entries with cp.async (own slots only)
     double* fring = reinterpret_cast<double*>(smem_raw + ((sizeof(double) * ((size_t)2 * KB * 32 + (size_t)C2_GT * MD + C2_GT * C2_NW + C2_GT) +
@@ -121,19 +123,23 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
     // Rows of a partial tile beyond its last fit repeat that fit (gfit is clamped): they are computed like the others and
     // only their stores to global memory are dropped, so the per-segment code carries no per-fit masking.  With a lone
     // last state (LONE) the 32 NBW columns of the DMMA warps are all inside the state space and no column masking either.
-    int upos[NBW];
+    // position of column block 0 in the message buffer (j0 even: j0, j0 + 1 adjacent, 16-byte aligned); block h is 64
+    // doubles further (jbase is a multiple of 8), so one address register serves all blocks
+    const int upos0 = c2_pos(gid, (helper ? 0 : jbase) + 2 * tig);
     bool ok0[NBW], ok1[NBW];
 #pragma unroll
     for (int h = 0; h < NBW; ++h) {
         const int j0 = jbase + 8 * h + 2 * tig;
         ok0[h] = !helper && (LONE || j0 < S);
         ok1[h] = !helper && (LONE || j0 + 1 < S);
-        upos[h] = c2_pos(gid, j0);                 // j0 even: j0, j0+1 adjacent, 16-byte aligned
     }
     const bool hok = helper && tig == 0;
 
     for (int e = t; e < 2 * KB * 32; e += T) u[e] = 0.;
-    for (int e = t; e < 2 * C2_GT * C2_NW; e += T) redi[e] = ((e % C2_NW) == 0) ? 1023 : 0;   // first message: max f = 1
+    // the exponent exchange: every thread leaves the largest HIGH WORD of the message entries it produced (the entries
+    // are non-negative, so the integer order of the high words is the order of the values) in its own slot of its fit;
+    // the reader takes the maximum of the fit's slots and its exponent field.  No shuffles on the serial path.
+    for (int e = t; e < 2 * C2_GT * C2_NW; e += T) redi[e] = ((e % C2_NW) == 0) ? 0x3ff00000 : 0;   // first message: max f = 1
     for (int e = t; e < S * M; e += T) {
         int s = e / M, m = e - s * M;
         tots[e] = (m == 0) ? 0 : (int8_t)(A.tab[(s * M + m) * 2] + A.tab[(s * M + m) * 2 + 1]);
@@ -156,7 +162,7 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
         if (ok1[h]) u1 = fp[8 * h + 1];
         if (ok0[h] && fit_ok) outp[8 * h] = dir == 0 ? u0 : 1.;
         if (ok1[h] && fit_ok) outp[8 * h + 1] = dir == 0 ? u1 : 1.;
-        if (ok0[h]) *reinterpret_cast<double2*>(u + upos[h]) = make_double2(u0, u1);
+        if (ok0[h]) *reinterpret_cast<double2*>(u + (upos0 + 64 * h)) = make_double2(u0, u1);
     }
     if (hok) {
         const double u0 = fp[0];
@@ -207,6 +213,14 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
     }
     int cur = 0, esum = 0, bad = 0;
 
+#ifdef C2_PROFILE
+    unsigned pt0 = 0, pd1 = 0, pd2 = 0, pd3 = 0, pd4 = 0, pd5 = 0, pn = 0;
+#ifdef C2_PROFILE2
+    unsigned pe1 = 0, pe2 = 0, pe3 = 0;
+#endif
+    auto pclk = []() { unsigned v; asm volatile("mov.u32 %0, %%clock;" : "=r"(v) :: "memory"); return v; };
+    pt0 = pclk();
+#endif
     for (int step = 0; step < nsteps; ++step) {
         outp += rowstep;
         const int ri = ri0;
@@ -214,8 +228,9 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
         const int cls = (ri & 0xff) - 1;
         const int br = (ri >> 12) - 1;
         const double* uc = u + cur * KB * 32;
-        double c[NBW][2], f[NBW][2];
+        double c[NBW][2], f[NBW][2];      // f: this segment's f values times the scale of the step
         int be = 1023;
+        double sc = 1.;
 #pragma unroll
         for (int h = 0; h < NBW; ++h) c[h][0] = c[h][1] = f[h][0] = f[h][1] = 0.;
 
@@ -223,34 +238,47 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
         auto chores = [&](int part) {
             if (part == 0) {
                 // exponent of the largest entry of the input message of fit gid (written before the last barrier)
-                const int4* rp = reinterpret_cast<const int4*>(redi + (cur * C2_GT + gid) * C2_NW);
-                const int4 r0 = rp[0], r1 = rp[1];
-                be = max(max(max(r0.x, r0.y), max(r0.z, r0.w)), max(max(r1.x, r1.y), max(r1.z, r1.w)));
+                const uint4* rp = reinterpret_cast<const uint4*>(redi + (cur * C2_GT + gid) * C2_NW);
+                unsigned mh = 0u;
+#pragma unroll
+                for (int q = 0; q < C2_NW / 4; ++q) {
+                    const uint4 r = rp[q];
+                    mh = max(mh, max(max(r.x, r.y), max(r.z, r.w)));
+                }
+                be = (int)((mh >> 20) & 0x7ffu);
+                sc = c2_pow2(be);
+                asm volatile("" : "+d"(sc));        // here, under the DMMAs, not in the epilogue
+                esum += be - 1023;
+                if (be <= 0 || be >= 2047) bad = 1;
             } else if (part == 1) {
                 asm volatile("cp.async.wait_group %0;" ::"n"(C2_FST - 2) : "memory");     // this step's f has landed
                 const double* fr = fring + ((step % C2_FST) * NSLOT) * T;
+                // f times the scale (a power of two: exact), so that the epilogue is one multiplication per entry
 #pragma unroll
-                for (int h = 0; h < NBW; ++h) { f[h][0] = fr[(h * 2) * T]; f[h][1] = fr[(h * 2 + 1) * T]; }
+                for (int h = 0; h < NBW; ++h) {
+                    f[h][0] = fr[(h * 2) * T] * sc;
+                    f[h][1] = fr[(h * 2 + 1) * T] * sc;
+                    asm volatile("" : "+d"(f[h][0]), "+d"(f[h][1]));
+                }
             } else {
                 f_issue();          // into the ring stage the previous step consumed
                 if (step + 2 < nsteps) ri1 = ri_at(step + 2);
             }
         };
 
-        int mx = 0;
+        unsigned mx = 0u;
         // epilogue of one column block (C-fragment layout): scale by the power of two that normalised the input message,
         // times f, store the message and pass it on in fragment order
         auto finish_block = [&](int h, double c0, double c1) {
-            const double sc = c2_pow2(be);
-            double v0 = c0 * sc, v1 = c1 * sc;
-            double u0 = v0 * f[h][0], u1 = v1 * f[h][1];      // the message passed on; forward it is also what is stored
-            if (dir == 0) { v0 = u0; v1 = u1; }
+            double u0 = c0 * f[h][0], u1 = c1 * f[h][1];      // the message passed on; forward it is also what is stored
             if (!ok0[h]) u0 = 0.;
             if (!ok1[h]) u1 = 0.;
-            if (ok0[h] && fit_ok) outp[8 * h] = v0;
-            if (ok1[h] && fit_ok) outp[8 * h + 1] = v1;
-            if (ok0[h]) *reinterpret_cast<double2*>(u + (cur ^ 1) * KB * 32 + upos[h]) = make_double2(u0, u1);
-            mx = max(mx, max(c2_expfield(u0), c2_expfield(u1)));
+#ifndef C2_NOSTG
+            if (ok0[h] && fit_ok) outp[8 * h] = dir == 0 ? u0 : c0 * sc;
+            if (ok1[h] && fit_ok) outp[8 * h + 1] = dir == 0 ? u1 : c1 * sc;
+#endif
+            if (ok0[h]) *reinterpret_cast<double2*>(u + (cur ^ 1) * KB * 32 + (upos0 + 64 * h)) = make_double2(u0, u1);
+            mx = max(mx, max((unsigned)__double2hiint(u0), (unsigned)__double2hiint(u1)));
         };
 
         if (br < 0) {
@@ -292,14 +320,28 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
 #pragma unroll
                 for (int kb = 0; kb < KB; ++kb) {
                     const double a = uc[kb * 32 + lane];
+#ifdef C2_PROFILE
+                    if (kb == 0) { asm volatile("" :: "d"(a)); unsigned q = pclk(); pd1 += q - pt0; pt0 = q; }
+#ifdef C2_PROFILE2
+                    if (kb == 4) { unsigned q = pclk(); pe1 += q - pt0; }
+                    if (kb == 8) { unsigned q = pclk(); pe2 += q - pt0; }
+                    if (kb == 14) { unsigned q = pclk(); pe3 += q - pt0; }
+#endif
+#endif
 #pragma unroll
                     for (int h = 0; h < NBW; ++h) c2_dmma(acc[h][kb & 1][0], acc[h][kb & 1][1], a, ereg[h][kb]);
                     if (kb == (KB > 6 ? 2 : 0)) chores(0);
                     if (kb == (KB > 12 ? 6 : 0)) chores(1);
                     if (kb == (KB > 18 ? 12 : 0)) chores(2);
                 }
+#ifdef C2_PROFILE
+                { unsigned q = pclk(); pd2 += q - pt0; pt0 = q; ++pn; }
+#endif
 #pragma unroll
                 for (int h = 0; h < NBW; ++h) finish_block(h, acc[h][0][0] + acc[h][1][0], acc[h][0][1] + acc[h][1][1]);
+#ifdef C2_PROFILE
+                { asm volatile("" :: "r"(mx)); unsigned q = pclk(); pd3 += q - pt0; pt0 = q; }
+#endif
             } else {
                 // the lone last state: out[g][jl] = sum_i u[g][i] E[i][jl], lane (g, q) takes rows i = q mod 4
                 chores(0);
@@ -407,30 +449,40 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
             }
         }
         // ---- what is left of the step
-        esum += be - 1023;
-        if (be <= 0 || be >= 2047) bad = 1;
         if (!helper) {
             if (br >= 0) {
 #pragma unroll
                 for (int h = 0; h < NBW; ++h) finish_block(h, c[h][0], c[h][1]);
             }
         } else {
-            double v0 = c[0][0] * c2_pow2(be);
-            double u0 = v0 * f[0][0];
-            if (dir == 0) v0 = u0;
+            double u0 = c[0][0] * f[0][0];
             if (!hok) u0 = 0.;
             if (hok) {
-                if (fit_ok) outp[0] = v0;
+                if (fit_ok) outp[0] = dir == 0 ? u0 : c[0][0] * sc;
                 u[(cur ^ 1) * KB * 32 + c2_pos(gid, jl)] = u0;
             }
-            mx = c2_expfield(u0);
+            mx = (unsigned)__double2hiint(u0);
         }
-        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-        if (tig == 0) redi[((cur ^ 1) * C2_GT + gid) * C2_NW + w] = mx;
+        redi[((cur ^ 1) * C2_GT + gid) * C2_NW + 4 * w + tig] = mx;
         cur ^= 1;
+#ifdef C2_PROFILE
+        { unsigned q = pclk(); if (br < 0 && !helper) pd4 += q - pt0; pt0 = q; }
+#endif
         __syncthreads();
+#ifdef C2_PROFILE
+        { unsigned q = pclk(); if (br < 0 && !helper) pd5 += q - pt0; pt0 = q; }
+#endif
     }
+#ifdef C2_PROFILE
+    if (blockIdx.x < 2 * A.ntiles && tile == 0 && lane == 0 && !helper)
+        printf("c2prof dir %d warp %d rows %u: head %.1f dmma %.1f epi %.1f tail %.1f barrier %.1f cycles per plain row\n", dir, w, pn,
+               (double)pd1 / pn, (double)pd2 / pn, (double)pd3 / pn, (double)pd4 / pn, (double)pd5 / pn);
+#ifdef C2_PROFILE2
+    if (blockIdx.x < 2 * A.ntiles && tile == 0 && lane == 0 && !helper)
+        printf("c2prof2 dir %d warp %d: DMMA phase up to row block 4: %.1f, 8: %.1f, 14: %.1f, 25: %.1f\n", dir, w, (double)pe1 / pn,
+               (double)pe2 / pn, (double)pe3 / pn, (double)pd2 / pn);
+#endif
+#endif
 
     // ---- log normaliser of the forward sweep: log(sum of the last message) + ln2 * esum + sum_n max F[n]
     {
@@ -442,7 +494,7 @@ __device__ __forceinline__ void c2_sweep(const Chain2Args& A, unsigned char* sme
 #pragma unroll
             for (int h = 0; h < NBW; ++h) {
                 if (ok0[h]) {
-                    const double2 q = *reinterpret_cast<const double2*>(ul + upos[h]);
+                    const double2 q = *reinterpret_cast<const double2*>(ul + (upos0 + 64 * h));
                     sv += q.x + q.y;
                 }
             }
