@@ -268,27 +268,27 @@ __global__ void __launch_bounds__(NW * 32, 1) k_chain_mma3(Chain3Args A) {
                 }
                 cur_class = cls;
             }
-            // column block after column block: the epilogue of block h runs under the DMMAs of block h + 1, so only
-            // the last block's epilogue is exposed; the bookkeeping sits under the DMMAs of block 0
-            double pc0 = 0., pc1 = 0.;
+            // row blocks outermost: one A fragment (one shared-memory load instead of NBW) feeds the DMMAs of all NBW column
+            // blocks, and consecutive DMMAs belong to different accumulators by construction (chain_mma2.cu: ptxas had
+            // re-ordered a block's even / odd row blocks into two dependent chains).  Every accumulator sums the row blocks
+            // it summed before: same values bit for bit.
+            double acc[NBW][2][2];
 #pragma unroll
-            for (int h = 0; h < NBW; ++h) {
-                double c0 = 0., c1 = 0., e0 = 0., e1 = 0.;
+            for (int h = 0; h < NBW; ++h) acc[h][0][0] = acc[h][0][1] = acc[h][1][0] = acc[h][1][1] = 0.;
 #pragma unroll
-                for (int kb = 0; kb < KB; ++kb) {
-                    const double a = uc[kb * 32 + lane];
+            for (int kb = 0; kb < KB; ++kb) {
+                const double a = uc[kb * 32 + lane];
+#pragma unroll
+                for (int h = 0; h < NBW; ++h) {
                     const double bf = kb < KR ? ereg[h][kb < KR ? kb : 0] : esm[(h * KO + (kb < KR ? 0 : kb - KR)) * T];
-                    if (kb & 1) c3_dmma(e0, e1, a, bf);
-                    else c3_dmma(c0, c1, a, bf);
-                    if (h == 0 && kb == 2) chores(0);
-                    if (h == 0 && kb == 6) chores(1);
-                    if (h == 0 && kb == 12) chores(2);
-                    if (h > 0 && kb == 3) finish_block(h - 1, pc0, pc1);   // under this block's DMMAs
+                    c3_dmma(acc[h][kb & 1][0], acc[h][kb & 1][1], a, bf);
                 }
-                pc0 = c0 + e0;
-                pc1 = c1 + e1;
+                if (kb == 2) chores(0);
+                if (kb == 6) chores(1);
+                if (kb == 12) chores(2);
             }
-            finish_block(NBW - 1, pc0, pc1);
+#pragma unroll
+            for (int h = 0; h < NBW; ++h) finish_block(h, acc[h][0][0] + acc[h][1][0], acc[h][0][1] + acc[h][1][1]);
         } else {
             // ---- breakend row: per-fit matrix  E_g[i][j] = flipE[i][j] * prod_m wexp[g][m][tot_i[m] - tot_j[m]].
             // The per-fit factor depends on (i, j) only through the states' tumour-clone totals.  With the states grouped

@@ -1,6 +1,6 @@
 """Per-phase cycle counts of the chain kernel (a build with -DC2_PROFILE prints them): one 8-fit update on config 2."""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 exp, inits = bench.load_workload(sys.argv[1] if len(sys.argv) > 1 else 'config2')
