@@ -1353,10 +1353,63 @@ void rmx_launch_frame(cudaStream_t st, const RmxTables& T, const RmxDims& d, con
     else k_frame<<<grid, 256, 0, st>>>(T, d, P, g0, LL, q_ot, q_oa, q_sw, F, fexp, mF, dflags);
 }
 
+// k_qsums with the row in registers (S <= 32 KS): every load of the segment's row -- the posterior and the planes that are
+// summed -- is issued before the first multiply-add, instead of one (posterior, planes) group per trip of a loop whose
+// trips wait for their own loads.  Same products in the same order per lane, same warp reduction: same values.
+template <int KS>
+__global__ void __launch_bounds__(256) k_qsums_reg(RmxDims d, int g0, const double* __restrict__ LL_all,
+                                                   const double* __restrict__ post_all, double* __restrict__ A_all,
+                                                   int planes_all, const __grid_constant__ RmxFitSel sel) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.N) return;
+    const int g = RMX_FIT_SEL(sel);
+    const int planes = RMX_PLANES_SEL(sel, planes_all);
+    const int n = warp;
+    const int64_t NS = (int64_t)d.N * d.S;
+    const double* LL = LL_all + (int64_t)g * RMX_NTERM * NS + (int64_t)n * d.S;
+    const double* post = post_all + (int64_t)g * NS + (int64_t)n * d.S;
+    const int tmask6 = (planes & 1) | (planes & 2) | ((planes & 4) ? 12 : 0) | ((planes & 8) ? 48 : 0);
+    double p[KS], ll[RMX_NTERM][KS];
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+        const int s = lane + 32 * k;
+        p[k] = s < d.S ? post[s] : 0.;
+#pragma unroll
+        for (int t = 0; t < RMX_NTERM; ++t) ll[t][k] = (s < d.S && ((tmask6 >> t) & 1)) ? LL[(int64_t)t * NS + s] : 0.;
+    }
+    double a[RMX_NTERM];
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t) a[t] = 0.;
+#pragma unroll
+    for (int k = 0; k < KS; ++k)
+        if (lane + 32 * k < d.S) {
+#pragma unroll
+            for (int t = 0; t < RMX_NTERM; ++t)
+                if ((tmask6 >> t) & 1) a[t] = fma(p[k], ll[t][k], a[t]);
+        }
+#pragma unroll
+    for (int t = 0; t < RMX_NTERM; ++t)
+        if ((tmask6 >> t) & 1) a[t] = warp_sum(a[t]);
+    if (lane < RMX_NTERM && ((tmask6 >> lane) & 1)) {
+        double v = a[0];
+#pragma unroll
+        for (int t = 1; t < RMX_NTERM; ++t) v = lane == t ? a[t] : v;
+        A_all[((int64_t)g * d.N + n) * RMX_NTERM + lane] = v;
+    }
+}
+
 void rmx_launch_qsums(cudaStream_t st, const RmxDims& d, int g0, int gn, const double* LL, const double* post,
                       double* A, int planes, const RmxFitSel* sel) {
     if (d.N <= 0 || gn <= 0) return;
-    k_qsums<<<dim3(cdiv((int64_t)d.N * 32, 256), gn), 256, 0, st>>>(d, g0, LL, post, A, planes, sel ? *sel : g_no_sel);
+    const dim3 grid(cdiv((int64_t)d.N * 32, 256), gn);
+    const RmxFitSel& fs = sel ? *sel : g_no_sel;
+    const int ks = (d.S + 31) / 32;
+    if (ks <= 1) k_qsums_reg<1><<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
+    else if (ks == 2) k_qsums_reg<2><<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
+    else if (ks == 3) k_qsums_reg<3><<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
+    else if (ks == 4) k_qsums_reg<4><<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
+    else if (ks <= 6) k_qsums_reg<6><<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
+    else k_qsums<<<grid, 256, 0, st>>>(d, g0, LL, post, A, planes, fs);
 }
 
 int rmx_round_ok(const RmxDims& d) { return d.S <= 192; }
