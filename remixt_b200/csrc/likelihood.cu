@@ -932,17 +932,30 @@ __global__ void __launch_bounds__(256, 3) k_ell_sample(RmxTables T, RmxDims d, c
     const RmxParams& P = Pg[g];
     const bool tab_sm = d.S <= 128;
     // this thread's posterior entries first: two dependent global loads each (row list, then the posterior), in flight
-    // under the set-up below instead of inside the unit loop (up to RMX_ELL_PF units; further ones load in the loop)
+    // under the set-up below instead of inside the unit loop (up to RMX_ELL_PF units; further ones load in the loop).
+    // The second load is a cp.async into the thread's own shared-memory slots: nothing waits for it before the unit
+    // loop (a register array was spilled to local memory by the compiler, and each spill store waited for its load:
+    // 17 % of the kernel's stall samples, ncu source view).
     const int units = nr * d.S;
-    double ppf[RMX_ELL_PF];
+    __shared__ double pps[RMX_ELL_PF * 256];
+    {
+        int rn[RMX_ELL_PF];
 #pragma unroll
-    for (int k = 0; k < RMX_ELL_PF; ++k) {
-        const int idx = threadIdx.x + k * 256;
-        ppf[k] = 0.;
-        if (idx < units) {
-            const int r = idx / d.S, s = idx - r * d.S;
-            ppf[k] = post_all[((int64_t)g * d.N + rows_all[(int64_t)g * d.N + r0 + r]) * d.S + s];
+        for (int k = 0; k < RMX_ELL_PF; ++k) {
+            const int idx = threadIdx.x + k * 256;
+            rn[k] = idx < units ? rows_all[(int64_t)g * d.N + r0 + idx / d.S] : -1;
         }
+#pragma unroll
+        for (int k = 0; k < RMX_ELL_PF; ++k) {
+            const int idx = threadIdx.x + k * 256;
+            if (rn[k] >= 0) {
+                const int r = idx / d.S, s = idx - r * d.S;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(pps + k * 256 + threadIdx.x)),
+                             "l"(post_all + ((int64_t)g * d.N + rn[k]) * d.S + s)
+                             : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (tab_sm)
         for (int e = threadIdx.x; e < d.S * d.M * 2; e += blockDim.x) stab[e] = T.tab[e];
@@ -963,9 +976,43 @@ __global__ void __launch_bounds__(256, 3) k_ell_sample(RmxTables T, RmxDims d, c
         rowd[8 * RMX_ELL_MAXROWS + r] = q_sw_all[2 * gn];
         rowd[9 * RMX_ELL_MAXROWS + r] = q_sw_all[2 * gn + 1];
         rowi[r] = (T.tmask[gn] != 0 ? 1 : 0) | (T.amask[gn] != 0 ? 2 : 0) | ((int)T.nrm[2 * n] << 8) | ((int)T.nrm[2 * n + 1] << 16);
-        segconst_row_cached(P, x, y0 + y1, rowc + ((int64_t)g * (RMX_ELL_CHUNKS * RMX_ELL_MAXROWS) + r0 + r) * 3, planes,
-                            segc + r, RMX_ELL_MAXROWS);
     }
+    // the hoisted constants of the rows (segconst_row_cached: up to sixteen lgamma per row, four per term group), one
+    // lgamma per thread instead of all of a row's on one thread while the others wait at the barrier: thread (row r,
+    // group j, q) with the four q of a group on adjacent lanes, combined through shuffles by the lane q = 0 with the
+    // operations and the order of segconst_row_cached (same values)
+    {
+        const int r = threadIdx.x >> 4, j = (threadIdx.x >> 2) & 3, q = threadIdx.x & 3;
+        const bool on = r < nr && ((planes >> j) & 1);
+        double lg = 0.;
+        const double* rc = rowc + ((int64_t)g * (RMX_ELL_CHUNKS * RMX_ELL_MAXROWS) + r0 + (r < nr ? r : 0)) * 3;
+        if (on && (q < 2 || !P.normal_contamination)) {
+            const int n = rows_all[(int64_t)g * d.N + r0 + r];
+            const double base = j < 2 ? T.x[n] : T.y0[n] + T.y1[n];
+            const double par = j < 2 ? (q < 2 ? P.negbin_r[j] : P.negbin_hdel_r[j]) : (q < 2 ? P.betabin_M[j - 2] : P.betabin_loh_M[j - 2]);
+            lg = lgamma((q & 1) ? par : base + par);
+        }
+        const double lg1 = __shfl_down_sync(0xffffffffu, lg, 1), lg2 = __shfl_down_sync(0xffffffffu, lg, 2),
+                     lg3 = __shfl_down_sync(0xffffffffu, lg, 3);
+        if (on && q == 0) {
+            double* o = segc + r;
+            if (j < 2) {
+                const double lgx1 = rc[0];
+                o[(0 + j) * RMX_ELL_MAXROWS] = lg - lgx1 - lg1;
+                o[(2 + j) * RMX_ELL_MAXROWS] = P.normal_contamination ? 0. : (lg2 - lgx1 - lg3);
+            } else {
+                const int v = j - 2;
+                const double t = -lg + lg1;
+                const double tl = P.normal_contamination ? 0. : (-lg2 + lg3);
+#pragma unroll
+                for (int w = 0; w < 2; ++w) {
+                    o[(4 + v * 2 + w) * RMX_ELL_MAXROWS] = rc[1 + w] + t;
+                    o[(8 + v * 2 + w) * RMX_ELL_MAXROWS] = rc[1 + w] + tl;
+                }
+            }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");       // own slots only: no barrier needed for them
     rmx_logtab_init(ltab);      // includes the barrier
     double acc[1] = {0.};
     int flags = 0;
@@ -974,14 +1021,7 @@ __global__ void __launch_bounds__(256, 3) k_ell_sample(RmxTables T, RmxDims d, c
     for (int idx = threadIdx.x; idx < units; idx += blockDim.x, ++kpf) {
         const int r = idx / d.S, s = idx - r * d.S;
         const int n = rown[r], ri = rowi[r];
-        double p;
-        if (kpf < RMX_ELL_PF) {
-            p = ppf[0];
-#pragma unroll
-            for (int k = 1; k < RMX_ELL_PF; ++k) p = kpf == k ? ppf[k] : p;
-        } else {
-            p = post_all[((int64_t)g * d.N + n) * d.S + s];
-        }
+        const double p = kpf < RMX_ELL_PF ? pps[kpf * 256 + threadIdx.x] : post_all[((int64_t)g * d.N + n) * d.S + s];
         SegIn in;
         in.segc = segc + r;
         in.sstride = RMX_ELL_MAXROWS;
