@@ -394,6 +394,24 @@ __device__ __forceinline__ void rmx_exp_normalize2(double a, double b, double* o
     out[0] = dlt <= 0. ? big : small;
     out[1] = dlt <= 0. ? small : big;
 }
+// Two independent 2-way exp-normalisations, (a0, a1) -> oa and (b0, b1) -> ob, evaluated by a whole warp whose lanes all
+// hold the same arguments (k_round: every lane has the segment's sums) with ONE exp and ONE division instead of two
+// and four: lane bit 0 picks the problem, lane bit 1 the quotient (1 / z or t / z), four shuffles hand every lane all
+// four quotients.  Each value goes through the operations of rmx_exp_normalize2 on the same inputs: same bits.
+__device__ __forceinline__ void rmx_exp_normalize2_x2(double a0, double a1, double b0, double b1, int lane, double* oa,
+                                                      double* ob) {
+    const double dA = __dadd_rn(a1, -a0), dB = __dadd_rn(b1, -b0);
+    const double dl = (lane & 1) ? dB : dA;
+    const double t = exp(-fabs(dl));
+    const double z = __dadd_rn(1., t);
+    const double quo = __ddiv_rn((lane & 2) ? t : 1., z);
+    const double bigA = __shfl_sync(0xffffffffu, quo, 0), bigB = __shfl_sync(0xffffffffu, quo, 1);
+    const double smallA = __shfl_sync(0xffffffffu, quo, 2), smallB = __shfl_sync(0xffffffffu, quo, 3);
+    if (isnan(dA)) { oa[0] = oa[1] = dA; }
+    else { oa[0] = dA <= 0. ? bigA : smallA; oa[1] = dA <= 0. ? smallA : bigA; }
+    if (isnan(dB)) { ob[0] = ob[1] = dB; }
+    else { ob[0] = dB <= 0. ? bigB : smallB; ob[1] = dB <= 0. ? smallB : bigB; }
+}
 // arguments of the three 2-way factor updates from the sums A[0..6) (bpmodel.pyx:987-1042)
 // lp0 = log(1 - prior), lp1 = log(prior), evaluated once on the host
 __device__ __forceinline__ void rmx_q_args(int which, const double* A, double q0, double q1, double lp0, double lp1,

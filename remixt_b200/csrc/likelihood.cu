@@ -600,12 +600,13 @@ __global__ void __launch_bounds__(256, KS <= 4 ? 3 : 2) k_round(RmxTables T, Rmx
         ot[0] = q_ot_all[gn * 2]; ot[1] = q_ot_all[gn * 2 + 1];
         oa[0] = q_oa_all[gn * 2]; oa[1] = q_oa_all[gn * 2 + 1];
     } else {
+        // the two outlier factors do not depend on each other: one exp and one division for both (common.cuh)
+        double qb[2];
         rmx_q_args(1, a, 0., 0., lpt0, lpt1, qa);
-        exp_normalize2(qa[0], qa[1], ot);
         sw[0] = q_sw_all[gn * 2];
         sw[1] = q_sw_all[gn * 2 + 1];
-        rmx_q_args(2, a, sw[0], sw[1], lpa0, lpa1, qa);
-        exp_normalize2(qa[0], qa[1], oa);
+        rmx_q_args(2, a, sw[0], sw[1], lpa0, lpa1, qb);
+        rmx_exp_normalize2_x2(qa[0], qa[1], qb[0], qb[1], lane, ot, oa);
         if (lane == 0) {
             q_ot_all[gn * 2] = ot[0]; q_ot_all[gn * 2 + 1] = ot[1];
             q_oa_all[gn * 2] = oa[0]; q_oa_all[gn * 2 + 1] = oa[1];
