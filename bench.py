@@ -461,7 +461,10 @@ def gpu_arm(args):
                      'e_step_share': prof['e_step'] / wall, 'm_step_share': prof['m_step'] / wall,
                      'phases_s': dict((k, v) for k, v in prof.items() if isinstance(v, float)),
                      'mstep_seconds': prof.get('mstep_seconds'), 'selected_init': best, 'failed_inits': n_err,
-                     'inits': G_total, 'num_em_iter': NUM_EM_ITER, 'num_update_iter': NUM_UPDATE_ITER},
+                     'inits': G_total, 'num_em_iter': NUM_EM_ITER, 'num_update_iter': NUM_UPDATE_ITER,
+                     'sub_batches': int(prof.get('sub_batches', 1)),
+                     'note': 'sub_batches > 1: the grid runs as interleaved sub-batches on their own host threads and '
+                             'streams, whose phases overlap; phases_s and the shares are the largest of a sub-batch'},
         'roofline': roofline, 'kernels': kernels,
         'elbo_checksum': res['elbo_checksum'],
     }

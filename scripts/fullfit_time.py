@@ -21,7 +21,9 @@ def main():
     if fits:
         inits = inits[:fits]
     cfg = {'max_copy_number': 6, 'num_em_iter': em, 'num_update_iter': 5}
-    for rep in range(2):
+    if '--sub-batches' in args:
+        cfg['sub_batches'] = int(args[args.index('--sub-batches') + 1])
+    for rep in range(3):
         prof = {}
         t0 = time.perf_counter()
         res, best, errors = pipeline.fit_grid_batched(exp, dict(enumerate(inits)), cfg, mstep=mstep, profile=prof)

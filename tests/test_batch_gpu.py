@@ -155,3 +155,22 @@ def test_close_recycles_blocks_and_broadcast_assignment():
     for a, b in zip(r1, r3):
         assert np.array_equal(a, b)
     b3.close()
+
+
+def test_sub_batches_give_the_results_of_one_batch():
+    """fit_grid_batched with K interleaved sub-batches on K host threads and streams: a fit does not depend on the batch
+    it rides in, so every fit's result, the statistics and the selection are those of one batch, bit for bit."""
+    from remixt_b200 import pipeline
+    exp = util.load_experiment('small')
+    inits = dict((i, util.init_params('small', i)) for i in FITS[:7])
+    cfg = {'max_copy_number': 6, 'num_em_iter': 2, 'num_update_iter': 3}
+    res_1, best_1, err_1 = pipeline.fit_grid_batched(exp, inits, cfg, sub_batches=1)
+    prof = {}
+    res_k, best_k, err_k = pipeline.fit_grid_batched(exp, inits, cfg, sub_batches=3, profile=prof)
+    assert prof['sub_batches'] == 3
+    assert sorted(err_1) == sorted(err_k) and list(res_1) == list(res_k) and best_1 == best_k
+    for i in res_1:
+        assert res_1[i]['stats']['elbo'] == res_k[i]['stats']['elbo']
+        assert np.array_equal(res_1[i]['h'], res_k[i]['h'])
+        assert np.array_equal(res_1[i]['cn'], res_k[i]['cn'])
+        assert all(np.array_equal(res_1[i]['brk_cn'][k], res_k[i]['brk_cn'][k]) for k in res_1[i]['brk_cn'])
