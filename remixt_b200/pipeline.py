@@ -433,6 +433,14 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         errors.update(e)
     if not results:
         raise next(iter(errors.values()))
+    import time
+    t_res = time.perf_counter()
+    pending = [i for i in results if callable(results[i])]
+    from . import mstep as _mstep
+    with concurrent.futures.ThreadPoolExecutor(max(1, min(len(pending), _mstep._host_threads()))) as pool:
+        for i, r in zip(pending, pool.map(lambda i: results[i](), pending)):
+            results[i] = r
+    t_res = time.perf_counter() - t_res
     results = dict((i, results[i]) for i in ids if i in results)      # the caller's order
     stats = dict((i, results[i]['stats']) for i in results)
     best = select_solution(stats, config) if stats else None
@@ -445,6 +453,7 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
                 profile[key] = sum(vals)
             else:
                 profile[key] = max(vals)
+        profile['results'] = profile.get('results', 0.) + t_res
         profile['sub_batches'] = K
     return results, best, errors
 
@@ -584,7 +593,11 @@ def _fit_grid_one_batch(experiment, init_params_by_id, config, device=None, rand
 
     # index remaps and length-weighted statistics over N segments per fit: numpy releases the GIL inside them
     nt = min(len(todo), _mstep._host_threads()) if model_class is None else 1
-    if nt > 1:
+    if not select:
+        # a sub-batch of a grid: the caller assembles the results of all sub-batches in ONE pool (every group doing it
+        # on its own threads at the same moment oversubscribes the host), from host arrays only
+        done = [(lambda g=g: assemble(g)) for g in todo]
+    elif nt > 1:
         import concurrent.futures
         with concurrent.futures.ThreadPoolExecutor(nt) as pool:
             done = list(pool.map(assemble, todo))
@@ -599,8 +612,10 @@ def _fit_grid_one_batch(experiment, init_params_by_id, config, device=None, rand
     errors_by_id = dict((ids[g], e) for g, e in errors.items())
     if errors_by_id and not results:
         raise next(iter(errors_by_id.values()))
-    stats = dict((i, results[i]['stats']) for i in ids if i in results)
-    best = select_solution(stats, config) if (stats and select) else None
+    best = None
+    if select:
+        stats = dict((i, results[i]['stats']) for i in ids if i in results)
+        best = select_solution(stats, config) if stats else None
     prof['decode'] += t1 - t0
     prof['results'] += time.perf_counter() - t1
     return results, best, errors_by_id
