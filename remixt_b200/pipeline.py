@@ -409,7 +409,7 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         K = (min(SUB_BATCH_MAX, len(ids) // SUB_BATCH_MIN_FITS)
              if (model_class is None and trace is None and mstep == 'lockstep') else 1)
     K = max(1, min(int(K), len(ids)))
-    if K == 1 or model_class is not None or trace is not None:
+    if K == 1 or trace is not None:
         return _fit_grid_one_batch(experiment, init_params_by_id, config, device=device, random_seed=random_seed,
                                    init_ids=ids, mstep=mstep, num_threads=num_threads, profile=profile,
                                    model_class=model_class, trace=trace)
@@ -421,7 +421,7 @@ def fit_grid_batched(experiment, init_params_by_id, config, device=None, random_
         try:
             return _fit_grid_one_batch(experiment, init_params_by_id, config, device=device, random_seed=random_seed,
                                        init_ids=groups[k], mstep=mstep, num_threads=num_threads, profile=profs[k],
-                                       select=False)
+                                       model_class=model_class, select=False)
         except Exception as e:          # every fit of the group failed (or its batch could not be built)
             return {}, None, dict((i, e) for i in groups[k])
 

@@ -113,6 +113,30 @@ def test_host_grid_driver_full_fits_on_reference_model_are_bit_exact(ref_bpmodel
     assert r['stats']['proportion_divergent'] == float(g['proportion_divergent'][k])
 
 
+def test_sub_batches_merge_on_reference_model(ref_bpmodel):
+    """pipeline.fit_grid_batched(sub_batches=K): interleaved groups on their own host threads, merged in the caller's
+    order with one selection over all statistics -- on the compiled reference model (no GPU): every fit as in one batch,
+    the failing initialisation reported, `best` the same."""
+    from remixt_b200 import pipeline
+    g = util.golden('grid_small.npz')
+    exp = util.load_experiment('small')
+    failed = int(g['failed_ids'][0])
+    ids = [1, failed, 5]
+    inits = dict((i, util.init_params('small', i)) for i in ids)
+    cfg = {'max_copy_number': 6, 'num_em_iter': 1, 'num_update_iter': 2}
+    one = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']), model_class=ref_bpmodel.RemixtModel,
+                                    sub_batches=1)
+    prof = {}
+    two = pipeline.fit_grid_batched(exp, inits, cfg, random_seed=int(g['seed']), model_class=ref_bpmodel.RemixtModel,
+                                    sub_batches=2, profile=prof)
+    assert prof['sub_batches'] == 2
+    assert list(one[0]) == list(two[0]) and one[1] == two[1] and sorted(one[2]) == sorted(two[2])
+    for i in one[0]:
+        assert one[0][i]['stats'] == two[0][i]['stats']
+        assert np.array_equal(one[0][i]['cn'], two[0][i]['cn']) and np.array_equal(one[0][i]['h'], two[0][i]['h'])
+        assert one[0][i]['decisions'] == two[0][i]['decisions']
+
+
 def test_select_solution_rule():
     """analysis/pipeline.py:253-259: best ELBO among proportion_divergent < 0.5, else among all."""
     from remixt_b200 import pipeline
